@@ -1,0 +1,186 @@
+/*
+ * lkcuda.h — C ABI of the B200-native Felsenstein-pruning likelihood engine.
+ *
+ * This is the drop-in boundary for IQ-TREE 1.4.3's likelihood kernels.  The reference has no plugin
+ * ABI; its seam is four PhyloTree member-function pointers plus one allocator routine
+ * (phylotree.h:658-659, 697-698, 742-743, 979-980, 587-600), bound in
+ * PhyloTree::setLikelihoodKernel (phylotreesse.cpp:60-311) and called through the wrappers at
+ * phylotreesse.cpp:335-357.  Each entry point below names the reference function it replaces.
+ * INTEGRATION.md shows the shim a maintainer adds on the reference side.
+ *
+ * Conventions
+ *   - plain C, no C++/torch types; all functions return an int status (0 = LKCUDA_OK) and never throw;
+ *     lkcuda_last_error() gives the text the caller hands to outError() (tools.cpp:99-106).
+ *   - one opaque engine per PhyloTree (per partition under PhyloSuperTree); engines are independent and
+ *     may be driven concurrently from different host threads (phylosupertree.cpp:969-976).
+ *   - an engine owns ONE pattern shard [its P observed patterns (+ the U unobserved +ASC patterns,
+ *     replicated)] on ONE device.  Every returned sum (lnL, df, ddf) is additive over shards: the
+ *     caller adds the shards' values (host sum, or an NCCL all-reduce on lkcuda_result_device_ptr()).
+ *   - "vector" v = one partial-likelihood buffer of the reference's central_partial_lh arena
+ *     (phylotree.cpp:863-974: central_partial_lh + indexlh*block_size) together with its scale_num
+ *     row (central_scale_num + indexlh*scale_block_size).  Layout inside a vector is the reference's:
+ *     partial_lh[ptn][blk][state] doubles (blk = category, or mixture*ncat + category) and
+ *     scale_num[ptn] as int16 (UBYTE = short, phylonode.h:17).
+ *   - a child/end of a branch is either a vector index (>= 0) or a tip: LKCUDA_TIP(taxon_id) < 0.
+ *   - all arithmetic is FP64.
+ */
+#ifndef LKCUDA_H
+#define LKCUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LKCUDA_ABI_VERSION 1
+
+enum {
+    LKCUDA_OK = 0,
+    LKCUDA_ERR_ARG = 1,      /* invalid argument                                   */
+    LKCUDA_ERR_CUDA = 2,     /* a CUDA runtime call or kernel failed               */
+    LKCUDA_ERR_STATE = 3,    /* call order violated (e.g. derv before theta)       */
+    LKCUDA_ERR_NOMEM = 4,    /* host or device allocation failed                   */
+    LKCUDA_ERR_NODEVICE = 5  /* no CUDA device / extension built without a device  */
+};
+
+/* flags of lkcuda_config.flags */
+enum {
+    /* scaling test is `lh_max < 2^-256` only — the mixture and fused mix-rate families
+       (phylokernelmixture.h:356,439; phylokernelmixrate.h:344,428).  Without it the plain family's
+       `&& ptn_invar[ptn] == 0.0` condition applies (phylokernel.h:381,463). */
+    LKCUDA_FLAG_SCALE_IGNORES_INVAR = 1,
+    /* the generic (non-SIMD) kernels' extra `lh_max == 0.0` branch: refill the block with
+       tip_partial_lh[STATE_UNKNOWN], scale_num += 4 (phylotreesse.cpp:777-789, 895-907, 976-988) */
+    LKCUDA_FLAG_ZERO_GUARD = 2,
+    /* also fill _pattern_lh_cat in every branch-lnL call (the generic kernels always do,
+       phylotreesse.cpp:1198,1225-1237; the SIMD kernels never do) */
+    LKCUDA_FLAG_PATTERN_LH_CAT = 4
+};
+
+#define LKCUDA_TIP(taxon) (-1 - (int32_t)(taxon))
+#define LKCUDA_IS_TIP(id) ((id) < 0)
+#define LKCUDA_TIP_TAXON(id) (-1 - (id))
+
+typedef struct lkcuda_engine lkcuda_engine;
+
+typedef struct lkcuda_config {
+    int32_t device;         /* CUDA device ordinal                                                    */
+    int32_t nstates;        /* S = aln->num_states (4 DNA, 20 AA, 64 codon, any other -> generic path) */
+    int32_t nblocks;        /* K = blocks per pattern: ncat (plain, fused mix-rate) or nmix*ncat       */
+    int32_t neigen;         /* E = eigensystems: 1 (plain), ncat (fused), nmix (mixture)               */
+    int32_t ntaxa;          /* leaves = rows of the tip-state matrix                                   */
+    int32_t state_unknown;  /* aln->STATE_UNKNOWN (18 DNA, 23 AA, S otherwise; alignment.cpp:470-472)  */
+    int32_t nvec;           /* vectors in the arena (central + nni buffers, phylotree.cpp:852-894)     */
+    int32_t flags;          /* LKCUDA_FLAG_*                                                           */
+    int64_t nptn;           /* P = observed patterns of this shard                                     */
+    int64_t nunobs;         /* U = model_factory->unobserved_ptns.size() (+ASC), 0 otherwise           */
+    int64_t nsite;          /* sites represented by this shard (= sum of its ptn_freq); +ASC term only */
+} lkcuda_config;
+
+/* one node of the post-order schedule: replaces one invocation of
+   PhyloTree::computePartialLikelihoodEigenSIMD (phylokernel.h:71-483) and its mixture / mix-rate /
+   generic twins (phylokernelmixture.h:21, phylokernelmixrate.h:23, phylotreesse.cpp:581/1350/2039)
+   for a bifurcating node.  The caller has already ordered a leaf child first (phylokernel.h:116-121). */
+typedef struct lkcuda_partial_op {
+    int32_t dst;            /* vector receiving L_dad                          */
+    int32_t left;           /* vector (>=0) or LKCUDA_TIP(taxon)               */
+    int32_t right;          /* vector (>=0) or LKCUDA_TIP(taxon)               */
+    int32_t reserved;
+    double  len_left;       /* left->length                                    */
+    double  len_right;      /* right->length                                   */
+} lkcuda_partial_op;
+
+/* results of the reductions, all additive over shards except [LKCUDA_R_PROB_CONST] */
+enum {
+    LKCUDA_R_LNL = 0,        /* tree_lh of the shard (scale factors and +ASC term included)  */
+    LKCUDA_R_DF = 1,
+    LKCUDA_R_DDF = 2,
+    LKCUDA_R_PROB_CONST = 3, /* +ASC: sum of unobserved-pattern likelihoods (replicated)     */
+    LKCUDA_R_NREPAIRED = 4,  /* patterns whose log-lh was NaN/Inf and got the repair value   */
+    LKCUDA_R_SCALE_SUM = 5,  /* lh_scale_factor(node)+lh_scale_factor(dad) of the shard      */
+    LKCUDA_NRESULT = 8
+};
+
+/* ---- life cycle : PhyloTree::initializeAllPartialLh / deleteAllPartialLh (phylotree.cpp:667-987, 718) ---- */
+int lkcuda_device_count(int32_t *count);
+int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out);
+int lkcuda_destroy(lkcuda_engine *e);
+const char *lkcuda_last_error(const lkcuda_engine *e);   /* e may be NULL: error of the last failed create */
+/* bytes of device memory the engine holds (getMemoryRequired analogue, phylotree.cpp:995-1024) */
+int lkcuda_memory_bytes(const lkcuda_engine *e, uint64_t *bytes);
+/* run on the caller's CUDA stream (cudaStream_t as void*); NULL = the engine's own stream */
+int lkcuda_set_stream(lkcuda_engine *e, void *cuda_stream);
+int lkcuda_synchronize(lkcuda_engine *e);
+
+/* ---- inputs ---- */
+/* states[taxon][ptn], ptn < P+U: aln->at(ptn)[taxon] then model_factory->unobserved_ptns (phylokernel.h:237-244) */
+int lkcuda_set_tip_states(lkcuda_engine *e, const uint8_t *states);
+/* PhyloTree::computePtnFreq / computePtnInvar outputs (phylotreesse.cpp:531-569): ptn_freq[P], ptn_invar[P+U] */
+int lkcuda_set_pattern_weights(lkcuda_engine *e, const double *ptn_freq, const double *ptn_invar);
+/* model->getEigenvalues/getEigenvectors/getInverseEigenvectors (model/modelsubst.h:248-258; mixtures
+   concatenated, model/modelmixture.cpp:1239-1262): eval[E*S], evec[E*S*S], inv_evec[E*S*S];
+   per block: its eigensystem, site_rate->getRate(c), and the weight site_rate->getProp(c) (* prop[m]);
+   tip_partial_lh[(state_unknown+1)][E][S] from computeTipPartialLikelihood (phylotreesse.cpp:359-529). */
+int lkcuda_set_model(lkcuda_engine *e, const double *eval, const double *evec, const double *inv_evec,
+                     const int32_t *blk_eigen, const double *blk_rate, const double *blk_weight,
+                     const double *tip_partial_lh);
+
+/* ---- partial likelihoods: PhyloTree::computePartialLikelihood (phylotreesse.cpp:335) ---- */
+/* ops are in post-order; level_start[nlevels+1] partitions them into groups of mutually independent
+   nodes (one launch per level).  Asynchronous: enqueues on the engine stream and returns. */
+int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t nops,
+                         const int32_t *level_start, int32_t nlevels);
+/* multifurcating node (degree > 3) — the generic kernel's path (phylotreesse.cpp:702-806) */
+int lkcuda_partial_multi(lkcuda_engine *e, int32_t dst, int32_t nchild, const int32_t *child,
+                         const double *child_len);
+
+/* ---- branch log-likelihood: PhyloTree::computeLikelihoodBranch (phylotreesse.cpp:339) ----
+   dad = vector or tip, node = vector (caller swapped so that only dad may be a leaf, phylokernel.h:739-746);
+   writes _pattern_lh (and _pattern_lh_cat with LKCUDA_FLAG_PATTERN_LH_CAT) on the device.
+   result == NULL: enqueue only (read later with lkcuda_read_result); else synchronises and fills
+   result[LKCUDA_NRESULT]. */
+int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result);
+
+/* ---- derivatives: PhyloTree::computeLikelihoodDerv (phylotreesse.cpp:344) split at its theta_computed flag ---- */
+/* theta_all = L_node * L_dad (phylokernel.h:535-579) */
+int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node);
+/* df, ddf at branch length len from theta_all (phylokernel.h:521-532, 599-725) */
+int lkcuda_derv(lkcuda_engine *e, double len, double *result);
+/* PhyloTree::computeLikelihoodFromBuffer (phylotreesse.cpp:349; phylokernel.h:1023-1192) */
+int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result);
+/* Optimization::minimizeNewton (optimization.cpp:388-465) driven on the device over theta_all:
+   same step sequence, one launch instead of one launch + one read-back per Newton step.
+   out[4]: [0] = optx, [1] = d2l, [2] = number of computeFuncDerv evaluations, [3] = the last length
+   evaluated (where the reference leaves current_it->length).  Single shard only. */
+int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, double xacc,
+                         int32_t max_nr_step, double *out);
+
+/* results of the last enqueued reduction (synchronises) / their device address (for NCCL) */
+int lkcuda_read_result(lkcuda_engine *e, double *result);
+int lkcuda_result_device_ptr(lkcuda_engine *e, void **dev_ptr);
+
+/* ---- host-visible mirrors (buffers host code reads or writes) ---- */
+int lkcuda_fetch_pattern_lh(lkcuda_engine *e, double *pattern_lh /*[P]*/);
+int lkcuda_fetch_pattern_lh_cat(lkcuda_engine *e, double *pattern_lh_cat /*[P][K]*/);
+int lkcuda_fetch_vector(lkcuda_engine *e, int32_t vec, double *partial_lh /*[(P+U)*K*S] or NULL*/,
+                        int16_t *scale_num /*[P+U] or NULL*/);
+int lkcuda_store_vector(lkcuda_engine *e, int32_t vec, const double *partial_lh, const int16_t *scale_num);
+int lkcuda_fetch_theta(lkcuda_engine *e, double *theta /*[(P+U)*K*S]*/);
+/* lh_scale_factor of a vector = sum_p LOG_SCALING_THRESHOLD * ptn_freq[p] * scale_num[p] (phylokernel.h:389,395) */
+int lkcuda_vector_scale_factor(lkcuda_engine *e, int32_t vec, double *lh_scale_factor);
+/* raw device addresses of a vector (PhyloNeighbor::partial_lh / scale_num become these) */
+int lkcuda_vector_device_ptr(lkcuda_engine *e, int32_t vec, void **partial_lh, void **scale_num);
+
+/* ---- instrumentation ---- */
+/* kernels launched by this engine since creation (bench.py's gpu_launches) */
+int lkcuda_launch_count(const lkcuda_engine *e, uint64_t *count);
+/* algorithmic bytes moved by those launches, for the roofline */
+int lkcuda_algorithmic_bytes(const lkcuda_engine *e, uint64_t *bytes);
+int lkcuda_reset_counters(lkcuda_engine *e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LKCUDA_H */

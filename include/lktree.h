@@ -1,0 +1,80 @@
+/*
+ * lktree.h — flat C entry points of the host-side PhyloTree mirror (iq-tree_b200/csrc/lk_phylotree.*).
+ *
+ * The mirror keeps the reference's PhyloTree likelihood API (same names, argument meaning and control
+ * flow: phylotree.cpp:1031 computeLikelihood, :2148 optimizeOneBranch, :2252 optimizeAllBranches,
+ * phylotreesse.cpp:335-357 the four kernel wrappers) and calls the device through include/lkcuda.h.
+ * These functions exist so that non-C++ hosts (the ctypes tests, bench.py) drive exactly that code.
+ * Every function returns 0 on success, 1 on error (text in lktree_last_error()).
+ * Nodes are addressed by their reference ids: leaves = alignment sequence index, internal nodes as
+ * numbered by MTree::initializeTree (mtree.cpp:561-583) or as given in an adjacency fixture.
+ */
+#ifndef LKTREE_H
+#define LKTREE_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include "lkcuda.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct lktree lktree;
+
+/* sum `n` doubles over the ranks of a one-process-per-GPU job: in place in `dev_buf` (device memory,
+   host_buf == NULL) or in `host_buf` (dev_buf == NULL) */
+typedef void (*lktree_allreduce_fn)(void *user, double *host_buf, void *dev_buf, int n);
+
+lktree *lktree_create(void);
+void lktree_destroy(lktree *h);
+const char *lktree_last_error(const lktree *h);
+
+/* inputs: the pattern-compressed alignment (Alignment : vector<Pattern>, alignment.h:50), taxon-major */
+int lktree_set_alignment(lktree *h, int32_t ntaxa, int64_t nptn, const uint8_t *states, const double *ptn_freq,
+                         const char *const *names, int32_t seq_type, int32_t nstates, int32_t state_unknown);
+int lktree_set_const_char(lktree *h, const int32_t *const_char);             /* Pattern::const_char */
+int lktree_set_unobserved(lktree *h, const uint8_t *unobs, int32_t n);       /* +ASC */
+/* family: 0 plain, 1 fused mix-rate, 2 mixture; eigensystems concatenated as ModelMixture does */
+int lktree_set_model(lktree *h, int32_t family, int32_t ncat, int32_t nmix, const double *eval, const double *evec,
+                     const double *inv_evec, const double *rates, const double *props, const double *mixprops,
+                     const double *state_freq, double p_invar);
+int lktree_read_newick(lktree *h, const char *newick);
+int lktree_read_adjacency(lktree *h, const char *text);
+int lktree_get_tree_string(lktree *h, char *buf, size_t buflen);
+
+/* placement */
+int lktree_set_devices(lktree *h, const int32_t *devices, int32_t n);        /* in-process shards, one per device */
+int lktree_set_process_shard(lktree *h, int32_t rank, int32_t world);        /* one process per GPU */
+int lktree_set_allreduce(lktree *h, lktree_allreduce_fn fn, void *user);
+int lktree_set_stream(lktree *h, void *cuda_stream);
+int lktree_set_params(lktree *h, double min_branch_length, double max_branch_length, int32_t device_newton, int32_t generic_kernel);
+
+/* PhyloTree API */
+int lktree_initialize_all_partial_lh(lktree *h);
+int lktree_delete_all_partial_lh(lktree *h);
+int lktree_clear_all_partial_lh(lktree *h);
+int lktree_compute_likelihood(lktree *h, double *lnl, double *pattern_lh /* [local P] or NULL */);
+int lktree_compute_likelihood_branch(lktree *h, int32_t node1, int32_t node2, double *lnl);
+int lktree_compute_likelihood_derv(lktree *h, int32_t node1, int32_t node2, int32_t reset_theta, double *df, double *ddf);
+int lktree_compute_likelihood_from_buffer(lktree *h, double *lnl);
+int lktree_optimize_one_branch(lktree *h, int32_t node1, int32_t node2, int32_t max_nr_step, double *len);
+int lktree_optimize_all_branches(lktree *h, int32_t iterations, double tolerance, int32_t max_nr_step, double *lnl);
+
+/* inspection */
+int lktree_set_branch_length(lktree *h, int32_t node1, int32_t node2, double len);
+int lktree_get_branch_length(lktree *h, int32_t node1, int32_t node2, double *len);
+int lktree_get_traversal(lktree *h, int32_t *pairs, int32_t capacity, int32_t *count);
+int lktree_branch_vector(lktree *h, int32_t from, int32_t to, int32_t *vec, int32_t *computed);
+int lktree_root_branch(lktree *h, int32_t *from, int32_t *to);
+int lktree_fetch_tip_partial_lh(lktree *h, double *out, int64_t capacity, int64_t *count);
+int lktree_fetch_ptn_invar(lktree *h, double *out);
+int lktree_fetch_pattern_lh_cat(lktree *h, double *out);
+lkcuda_engine *lktree_engine(lktree *h, int32_t i);
+int lktree_local_patterns(lktree *h, int64_t *begin, int64_t *end);
+uint64_t lktree_num_partial_lh_computations(lktree *h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

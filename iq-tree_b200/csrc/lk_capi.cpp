@@ -1,0 +1,195 @@
+/*
+ * lk_capi.cpp — flat C entry points over lk::PhyloTree (the host mirror of the reference's PhyloTree
+ * likelihood API) so that Python (ctypes) tests and bench.py drive exactly the code a C++ host would.
+ * Declared in include/lktree.h.  C++ exceptions (the mirror's outError analogue) become status 1 +
+ * lktree_last_error().
+ */
+#include "lk_phylotree.h"
+#include "../../include/lktree.h"
+#include <cstring>
+#include <map>
+
+using lk::PhyloTree;
+using lk::Node;
+using lk::Neighbor;
+
+struct lktree {
+    PhyloTree tree;
+    std::string err;
+    std::string text;
+};
+
+#define LK_TRY(h) try {
+#define LK_CATCH(h) } catch (const std::exception &ex) { (h)->err = ex.what(); return 1; } catch (...) { (h)->err = "unknown error"; return 1; } return 0;
+
+static Node *nodeById(lktree *h, int id) {
+    for (size_t i = 0; i < h->tree.allNodes.size(); i++) if (h->tree.allNodes[i]->id == id) return h->tree.allNodes[i];
+    throw std::runtime_error("no node with id " + std::to_string(id));
+}
+
+extern "C" {
+
+lktree *lktree_create(void) { return new (std::nothrow) lktree(); }
+void lktree_destroy(lktree *h) { delete h; }
+const char *lktree_last_error(const lktree *h) { return h ? h->err.c_str() : "null handle"; }
+
+int lktree_set_alignment(lktree *h, int32_t ntaxa, int64_t nptn, const uint8_t *states, const double *ptn_freq,
+                         const char *const *names, int32_t seq_type, int32_t nstates, int32_t state_unknown) {
+    LK_TRY(h)
+    std::vector<std::string> nm;
+    for (int i = 0; i < ntaxa; i++) nm.push_back(names ? names[i] : ("t" + std::to_string(i)));
+    h->tree.setAlignment(ntaxa, nptn, states, ptn_freq, nm, seq_type, nstates, state_unknown);
+    LK_CATCH(h)
+}
+
+int lktree_set_const_char(lktree *h, const int32_t *const_char) { LK_TRY(h) h->tree.setConstChar(const_char); LK_CATCH(h) }
+
+int lktree_set_unobserved(lktree *h, const uint8_t *unobs, int32_t n) {
+    LK_TRY(h) h->tree.setUnobservedPatterns(std::vector<uint8_t>(unobs, unobs + n)); LK_CATCH(h)
+}
+
+int lktree_set_model(lktree *h, int32_t family, int32_t ncat, int32_t nmix, const double *eval, const double *evec,
+                     const double *inv_evec, const double *rates, const double *props, const double *mixprops,
+                     const double *state_freq, double p_invar) {
+    LK_TRY(h) h->tree.setModel(family, ncat, nmix, eval, evec, inv_evec, rates, props, mixprops, state_freq, p_invar); LK_CATCH(h)
+}
+
+int lktree_read_newick(lktree *h, const char *newick) { LK_TRY(h) h->tree.readTreeString(newick); LK_CATCH(h) }
+int lktree_read_adjacency(lktree *h, const char *text) { LK_TRY(h) h->tree.readAdjacency(text); LK_CATCH(h) }
+
+int lktree_get_tree_string(lktree *h, char *buf, size_t buflen) {
+    LK_TRY(h)
+    std::string s = h->tree.getTreeString();
+    if (s.size() + 1 > buflen) throw std::runtime_error("buffer too small");
+    memcpy(buf, s.c_str(), s.size() + 1);
+    LK_CATCH(h)
+}
+
+int lktree_set_devices(lktree *h, const int32_t *devices, int32_t n) {
+    LK_TRY(h) h->tree.setDevices(std::vector<int>(devices, devices + n)); LK_CATCH(h)
+}
+int lktree_set_process_shard(lktree *h, int32_t rank, int32_t world) { LK_TRY(h) h->tree.setProcessShard(rank, world); LK_CATCH(h) }
+int lktree_set_allreduce(lktree *h, lktree_allreduce_fn fn, void *user) { LK_TRY(h) h->tree.setAllReduce(fn, user); LK_CATCH(h) }
+int lktree_set_stream(lktree *h, void *stream) { LK_TRY(h) h->tree.setStream(stream); LK_CATCH(h) }
+
+int lktree_set_params(lktree *h, double min_branch_length, double max_branch_length, int32_t device_newton, int32_t generic_kernel) {
+    LK_TRY(h)
+    h->tree.min_branch_length = min_branch_length;
+    h->tree.max_branch_length = max_branch_length;
+    h->tree.device_newton = device_newton != 0;
+    if ((generic_kernel != 0) != h->tree.generic_kernel) { h->tree.generic_kernel = generic_kernel != 0; h->tree.deleteAllPartialLh(); }
+    LK_CATCH(h)
+}
+
+int lktree_initialize_all_partial_lh(lktree *h) { LK_TRY(h) h->tree.initializeAllPartialLh(); LK_CATCH(h) }
+int lktree_delete_all_partial_lh(lktree *h) { LK_TRY(h) h->tree.deleteAllPartialLh(); LK_CATCH(h) }
+int lktree_clear_all_partial_lh(lktree *h) { LK_TRY(h) h->tree.clearAllPartialLH(); LK_CATCH(h) }
+
+int lktree_compute_likelihood(lktree *h, double *lnl, double *pattern_lh) {
+    LK_TRY(h) *lnl = h->tree.computeLikelihood(pattern_lh); LK_CATCH(h)
+}
+
+int lktree_compute_likelihood_branch(lktree *h, int32_t node1, int32_t node2, double *lnl) {
+    LK_TRY(h)
+    Node *n1 = nodeById(h, node1), *n2 = nodeById(h, node2);
+    Neighbor *nb = n1->findNeighbor(n2);
+    if (!nb) throw std::runtime_error("nodes are not adjacent");
+    *lnl = h->tree.computeLikelihoodBranch(nb, n1);
+    LK_CATCH(h)
+}
+
+int lktree_compute_likelihood_derv(lktree *h, int32_t node1, int32_t node2, int32_t reset_theta, double *df, double *ddf) {
+    LK_TRY(h)
+    Node *n1 = nodeById(h, node1), *n2 = nodeById(h, node2);
+    Neighbor *nb = n1->findNeighbor(n2);
+    if (!nb) throw std::runtime_error("nodes are not adjacent");
+    if (reset_theta) h->tree.theta_computed = false;
+    h->tree.current_it = nb;
+    h->tree.current_it_back = n2->findNeighbor(n1);
+    h->tree.computeLikelihoodDerv(nb, n1, *df, *ddf);
+    LK_CATCH(h)
+}
+
+int lktree_compute_likelihood_from_buffer(lktree *h, double *lnl) { LK_TRY(h) *lnl = h->tree.computeLikelihoodFromBuffer(); LK_CATCH(h) }
+
+int lktree_set_branch_length(lktree *h, int32_t node1, int32_t node2, double len) {
+    LK_TRY(h)
+    Node *n1 = nodeById(h, node1), *n2 = nodeById(h, node2);
+    Neighbor *a = n1->findNeighbor(n2), *b = n2->findNeighbor(n1);
+    if (!a || !b) throw std::runtime_error("nodes are not adjacent");
+    a->length = b->length = len;
+    LK_CATCH(h)
+}
+
+int lktree_optimize_one_branch(lktree *h, int32_t node1, int32_t node2, int32_t max_nr_step, double *len) {
+    LK_TRY(h)
+    Node *n1 = nodeById(h, node1), *n2 = nodeById(h, node2);
+    h->tree.optimizeOneBranch(n1, n2, true, max_nr_step);
+    if (len) *len = n1->findNeighbor(n2)->length;
+    LK_CATCH(h)
+}
+
+int lktree_optimize_all_branches(lktree *h, int32_t iterations, double tolerance, int32_t max_nr_step, double *lnl) {
+    LK_TRY(h) *lnl = h->tree.optimizeAllBranches(iterations, tolerance, max_nr_step); LK_CATCH(h)
+}
+
+int lktree_get_traversal(lktree *h, int32_t *pairs, int32_t capacity, int32_t *count) {
+    LK_TRY(h)
+    std::vector<Node*> a, b;
+    h->tree.computeBestTraversal(a, b);
+    *count = (int32_t)a.size();
+    for (size_t i = 0; i < a.size() && (int32_t)i < capacity; i++) { pairs[2 * i] = a[i]->id; pairs[2 * i + 1] = b[i]->id; }
+    LK_CATCH(h)
+}
+
+int lktree_get_branch_length(lktree *h, int32_t node1, int32_t node2, double *len) {
+    LK_TRY(h)
+    Neighbor *a = nodeById(h, node1)->findNeighbor(nodeById(h, node2));
+    if (!a) throw std::runtime_error("nodes are not adjacent");
+    *len = a->length;
+    LK_CATCH(h)
+}
+
+int lktree_branch_vector(lktree *h, int32_t from, int32_t to, int32_t *vec, int32_t *computed) {
+    LK_TRY(h)
+    Neighbor *a = nodeById(h, from)->findNeighbor(nodeById(h, to));
+    if (!a) throw std::runtime_error("nodes are not adjacent");
+    *vec = a->vec;
+    if (computed) *computed = a->partial_lh_computed & 1;
+    LK_CATCH(h)
+}
+
+int lktree_root_branch(lktree *h, int32_t *from, int32_t *to) {
+    LK_TRY(h)
+    if (!h->tree.current_it) throw std::runtime_error("no current branch");
+    *from = h->tree.current_it_back->node->id;
+    *to = h->tree.current_it->node->id;
+    LK_CATCH(h)
+}
+
+int lktree_fetch_tip_partial_lh(lktree *h, double *out, int64_t capacity, int64_t *count) {
+    LK_TRY(h)
+    h->tree.computeTipPartialLikelihood();
+    *count = (int64_t)h->tree.tip_partial_lh.size();
+    if (*count <= capacity) memcpy(out, &h->tree.tip_partial_lh[0], (size_t)*count * 8);
+    LK_CATCH(h)
+}
+
+int lktree_fetch_ptn_invar(lktree *h, double *out) {
+    LK_TRY(h)
+    h->tree.computeTipPartialLikelihood();
+    memcpy(out, &h->tree.ptn_invar[0], h->tree.ptn_invar.size() * 8);
+    LK_CATCH(h)
+}
+
+int lktree_fetch_pattern_lh_cat(lktree *h, double *out) { LK_TRY(h) h->tree.computePatternLhCat(out); LK_CATCH(h) }
+
+lkcuda_engine *lktree_engine(lktree *h, int32_t i) { return h ? h->tree.engine((size_t)i) : NULL; }
+
+int lktree_local_patterns(lktree *h, int64_t *begin, int64_t *end) {
+    LK_TRY(h) *begin = h->tree.localPatternBegin(); *end = h->tree.localPatternEnd(); LK_CATCH(h)
+}
+
+uint64_t lktree_num_partial_lh_computations(lktree *h) { return h ? h->tree.num_partial_lh_computations : 0; }
+
+}  // extern "C"

@@ -1,0 +1,807 @@
+/*
+ * lk_phylotree.cpp — host-side mirror of the reference's PhyloTree likelihood API over the lkcuda C ABI.
+ * See lk_phylotree.h for the reference file:line of every mirrored function.
+ *
+ * What is different from the reference by design (B200-first):
+ *   - computePartialLikelihood does not compute: its post-order recursion (same dirty-bit and
+ *     leaf-left rules) only RECORDS nodes; the recorded schedule is levelised and handed to the device
+ *     in one lkcuda_partial_batch call (one launch per tree level instead of one per node).
+ *   - lh_scale_factor is not carried on the host: the device derives it from scale_num.
+ *   - patterns are split into shards (one engine per device / per process); lnL, df, ddf are sums.
+ */
+#include "lk_phylotree.h"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <sstream>
+
+namespace lk {
+
+#define FOR_NEI(nd_, dad_, it) \
+    for (std::vector<Neighbor*>::iterator it = (nd_)->neighbors.begin(); it != (nd_)->neighbors.end(); ++it) \
+        if ((*it)->node != (dad_))
+
+PhyloTree::PhyloTree()
+    : leafNum(0), nodeNum(0), root(NULL), min_branch_length(1e-6), max_branch_length(100.0),
+      device_newton(false), generic_kernel(false), current_it(NULL), current_it_back(NULL),
+      theta_computed(false), num_partial_lh_computations(0), nstates(0), ncat(1), nmix(1), family(FAMILY_PLAIN),
+      state_unknown(0), seq_type(SEQ_DNA), ntaxa(0), nptn(0), nunobs(0), nsite(0), p_invar_(0.0),
+      proc_rank_(0), proc_world_(1), allreduce_(NULL), allreduce_user_(NULL), stream_(NULL),
+      ptn_begin_(0), ptn_end_(0), tip_partial_lh_computed_(false), inputs_uploaded_(false), nvec_(0) {}
+
+PhyloTree::~PhyloTree() {
+    deleteAllPartialLh();
+    for (size_t i = 0; i < allNodes.size(); i++) {
+        for (size_t k = 0; k < allNodes[i]->neighbors.size(); k++) delete allNodes[i]->neighbors[k];
+        delete allNodes[i];
+    }
+}
+
+void PhyloTree::check(int rc, lkcuda_engine *e, const char *what) {
+    if (rc == LKCUDA_OK) return;
+    std::string msg = std::string(what) + ": " + lkcuda_last_error(e) + " (status " + std::to_string(rc) + ")";
+    throw std::runtime_error(msg);   // the reference's outError(): fatal (tools.cpp:99-106)
+}
+
+/* ------------------------------------------------------------------ tree ------------------------------------------------------------------ */
+
+Node *PhyloTree::newNode() {
+    Node *n = new Node();
+    allNodes.push_back(n);
+    return n;
+}
+
+static bool isNewickToken(char ch) { return ch == ':' || ch == ';' || ch == ',' || ch == ')' || ch == '(' || ch == '[' || ch == ']'; }
+static bool isControl(char ch) { return ch <= 32; }
+
+static char nextChar(const std::string &s, size_t &pos) {
+    // skip whitespace and [comments] (mtree.cpp readNextChar)
+    while (pos < s.size()) {
+        char ch = s[pos++];
+        if (isControl(ch)) continue;
+        if (ch == '[') {
+            while (pos < s.size() && s[pos] != ']') pos++;
+            if (pos < s.size()) pos++;
+            continue;
+        }
+        return ch;
+    }
+    return 0;
+}
+
+/* recursive-descent Newick reader with the reference's neighbour order: children in file order, then the
+   parent (mtree.cpp:586-680); `ch` convention: s[pos-1] is the current character */
+void PhyloTree::parseNewick(const std::string &s, size_t &pos, Node *&node, double &branch_len) {
+    branch_len = -1.0;
+    node = newNode();
+    char ch = s[pos - 1];
+    if (ch == '(') {
+        ch = nextChar(s, pos);
+        while (ch != ')' && ch != 0) {
+            Node *child = NULL;
+            double brlen;
+            parseNewick(s, pos, child, brlen);
+            node->neighbors.push_back(new Neighbor(child, brlen));
+            child->neighbors.push_back(new Neighbor(node, brlen));
+            ch = s[pos - 1];
+            if (ch == ',') ch = nextChar(s, pos);
+            else if (ch != ')') throw std::runtime_error(std::string("Expecting ')', but found '") + ch + "' instead");
+        }
+        if (ch == 0) throw std::runtime_error("Expecting ')', but end of file instead");
+        ch = nextChar(s, pos);
+    }
+    std::string name;
+    char end_ch = (ch == '\'' || ch == '"') ? ch : 0;
+    while (ch != 0) {
+        if (end_ch == 0 && (isNewickToken(ch) || isControl(ch))) break;
+        name += ch;
+        ch = pos < s.size() ? s[pos++] : 0;
+        if (end_ch != 0 && ch == end_ch) { name += ch; ch = nextChar(s, pos); break; }
+    }
+    if (isControl(ch) && ch != 0) ch = nextChar(s, pos);
+    if (name.empty() && node->isLeaf()) throw std::runtime_error("A taxon has no name.");
+    node->name = name;
+    if (node->isLeaf()) { node->id = leafNum; leafNum++; }
+    if (ch == ';' || ch == 0) return;
+    if (ch == ':') {
+        ch = nextChar(s, pos);
+        std::string num;
+        while (ch != 0 && !isNewickToken(ch) && !isControl(ch)) { num += ch; ch = pos < s.size() ? s[pos++] : 0; }
+        if (isControl(ch) && ch != 0) ch = nextChar(s, pos);
+        if (ch == 0) throw std::runtime_error("branch length format error.");
+        branch_len = strtod(num.c_str(), NULL);
+    }
+}
+
+void PhyloTree::initializeTreeIds(Node *node, Node *dad) {   // mtree.cpp:561-583
+    if (!node->isLeaf()) node->id = nodeNum++;
+    FOR_NEI(node, dad, it) {
+        initializeTreeIds((*it)->node, node);
+    }
+}
+
+void PhyloTree::readTreeString(const std::string &newick) {
+    deleteAllPartialLh();
+    for (size_t i = 0; i < allNodes.size(); i++) {
+        for (size_t k = 0; k < allNodes[i]->neighbors.size(); k++) delete allNodes[i]->neighbors[k];
+        delete allNodes[i];
+    }
+    allNodes.clear();
+    leafNum = 0; root = NULL;
+    size_t pos = 0;
+    char ch = nextChar(newick, pos);
+    if (ch != '(') throw std::runtime_error("Tree file does not start with an opening-bracket '('");
+    Node *top = NULL;
+    double brlen;
+    parseNewick(newick, pos, top, brlen);
+    if (brlen > 0.0) throw std::runtime_error("rooted trees are not supported by the likelihood engine");
+    if (pos == 0 || newick[pos - 1] != ';') throw std::runtime_error("Tree file must be ended with a semi-colon ';'");
+    FOR_NEI(top, (Node*)NULL, it) if ((*it)->node->isLeaf()) { root = (*it)->node; break; }
+    if (!root) for (size_t i = 0; i < allNodes.size(); i++) if (allNodes[i]->isLeaf() && allNodes[i]->id == 0) root = allNodes[i];
+    nodeNum = leafNum;
+    initializeTreeIds(root, NULL);
+    // setAlignment (phylotree.cpp:315-342): leaf ids = alignment sequence ids; setRootNode: first sequence
+    if (!seq_names.empty()) {
+        if ((int)seq_names.size() != leafNum) throw std::runtime_error("Tree taxa and alignment sequence do not match");
+        for (size_t i = 0; i < allNodes.size(); i++) {
+            Node *n = allNodes[i];
+            if (!n->isLeaf()) continue;
+            std::vector<std::string>::iterator f = std::find(seq_names.begin(), seq_names.end(), n->name);
+            if (f == seq_names.end()) throw std::runtime_error("Tree taxon " + n->name + " does not appear in the alignment");
+            n->id = (int)(f - seq_names.begin());
+        }
+        setRootNode(seq_names[0]);
+    }
+    current_it = current_it_back = NULL;
+}
+
+void PhyloTree::readAdjacency(const std::string &text) {
+    deleteAllPartialLh();
+    for (size_t i = 0; i < allNodes.size(); i++) {
+        for (size_t k = 0; k < allNodes[i]->neighbors.size(); k++) delete allNodes[i]->neighbors[k];
+        delete allNodes[i];
+    }
+    allNodes.clear();
+    std::istringstream in(text);
+    std::string tok;
+    int root_id = -1, nnodes = 0, nleaves = 0;
+    in >> tok >> root_id >> tok >> nnodes >> tok >> nleaves;
+    struct Rec { int id, leaf; std::string name; std::vector<int> nb; std::vector<double> len; };
+    std::vector<Rec> recs(nnodes);
+    int maxid = -1;
+    for (int i = 0; i < nnodes; i++) {
+        int deg;
+        in >> tok >> recs[i].id >> recs[i].leaf >> recs[i].name >> deg;
+        if (!in) throw std::runtime_error("bad adjacency text");
+        recs[i].nb.resize(deg); recs[i].len.resize(deg);
+        for (int k = 0; k < deg; k++) in >> recs[i].nb[k] >> recs[i].len[k];
+        maxid = std::max(maxid, recs[i].id);
+    }
+    std::vector<Node*> byid(maxid + 1, (Node*)NULL);
+    for (int i = 0; i < nnodes; i++) {
+        Node *n = newNode();
+        n->id = recs[i].id;
+        n->name = recs[i].name == "-" ? "" : recs[i].name;
+        byid[n->id] = n;
+    }
+    for (int i = 0; i < nnodes; i++)
+        for (size_t k = 0; k < recs[i].nb.size(); k++)
+            byid[recs[i].id]->neighbors.push_back(new Neighbor(byid[recs[i].nb[k]], recs[i].len[k]));
+    leafNum = nleaves; nodeNum = nnodes;
+    root = byid[root_id];
+    current_it = current_it_back = NULL;
+}
+
+void PhyloTree::setRootNode(const std::string &name) {
+    for (size_t i = 0; i < allNodes.size(); i++)
+        if (allNodes[i]->name == name) { root = allNodes[i]; return; }
+    throw std::runtime_error("setRootNode: no node named " + name);
+}
+
+void PhyloTree::printSubtree(std::string &out, const Node *node, const Node *dad, int precision) const {
+    char buf[64];
+    if (node->isLeaf() && dad) { out += node->name; return; }
+    out += "(";
+    bool first = true;
+    for (size_t i = 0; i < node->neighbors.size(); i++) {
+        const Neighbor *nb = node->neighbors[i];
+        if (nb->node == dad) continue;
+        if (!first) out += ",";
+        first = false;
+        printSubtree(out, nb->node, node, precision);
+        snprintf(buf, sizeof(buf), ":%.*g", precision, nb->length);
+        out += buf;
+    }
+    out += ")";
+}
+
+std::string PhyloTree::getTreeString(int precision) const {
+    // printed from the root leaf's neighbour, root leaf first (same topology, reference-independent text)
+    std::string out;
+    if (!root) return out;
+    const Neighbor *nb = root->neighbors[0];
+    char buf[64];
+    out += "(" + root->name;
+    snprintf(buf, sizeof(buf), ":%.*g", precision, nb->length);
+    out += buf;
+    for (size_t i = 0; i < nb->node->neighbors.size(); i++) {
+        const Neighbor *c = nb->node->neighbors[i];
+        if (c->node == root) continue;
+        out += ",";
+        printSubtree(out, c->node, nb->node, precision);
+        snprintf(buf, sizeof(buf), ":%.*g", precision, c->length);
+        out += buf;
+    }
+    out += ");";
+    return out;
+}
+
+/* ------------------------------------------------------------ alignment / model ------------------------------------------------------------ */
+
+void PhyloTree::setAlignment(int ntaxa_, int64_t nptn_, const uint8_t *states, const double *freq,
+                             const std::vector<std::string> &names, int seq_type_, int nstates_, int state_unknown_) {
+    deleteAllPartialLh();
+    ntaxa = ntaxa_; nptn = nptn_; seq_type = seq_type_; nstates = nstates_; state_unknown = state_unknown_;
+    states_.assign(states, states + (size_t)ntaxa * (size_t)nptn);
+    freq_global_.assign(freq, freq + nptn);
+    nsite = 0;
+    for (int64_t p = 0; p < nptn; p++) nsite += (int64_t)freq[p];
+    seq_names = names;
+    const_char_.clear();
+    unobs_.clear(); nunobs = 0;
+}
+
+void PhyloTree::setUnobservedPatterns(const std::vector<uint8_t> &unobs) {
+    deleteAllPartialLh();
+    unobs_ = unobs; nunobs = (int64_t)unobs.size();
+}
+
+void PhyloTree::setConstChar(const int32_t *cc) { const_char_.assign(cc, cc + nptn); inputs_uploaded_ = false; tip_partial_lh_computed_ = false; }
+
+void PhyloTree::setModel(int family_, int ncat_, int nmix_, const double *eval, const double *evec, const double *inv_evec,
+                         const double *rates, const double *props, const double *mixprops,
+                         const double *state_freq, double p_invar) {
+    if (!engines_.empty() && (family_ != family || ncat_ != ncat || nmix_ != nmix)) deleteAllPartialLh();
+    family = family_; ncat = ncat_; nmix = nmix_;
+    size_t E = (size_t)nmix, S = (size_t)nstates;
+    eval_.assign(eval, eval + E * S);
+    evec_.assign(evec, evec + E * S * S);
+    inv_evec_.assign(inv_evec, inv_evec + E * S * S);
+    rates_.assign(rates, rates + ncat);
+    props_.assign(props, props + ncat);
+    if (mixprops) mixprops_.assign(mixprops, mixprops + nmix); else mixprops_.assign(nmix, 1.0);
+    if (state_freq) state_freq_.assign(state_freq, state_freq + S); else state_freq_.assign(S, 1.0 / S);
+    p_invar_ = p_invar;
+    // every parameter change is followed by clearAllPartialLH in the reference; the tip table must be redone
+    tip_partial_lh_computed_ = false;
+}
+
+/* phylotreesse.cpp:459-527 */
+void PhyloTree::computeTipPartialLikelihood() {
+    if (tip_partial_lh_computed_) return;
+    tip_partial_lh_computed_ = true;
+    computePtnFreq();
+    computePtnInvar();
+    int S = nstates, M = nmix;
+    tip_partial_lh.assign((size_t)(state_unknown + 1) * S * M, 0.0);
+    const double *all_inv_evec = &inv_evec_[0];
+    for (int state = 0; state < S; state++)
+        for (int m = 0; m < M; m++) {
+            const double *inv_evec = all_inv_evec + (size_t)m * S * S;
+            for (int i = 0; i < S; i++) tip_partial_lh[(size_t)state * S * M + m * S + i] = inv_evec[i * S + state];
+        }
+    for (int i = 0; i < S; i++)
+        for (int m = 0; m < M; m++) {
+            const double *inv_evec = all_inv_evec + (size_t)m * S * S;
+            double lh_unknown = 0.0;
+            for (int x = 0; x < S; x++) lh_unknown += inv_evec[i * S + x];
+            tip_partial_lh[(size_t)state_unknown * S * M + m * S + i] = lh_unknown;
+        }
+    static const int ambi_aa[] = {4 + 8, 32 + 64, 512 + 1024};
+    if (seq_type == SEQ_DNA && S == 4) {
+        for (int state = 4; state < 18; state++) {
+            int cstate = state - S + 1;
+            for (int m = 0; m < M; m++) {
+                const double *inv_evec = all_inv_evec + (size_t)m * S * S;
+                for (int i = 0; i < S; i++) {
+                    double lh_ambiguous = 0.0;
+                    for (int x = 0; x < S; x++) if (cstate & (1 << x)) lh_ambiguous += inv_evec[i * S + x];
+                    tip_partial_lh[(size_t)state * S * M + m * S + i] = lh_ambiguous;
+                }
+            }
+        }
+    } else if (seq_type == SEQ_PROTEIN && S == 20) {
+        for (int state = 0; state < 3; state++)
+            for (int m = 0; m < M; m++) {
+                const double *inv_evec = all_inv_evec + (size_t)m * S * S;
+                for (int i = 0; i < S; i++) {
+                    double lh_ambiguous = 0.0;
+                    for (int x = 0; x < 11; x++) if (ambi_aa[state] & (1 << x)) lh_ambiguous += inv_evec[i * S + x];
+                    tip_partial_lh[(size_t)(state + 20) * S * M + m * S + i] = lh_ambiguous;
+                }
+            }
+    }
+    inputs_uploaded_ = false;
+}
+
+void PhyloTree::computePtnFreq() {   // phylotreesse.cpp:531-541
+    ptn_freq.assign(freq_global_.begin(), freq_global_.end());
+}
+
+void PhyloTree::computePtnInvar() {  // phylotreesse.cpp:543-569
+    ptn_invar.assign((size_t)(nptn + nunobs), 0.0);
+    if (p_invar_ != 0.0) {
+        if ((int64_t)const_char_.size() != nptn) throw std::runtime_error("computePtnInvar: +I needs Pattern::const_char (setConstChar)");
+        for (int64_t p = 0; p < nptn; p++) {
+            if (const_char_[p] == nstates) ptn_invar[p] = p_invar_;
+            else if (const_char_[p] >= 0 && const_char_[p] < nstates) ptn_invar[p] = p_invar_ * state_freq_[const_char_[p]];
+        }
+        for (int64_t u = 0; u < nunobs; u++) ptn_invar[nptn + u] = p_invar_ * state_freq_[unobs_[u]];
+    }
+}
+
+/* ------------------------------------------------------------ buffers / engines ------------------------------------------------------------ */
+
+int PhyloTree::assignVectors(Node *node, Node *dad, int index) {
+    // every neighbour pointing to an internal node owns a vector (LM_ALL_BRANCH, phylotree.cpp:916-974)
+    FOR_NEI(node, dad, it) {
+        Neighbor *nei = *it, *back = nei->node->findNeighbor(node);
+        nei->vec = nei->node->isLeaf() ? -1 : index++;
+        back->vec = node->isLeaf() ? -1 : index++;
+        nei->partial_lh_computed = back->partial_lh_computed = 0;
+        index = assignVectors(nei->node, node, index);
+    }
+    return index;
+}
+
+void PhyloTree::setStream(void *s) {
+    stream_ = s;
+    for (size_t i = 0; i < engines_.size(); i++) check(lkcuda_set_stream(engines_[i], s), engines_[i], "lkcuda_set_stream");
+}
+
+void PhyloTree::initializeAllPartialLh() {
+    if (!engines_.empty()) return;
+    if (!root) throw std::runtime_error("initializeAllPartialLh: no tree");
+    if (states_.empty() || eval_.empty()) throw std::runtime_error("initializeAllPartialLh: alignment and model must be set first");
+    nvec_ = assignVectors(root, NULL, 0);
+    // this process' pattern range, then one sub-shard per device
+    int64_t pb = nptn * proc_rank_ / proc_world_, pe = nptn * (proc_rank_ + 1) / proc_world_;
+    ptn_begin_ = pb; ptn_end_ = pe;
+    std::vector<int> devs = devices_;
+    if (devs.empty()) devs.push_back(0);
+    size_t nd = devs.size();
+    shard_begin_.resize(nd + 1);
+    for (size_t d = 0; d <= nd; d++) shard_begin_[d] = pb + (pe - pb) * (int64_t)d / (int64_t)nd;
+    int K = family == FAMILY_MIXTURE ? ncat * nmix : ncat;
+    for (size_t d = 0; d < nd; d++) {
+        lkcuda_config cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.device = devs[d];
+        cfg.nstates = nstates; cfg.nblocks = K; cfg.neigen = nmix; cfg.ntaxa = ntaxa;
+        cfg.state_unknown = state_unknown; cfg.nvec = nvec_;
+        cfg.flags = (family != FAMILY_PLAIN ? LKCUDA_FLAG_SCALE_IGNORES_INVAR : 0) |
+                    (generic_kernel ? (LKCUDA_FLAG_ZERO_GUARD | LKCUDA_FLAG_PATTERN_LH_CAT) : 0);
+        cfg.nptn = shard_begin_[d + 1] - shard_begin_[d];
+        cfg.nunobs = nunobs;
+        int64_t ns = 0;
+        for (int64_t p = shard_begin_[d]; p < shard_begin_[d + 1]; p++) ns += (int64_t)freq_global_[p];
+        cfg.nsite = ns;
+        lkcuda_engine *e = NULL;
+        int rc = lkcuda_create(&cfg, &e);
+        if (rc != LKCUDA_OK) {
+            std::string msg = std::string("lkcuda_create: ") + lkcuda_last_error(NULL);
+            deleteAllPartialLh();
+            throw std::runtime_error(msg);
+        }
+        engines_.push_back(e);
+        if (stream_) check(lkcuda_set_stream(e, stream_), e, "lkcuda_set_stream");
+        // tip states of the shard: [taxon][local ptn + unobserved]
+        size_t np = (size_t)cfg.nptn, na = np + (size_t)nunobs;
+        std::vector<uint8_t> st((size_t)ntaxa * na);
+        for (int t = 0; t < ntaxa; t++) {
+            memcpy(&st[(size_t)t * na], &states_[(size_t)t * nptn + shard_begin_[d]], np);
+            for (int64_t u = 0; u < nunobs; u++) st[(size_t)t * na + np + u] = unobs_[u];
+        }
+        check(lkcuda_set_tip_states(e, na ? &st[0] : (const uint8_t*)""), e, "lkcuda_set_tip_states");
+    }
+    inputs_uploaded_ = false;
+    tip_partial_lh_computed_ = false;
+    vec_level_.assign(nvec_, 0);
+    clearAllPartialLH();
+}
+
+void PhyloTree::deleteAllPartialLh() {
+    for (size_t i = 0; i < engines_.size(); i++) lkcuda_destroy(engines_[i]);
+    engines_.clear();
+    pending_ops_.clear(); pending_level_.clear();
+    theta_computed = false;
+}
+
+void PhyloTree::ensureInputs() {
+    if (!tip_partial_lh_computed_) computeTipPartialLikelihood();
+    if (inputs_uploaded_) return;
+    int K = family == FAMILY_MIXTURE ? ncat * nmix : ncat;
+    std::vector<int32_t> blk_eigen(K);
+    std::vector<double> blk_rate(K), blk_weight(K);
+    for (int k = 0; k < K; k++) {
+        if (family == FAMILY_MIXTURE) {        // block = m*ncat + c (phylokernelmixture.h:121)
+            int m = k / ncat, c = k % ncat;
+            blk_eigen[k] = m; blk_rate[k] = rates_[c]; blk_weight[k] = props_[c] * mixprops_[m];
+        } else if (family == FAMILY_MIXRATE) { // category c uses component c (phylokernelmixrate.h:52,99-130)
+            blk_eigen[k] = k; blk_rate[k] = rates_[k]; blk_weight[k] = props_[k];
+        } else {
+            blk_eigen[k] = 0; blk_rate[k] = rates_[k]; blk_weight[k] = props_[k];
+        }
+    }
+    for (size_t d = 0; d < engines_.size(); d++) {
+        lkcuda_engine *e = engines_[d];
+        size_t np = (size_t)(shard_begin_[d + 1] - shard_begin_[d]);
+        std::vector<double> inv(np + (size_t)nunobs + 1);
+        if (np) memcpy(&inv[0], &ptn_invar[shard_begin_[d]], np * 8);
+        for (int64_t u = 0; u < nunobs; u++) inv[np + u] = ptn_invar[nptn + u];
+        static const double zero = 0.0;
+        check(lkcuda_set_pattern_weights(e, np ? &ptn_freq[shard_begin_[d]] : &zero, &inv[0]), e, "lkcuda_set_pattern_weights");
+        check(lkcuda_set_model(e, &eval_[0], &evec_[0], &inv_evec_[0], &blk_eigen[0], &blk_rate[0], &blk_weight[0],
+                               &tip_partial_lh[0]), e, "lkcuda_set_model");
+    }
+    inputs_uploaded_ = true;
+}
+
+/* ------------------------------------------------------------ dirty bits ------------------------------------------------------------ */
+
+static void clearAllRec(Node *node, Node *dad) {     // phylonode.cpp:53-65
+    node->findNeighbor(dad)->partial_lh_computed = 0;
+    dad->findNeighbor(node)->partial_lh_computed = 0;
+    FOR_NEI(node, dad, it) clearAllRec((*it)->node, node);
+}
+
+void PhyloTree::clearAllPartialLH() {                // phylotree.cpp:495-502
+    if (!root) return;
+    clearAllRec(root->neighbors[0]->node, root);
+    tip_partial_lh_computed_ = false;
+    current_it = current_it_back = NULL;
+    pending_ops_.clear(); pending_level_.clear();
+    std::fill(vec_level_.begin(), vec_level_.end(), 0);
+}
+
+void PhyloTree::clearReversePartialLh(Node *node, Node *dad) {   // phylonode.cpp:42-51
+    FOR_NEI(node, dad, it) {
+        (*it)->node->findNeighbor(node)->partial_lh_computed = 0;
+        clearReversePartialLh((*it)->node, node);
+    }
+}
+
+/* ------------------------------------------------------------ kernels ------------------------------------------------------------ */
+
+int PhyloTree::opLevel(Neighbor *child) {
+    return (child->vec >= 0) ? vec_level_[child->vec] : 0;
+}
+
+/* phylokernel.h:71-143: same early-outs, same recursion order (left then right), same leaf-left swap.
+   Records the node instead of computing it. */
+void PhyloTree::computePartialLikelihood(Neighbor *dad_branch, Node *dad) {
+    if (dad_branch->partial_lh_computed & 1) return;
+    dad_branch->partial_lh_computed |= 1;
+    num_partial_lh_computations++;
+    Node *node = dad_branch->node;
+    if (node->isLeaf()) return;
+    if (node->degree() > 3) {
+        // multifurcating node: generic path, issued immediately after its children (phylotreesse.cpp:702-806)
+        std::vector<int32_t> child; std::vector<double> len;
+        FOR_NEI(node, dad, it) {
+            if (((*it)->partial_lh_computed & 1) == 0) computePartialLikelihood(*it, node);
+            child.push_back((*it)->node->isLeaf() ? LKCUDA_TIP((*it)->node->id) : (*it)->vec);
+            len.push_back((*it)->length);
+        }
+        flushPartialOps();
+        for (size_t d = 0; d < engines_.size(); d++)
+            check(lkcuda_partial_multi(engines_[d], dad_branch->vec, (int32_t)child.size(), &child[0], &len[0]), engines_[d], "lkcuda_partial_multi");
+        return;
+    }
+    Neighbor *left = NULL, *right = NULL;
+    FOR_NEI(node, dad, it) { if (!left) left = *it; else right = *it; }
+    if (!left->node->isLeaf() && right->node->isLeaf()) std::swap(left, right);
+    if ((left->partial_lh_computed & 1) == 0) computePartialLikelihood(left, node);
+    if ((right->partial_lh_computed & 1) == 0) computePartialLikelihood(right, node);
+    lkcuda_partial_op op;
+    op.dst = dad_branch->vec;
+    op.left = left->node->isLeaf() ? LKCUDA_TIP(left->node->id) : left->vec;
+    op.right = right->node->isLeaf() ? LKCUDA_TIP(right->node->id) : right->vec;
+    op.reserved = 0;
+    op.len_left = left->length;
+    op.len_right = right->length;
+    int level = 1 + std::max(opLevel(left), opLevel(right));
+    vec_level_[op.dst] = level;
+    pending_ops_.push_back(op);
+    pending_level_.push_back(level);
+}
+
+/* hand the recorded post-order schedule to the device, grouped by tree level */
+void PhyloTree::flushPartialOps() {
+    ensureInputs();
+    if (pending_ops_.empty()) return;
+    size_t n = pending_ops_.size();
+    int maxlevel = 0;
+    for (size_t i = 0; i < n; i++) maxlevel = std::max(maxlevel, pending_level_[i]);
+    std::vector<int32_t> level_start(maxlevel + 1, 0);
+    for (size_t i = 0; i < n; i++) level_start[pending_level_[i]]++;       // counts at [level]
+    int32_t acc = 0;
+    for (int l = 1; l <= maxlevel; l++) { int32_t c = level_start[l]; level_start[l] = acc; acc += c; }
+    // level_start[l] = first slot of level l (1-based levels) -> shift to 0-based array of size maxlevel+1
+    std::vector<lkcuda_partial_op> sorted(n);
+    std::vector<int32_t> cursor(level_start.begin(), level_start.end());
+    for (size_t i = 0; i < n; i++) sorted[cursor[pending_level_[i]]++] = pending_ops_[i];   // stable
+    std::vector<int32_t> starts(maxlevel + 1);
+    for (int l = 1; l <= maxlevel; l++) starts[l - 1] = level_start[l];
+    starts[maxlevel] = (int32_t)n;
+    for (size_t d = 0; d < engines_.size(); d++)
+        check(lkcuda_partial_batch(engines_[d], &sorted[0], (int32_t)n, &starts[0], maxlevel), engines_[d], "lkcuda_partial_batch");
+    for (size_t i = 0; i < n; i++) vec_level_[pending_ops_[i].dst] = 0;
+    pending_ops_.clear(); pending_level_.clear();
+}
+
+/* sum the shards' results; under one-process-per-GPU the caller-supplied all-reduce sums across ranks */
+void PhyloTree::reduceResult(double *result) {
+    double tot[LKCUDA_NRESULT];
+    memset(tot, 0, sizeof(tot));
+    if (allreduce_ && engines_.size() == 1) {
+        void *dev = NULL;
+        check(lkcuda_result_device_ptr(engines_[0], &dev), engines_[0], "lkcuda_result_device_ptr");
+        allreduce_(allreduce_user_, NULL, dev, LKCUDA_NRESULT);
+        check(lkcuda_read_result(engines_[0], tot), engines_[0], "lkcuda_read_result");
+    } else {
+        for (size_t d = 0; d < engines_.size(); d++) {
+            double r[LKCUDA_NRESULT];
+            check(lkcuda_read_result(engines_[d], r), engines_[d], "lkcuda_read_result");
+            for (int i = 0; i < LKCUDA_NRESULT; i++) tot[i] += r[i];
+        }
+        if (allreduce_) allreduce_(allreduce_user_, tot, NULL, LKCUDA_NRESULT);
+    }
+    memcpy(result, tot, sizeof(tot));
+}
+
+double PhyloTree::computeLikelihoodBranch(Neighbor *dad_branch, Node *dad) {   // phylokernel.h:734-751
+    Node *node = dad_branch->node;
+    Neighbor *node_branch = node->findNeighbor(dad);
+    if (engines_.empty()) initializeAllPartialLh();
+    if (node->isLeaf()) { std::swap(dad, node); std::swap(dad_branch, node_branch); }
+    if ((dad_branch->partial_lh_computed & 1) == 0) computePartialLikelihood(dad_branch, dad);
+    if ((node_branch->partial_lh_computed & 1) == 0) computePartialLikelihood(node_branch, node);
+    flushPartialOps();
+    // dad_branch points from dad to node: its vector is the subtree at `node`; node_branch's is the subtree at `dad`
+    int32_t dad_end = dad->isLeaf() ? LKCUDA_TIP(dad->id) : node_branch->vec;
+    for (size_t d = 0; d < engines_.size(); d++)
+        check(lkcuda_branch_lnl(engines_[d], dad_end, dad_branch->vec, dad_branch->length, NULL), engines_[d], "lkcuda_branch_lnl");
+    double r[LKCUDA_NRESULT];
+    reduceResult(r);
+    if (r[LKCUDA_R_NREPAIRED] > 0)
+        fprintf(stderr, "WARNING: Numerical underflow caused by %.0f alignment patterns\n", r[LKCUDA_R_NREPAIRED]);
+    return r[LKCUDA_R_LNL];
+}
+
+void PhyloTree::computeLikelihoodDerv(Neighbor *dad_branch, Node *dad, double &df, double &ddf) {   // phylokernel.h:486-503
+    Node *node = dad_branch->node;
+    Neighbor *node_branch = node->findNeighbor(dad);
+    if (engines_.empty()) initializeAllPartialLh();
+    if (node->isLeaf()) { std::swap(dad, node); std::swap(dad_branch, node_branch); }
+    if ((dad_branch->partial_lh_computed & 1) == 0) computePartialLikelihood(dad_branch, dad);
+    if ((node_branch->partial_lh_computed & 1) == 0) computePartialLikelihood(node_branch, node);
+    flushPartialOps();
+    if (!theta_computed) {
+        theta_computed = true;
+        int32_t dad_end = dad->isLeaf() ? LKCUDA_TIP(dad->id) : node_branch->vec;
+        for (size_t d = 0; d < engines_.size(); d++)
+            check(lkcuda_theta_build(engines_[d], dad_end, dad_branch->vec), engines_[d], "lkcuda_theta_build");
+    }
+    for (size_t d = 0; d < engines_.size(); d++)
+        check(lkcuda_derv(engines_[d], dad_branch->length, NULL), engines_[d], "lkcuda_derv");
+    double r[LKCUDA_NRESULT];
+    reduceResult(r);
+    df = r[LKCUDA_R_DF]; ddf = r[LKCUDA_R_DDF];
+    if (std::isnan(df) || std::isinf(df)) { df = 0.0; ddf = 0.0; }
+}
+
+double PhyloTree::computeLikelihoodFromBuffer() {   // phylotreesse.cpp:349-357, phylokernel.h:1023-1192
+    if (!current_it || !current_it_back) throw std::runtime_error("computeLikelihoodFromBuffer: no current branch");
+    if (!theta_computed) return computeLikelihoodBranch(current_it, current_it_back->node);
+    for (size_t d = 0; d < engines_.size(); d++)
+        check(lkcuda_lnl_from_buffer(engines_[d], current_it->length, NULL), engines_[d], "lkcuda_lnl_from_buffer");
+    double r[LKCUDA_NRESULT];
+    reduceResult(r);
+    return r[LKCUDA_R_LNL];
+}
+
+Node *PhyloTree::findFarthestLeaf(Node *node, Node *dad) {   // mtree.cpp:2052-2068
+    if (!node) node = root;
+    if (dad && node->isLeaf()) { node->height = 0.0; return node; }
+    Node *res = NULL;
+    node->height = 0.0;
+    FOR_NEI(node, dad, it) {
+        Node *leaf = findFarthestLeaf((*it)->node, node);
+        if (node->height < (*it)->node->height + 1) {
+            node->height = (*it)->node->height + 1;
+            res = leaf;
+        }
+    }
+    return res;
+}
+
+void PhyloTree::getPreOrderBranches(std::vector<Node*> &nodes, std::vector<Node*> &nodes2, Node *node, Node *dad) {   // mtree.cpp:2096-2116
+    if (dad) { nodes.push_back(node); nodes2.push_back(dad); }
+    std::vector<Neighbor*> neivec = node->neighbors;
+    for (size_t i1 = 0; i1 < neivec.size(); i1++)
+        for (size_t i2 = i1 + 1; i2 < neivec.size(); i2++)
+            if (neivec[i1]->node->height > neivec[i2]->node->height) std::swap(neivec[i1], neivec[i2]);
+    for (size_t i1 = 0; i1 < neivec.size(); i1++)
+        if (neivec[i1]->node != dad) getPreOrderBranches(nodes, nodes2, neivec[i1]->node, node);
+}
+
+void PhyloTree::computeBestTraversal(std::vector<Node*> &nodes, std::vector<Node*> &nodes2) {   // phylotree.cpp:2241-2250
+    Node *farleaf = findFarthestLeaf();
+    findFarthestLeaf(farleaf);
+    getPreOrderBranches(nodes, nodes2, farleaf);
+}
+
+double PhyloTree::computeLikelihood(double *pattern_lh) {   // phylotree.cpp:1031-1071
+    if (!root || !root->isLeaf()) throw std::runtime_error("computeLikelihood: root must be a leaf");
+    if (!current_it) {
+        Node *leaf = findFarthestLeaf();
+        current_it = leaf->neighbors[0];
+        current_it_back = current_it->node->findNeighbor(leaf);
+    }
+    double score = computeLikelihoodBranch(current_it, current_it_back->node);
+    if (pattern_lh) {
+        // _pattern_lh + max(scale_num,0)*LOG_SCALING_THRESHOLD of current_it (phylotree.cpp:1055-1069)
+        const double LOG_THR = std::log(1.0 / 115792089237316195423570985008687907853269984665640564039457584007913129639936.0);
+        for (size_t d = 0; d < engines_.size(); d++) {
+            int64_t b = shard_begin_[d] - ptn_begin_, np = shard_begin_[d + 1] - shard_begin_[d];
+            if (!np) continue;
+            check(lkcuda_fetch_pattern_lh(engines_[d], pattern_lh + b), engines_[d], "lkcuda_fetch_pattern_lh");
+            if (current_it->vec >= 0) {
+                std::vector<int16_t> sc((size_t)(np + nunobs));
+                check(lkcuda_fetch_vector(engines_[d], current_it->vec, NULL, &sc[0]), engines_[d], "lkcuda_fetch_vector");
+                bool any = false;
+                for (int64_t i = 0; i < np; i++) if (sc[i] > 0) { any = true; break; }
+                if (any) for (int64_t i = 0; i < np; i++) pattern_lh[b + i] += std::max<int16_t>(sc[i], 0) * LOG_THR;
+            }
+        }
+    }
+    return score;
+}
+
+void PhyloTree::computePatternLhCat(double *out) {
+    int K = family == FAMILY_MIXTURE ? ncat * nmix : ncat;
+    for (size_t d = 0; d < engines_.size(); d++) {
+        int64_t b = shard_begin_[d] - ptn_begin_;
+        check(lkcuda_fetch_pattern_lh_cat(engines_[d], out + b * K), engines_[d], "lkcuda_fetch_pattern_lh_cat");
+    }
+}
+
+void PhyloTree::computeFuncDerv(double value, double &df, double &ddf) {   // phylotree.cpp:2135-2146
+    current_it->length = value;
+    current_it_back->length = value;
+    computeLikelihoodDerv(current_it, current_it_back->node, df, ddf);
+    df = -df;
+    ddf = -ddf;
+}
+
+/* optimization.cpp:388-465, statement for statement */
+double PhyloTree::minimizeNewton(double x1, double xguess, double x2, double xacc, double &d2l, int maxNRStep) {
+    int j;
+    double df, dx, dxold, f;
+    double temp, xh, xl, rts, rts_old;
+    rts = xguess;
+    if (rts < x1) rts = x1;
+    if (rts > x2) rts = x2;
+    computeFuncDerv(rts, f, df);
+    d2l = df;
+    if (!std::isfinite(f) || !std::isfinite(df)) throw std::runtime_error("Wrong computeFuncDerv");
+    if (df >= 0.0 && fabs(f) < xacc) return rts;
+    if (f < 0.0) { xl = rts; xh = x2; } else { xh = rts; xl = x1; }
+    dx = dxold = fabs(xh - xl);
+    (void)dxold;
+    for (j = 1; j <= maxNRStep; j++) {
+        rts_old = rts;
+        if ((df <= 0.0) || (((rts - xh) * df - f) * ((rts - xl) * df - f) >= 0.0)) {
+            dxold = dx; dx = 0.5 * (xh - xl); rts = xl + dx; d2l = df;
+            if (xl == rts) return rts;
+        } else {
+            dxold = dx; dx = f / df; temp = rts; rts -= dx; d2l = df;
+            if (temp == rts) return rts;
+        }
+        if (fabs(dx) < xacc || (j == maxNRStep)) return rts_old;
+        computeFuncDerv(rts, f, df);
+        if (!std::isfinite(f) || !std::isfinite(df)) throw std::runtime_error("Wrong computeFuncDerv");
+        if (df > 0.0 && fabs(f) < xacc) { d2l = df; return rts; }
+        if (f < 0.0) xl = rts; else xh = rts;
+    }
+    throw std::runtime_error("Maximum number of iterations exceeded in minimizeNewton");
+}
+
+void PhyloTree::optimizeOneBranch(Node *node1, Node *node2, bool clearLH, int maxNRStep) {   // phylotree.cpp:2148-2192
+    current_it = node1->findNeighbor(node2);
+    current_it_back = node2->findNeighbor(node1);
+    if (!current_it || !current_it_back) throw std::runtime_error("optimizeOneBranch: nodes are not adjacent");
+    double current_len = current_it->length;
+    theta_computed = false;
+    double optx, d2l;
+    if (device_newton && engines_.size() == 1 && !allreduce_) {
+        // same Newton sequence, driven on the device: one launch instead of one per step
+        Node *dad = current_it_back->node;
+        Neighbor *dad_branch = current_it; Node *node = dad_branch->node; Neighbor *node_branch = current_it_back;
+        if (node->isLeaf()) { std::swap(dad, node); std::swap(dad_branch, node_branch); }
+        if ((dad_branch->partial_lh_computed & 1) == 0) computePartialLikelihood(dad_branch, dad);
+        if ((node_branch->partial_lh_computed & 1) == 0) computePartialLikelihood(node_branch, node);
+        flushPartialOps();
+        theta_computed = true;
+        int32_t dad_end = dad->isLeaf() ? LKCUDA_TIP(dad->id) : node_branch->vec;
+        check(lkcuda_theta_build(engines_[0], dad_end, dad_branch->vec), engines_[0], "lkcuda_theta_build");
+        double out[4];
+        check(lkcuda_newton_branch(engines_[0], min_branch_length, current_len, max_branch_length, min_branch_length, maxNRStep, out),
+              engines_[0], "lkcuda_newton_branch");
+        optx = out[0]; d2l = out[1];
+        // minimizeNewton leaves the branch at the last length it evaluated (computeFuncDerv, phylotree.cpp:2136-2137)
+        current_it->length = out[3]; current_it_back->length = out[3];
+    } else {
+        optx = minimizeNewton(min_branch_length, current_len, max_branch_length, min_branch_length, d2l, maxNRStep);
+    }
+    if (optx > max_branch_length * 0.95) {
+        // newton raphson diverged, reset
+        double opt_lh = computeLikelihoodFromBuffer();
+        current_it->length = current_len;
+        current_it_back->length = current_len;
+        double orig_lh = computeLikelihoodFromBuffer();
+        if (orig_lh > opt_lh) optx = current_len;
+    }
+    current_it->length = optx;
+    current_it_back->length = optx;
+    if (clearLH && current_len != optx) {
+        clearReversePartialLh(node1, node2);
+        clearReversePartialLh(node2, node1);
+    }
+}
+
+void PhyloTree::saveBranchLengths(std::vector<double> &lenvec, int startid, Node *node, Node *dad) {
+    if (!node) { node = root; lenvec.clear(); }
+    FOR_NEI(node, dad, it) {
+        lenvec.push_back((*it)->length);
+        saveBranchLengths(lenvec, startid, (*it)->node, node);
+    }
+}
+
+static void restoreRec(const std::vector<double> &lenvec, size_t &pos, Node *node, Node *dad) {
+    FOR_NEI(node, dad, it) {
+        (*it)->length = (*it)->node->findNeighbor(node)->length = lenvec[pos++];
+        restoreRec(lenvec, pos, (*it)->node, node);
+    }
+}
+
+void PhyloTree::restoreBranchLengths(const std::vector<double> &lenvec, int, Node *, Node *) {
+    size_t pos = 0;
+    restoreRec(lenvec, pos, root, NULL);
+}
+
+double PhyloTree::optimizeAllBranches(int my_iterations, double tolerance, int maxNRStep) {   // phylotree.cpp:2252-2332
+    std::vector<Node*> nodes, nodes2;
+    computeBestTraversal(nodes, nodes2);
+    double tree_lh = computeLikelihoodBranch(nodes[0]->findNeighbor(nodes2[0]), nodes[0]);
+    for (int i = 0; i < my_iterations; i++) {
+        std::vector<double> lenvec;
+        saveBranchLengths(lenvec);
+        for (size_t j = 0; j < nodes.size(); j++) optimizeOneBranch(nodes[j], nodes2[j], true, maxNRStep);
+        double new_tree_lh = computeLikelihoodFromBuffer();
+        if (new_tree_lh < tree_lh) {
+            // IN RARE CASE: tree log-likelihood decreases, revert the branch length and stop
+            clearAllPartialLH();
+            restoreBranchLengths(lenvec);
+            new_tree_lh = computeLikelihood();
+            return new_tree_lh;
+        }
+        if (tree_lh <= new_tree_lh && new_tree_lh <= tree_lh + tolerance) return new_tree_lh;
+        tree_lh = new_tree_lh;
+    }
+    return tree_lh;
+}
+
+}  // namespace lk

@@ -1,0 +1,178 @@
+/*
+ * lk_phylotree.h — host-side mirror of the reference's PhyloTree likelihood API, written against the
+ * C ABI of include/lkcuda.h.  It keeps the reference's names, argument meaning and control flow for
+ * the functions that decide ORDER: which partials are recomputed, left/right
+ * orientation, root-branch choice, branch visiting order and the Newton step sequence.  All
+ * per-pattern arithmetic happens on the device behind lkcuda_*.
+ *
+ * Mirrors (reference file:line):
+ *   Node / Neighbor / PhyloNeighbor      node.h, phylonode.h:102-127
+ *   clearAllPartialLH                    phylotree.cpp:495-502, phylonode.cpp:53-65
+ *   clearReversePartialLh                phylonode.cpp:42-51
+ *   initializeAllPartialLh               phylotree.cpp:667-716, 834-987 (index assignment :916-974)
+ *   computeTipPartialLikelihood          phylotreesse.cpp:359-529
+ *   computePtnFreq / computePtnInvar     phylotreesse.cpp:531-569
+ *   computePartialLikelihood             phylokernel.h:71-143 (recursion + dirty bits + leaf-left swap)
+ *   computeLikelihoodBranch              phylokernel.h:734-751
+ *   computeLikelihoodDerv                phylokernel.h:486-503 (theta_computed flag :535)
+ *   computeLikelihoodFromBuffer          phylotreesse.cpp:349-357
+ *   computeLikelihood                    phylotree.cpp:1031-1071
+ *   findFarthestLeaf / getPreOrderBranches   mtree.cpp:2052-2068, 2096-2116
+ *   computeBestTraversal                 phylotree.cpp:2241-2250
+ *   computeFuncDerv                      phylotree.cpp:2135-2146
+ *   minimizeNewton                       optimization.cpp:388-465
+ *   optimizeOneBranch / optimizeAllBranches  phylotree.cpp:2148-2192, 2252-2332
+ *   readTree / parseFile (Newick)        mtree.cpp:503-680
+ */
+#ifndef LK_PHYLOTREE_H
+#define LK_PHYLOTREE_H
+
+#include <cstdint>
+#include <string>
+#include <vector>
+#include <stdexcept>
+#include "../../include/lkcuda.h"
+
+namespace lk {
+
+struct Node;
+
+/* PhyloNeighbor (phylonode.h:102-127): partial_lh/scale_num become the arena vector index `vec` */
+struct Neighbor {
+    Node *node;                 // the node this neighbour points to
+    double length;
+    int id;
+    int vec;                    // arena vector holding the partial of the subtree rooted at `node`; -1 = none (leaf)
+    int partial_lh_computed;    // bit 0 = likelihood partial up to date
+    Neighbor(Node *n, double len) : node(n), length(len), id(-1), vec(-1), partial_lh_computed(0) {}
+};
+
+struct Node {
+    int id;
+    std::string name;
+    std::vector<Neighbor*> neighbors;
+    double height;
+    Node() : id(-1), height(0.0) {}
+    bool isLeaf() const { return neighbors.size() <= 1; }
+    int degree() const { return (int)neighbors.size(); }
+    Neighbor *findNeighbor(const Node *n) const {
+        for (size_t i = 0; i < neighbors.size(); i++) if (neighbors[i]->node == n) return neighbors[i];
+        return NULL;
+    }
+};
+
+enum SeqType { SEQ_DNA = 0, SEQ_PROTEIN = 1, SEQ_BINARY = 2, SEQ_MORPH = 3, SEQ_MULTISTATE = 4, SEQ_CODON = 5 };
+enum ModelFamily { FAMILY_PLAIN = 0, FAMILY_MIXRATE = 1, FAMILY_MIXTURE = 2 };
+
+typedef void (*AllReduceFn)(void *user, double *host_buf /*may be NULL*/, void *dev_buf, int n);
+
+class PhyloTree {
+public:
+    PhyloTree();
+    ~PhyloTree();
+
+    /* ---- tree ---- */
+    void readTreeString(const std::string &newick);                 // mtree.cpp:503-680 + setAlignment leaf ids
+    void readAdjacency(const std::string &adj_text);                // fixture format of oracle/ref_harness.cpp
+    std::string getTreeString(int precision = 17) const;
+    void setRootNode(const std::string &name);                      // phylotree.cpp:344-352
+    int leafNum, nodeNum;
+    Node *root;
+    std::vector<Node*> allNodes;
+
+    /* ---- alignment (already pattern-compressed; taxon-major states) ---- */
+    void setAlignment(int ntaxa, int64_t nptn, const uint8_t *states, const double *ptn_freq,
+                      const std::vector<std::string> &names, int seq_type, int nstates, int state_unknown);
+    void setUnobservedPatterns(const std::vector<uint8_t> &unobs);  // +ASC (model_factory->unobserved_ptns)
+    void setConstChar(const int32_t *const_char);                   // Pattern::const_char, for ptn_invar
+
+    /* ---- model (host-side contract: SURVEY §2 rows 8, 9) ---- */
+    void setModel(int family, int ncat, int nmix, const double *eval, const double *evec, const double *inv_evec,
+                  const double *rates, const double *props, const double *mixprops,
+                  const double *state_freq, double p_invar);
+
+    /* ---- engine / shards ---- */
+    // devices: CUDA ordinals, one pattern shard per entry; shard_rank/shard_world further restrict this
+    // process to the patterns of one rank (one process per GPU under torchrun)
+    void setDevices(const std::vector<int> &devices) { devices_ = devices; }
+    void setProcessShard(int rank, int world) { proc_rank_ = rank; proc_world_ = world; }
+    void setAllReduce(AllReduceFn fn, void *user) { allreduce_ = fn; allreduce_user_ = user; }
+    void setStream(void *cuda_stream);
+    void initializeAllPartialLh();
+    void deleteAllPartialLh();
+    int64_t localPatternBegin() const { return ptn_begin_; }
+    int64_t localPatternEnd() const { return ptn_end_; }
+    lkcuda_engine *engine(size_t i = 0) { return i < engines_.size() ? engines_[i] : NULL; }
+
+    /* ---- the PhyloTree likelihood API ---- */
+    void clearAllPartialLH();
+    void computeTipPartialLikelihood();
+    void computePtnFreq();
+    void computePtnInvar();
+    void computePartialLikelihood(Neighbor *dad_branch, Node *dad);
+    double computeLikelihoodBranch(Neighbor *dad_branch, Node *dad);
+    void computeLikelihoodDerv(Neighbor *dad_branch, Node *dad, double &df, double &ddf);
+    double computeLikelihoodFromBuffer();
+    double computeLikelihood(double *pattern_lh = NULL);
+    void computePatternLhCat(double *pattern_lh_cat);               // phylotree.cpp:1108-1124 (values only)
+    void computeFuncDerv(double value, double &df, double &ddf);
+    double minimizeNewton(double x1, double xguess, double x2, double xacc, double &d2l, int maxNRStep = 100);
+    void optimizeOneBranch(Node *node1, Node *node2, bool clearLH = true, int maxNRStep = 100);
+    double optimizeAllBranches(int my_iterations = 100, double tolerance = 0.001, int maxNRStep = 100);
+    Node *findFarthestLeaf(Node *node = NULL, Node *dad = NULL);
+    void getPreOrderBranches(std::vector<Node*> &nodes, std::vector<Node*> &nodes2, Node *node, Node *dad = NULL);
+    void computeBestTraversal(std::vector<Node*> &nodes, std::vector<Node*> &nodes2);
+    void saveBranchLengths(std::vector<double> &lenvec, int startid = 0, Node *node = NULL, Node *dad = NULL);
+    void restoreBranchLengths(const std::vector<double> &lenvec, int startid = 0, Node *node = NULL, Node *dad = NULL);
+    void clearReversePartialLh(Node *node, Node *dad);
+
+    /* parameters (tools.cpp:785-786, phyloanalysis.cpp:2488-2497) */
+    double min_branch_length, max_branch_length;
+    bool device_newton;          // run minimizeNewton's loop on the device (single shard only)
+    bool generic_kernel;         // -fastlk semantics: zero guard + _pattern_lh_cat in every branch call
+
+    Neighbor *current_it, *current_it_back;
+    bool theta_computed;
+    uint64_t num_partial_lh_computations;
+
+    /* data exposed for tests */
+    int nstates, ncat, nmix, family, state_unknown, seq_type, ntaxa;
+    int64_t nptn, nunobs, nsite;
+    std::vector<double> ptn_freq, ptn_invar, tip_partial_lh;
+    std::vector<std::string> seq_names;
+
+private:
+    void flushPartialOps();
+    void check(int rc, lkcuda_engine *e, const char *what);
+    void reduceResult(double *result);
+    Node *newNode();
+    void parseNewick(const std::string &s, size_t &pos, Node *&node, double &branch_len);
+    void initializeTreeIds(Node *node, Node *dad);
+    void printSubtree(std::string &out, const Node *node, const Node *dad, int precision) const;
+    int assignVectors(Node *node, Node *dad, int index);
+    int opLevel(Neighbor *child);
+    void ensureInputs();
+
+    std::vector<uint8_t> states_;          // [ntaxa][nptn] global
+    std::vector<uint8_t> unobs_;
+    std::vector<int32_t> const_char_;
+    std::vector<double> freq_global_;
+    std::vector<double> eval_, evec_, inv_evec_, rates_, props_, mixprops_, state_freq_;
+    double p_invar_;
+    std::vector<int> devices_;
+    int proc_rank_, proc_world_;
+    AllReduceFn allreduce_;
+    void *allreduce_user_;
+    void *stream_;
+    std::vector<lkcuda_engine*> engines_;
+    std::vector<int64_t> shard_begin_;     // per engine, global pattern offsets (size engines+1)
+    int64_t ptn_begin_, ptn_end_;
+    bool tip_partial_lh_computed_, inputs_uploaded_;
+    int nvec_;
+    std::vector<lkcuda_partial_op> pending_ops_;
+    std::vector<int> pending_level_;
+    std::vector<int> vec_level_;           // level of the pending op writing each vector (0 = none)
+};
+
+}  // namespace lk
+#endif

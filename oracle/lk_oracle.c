@@ -1,0 +1,580 @@
+/*
+ * lk_oracle.c — ORACLE: CPU restatement of the reference's likelihood kernels.  TEST INFRASTRUCTURE.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may build, link or call this
+ * file.  It is never part of the product path (the product is iq-tree_b200/csrc, CUDA only).
+ *
+ * It implements the same C ABI as the CUDA engine (include/lkcuda.h) with plain scalar C following
+ * the reference's generic kernels statement by statement (same loop nests, same summation order as
+ * phylotreesse.cpp), so that the host mirror can be linked against either and the two compared.
+ * Parity pin: checked against the golden fixtures produced by the UNMODIFIED reference
+ * (oracle/_ref/ref_harness, see oracle/make_golden.py and tests/test_oracle_golden.py).
+ *
+ * Reference functions restated (IQ-TREE 1.4.3-beta, /root/reference):
+ *   partial likelihoods  phylotreesse.cpp:581-1010 (generic), phylokernel.h:71-483 (SIMD semantics of the
+ *                        scaling test), phylokernelmixture.h:21-460, phylokernelmixrate.h:23-449
+ *   branch lnL           phylotreesse.cpp:1158-1339, phylokernel.h:734-1020
+ *   theta + df/ddf       phylotreesse.cpp:1013-1155, phylokernel.h:486-730
+ *   lnL from buffer      phylokernel.h:1023-1192
+ *   Newton               optimization.cpp:388-465
+ */
+#include "../include/lkcuda.h"
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+/* phylotree.h:52-54 */
+#define SCALING_THRESHOLD_INVER 115792089237316195423570985008687907853269984665640564039457584007913129639936.0
+#define SCALING_THRESHOLD (1.0 / SCALING_THRESHOLD_INVER)
+#define LOG_SCALING_THRESHOLD log(SCALING_THRESHOLD)
+
+struct lkcuda_engine {
+    lkcuda_config cfg;
+    size_t S, K, E, block, nptn_all;
+    uint8_t *states;                 /* [ntaxa][P+U] */
+    double *ptn_freq, *ptn_invar;    /* [P], [P+U]   */
+    double *eval, *evec, *inv_evec;  /* [E*S], [E*S*S], [E*S*S] */
+    int32_t *blk_eigen; double *blk_rate, *blk_weight;
+    double *tip_lh;                  /* [(SU+1)][E][S] */
+    double *arena;                   /* [nvec][(P+U)*block] */
+    int16_t *scale;                  /* [nvec][P+U] */
+    double *theta;                   /* [(P+U)*block] */
+    double *pattern_lh, *pattern_lh_cat;
+    int theta_ready, theta_dad_tip;
+    double theta_scale_sum;
+    int16_t *theta_scale_num;        /* [U] summed scale_num of the unobserved patterns */
+    double result[LKCUDA_NRESULT];
+    uint64_t launches, bytes;
+    char err[256];
+};
+
+static char g_create_err[256];
+
+static int fail(lkcuda_engine *e, int code, const char *msg) {
+    snprintf(e ? e->err : g_create_err, 256, "%s", msg);
+    return code;
+}
+
+int lkcuda_device_count(int32_t *count) { if (count) *count = 0; return LKCUDA_OK; }
+
+const char *lkcuda_last_error(const lkcuda_engine *e) { return e ? e->err : g_create_err; }
+
+int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
+    if (!cfg || !out) return fail(NULL, LKCUDA_ERR_ARG, "null argument");
+    if (cfg->nstates < 1 || cfg->nblocks < 1 || cfg->neigen < 1 || cfg->ntaxa < 1 || cfg->nptn < 0 ||
+        cfg->nunobs < 0 || cfg->nvec < 0 || cfg->state_unknown < cfg->nstates)
+        return fail(NULL, LKCUDA_ERR_ARG, "invalid configuration");
+    lkcuda_engine *e = (lkcuda_engine *)calloc(1, sizeof(*e));
+    if (!e) return fail(NULL, LKCUDA_ERR_NOMEM, "out of memory");
+    e->cfg = *cfg;
+    e->S = cfg->nstates; e->K = cfg->nblocks; e->E = cfg->neigen;
+    e->block = e->S * e->K; e->nptn_all = (size_t)(cfg->nptn + cfg->nunobs);
+    size_t n = e->nptn_all ? e->nptn_all : 1;
+    e->states = (uint8_t *)calloc((size_t)cfg->ntaxa * n, 1);
+    e->ptn_freq = (double *)calloc(n, 8); e->ptn_invar = (double *)calloc(n, 8);
+    e->eval = (double *)calloc(e->E * e->S, 8);
+    e->evec = (double *)calloc(e->E * e->S * e->S, 8); e->inv_evec = (double *)calloc(e->E * e->S * e->S, 8);
+    e->blk_eigen = (int32_t *)calloc(e->K, 4); e->blk_rate = (double *)calloc(e->K, 8); e->blk_weight = (double *)calloc(e->K, 8);
+    e->tip_lh = (double *)calloc((size_t)(cfg->state_unknown + 1) * e->E * e->S, 8);
+    e->arena = (double *)calloc((size_t)(cfg->nvec ? cfg->nvec : 1) * n * e->block, 8);
+    e->scale = (int16_t *)calloc((size_t)(cfg->nvec ? cfg->nvec : 1) * n, 2);
+    e->theta = (double *)calloc(n * e->block, 8);
+    e->pattern_lh = (double *)calloc(n, 8); e->pattern_lh_cat = (double *)calloc(n * e->K, 8);
+    e->theta_scale_num = (int16_t *)calloc((size_t)cfg->nunobs + 1, 2);
+    if (!e->states || !e->arena || !e->scale || !e->theta || !e->pattern_lh_cat) {
+        lkcuda_destroy(e);
+        return fail(NULL, LKCUDA_ERR_NOMEM, "out of memory");
+    }
+    *out = e;
+    return LKCUDA_OK;
+}
+
+int lkcuda_destroy(lkcuda_engine *e) {
+    if (!e) return LKCUDA_OK;
+    free(e->states); free(e->ptn_freq); free(e->ptn_invar); free(e->eval); free(e->evec); free(e->inv_evec);
+    free(e->blk_eigen); free(e->blk_rate); free(e->blk_weight); free(e->tip_lh); free(e->arena); free(e->scale);
+    free(e->theta); free(e->pattern_lh); free(e->pattern_lh_cat); free(e->theta_scale_num);
+    free(e);
+    return LKCUDA_OK;
+}
+
+int lkcuda_memory_bytes(const lkcuda_engine *e, uint64_t *bytes) {
+    if (!e || !bytes) return LKCUDA_ERR_ARG;
+    *bytes = 0;
+    return LKCUDA_OK;
+}
+int lkcuda_set_stream(lkcuda_engine *e, void *s) { (void)s; return e ? LKCUDA_OK : LKCUDA_ERR_ARG; }
+int lkcuda_synchronize(lkcuda_engine *e) { return e ? LKCUDA_OK : LKCUDA_ERR_ARG; }
+
+int lkcuda_set_tip_states(lkcuda_engine *e, const uint8_t *states) {
+    if (!e || !states) return LKCUDA_ERR_ARG;
+    size_t n = (size_t)e->cfg.ntaxa * e->nptn_all;
+    for (size_t i = 0; i < n; i++)
+        if (states[i] > e->cfg.state_unknown) return fail(e, LKCUDA_ERR_ARG, "tip state out of range");
+    memcpy(e->states, states, n);
+    return LKCUDA_OK;
+}
+
+int lkcuda_set_pattern_weights(lkcuda_engine *e, const double *ptn_freq, const double *ptn_invar) {
+    if (!e || !ptn_freq || !ptn_invar) return LKCUDA_ERR_ARG;
+    memcpy(e->ptn_freq, ptn_freq, (size_t)e->cfg.nptn * 8);
+    memcpy(e->ptn_invar, ptn_invar, e->nptn_all * 8);
+    return LKCUDA_OK;
+}
+
+int lkcuda_set_model(lkcuda_engine *e, const double *eval, const double *evec, const double *inv_evec,
+                     const int32_t *blk_eigen, const double *blk_rate, const double *blk_weight,
+                     const double *tip_partial_lh) {
+    if (!e || !eval || !evec || !inv_evec || !blk_eigen || !blk_rate || !blk_weight || !tip_partial_lh)
+        return LKCUDA_ERR_ARG;
+    for (size_t k = 0; k < e->K; k++)
+        if (blk_eigen[k] < 0 || (size_t)blk_eigen[k] >= e->E) return fail(e, LKCUDA_ERR_ARG, "blk_eigen out of range");
+    memcpy(e->eval, eval, e->E * e->S * 8);
+    memcpy(e->evec, evec, e->E * e->S * e->S * 8);
+    memcpy(e->inv_evec, inv_evec, e->E * e->S * e->S * 8);
+    memcpy(e->blk_eigen, blk_eigen, e->K * 4);
+    memcpy(e->blk_rate, blk_rate, e->K * 8);
+    memcpy(e->blk_weight, blk_weight, e->K * 8);
+    memcpy(e->tip_lh, tip_partial_lh, (size_t)(e->cfg.state_unknown + 1) * e->E * e->S * 8);
+    e->theta_ready = 0;
+    return LKCUDA_OK;
+}
+
+static double *vec_lh(lkcuda_engine *e, int32_t v) { return e->arena + (size_t)v * e->nptn_all * e->block; }
+static int16_t *vec_sc(lkcuda_engine *e, int32_t v) { return e->scale + (size_t)v * e->nptn_all; }
+static int bad_end(lkcuda_engine *e, int32_t id) {
+    return id >= 0 ? id >= e->cfg.nvec : LKCUDA_TIP_TAXON(id) >= e->cfg.ntaxa;
+}
+
+/* echild[k][x][i] = evec[e(k)][x][i] * exp(eval[e(k)][i] * rate_k * len)   (phylotreesse.cpp:654-663) */
+static void build_echild(lkcuda_engine *e, double len, double *echild) {
+    size_t S = e->S;
+    for (size_t k = 0; k < e->K; k++) {
+        const double *eval = e->eval + (size_t)e->blk_eigen[k] * S;
+        const double *evec = e->evec + (size_t)e->blk_eigen[k] * S * S;
+        double len_child = e->blk_rate[k] * len;
+        for (size_t x = 0; x < S; x++)
+            for (size_t i = 0; i < S; i++)
+                echild[k * S * S + x * S + i] = evec[x * S + i] * exp(eval[i] * len_child);
+    }
+}
+
+/* partial_lh_leaf[state][k][x] = sum_i echild[k][x][i] * tip_partial_lh[state][e(k)][i]; unknown row = 1
+   (phylotreesse.cpp:666-683; mixture indexing phylokernelmixture.h:150) */
+static void build_leaf_table(lkcuda_engine *e, const double *echild, double *tab) {
+    size_t S = e->S, SU = (size_t)e->cfg.state_unknown;
+    for (size_t st = 0; st < SU; st++)
+        for (size_t k = 0; k < e->K; k++) {
+            const double *tip = e->tip_lh + (st * e->E + (size_t)e->blk_eigen[k]) * S;
+            for (size_t x = 0; x < S; x++) {
+                double v = 0.0;
+                for (size_t i = 0; i < S; i++) v += echild[k * S * S + x * S + i] * tip[i];
+                tab[st * e->block + k * S + x] = v;
+            }
+        }
+    for (size_t x = 0; x < e->block; x++) tab[SU * e->block + x] = 1.0;
+}
+
+/* the scaling epilogue shared by all cases (phylokernel.h:380-392; generic phylotreesse.cpp:893-919) */
+static void scale_pattern(lkcuda_engine *e, double *partial_lh, int16_t *scale_num, size_t ptn, double lh_max) {
+    size_t S = e->S;
+    if (!(lh_max < SCALING_THRESHOLD)) return;
+    if ((e->cfg.flags & LKCUDA_FLAG_ZERO_GUARD) && lh_max == 0.0) {
+        for (size_t k = 0; k < e->K; k++)
+            memcpy(&partial_lh[k * S], e->tip_lh + ((size_t)e->cfg.state_unknown * e->E + (size_t)e->blk_eigen[k]) * S, S * 8);
+        scale_num[ptn] += 4;
+        return;
+    }
+    if ((e->cfg.flags & LKCUDA_FLAG_SCALE_IGNORES_INVAR) || e->ptn_invar[ptn] == 0.0) {
+        for (size_t i = 0; i < e->block; i++) partial_lh[i] *= SCALING_THRESHOLD_INVER;
+        scale_num[ptn] += 1;
+    }
+}
+
+static int partial_one(lkcuda_engine *e, const lkcuda_partial_op *op) {
+    size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all, SU = (size_t)e->cfg.state_unknown;
+    if (op->dst < 0 || op->dst >= e->cfg.nvec || bad_end(e, op->left) || bad_end(e, op->right))
+        return fail(e, LKCUDA_ERR_ARG, "partial op: bad vector / taxon id");
+    if (!LKCUDA_IS_TIP(op->left) && LKCUDA_IS_TIP(op->right))
+        return fail(e, LKCUDA_ERR_ARG, "partial op: a leaf child must be 'left' (phylokernel.h:116-121)");
+    double *eleft = (double *)malloc(block * S * 8), *eright = (double *)malloc(block * S * 8);
+    double *tab_l = NULL, *tab_r = NULL;
+    double *tmp = (double *)malloc(S * 8);
+    build_echild(e, op->len_left, eleft);
+    build_echild(e, op->len_right, eright);
+    if (LKCUDA_IS_TIP(op->left)) { tab_l = (double *)malloc((SU + 1) * block * 8); build_leaf_table(e, eleft, tab_l); }
+    if (LKCUDA_IS_TIP(op->right)) { tab_r = (double *)malloc((SU + 1) * block * 8); build_leaf_table(e, eright, tab_r); }
+    double *dst = vec_lh(e, op->dst);
+    int16_t *dsc = vec_sc(e, op->dst);
+    const uint8_t *st_l = LKCUDA_IS_TIP(op->left) ? e->states + (size_t)LKCUDA_TIP_TAXON(op->left) * nptn : NULL;
+    const uint8_t *st_r = LKCUDA_IS_TIP(op->right) ? e->states + (size_t)LKCUDA_TIP_TAXON(op->right) * nptn : NULL;
+    const double *lh_l = st_l ? NULL : vec_lh(e, op->left), *lh_r = st_r ? NULL : vec_lh(e, op->right);
+    const int16_t *sc_l = st_l ? NULL : vec_sc(e, op->left), *sc_r = st_r ? NULL : vec_sc(e, op->right);
+
+    for (size_t ptn = 0; ptn < nptn; ptn++) {
+        double *partial_lh = dst + ptn * block;
+        double lh_max = 0.0;
+        /* scale_num: 0 for tip-tip (phylokernel.h:247), right's for tip-internal (:290), sum otherwise (:418) */
+        dsc[ptn] = (int16_t)((sc_l ? sc_l[ptn] : 0) + (sc_r ? sc_r[ptn] : 0));
+        for (size_t k = 0; k < K; k++) {
+            const double *inv_evec = e->inv_evec + (size_t)e->blk_eigen[k] * S * S;
+            for (size_t x = 0; x < S; x++) {
+                double vleft, vright;
+                if (st_l) vleft = tab_l[(size_t)st_l[ptn] * block + k * S + x];
+                else {
+                    vleft = 0.0;
+                    for (size_t i = 0; i < S; i++) vleft += eleft[k * S * S + x * S + i] * lh_l[ptn * block + k * S + i];
+                }
+                if (st_r) vright = tab_r[(size_t)st_r[ptn] * block + k * S + x];
+                else {
+                    vright = 0.0;
+                    for (size_t i = 0; i < S; i++) vright += eright[k * S * S + x * S + i] * lh_r[ptn * block + k * S + i];
+                }
+                tmp[x] = vleft * vright;
+            }
+            for (size_t i = 0; i < S; i++) {
+                double res = 0.0;
+                for (size_t x = 0; x < S; x++) res += tmp[x] * inv_evec[i * S + x];
+                partial_lh[k * S + i] = res;
+                if (fabs(res) > lh_max) lh_max = fabs(res);
+            }
+        }
+        /* tip-tip never scales (phylokernel.h:246-281) */
+        if (!(st_l && st_r)) scale_pattern(e, partial_lh, dsc, ptn, lh_max);
+    }
+    free(eleft); free(eright); free(tab_l); free(tab_r); free(tmp);
+    e->launches++;
+    return LKCUDA_OK;
+}
+
+int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t nops,
+                         const int32_t *level_start, int32_t nlevels) {
+    if (!e || (nops && !ops) || nops < 0) return LKCUDA_ERR_ARG;
+    if (level_start) {
+        if (nlevels < 0 || level_start[0] != 0 || level_start[nlevels] != nops) return fail(e, LKCUDA_ERR_ARG, "bad level_start");
+        for (int32_t l = 0; l < nlevels; l++)
+            if (level_start[l] > level_start[l + 1]) return fail(e, LKCUDA_ERR_ARG, "bad level_start");
+    }
+    for (int32_t i = 0; i < nops; i++) {
+        int rc = partial_one(e, &ops[i]);
+        if (rc) return rc;
+    }
+    e->theta_ready = 0;
+    return LKCUDA_OK;
+}
+
+/* multifurcating node, phylotreesse.cpp:702-806 */
+int lkcuda_partial_multi(lkcuda_engine *e, int32_t dst, int32_t nchild, const int32_t *child, const double *child_len) {
+    if (!e || !child || !child_len || nchild < 2 || dst < 0 || dst >= e->cfg.nvec) return LKCUDA_ERR_ARG;
+    size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all, SU = (size_t)e->cfg.state_unknown;
+    for (int32_t c = 0; c < nchild; c++) if (bad_end(e, child[c])) return fail(e, LKCUDA_ERR_ARG, "bad child");
+    double *ech = (double *)malloc((size_t)nchild * block * S * 8);
+    double *tabs = (double *)malloc((size_t)nchild * (SU + 1) * block * 8);
+    double *all = (double *)malloc(block * 8);
+    for (int32_t c = 0; c < nchild; c++) {
+        build_echild(e, child_len[c], ech + (size_t)c * block * S);
+        if (LKCUDA_IS_TIP(child[c])) build_leaf_table(e, ech + (size_t)c * block * S, tabs + (size_t)c * (SU + 1) * block);
+    }
+    double *dlh = vec_lh(e, dst); int16_t *dsc = vec_sc(e, dst);
+    for (size_t ptn = 0; ptn < nptn; ptn++) {
+        for (size_t i = 0; i < block; i++) all[i] = 1.0;
+        dsc[ptn] = 0;
+        for (int32_t c = 0; c < nchild; c++) {
+            if (LKCUDA_IS_TIP(child[c])) {
+                size_t st = e->states[(size_t)LKCUDA_TIP_TAXON(child[c]) * nptn + ptn];
+                const double *t = tabs + (size_t)c * (SU + 1) * block + st * block;
+                for (size_t i = 0; i < block; i++) all[i] *= t[i];
+            } else {
+                const double *lh = vec_lh(e, child[c]) + ptn * block;
+                const double *ec = ech + (size_t)c * block * S;
+                dsc[ptn] = (int16_t)(dsc[ptn] + vec_sc(e, child[c])[ptn]);
+                for (size_t k = 0; k < K; k++)
+                    for (size_t x = 0; x < S; x++) {
+                        double v = 0.0;
+                        for (size_t i = 0; i < S; i++) v += ec[k * S * S + x * S + i] * lh[k * S + i];
+                        all[k * S + x] *= v;
+                    }
+            }
+        }
+        double lh_max = 0.0, *partial_lh = dlh + ptn * block;
+        for (size_t k = 0; k < K; k++) {
+            const double *inv_evec = e->inv_evec + (size_t)e->blk_eigen[k] * S * S;
+            for (size_t i = 0; i < S; i++) {
+                double res = 0.0;
+                for (size_t x = 0; x < S; x++) res += all[k * S + x] * inv_evec[i * S + x];
+                partial_lh[k * S + i] = res;
+                if (fabs(res) > lh_max) lh_max = fabs(res);
+            }
+        }
+        scale_pattern(e, partial_lh, dsc, ptn, lh_max);
+    }
+    free(ech); free(tabs); free(all);
+    e->launches++; e->theta_ready = 0;
+    return LKCUDA_OK;
+}
+
+/* lh_scale_factor of a vector = sum over its patterns of LOG_SCALING_THRESHOLD * ptn_freq * scale_num
+   (closed form of the recursion phylokernel.h:157,389,395,471,477) */
+static double vec_scale_factor(lkcuda_engine *e, int32_t v) {
+    if (v < 0) return 0.0;
+    const int16_t *sc = vec_sc(e, v);
+    double s = 0.0;
+    for (size_t p = 0; p < (size_t)e->cfg.nptn; p++)
+        if (sc[p]) s += LOG_SCALING_THRESHOLD * e->ptn_freq[p] * (double)sc[p];
+    return s;
+}
+
+int lkcuda_vector_scale_factor(lkcuda_engine *e, int32_t vec, double *out) {
+    if (!e || !out || vec < 0 || vec >= e->cfg.nvec) return LKCUDA_ERR_ARG;
+    *out = vec_scale_factor(e, vec);
+    return LKCUDA_OK;
+}
+
+static void build_val(lkcuda_engine *e, double len, double *val0, double *val1, double *val2) {
+    /* phylokernel.h:521-532, 767-775; mixture weight phylokernelmixture.h:505,766 */
+    for (size_t k = 0; k < e->K; k++) {
+        const double *eval = e->eval + (size_t)e->blk_eigen[k] * e->S;
+        for (size_t i = 0; i < e->S; i++) {
+            double cof = eval[i] * e->blk_rate[k];
+            double val = exp(cof * len) * e->blk_weight[k];
+            val0[k * e->S + i] = val;
+            if (val1) { val1[k * e->S + i] = cof * val; val2[k * e->S + i] = cof * (cof * val); }
+        }
+    }
+}
+
+/* common tail of branch lnL and lnL-from-buffer: log, pattern_lh, NaN repair, +ASC (phylokernel.h:828-866, 1009-1016) */
+static void finish_lnl(lkcuda_engine *e, const double *lh_ptn_all, const int16_t *sum_scale_unobs, double scale_sum) {
+    size_t P = (size_t)e->cfg.nptn, U = (size_t)e->cfg.nunobs;
+    double tree_lh = 0.0, nrep = 0.0;
+    for (size_t p = 0; p < P; p++) {
+        double l = log(fabs(lh_ptn_all[p]));
+        if (isnan(l) || isinf(l)) { l = LOG_SCALING_THRESHOLD * 4; nrep += 1.0; }
+        e->pattern_lh[p] = l;
+        tree_lh += l * e->ptn_freq[p];
+    }
+    tree_lh += scale_sum;
+    double prob_const = 0.0;
+    if (U) {
+        for (size_t u = 0; u < U; u++) {
+            double l = lh_ptn_all[P + u];                              /* sum part only, ptn_invar not yet added */
+            if (sum_scale_unobs[u] >= 1) l *= SCALING_THRESHOLD;      /* bugfix 2016-01-21, phylokernel.h:895-900 */
+            prob_const += l + e->ptn_invar[P + u];
+        }
+        double lc = log(1.0 - prob_const);
+        for (size_t p = 0; p < P; p++) e->pattern_lh[p] -= lc;
+        tree_lh -= (double)e->cfg.nsite * lc;
+    }
+    memset(e->result, 0, sizeof(e->result));
+    e->result[LKCUDA_R_LNL] = tree_lh;
+    e->result[LKCUDA_R_PROB_CONST] = prob_const;
+    e->result[LKCUDA_R_NREPAIRED] = nrep;
+    e->result[LKCUDA_R_SCALE_SUM] = scale_sum;
+}
+
+int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result) {
+    if (!e || node < 0 || node >= e->cfg.nvec || bad_end(e, dad)) return LKCUDA_ERR_ARG;
+    size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all, P = (size_t)e->cfg.nptn;
+    double *val = (double *)malloc(block * 8);
+    double *lh_all = (double *)malloc((nptn + 1) * 8);
+    int16_t *ssn = (int16_t *)calloc((size_t)e->cfg.nunobs + 1, 2);
+    build_val(e, len, val, NULL, NULL);
+    const double *lh_node = vec_lh(e, node);
+    const uint8_t *st = LKCUDA_IS_TIP(dad) ? e->states + (size_t)LKCUDA_TIP_TAXON(dad) * nptn : NULL;
+    const double *lh_dad = st ? NULL : vec_lh(e, dad);
+    for (size_t ptn = 0; ptn < nptn; ptn++) {
+        double lh_ptn = 0.0;
+        for (size_t k = 0; k < K; k++) {
+            double lh_cat = 0.0;
+            if (st) {   /* phylotreesse.cpp:1206-1237: lh_node = val * tip_partial_lh[state] */
+                const double *tip = e->tip_lh + ((size_t)st[ptn] * e->E + (size_t)e->blk_eigen[k]) * S;
+                for (size_t i = 0; i < S; i++) lh_cat += (val[k * S + i] * tip[i]) * lh_node[ptn * block + k * S + i];
+            } else {    /* phylotreesse.cpp:1263-1272 */
+                for (size_t i = 0; i < S; i++) lh_cat += val[k * S + i] * lh_node[ptn * block + k * S + i] * lh_dad[ptn * block + k * S + i];
+            }
+            if (ptn < P) e->pattern_lh_cat[ptn * K + k] = lh_cat;
+            lh_ptn += lh_cat;
+        }
+        lh_all[ptn] = (ptn < P) ? lh_ptn + e->ptn_invar[ptn] : lh_ptn;   /* unobserved: invar added after rescaling */
+        if (ptn >= P) ssn[ptn - P] = (int16_t)(vec_sc(e, node)[ptn] + (st ? 0 : vec_sc(e, dad)[ptn]));
+    }
+    double scale_sum = vec_scale_factor(e, node) + (st ? 0.0 : vec_scale_factor(e, dad));
+    finish_lnl(e, lh_all, ssn, scale_sum);
+    free(val); free(lh_all); free(ssn);
+    e->launches++;
+    if (result) memcpy(result, e->result, sizeof(e->result));
+    return LKCUDA_OK;
+}
+
+int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node) {
+    if (!e || node < 0 || node >= e->cfg.nvec || bad_end(e, dad)) return LKCUDA_ERR_ARG;
+    size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all, P = (size_t)e->cfg.nptn;
+    const double *lh_node = vec_lh(e, node);
+    if (LKCUDA_IS_TIP(dad)) {   /* phylotreesse.cpp:1046-1063 */
+        const uint8_t *st = e->states + (size_t)LKCUDA_TIP_TAXON(dad) * nptn;
+        for (size_t ptn = 0; ptn < nptn; ptn++)
+            for (size_t k = 0; k < K; k++) {
+                const double *tip = e->tip_lh + ((size_t)st[ptn] * e->E + (size_t)e->blk_eigen[k]) * S;
+                for (size_t i = 0; i < S; i++) e->theta[ptn * block + k * S + i] = tip[i] * lh_node[ptn * block + k * S + i];
+            }
+    } else {                    /* phylotreesse.cpp:1072-1079 */
+        const double *lh_dad = vec_lh(e, dad);
+        for (size_t i = 0; i < nptn * block; i++) e->theta[i] = lh_node[i] * lh_dad[i];
+    }
+    e->theta_scale_sum = vec_scale_factor(e, node) + (LKCUDA_IS_TIP(dad) ? 0.0 : vec_scale_factor(e, dad));
+    for (size_t u = 0; u < (size_t)e->cfg.nunobs; u++)
+        e->theta_scale_num[u] = (int16_t)(vec_sc(e, node)[P + u] + (LKCUDA_IS_TIP(dad) ? 0 : vec_sc(e, dad)[P + u]));
+    e->theta_ready = 1;
+    e->launches++;
+    return LKCUDA_OK;
+}
+
+static int derv_at(lkcuda_engine *e, double len, double *df_out, double *ddf_out) {
+    size_t block = e->block, nptn = e->nptn_all, P = (size_t)e->cfg.nptn;
+    double *val0 = (double *)malloc(block * 8), *val1 = (double *)malloc(block * 8), *val2 = (double *)malloc(block * 8);
+    build_val(e, len, val0, val1, val2);
+    double my_df = 0.0, my_ddf = 0.0, prob_const = 0.0, df_const = 0.0, ddf_const = 0.0;
+    for (size_t ptn = 0; ptn < nptn; ptn++) {   /* phylotreesse.cpp:1106-1132 */
+        double lh_ptn = e->ptn_invar[ptn], df_ptn = 0.0, ddf_ptn = 0.0;
+        const double *theta = e->theta + ptn * block;
+        for (size_t i = 0; i < block; i++) {
+            lh_ptn += val0[i] * theta[i];
+            df_ptn += val1[i] * theta[i];
+            ddf_ptn += val2[i] * theta[i];
+        }
+        lh_ptn = fabs(lh_ptn);
+        if (ptn < P) {
+            double df_frac = df_ptn / lh_ptn, ddf_frac = ddf_ptn / lh_ptn, freq = e->ptn_freq[ptn];
+            double tmp1 = df_frac * freq, tmp2 = ddf_frac * freq;
+            my_df += tmp1;
+            my_ddf += tmp2 - tmp1 * df_frac;
+        } else {
+            prob_const += lh_ptn; df_const += df_ptn; ddf_const += ddf_ptn;
+        }
+    }
+    if (isnan(my_df) || isinf(my_df)) { my_df = 0.0; my_ddf = 0.0; }   /* phylokernel.h:647-651 */
+    if (P < nptn) {                                                    /* phylokernel.h:719-724 */
+        prob_const = 1.0 - prob_const;
+        double df_frac = df_const / prob_const, ddf_frac = ddf_const / prob_const;
+        my_df += (double)e->cfg.nsite * df_frac;
+        my_ddf += (double)e->cfg.nsite * (ddf_frac + df_frac * df_frac);
+    }
+    free(val0); free(val1); free(val2);
+    *df_out = my_df; *ddf_out = my_ddf;
+    e->launches++;
+    return LKCUDA_OK;
+}
+
+int lkcuda_derv(lkcuda_engine *e, double len, double *result) {
+    if (!e) return LKCUDA_ERR_ARG;
+    if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_derv: theta_all not built");
+    double df, ddf;
+    derv_at(e, len, &df, &ddf);
+    memset(e->result, 0, sizeof(e->result));
+    e->result[LKCUDA_R_DF] = df; e->result[LKCUDA_R_DDF] = ddf;
+    if (result) memcpy(result, e->result, sizeof(e->result));
+    return LKCUDA_OK;
+}
+
+int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result) {
+    if (!e) return LKCUDA_ERR_ARG;
+    if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lnl_from_buffer: theta_all not built");
+    size_t block = e->block, nptn = e->nptn_all;
+    double *val0 = (double *)malloc(block * 8);
+    double *lh_all = (double *)malloc((nptn + 1) * 8);
+    build_val(e, len, val0, NULL, NULL);
+    for (size_t ptn = 0; ptn < nptn; ptn++) {   /* phylokernel.h:1067-1090 */
+        double lh = 0.0;
+        const double *theta = e->theta + ptn * block;
+        for (size_t i = 0; i < block; i++) lh += val0[i] * theta[i];
+        lh_all[ptn] = (ptn < (size_t)e->cfg.nptn) ? lh + e->ptn_invar[ptn] : lh;
+    }
+    finish_lnl(e, lh_all, e->theta_scale_num, e->theta_scale_sum);
+    free(val0); free(lh_all);
+    e->launches++;
+    if (result) memcpy(result, e->result, sizeof(e->result));
+    return LKCUDA_OK;
+}
+
+/* Optimization::minimizeNewton (optimization.cpp:388-465) with computeFuncDerv = -(df, ddf) (phylotree.cpp:2135-2146) */
+int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, double xacc, int32_t maxNRStep, double *out) {
+    if (!e || !out) return LKCUDA_ERR_ARG;
+    if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_newton_branch: theta_all not built");
+    int j, nev = 0;
+    double df, dx, dxold, f, temp, xh, xl, rts, rts_old, d2l;
+    (void)dxold;
+#define FUNC_DERV(x) do { double a_, b_; derv_at(e, (x), &a_, &b_); f = -a_; df = -b_; nev++; out[3] = (x); } while (0)
+#define RETURN(x) do { out[0] = (x); out[1] = d2l; out[2] = (double)nev; return LKCUDA_OK; } while (0)
+    rts = xguess;
+    if (rts < x1) rts = x1;
+    if (rts > x2) rts = x2;
+    FUNC_DERV(rts);
+    d2l = df;
+    if (!isfinite(f) || !isfinite(df)) return fail(e, LKCUDA_ERR_STATE, "Wrong computeFuncDerv");
+    if (df >= 0.0 && fabs(f) < xacc) RETURN(rts);
+    if (f < 0.0) { xl = rts; xh = x2; } else { xh = rts; xl = x1; }
+    dx = dxold = fabs(xh - xl);
+    for (j = 1; j <= maxNRStep; j++) {
+        rts_old = rts;
+        if ((df <= 0.0) || (((rts - xh) * df - f) * ((rts - xl) * df - f) >= 0.0)) {
+            dxold = dx; dx = 0.5 * (xh - xl); rts = xl + dx; d2l = df;
+            if (xl == rts) RETURN(rts);
+        } else {
+            dxold = dx; dx = f / df; temp = rts; rts -= dx; d2l = df;
+            if (temp == rts) RETURN(rts);
+        }
+        if (fabs(dx) < xacc || (j == maxNRStep)) RETURN(rts_old);
+        FUNC_DERV(rts);
+        if (!isfinite(f) || !isfinite(df)) return fail(e, LKCUDA_ERR_STATE, "Wrong computeFuncDerv");
+        if (df > 0.0 && fabs(f) < xacc) { d2l = df; RETURN(rts); }
+        if (f < 0.0) xl = rts; else xh = rts;
+    }
+    return fail(e, LKCUDA_ERR_STATE, "Maximum number of iterations exceeded in minimizeNewton");
+#undef FUNC_DERV
+#undef RETURN
+}
+
+int lkcuda_read_result(lkcuda_engine *e, double *result) {
+    if (!e || !result) return LKCUDA_ERR_ARG;
+    memcpy(result, e->result, sizeof(e->result));
+    return LKCUDA_OK;
+}
+int lkcuda_result_device_ptr(lkcuda_engine *e, void **p) { if (!e || !p) return LKCUDA_ERR_ARG; *p = e->result; return LKCUDA_OK; }
+
+int lkcuda_fetch_pattern_lh(lkcuda_engine *e, double *dst) {
+    if (!e || !dst) return LKCUDA_ERR_ARG;
+    memcpy(dst, e->pattern_lh, (size_t)e->cfg.nptn * 8);
+    return LKCUDA_OK;
+}
+int lkcuda_fetch_pattern_lh_cat(lkcuda_engine *e, double *dst) {
+    if (!e || !dst) return LKCUDA_ERR_ARG;
+    memcpy(dst, e->pattern_lh_cat, (size_t)e->cfg.nptn * e->K * 8);
+    return LKCUDA_OK;
+}
+int lkcuda_fetch_vector(lkcuda_engine *e, int32_t vec, double *partial_lh, int16_t *scale_num) {
+    if (!e || vec < 0 || vec >= e->cfg.nvec) return LKCUDA_ERR_ARG;
+    if (partial_lh) memcpy(partial_lh, vec_lh(e, vec), e->nptn_all * e->block * 8);
+    if (scale_num) memcpy(scale_num, vec_sc(e, vec), e->nptn_all * 2);
+    return LKCUDA_OK;
+}
+int lkcuda_store_vector(lkcuda_engine *e, int32_t vec, const double *partial_lh, const int16_t *scale_num) {
+    if (!e || vec < 0 || vec >= e->cfg.nvec) return LKCUDA_ERR_ARG;
+    if (partial_lh) memcpy(vec_lh(e, vec), partial_lh, e->nptn_all * e->block * 8);
+    if (scale_num) memcpy(vec_sc(e, vec), scale_num, e->nptn_all * 2);
+    return LKCUDA_OK;
+}
+int lkcuda_fetch_theta(lkcuda_engine *e, double *theta) {
+    if (!e || !theta) return LKCUDA_ERR_ARG;
+    memcpy(theta, e->theta, e->nptn_all * e->block * 8);
+    return LKCUDA_OK;
+}
+int lkcuda_vector_device_ptr(lkcuda_engine *e, int32_t vec, void **partial_lh, void **scale_num) {
+    if (!e || vec < 0 || vec >= e->cfg.nvec) return LKCUDA_ERR_ARG;
+    if (partial_lh) *partial_lh = vec_lh(e, vec);
+    if (scale_num) *scale_num = vec_sc(e, vec);
+    return LKCUDA_OK;
+}
+int lkcuda_launch_count(const lkcuda_engine *e, uint64_t *c) { if (!e || !c) return LKCUDA_ERR_ARG; *c = e->launches; return LKCUDA_OK; }
+int lkcuda_algorithmic_bytes(const lkcuda_engine *e, uint64_t *b) { if (!e || !b) return LKCUDA_ERR_ARG; *b = e->bytes; return LKCUDA_OK; }
+int lkcuda_reset_counters(lkcuda_engine *e) { if (!e) return LKCUDA_ERR_ARG; e->launches = 0; e->bytes = 0; return LKCUDA_OK; }

@@ -1,0 +1,330 @@
+/*
+ * ref_harness — TEST INFRASTRUCTURE (oracle), not product code.
+ *
+ * Drives the UNMODIFIED reference PhyloTree (IQ-TREE 1.4.3-beta, compiled by oracle/Makefile.ref
+ * from /root/reference) as a library and
+ *   (1) dumps golden fixtures: the exact kernel inputs the reference sees (pattern matrix, eigen
+ *       system, rates, tip table, tree adjacency) and the reference's own outputs (lnL, _pattern_lh,
+ *       _pattern_lh_cat, df/ddf, partial_lh / scale_num of every computed neighbour, branch lengths
+ *       after optimizeAllBranches, the branch traversal order);
+ *   (2) times the reference's CPU kernels (AVX + OpenMP) for bench.py --impl reference.
+ *
+ * The set-up sequence mirrors runTreeReconstruction (phyloanalysis.cpp:1611-1726).
+ *
+ * usage: ref_harness dump <outdir> <iqtree args: -s aln -m MODEL -te tree -nt N ...>
+ *        ref_harness time <lnl_reps> <derv_reps> <oab_reps> <iqtree args ...>
+ */
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <string>
+#include <vector>
+#include <map>
+#include <set>
+#include <sstream>
+#include <fstream>
+#include <iostream>
+#include <iomanip>
+#include <algorithm>
+#include <sys/stat.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#define private public
+#define protected public
+#include "phylotree.h"
+#include "iqtree.h"
+#include "phyloanalysis.h"
+#include "tools.h"
+#include "alignment.h"
+#include "checkpoint.h"
+#include "timeutil.h"
+#include "model/modelfactory.h"
+#include "model/modelmixture.h"
+#include "model/rateheterogeneity.h"
+#include "vectorclass/instrset.h"
+#undef private
+#undef protected
+
+extern int instruction_set;   // pda.cpp:2135
+
+static std::string g_out;
+
+static void wbin(const std::string &name, const void *p, size_t bytes) {
+    std::string fn = g_out + "/" + name;
+    FILE *f = fopen(fn.c_str(), "wb");
+    if (!f) { perror(fn.c_str()); exit(3); }
+    if (bytes) fwrite(p, 1, bytes, f);
+    fclose(f);
+}
+
+static void collectNodes(Node *node, Node *dad, std::vector<Node*> &out) {
+    out.push_back(node);
+    FOR_NEIGHBOR_IT(node, dad, it) collectNodes((*it)->node, node, out);
+}
+
+/* adjacency dump: one line per (node, neighbour) in the reference's own neighbour order */
+static void dumpAdjacency(IQTree *tree, const std::string &name) {
+    std::vector<Node*> nodes;
+    collectNodes(tree->root, NULL, nodes);
+    std::ofstream f((g_out + "/" + name).c_str());
+    f << std::setprecision(17);
+    f << "root " << tree->root->id << " nodes " << nodes.size() << " leaves " << tree->leafNum << "\n";
+    for (size_t i = 0; i < nodes.size(); i++) {
+        Node *n = nodes[i];
+        f << "node " << n->id << " " << (n->isLeaf() ? 1 : 0) << " " << (n->name.empty() ? "-" : n->name)
+          << " " << n->neighbors.size();
+        for (size_t k = 0; k < n->neighbors.size(); k++)
+            f << " " << n->neighbors[k]->node->id << " " << n->neighbors[k]->length;
+        f << "\n";
+    }
+}
+
+static void dumpPartials(IQTree *tree, Node *node, Node *dad, std::ofstream &idx, size_t nptn, size_t block) {
+    FOR_NEIGHBOR_IT(node, dad, it) {
+        PhyloNeighbor *nei = (PhyloNeighbor*)(*it);
+        PhyloNeighbor *back = (PhyloNeighbor*)(*it)->node->findNeighbor(node);
+        PhyloNeighbor *both[2] = {nei, back};
+        Node *from[2] = {node, (*it)->node};
+        for (int k = 0; k < 2; k++) {
+            PhyloNeighbor *b = both[k];
+            // neighbour b: stored at from[k], pointing to b->node; holds partial of subtree rooted at b->node
+            if ((b->partial_lh_computed & 1) && b->partial_lh && !b->node->isLeaf()) {
+                std::ostringstream nm;
+                nm << "partial_" << from[k]->id << "_" << b->node->id;
+                wbin(nm.str() + ".f64", b->partial_lh, nptn * block * sizeof(double));
+                wbin(nm.str() + ".i16", b->scale_num, nptn * sizeof(UBYTE));
+                idx << from[k]->id << " " << b->node->id << " " << std::setprecision(17) << b->lh_scale_factor << "\n";
+            }
+        }
+        dumpPartials(tree, (*it)->node, node, idx, nptn, block);
+    }
+}
+
+static IQTree *setup(int argc, char **argv, Params &params) {
+    parseArg(argc, argv, params);
+    instruction_set = instrset_detect();
+#ifdef _OPENMP
+    if (params.num_threads) omp_set_num_threads(params.num_threads);
+    omp_set_nested(false);
+#endif
+    init_random(params.ran_seed, false);
+    Alignment *aln = new Alignment(params.aln_file, params.sequence_type, params.intype);
+    IQTree *tree = new IQTree(aln);
+    tree->setCheckpoint(new Checkpoint);
+    if (params.min_branch_length <= 0.0) {       // phyloanalysis.cpp:2488-2497
+        params.min_branch_length = 1e-6;
+        if (tree->getAlnNSite() >= 100000)
+            params.min_branch_length = 0.1 / (tree->getAlnNSite());
+    }
+    tree->setParams(&params);
+    std::string dist_file;
+    tree->computeInitialTree(dist_file, params.SSE);
+    tree->setRootNode(params.root);
+    ModelsBlock *mb = readModelsDefinition(params);
+    tree->initSettings(params);
+    tree->initializeModel(params, mb);
+    delete mb;
+    tree->initializeAllPartialLh();
+    return tree;
+}
+
+static const char *familyName(IQTree *tree) {
+    if (tree->getModel()->isMixture())
+        return tree->getModelFactory()->fused_mix_rate ? "mixrate" : "mixture";
+    return "plain";
+}
+
+static int do_dump(int argc, char **argv) {
+    g_out = argv[2];
+    mkdir(g_out.c_str(), 0755);
+    std::vector<char*> args; args.push_back(argv[0]);
+    for (int i = 3; i < argc; i++) args.push_back(argv[i]);
+    Params &params = Params::getInstance();
+    IQTree *tree = setup((int)args.size(), &args[0], params);
+    Alignment *aln = tree->aln;
+    ModelSubst *model = tree->getModel();
+    RateHeterogeneity *rate = tree->getRate();
+    ModelFactory *mf = tree->getModelFactory();
+
+    size_t S = aln->num_states, C = rate->getNRate(), M = model->getNMixtures();
+    bool fused = mf->fused_mix_rate;
+    size_t P = aln->size(), U = mf->unobserved_ptns.size(), nptn = P + U, ntaxa = aln->getNSeq();
+    size_t block = tree->getModel()->isMixture() && !fused ? S * C * M : S * C;
+    size_t E = M;   // number of eigensystems
+
+    /* ---- kernel inputs ---- */
+    std::vector<unsigned char> states(ntaxa * nptn);
+    for (size_t t = 0; t < ntaxa; t++) {
+        for (size_t p = 0; p < P; p++) states[t * nptn + p] = (unsigned char)(aln->at(p))[t];
+        for (size_t u = 0; u < U; u++) states[t * nptn + P + u] = (unsigned char)mf->unobserved_ptns[u];
+    }
+    wbin("tip_states.u8", &states[0], states.size());
+    std::vector<int> site2ptn(aln->getNSite());
+    for (int s = 0; s < aln->getNSite(); s++) site2ptn[s] = aln->getPatternID(s);
+    wbin("site_pattern.i32", &site2ptn[0], site2ptn.size() * sizeof(int));
+    std::vector<int> cc(P);
+    for (size_t p = 0; p < P; p++) cc[p] = (int)(signed char)aln->at(p).const_char;
+    wbin("const_char.i32", &cc[0], P * sizeof(int));
+    {
+        std::ofstream f((g_out + "/taxa.txt").c_str());
+        for (size_t t = 0; t < ntaxa; t++) f << aln->getSeqName(t) << "\n";
+    }
+    wbin("eval.f64", model->getEigenvalues(), E * S * sizeof(double));
+    wbin("evec.f64", model->getEigenvectors(), E * S * S * sizeof(double));
+    wbin("inv_evec.f64", model->getInverseEigenvectors(), E * S * S * sizeof(double));
+    std::vector<double> rates(C), props(C), mixprops(M, 1.0), sfreq(S);
+    for (size_t c = 0; c < C; c++) { rates[c] = rate->getRate(c); props[c] = rate->getProp(c); }
+    if (model->isMixture()) for (size_t m = 0; m < M; m++) mixprops[m] = ((ModelMixture*)model)->prop[m];
+    model->getStateFrequency(&sfreq[0]);
+    wbin("rates.f64", &rates[0], C * 8); wbin("props.f64", &props[0], C * 8);
+    wbin("mixprops.f64", &mixprops[0], M * 8); wbin("state_freq.f64", &sfreq[0], S * 8);
+    dumpAdjacency(tree, "tree_adj.txt");
+    {
+        std::ofstream f((g_out + "/tree0.nwk").c_str());
+        f << std::setprecision(17);
+        tree->printTree(f, WT_BR_LEN);
+        f << "\n";
+    }
+
+    /* ---- reference outputs ---- */
+    tree->clearAllPartialLH();
+    double lnl = tree->computeLikelihood();
+    // computeTipPartialLikelihood has run now
+    wbin("tip_partial_lh.f64", tree->tip_partial_lh, (aln->STATE_UNKNOWN + 1) * S * E * sizeof(double));
+    wbin("ptn_freq.f64", tree->ptn_freq, P * 8);
+    wbin("ptn_invar.f64", tree->ptn_invar, nptn * 8);
+    wbin("pattern_lh.f64", tree->_pattern_lh, P * 8);
+    int root_from = tree->current_it_back->node->id, root_to = tree->current_it->node->id;
+    {
+        std::vector<double> plh(P);
+        double l2 = tree->computeLikelihood(&plh[0]);       // with scale_num correction
+        (void)l2;
+        wbin("pattern_lh_scaled.f64", &plh[0], P * 8);
+    }
+    {
+        std::ofstream idx((g_out + "/partials.txt").c_str());
+        dumpPartials(tree, tree->root, NULL, idx, nptn, block);
+    }
+    /* per-category pattern likelihoods via the generic kernel (phylotree.cpp:1108) */
+    {
+        tree->computePatternLhCat(WSL_RATECAT);
+        size_t ncat_tot = (model->isMixture() && !fused) ? C * M : C;
+        wbin("pattern_lh_cat.f64", tree->_pattern_lh_cat, P * ncat_tot * 8);
+        tree->clearAllPartialLH();
+        tree->computeLikelihood();
+    }
+
+    /* df/ddf on the root-leaf branch (root = tree->root, a leaf) and on every branch */
+    PhyloNode *n1 = (PhyloNode*)tree->root, *n2 = (PhyloNode*)tree->root->neighbors[0]->node;
+    double df, ddf;
+    tree->theta_computed = false;
+    tree->computeLikelihoodDerv((PhyloNeighbor*)n1->findNeighbor(n2), n1, df, ddf);
+    wbin("theta_root.f64", tree->theta_all, nptn * block * 8);
+    NodeVector nodes, nodes2;
+    tree->computeBestTraversal(nodes, nodes2);
+    std::vector<int> trav(nodes.size() * 2);
+    std::vector<double> dervs(nodes.size() * 3);
+    for (size_t j = 0; j < nodes.size(); j++) {
+        trav[2 * j] = nodes[j]->id; trav[2 * j + 1] = nodes2[j]->id;
+        double a, b;
+        tree->theta_computed = false;
+        PhyloNeighbor *nb = (PhyloNeighbor*)nodes[j]->findNeighbor(nodes2[j]);
+        tree->computeLikelihoodDerv(nb, (PhyloNode*)nodes[j], a, b);
+        tree->current_it = nb;
+        tree->current_it_back = (PhyloNeighbor*)nodes2[j]->findNeighbor(nodes[j]);
+        double fb = tree->computeLikelihoodFromBuffer();
+        dervs[3 * j] = a; dervs[3 * j + 1] = b; dervs[3 * j + 2] = fb;
+    }
+    wbin("traversal.i32", &trav[0], trav.size() * sizeof(int));
+    wbin("branch_derv.f64", &dervs[0], dervs.size() * 8);
+
+    /* one pass and full branch-length optimisation */
+    tree->clearAllPartialLH();
+    tree->current_it = tree->current_it_back = NULL;
+    tree->computeLikelihood();
+    double oab1 = tree->optimizeAllBranches(1);
+    dumpAdjacency(tree, "tree_adj_oab1.txt");
+    double oabfull = tree->optimizeAllBranches();
+    dumpAdjacency(tree, "tree_adj_oabfull.txt");
+
+    {
+        std::ofstream f((g_out + "/meta.json").c_str());
+        f << std::setprecision(17);
+        f << "{\n"
+          << " \"nstates\": " << S << ", \"ncat\": " << C << ", \"nmix\": " << M << ",\n"
+          << " \"family\": \"" << familyName(tree) << "\", \"block\": " << block << ",\n"
+          << " \"nptn\": " << P << ", \"nunobs\": " << U << ", \"ntaxa\": " << ntaxa << ", \"nsite\": " << aln->getNSite() << ",\n"
+          << " \"state_unknown\": " << (int)aln->STATE_UNKNOWN << ", \"seq_type\": " << (int)aln->seq_type << ",\n"
+          << " \"model\": \"" << tree->getModelName() << "\", \"p_invar\": " << rate->getPInvar() << ",\n"
+          << " \"min_branch_length\": " << params.min_branch_length << ", \"max_branch_length\": " << params.max_branch_length << ",\n"
+          << " \"root_branch\": [" << root_from << ", " << root_to << "],\n"
+          << " \"lnl\": " << lnl << ", \"df_root\": " << df << ", \"ddf_root\": " << ddf << ",\n"
+          << " \"derv_branch\": [" << n1->id << ", " << n2->id << "],\n"
+          << " \"oab1_lnl\": " << oab1 << ", \"oabfull_lnl\": " << oabfull << ",\n"
+          << " \"kernel\": \"" << (tree->sse == LK_EIGEN_SSE ? (instruction_set >= 7 ? "AVX" : "SSE") : "generic") << "\",\n"
+          << " \"threads\": " << params.num_threads << "\n}\n";
+    }
+    printf("lnl %.10f df %.10g ddf %.10g oab1 %.10f oabfull %.10f\n", lnl, df, ddf, oab1, oabfull);
+    return 0;
+}
+
+static int do_time(int argc, char **argv) {
+    int lnl_reps = atoi(argv[2]), derv_reps = atoi(argv[3]), oab_reps = atoi(argv[4]);
+    std::vector<char*> args; args.push_back(argv[0]);
+    for (int i = 5; i < argc; i++) args.push_back(argv[i]);
+    Params &params = Params::getInstance();
+    double t0 = getRealTime();
+    IQTree *tree = setup((int)args.size(), &args[0], params);
+    double t_setup = getRealTime() - t0;
+    Alignment *aln = tree->aln;
+    size_t C = tree->getRate()->getNRate(), M = tree->getModel()->getNMixtures();
+    bool fused = tree->getModelFactory()->fused_mix_rate;
+    size_t P = aln->size(), ntaxa = aln->getNSeq();
+    size_t blocks = (tree->getModel()->isMixture() && !fused) ? C * M : C;
+
+    tree->clearAllPartialLH();
+    double lnl = tree->computeLikelihood();           // warm-up
+    std::vector<double> lnl_t;
+    for (int r = 0; r < lnl_reps; r++) {
+        double a = getRealTime();
+        tree->clearAllPartialLH();
+        lnl = tree->computeLikelihood();
+        lnl_t.push_back(getRealTime() - a);
+    }
+    PhyloNode *n1 = (PhyloNode*)tree->root, *n2 = (PhyloNode*)tree->root->neighbors[0]->node;
+    double df = 0, ddf = 0;
+    tree->theta_computed = false;
+    tree->computeLikelihoodDerv((PhyloNeighbor*)n1->findNeighbor(n2), n1, df, ddf);   // builds theta
+    double a = getRealTime();
+    for (int r = 0; r < derv_reps; r++)
+        tree->computeLikelihoodDerv((PhyloNeighbor*)n1->findNeighbor(n2), n1, df, ddf);
+    double t_derv = derv_reps ? (getRealTime() - a) / derv_reps : 0.0;
+    double oab = 0, t_oab = 0;
+    for (int r = 0; r < oab_reps; r++) {
+        a = getRealTime();
+        oab = tree->optimizeAllBranches(1);
+        t_oab += getRealTime() - a;
+    }
+    if (oab_reps) t_oab /= oab_reps;
+    double sum = 0, best = 1e300;
+    for (size_t i = 0; i < lnl_t.size(); i++) { sum += lnl_t[i]; best = std::min(best, lnl_t[i]); }
+    double mean = lnl_t.empty() ? 0 : sum / lnl_t.size();
+    printf("{\"ref_time\": true, \"kernel\": \"%s\", \"threads\": %d, \"nptn\": %zu, \"ntaxa\": %zu, \"blocks\": %zu, "
+           "\"lnl\": %.12f, \"lnl_reps\": %d, \"lnl_s_mean\": %.6g, \"lnl_s_best\": %.6g, "
+           "\"df\": %.12g, \"ddf\": %.12g, \"derv_reps\": %d, \"derv_s_mean\": %.6g, "
+           "\"oab_lnl\": %.12f, \"oab_reps\": %d, \"oab_s_mean\": %.6g, \"setup_s\": %.4g}\n",
+           tree->sse == LK_EIGEN_SSE ? (instruction_set >= 7 ? "AVX" : "SSE") : "generic",
+           params.num_threads, P, ntaxa, blocks, lnl, lnl_reps, mean, lnl_t.empty() ? 0.0 : best,
+           df, ddf, derv_reps, t_derv, oab, oab_reps, t_oab, t_setup);
+    return 0;
+}
+
+int main(int argc, char **argv) {
+    if (argc >= 4 && !strcmp(argv[1], "dump")) return do_dump(argc, argv);
+    if (argc >= 6 && !strcmp(argv[1], "time")) return do_time(argc, argv);
+    fprintf(stderr, "usage: %s dump <outdir> <iqtree args>\n       %s time <lnl_reps> <derv_reps> <oab_reps> <iqtree args>\n", argv[0], argv[0]);
+    return 2;
+}
