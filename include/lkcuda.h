@@ -142,6 +142,9 @@ int lkcuda_partial_multi(lkcuda_engine *e, int32_t dst, int32_t nchild, const in
    result == NULL: enqueue only (read later with lkcuda_read_result); else synchronises and fills
    result[LKCUDA_NRESULT]. */
 int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result);
+/* fill only _pattern_lh_cat[p][k] for that branch: what PhyloTree::computePatternLhCat (phylotree.cpp:1108-1124)
+   obtains by calling the generic branch kernels (phylotreesse.cpp:1194-1237, 2588-2635).  Asynchronous. */
+int lkcuda_pattern_lh_cat(lkcuda_engine *e, int32_t dad, int32_t node, double len);
 
 /* ---- derivatives: PhyloTree::computeLikelihoodDerv (phylotreesse.cpp:344) split at its theta_computed flag ---- */
 /* theta_all = L_node * L_dad (phylokernel.h:535-579) */
@@ -179,6 +182,15 @@ int lkcuda_launch_count(const lkcuda_engine *e, uint64_t *count);
 /* algorithmic bytes moved by those launches, for the roofline */
 int lkcuda_algorithmic_bytes(const lkcuda_engine *e, uint64_t *bytes);
 int lkcuda_reset_counters(lkcuda_engine *e);
+/* per-kernel-kind statistics; with profiling on, every launch is bracketed by CUDA events on the engine
+   stream and device_ms is their summed elapsed time (the reference's num_partial_lh_computations /
+   getRealTime instrumentation, phylokernel.h:85, timeutil.h:134) */
+enum {
+    LKCUDA_KIND_PREP = 0, LKCUDA_KIND_PARTIAL = 1, LKCUDA_KIND_BRANCH = 2, LKCUDA_KIND_THETA = 3,
+    LKCUDA_KIND_DERV = 4, LKCUDA_KIND_FROMBUF = 5, LKCUDA_KIND_NEWTON = 6, LKCUDA_KIND_MISC = 7, LKCUDA_NKIND = 8
+};
+int lkcuda_set_profiling(lkcuda_engine *e, int32_t on);
+int lkcuda_kernel_stats(lkcuda_engine *e, int32_t kind, uint64_t *launches, uint64_t *bytes, double *device_ms);
 
 #ifdef __cplusplus
 }

@@ -69,7 +69,9 @@ int lktree_branch_vector(lktree *h, int32_t from, int32_t to, int32_t *vec, int3
 int lktree_root_branch(lktree *h, int32_t *from, int32_t *to);
 int lktree_fetch_tip_partial_lh(lktree *h, double *out, int64_t capacity, int64_t *count);
 int lktree_fetch_ptn_invar(lktree *h, double *out);
-int lktree_fetch_pattern_lh_cat(lktree *h, double *out);
+/* PhyloTree::computePatternLhCat (phylotree.cpp:1108-1160); wsl = 2 rate categories, 3 mixture classes, 4 both;
+   out holds [local P][nmix*ncat] doubles at most, *ncol = entries per pattern actually written */
+int lktree_compute_pattern_lh_cat(lktree *h, int32_t wsl, double *out, int32_t *ncol);
 lkcuda_engine *lktree_engine(lktree *h, int32_t i);
 int lktree_local_patterns(lktree *h, int64_t *begin, int64_t *end);
 uint64_t lktree_num_partial_lh_computations(lktree *h);

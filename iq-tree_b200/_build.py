@@ -1,0 +1,102 @@
+"""In-tree builds of the native libraries.
+
+* ``build_cuda()``   -> iq-tree_b200/lib/liblktree_cuda.so : the product (sm_100a kernels + C ABI of
+  include/lkcuda.h + the host PhyloTree mirror of include/lktree.h).  nvcc cross-compiles it without a GPU.
+* ``build_oracle()`` -> oracle/_build/liblktree_oracle.so  : TEST INFRASTRUCTURE.  The same host mirror linked
+  against the scalar C restatement oracle/lk_oracle.c instead of the CUDA engine; only tests/,
+  __graft_entry__.smoke() and bench.py's cpu_baseline leg load it.
+* ``build_reference()`` -> oracle/_ref/ref_harness : the UNMODIFIED reference compiled from /root/reference by
+  oracle/Makefile.ref (only where /root/reference exists; the GPU box uses the prebuilt binary).
+"""
+import os
+import shutil
+import subprocess
+import sys
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(PKG)
+CSRC = os.path.join(PKG, "csrc")
+LIBDIR = os.path.join(PKG, "lib")
+CUDA_LIB = os.path.join(LIBDIR, "liblktree_cuda.so")
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+ORACLE_LIB = os.path.join(ORACLE_DIR, "_build", "liblktree_oracle.so")
+REF_HARNESS = os.path.join(ORACLE_DIR, "_ref", "ref_harness")
+REFERENCE = "/root/reference"
+
+CUDA_SOURCES = ["lkcuda_engine.cu", "lkcuda_partial.cu", "lkcuda_reduce.cu", "lk_phylotree.cpp", "lk_capi.cpp"]
+HOST_SOURCES = ["lk_phylotree.cpp", "lk_capi.cpp"]
+HEADERS = [os.path.join(CSRC, "lkcuda_common.cuh"), os.path.join(CSRC, "lk_phylotree.h"),
+           os.path.join(ROOT, "include", "lkcuda.h"), os.path.join(ROOT, "include", "lktree.h")]
+
+
+def _newer(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources if os.path.exists(s))
+
+
+def _run(cmd, **kw):
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, **kw)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout)
+        raise RuntimeError("build failed: " + " ".join(cmd))
+    return r.stdout
+
+
+def nvcc_path():
+    for c in (shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if c and os.path.exists(c):
+            return c
+    return None
+
+
+def build_cuda(force=False, verbose=False):
+    """Compile every CUDA source for sm_100a into one shared library (in-tree, travels to the GPU box)."""
+    srcs = [os.path.join(CSRC, s) for s in CUDA_SOURCES]
+    if not force and not _newer(CUDA_LIB, srcs + HEADERS):
+        return CUDA_LIB
+    nvcc = nvcc_path()
+    if nvcc is None:
+        if os.path.exists(CUDA_LIB):
+            return CUDA_LIB       # a GPU box without nvcc uses the prebuilt library
+        raise RuntimeError("nvcc not found and %s is not built" % CUDA_LIB)
+    os.makedirs(LIBDIR, exist_ok=True)
+    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+           "-shared", "-Xcompiler", "-fPIC", "-Xptxas", "-v" if verbose else "-O3",
+           "-o", CUDA_LIB] + srcs
+    out = _run(cmd)
+    if verbose:
+        print(out)
+    return CUDA_LIB
+
+
+def build_oracle(force=False):
+    """TEST INFRASTRUCTURE: host mirror + scalar C oracle (no CUDA)."""
+    srcs = [os.path.join(CSRC, s) for s in HOST_SOURCES] + [os.path.join(ORACLE_DIR, "lk_oracle.c")]
+    if not force and not _newer(ORACLE_LIB, srcs + HEADERS):
+        return ORACLE_LIB
+    if shutil.which("gcc") is None or shutil.which("g++") is None:
+        if os.path.exists(ORACLE_LIB):
+            return ORACLE_LIB
+        raise RuntimeError("gcc/g++ not found and %s is not built" % ORACLE_LIB)
+    bdir = os.path.dirname(ORACLE_LIB)
+    os.makedirs(bdir, exist_ok=True)
+    objs = []
+    o = os.path.join(bdir, "lk_oracle.o")
+    _run(["gcc", "-O2", "-fPIC", "-ffp-contract=off", "-c", os.path.join(ORACLE_DIR, "lk_oracle.c"), "-o", o])
+    objs.append(o)
+    for s in HOST_SOURCES:
+        o = os.path.join(bdir, s.replace(".cpp", ".o"))
+        _run(["g++", "-O2", "-fPIC", "-std=c++17", "-c", os.path.join(CSRC, s), "-o", o])
+        objs.append(o)
+    _run(["g++", "-shared", "-o", ORACLE_LIB] + objs + ["-lm"])
+    return ORACLE_LIB
+
+
+def build_reference(jobs=8):
+    """TEST INFRASTRUCTURE: compile the unmodified reference into oracle/_ref/ref_harness (needs /root/reference)."""
+    if not os.path.isdir(REFERENCE):
+        return REF_HARNESS if os.path.exists(REF_HARNESS) else None
+    _run(["make", "-f", os.path.join("oracle", "Makefile.ref"), "-j%d" % jobs], cwd=ROOT)
+    return REF_HARNESS

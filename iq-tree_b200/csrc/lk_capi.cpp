@@ -182,7 +182,9 @@ int lktree_fetch_ptn_invar(lktree *h, double *out) {
     LK_CATCH(h)
 }
 
-int lktree_fetch_pattern_lh_cat(lktree *h, double *out) { LK_TRY(h) h->tree.computePatternLhCat(out); LK_CATCH(h) }
+int lktree_compute_pattern_lh_cat(lktree *h, int32_t wsl, double *out, int32_t *ncol) {
+    LK_TRY(h) int n = h->tree.computePatternLhCat(out, wsl); if (ncol) *ncol = n; LK_CATCH(h)
+}
 
 lkcuda_engine *lktree_engine(lktree *h, int32_t i) { return h ? h->tree.engine((size_t)i) : NULL; }
 

@@ -670,12 +670,52 @@ double PhyloTree::computeLikelihood(double *pattern_lh) {   // phylotree.cpp:103
     return score;
 }
 
-void PhyloTree::computePatternLhCat(double *out) {
+/* phylotree.cpp:1108-1160: per-category pattern likelihoods on current_it (picked like the reference when unset);
+   wsl: 2 = WSL_RATECAT, 3 = WSL_MIXTURE, 4 = WSL_MIXTURE_RATECAT (tools.h:406). Returns the entries per pattern. */
+int PhyloTree::computePatternLhCat(double *out, int wsl) {
+    if (engines_.empty()) initializeAllPartialLh();
+    if (!current_it) {
+        Node *leaf = findFarthestLeaf();   // findFirstFarLeaf (phylotree.cpp:1018) picks the same leaf: first maximal height
+        current_it = leaf->neighbors[0];
+        current_it_back = current_it->node->findNeighbor(leaf);
+    }
+    Neighbor *dad_branch = current_it; Node *dad = current_it_back->node;
+    Node *node = dad_branch->node;
+    Neighbor *node_branch = current_it_back;
+    if (node->isLeaf()) { std::swap(dad, node); std::swap(dad_branch, node_branch); }
+    if ((dad_branch->partial_lh_computed & 1) == 0) computePartialLikelihood(dad_branch, dad);
+    if ((node_branch->partial_lh_computed & 1) == 0) computePartialLikelihood(node_branch, node);
+    flushPartialOps();
+    int32_t dad_end = dad->isLeaf() ? LKCUDA_TIP(dad->id) : node_branch->vec;
     int K = family == FAMILY_MIXTURE ? ncat * nmix : ncat;
+    std::vector<double> raw((size_t)(ptn_end_ - ptn_begin_) * K + 1);
     for (size_t d = 0; d < engines_.size(); d++) {
         int64_t b = shard_begin_[d] - ptn_begin_;
-        check(lkcuda_fetch_pattern_lh_cat(engines_[d], out + b * K), engines_[d], "lkcuda_fetch_pattern_lh_cat");
+        check(lkcuda_pattern_lh_cat(engines_[d], dad_end, dad_branch->vec, dad_branch->length), engines_[d], "lkcuda_pattern_lh_cat");
+        check(lkcuda_fetch_pattern_lh_cat(engines_[d], &raw[b * K]), engines_[d], "lkcuda_fetch_pattern_lh_cat");
     }
+    int64_t np = ptn_end_ - ptn_begin_;
+    if (family == FAMILY_MIXTURE && wsl == 3 && ncat > 1) {          // per mixture class
+        for (int64_t p = 0; p < np; p++)
+            for (int m = 0; m < nmix; m++) {
+                const double *lc = &raw[(size_t)p * K + (size_t)m * ncat];
+                double lh = lc[0];
+                for (int c = 1; c < ncat; c++) lh += lc[c];
+                out[p * nmix + m] = lh;
+            }
+        return nmix;
+    }
+    if (family == FAMILY_MIXTURE && wsl == 2 && nmix > 1) {          // per rate category
+        for (int64_t p = 0; p < np; p++)
+            for (int c = 0; c < ncat; c++) {
+                double lh = raw[(size_t)p * K + c];
+                for (int m = 1; m < nmix; m++) lh += raw[(size_t)p * K + (size_t)m * ncat + c];
+                out[p * ncat + c] = lh;
+            }
+        return ncat;
+    }
+    memcpy(out, &raw[0], (size_t)np * K * 8);
+    return K;
 }
 
 void PhyloTree::computeFuncDerv(double value, double &df, double &ddf) {   // phylotree.cpp:2135-2146

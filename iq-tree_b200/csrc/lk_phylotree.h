@@ -114,7 +114,7 @@ public:
     void computeLikelihoodDerv(Neighbor *dad_branch, Node *dad, double &df, double &ddf);
     double computeLikelihoodFromBuffer();
     double computeLikelihood(double *pattern_lh = NULL);
-    void computePatternLhCat(double *pattern_lh_cat);               // phylotree.cpp:1108-1124 (values only)
+    int computePatternLhCat(double *pattern_lh_cat, int wsl = 4);    // phylotree.cpp:1108-1160; returns entries per pattern
     void computeFuncDerv(double value, double &df, double &ddf);
     double minimizeNewton(double x1, double xguess, double x2, double xacc, double &d2l, int maxNRStep = 100);
     void optimizeOneBranch(Node *node1, Node *node2, bool clearLH = true, int maxNRStep = 100);

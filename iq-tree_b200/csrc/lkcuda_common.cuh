@@ -1,0 +1,218 @@
+/*
+ * lkcuda_common.cuh — shared declarations of the sm_100a likelihood engine behind include/lkcuda.h.
+ *
+ * Data layout in HBM (one engine = one pattern shard on one device), NP = P + U patterns:
+ *   arena     double[nvec][vec_stride]      vector v = partial_lh[ptn][blk][state], the reference's layout
+ *                                           (phylotree.cpp:863-974); vec_stride = NP*B rounded up to 256 B
+ *   scale     int16 [nvec][sc_stride]       scale_num[ptn] (UBYTE = short, phylonode.h:17)
+ *   states    uint8 [ntaxa][st_stride]      taxon-major tip states (pattern-major strings in the reference)
+ *   theta     double[NP*B]                  theta_all (phylotree.cpp:687)
+ *   pattern_lh double[NP], pattern_lh_cat double[P*K], ptn_freq double[P], ptn_invar double[NP]
+ * Every vector starts on a 256-byte boundary and B*8 is normally a multiple of 32, so a lane always
+ * moves whole 32-byte sectors (LDG.E.256 / STG.E.256) whatever the thread<->pattern mapping is.
+ */
+#ifndef LKCUDA_COMMON_CUH
+#define LKCUDA_COMMON_CUH
+
+#include "../../include/lkcuda.h"
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <vector>
+
+namespace lkc {
+
+/* phylotree.h:52-54 */
+#define LK_THR_INV 0x1p256
+#define LK_THR 0x1p-256
+#define LK_LOG_THR (-177.44567822334599)   /* log(2^-256) */
+
+enum KernelKind {
+    KIND_PREP = 0, KIND_PARTIAL = 1, KIND_BRANCH = 2, KIND_THETA = 3, KIND_DERV = 4, KIND_FROMBUF = 5,
+    KIND_NEWTON = 6, KIND_MISC = 7, KIND_COUNT = 8
+};
+
+/* slots of the cross-block reduction buffer */
+enum { RED_SLOTS = 8 };
+
+struct PendingEvent { int kind; cudaEvent_t start, stop; };
+
+/* device-side op record of one node of the schedule */
+struct DevOp {
+    int32_t dst;        /* destination vector                                   */
+    int32_t nchild;     /* 2 for a bifurcating node                             */
+    int32_t child0;     /* first entry in the child list / child-table slots    */
+    int32_t pad;
+};
+
+struct DevChild {
+    int32_t id;         /* vector (>=0) or LKCUDA_TIP(taxon)                    */
+    int32_t pad;
+    double  len;
+};
+
+/* everything a kernel needs to know about the engine, passed by value */
+struct DevView {
+    int S, K, E, B;             /* states, blocks per pattern, eigensystems, B = S*K        */
+    int SU;                     /* state_unknown                                             */
+    int flags;
+    long long P, U, NP;         /* observed, unobserved, total patterns                      */
+    long long vec_stride, sc_stride, st_stride;
+    double nsite;
+    const uint8_t *states;
+    const double *freq, *invar;
+    const double *eval, *evec, *inv_evec, *blk_rate, *blk_weight, *tip;
+    const int32_t *blk_eigen;
+    double *arena; int16_t *scale;
+    double *theta; int16_t *theta_sc; double *theta_meta;   /* theta_meta[0] = scale sum of the theta branch */
+    double *pattern_lh, *pattern_lh_cat;
+    double *red; unsigned int *counter; double *result;
+    /* per-child transition tables built by the prep kernel:
+       slot c: ech[K*S*S] then tab[(SU+1)*B]                                                   */
+    double *tables; long long table_slot;   /* doubles per slot */
+};
+
+}  // namespace lkc
+
+struct lkcuda_engine {
+    lkcuda_config cfg;
+    lkc::DevView v;
+    int device;
+    cudaStream_t stream; bool own_stream;
+    /* owned device allocations */
+    uint8_t *d_states; double *d_freq, *d_invar;
+    double *d_eval, *d_evec, *d_inv, *d_rate, *d_weight, *d_tip; int32_t *d_eigen;
+    double *d_arena; int16_t *d_scale;
+    double *d_theta; int16_t *d_theta_sc; double *d_theta_meta;
+    double *d_plh, *d_plhcat;
+    double *d_red; unsigned int *d_counter; double *d_result;
+    double *h_result;                       /* pinned */
+    double *d_newton_out; double *h_newton_out;
+    /* transition tables */
+    double *d_tables; long long table_slots_cap;
+    /* op upload ring (pinned host + device) */
+    enum { RING = 4 };
+    lkc::DevOp *h_ops[RING], *d_ops[RING]; lkc::DevChild *h_child[RING], *d_child[RING];
+    int ring_cap_ops[RING], ring_cap_child[RING]; cudaEvent_t ring_ev[RING]; bool ring_used[RING]; int ring_next;
+    int red_blocks;                         /* capacity of d_red in blocks */
+    bool theta_ready; int theta_dad; int theta_node;
+    bool model_set, states_set, weights_set;
+    int num_sms;
+    uint64_t launches, bytes;
+    /* optional per-kernel-kind timing */
+    bool profiling;
+    std::vector<lkc::PendingEvent> pending;
+    std::vector<cudaEvent_t> event_pool;
+    double kind_ms[lkc::KIND_COUNT]; uint64_t kind_launches[lkc::KIND_COUNT]; uint64_t kind_bytes[lkc::KIND_COUNT];
+    uint64_t total_dev_bytes;
+    char err[512];
+};
+
+namespace lkc {
+
+int fail(lkcuda_engine *e, int code, const char *fmt, ...);
+int cuda_fail(lkcuda_engine *e, cudaError_t rc, const char *what);
+
+#define LK_CUDA(e, call) do { cudaError_t rc_ = (call); if (rc_ != cudaSuccess) return lkc::cuda_fail((e), rc_, #call); } while (0)
+#define LK_ENTER(e) do { if (!(e)) return LKCUDA_ERR_ARG; cudaError_t rc_ = cudaSetDevice((e)->device); \
+                         if (rc_ != cudaSuccess) return lkc::cuda_fail((e), rc_, "cudaSetDevice"); } while (0)
+
+/* bracket a launch for statistics (and CUDA-event timing when profiling is on) */
+void launch_begin(lkcuda_engine *e, int kind);
+int launch_end(lkcuda_engine *e, int kind, uint64_t algorithmic_bytes, const char *what);
+void drain_events(lkcuda_engine *e);
+
+inline bool valid_end(const lkcuda_engine *e, int32_t id) {
+    return id >= 0 ? id < e->cfg.nvec : LKCUDA_TIP_TAXON(id) < e->cfg.ntaxa;
+}
+
+/* implemented in lkcuda_partial.cu / lkcuda_reduce.cu */
+int ensure_tables(lkcuda_engine *e, long long slots);
+
+}  // namespace lkc
+
+/* ------------------------------------------------------------------ device helpers ------------------------------------------------------------------ */
+#ifdef __CUDACC__
+namespace lkc {
+
+struct __align__(32) d4 { double x, y, z, w; };
+
+/* whole-sector streaming accesses: LDG.E.256 / STG.E.256 on sm_100a */
+__device__ __forceinline__ d4 ld_stream256(const double *p) {
+    d4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];"
+                 : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st_stream256(double *p, const d4 &v) {
+    asm volatile("st.global.L1::no_allocate.v4.f64 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "d"(v.x), "d"(v.y), "d"(v.z), "d"(v.w) : "memory");
+}
+
+__device__ __forceinline__ const double *vec_lh(const DevView &v, int id) { return v.arena + (long long)id * v.vec_stride; }
+__device__ __forceinline__ double *vec_lh_w(const DevView &v, int id) { return v.arena + (long long)id * v.vec_stride; }
+__device__ __forceinline__ const int16_t *vec_sc(const DevView &v, int id) { return v.scale + (long long)id * v.sc_stride; }
+__device__ __forceinline__ int16_t *vec_sc_w(const DevView &v, int id) { return v.scale + (long long)id * v.sc_stride; }
+__device__ __forceinline__ const uint8_t *tip_states(const DevView &v, int id) { return v.states + (long long)LKCUDA_TIP_TAXON(id) * v.st_stride; }
+
+/* fixed-order block reduction of N doubles per thread; result valid in thread 0.
+   `sh` must hold N * 32 doubles. Deterministic for a fixed block size. */
+template <int N>
+__device__ __forceinline__ void block_reduce(double (&val)[N], double *sh) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+        double x = val[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+        if (lane == 0) sh[i * 32 + warp] = x;
+    }
+    __syncthreads();
+    if (warp == 0) {
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+            double x = lane < nwarp ? sh[i * 32 + lane] : 0.0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+            val[i] = x;
+        }
+    }
+}
+
+/* cross-block stage: every block deposits its N sums; the last block to arrive (ticket counter) adds the
+   deposits in block order and returns true in its thread 0 with the totals in `val`. The counter resets itself. */
+template <int N>
+__device__ __forceinline__ bool grid_reduce(double (&val)[N], double *sh, double *red, unsigned int *counter) {
+    __shared__ bool is_last;
+    block_reduce<N>(val, sh);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < N; i++) red[(size_t)blockIdx.x * RED_SLOTS + i] = val[i];
+        __threadfence();
+        unsigned int ticket = atomicAdd(counter, 1u);
+        is_last = (ticket == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!is_last) return false;
+    __threadfence();
+    double acc[N];
+#pragma unroll
+    for (int i = 0; i < N; i++) acc[i] = 0.0;
+    for (unsigned int b = threadIdx.x; b < gridDim.x; b += blockDim.x) {
+#pragma unroll
+        for (int i = 0; i < N; i++) acc[i] += __ldcg(&red[(size_t)b * RED_SLOTS + i]);
+    }
+    __syncthreads();
+    block_reduce<N>(acc, sh);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < N; i++) val[i] = acc[i];
+        *counter = 0u;
+    }
+    return threadIdx.x == 0;
+}
+
+}  // namespace lkc
+#endif  /* __CUDACC__ */
+#endif

@@ -1,0 +1,404 @@
+/*
+ * lkcuda_engine.cu — life cycle, inputs, host-visible mirrors and instrumentation of the sm_100a
+ * likelihood engine (C ABI: include/lkcuda.h).  The kernels live in lkcuda_partial.cu and
+ * lkcuda_reduce.cu.  There is no CPU fallback: without a CUDA device lkcuda_create fails with
+ * LKCUDA_ERR_NODEVICE.
+ *
+ * Replaces the buffer management of PhyloTree::initializeAllPartialLh / deleteAllPartialLh
+ * (phylotree.cpp:667-716, 718-760, 834-987): one arena for all partial-likelihood vectors, one for the
+ * scale_num rows, plus _pattern_lh, _pattern_lh_cat, theta_all, ptn_freq, ptn_invar.
+ */
+#include "lkcuda_common.cuh"
+#include <stdarg.h>
+#include <stdlib.h>
+#include <new>
+
+static char g_create_err[512] = "";
+
+namespace lkc {
+
+int fail(lkcuda_engine *e, int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(e ? e->err : g_create_err, 512, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int cuda_fail(lkcuda_engine *e, cudaError_t rc, const char *what) {
+    return fail(e, rc == cudaErrorMemoryAllocation ? LKCUDA_ERR_NOMEM : LKCUDA_ERR_CUDA, "%s: %s", what, cudaGetErrorString(rc));
+}
+
+static cudaEvent_t get_event(lkcuda_engine *e) {
+    cudaEvent_t ev = NULL;
+    if (!e->event_pool.empty()) { ev = e->event_pool.back(); e->event_pool.pop_back(); return ev; }
+    cudaEventCreate(&ev);
+    return ev;
+}
+
+void launch_begin(lkcuda_engine *e, int kind) {
+    if (!e->profiling) return;
+    PendingEvent pe;
+    pe.kind = kind; pe.start = get_event(e); pe.stop = get_event(e);
+    cudaEventRecord(pe.start, e->stream);
+    e->pending.push_back(pe);
+}
+
+int launch_end(lkcuda_engine *e, int kind, uint64_t algorithmic_bytes, const char *what) {
+    cudaError_t rc = cudaGetLastError();
+    if (e->profiling && !e->pending.empty()) cudaEventRecord(e->pending.back().stop, e->stream);
+    e->launches++; e->bytes += algorithmic_bytes;
+    e->kind_launches[kind]++; e->kind_bytes[kind] += algorithmic_bytes;
+    if (rc != cudaSuccess) return cuda_fail(e, rc, what);
+    if (e->pending.size() > 4096) drain_events(e);
+    return LKCUDA_OK;
+}
+
+/* fold finished event pairs into kind_ms (synchronises on them) */
+void drain_events(lkcuda_engine *e) {
+    for (size_t i = 0; i < e->pending.size(); i++) {
+        PendingEvent &pe = e->pending[i];
+        float ms = 0.f;
+        if (cudaEventSynchronize(pe.stop) == cudaSuccess && cudaEventElapsedTime(&ms, pe.start, pe.stop) == cudaSuccess)
+            e->kind_ms[pe.kind] += ms;
+        e->event_pool.push_back(pe.start); e->event_pool.push_back(pe.stop);
+    }
+    e->pending.clear();
+}
+
+}  // namespace lkc
+
+using namespace lkc;
+
+static long long round_up(long long x, long long m) { return (x + m - 1) / m * m; }
+
+template <typename T>
+static cudaError_t dev_alloc(lkcuda_engine *e, T **p, size_t count) {
+    size_t bytes = (count ? count : 1) * sizeof(T);
+    cudaError_t rc = cudaMalloc((void **)p, bytes);
+    if (rc == cudaSuccess) e->total_dev_bytes += bytes;
+    return rc;
+}
+
+/* flags any state code above state_unknown (16 bytes per thread per step) */
+__global__ void validate_states_kernel(const uint8_t *states, long long total, long long stride, long long np, int su, unsigned int *flag) {
+    bool bad = false;
+    for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 16; i < total; i += (long long)gridDim.x * blockDim.x * 16) {
+        uint4 w = *reinterpret_cast<const uint4 *>(states + i);
+        unsigned int x[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            long long col = (i + k) % stride;
+            int b = (x[k >> 2] >> ((k & 3) * 8)) & 0xff;
+            if (col < np && b > su) bad = true;
+        }
+    }
+    if (bad) atomicOr(flag, 1u);
+}
+
+extern "C" {
+
+int lkcuda_device_count(int32_t *count) {
+    if (!count) return LKCUDA_ERR_ARG;
+    int n = 0;
+    cudaError_t rc = cudaGetDeviceCount(&n);
+    if (rc != cudaSuccess) { *count = 0; cudaGetLastError(); return LKCUDA_ERR_NODEVICE; }
+    *count = n;
+    return LKCUDA_OK;
+}
+
+const char *lkcuda_last_error(const lkcuda_engine *e) { return e ? e->err : g_create_err; }
+
+int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
+    if (!cfg || !out) return fail(NULL, LKCUDA_ERR_ARG, "null argument");
+    *out = NULL;
+    if (cfg->nstates < 1 || cfg->nblocks < 1 || cfg->neigen < 1 || cfg->ntaxa < 1 || cfg->nptn < 0 ||
+        cfg->nunobs < 0 || cfg->nvec < 0 || cfg->state_unknown < cfg->nstates || cfg->state_unknown > 255)
+        return fail(NULL, LKCUDA_ERR_ARG, "invalid configuration");
+    if ((long long)cfg->nstates * cfg->nblocks > (1 << 20)) return fail(NULL, LKCUDA_ERR_ARG, "block too large");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+        cudaGetLastError();
+        return fail(NULL, LKCUDA_ERR_NODEVICE, "no CUDA device available (this engine has no CPU path)");
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(NULL, LKCUDA_ERR_ARG, "device ordinal %d out of range (%d devices)", cfg->device, ndev);
+    cudaError_t rc = cudaSetDevice(cfg->device);
+    if (rc != cudaSuccess) return cuda_fail(NULL, rc, "cudaSetDevice");
+
+    lkcuda_engine *e = new (std::nothrow) lkcuda_engine();
+    if (!e) return fail(NULL, LKCUDA_ERR_NOMEM, "out of host memory");
+    /* lkcuda_engine holds std::vector members: value-initialise the POD part by hand */
+    e->cfg = *cfg; e->device = cfg->device; e->stream = NULL; e->own_stream = false;
+    e->d_states = NULL; e->d_freq = e->d_invar = NULL;
+    e->d_eval = e->d_evec = e->d_inv = e->d_rate = e->d_weight = e->d_tip = NULL; e->d_eigen = NULL;
+    e->d_arena = NULL; e->d_scale = NULL; e->d_theta = NULL; e->d_theta_sc = NULL; e->d_theta_meta = NULL;
+    e->d_plh = e->d_plhcat = NULL; e->d_red = NULL; e->d_counter = NULL; e->d_result = NULL; e->h_result = NULL;
+    e->d_newton_out = NULL; e->h_newton_out = NULL;
+    e->d_tables = NULL; e->table_slots_cap = 0;
+    for (int i = 0; i < lkcuda_engine::RING; i++) {
+        e->h_ops[i] = e->d_ops[i] = NULL; e->h_child[i] = e->d_child[i] = NULL;
+        e->ring_cap_ops[i] = e->ring_cap_child[i] = 0; e->ring_ev[i] = NULL; e->ring_used[i] = false;
+    }
+    e->ring_next = 0; e->red_blocks = 0;
+    e->theta_ready = false; e->theta_dad = e->theta_node = 0;
+    e->model_set = e->states_set = e->weights_set = false;
+    e->launches = e->bytes = 0; e->profiling = false; e->total_dev_bytes = 0;
+    memset(e->kind_ms, 0, sizeof(e->kind_ms)); memset(e->kind_launches, 0, sizeof(e->kind_launches)); memset(e->kind_bytes, 0, sizeof(e->kind_bytes));
+    e->err[0] = 0;
+
+    DevView &v = e->v;
+    memset(&v, 0, sizeof(v));
+    v.S = cfg->nstates; v.K = cfg->nblocks; v.E = cfg->neigen; v.B = v.S * v.K; v.SU = cfg->state_unknown;
+    v.flags = cfg->flags; v.P = cfg->nptn; v.U = cfg->nunobs; v.NP = v.P + v.U; v.nsite = (double)cfg->nsite;
+    v.vec_stride = round_up(v.NP * v.B, 32);     /* 256-byte multiple */
+    v.sc_stride = round_up(v.NP, 64);            /* 128-byte multiple */
+    v.st_stride = round_up(v.NP, 128);
+    v.table_slot = round_up((long long)v.K * v.S * v.S + (long long)(v.SU + 1) * v.B, 4);
+
+    cudaDeviceProp prop;
+    rc = cudaGetDeviceProperties(&prop, cfg->device);
+    e->num_sms = rc == cudaSuccess ? prop.multiProcessorCount : 148;
+    e->red_blocks = e->num_sms * 16;
+
+    bool ok = true;
+#define ALLOC(ptr, count) do { if (ok) { rc = dev_alloc(e, &(ptr), (size_t)(count)); if (rc != cudaSuccess) ok = false; } } while (0)
+    if (ok) { rc = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking); ok = rc == cudaSuccess; e->own_stream = ok; }
+    size_t nvec = (size_t)(cfg->nvec ? cfg->nvec : 1);
+    ALLOC(e->d_states, (size_t)cfg->ntaxa * v.st_stride);
+    ALLOC(e->d_freq, v.P + 4); ALLOC(e->d_invar, v.NP + 4);
+    ALLOC(e->d_eval, v.E * v.S); ALLOC(e->d_evec, (size_t)v.E * v.S * v.S); ALLOC(e->d_inv, (size_t)v.E * v.S * v.S);
+    ALLOC(e->d_rate, v.K); ALLOC(e->d_weight, v.K); ALLOC(e->d_eigen, v.K);
+    ALLOC(e->d_tip, (size_t)(v.SU + 1) * v.E * v.S);
+    ALLOC(e->d_arena, nvec * (size_t)v.vec_stride);
+    ALLOC(e->d_scale, nvec * (size_t)v.sc_stride);
+    ALLOC(e->d_theta, (size_t)v.vec_stride);
+    ALLOC(e->d_theta_sc, v.U + 4); ALLOC(e->d_theta_meta, 8);
+    ALLOC(e->d_plh, v.NP + 4); ALLOC(e->d_plhcat, (size_t)v.P * v.K + 4);
+    ALLOC(e->d_red, (size_t)e->red_blocks * RED_SLOTS); ALLOC(e->d_counter, 4); ALLOC(e->d_result, LKCUDA_NRESULT);
+    ALLOC(e->d_newton_out, 8);
+#undef ALLOC
+    if (ok) { rc = cudaMallocHost((void **)&e->h_result, sizeof(double) * LKCUDA_NRESULT); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMallocHost((void **)&e->h_newton_out, sizeof(double) * 8); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMemsetAsync(e->d_counter, 0, 4 * sizeof(unsigned int), e->stream); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMemsetAsync(e->d_result, 0, sizeof(double) * LKCUDA_NRESULT, e->stream); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMemsetAsync(e->d_theta_meta, 0, sizeof(double) * 8, e->stream); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMemsetAsync(e->d_states, 0, (size_t)cfg->ntaxa * v.st_stride, e->stream); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMemsetAsync(e->d_scale, 0, nvec * (size_t)v.sc_stride * sizeof(int16_t), e->stream); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaStreamSynchronize(e->stream); ok = rc == cudaSuccess; }
+    if (!ok) {
+        int code = cuda_fail(NULL, rc, "engine allocation");
+        lkcuda_destroy(e);
+        return code;
+    }
+    v.states = e->d_states; v.freq = e->d_freq; v.invar = e->d_invar;
+    v.eval = e->d_eval; v.evec = e->d_evec; v.inv_evec = e->d_inv; v.blk_rate = e->d_rate; v.blk_weight = e->d_weight;
+    v.tip = e->d_tip; v.blk_eigen = e->d_eigen;
+    v.arena = e->d_arena; v.scale = e->d_scale; v.theta = e->d_theta; v.theta_sc = e->d_theta_sc; v.theta_meta = e->d_theta_meta;
+    v.pattern_lh = e->d_plh; v.pattern_lh_cat = e->d_plhcat;
+    v.red = e->d_red; v.counter = e->d_counter; v.result = e->d_result;
+    v.tables = NULL;
+    *out = e;
+    return LKCUDA_OK;
+}
+
+int lkcuda_destroy(lkcuda_engine *e) {
+    if (!e) return LKCUDA_OK;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    drain_events(e);
+    for (size_t i = 0; i < e->event_pool.size(); i++) cudaEventDestroy(e->event_pool[i]);
+    cudaFree(e->d_states); cudaFree(e->d_freq); cudaFree(e->d_invar);
+    cudaFree(e->d_eval); cudaFree(e->d_evec); cudaFree(e->d_inv); cudaFree(e->d_rate); cudaFree(e->d_weight); cudaFree(e->d_eigen);
+    cudaFree(e->d_tip); cudaFree(e->d_arena); cudaFree(e->d_scale); cudaFree(e->d_theta); cudaFree(e->d_theta_sc); cudaFree(e->d_theta_meta);
+    cudaFree(e->d_plh); cudaFree(e->d_plhcat); cudaFree(e->d_red); cudaFree(e->d_counter); cudaFree(e->d_result);
+    cudaFree(e->d_newton_out); cudaFree(e->d_tables);
+    if (e->h_result) cudaFreeHost(e->h_result);
+    if (e->h_newton_out) cudaFreeHost(e->h_newton_out);
+    for (int i = 0; i < lkcuda_engine::RING; i++) {
+        if (e->h_ops[i]) cudaFreeHost(e->h_ops[i]);
+        if (e->h_child[i]) cudaFreeHost(e->h_child[i]);
+        cudaFree(e->d_ops[i]); cudaFree(e->d_child[i]);
+        if (e->ring_ev[i]) cudaEventDestroy(e->ring_ev[i]);
+    }
+    if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
+    cudaGetLastError();
+    delete e;
+    return LKCUDA_OK;
+}
+
+int lkcuda_memory_bytes(const lkcuda_engine *e, uint64_t *bytes) {
+    if (!e || !bytes) return LKCUDA_ERR_ARG;
+    *bytes = e->total_dev_bytes;
+    return LKCUDA_OK;
+}
+
+int lkcuda_set_stream(lkcuda_engine *e, void *s) {
+    LK_ENTER(e);
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    drain_events(e);
+    if (e->own_stream) { cudaStreamDestroy(e->stream); e->own_stream = false; }
+    if (s) e->stream = (cudaStream_t)s;
+    else { LK_CUDA(e, cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)); e->own_stream = true; }
+    return LKCUDA_OK;
+}
+
+int lkcuda_synchronize(lkcuda_engine *e) {
+    LK_ENTER(e);
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    return LKCUDA_OK;
+}
+
+int lkcuda_set_tip_states(lkcuda_engine *e, const uint8_t *states) {
+    LK_ENTER(e);
+    if (!states) return fail(e, LKCUDA_ERR_ARG, "null tip states");
+    const DevView &v = e->v;
+    if (v.NP > 0) {
+        /* `states` may be pinned (then this is one DMA at link speed) or pageable caller memory */
+        LK_CUDA(e, cudaMemcpy2DAsync(e->d_states, (size_t)v.st_stride, states, (size_t)v.NP, (size_t)v.NP, (size_t)e->cfg.ntaxa,
+                                     cudaMemcpyHostToDevice, e->stream));
+        /* range check on the device: the matrix is 100 MB at the BASELINE shape, a host scan would cost more than the copy */
+        LK_CUDA(e, cudaMemsetAsync(e->d_counter + 2, 0, sizeof(unsigned int), e->stream));
+        long long total = (long long)e->cfg.ntaxa * v.st_stride;
+        int grid = (int)((total / 16 + 255) / 256 < (long long)e->num_sms * 8 ? (total / 16 + 255) / 256 : (long long)e->num_sms * 8);
+        if (grid < 1) grid = 1;
+        launch_begin(e, KIND_MISC);
+        validate_states_kernel<<<grid, 256, 0, e->stream>>>(e->d_states, total, v.st_stride, v.NP, e->cfg.state_unknown, e->d_counter + 2);
+        int rc = launch_end(e, KIND_MISC, 0, "validate_states_kernel");
+        if (rc) return rc;
+        LK_CUDA(e, cudaMemcpyAsync(e->h_newton_out, e->d_counter + 2, sizeof(unsigned int), cudaMemcpyDeviceToHost, e->stream));
+    }
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (v.NP > 0 && *(unsigned int *)e->h_newton_out != 0) { e->states_set = false; return fail(e, LKCUDA_ERR_ARG, "tip state out of range"); }
+    e->states_set = true; e->theta_ready = false;
+    return LKCUDA_OK;
+}
+
+int lkcuda_set_pattern_weights(lkcuda_engine *e, const double *ptn_freq, const double *ptn_invar) {
+    LK_ENTER(e);
+    if (!ptn_freq || !ptn_invar) return fail(e, LKCUDA_ERR_ARG, "null pattern weights");
+    const DevView &v = e->v;
+    if (v.P) LK_CUDA(e, cudaMemcpyAsync(e->d_freq, ptn_freq, (size_t)v.P * 8, cudaMemcpyHostToDevice, e->stream));
+    if (v.NP) LK_CUDA(e, cudaMemcpyAsync(e->d_invar, ptn_invar, (size_t)v.NP * 8, cudaMemcpyHostToDevice, e->stream));
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    e->weights_set = true; e->theta_ready = false;
+    return LKCUDA_OK;
+}
+
+int lkcuda_set_model(lkcuda_engine *e, const double *eval, const double *evec, const double *inv_evec,
+                     const int32_t *blk_eigen, const double *blk_rate, const double *blk_weight,
+                     const double *tip_partial_lh) {
+    LK_ENTER(e);
+    if (!eval || !evec || !inv_evec || !blk_eigen || !blk_rate || !blk_weight || !tip_partial_lh)
+        return fail(e, LKCUDA_ERR_ARG, "null model argument");
+    const DevView &v = e->v;
+    for (int k = 0; k < v.K; k++)
+        if (blk_eigen[k] < 0 || blk_eigen[k] >= v.E) return fail(e, LKCUDA_ERR_ARG, "blk_eigen out of range");
+    size_t S = (size_t)v.S, E = (size_t)v.E, K = (size_t)v.K;
+    LK_CUDA(e, cudaMemcpyAsync(e->d_eval, eval, E * S * 8, cudaMemcpyHostToDevice, e->stream));
+    LK_CUDA(e, cudaMemcpyAsync(e->d_evec, evec, E * S * S * 8, cudaMemcpyHostToDevice, e->stream));
+    LK_CUDA(e, cudaMemcpyAsync(e->d_inv, inv_evec, E * S * S * 8, cudaMemcpyHostToDevice, e->stream));
+    LK_CUDA(e, cudaMemcpyAsync(e->d_eigen, blk_eigen, K * 4, cudaMemcpyHostToDevice, e->stream));
+    LK_CUDA(e, cudaMemcpyAsync(e->d_rate, blk_rate, K * 8, cudaMemcpyHostToDevice, e->stream));
+    LK_CUDA(e, cudaMemcpyAsync(e->d_weight, blk_weight, K * 8, cudaMemcpyHostToDevice, e->stream));
+    LK_CUDA(e, cudaMemcpyAsync(e->d_tip, tip_partial_lh, (size_t)(v.SU + 1) * E * S * 8, cudaMemcpyHostToDevice, e->stream));
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));   /* the sources are pageable caller memory */
+    e->model_set = true; e->theta_ready = false;
+    return LKCUDA_OK;
+}
+
+int lkcuda_read_result(lkcuda_engine *e, double *result) {
+    LK_ENTER(e);
+    if (!result) return fail(e, LKCUDA_ERR_ARG, "null result");
+    LK_CUDA(e, cudaMemcpyAsync(e->h_result, e->d_result, sizeof(double) * LKCUDA_NRESULT, cudaMemcpyDeviceToHost, e->stream));
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    memcpy(result, e->h_result, sizeof(double) * LKCUDA_NRESULT);
+    return LKCUDA_OK;
+}
+
+int lkcuda_result_device_ptr(lkcuda_engine *e, void **p) {
+    if (!e || !p) return LKCUDA_ERR_ARG;
+    *p = e->d_result;
+    return LKCUDA_OK;
+}
+
+int lkcuda_fetch_pattern_lh(lkcuda_engine *e, double *dst) {
+    LK_ENTER(e);
+    if (!dst) return fail(e, LKCUDA_ERR_ARG, "null destination");
+    if (e->v.P) LK_CUDA(e, cudaMemcpyAsync(dst, e->d_plh, (size_t)e->v.P * 8, cudaMemcpyDeviceToHost, e->stream));
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    return LKCUDA_OK;
+}
+
+int lkcuda_fetch_pattern_lh_cat(lkcuda_engine *e, double *dst) {
+    LK_ENTER(e);
+    if (!dst) return fail(e, LKCUDA_ERR_ARG, "null destination");
+    if (e->v.P) LK_CUDA(e, cudaMemcpyAsync(dst, e->d_plhcat, (size_t)e->v.P * e->v.K * 8, cudaMemcpyDeviceToHost, e->stream));
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    return LKCUDA_OK;
+}
+
+int lkcuda_fetch_vector(lkcuda_engine *e, int32_t vec, double *partial_lh, int16_t *scale_num) {
+    LK_ENTER(e);
+    if (vec < 0 || vec >= e->cfg.nvec) return fail(e, LKCUDA_ERR_ARG, "vector index out of range");
+    const DevView &v = e->v;
+    if (partial_lh && v.NP) LK_CUDA(e, cudaMemcpyAsync(partial_lh, e->d_arena + (size_t)vec * v.vec_stride, (size_t)v.NP * v.B * 8, cudaMemcpyDeviceToHost, e->stream));
+    if (scale_num && v.NP) LK_CUDA(e, cudaMemcpyAsync(scale_num, e->d_scale + (size_t)vec * v.sc_stride, (size_t)v.NP * 2, cudaMemcpyDeviceToHost, e->stream));
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    return LKCUDA_OK;
+}
+
+int lkcuda_store_vector(lkcuda_engine *e, int32_t vec, const double *partial_lh, const int16_t *scale_num) {
+    LK_ENTER(e);
+    if (vec < 0 || vec >= e->cfg.nvec) return fail(e, LKCUDA_ERR_ARG, "vector index out of range");
+    const DevView &v = e->v;
+    if (partial_lh && v.NP) LK_CUDA(e, cudaMemcpyAsync(e->d_arena + (size_t)vec * v.vec_stride, partial_lh, (size_t)v.NP * v.B * 8, cudaMemcpyHostToDevice, e->stream));
+    if (scale_num && v.NP) LK_CUDA(e, cudaMemcpyAsync(e->d_scale + (size_t)vec * v.sc_stride, scale_num, (size_t)v.NP * 2, cudaMemcpyHostToDevice, e->stream));
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    e->theta_ready = false;
+    return LKCUDA_OK;
+}
+
+int lkcuda_fetch_theta(lkcuda_engine *e, double *theta) {
+    LK_ENTER(e);
+    if (!theta) return fail(e, LKCUDA_ERR_ARG, "null destination");
+    if (e->v.NP) LK_CUDA(e, cudaMemcpyAsync(theta, e->d_theta, (size_t)e->v.NP * e->v.B * 8, cudaMemcpyDeviceToHost, e->stream));
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    return LKCUDA_OK;
+}
+
+int lkcuda_vector_device_ptr(lkcuda_engine *e, int32_t vec, void **partial_lh, void **scale_num) {
+    if (!e || vec < 0 || vec >= e->cfg.nvec) return LKCUDA_ERR_ARG;
+    if (partial_lh) *partial_lh = e->d_arena + (size_t)vec * e->v.vec_stride;
+    if (scale_num) *scale_num = e->d_scale + (size_t)vec * e->v.sc_stride;
+    return LKCUDA_OK;
+}
+
+int lkcuda_launch_count(const lkcuda_engine *e, uint64_t *c) { if (!e || !c) return LKCUDA_ERR_ARG; *c = e->launches; return LKCUDA_OK; }
+int lkcuda_algorithmic_bytes(const lkcuda_engine *e, uint64_t *b) { if (!e || !b) return LKCUDA_ERR_ARG; *b = e->bytes; return LKCUDA_OK; }
+
+int lkcuda_reset_counters(lkcuda_engine *e) {
+    LK_ENTER(e);
+    drain_events(e);
+    e->launches = 0; e->bytes = 0;
+    memset(e->kind_ms, 0, sizeof(e->kind_ms)); memset(e->kind_launches, 0, sizeof(e->kind_launches)); memset(e->kind_bytes, 0, sizeof(e->kind_bytes));
+    return LKCUDA_OK;
+}
+
+int lkcuda_set_profiling(lkcuda_engine *e, int32_t on) {
+    LK_ENTER(e);
+    drain_events(e);
+    e->profiling = on != 0;
+    return LKCUDA_OK;
+}
+
+int lkcuda_kernel_stats(lkcuda_engine *e, int32_t kind, uint64_t *launches, uint64_t *bytes, double *device_ms) {
+    LK_ENTER(e);
+    if (kind < 0 || kind >= KIND_COUNT) return fail(e, LKCUDA_ERR_ARG, "bad kernel kind");
+    drain_events(e);
+    if (launches) *launches = e->kind_launches[kind];
+    if (bytes) *bytes = e->kind_bytes[kind];
+    if (device_ms) *device_ms = e->kind_ms[kind];
+    return LKCUDA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,558 @@
+/*
+ * lkcuda_reduce.cu — the streaming reductions of the likelihood engine (sm_100a, FP64):
+ *   branch log-likelihood   computeLikelihoodBranchEigenSIMD   phylokernel.h:734-1020 (+ mixture :728, mixrate :700,
+ *                                                               generic phylotreesse.cpp:1158/1892/2549)
+ *   theta_all build         computeLikelihoodDervEigenSIMD      phylokernel.h:535-579
+ *   df / ddf                computeLikelihoodDervEigenSIMD      phylokernel.h:521-532, 599-725
+ *   lnL from theta_all      computeLikelihoodFromBufferEigenSIMD phylokernel.h:1023-1192
+ *   Newton-Raphson          Optimization::minimizeNewton        optimization.cpp:388-465
+ *
+ * All of them stream `B = K*S` doubles per pattern once and are HBM-bound.  Mapping: G lanes share one
+ * pattern (G = largest power of two dividing B/4, <= 32); lane g reads the 32-byte sectors g, g+G, ... of
+ * the pattern's block, so every load instruction covers G*32 contiguous bytes per pattern and only whole
+ * sectors move.  Per-pattern sums are finished with shuffles inside the G-lane group; the cross-pattern
+ * sums use a fixed-order block reduction and a last-block-done pass (deterministic run to run).
+ * Shapes with B % 4 != 0 take the scalar path (G = 1).
+ */
+#include "lkcuda_common.cuh"
+#include <math.h>
+
+using namespace lkc;
+
+#define RED_THREADS 256
+
+struct GroupShape { int G, gshift, vec; };
+
+static GroupShape group_shape(const DevView &v) {
+    GroupShape s;
+    if (v.B % 4 != 0) { s.G = 1; s.gshift = 0; s.vec = 0; return s; }
+    int nsec = v.B / 4, g = 1, sh = 0;
+    while (g < 32 && nsec % (g * 2) == 0) { g *= 2; sh++; }
+    s.G = g; s.gshift = sh; s.vec = 1;
+    return s;
+}
+
+static int red_grid(const lkcuda_engine *e, long long NP, int G) {
+    long long groups_per_block = RED_THREADS / G;
+    long long need = (NP + groups_per_block - 1) / groups_per_block;
+    long long cap = (long long)e->num_sms * 8;
+    if (cap > e->red_blocks) cap = e->red_blocks;
+    if (need < 1) need = 1;
+    return (int)(need < cap ? need : cap);
+}
+
+/* val0[j] = exp(eval*rate*len) * weight, optionally val1 = cof*val0, val2 = cof*val1  (phylokernel.h:521-532, 767-775) */
+__device__ __forceinline__ void build_val(const DevView &v, double len, double *val0, double *val1, double *val2) {
+    for (int j = threadIdx.x; j < v.B; j += blockDim.x) {
+        int k = j / v.S, i = j - k * v.S;
+        double cof = v.eval[v.blk_eigen[k] * v.S + i] * v.blk_rate[k];
+        double x = exp(cof * len) * v.blk_weight[k];
+        val0[j] = x;
+        if (val1) { double y = cof * x; val1[j] = y; val2[j] = cof * y; }
+    }
+}
+
+/* tipB[st][j] = tip_partial_lh[st][eigen(k)][i] (* val[j]): the tip end's partial expanded to block layout */
+__device__ __forceinline__ void build_tipB(const DevView &v, double *tipB, const double *val) {
+    const int n = (v.SU + 1) * v.B;
+    for (int idx = threadIdx.x; idx < n; idx += blockDim.x) {
+        int st = idx / v.B, j = idx - st * v.B, k = j / v.S, i = j - k * v.S;
+        double t = v.tip[((long long)st * v.E + v.blk_eigen[k]) * v.S + i];
+        tipB[idx] = val ? val[j] * t : t;
+    }
+}
+
+__device__ __forceinline__ double tip_elem(const DevView &v, int st, int j, const double *val) {
+    int k = j / v.S, i = j - k * v.S;
+    double t = v.tip[((long long)st * v.E + v.blk_eigen[k]) * v.S + i];
+    return val ? val[j] * t : t;
+}
+
+template <int N>
+__device__ __forceinline__ void group_sum(double (&a)[N], int G) {
+    for (int off = 1; off < G; off <<= 1) {
+#pragma unroll
+        for (int i = 0; i < N; i++) a[i] += __shfl_xor_sync(0xffffffffu, a[i], off);
+    }
+}
+
+/* log, NaN repair, pattern_lh, frequency weighting, +ASC accumulation: the common tail of branch lnL and
+   lnL-from-buffer (phylokernel.h:828-866, 895-900, 1009-1016). acc[0..3] = {sum freq*log, scale sum, prob_const, repaired} */
+__device__ __forceinline__ void lnl_tail(const DevView &v, long long p, double lh, int sc, double (&acc)[4]) {
+    if (p < v.P) {
+        double l = log(fabs(lh + v.invar[p]));
+        if (isnan(l) || isinf(l)) { l = LK_LOG_THR * 4.0; acc[3] += 1.0; }
+        v.pattern_lh[p] = l;
+        double f = v.freq[p];
+        acc[0] += l * f;
+        if (sc) acc[1] += LK_LOG_THR * f * (double)sc;
+    } else {
+        if (sc >= 1) lh *= LK_THR;
+        acc[2] += lh + v.invar[p];
+    }
+}
+
+__device__ __forceinline__ void lnl_finish(const DevView &v, const double (&acc)[4], double scale_sum) {
+    double lnl = acc[0] + scale_sum, lc = 0.0;
+    if (v.U > 0) { lc = log(1.0 - acc[2]); lnl -= v.nsite * lc; }
+    v.result[LKCUDA_R_LNL] = lnl; v.result[LKCUDA_R_DF] = 0.0; v.result[LKCUDA_R_DDF] = 0.0;
+    v.result[LKCUDA_R_PROB_CONST] = acc[2]; v.result[LKCUDA_R_NREPAIRED] = acc[3]; v.result[LKCUDA_R_SCALE_SUM] = scale_sum;
+    v.result[6] = lc; v.result[7] = 0.0;
+}
+
+/* ------------------------------------------------------------------ branch lnL ------------------------------------------------------------------ */
+
+template <bool TIP, bool VEC>
+__global__ void __launch_bounds__(RED_THREADS) branch_kernel(DevView v, int dad, int node, double len, int gshift, int use_tab) {
+    extern __shared__ __align__(32) double sh[];
+    __shared__ double sred[4 * 32];
+    double *val = sh, *tipB = sh + ((v.B + 3) & ~3);
+    build_val(v, len, val, NULL, NULL);
+    __syncthreads();
+    if (TIP && use_tab) { build_tipB(v, tipB, val); __syncthreads(); }
+
+    const int G = 1 << gshift, g = threadIdx.x & (G - 1);
+    const int gpw = 32 >> gshift;                                  /* groups per warp */
+    const long long warp_id = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    const int gin = (threadIdx.x & 31) >> gshift;
+    const double *lh_node = vec_lh(v, node);
+    const double *lh_dad = TIP ? NULL : vec_lh(v, dad);
+    const int16_t *sc_node = vec_sc(v, node), *sc_dad = TIP ? NULL : vec_sc(v, dad);
+    const uint8_t *st = TIP ? tip_states(v, dad) : NULL;
+    const int nsec = v.B >> 2;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+
+    for (long long base = warp_id * gpw; base < v.NP; base += nwarps * gpw) {
+        const long long p = base + gin;
+        const bool active = p < v.NP;
+        double s[1] = {0.0};
+        if (active) {
+            const int state = TIP ? st[p] : 0;
+            if (VEC) {
+                const double *a = lh_node + p * v.B;
+                for (int q = g; q < nsec; q += G) {
+                    d4 x = ld_stream256(a + 4 * q);
+                    if (TIP) {
+                        double t0, t1, t2, t3;
+                        if (use_tab) { const double *t = tipB + state * v.B + 4 * q; t0 = t[0]; t1 = t[1]; t2 = t[2]; t3 = t[3]; }
+                        else { t0 = tip_elem(v, state, 4 * q, val); t1 = tip_elem(v, state, 4 * q + 1, val); t2 = tip_elem(v, state, 4 * q + 2, val); t3 = tip_elem(v, state, 4 * q + 3, val); }
+                        s[0] = fma(t0, x.x, s[0]); s[0] = fma(t1, x.y, s[0]); s[0] = fma(t2, x.z, s[0]); s[0] = fma(t3, x.w, s[0]);
+                    } else {
+                        d4 y = ld_stream256(lh_dad + p * v.B + 4 * q);
+                        const double *w = val + 4 * q;
+                        s[0] = fma(w[0] * x.x, y.x, s[0]); s[0] = fma(w[1] * x.y, y.y, s[0]);
+                        s[0] = fma(w[2] * x.z, y.z, s[0]); s[0] = fma(w[3] * x.w, y.w, s[0]);
+                    }
+                }
+            } else {
+                const double *a = lh_node + p * v.B;
+                for (int j = 0; j < v.B; j++) {
+                    if (TIP) s[0] = fma(use_tab ? tipB[state * v.B + j] : tip_elem(v, state, j, val), a[j], s[0]);
+                    else s[0] = fma(val[j] * a[j], lh_dad[p * v.B + j], s[0]);
+                }
+            }
+        }
+        group_sum<1>(s, G);
+        if (active && g == 0) {
+            int sc = sc_node[p] + (TIP ? 0 : sc_dad[p]);
+            lnl_tail(v, p, s[0], sc, acc);
+        }
+    }
+    if (grid_reduce<4>(acc, sred, v.red, v.counter)) lnl_finish(v, acc, acc[1]);
+}
+
+/* _pattern_lh[p] -= log(1 - prob_const) for the observed patterns (+ASC, phylokernel.h:1009-1016) */
+__global__ void asc_adjust_kernel(DevView v) {
+    const double lc = v.result[6];
+    for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < v.P; p += (long long)gridDim.x * blockDim.x)
+        v.pattern_lh[p] -= lc;
+}
+
+/* _pattern_lh_cat[p][k] = sum_i val[k][i] * L_node * L_dad (weighted by the block weight, without ptn_invar and
+   scaling: phylotreesse.cpp:1194-1237, 2588-2635) */
+__global__ void __launch_bounds__(RED_THREADS) pattern_lh_cat_kernel(DevView v, int dad, int node, double len) {
+    extern __shared__ __align__(32) double sh[];
+    double *val = sh;
+    build_val(v, len, val, NULL, NULL);
+    __syncthreads();
+    const bool tip = LKCUDA_IS_TIP(dad);
+    const double *lh_node = vec_lh(v, node);
+    const long long total = v.P * v.K;
+    for (long long u = (long long)blockIdx.x * blockDim.x + threadIdx.x; u < total; u += (long long)gridDim.x * blockDim.x) {
+        long long p = u / v.K; int k = (int)(u - p * v.K);
+        const double *a = lh_node + p * v.B + k * v.S;
+        double s = 0.0;
+        if (tip) {
+            int state = tip_states(v, dad)[p];
+            const double *t = v.tip + ((long long)state * v.E + v.blk_eigen[k]) * v.S;
+            for (int i = 0; i < v.S; i++) s += (val[k * v.S + i] * t[i]) * a[i];
+        } else {
+            const double *b = vec_lh(v, dad) + p * v.B + k * v.S;
+            for (int i = 0; i < v.S; i++) s += val[k * v.S + i] * a[i] * b[i];
+        }
+        v.pattern_lh_cat[u] = s;
+    }
+}
+
+/* ------------------------------------------------------------------ theta_all ------------------------------------------------------------------ */
+
+template <bool TIP, bool VEC>
+__global__ void __launch_bounds__(RED_THREADS) theta_kernel(DevView v, int dad, int node, int use_tab) {
+    extern __shared__ __align__(32) double sh[];
+    __shared__ double sred[32];
+    double *tipB = sh;
+    if (TIP && use_tab) { build_tipB(v, tipB, NULL); __syncthreads(); }
+    const double *lh_node = vec_lh(v, node);
+    const double *lh_dad = TIP ? NULL : vec_lh(v, dad);
+    const uint8_t *st = TIP ? tip_states(v, dad) : NULL;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
+    if (VEC) {
+        const int nsec = v.B >> 2;
+        const long long total = v.NP * nsec;
+        for (long long idx = tid; idx < total; idx += nthr) {
+            d4 x = ld_stream256(lh_node + 4 * idx), r;
+            if (TIP) {
+                long long p = idx / nsec; int q = (int)(idx - p * nsec), state = st[p];
+                if (use_tab) { const double *t = tipB + state * v.B + 4 * q; r.x = t[0] * x.x; r.y = t[1] * x.y; r.z = t[2] * x.z; r.w = t[3] * x.w; }
+                else { r.x = tip_elem(v, state, 4 * q, NULL) * x.x; r.y = tip_elem(v, state, 4 * q + 1, NULL) * x.y;
+                       r.z = tip_elem(v, state, 4 * q + 2, NULL) * x.z; r.w = tip_elem(v, state, 4 * q + 3, NULL) * x.w; }
+            } else {
+                d4 y = ld_stream256(lh_dad + 4 * idx);
+                r.x = x.x * y.x; r.y = x.y * y.y; r.z = x.z * y.z; r.w = x.w * y.w;
+            }
+            st_stream256(v.theta + 4 * idx, r);
+        }
+    } else {
+        const long long total = v.NP * v.B;
+        for (long long idx = tid; idx < total; idx += nthr) {
+            if (TIP) { long long p = idx / v.B; int j = (int)(idx - p * v.B); v.theta[idx] = tip_elem(v, st[p], j, NULL) * lh_node[idx]; }
+            else v.theta[idx] = lh_node[idx] * lh_dad[idx];
+        }
+    }
+    /* scale bookkeeping of the branch: lh_scale_factor(node)+lh_scale_factor(dad) and the unobserved patterns' scale_num */
+    const int16_t *sc_node = vec_sc(v, node), *sc_dad = TIP ? NULL : vec_sc(v, dad);
+    double acc[1] = {0.0};
+    for (long long p = tid; p < v.NP; p += nthr) {
+        int sc = sc_node[p] + (TIP ? 0 : sc_dad[p]);
+        if (p < v.P) { if (sc) acc[0] += LK_LOG_THR * v.freq[p] * (double)sc; }
+        else v.theta_sc[p - v.P] = (int16_t)sc;
+    }
+    if (grid_reduce<1>(acc, sred, v.red, v.counter)) v.theta_meta[0] = acc[0];
+}
+
+/* ------------------------------------------------------------------ df / ddf and lnL from theta_all ------------------------------------------------------------------ */
+
+/* per-pattern sums over theta: NV = 3 (lh, df, ddf) or 1 (lh) */
+template <int NV, bool VEC>
+__device__ __forceinline__ void theta_dot(const DevView &v, long long p, int g, int G, const double *val0, const double *val1, const double *val2, double (&s)[NV]) {
+    const double *th = v.theta + p * v.B;
+    if (VEC) {
+        const int nsec = v.B >> 2;
+        for (int q = g; q < nsec; q += G) {
+            d4 x = ld_stream256(th + 4 * q);
+            const double *w0 = val0 + 4 * q;
+            s[0] = fma(x.x, w0[0], s[0]); s[0] = fma(x.y, w0[1], s[0]); s[0] = fma(x.z, w0[2], s[0]); s[0] = fma(x.w, w0[3], s[0]);
+            if (NV == 3) {
+                const double *w1 = val1 + 4 * q, *w2 = val2 + 4 * q;
+                s[1] = fma(x.x, w1[0], s[1]); s[1] = fma(x.y, w1[1], s[1]); s[1] = fma(x.z, w1[2], s[1]); s[1] = fma(x.w, w1[3], s[1]);
+                s[2] = fma(x.x, w2[0], s[2]); s[2] = fma(x.y, w2[1], s[2]); s[2] = fma(x.z, w2[2], s[2]); s[2] = fma(x.w, w2[3], s[2]);
+            }
+        }
+    } else {
+        for (int j = 0; j < v.B; j++) {
+            double x = th[j];
+            s[0] = fma(x, val0[j], s[0]);
+            if (NV == 3) { s[1] = fma(x, val1[j], s[1]); s[2] = fma(x, val2[j], s[2]); }
+        }
+    }
+}
+
+struct DervOut { double df, ddf; };
+
+/* one pass over theta_all at branch length len: returns in the LAST block's thread 0 (true) the finished df, ddf */
+template <bool VEC>
+__device__ __forceinline__ bool derv_pass(const DevView &v, double len, int gshift, double *val0, double *val1, double *val2, double *sred, DervOut *out) {
+    build_val(v, len, val0, val1, val2);
+    __syncthreads();
+    const int G = 1 << gshift, g = threadIdx.x & (G - 1);
+    const int gpw = 32 >> gshift;
+    const long long warp_id = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    const int gin = (threadIdx.x & 31) >> gshift;
+    double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+    for (long long base = warp_id * gpw; base < v.NP; base += nwarps * gpw) {
+        const long long p = base + gin;
+        const bool active = p < v.NP;
+        double s[3] = {0.0, 0.0, 0.0};
+        if (active) theta_dot<3, VEC>(v, p, g, G, val0, val1, val2, s);
+        group_sum<3>(s, G);
+        if (active && g == 0) {
+            double lh = fabs(s[0] + v.invar[p]);
+            if (p < v.P) {      /* phylotreesse.cpp:1106-1132 */
+                double df_frac = s[1] / lh, ddf_frac = s[2] / lh, f = v.freq[p];
+                double t1 = df_frac * f, t2 = ddf_frac * f;
+                acc[0] += t1;
+                acc[1] += t2 - t1 * df_frac;
+            } else { acc[2] += lh; acc[3] += s[1]; acc[4] += s[2]; }
+        }
+    }
+    if (!grid_reduce<5>(acc, sred, v.red, v.counter)) return false;
+    double df = acc[0], ddf = acc[1];
+    if (isnan(df) || isinf(df)) { df = 0.0; ddf = 0.0; }            /* phylokernel.h:647-651 */
+    if (v.U > 0) {                                                  /* phylokernel.h:719-724 */
+        double pc = 1.0 - acc[2], df_frac = acc[3] / pc, ddf_frac = acc[4] / pc;
+        df += v.nsite * df_frac;
+        ddf += v.nsite * (ddf_frac + df_frac * df_frac);
+    }
+    out->df = df; out->ddf = ddf;
+    return true;
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(RED_THREADS) derv_kernel(DevView v, double len, int gshift) {
+    extern __shared__ __align__(32) double sh[];
+    __shared__ double sred[5 * 32];
+    const int Bp = (v.B + 3) & ~3;
+    DervOut o;
+    if (derv_pass<VEC>(v, len, gshift, sh, sh + Bp, sh + 2 * Bp, sred, &o)) {
+        v.result[LKCUDA_R_LNL] = 0.0; v.result[LKCUDA_R_DF] = o.df; v.result[LKCUDA_R_DDF] = o.ddf;
+        v.result[LKCUDA_R_PROB_CONST] = 0.0; v.result[LKCUDA_R_NREPAIRED] = 0.0; v.result[LKCUDA_R_SCALE_SUM] = 0.0;
+        v.result[6] = 0.0; v.result[7] = 0.0;
+    }
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(DevView v, double len, int gshift) {
+    extern __shared__ __align__(32) double sh[];
+    __shared__ double sred[4 * 32];
+    build_val(v, len, sh, NULL, NULL);
+    __syncthreads();
+    const int G = 1 << gshift, g = threadIdx.x & (G - 1);
+    const int gpw = 32 >> gshift;
+    const long long warp_id = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    const int gin = (threadIdx.x & 31) >> gshift;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    for (long long base = warp_id * gpw; base < v.NP; base += nwarps * gpw) {
+        const long long p = base + gin;
+        const bool active = p < v.NP;
+        double s[1] = {0.0};
+        if (active) theta_dot<1, VEC>(v, p, g, G, sh, NULL, NULL, s);
+        group_sum<1>(s, G);
+        /* scale factors were folded into theta_meta[0] when theta_all was built: pass sc = 0 for observed patterns */
+        if (active && g == 0) lnl_tail(v, p, s[0], p < v.P ? 0 : (int)v.theta_sc[p - v.P], acc);
+    }
+    if (grid_reduce<4>(acc, sred, v.red, v.counter)) lnl_finish(v, acc, v.theta_meta[0]);
+}
+
+/* lh_scale_factor of one vector = sum_p LOG_SCALING_THRESHOLD * ptn_freq[p] * scale_num[p] */
+__global__ void __launch_bounds__(RED_THREADS) scale_factor_kernel(DevView v, int vec) {
+    __shared__ double sred[32];
+    const int16_t *sc = vec_sc(v, vec);
+    double acc[1] = {0.0};
+    for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < v.P; p += (long long)gridDim.x * blockDim.x)
+        if (sc[p]) acc[0] += LK_LOG_THR * v.freq[p] * (double)sc[p];
+    if (grid_reduce<1>(acc, sred, v.red, v.counter)) v.result[7] = acc[0];
+}
+
+/* ------------------------------------------------------------------ host side ------------------------------------------------------------------ */
+
+#define TAB_SMEM_LIMIT (44 * 1024)
+
+static int check_ready(lkcuda_engine *e, const char *who) {
+    if (!e->model_set || !e->states_set || !e->weights_set) return fail(e, LKCUDA_ERR_STATE, "%s: tip states, pattern weights and model must be set first", who);
+    return LKCUDA_OK;
+}
+
+static int finish_result(lkcuda_engine *e, double *result) {
+    if (!result) return LKCUDA_OK;
+    return lkcuda_read_result(e, result);
+}
+
+template <bool TIP>
+static void launch_branch(lkcuda_engine *e, const GroupShape &gs, int grid, size_t sm, int dad, int node, double len, int use_tab) {
+    if (gs.vec) branch_kernel<TIP, true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, dad, node, len, gs.gshift, use_tab);
+    else branch_kernel<TIP, false><<<grid, RED_THREADS, sm, e->stream>>>(e->v, dad, node, len, gs.gshift, use_tab);
+}
+
+template <bool TIP>
+static void launch_theta(lkcuda_engine *e, const GroupShape &gs, int grid, size_t sm, int dad, int node, int use_tab) {
+    if (gs.vec) theta_kernel<TIP, true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, dad, node, use_tab);
+    else theta_kernel<TIP, false><<<grid, RED_THREADS, sm, e->stream>>>(e->v, dad, node, use_tab);
+}
+
+static int enqueue_derv(lkcuda_engine *e, double len) {
+    const DevView &v = e->v;
+    GroupShape gs = group_shape(v);
+    int grid = red_grid(e, v.NP, gs.G);
+    size_t sm = (size_t)3 * ((v.B + 3) & ~3) * 8;
+    launch_begin(e, KIND_DERV);
+    if (gs.vec) derv_kernel<true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
+    else derv_kernel<false><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
+    return launch_end(e, KIND_DERV, (uint64_t)v.NP * ((uint64_t)v.B * 8 + 16), "derv_kernel");
+}
+
+extern "C" {
+
+int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result) {
+    LK_ENTER(e);
+    if (node < 0 || node >= e->cfg.nvec || !valid_end(e, dad) || dad == node) return fail(e, LKCUDA_ERR_ARG, "lkcuda_branch_lnl: bad vector / taxon id");
+    int rc = check_ready(e, "lkcuda_branch_lnl");
+    if (rc) return rc;
+    const DevView &v = e->v;
+    GroupShape gs = group_shape(v);
+    const bool tip = LKCUDA_IS_TIP(dad);
+    int grid = red_grid(e, v.NP, gs.G);
+    size_t Bp = (size_t)((v.B + 3) & ~3);
+    size_t tabsz = (size_t)(v.SU + 1) * v.B * 8;
+    int use_tab = tip && (Bp * 8 + tabsz <= TAB_SMEM_LIMIT);
+    size_t sm = Bp * 8 + (use_tab ? tabsz : 0);
+    launch_begin(e, KIND_BRANCH);
+    if (tip) launch_branch<true>(e, gs, grid, sm, dad, node, len, use_tab);
+    else launch_branch<false>(e, gs, grid, sm, dad, node, len, use_tab);
+    uint64_t b = (uint64_t)v.B * 8;
+    rc = launch_end(e, KIND_BRANCH, (uint64_t)v.NP * (tip ? b + 1 + 24 : 2 * b + 24), "branch_kernel");
+    if (rc) return rc;
+    if (v.U > 0 && v.P > 0) {
+        launch_begin(e, KIND_MISC);
+        asc_adjust_kernel<<<(int)((v.P + 255) / 256 < 1184 ? (v.P + 255) / 256 : 1184), 256, 0, e->stream>>>(e->v);
+        rc = launch_end(e, KIND_MISC, 0, "asc_adjust_kernel");
+        if (rc) return rc;
+    }
+    if ((v.flags & LKCUDA_FLAG_PATTERN_LH_CAT) && v.P > 0) {
+        long long total = v.P * v.K;
+        int g2 = (int)((total + RED_THREADS - 1) / RED_THREADS < (long long)e->num_sms * 8 ? (total + RED_THREADS - 1) / RED_THREADS : (long long)e->num_sms * 8);
+        launch_begin(e, KIND_MISC);
+        pattern_lh_cat_kernel<<<g2, RED_THREADS, Bp * 8, e->stream>>>(e->v, dad, node, len);
+        rc = launch_end(e, KIND_MISC, 0, "pattern_lh_cat_kernel");
+        if (rc) return rc;
+    }
+    return finish_result(e, result);
+}
+
+int lkcuda_pattern_lh_cat(lkcuda_engine *e, int32_t dad, int32_t node, double len) {
+    LK_ENTER(e);
+    if (node < 0 || node >= e->cfg.nvec || !valid_end(e, dad) || dad == node) return fail(e, LKCUDA_ERR_ARG, "lkcuda_pattern_lh_cat: bad vector / taxon id");
+    int rc = check_ready(e, "lkcuda_pattern_lh_cat");
+    if (rc) return rc;
+    const DevView &v = e->v;
+    if (v.P == 0) return LKCUDA_OK;
+    long long total = v.P * v.K;
+    int g2 = (int)((total + RED_THREADS - 1) / RED_THREADS < (long long)e->num_sms * 8 ? (total + RED_THREADS - 1) / RED_THREADS : (long long)e->num_sms * 8);
+    launch_begin(e, KIND_MISC);
+    pattern_lh_cat_kernel<<<g2, RED_THREADS, (size_t)((v.B + 3) & ~3) * 8, e->stream>>>(e->v, dad, node, len);
+    return launch_end(e, KIND_MISC, 0, "pattern_lh_cat_kernel");
+}
+
+int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node) {
+    LK_ENTER(e);
+    if (node < 0 || node >= e->cfg.nvec || !valid_end(e, dad) || dad == node) return fail(e, LKCUDA_ERR_ARG, "lkcuda_theta_build: bad vector / taxon id");
+    int rc = check_ready(e, "lkcuda_theta_build");
+    if (rc) return rc;
+    const DevView &v = e->v;
+    GroupShape gs = group_shape(v);
+    const bool tip = LKCUDA_IS_TIP(dad);
+    long long work = gs.vec ? v.NP * (v.B / 4) : v.NP * v.B;
+    long long need = (work + RED_THREADS - 1) / RED_THREADS;
+    long long cap = (long long)e->num_sms * 8 < e->red_blocks ? (long long)e->num_sms * 8 : e->red_blocks;
+    int grid = (int)(need < 1 ? 1 : (need < cap ? need : cap));
+    size_t tabsz = (size_t)(v.SU + 1) * v.B * 8;
+    int use_tab = tip && tabsz <= TAB_SMEM_LIMIT;
+    size_t sm = use_tab ? tabsz : 0;
+    launch_begin(e, KIND_THETA);
+    if (tip) launch_theta<true>(e, gs, grid, sm, dad, node, use_tab);
+    else launch_theta<false>(e, gs, grid, sm, dad, node, use_tab);
+    uint64_t b = (uint64_t)v.B * 8;
+    rc = launch_end(e, KIND_THETA, (uint64_t)v.NP * (tip ? 2 * b + 1 : 3 * b), "theta_kernel");
+    if (rc) return rc;
+    e->theta_ready = true; e->theta_dad = dad; e->theta_node = node;
+    return LKCUDA_OK;
+}
+
+int lkcuda_derv(lkcuda_engine *e, double len, double *result) {
+    LK_ENTER(e);
+    if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_derv: theta_all not built");
+    int rc = enqueue_derv(e, len);
+    if (rc) return rc;
+    return finish_result(e, result);
+}
+
+int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result) {
+    LK_ENTER(e);
+    if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lnl_from_buffer: theta_all not built");
+    const DevView &v = e->v;
+    GroupShape gs = group_shape(v);
+    int grid = red_grid(e, v.NP, gs.G);
+    size_t sm = (size_t)((v.B + 3) & ~3) * 8;
+    launch_begin(e, KIND_FROMBUF);
+    if (gs.vec) frombuf_kernel<true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
+    else frombuf_kernel<false><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
+    int rc = launch_end(e, KIND_FROMBUF, (uint64_t)v.NP * ((uint64_t)v.B * 8 + 24), "frombuf_kernel");
+    if (rc) return rc;
+    if (v.U > 0 && v.P > 0) {
+        launch_begin(e, KIND_MISC);
+        asc_adjust_kernel<<<(int)((v.P + 255) / 256 < 1184 ? (v.P + 255) / 256 : 1184), 256, 0, e->stream>>>(e->v);
+        rc = launch_end(e, KIND_MISC, 0, "asc_adjust_kernel");
+        if (rc) return rc;
+    }
+    return finish_result(e, result);
+}
+
+/* Optimization::minimizeNewton (optimization.cpp:388-465) with computeFuncDerv = -(df, ddf) (phylotree.cpp:2135-2146).
+   v1: the step sequence is driven from the host, one df/ddf launch + one 64-byte read-back per step. */
+int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, double xacc, int32_t maxNRStep, double *out) {
+    LK_ENTER(e);
+    if (!out) return fail(e, LKCUDA_ERR_ARG, "null output");
+    if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_newton_branch: theta_all not built");
+    int j, nev = 0, rc;
+    double df, dx, f, temp, xh, xl, rts, rts_old, d2l, r[LKCUDA_NRESULT];
+#define FUNC_DERV(x) do { rc = enqueue_derv(e, (x)); if (rc) return rc; rc = lkcuda_read_result(e, r); if (rc) return rc; \
+                          f = -r[LKCUDA_R_DF]; df = -r[LKCUDA_R_DDF]; nev++; out[3] = (x); } while (0)
+#define NR_RETURN(x) do { out[0] = (x); out[1] = d2l; out[2] = (double)nev; return LKCUDA_OK; } while (0)
+    rts = xguess;
+    if (rts < x1) rts = x1;
+    if (rts > x2) rts = x2;
+    FUNC_DERV(rts);
+    d2l = df;
+    if (!isfinite(f) || !isfinite(df)) return fail(e, LKCUDA_ERR_STATE, "Wrong computeFuncDerv");
+    if (df >= 0.0 && fabs(f) < xacc) NR_RETURN(rts);
+    if (f < 0.0) { xl = rts; xh = x2; } else { xh = rts; xl = x1; }
+    dx = fabs(xh - xl);
+    for (j = 1; j <= maxNRStep; j++) {
+        rts_old = rts;
+        if ((df <= 0.0) || (((rts - xh) * df - f) * ((rts - xl) * df - f) >= 0.0)) {
+            dx = 0.5 * (xh - xl); rts = xl + dx; d2l = df;
+            if (xl == rts) NR_RETURN(rts);
+        } else {
+            dx = f / df; temp = rts; rts -= dx; d2l = df;
+            if (temp == rts) NR_RETURN(rts);
+        }
+        if (fabs(dx) < xacc || (j == maxNRStep)) NR_RETURN(rts_old);
+        FUNC_DERV(rts);
+        if (!isfinite(f) || !isfinite(df)) return fail(e, LKCUDA_ERR_STATE, "Wrong computeFuncDerv");
+        if (df > 0.0 && fabs(f) < xacc) { d2l = df; NR_RETURN(rts); }
+        if (f < 0.0) xl = rts; else xh = rts;
+    }
+    return fail(e, LKCUDA_ERR_STATE, "Maximum number of iterations exceeded in minimizeNewton");
+#undef FUNC_DERV
+#undef NR_RETURN
+}
+
+int lkcuda_vector_scale_factor(lkcuda_engine *e, int32_t vec, double *out) {
+    LK_ENTER(e);
+    if (!out || vec < 0 || vec >= e->cfg.nvec) return fail(e, LKCUDA_ERR_ARG, "lkcuda_vector_scale_factor: bad argument");
+    if (!e->weights_set) return fail(e, LKCUDA_ERR_STATE, "lkcuda_vector_scale_factor: pattern weights not set");
+    const DevView &v = e->v;
+    int grid = red_grid(e, v.P, 1);
+    launch_begin(e, KIND_MISC);
+    scale_factor_kernel<<<grid, RED_THREADS, 0, e->stream>>>(e->v, vec);
+    int rc = launch_end(e, KIND_MISC, 0, "scale_factor_kernel");
+    if (rc) return rc;
+    LK_CUDA(e, cudaMemcpyAsync(e->h_newton_out, e->d_result + 7, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    *out = e->h_newton_out[0];
+    return LKCUDA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,428 @@
+"""ctypes binding of the host PhyloTree mirror (include/lktree.h) and of the engine C ABI (include/lkcuda.h).
+
+The method names follow the reference's PhyloTree likelihood API (phylotree.h:307 ff.): computeLikelihood,
+computeLikelihoodBranch, computeLikelihoodDerv, computeLikelihoodFromBuffer, optimizeOneBranch,
+optimizeAllBranches, clearAllPartialLH, initializeAllPartialLh, computePatternLhCat.  All arithmetic happens
+behind the C ABI on the GPU; this file only marshals numpy arrays.  There is no CPU fallback: the product
+library is the CUDA one, and loading it or creating an engine without a device raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _build
+
+c_double_p = C.POINTER(C.c_double)
+c_int32_p = C.POINTER(C.c_int32)
+c_int16_p = C.POINTER(C.c_int16)
+c_uint8_p = C.POINTER(C.c_uint8)
+c_int64_p = C.POINTER(C.c_int64)
+c_uint64_p = C.POINTER(C.c_uint64)
+
+ALLREDUCE_FN = C.CFUNCTYPE(None, C.c_void_p, c_double_p, C.c_void_p, C.c_int)
+
+NRESULT = 8
+R_LNL, R_DF, R_DDF, R_PROB_CONST, R_NREPAIRED, R_SCALE_SUM = 0, 1, 2, 3, 4, 5
+KIND_PREP, KIND_PARTIAL, KIND_BRANCH, KIND_THETA, KIND_DERV, KIND_FROMBUF, KIND_NEWTON, KIND_MISC = range(8)
+KIND_NAMES = ["prep", "partial", "branch", "theta", "derv", "frombuf", "newton", "misc"]
+FAMILY_PLAIN, FAMILY_MIXRATE, FAMILY_MIXTURE = 0, 1, 2
+SEQ_DNA, SEQ_PROTEIN, SEQ_BINARY, SEQ_MORPH, SEQ_MULTISTATE, SEQ_CODON = range(6)
+WSL_RATECAT, WSL_MIXTURE, WSL_MIXTURE_RATECAT = 2, 3, 4
+
+# name -> (restype, argtypes); every symbol include/lkcuda.h and include/lktree.h declare
+LKCUDA_SYMBOLS = {
+    "lkcuda_device_count": (C.c_int, [c_int32_p]),
+    "lkcuda_create": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "lkcuda_destroy": (C.c_int, [C.c_void_p]),
+    "lkcuda_last_error": (C.c_char_p, [C.c_void_p]),
+    "lkcuda_memory_bytes": (C.c_int, [C.c_void_p, c_uint64_p]),
+    "lkcuda_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "lkcuda_synchronize": (C.c_int, [C.c_void_p]),
+    "lkcuda_set_tip_states": (C.c_int, [C.c_void_p, c_uint8_p]),
+    "lkcuda_set_pattern_weights": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
+    "lkcuda_set_model": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p, c_int32_p, c_double_p, c_double_p, c_double_p]),
+    "lkcuda_partial_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, c_int32_p, C.c_int32]),
+    "lkcuda_partial_multi": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_int32_p, c_double_p]),
+    "lkcuda_branch_lnl": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_double, c_double_p]),
+    "lkcuda_pattern_lh_cat": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_double]),
+    "lkcuda_theta_build": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "lkcuda_derv": (C.c_int, [C.c_void_p, C.c_double, c_double_p]),
+    "lkcuda_lnl_from_buffer": (C.c_int, [C.c_void_p, C.c_double, c_double_p]),
+    "lkcuda_newton_branch": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32, c_double_p]),
+    "lkcuda_read_result": (C.c_int, [C.c_void_p, c_double_p]),
+    "lkcuda_result_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "lkcuda_fetch_pattern_lh": (C.c_int, [C.c_void_p, c_double_p]),
+    "lkcuda_fetch_pattern_lh_cat": (C.c_int, [C.c_void_p, c_double_p]),
+    "lkcuda_fetch_vector": (C.c_int, [C.c_void_p, C.c_int32, c_double_p, c_int16_p]),
+    "lkcuda_store_vector": (C.c_int, [C.c_void_p, C.c_int32, c_double_p, c_int16_p]),
+    "lkcuda_fetch_theta": (C.c_int, [C.c_void_p, c_double_p]),
+    "lkcuda_vector_scale_factor": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),
+    "lkcuda_vector_device_ptr": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
+    "lkcuda_launch_count": (C.c_int, [C.c_void_p, c_uint64_p]),
+    "lkcuda_algorithmic_bytes": (C.c_int, [C.c_void_p, c_uint64_p]),
+    "lkcuda_reset_counters": (C.c_int, [C.c_void_p]),
+    "lkcuda_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
+    "lkcuda_kernel_stats": (C.c_int, [C.c_void_p, C.c_int32, c_uint64_p, c_uint64_p, c_double_p]),
+}
+
+LKTREE_SYMBOLS = {
+    "lktree_create": (C.c_void_p, []),
+    "lktree_destroy": (None, [C.c_void_p]),
+    "lktree_last_error": (C.c_char_p, [C.c_void_p]),
+    "lktree_set_alignment": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, c_uint8_p, c_double_p, C.POINTER(C.c_char_p), C.c_int32, C.c_int32, C.c_int32]),
+    "lktree_set_const_char": (C.c_int, [C.c_void_p, c_int32_p]),
+    "lktree_set_unobserved": (C.c_int, [C.c_void_p, c_uint8_p, C.c_int32]),
+    "lktree_set_model": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, C.c_double]),
+    "lktree_read_newick": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "lktree_read_adjacency": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "lktree_get_tree_string": (C.c_int, [C.c_void_p, C.c_char_p, C.c_size_t]),
+    "lktree_set_devices": (C.c_int, [C.c_void_p, c_int32_p, C.c_int32]),
+    "lktree_set_process_shard": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "lktree_set_allreduce": (C.c_int, [C.c_void_p, ALLREDUCE_FN, C.c_void_p]),
+    "lktree_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "lktree_set_params": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_int32, C.c_int32]),
+    "lktree_initialize_all_partial_lh": (C.c_int, [C.c_void_p]),
+    "lktree_delete_all_partial_lh": (C.c_int, [C.c_void_p]),
+    "lktree_clear_all_partial_lh": (C.c_int, [C.c_void_p]),
+    "lktree_compute_likelihood": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
+    "lktree_compute_likelihood_branch": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_double_p]),
+    "lktree_compute_likelihood_derv": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p]),
+    "lktree_compute_likelihood_from_buffer": (C.c_int, [C.c_void_p, c_double_p]),
+    "lktree_optimize_one_branch": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p]),
+    "lktree_optimize_all_branches": (C.c_int, [C.c_void_p, C.c_int32, C.c_double, C.c_int32, c_double_p]),
+    "lktree_set_branch_length": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_double]),
+    "lktree_get_branch_length": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_double_p]),
+    "lktree_get_traversal": (C.c_int, [C.c_void_p, c_int32_p, C.c_int32, c_int32_p]),
+    "lktree_branch_vector": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_int32_p, c_int32_p]),
+    "lktree_root_branch": (C.c_int, [C.c_void_p, c_int32_p, c_int32_p]),
+    "lktree_fetch_tip_partial_lh": (C.c_int, [C.c_void_p, c_double_p, C.c_int64, c_int64_p]),
+    "lktree_fetch_ptn_invar": (C.c_int, [C.c_void_p, c_double_p]),
+    "lktree_compute_pattern_lh_cat": (C.c_int, [C.c_void_p, C.c_int32, c_double_p, c_int32_p]),
+    "lktree_engine": (C.c_void_p, [C.c_void_p, C.c_int32]),
+    "lktree_local_patterns": (C.c_int, [C.c_void_p, c_int64_p, c_int64_p]),
+    "lktree_num_partial_lh_computations": (C.c_uint64, [C.c_void_p]),
+}
+
+
+class LkError(RuntimeError):
+    pass
+
+
+def _bind(lib):
+    for table in (LKCUDA_SYMBOLS, LKTREE_SYMBOLS):
+        for name, (res, args) in table.items():
+            fn = getattr(lib, name)      # AttributeError if the library does not export it
+            fn.restype = res
+            fn.argtypes = args
+    return lib
+
+
+_libs = {}
+
+
+def load_library(path=None):
+    """Load (building first if sources are newer) the CUDA product library.  Never falls back to a CPU library."""
+    if path is None:
+        path = _build.build_cuda()
+    path = os.path.abspath(path)
+    if path not in _libs:
+        if not os.path.exists(path):
+            raise LkError("native library %s is missing: run __graft_entry__.build()" % path)
+        _libs[path] = _bind(C.CDLL(path))
+    return _libs[path]
+
+
+def _dp(a):
+    return a.ctypes.data_as(c_double_p)
+
+
+def _f64(a, n=None):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    if n is not None and a.size != n:
+        raise ValueError("expected %d doubles, got %d" % (n, a.size))
+    return a
+
+
+class PhyloTree:
+    """Host-side handle with the reference's PhyloTree likelihood API, backed by the CUDA engine."""
+
+    def __init__(self, lib=None):
+        self.lib = lib if lib is not None else load_library()
+        self.h = self.lib.lktree_create()
+        if not self.h:
+            raise LkError("lktree_create failed")
+        self._cb = None
+        self.ntaxa = 0
+        self.nptn = 0
+        self.nstates = 0
+        self.block = 0
+        self.nblocks = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.lktree_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise LkError(self.lib.lktree_last_error(self.h).decode())
+
+    # ---- inputs -------------------------------------------------------------------------------------------
+    def setAlignment(self, states, ptn_freq, names=None, seq_type=SEQ_DNA, nstates=4, state_unknown=18):
+        states = np.ascontiguousarray(states, dtype=np.uint8)
+        ntaxa, nptn = states.shape
+        freq = _f64(ptn_freq, nptn)
+        arr = None
+        if names is not None:
+            arr = (C.c_char_p * ntaxa)(*[n.encode() for n in names])
+        self._ck(self.lib.lktree_set_alignment(self.h, ntaxa, nptn, states.ctypes.data_as(c_uint8_p), _dp(freq), arr,
+                                               seq_type, nstates, state_unknown))
+        self.ntaxa, self.nptn, self.nstates = ntaxa, nptn, nstates
+        self.nunobs = 0
+
+    def setConstChar(self, const_char):
+        cc = np.ascontiguousarray(const_char, dtype=np.int32)
+        self._ck(self.lib.lktree_set_const_char(self.h, cc.ctypes.data_as(c_int32_p)))
+
+    def setUnobservedPatterns(self, unobs):
+        u = np.ascontiguousarray(unobs, dtype=np.uint8)
+        self._ck(self.lib.lktree_set_unobserved(self.h, u.ctypes.data_as(c_uint8_p), u.size))
+        self.nunobs = int(u.size)
+
+    def setModel(self, family, ncat, nmix, eval_, evec, inv_evec, rates, props, mixprops=None, state_freq=None, p_invar=0.0):
+        S = self.nstates
+        ev, evc, inv = _f64(eval_, nmix * S), _f64(evec, nmix * S * S), _f64(inv_evec, nmix * S * S)
+        r, p = _f64(rates, ncat), _f64(props, ncat)
+        mp = _f64(mixprops, nmix) if mixprops is not None else None
+        sf = _f64(state_freq, S) if state_freq is not None else None
+        self._ck(self.lib.lktree_set_model(self.h, family, ncat, nmix, _dp(ev), _dp(evc), _dp(inv), _dp(r), _dp(p),
+                                           _dp(mp) if mp is not None else None, _dp(sf) if sf is not None else None, float(p_invar)))
+        self.family, self.ncat, self.nmix = family, ncat, nmix
+        self.nblocks = ncat * nmix if family == FAMILY_MIXTURE else ncat
+        self.block = self.nblocks * S
+
+    def readTreeString(self, newick):
+        self._ck(self.lib.lktree_read_newick(self.h, newick.encode()))
+
+    def readAdjacency(self, text):
+        self._ck(self.lib.lktree_read_adjacency(self.h, text.encode()))
+
+    def getTreeString(self):
+        buf = C.create_string_buffer(1 << 22)
+        self._ck(self.lib.lktree_get_tree_string(self.h, buf, len(buf)))
+        return buf.value.decode()
+
+    # ---- placement ----------------------------------------------------------------------------------------
+    def setDevices(self, devices):
+        d = np.ascontiguousarray(devices, dtype=np.int32)
+        self._ck(self.lib.lktree_set_devices(self.h, d.ctypes.data_as(c_int32_p), d.size))
+
+    def setProcessShard(self, rank, world):
+        self._ck(self.lib.lktree_set_process_shard(self.h, rank, world))
+
+    def setAllReduce(self, fn):
+        """fn(host_array_or_None, dev_ptr_or_None, n): sum n doubles over the ranks in place."""
+        if fn is None:
+            self._cb = None
+            self._ck(self.lib.lktree_set_allreduce(self.h, C.cast(None, ALLREDUCE_FN), None))
+            return
+
+        def tramp(user, host_buf, dev_buf, n):
+            if host_buf:
+                fn(np.ctypeslib.as_array(host_buf, shape=(n,)), None, n)
+            else:
+                fn(None, dev_buf, n)
+
+        self._cb = ALLREDUCE_FN(tramp)
+        self._ck(self.lib.lktree_set_allreduce(self.h, self._cb, None))
+
+    def setStream(self, cuda_stream):
+        self._ck(self.lib.lktree_set_stream(self.h, C.c_void_p(cuda_stream)))
+
+    def setParams(self, min_branch_length=1e-6, max_branch_length=100.0, device_newton=False, generic_kernel=False):
+        self._ck(self.lib.lktree_set_params(self.h, min_branch_length, max_branch_length, int(device_newton), int(generic_kernel)))
+
+    # ---- PhyloTree API ------------------------------------------------------------------------------------
+    def initializeAllPartialLh(self):
+        self._ck(self.lib.lktree_initialize_all_partial_lh(self.h))
+
+    def deleteAllPartialLh(self):
+        self._ck(self.lib.lktree_delete_all_partial_lh(self.h))
+
+    def clearAllPartialLH(self):
+        self._ck(self.lib.lktree_clear_all_partial_lh(self.h))
+
+    def localPatterns(self):
+        b, e = C.c_int64(), C.c_int64()
+        self._ck(self.lib.lktree_local_patterns(self.h, C.byref(b), C.byref(e)))
+        return b.value, e.value
+
+    def computeLikelihood(self, pattern_lh=False):
+        lnl = C.c_double()
+        if pattern_lh:
+            b, e = self.localPatterns()
+            out = np.zeros(max(e - b, 1), dtype=np.float64)
+            self._ck(self.lib.lktree_compute_likelihood(self.h, C.byref(lnl), _dp(out)))
+            return lnl.value, out[: e - b]
+        self._ck(self.lib.lktree_compute_likelihood(self.h, C.byref(lnl), None))
+        return lnl.value
+
+    def computeLikelihoodBranch(self, node1, node2):
+        lnl = C.c_double()
+        self._ck(self.lib.lktree_compute_likelihood_branch(self.h, node1, node2, C.byref(lnl)))
+        return lnl.value
+
+    def computeLikelihoodDerv(self, node1, node2, reset_theta=True):
+        df, ddf = C.c_double(), C.c_double()
+        self._ck(self.lib.lktree_compute_likelihood_derv(self.h, node1, node2, int(reset_theta), C.byref(df), C.byref(ddf)))
+        return df.value, ddf.value
+
+    def computeLikelihoodFromBuffer(self):
+        lnl = C.c_double()
+        self._ck(self.lib.lktree_compute_likelihood_from_buffer(self.h, C.byref(lnl)))
+        return lnl.value
+
+    def optimizeOneBranch(self, node1, node2, max_nr_step=100):
+        ln = C.c_double()
+        self._ck(self.lib.lktree_optimize_one_branch(self.h, node1, node2, max_nr_step, C.byref(ln)))
+        return ln.value
+
+    def optimizeAllBranches(self, iterations=100, tolerance=0.001, max_nr_step=100):
+        lnl = C.c_double()
+        self._ck(self.lib.lktree_optimize_all_branches(self.h, iterations, tolerance, max_nr_step, C.byref(lnl)))
+        return lnl.value
+
+    def computePatternLhCat(self, wsl=WSL_MIXTURE_RATECAT):
+        b, e = self.localPatterns()
+        out = np.zeros(max((e - b) * max(self.nblocks, 1), 1), dtype=np.float64)
+        ncol = C.c_int32()
+        self._ck(self.lib.lktree_compute_pattern_lh_cat(self.h, wsl, _dp(out), C.byref(ncol)))
+        return out[: (e - b) * ncol.value].reshape(e - b, ncol.value)
+
+    # ---- inspection ---------------------------------------------------------------------------------------
+    def setBranchLength(self, node1, node2, length):
+        self._ck(self.lib.lktree_set_branch_length(self.h, node1, node2, float(length)))
+
+    def getBranchLength(self, node1, node2):
+        v = C.c_double()
+        self._ck(self.lib.lktree_get_branch_length(self.h, node1, node2, C.byref(v)))
+        return v.value
+
+    def getTraversal(self):
+        cap = 4 * max(self.ntaxa, 2)
+        pairs = np.zeros(2 * cap, dtype=np.int32)
+        cnt = C.c_int32()
+        self._ck(self.lib.lktree_get_traversal(self.h, pairs.ctypes.data_as(c_int32_p), cap, C.byref(cnt)))
+        return pairs[: 2 * cnt.value].reshape(-1, 2).copy()
+
+    def branchVector(self, frm, to):
+        vec, comp = C.c_int32(), C.c_int32()
+        self._ck(self.lib.lktree_branch_vector(self.h, frm, to, C.byref(vec), C.byref(comp)))
+        return vec.value, bool(comp.value)
+
+    def rootBranch(self):
+        a, b = C.c_int32(), C.c_int32()
+        self._ck(self.lib.lktree_root_branch(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def tipPartialLh(self):
+        cap = 1 << 20
+        out = np.zeros(cap, dtype=np.float64)
+        cnt = C.c_int64()
+        self._ck(self.lib.lktree_fetch_tip_partial_lh(self.h, _dp(out), cap, C.byref(cnt)))
+        return out[: cnt.value].copy()
+
+    def ptnInvar(self):
+        out = np.zeros(self.nptn + self.nunobs + 1, dtype=np.float64)
+        self._ck(self.lib.lktree_fetch_ptn_invar(self.h, _dp(out)))
+        return out[: self.nptn + self.nunobs]
+
+    def numPartialLhComputations(self):
+        return int(self.lib.lktree_num_partial_lh_computations(self.h))
+
+    # ---- engine-level access (shard i) --------------------------------------------------------------------
+    def engine(self, i=0):
+        e = self.lib.lktree_engine(self.h, i)
+        if not e:
+            raise LkError("no engine %d (initializeAllPartialLh first)" % i)
+        return e
+
+    def _eck(self, e, rc):
+        if rc != 0:
+            raise LkError(self.lib.lkcuda_last_error(e).decode() + " (status %d)" % rc)
+
+    def fetchVector(self, vec, shard=0):
+        e = self.engine(shard)
+        b, en = self.localPatterns()
+        npat = (en - b) + self.nunobs
+        lh = np.zeros(npat * self.block, dtype=np.float64)
+        sc = np.zeros(npat, dtype=np.int16)
+        self._eck(e, self.lib.lkcuda_fetch_vector(e, vec, _dp(lh), sc.ctypes.data_as(c_int16_p)))
+        return lh.reshape(npat, self.block), sc
+
+    def fetchTheta(self, shard=0):
+        e = self.engine(shard)
+        b, en = self.localPatterns()
+        npat = (en - b) + self.nunobs
+        th = np.zeros(npat * self.block, dtype=np.float64)
+        self._eck(e, self.lib.lkcuda_fetch_theta(e, _dp(th)))
+        return th.reshape(npat, self.block)
+
+    def vectorScaleFactor(self, vec, shard=0):
+        e = self.engine(shard)
+        v = C.c_double()
+        self._eck(e, self.lib.lkcuda_vector_scale_factor(e, vec, C.byref(v)))
+        return v.value
+
+    def launchCount(self, shard=0):
+        e = self.engine(shard)
+        v = C.c_uint64()
+        self._eck(e, self.lib.lkcuda_launch_count(e, C.byref(v)))
+        return v.value
+
+    def algorithmicBytes(self, shard=0):
+        e = self.engine(shard)
+        v = C.c_uint64()
+        self._eck(e, self.lib.lkcuda_algorithmic_bytes(e, C.byref(v)))
+        return v.value
+
+    def memoryBytes(self, shard=0):
+        e = self.engine(shard)
+        v = C.c_uint64()
+        self._eck(e, self.lib.lkcuda_memory_bytes(e, C.byref(v)))
+        return v.value
+
+    def resetCounters(self, shard=0):
+        e = self.engine(shard)
+        self._eck(e, self.lib.lkcuda_reset_counters(e))
+
+    def setProfiling(self, on, shard=0):
+        e = self.engine(shard)
+        self._eck(e, self.lib.lkcuda_set_profiling(e, int(on)))
+
+    def kernelStats(self, shard=0):
+        """{kind: (launches, algorithmic bytes, device ms)}"""
+        e = self.engine(shard)
+        out = {}
+        for k, name in enumerate(KIND_NAMES):
+            n, b, ms = C.c_uint64(), C.c_uint64(), C.c_double()
+            self._eck(e, self.lib.lkcuda_kernel_stats(e, k, C.byref(n), C.byref(b), C.byref(ms)))
+            out[name] = (n.value, b.value, ms.value)
+        return out
+
+    def resultDevicePtr(self, shard=0):
+        e = self.engine(shard)
+        p = C.c_void_p()
+        self._eck(e, self.lib.lkcuda_result_device_ptr(e, C.byref(p)))
+        return p.value
+
+    def synchronize(self, shard=0):
+        e = self.engine(shard)
+        self._eck(e, self.lib.lkcuda_synchronize(e))

@@ -407,6 +407,31 @@ int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     return LKCUDA_OK;
 }
 
+/* _pattern_lh_cat only (phylotreesse.cpp:1194-1237) */
+int lkcuda_pattern_lh_cat(lkcuda_engine *e, int32_t dad, int32_t node, double len) {
+    if (!e || node < 0 || node >= e->cfg.nvec || bad_end(e, dad)) return LKCUDA_ERR_ARG;
+    size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all, P = (size_t)e->cfg.nptn;
+    double *val = (double *)malloc(block * 8);
+    build_val(e, len, val, NULL, NULL);
+    const double *lh_node = vec_lh(e, node);
+    const uint8_t *st = LKCUDA_IS_TIP(dad) ? e->states + (size_t)LKCUDA_TIP_TAXON(dad) * nptn : NULL;
+    const double *lh_dad = st ? NULL : vec_lh(e, dad);
+    for (size_t ptn = 0; ptn < P; ptn++)
+        for (size_t k = 0; k < K; k++) {
+            double lh_cat = 0.0;
+            if (st) {
+                const double *tip = e->tip_lh + ((size_t)st[ptn] * e->E + (size_t)e->blk_eigen[k]) * S;
+                for (size_t i = 0; i < S; i++) lh_cat += (val[k * S + i] * tip[i]) * lh_node[ptn * block + k * S + i];
+            } else {
+                for (size_t i = 0; i < S; i++) lh_cat += val[k * S + i] * lh_node[ptn * block + k * S + i] * lh_dad[ptn * block + k * S + i];
+            }
+            e->pattern_lh_cat[ptn * K + k] = lh_cat;
+        }
+    free(val);
+    e->launches++;
+    return LKCUDA_OK;
+}
+
 int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node) {
     if (!e || node < 0 || node >= e->cfg.nvec || bad_end(e, dad)) return LKCUDA_ERR_ARG;
     size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all, P = (size_t)e->cfg.nptn;
@@ -578,3 +603,9 @@ int lkcuda_vector_device_ptr(lkcuda_engine *e, int32_t vec, void **partial_lh, v
 int lkcuda_launch_count(const lkcuda_engine *e, uint64_t *c) { if (!e || !c) return LKCUDA_ERR_ARG; *c = e->launches; return LKCUDA_OK; }
 int lkcuda_algorithmic_bytes(const lkcuda_engine *e, uint64_t *b) { if (!e || !b) return LKCUDA_ERR_ARG; *b = e->bytes; return LKCUDA_OK; }
 int lkcuda_reset_counters(lkcuda_engine *e) { if (!e) return LKCUDA_ERR_ARG; e->launches = 0; e->bytes = 0; return LKCUDA_OK; }
+int lkcuda_set_profiling(lkcuda_engine *e, int32_t on) { (void)on; return e ? LKCUDA_OK : LKCUDA_ERR_ARG; }
+int lkcuda_kernel_stats(lkcuda_engine *e, int32_t kind, uint64_t *launches, uint64_t *bytes, double *device_ms) {
+    if (!e || kind < 0 || kind >= LKCUDA_NKIND) return LKCUDA_ERR_ARG;
+    if (launches) *launches = 0; if (bytes) *bytes = 0; if (device_ms) *device_ms = 0.0;
+    return LKCUDA_OK;
+}

@@ -287,15 +287,21 @@ static int do_time(int argc, char **argv) {
 
     tree->clearAllPartialLH();
     double lnl = tree->computeLikelihood();           // warm-up
-    std::vector<double> lnl_t;
+    PhyloNode *n1 = (PhyloNode*)tree->root, *n2 = (PhyloNode*)tree->root->neighbors[0]->node;
+    double df = 0, ddf = 0;
+    /* one "step" = full-tree lnL (all partials recomputed) + theta_all rebuild + df/ddf on the root-leaf branch */
+    std::vector<double> lnl_t, step_t;
     for (int r = 0; r < lnl_reps; r++) {
         double a = getRealTime();
         tree->clearAllPartialLH();
         lnl = tree->computeLikelihood();
-        lnl_t.push_back(getRealTime() - a);
+        double b = getRealTime();
+        tree->theta_computed = false;
+        tree->computeLikelihoodDerv((PhyloNeighbor*)n1->findNeighbor(n2), n1, df, ddf);
+        double c = getRealTime();
+        lnl_t.push_back(b - a);
+        step_t.push_back(c - a);
     }
-    PhyloNode *n1 = (PhyloNode*)tree->root, *n2 = (PhyloNode*)tree->root->neighbors[0]->node;
-    double df = 0, ddf = 0;
     tree->theta_computed = false;
     tree->computeLikelihoodDerv((PhyloNeighbor*)n1->findNeighbor(n2), n1, df, ddf);   // builds theta
     double a = getRealTime();
@@ -312,12 +318,15 @@ static int do_time(int argc, char **argv) {
     double sum = 0, best = 1e300;
     for (size_t i = 0; i < lnl_t.size(); i++) { sum += lnl_t[i]; best = std::min(best, lnl_t[i]); }
     double mean = lnl_t.empty() ? 0 : sum / lnl_t.size();
+    double step_sum = 0;
+    for (size_t i = 0; i < step_t.size(); i++) step_sum += step_t[i];
+    double step_mean = step_t.empty() ? 0 : step_sum / step_t.size();
     printf("{\"ref_time\": true, \"kernel\": \"%s\", \"threads\": %d, \"nptn\": %zu, \"ntaxa\": %zu, \"blocks\": %zu, "
-           "\"lnl\": %.12f, \"lnl_reps\": %d, \"lnl_s_mean\": %.6g, \"lnl_s_best\": %.6g, "
+           "\"lnl\": %.12f, \"lnl_reps\": %d, \"lnl_s_mean\": %.6g, \"lnl_s_best\": %.6g, \"step_s_mean\": %.6g, \"step_s_total\": %.6g, "
            "\"df\": %.12g, \"ddf\": %.12g, \"derv_reps\": %d, \"derv_s_mean\": %.6g, "
            "\"oab_lnl\": %.12f, \"oab_reps\": %d, \"oab_s_mean\": %.6g, \"setup_s\": %.4g}\n",
            tree->sse == LK_EIGEN_SSE ? (instruction_set >= 7 ? "AVX" : "SSE") : "generic",
-           params.num_threads, P, ntaxa, blocks, lnl, lnl_reps, mean, lnl_t.empty() ? 0.0 : best,
+           params.num_threads, P, ntaxa, blocks, lnl, lnl_reps, mean, lnl_t.empty() ? 0.0 : best, step_mean, step_sum,
            df, ddf, derv_reps, t_derv, oab, oab_reps, t_oab, t_setup);
     return 0;
 }

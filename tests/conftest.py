@@ -1,0 +1,30 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session")
+def cuda_lib():
+    """The product library; tests marked gpu fail loudly if it cannot be loaded or no device exists."""
+    import ctypes
+    import iqtree_b200
+    lib = iqtree_b200.load_library()
+    n = ctypes.c_int32()
+    rc = lib.lkcuda_device_count(ctypes.byref(n))
+    assert rc == 0 and n.value > 0, "gpu test without a CUDA device (lkcuda_device_count -> %d, %d devices)" % (rc, n.value)
+    return lib
+
+
+@pytest.fixture(scope="session")
+def oracle_lib():
+    from oracle.oracle_lib import load_oracle_library
+    return load_oracle_library()

@@ -1,0 +1,53 @@
+"""CPU suite: the product C-ABI library loads without a GPU, exports every symbol include/*.h declares, and
+refuses to compute without a device (no CPU fallback)."""
+import ctypes
+import os
+import re
+
+import iqtree_b200
+from iqtree_b200 import _build
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared(header):
+    text = open(os.path.join(ROOT, "include", header)).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(lk(?:cuda|tree)_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_cuda_library_exports_every_declared_symbol():
+    lib = ctypes.CDLL(_build.build_cuda())
+    names = declared("lkcuda.h") + declared("lktree.h")
+    assert len(names) > 60
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+    bound = set(iqtree_b200.LKCUDA_SYMBOLS) | set(iqtree_b200.LKTREE_SYMBOLS)
+    assert set(names) - {"lktree_allreduce_fn"} <= bound, sorted(set(names) - bound)
+
+
+def test_oracle_library_exports_the_same_abi(oracle_lib):
+    for n in declared("lkcuda.h") + declared("lktree.h"):
+        assert hasattr(oracle_lib, n), n
+
+
+def test_no_cpu_fallback_without_device():
+    lib = iqtree_b200.load_library()
+    n = ctypes.c_int32(-1)
+    rc = lib.lkcuda_device_count(ctypes.byref(n))
+    if rc == 0 and n.value > 0:
+        return      # running on a GPU box: nothing to check here
+    import numpy as np
+    from iqtree_b200 import modelinputs as mi
+    t = iqtree_b200.PhyloTree(lib=lib)
+    names = ["t%d" % i for i in range(4)]
+    t.setAlignment(np.zeros((4, 8), dtype=np.uint8), np.ones(8), names=names)
+    t.readTreeString("(t0:0.1,t1:0.1,(t2:0.1,t3:0.1):0.1);")
+    m = mi.gtr_g4_inputs()
+    t.setModel(0, 4, 1, m["eval"], m["evec"], m["inv_evec"], m["rates"], m["props"])
+    try:
+        t.computeLikelihood()
+    except iqtree_b200.LkError as ex:
+        assert "no CUDA device" in str(ex)
+    else:
+        raise AssertionError("the product path computed something without a GPU")

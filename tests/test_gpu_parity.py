@@ -1,0 +1,100 @@
+"""GPU suite (-m gpu): the CUDA engine, driven through the C ABI, against the golden fixtures of the unmodified
+reference AND against the CPU oracle on the same inputs."""
+import numpy as np
+import pytest
+
+import golden_util as gu
+import iqtree_b200
+from iqtree_b200 import modelinputs as mi
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("case", gu.golden_cases())
+def test_cuda_matches_reference(case, cuda_lib):
+    g = gu.Golden(case)
+    t = gu.build_tree(g, cuda_lib)
+    gu.run_all_checks(t, g, full_opt=g.meta["block"] <= 256)
+    assert t.launchCount() > 0
+    t.close()
+
+
+@pytest.mark.parametrize("case", ["dna_example_gtr_g4", "dna_deep_scaling", "aa_lg_g4", "morph_mk_asc"])
+def test_cuda_device_newton(case, cuda_lib):
+    """optimizeAllBranches with the Newton loop driven inside the engine gives the same lengths"""
+    g = gu.Golden(case)
+    t = gu.build_tree(g, cuda_lib, device_newton=True)
+    t.initializeAllPartialLh()
+    gu.check_optimize(t, g, full=True)
+    t.close()
+
+
+@pytest.mark.parametrize("case", ["dna_example_gtr_g4", "aa_lg_g4", "codon_gy", "dna_example_hky_r3"])
+def test_generic_kernel_flag(case, cuda_lib):
+    """the -fastlk semantics (zero guard, _pattern_lh_cat filled by every branch call) on non-generic fixtures"""
+    g = gu.Golden(case)
+    t = gu.build_tree(g, cuda_lib, generic=True)
+    t.initializeAllPartialLh()
+    gu.check_likelihood(t, g)
+    t.close()
+
+
+def _synthetic(lib, ntaxa, nptn, nstates, ncat, seed, state_unknown):
+    names = ["t%d" % i for i in range(ntaxa)]
+    nwk = mi.random_tree_newick(ntaxa, seed, names)
+    st = mi.simulate_patterns(nwk, names, nptn, nstates, seed)
+    rng = np.random.default_rng(seed)
+    st[rng.integers(0, ntaxa, nptn // 50), rng.integers(0, nptn, nptn // 50)] = state_unknown
+    freq = rng.integers(1, 4, nptn).astype(np.float64)
+    mdl = mi.gtr_g4_inputs(seed, ncat=ncat) if nstates == 4 else mi.random_reversible_inputs(nstates, seed, ncat=ncat)
+    t = iqtree_b200.PhyloTree(lib=lib)
+    t.setAlignment(st, freq, names=names, seq_type=0 if nstates == 4 else (1 if nstates == 20 else 4), nstates=nstates,
+                   state_unknown=state_unknown)
+    t.readTreeString(nwk)
+    t.setModel(0, ncat, 1, mdl["eval"], mdl["evec"], mdl["inv_evec"], mdl["rates"], mdl["props"], None, mdl["state_freq"], 0.0)
+    return t
+
+
+@pytest.mark.parametrize("shape", [(24, 5000, 4, 4, 18), (150, 2000, 4, 4, 18), (12, 700, 20, 4, 23), (10, 300, 64, 1, 64),
+                                   (9, 257, 4, 8, 18), (7, 100, 7, 3, 7), (6, 33, 4, 1, 18), (5, 1, 4, 4, 18)])
+def test_cuda_matches_oracle_synthetic(shape, cuda_lib, oracle_lib):
+    """same seeded inputs through the CUDA engine and through the CPU oracle: lnL, pattern lh, scale_num, df/ddf, OAB"""
+    ntaxa, nptn, S, C, SU = shape
+    a = _synthetic(cuda_lib, ntaxa, nptn, S, C, 3, SU)
+    b = _synthetic(oracle_lib, ntaxa, nptn, S, C, 3, SU)
+    for t in (a, b):
+        t.initializeAllPartialLh()
+    la, pa = a.computeLikelihood(pattern_lh=True)
+    lb, pb = b.computeLikelihood(pattern_lh=True)
+    assert abs(la - lb) <= gu.LNL_RTOL * abs(lb)
+    gu.rel_close(pa, pb, gu.PTN_RTOL, "pattern_lh")
+    assert a.rootBranch() == b.rootBranch()
+    trav = a.getTraversal()
+    assert np.array_equal(trav, b.getTraversal())
+    for (n1, n2) in trav[:: max(1, len(trav) // 12)]:
+        va, ca = a.branchVector(int(n1), int(n2))
+        vb, cb = b.branchVector(int(n1), int(n2))
+        assert va == vb and ca == cb
+        da, db = a.computeLikelihoodDerv(int(n1), int(n2)), b.computeLikelihoodDerv(int(n1), int(n2))
+        tol = (1e-7 if S >= 64 else 1e-9) * max(abs(db[0]), abs(db[1]), 1.0)
+        assert abs(da[0] - db[0]) <= tol and abs(da[1] - db[1]) <= tol
+        if va >= 0 and ca:
+            (lha, sca), (lhb, scb) = a.fetchVector(va), b.fetchVector(vb)
+            assert np.array_equal(sca, scb)
+            gu.block_close(lha, lhb, 1e-7 if S >= 64 else 1e-9, "partial_lh")
+    oa, ob = a.optimizeAllBranches(2), b.optimizeAllBranches(2)
+    assert abs(oa - ob) <= gu.LNL_RTOL * abs(ob)
+    for (n1, n2) in trav:
+        assert abs(a.getBranchLength(int(n1), int(n2)) - b.getBranchLength(int(n1), int(n2))) <= gu.BRLEN_ATOL
+    a.close(); b.close()
+
+
+def test_two_shards_one_device(cuda_lib):
+    """pattern sharding: two engines on the same device give the sums of one (host-side reduction of the shards)"""
+    g = gu.Golden("dna_example_gtr_i_g4")
+    t = gu.build_tree(g, cuda_lib, devices=[0, 0])
+    t.initializeAllPartialLh()
+    gu.check_likelihood(t, g)
+    gu.check_derivatives(t, g)
+    gu.check_optimize(t, g, full=False)
+    t.close()
