@@ -74,6 +74,8 @@ int lktree_fetch_ptn_invar(lktree *h, double *out);
 int lktree_compute_pattern_lh_cat(lktree *h, int32_t wsl, double *out, int32_t *ncol);
 lkcuda_engine *lktree_engine(lktree *h, int32_t i);
 int lktree_local_patterns(lktree *h, int64_t *begin, int64_t *end);
+/* global pattern range of in-process shard i (engine i) */
+int lktree_shard_patterns(lktree *h, int32_t i, int64_t *begin, int64_t *end);
 uint64_t lktree_num_partial_lh_computations(lktree *h);
 
 #ifdef __cplusplus

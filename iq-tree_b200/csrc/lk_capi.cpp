@@ -192,6 +192,13 @@ int lktree_local_patterns(lktree *h, int64_t *begin, int64_t *end) {
     LK_TRY(h) *begin = h->tree.localPatternBegin(); *end = h->tree.localPatternEnd(); LK_CATCH(h)
 }
 
+int lktree_shard_patterns(lktree *h, int32_t i, int64_t *begin, int64_t *end) {
+    LK_TRY(h)
+    if (!h->tree.engine((size_t)i)) throw std::runtime_error("no such shard");
+    *begin = h->tree.shardBegin((size_t)i); *end = h->tree.shardBegin((size_t)i + 1);
+    LK_CATCH(h)
+}
+
 uint64_t lktree_num_partial_lh_computations(lktree *h) { return h ? h->tree.num_partial_lh_computations : 0; }
 
 }  // extern "C"

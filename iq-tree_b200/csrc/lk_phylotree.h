@@ -102,6 +102,8 @@ public:
     void deleteAllPartialLh();
     int64_t localPatternBegin() const { return ptn_begin_; }
     int64_t localPatternEnd() const { return ptn_end_; }
+    int64_t shardBegin(size_t i) const { return i < shard_begin_.size() ? shard_begin_[i] : ptn_end_; }
+    size_t numEngines() const { return engines_.size(); }
     lkcuda_engine *engine(size_t i = 0) { return i < engines_.size() ? engines_[i] : NULL; }
 
     /* ---- the PhyloTree likelihood API ---- */

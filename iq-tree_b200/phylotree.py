@@ -101,6 +101,7 @@ LKTREE_SYMBOLS = {
     "lktree_compute_pattern_lh_cat": (C.c_int, [C.c_void_p, C.c_int32, c_double_p, c_int32_p]),
     "lktree_engine": (C.c_void_p, [C.c_void_p, C.c_int32]),
     "lktree_local_patterns": (C.c_int, [C.c_void_p, c_int64_p, c_int64_p]),
+    "lktree_shard_patterns": (C.c_int, [C.c_void_p, C.c_int32, c_int64_p, c_int64_p]),
     "lktree_num_partial_lh_computations": (C.c_uint64, [C.c_void_p]),
 }
 
@@ -358,28 +359,49 @@ class PhyloTree:
         if rc != 0:
             raise LkError(self.lib.lkcuda_last_error(e).decode() + " (status %d)" % rc)
 
-    def fetchVector(self, vec, shard=0):
-        e = self.engine(shard)
-        b, en = self.localPatterns()
-        npat = (en - b) + self.nunobs
-        lh = np.zeros(npat * self.block, dtype=np.float64)
-        sc = np.zeros(npat, dtype=np.int16)
-        self._eck(e, self.lib.lkcuda_fetch_vector(e, vec, _dp(lh), sc.ctypes.data_as(c_int16_p)))
-        return lh.reshape(npat, self.block), sc
+    def numShards(self):
+        n = 0
+        while self.lib.lktree_engine(self.h, n):
+            n += 1
+        return n
 
-    def fetchTheta(self, shard=0):
-        e = self.engine(shard)
-        b, en = self.localPatterns()
-        npat = (en - b) + self.nunobs
-        th = np.zeros(npat * self.block, dtype=np.float64)
-        self._eck(e, self.lib.lkcuda_fetch_theta(e, _dp(th)))
-        return th.reshape(npat, self.block)
+    def shardPatterns(self, i):
+        b, e = C.c_int64(), C.c_int64()
+        self._ck(self.lib.lktree_shard_patterns(self.h, i, C.byref(b), C.byref(e)))
+        return b.value, e.value
 
-    def vectorScaleFactor(self, vec, shard=0):
-        e = self.engine(shard)
-        v = C.c_double()
-        self._eck(e, self.lib.lkcuda_vector_scale_factor(e, vec, C.byref(v)))
-        return v.value
+    def _fetch_shards(self, width, dtype, fetch):
+        """concatenate the in-process shards: observed patterns in order, then the (replicated) unobserved ones"""
+        obs, unobs = [], None
+        for i in range(self.numShards()):
+            b, en = self.shardPatterns(i)
+            npat = (en - b) + self.nunobs
+            buf = np.zeros(max(npat * width, 1), dtype=dtype)
+            fetch(self.engine(i), buf)
+            buf = buf[: npat * width].reshape(npat, width)
+            obs.append(buf[: en - b])
+            if unobs is None:
+                unobs = buf[en - b:]
+        return np.concatenate(obs + [unobs], axis=0)
+
+    def fetchVector(self, vec):
+        lh = self._fetch_shards(self.block, np.float64,
+                                lambda e, buf: self._eck(e, self.lib.lkcuda_fetch_vector(e, vec, _dp(buf), None)))
+        sc = self._fetch_shards(1, np.int16,
+                                lambda e, buf: self._eck(e, self.lib.lkcuda_fetch_vector(e, vec, None, buf.ctypes.data_as(c_int16_p))))
+        return lh, sc[:, 0].copy()
+
+    def fetchTheta(self):
+        return self._fetch_shards(self.block, np.float64, lambda e, buf: self._eck(e, self.lib.lkcuda_fetch_theta(e, _dp(buf))))
+
+    def vectorScaleFactor(self, vec):
+        tot = 0.0
+        for i in range(self.numShards()):
+            e = self.engine(i)
+            v = C.c_double()
+            self._eck(e, self.lib.lkcuda_vector_scale_factor(e, vec, C.byref(v)))
+            tot += v.value
+        return tot
 
     def launchCount(self, shard=0):
         e = self.engine(shard)
