@@ -28,7 +28,8 @@ PhyloTree::PhyloTree()
       theta_computed(false), num_partial_lh_computations(0), nstates(0), ncat(1), nmix(1), family(FAMILY_PLAIN),
       state_unknown(0), seq_type(SEQ_DNA), ntaxa(0), nptn(0), nunobs(0), nsite(0), p_invar_(0.0),
       proc_rank_(0), proc_world_(1), allreduce_(NULL), allreduce_user_(NULL), stream_(NULL),
-      ptn_begin_(0), ptn_end_(0), tip_partial_lh_computed_(false), inputs_uploaded_(false), nvec_(0) {}
+      ptn_begin_(0), ptn_end_(0), tip_partial_lh_computed_(false), weights_uploaded_(false), model_uploaded_(false),
+      freq_dirty_(true), invar_dirty_(true), model_dirty_(true), nvec_(0) {}
 
 PhyloTree::~PhyloTree() {
     deleteAllPartialLh();
@@ -250,14 +251,16 @@ void PhyloTree::setAlignment(int ntaxa_, int64_t nptn_, const uint8_t *states, c
     seq_names = names;
     const_char_.clear();
     unobs_.clear(); nunobs = 0;
+    freq_dirty_ = invar_dirty_ = true;
 }
 
 void PhyloTree::setUnobservedPatterns(const std::vector<uint8_t> &unobs) {
     deleteAllPartialLh();
     unobs_ = unobs; nunobs = (int64_t)unobs.size();
+    invar_dirty_ = true;
 }
 
-void PhyloTree::setConstChar(const int32_t *cc) { const_char_.assign(cc, cc + nptn); inputs_uploaded_ = false; tip_partial_lh_computed_ = false; }
+void PhyloTree::setConstChar(const int32_t *cc) { const_char_.assign(cc, cc + nptn); invar_dirty_ = true; tip_partial_lh_computed_ = false; }
 
 void PhyloTree::setModel(int family_, int ncat_, int nmix_, const double *eval, const double *evec, const double *inv_evec,
                          const double *rates, const double *props, const double *mixprops,
@@ -271,18 +274,27 @@ void PhyloTree::setModel(int family_, int ncat_, int nmix_, const double *eval, 
     rates_.assign(rates, rates + ncat);
     props_.assign(props, props + ncat);
     if (mixprops) mixprops_.assign(mixprops, mixprops + nmix); else mixprops_.assign(nmix, 1.0);
-    if (state_freq) state_freq_.assign(state_freq, state_freq + S); else state_freq_.assign(S, 1.0 / S);
+    std::vector<double> sf;
+    if (state_freq) sf.assign(state_freq, state_freq + S); else sf.assign(S, 1.0 / S);
+    // ptn_invar (phylotreesse.cpp:543-569) depends on p_invar and the state frequencies only
+    if (p_invar != p_invar_ || sf != state_freq_) invar_dirty_ = true;
+    state_freq_.swap(sf);
     p_invar_ = p_invar;
     // every parameter change is followed by clearAllPartialLH in the reference; the tip table must be redone
     tip_partial_lh_computed_ = false;
+    model_dirty_ = true;
 }
 
 /* phylotreesse.cpp:459-527 */
 void PhyloTree::computeTipPartialLikelihood() {
     if (tip_partial_lh_computed_) return;
     tip_partial_lh_computed_ = true;
-    computePtnFreq();
-    computePtnInvar();
+    // the reference recomputes all three after every clearAllPartialLH (phylotree.cpp:499); their inputs are tracked
+    // here so that an unchanged 8 MB ptn_freq / ptn_invar is neither rebuilt nor sent to the device again
+    if (freq_dirty_) { computePtnFreq(); freq_dirty_ = false; weights_uploaded_ = false; }
+    if (invar_dirty_) { computePtnInvar(); invar_dirty_ = false; weights_uploaded_ = false; }
+    if (!model_dirty_) return;
+    model_dirty_ = false; model_uploaded_ = false;
     int S = nstates, M = nmix;
     tip_partial_lh.assign((size_t)(state_unknown + 1) * S * M, 0.0);
     const double *all_inv_evec = &inv_evec_[0];
@@ -322,7 +334,6 @@ void PhyloTree::computeTipPartialLikelihood() {
                 }
             }
     }
-    inputs_uploaded_ = false;
 }
 
 void PhyloTree::computePtnFreq() {   // phylotreesse.cpp:531-541
@@ -405,7 +416,8 @@ void PhyloTree::initializeAllPartialLh() {
         }
         check(lkcuda_set_tip_states(e, na ? &st[0] : (const uint8_t*)""), e, "lkcuda_set_tip_states");
     }
-    inputs_uploaded_ = false;
+    weights_uploaded_ = model_uploaded_ = false;
+    freq_dirty_ = invar_dirty_ = model_dirty_ = true;
     tip_partial_lh_computed_ = false;
     vec_level_.assign(nvec_, 0);
     clearAllPartialLH();
@@ -420,7 +432,7 @@ void PhyloTree::deleteAllPartialLh() {
 
 void PhyloTree::ensureInputs() {
     if (!tip_partial_lh_computed_) computeTipPartialLikelihood();
-    if (inputs_uploaded_) return;
+    if (weights_uploaded_ && model_uploaded_) return;
     int K = family == FAMILY_MIXTURE ? ncat * nmix : ncat;
     std::vector<int32_t> blk_eigen(K);
     std::vector<double> blk_rate(K), blk_weight(K);
@@ -441,11 +453,13 @@ void PhyloTree::ensureInputs() {
         if (np) memcpy(&inv[0], &ptn_invar[shard_begin_[d]], np * 8);
         for (int64_t u = 0; u < nunobs; u++) inv[np + u] = ptn_invar[nptn + u];
         static const double zero = 0.0;
-        check(lkcuda_set_pattern_weights(e, np ? &ptn_freq[shard_begin_[d]] : &zero, &inv[0]), e, "lkcuda_set_pattern_weights");
-        check(lkcuda_set_model(e, &eval_[0], &evec_[0], &inv_evec_[0], &blk_eigen[0], &blk_rate[0], &blk_weight[0],
-                               &tip_partial_lh[0]), e, "lkcuda_set_model");
+        if (!weights_uploaded_)
+            check(lkcuda_set_pattern_weights(e, np ? &ptn_freq[shard_begin_[d]] : &zero, &inv[0]), e, "lkcuda_set_pattern_weights");
+        if (!model_uploaded_)
+            check(lkcuda_set_model(e, &eval_[0], &evec_[0], &inv_evec_[0], &blk_eigen[0], &blk_rate[0], &blk_weight[0],
+                                   &tip_partial_lh[0]), e, "lkcuda_set_model");
     }
-    inputs_uploaded_ = true;
+    weights_uploaded_ = model_uploaded_ = true;
 }
 
 /* ------------------------------------------------------------ dirty bits ------------------------------------------------------------ */

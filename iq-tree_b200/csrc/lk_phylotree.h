@@ -169,7 +169,8 @@ private:
     std::vector<lkcuda_engine*> engines_;
     std::vector<int64_t> shard_begin_;     // per engine, global pattern offsets (size engines+1)
     int64_t ptn_begin_, ptn_end_;
-    bool tip_partial_lh_computed_, inputs_uploaded_;
+    bool tip_partial_lh_computed_, weights_uploaded_, model_uploaded_;
+    bool freq_dirty_, invar_dirty_, model_dirty_;   // which host inputs changed since they were last derived / uploaded
     int nvec_;
     std::vector<lkcuda_partial_op> pending_ops_;
     std::vector<int> pending_level_;

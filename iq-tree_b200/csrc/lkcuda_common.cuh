@@ -96,6 +96,8 @@ struct lkcuda_engine {
     lkc::DevOp *h_ops[RING], *d_ops[RING]; lkc::DevChild *h_child[RING], *d_child[RING];
     int ring_cap_ops[RING], ring_cap_child[RING]; cudaEvent_t ring_ev[RING]; bool ring_used[RING]; int ring_next;
     int red_blocks;                         /* capacity of d_red in blocks */
+    size_t trav_smem_set;                   /* dynamic shared memory the traversal kernel is currently allowed */
+    int trav_maxslots;                      /* LKCUDA_TRV_MAXSLOTS: cap on shared-memory slots (-1 = what fits) */
     bool theta_ready; int theta_dad; int theta_node;
     bool model_set, states_set, weights_set;
     int num_sms;

@@ -139,7 +139,8 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
         e->h_ops[i] = e->d_ops[i] = NULL; e->h_child[i] = e->d_child[i] = NULL;
         e->ring_cap_ops[i] = e->ring_cap_child[i] = 0; e->ring_ev[i] = NULL; e->ring_used[i] = false;
     }
-    e->ring_next = 0; e->red_blocks = 0;
+    e->ring_next = 0; e->red_blocks = 0; e->trav_smem_set = 48 * 1024;
+    { const char *r = getenv("LKCUDA_TRV_MAXSLOTS"); e->trav_maxslots = r ? atoi(r) : -1; }
     e->theta_ready = false; e->theta_dad = e->theta_node = 0;
     e->model_set = e->states_set = e->weights_set = false;
     e->launches = e->bytes = 0; e->profiling = false; e->total_dev_bytes = 0;
@@ -153,7 +154,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     v.vec_stride = round_up(v.NP * v.B, 32);     /* 256-byte multiple */
     v.sc_stride = round_up(v.NP, 64);            /* 128-byte multiple */
     v.st_stride = round_up(v.NP, 128);
-    v.table_slot = round_up((long long)v.K * v.S * v.S + (long long)(v.SU + 1) * v.B, 4);
+    v.table_slot = round_up((long long)v.K * (v.S * v.S + 2) + (long long)(v.SU + 1) * v.B, 4);   /* + 2: padded matrices of the DNA traversal kernel */
 
     cudaDeviceProp prop;
     rc = cudaGetDeviceProperties(&prop, cfg->device);

@@ -8,17 +8,15 @@
  *     echild_k[x][j] = evec_k[x][j] * exp(eval_k[j] * rate_k * len_child)          (phylokernel.h:163-181)
  * followed by the scaling test on lh_max = max_{k,i} |L_dad[p][k][i]| (phylokernel.h:380-392, 462-474).
  *
- * Launch structure: the host hands over a post-order schedule already grouped into tree levels; one
- * `prep_tables_kernel` launch builds every child's transition table (and, for tip children, the
- * per-state lookup table of phylokernel.h:191-232), then ONE launch per level covers all nodes of the
- * level (gridDim.y = nodes of the level) instead of one launch per node.
- *
- * Kernels
- *   partial_s4_kernel      DNA fast path (S = 4, K a power of two <= 32): one thread per (pattern, category),
- *                          each lane moves exactly one 32-byte sector per child and per result
- *                          (LDG.E.256 / STG.E.256), lh_max via warp shuffles. HBM-bound by design.
- *   partial_generic_kernel any S, any K, any number of children (multifurcations): pattern tiles staged
- *                          in shared memory; correctness fallback for shapes without a tuned kernel.
+ * Launch structure: the host hands over a post-order schedule; one `prep_tables_kernel` launch builds
+ * every child's transition table (and, for tip children, the per-state lookup table of
+ * phylokernel.h:191-232), then
+ *   traverse_s4_kernel     DNA (S = 4, K <= 32): ONE launch executes the whole schedule, pattern tile by
+ *                          pattern tile, with the intermediate partials parked in shared memory; see the
+ *                          comment above the kernel.
+ *   partial_generic_kernel any S, any K, any number of children (multifurcations): one launch per tree
+ *                          level (gridDim.y = nodes of the level), pattern tiles staged in shared memory;
+ *                          correctness fallback for shapes without a tuned kernel.
  */
 #include "lkcuda_common.cuh"
 
@@ -48,13 +46,16 @@ int ensure_tables(lkcuda_engine *e, long long slots) {
 /* ------------------------------------------------------------------ table preparation ------------------------------------------------------------------ */
 
 /* one CTA per child slot: ech[k][x][j] and, for a tip child, tab[state][k][x] (unknown-state row = 1) */
-__global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevChild *__restrict__ children) {
+/* mpad: doubles of padding after each k's S*S matrix (0 for the generic kernel, 2 for the DNA traversal kernel's
+   conflict-free shared-memory image); the tip table follows the K padded matrices */
+__global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevChild *__restrict__ children, int mpad) {
     extern __shared__ __align__(32) double sh_ex[];            /* exp(eval*rate*len) per (k, j): B doubles */
     const int c = blockIdx.x;
     const DevChild ch = children[c];
     const int S = v.S, K = v.K, B = v.B;
     double *ech = v.tables + (long long)c * v.table_slot;
-    double *tab = ech + (long long)K * S * S;
+    const int MS = S * S + mpad;
+    double *tab = ech + (long long)K * MS;
     for (int idx = threadIdx.x; idx < B; idx += blockDim.x) {
         int k = idx / S, j = idx - k * S;
         sh_ex[idx] = exp(v.eval[v.blk_eigen[k] * S + j] * (v.blk_rate[k] * ch.len));
@@ -63,7 +64,7 @@ __global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevCh
     const int SS = S * S;
     for (int idx = threadIdx.x; idx < K * SS; idx += blockDim.x) {
         int k = idx / SS, r = idx - k * SS, j = r % S;
-        ech[idx] = v.evec[(long long)v.blk_eigen[k] * SS + r] * sh_ex[k * S + j];
+        ech[k * MS + r] = v.evec[(long long)v.blk_eigen[k] * SS + r] * sh_ex[k * S + j];
     }
     if (!LKCUDA_IS_TIP(ch.id)) return;
     __syncthreads();
@@ -73,7 +74,7 @@ __global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevCh
         double val = 1.0;
         if (st < SU) {
             int k = r / S, x = r - k * S;
-            const double *row = ech + (long long)k * SS + (long long)x * S;
+            const double *row = ech + (long long)k * MS + (long long)x * S;
             const double *tip = v.tip + ((long long)st * v.E + v.blk_eigen[k]) * S;
             val = 0.0;
             for (int j = 0; j < S; j++) val += row[j] * tip[j];
@@ -82,94 +83,326 @@ __global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevCh
     }
 }
 
-/* ------------------------------------------------------------------ DNA fast path ------------------------------------------------------------------ */
+/* ------------------------------------------------------------------ DNA: whole-traversal kernel ------------------------------------------------------------------ */
 
-#define S4_PAD 18   /* doubles per (k) matrix row group in shared memory: 16 + 2 keeps LDS.128 conflict-free across k */
+/*
+ * Every per-pattern quantity of the pruning recursion is independent of every other pattern, so the
+ * tree does not have to be walked level by level across the whole alignment: a CTA takes a TILE of
+ * patterns and executes the ENTIRE post-order schedule for it.  A thread owns the same units
+ * (pattern, category) for all nodes, therefore
+ *   - a node's result is consumed by the very thread that produced it: no inter-thread (let alone
+ *     inter-CTA) synchronisation on the data exists in the loop;
+ *   - results that a later node of the same schedule needs are parked in shared-memory SLOTS (allocated
+ *     by the host with a Sethi-Ullman ordering of the schedule, so ~log2(taxa) slots suffice): internal
+ *     children are read from shared memory, not from HBM;
+ *   - every node's partial_lh / scale_num is still written to its arena vector (the reference's buffer
+ *     semantics: other branches' derivatives read them later), as whole-sector streaming stores.
+ * HBM traffic per node drops from "read 2 children + write 1" to "write 1" (+ 1 byte per tip child).
+ *
+ * Unit mapping: unit u = ptn*K + k is 32-byte sector u of a vector.  A warp covers UPW = (32/K)*K
+ * consecutive units (all K units of a pattern in one warp, so lh_max is a shuffle reduction inside the
+ * lane group); a thread handles R units spaced by the CTA's unit count, all with the same k, so the
+ * 4x4 transition matrices it pulls into registers are used R times.
+ *
+ * Warp specialisation: TRV_CWARPS consumer warps do the arithmetic; ONE producer warp streams the
+ * per-node operands (node descriptor + the two children's transition matrix / tip lookup table, built
+ * by prep_tables_kernel) from global memory into a TRV_STAGES-deep shared-memory ring with bulk
+ * asynchronous copies (cp.async.bulk -> UBLKCP) that complete on mbarriers; consumers hand a stage
+ * back through a second mbarrier.  Nothing in the consumers' inner loop reads a table from global memory.
+ */
+#define TRV_CWARPS 11
+#define TRV_CTHREADS (TRV_CWARPS * 32)
+#define TRV_THREADS (TRV_CTHREADS + 32)
+#define TRV_STAGES 4
+#define TRV_R 4
+#define S4_MPAD 18  /* doubles per k of a staged 4x4 matrix: 16 + 2 keeps LDS.128 conflict-free across k */
+#define THR_HI 0x2FF00000   /* high word of 2^-256: |x| < 2^-256  <=>  (hi(x) & 0x7fffffff) < THR_HI */
+#define TRV_SLOT_PREV (-3)  /* child 1 is the result of the node executed immediately before: still in registers */
 
-__global__ void __launch_bounds__(256) partial_s4_kernel(DevView v, const DevOp *__restrict__ ops, const DevChild *__restrict__ children,
-                                                         int op_begin, int kshift) {
-    extern __shared__ __align__(32) double sh[];
-    const int K = 1 << kshift;
-    const DevOp op = ops[op_begin + blockIdx.y];
-    const DevChild cl = children[op.child0], cr = children[op.child0 + 1];
-    const bool tipl = LKCUDA_IS_TIP(cl.id), tipr = LKCUDA_IS_TIP(cr.id);
-    double *sEL = sh, *sER = sEL + K * S4_PAD, *sINV = sER + K * S4_PAD;
-    double *sTL = sINV + K * S4_PAD;                 /* [(SU+1)][K][4] */
-    double *sTR = sTL + (v.SU + 1) * K * 4;
+struct TravOp {
+    int32_t dst, dst_slot;      /* arena vector receiving the result; slot it is parked in (-1: not needed again in this launch or
+                                   consumed by the very next node from registers, -2: needed but no slot was free: the consumer
+                                   re-reads the arena vector) */
+    int32_t src0, slot0;        /* child 0: vector (>=0) or LKCUDA_TIP(taxon); slot holding it (-1: read the vector from global memory) */
+    int32_t src1, slot1;        /* child 1: likewise, or TRV_SLOT_PREV */
+    int32_t tab0, tab1;         /* table slots of the two children (prep_tables_kernel output) */
+};
 
-    const long long unit = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long p = unit >> kshift;
-    const int k = (int)(unit & (K - 1));
-    const bool active = p < v.NP;
+__device__ __forceinline__ d4 ld_coherent256(const double *p) { /* may have been written earlier by this very thread */
+    d4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}\n" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
 
-    /* issue the streaming loads first, stage the tables while they are in flight */
-    d4 ll = {0, 0, 0, 0}, lr = {0, 0, 0, 0};
-    int stl = 0, str = 0;
-    if (active) {
-        if (tipl) stl = tip_states(v, cl.id)[p]; else ll = ld_stream256(vec_lh(v, cl.id) + p * v.B + k * 4);
-        if (tipr) str = tip_states(v, cr.id)[p]; else lr = ld_stream256(vec_lh(v, cr.id) + p * v.B + k * 4);
-    }
-    int sc = 0;
-    if (active && k == 0) {
-        if (!tipl) sc += vec_sc(v, cl.id)[p];
-        if (!tipr) sc += vec_sc(v, cr.id)[p];
-    }
+/* bytes of one ring stage: descriptor (32) + two child blocks of cbs doubles */
+__host__ __device__ __forceinline__ size_t trv_stage_bytes(int cbs) { return 32 + (size_t)2 * cbs * 8; }
 
-    const double *gl = v.tables + (long long)op.child0 * v.table_slot;
-    const double *gr = gl + v.table_slot;
-    for (int idx = threadIdx.x; idx < K * 16; idx += blockDim.x) {
+/* t = M * L for the staged 4x4 matrix M (row-major, 8 double2) */
+#define TRV_MATVEC(dst, m, L)                                                   \
+    dst[0] = m[0].x * L.x + m[0].y * L.y + m[1].x * L.z + m[1].y * L.w;         \
+    dst[1] = m[2].x * L.x + m[2].y * L.y + m[3].x * L.z + m[3].y * L.w;         \
+    dst[2] = m[4].x * L.x + m[4].y * L.y + m[5].x * L.z + m[5].y * L.w;         \
+    dst[3] = m[6].x * L.x + m[6].y * L.y + m[7].x * L.z + m[7].y * L.w;
+
+__global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, const TravOp *__restrict__ ops, int nops, int upw, int nslots,
+                                                                     int cbs, long long total_units, long long ntiles) {
+    constexpr int R = TRV_R, CT = TRV_CTHREADS;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int K = v.K, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int stage_bytes = (int)trv_stage_bytes(cbs);
+    unsigned char *ring = smem_raw;                                                          /* [TRV_STAGES][stage_bytes] */
+    double2 *sl = reinterpret_cast<double2 *>(ring + TRV_STAGES * stage_bytes);              /* [nslots][R][2][CT] */
+    int *ssc = reinterpret_cast<int *>(sl + nslots * R * 2 * CT);                            /* [nslots][R][CT] */
+    double *sINV = reinterpret_cast<double *>(ssc + nslots * R * CT);                        /* [K][S4_MPAD] */
+    uint64_t *full = reinterpret_cast<uint64_t *>(sINV + K * S4_MPAD), *empty = full + TRV_STAGES;
+    for (int idx = tid; idx < K * 16; idx += TRV_THREADS) {
         int kk = idx >> 4, r = idx & 15;
-        if (!tipl) sEL[kk * S4_PAD + r] = gl[idx];
-        if (!tipr) sER[kk * S4_PAD + r] = gr[idx];
-        sINV[kk * S4_PAD + r] = v.inv_evec[v.blk_eigen[kk] * 16 + r];
+        sINV[kk * S4_MPAD + r] = v.inv_evec[v.blk_eigen[kk] * 16 + r];
     }
-    const int ntab = (v.SU + 1) * K * 4;
-    if (tipl) for (int idx = threadIdx.x; idx < ntab; idx += blockDim.x) sTL[idx] = gl[K * 16 + idx];
-    if (tipr) for (int idx = threadIdx.x; idx < ntab; idx += blockDim.x) sTR[idx] = gr[K * 16 + idx];
+    if (tid == 0) {
+        for (int s = 0; s < TRV_STAGES; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], TRV_CWARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncthreads();
 
-    double vl[4], vr[4];
-    if (tipl) {
-        const double *t = sTL + (stl * K + k) * 4;
-        vl[0] = t[0]; vl[1] = t[1]; vl[2] = t[2]; vl[3] = t[3];
-    } else {
-        const double *m = sEL + k * S4_PAD;
-#pragma unroll
-        for (int x = 0; x < 4; x++) vl[x] = m[x * 4 + 0] * ll.x + m[x * 4 + 1] * ll.y + m[x * 4 + 2] * ll.z + m[x * 4 + 3] * ll.w;
-    }
-    if (tipr) {
-        const double *t = sTR + (str * K + k) * 4;
-        vr[0] = t[0]; vr[1] = t[1]; vr[2] = t[2]; vr[3] = t[3];
-    } else {
-        const double *m = sER + k * S4_PAD;
-#pragma unroll
-        for (int x = 0; x < 4; x++) vr[x] = m[x * 4 + 0] * lr.x + m[x * 4 + 1] * lr.y + m[x * 4 + 2] * lr.z + m[x * 4 + 3] * lr.w;
-    }
-#pragma unroll
-    for (int x = 0; x < 4; x++) vl[x] *= vr[x];
-    const double *inv = sINV + k * S4_PAD;
-    double o[4];
-#pragma unroll
-    for (int i = 0; i < 4; i++) o[i] = inv[i * 4 + 0] * vl[0] + inv[i * 4 + 1] * vl[1] + inv[i * 4 + 2] * vl[2] + inv[i * 4 + 3] * vl[3];
-
-    if (!(tipl && tipr)) {   /* tip-tip never scales (phylokernel.h:246-281) */
-        double lmax = fmax(fmax(fabs(o[0]), fabs(o[1])), fmax(fabs(o[2]), fabs(o[3])));
-        for (int off = 1; off < K; off <<= 1) lmax = fmax(lmax, __shfl_xor_sync(0xffffffffu, lmax, off));
-        if (active && lmax < LK_THR) {
-            if ((v.flags & LKCUDA_FLAG_ZERO_GUARD) && lmax == 0.0) {
-                const double *t = v.tip + ((long long)v.SU * v.E + v.blk_eigen[k]) * 4;
-                o[0] = t[0]; o[1] = t[1]; o[2] = t[2]; o[3] = t[3];
-                sc += 4;
-            } else if ((v.flags & LKCUDA_FLAG_SCALE_IGNORES_INVAR) || v.invar[p] == 0.0) {
-                o[0] *= LK_THR_INV; o[1] *= LK_THR_INV; o[2] *= LK_THR_INV; o[3] *= LK_THR_INV;
-                sc += 1;
+    if (warp == TRV_CWARPS) {
+        /* ------------------------------ producer: one lane feeds the ring ------------------------------ */
+        if (lane == 0) {
+            uint32_t c = 0;
+            const uint32_t mat_bytes = (uint32_t)K * S4_MPAD * 8, tab_bytes = (uint32_t)(v.SU + 1) * K * 32;
+            for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                for (int i = 0; i < nops; i++, c++) {
+                    const uint32_t s = c % TRV_STAGES, ph = (c / TRV_STAGES) & 1;
+                    const TravOp op = ops[i];
+                    unsigned char *st = ring + s * stage_bytes;
+                    const bool t0 = LKCUDA_IS_TIP(op.src0), t1 = LKCUDA_IS_TIP(op.src1);
+                    const uint32_t b0 = t0 ? tab_bytes : mat_bytes, b1 = t1 ? tab_bytes : mat_bytes;
+                    const double *g0 = v.tables + (long long)op.tab0 * v.table_slot + (t0 ? K * S4_MPAD : 0);
+                    const double *g1 = v.tables + (long long)op.tab1 * v.table_slot + (t1 ? K * S4_MPAD : 0);
+                    mbar_wait(&empty[s], ph ^ 1);
+                    mbar_expect_tx(&full[s], 32 + b0 + b1);
+                    bulk_g2s(st, ops + i, 32, &full[s]);
+                    bulk_g2s(st + 32, g0, b0, &full[s]);
+                    bulk_g2s(st + 32 + cbs * 8, g1, b1, &full[s]);
+                }
             }
         }
+        return;
     }
-    if (active) {
-        d4 r = {o[0], o[1], o[2], o[3]};
-        st_stream256(vec_lh_w(v, op.dst) + p * v.B + k * 4, r);
-        if (k == 0) vec_sc_w(v, op.dst)[p] = (int16_t)sc;
+
+    /* ------------------------------ consumers ------------------------------ */
+    const bool lane_on = lane < upw;
+    const int k = lane_on ? lane % K : 0;
+    const int gbase = lane_on ? lane - k : lane;
+    const unsigned gmask = K >= 32 ? 0xffffffffu : ((1u << K) - 1u);
+    const int cta_units = TRV_CWARPS * upw;
+    const double2 *inv = reinterpret_cast<const double2 *>(sINV + k * S4_MPAD);
+    const bool zero_guard = (v.flags & LKCUDA_FLAG_ZERO_GUARD) != 0, ignore_invar = (v.flags & LKCUDA_FLAG_SCALE_IGNORES_INVAR) != 0;
+    double2 *const sl_t = sl + tid;
+    int *const ssc_t = ssc + tid;
+    const int B = v.B;
+    uint32_t c = 0;     /* ring position of the node being computed, continues across tiles */
+
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        long long p[R], off[R];     /* pattern, element offset of the unit inside a vector */
+        bool valid[R];
+        const long long u0 = tile * ((long long)cta_units * R) + warp * upw + lane;
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            long long u = u0 + (long long)r * cta_units;
+            valid[r] = lane_on && u < total_units;
+            p[r] = valid[r] ? u / K : v.NP - 1;      /* out-of-range units shadow the last pattern; only their stores are masked */
+            off[r] = p[r] * B + k * 4;
+        }
+        /* software pipeline: node i+1's descriptor is awaited, and its tip states requested, before node i is computed */
+        mbar_wait(&full[c % TRV_STAGES], (c / TRV_STAGES) & 1);
+        TravOp nxt = *reinterpret_cast<const TravOp *>(ring + (c % TRV_STAGES) * stage_bytes);
+        int st0n[R], st1n[R];
+        {
+            const uint8_t *s0 = tip_states(v, LKCUDA_IS_TIP(nxt.src0) ? nxt.src0 : -1), *s1 = tip_states(v, LKCUDA_IS_TIP(nxt.src1) ? nxt.src1 : -1);
+#pragma unroll
+            for (int r = 0; r < R; r++) { st0n[r] = s0[p[r]]; st1n[r] = s1[p[r]]; }
+        }
+        d4 pv[R];       /* result of the previous node (TRV_SLOT_PREV) */
+        int pvsc[R];
+#pragma unroll
+        for (int r = 0; r < R; r++) { pv[r].x = pv[r].y = pv[r].z = pv[r].w = 0.0; pvsc[r] = 0; }
+
+        for (int i = 0; i < nops; i++, c++) {
+            const TravOp op = nxt;
+            const uint32_t s = c % TRV_STAGES;
+            int st0[R], st1[R];
+#pragma unroll
+            for (int r = 0; r < R; r++) { st0[r] = st0n[r]; st1[r] = st1n[r]; }
+            if (i + 1 < nops) {
+                const uint32_t c1 = c + 1;
+                mbar_wait(&full[c1 % TRV_STAGES], (c1 / TRV_STAGES) & 1);
+                nxt = *reinterpret_cast<const TravOp *>(ring + (c1 % TRV_STAGES) * stage_bytes);
+                /* a non-tip child prefetches taxon 0's row: a harmless, unused byte */
+                const uint8_t *s0 = tip_states(v, LKCUDA_IS_TIP(nxt.src0) ? nxt.src0 : -1), *s1 = tip_states(v, LKCUDA_IS_TIP(nxt.src1) ? nxt.src1 : -1);
+#pragma unroll
+                for (int r = 0; r < R; r++) { st0n[r] = s0[p[r]]; st1n[r] = s1[p[r]]; }
+            }
+            const bool tip0 = LKCUDA_IS_TIP(op.src0), tip1 = LKCUDA_IS_TIP(op.src1);
+            const double *blk0 = reinterpret_cast<const double *>(ring + s * stage_bytes + 32), *blk1 = blk0 + cbs;
+            double t[R][4];
+            int sc[R];
+            /* ---- child 0: tip | slot | arena ---- */
+            if (tip0) {
+                const double *tab = blk0 + k * 4;
+#pragma unroll
+                for (int r = 0; r < R; r++) {
+                    const double2 *row = reinterpret_cast<const double2 *>(tab + st0[r] * (K * 4));
+                    const double2 a = row[0], b = row[1];
+                    t[r][0] = a.x; t[r][1] = a.y; t[r][2] = b.x; t[r][3] = b.y; sc[r] = 0;
+                }
+            } else {
+                const double2 *mp = reinterpret_cast<const double2 *>(blk0 + k * S4_MPAD);
+                const double2 m[8] = {mp[0], mp[1], mp[2], mp[3], mp[4], mp[5], mp[6], mp[7]};
+                if (op.slot0 >= 0) {
+                    const double2 *ps = sl_t + op.slot0 * (R * 2 * CT);
+                    const int *pc = ssc_t + op.slot0 * (R * CT);
+#pragma unroll
+                    for (int r = 0; r < R; r++) {
+                        const double2 a = ps[(r * 2) * CT], b = ps[(r * 2 + 1) * CT];
+                        d4 L; L.x = a.x; L.y = a.y; L.z = b.x; L.w = b.y;
+                        sc[r] = pc[r * CT];
+                        TRV_MATVEC(t[r], m, L)
+                    }
+                } else {
+                    const double *g = vec_lh(v, op.src0);
+                    const int16_t *gs = vec_sc(v, op.src0);
+#pragma unroll
+                    for (int r = 0; r < R; r++) {
+                        const d4 L = ld_coherent256(g + off[r]);
+                        sc[r] = gs[p[r]];
+                        TRV_MATVEC(t[r], m, L)
+                    }
+                }
+            }
+            /* ---- child 1: tip | previous node (registers) | slot | arena ---- */
+            if (tip1) {
+                const double *tab = blk1 + k * 4;
+#pragma unroll
+                for (int r = 0; r < R; r++) {
+                    const double2 *row = reinterpret_cast<const double2 *>(tab + st1[r] * (K * 4));
+                    const double2 a = row[0], b = row[1];
+                    t[r][0] *= a.x; t[r][1] *= a.y; t[r][2] *= b.x; t[r][3] *= b.y;
+                }
+            } else {
+                const double2 *mp = reinterpret_cast<const double2 *>(blk1 + k * S4_MPAD);
+                const double2 m[8] = {mp[0], mp[1], mp[2], mp[3], mp[4], mp[5], mp[6], mp[7]};
+                double u[4];
+                if (op.slot1 == TRV_SLOT_PREV) {
+#pragma unroll
+                    for (int r = 0; r < R; r++) {
+                        sc[r] += pvsc[r];
+                        TRV_MATVEC(u, m, pv[r])
+                        t[r][0] *= u[0]; t[r][1] *= u[1]; t[r][2] *= u[2]; t[r][3] *= u[3];
+                    }
+                } else if (op.slot1 >= 0) {
+                    const double2 *ps = sl_t + op.slot1 * (R * 2 * CT);
+                    const int *pc = ssc_t + op.slot1 * (R * CT);
+#pragma unroll
+                    for (int r = 0; r < R; r++) {
+                        const double2 a = ps[(r * 2) * CT], b = ps[(r * 2 + 1) * CT];
+                        d4 L; L.x = a.x; L.y = a.y; L.z = b.x; L.w = b.y;
+                        sc[r] += pc[r * CT];
+                        TRV_MATVEC(u, m, L)
+                        t[r][0] *= u[0]; t[r][1] *= u[1]; t[r][2] *= u[2]; t[r][3] *= u[3];
+                    }
+                } else {
+                    const double *g = vec_lh(v, op.src1);
+                    const int16_t *gs = vec_sc(v, op.src1);
+#pragma unroll
+                    for (int r = 0; r < R; r++) {
+                        const d4 L = ld_coherent256(g + off[r]);
+                        sc[r] += gs[p[r]];
+                        TRV_MATVEC(u, m, L)
+                        t[r][0] *= u[0]; t[r][1] *= u[1]; t[r][2] *= u[2]; t[r][3] *= u[3];
+                    }
+                }
+            }
+            /* the stage's tables are in registers now: hand the stage back to the producer */
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);
+            /* ---- back to state space, scaling test, stores ---- */
+            const double2 iv[8] = {inv[0], inv[1], inv[2], inv[3], inv[4], inv[5], inv[6], inv[7]};
+            const bool may_scale = !(tip0 && tip1);   /* tip-tip never scales (phylokernel.h:246-281) */
+            double *dst_lh = vec_lh_w(v, op.dst);
+            int16_t *dst_sc = vec_sc_w(v, op.dst);
+            double2 *pd = sl_t + op.dst_slot * (R * 2 * CT);
+            int *pdc = ssc_t + op.dst_slot * (R * CT);
+#pragma unroll
+            for (int r = 0; r < R; r++) {
+                d4 o;
+                {
+                    const d4 T = {t[r][0], t[r][1], t[r][2], t[r][3]};
+                    double w[4];
+                    TRV_MATVEC(w, iv, T)
+                    o.x = w[0]; o.y = w[1]; o.z = w[2]; o.w = w[3];
+                }
+                if (may_scale) {
+                    /* lh_max < 2^-256 decided on the exponent words (integer pipe), agreed inside the pattern's lane group by a ballot */
+                    const int h0 = __double2hiint(o.x) & 0x7fffffff, h1 = __double2hiint(o.y) & 0x7fffffff,
+                              h2 = __double2hiint(o.z) & 0x7fffffff, h3 = __double2hiint(o.w) & 0x7fffffff;
+                    const unsigned small = __ballot_sync(0xffffffffu, max(max(h0, h1), max(h2, h3)) < THR_HI);
+                    if (((small >> gbase) & gmask) == gmask) {
+                        bool refill = false;
+                        if (zero_guard) {
+                            const bool nz = (h0 | h1 | h2 | h3 | __double2loint(o.x) | __double2loint(o.y) | __double2loint(o.z) | __double2loint(o.w)) != 0;
+                            const unsigned anynz = __ballot_sync(__activemask(), nz);
+                            refill = ((anynz >> gbase) & gmask) == 0;
+                        }
+                        if (refill) {
+                            const double *tu = v.tip + ((long long)v.SU * v.E + v.blk_eigen[k]) * 4;
+                            o.x = tu[0]; o.y = tu[1]; o.z = tu[2]; o.w = tu[3];
+                            sc[r] += 4;
+                        } else if (ignore_invar || v.invar[p[r]] == 0.0) {
+                            o.x *= LK_THR_INV; o.y *= LK_THR_INV; o.z *= LK_THR_INV; o.w *= LK_THR_INV;
+                            sc[r] += 1;
+                        }
+                    }
+                }
+                if (valid[r]) {
+                    st_stream256(dst_lh + off[r], o);
+                    if (k == 0) dst_sc[p[r]] = (int16_t)sc[r];
+                }
+                if (op.dst_slot >= 0) {   /* parked for a later node of this launch */
+                    pd[(r * 2) * CT] = make_double2(o.x, o.y);
+                    pd[(r * 2 + 1) * CT] = make_double2(o.z, o.w);
+                    pdc[r * CT] = sc[r];
+                }
+                pv[r] = o; pvsc[r] = sc[r];
+            }
+            /* spilled result: its consumer re-reads scale_num, which lane k == 0 wrote for the whole lane group */
+            if (op.dst_slot == -2) { __threadfence_block(); __syncwarp(); }
+        }
     }
 }
 
@@ -291,12 +524,124 @@ static size_t generic_smem(const DevView &v) {
     return ((size_t)2 * v.S * v.S + (size_t)2 * GEN_TP * (v.S + 1)) * 8 + GEN_TP * 8 + GEN_TP * 4;
 }
 
-static bool use_s4(const DevView &v, int *kshift) {
-    if (v.S != 4 || v.K > 32 || (v.K & (v.K - 1))) return false;
-    int s = 0;
-    while ((1 << s) < v.K) s++;
-    *kshift = s;
-    return true;
+static_assert(sizeof(TravOp) == 2 * sizeof(DevOp), "the op ring is sized in TravOp units");
+
+static bool use_traverse(const DevView &v) { return v.S == 4 && v.K <= 32; }
+
+/*
+ * Order a batch of nodes for the whole-traversal kernel and decide where each node finds its children:
+ *   - the child executed immediately before its parent stays in REGISTERS (TRV_SLOT_PREV) - in a
+ *     post-order schedule that is one child of every internal-internal node and the only internal child of
+ *     every tip-internal node;
+ *   - the other internal child of an internal-internal node is parked in a shared-memory SLOT.
+ *     Sethi-Ullman: evaluating the child that needs more slots first, a node needs max(a, b + 1) slots
+ *     (a >= b the children's needs), so a tree with n leaves never needs more than ~log2(n) - 1;
+ *   - when the slots run out the result is not parked (dst_slot = -2) and its consumer reads it back from
+ *     its arena vector, like a child that was computed by an earlier launch.
+ * Multiplication commutes exactly in IEEE arithmetic, so the two children may be swapped freely.
+ */
+struct TravNode { int op; int32_t src0, slot0, src1, slot1, dst_slot; double len0, len1; };
+struct TravSchedule { std::vector<TravNode> nodes; int nslots; };
+
+static int schedule_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops, int maxslots, TravSchedule &sch) {
+    std::vector<int> producer(e->cfg.nvec, -1);
+    for (int i = 0; i < nops; i++) {
+        if (producer[ops[i].dst] >= 0) return fail(e, LKCUDA_ERR_ARG, "partial ops %d and %d write the same vector", producer[ops[i].dst], i);
+        producer[ops[i].dst] = i;
+    }
+    std::vector<int> kid0(nops), kid1(nops), nconsumer(nops, 0), need(nops, 0), state(nops, 0), last_kid(nops, 0), pos(nops, -1);
+    for (int i = 0; i < nops; i++) {
+        kid0[i] = ops[i].left >= 0 ? producer[ops[i].left] : -1;
+        kid1[i] = ops[i].right >= 0 ? producer[ops[i].right] : -1;
+        if (kid0[i] >= 0) nconsumer[kid0[i]]++;
+        if (kid1[i] >= 0) nconsumer[kid1[i]]++;
+    }
+    /* pass 1: slot need of every node (iterative post-order; state 0 = new, 1 = open, 2 = done) */
+    std::vector<int> stack;
+    for (int root = 0; root < nops; root++) {
+        if (state[root]) continue;
+        stack.push_back(root);
+        while (!stack.empty()) {
+            int i = stack.back();
+            if (state[i] == 0) {
+                state[i] = 1;
+                if (kid0[i] >= 0) { if (state[kid0[i]] == 1) return fail(e, LKCUDA_ERR_ARG, "partial ops form a cycle"); if (!state[kid0[i]]) stack.push_back(kid0[i]); }
+                if (kid1[i] >= 0) { if (state[kid1[i]] == 1) return fail(e, LKCUDA_ERR_ARG, "partial ops form a cycle"); if (!state[kid1[i]]) stack.push_back(kid1[i]); }
+            } else {
+                stack.pop_back();
+                if (state[i] == 2) continue;
+                state[i] = 2;
+                if (kid0[i] >= 0 && kid1[i] >= 0) {
+                    int a = need[kid0[i]], b = need[kid1[i]];
+                    int hi = a > b ? a : b, lo = a > b ? b : a;
+                    need[i] = hi > lo + 1 ? hi : lo + 1;
+                } else need[i] = kid0[i] >= 0 ? need[kid0[i]] : (kid1[i] >= 0 ? need[kid1[i]] : 0);
+            }
+        }
+    }
+    /* pass 2: emit, needier child first; slots from a free list */
+    sch.nodes.clear(); sch.nodes.reserve(nops);
+    std::vector<int> free_slots, slot_of(nops, -1);
+    for (int sidx = maxslots - 1; sidx >= 0; sidx--) free_slots.push_back(sidx);
+    int used = 0;
+    std::fill(state.begin(), state.end(), 0);
+    for (int root = 0; root < nops; root++) {
+        if (nconsumer[root] || state[root]) continue;       /* start from the nodes nobody in the batch consumes */
+        stack.push_back(root);
+        while (!stack.empty()) {
+            int i = stack.back();
+            if (state[i] == 0) {
+                state[i] = 1;
+                int first = kid0[i], second = kid1[i];
+                if (first >= 0 && second >= 0 && need[second] > need[first]) { int t = first; first = second; second = t; }
+                if (second < 0) { second = first; first = -1; }
+                if (second >= 0 && first == second) first = -1;      /* both children are the same vector */
+                /* pushed in reverse: `first` is expanded (and finished) before `second`, which ends right before i */
+                if (second >= 0 && !state[second]) { stack.push_back(second); last_kid[second] = nconsumer[second] == 1; }
+                if (first >= 0 && !state[first]) stack.push_back(first);
+            } else {
+                stack.pop_back();
+                if (state[i] == 2) continue;
+                state[i] = 2;
+                const int j = (int)sch.nodes.size();
+                pos[i] = j;
+                TravNode n;
+                n.op = i; n.dst_slot = -1;
+                int k0 = kid0[i], k1 = kid1[i];
+                n.src0 = ops[i].left; n.len0 = ops[i].len_left; n.src1 = ops[i].right; n.len1 = ops[i].len_right;
+                /* the child executed right before this node goes to position 1 and is taken from registers */
+                if (k0 >= 0 && k0 != k1 && pos[k0] == j - 1 && last_kid[k0] && !(k1 >= 0 && pos[k1] == j - 1)) {
+                    std::swap(n.src0, n.src1); std::swap(n.len0, n.len1); std::swap(k0, k1);
+                }
+                n.slot0 = n.slot1 = -1;
+                if (k0 >= 0) { n.slot0 = slot_of[k0]; }
+                if (k1 >= 0) {
+                    if (pos[k1] == j - 1 && last_kid[k1] && k1 != k0) n.slot1 = TRV_SLOT_PREV;
+                    else n.slot1 = slot_of[k1];
+                }
+                if (k0 >= 0 && slot_of[k0] >= 0 && --nconsumer[k0] == 0) { free_slots.push_back(slot_of[k0]); slot_of[k0] = -1; }
+                else if (k0 >= 0 && slot_of[k0] < 0) --nconsumer[k0];
+                if (k1 >= 0 && k1 != k0) {
+                    if (slot_of[k1] >= 0 && --nconsumer[k1] == 0) { free_slots.push_back(slot_of[k1]); slot_of[k1] = -1; }
+                    else if (slot_of[k1] < 0) --nconsumer[k1];
+                } else if (k1 >= 0 && k1 == k0) {
+                    if (slot_of[k1] >= 0 && --nconsumer[k1] == 0) { free_slots.push_back(slot_of[k1]); slot_of[k1] = -1; }
+                    else if (slot_of[k1] < 0) --nconsumer[k1];
+                }
+                if (nconsumer[i] > 0 && !last_kid[i]) {
+                    if (!free_slots.empty()) {
+                        slot_of[i] = free_slots.back(); free_slots.pop_back();
+                        n.dst_slot = slot_of[i];
+                        if (slot_of[i] + 1 > used) used = slot_of[i] + 1;
+                    } else n.dst_slot = -2;     /* spilled: the consumer reads the arena vector */
+                }
+                sch.nodes.push_back(n);
+            }
+        }
+    }
+    if ((int)sch.nodes.size() != nops) return fail(e, LKCUDA_ERR_ARG, "partial ops form a cycle");
+    sch.nslots = used;
+    return LKCUDA_OK;
 }
 
 static int ring_acquire(lkcuda_engine *e, int nops, int nchild, int *slot_out) {
@@ -308,8 +653,8 @@ static int ring_acquire(lkcuda_engine *e, int nops, int nchild, int *slot_out) {
         if (e->h_ops[s]) cudaFreeHost(e->h_ops[s]);
         cudaFree(e->d_ops[s]);
         int cap = nops < 256 ? 256 : nops * 2;
-        LK_CUDA(e, cudaMallocHost((void **)&e->h_ops[s], sizeof(DevOp) * cap));
-        LK_CUDA(e, cudaMalloc((void **)&e->d_ops[s], sizeof(DevOp) * cap));
+        LK_CUDA(e, cudaMallocHost((void **)&e->h_ops[s], sizeof(TravOp) * cap));
+        LK_CUDA(e, cudaMalloc((void **)&e->d_ops[s], sizeof(TravOp) * cap));
         e->ring_cap_ops[s] = cap;
     }
     if (nchild > e->ring_cap_child[s]) {
@@ -341,14 +686,12 @@ static int launch_ops(lkcuda_engine *e, int slot, int nops, int nchild_total, co
     if (v.NP == 0) return LKCUDA_OK;
 
     launch_begin(e, KIND_PREP);
-    prep_tables_kernel<<<nchild_total, 256, (size_t)v.B * 8, e->stream>>>(e->v, e->d_child[slot]);
+    prep_tables_kernel<<<nchild_total, 256, (size_t)v.B * 8, e->stream>>>(e->v, e->d_child[slot], 0);
     rc = launch_end(e, KIND_PREP, 0, "prep_tables_kernel");
     if (rc) return rc;
 
-    int kshift = 0;
-    const bool s4 = use_s4(v, &kshift);
     size_t gsm = generic_smem(v);
-    if (!s4 && gsm > 48 * 1024) {
+    if (gsm > 48 * 1024) {
         if (gsm > 227 * 1024) return fail(e, LKCUDA_ERR_ARG, "state space too large for the generic kernel (%d states)", v.S);
         LK_CUDA(e, cudaFuncSetAttribute(partial_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm));
     }
@@ -357,18 +700,72 @@ static int launch_ops(lkcuda_engine *e, int slot, int nops, int nchild_total, co
         if (n <= 0) continue;
         if (n > 65535) return fail(e, LKCUDA_ERR_ARG, "more than 65535 nodes in one level");
         launch_begin(e, KIND_PARTIAL);
-        if (s4) {
-            size_t sm = ((size_t)3 * v.K * S4_PAD + (size_t)2 * (v.SU + 1) * v.K * 4) * 8;
-            dim3 grid((unsigned)((v.NP * v.K + 255) / 256), (unsigned)n);
-            partial_s4_kernel<<<grid, 256, sm, e->stream>>>(e->v, e->d_ops[slot], e->d_child[slot], b, kshift);
-        } else {
-            dim3 grid((unsigned)((v.NP + GEN_TP - 1) / GEN_TP), (unsigned)n);
-            partial_generic_kernel<<<grid, GEN_THREADS, gsm, e->stream>>>(e->v, e->d_ops[slot], e->d_child[slot], b);
-        }
+        dim3 grid((unsigned)((v.NP + GEN_TP - 1) / GEN_TP), (unsigned)n);
+        partial_generic_kernel<<<grid, GEN_THREADS, gsm, e->stream>>>(e->v, e->d_ops[slot], e->d_child[slot], b);
         rc = launch_end(e, KIND_PARTIAL, bytes_per_level[l], "partial kernel");
         if (rc) return rc;
     }
     return LKCUDA_OK;
+}
+
+/* the whole batch in ONE launch of the whole-traversal kernel (+ one table-preparation launch) */
+static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops) {
+    const DevView &v = e->v;
+    /* child block of a ring stage: a padded matrix set or a tip lookup table, whichever is larger */
+    const int cbs_mat = v.K * S4_MPAD, cbs_tab = (v.SU + 1) * v.K * 4, cbs = cbs_mat > cbs_tab ? cbs_mat : cbs_tab;
+    const size_t slot_bytes = (size_t)TRV_R * TRV_CTHREADS * (32 + 4);
+    const size_t fixed = TRV_STAGES * trv_stage_bytes(cbs) + (size_t)v.K * S4_MPAD * 8 + 2 * TRV_STAGES * 8;
+    if (fixed + 128 > 227 * 1024) return fail(e, LKCUDA_ERR_ARG, "too many categories for the DNA traversal kernel");
+    int maxslots = (int)((227 * 1024 - 128 - fixed) / slot_bytes);
+    if (e->trav_maxslots >= 0 && e->trav_maxslots < maxslots) maxslots = e->trav_maxslots;   /* test knob: forces the spill path */
+    TravSchedule sch;
+    int rc = schedule_traverse(e, ops, nops, maxslots, sch);
+    if (rc) return rc;
+    int slot;
+    rc = ring_acquire(e, nops, 2 * nops, &slot);
+    if (rc) return rc;
+    TravOp *h = reinterpret_cast<TravOp *>(e->h_ops[slot]);
+    uint64_t bytes = 0;
+    for (int j = 0; j < nops; j++) {
+        const TravNode &n = sch.nodes[j];
+        TravOp &t = h[j];
+        t.dst = ops[n.op].dst; t.dst_slot = n.dst_slot;
+        t.src0 = n.src0; t.slot0 = n.slot0;
+        t.src1 = n.src1; t.slot1 = n.slot1;
+        t.tab0 = 2 * j; t.tab1 = 2 * j + 1;
+        DevChild &a = e->h_child[slot][2 * j], &b = e->h_child[slot][2 * j + 1];
+        a.id = n.src0; a.pad = 0; a.len = n.len0;
+        b.id = n.src1; b.pad = 0; b.len = n.len1;
+        int ntip = (LKCUDA_IS_TIP(a.id) ? 1 : 0) + (LKCUDA_IS_TIP(b.id) ? 1 : 0);
+        bytes += op_bytes(v, ntip, 2 - ntip);
+    }
+    rc = ensure_tables(e, 2 * nops);
+    if (rc) return rc;
+    TravOp *d = reinterpret_cast<TravOp *>(e->d_ops[slot]);
+    LK_CUDA(e, cudaMemcpyAsync(d, h, sizeof(TravOp) * nops, cudaMemcpyHostToDevice, e->stream));
+    LK_CUDA(e, cudaMemcpyAsync(e->d_child[slot], e->h_child[slot], sizeof(DevChild) * 2 * nops, cudaMemcpyHostToDevice, e->stream));
+    LK_CUDA(e, cudaEventRecord(e->ring_ev[slot], e->stream));
+    e->ring_used[slot] = true;
+    if (v.NP == 0) return LKCUDA_OK;
+
+    launch_begin(e, KIND_PREP);
+    prep_tables_kernel<<<2 * nops, 256, (size_t)v.B * 8, e->stream>>>(e->v, e->d_child[slot], S4_MPAD - 16);
+    rc = launch_end(e, KIND_PREP, 0, "prep_tables_kernel");
+    if (rc) return rc;
+
+    const int upw = (32 / v.K) * v.K;
+    const long long total_units = v.NP * v.K, tile_units = (long long)TRV_CWARPS * upw * TRV_R;
+    const long long ntiles = (total_units + tile_units - 1) / tile_units;
+    const size_t sm = (size_t)sch.nslots * slot_bytes + fixed + 128;
+    if (sm > e->trav_smem_set) {
+        LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        e->trav_smem_set = sm;
+    }
+    long long grid = e->num_sms;      /* one persistent CTA per SM (512 threads, shared memory bound) */
+    if (grid > ntiles) grid = ntiles;
+    launch_begin(e, KIND_PARTIAL);
+    traverse_s4_kernel<<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, total_units, ntiles);
+    return launch_end(e, KIND_PARTIAL, bytes, "traverse_s4_kernel");
 }
 
 extern "C" {
@@ -395,6 +792,10 @@ int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t
         if (!LKCUDA_IS_TIP(op.left) && LKCUDA_IS_TIP(op.right))
             return fail(e, LKCUDA_ERR_ARG, "partial op %d: a leaf child must be 'left' (phylokernel.h:116-121)", i);
         if (op.dst == op.left || op.dst == op.right) return fail(e, LKCUDA_ERR_ARG, "partial op %d: destination aliases a child", i);
+    }
+    if (use_traverse(e->v)) {
+        e->theta_ready = false;
+        return launch_traverse(e, ops, nops);
     }
     int slot;
     int rc = ring_acquire(e, nops, 2 * nops, &slot);
@@ -443,7 +844,7 @@ int lkcuda_partial_multi(lkcuda_engine *e, int32_t dst, int32_t nchild, const in
     e->ring_used[slot] = true;
     if (v.NP == 0) return LKCUDA_OK;
     launch_begin(e, KIND_PREP);
-    prep_tables_kernel<<<nchild, 256, (size_t)v.B * 8, e->stream>>>(e->v, e->d_child[slot]);
+    prep_tables_kernel<<<nchild, 256, (size_t)v.B * 8, e->stream>>>(e->v, e->d_child[slot], 0);
     rc = launch_end(e, KIND_PREP, 0, "prep_tables_kernel");
     if (rc) return rc;
     size_t gsm = generic_smem(v);

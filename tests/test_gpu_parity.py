@@ -98,3 +98,17 @@ def test_two_shards_one_device(cuda_lib):
     gu.check_derivatives(t, g)
     gu.check_optimize(t, g, full=False)
     t.close()
+
+
+@pytest.mark.parametrize("maxslots", [0, 1, 2])
+@pytest.mark.parametrize("case", ["dna_example_gtr_g4", "dna_deep_scaling", "dna_example_hky_r3", "dna_example_jc"])
+def test_traversal_kernel_slot_spill(case, maxslots, cuda_lib, monkeypatch):
+    """whole-traversal kernel with the shared-memory slots capped: spilled results are re-read from the arena"""
+    monkeypatch.setenv("LKCUDA_TRV_MAXSLOTS", str(maxslots))
+    g = gu.Golden(case)
+    t = gu.build_tree(g, cuda_lib)
+    t.initializeAllPartialLh()
+    gu.check_likelihood(t, g)
+    gu.check_partials(t, g)
+    gu.check_derivatives(t, g)
+    t.close()
