@@ -154,7 +154,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     v.vec_stride = round_up(v.NP * v.B, 32);     /* 256-byte multiple */
     v.sc_stride = round_up(v.NP, 64);            /* 128-byte multiple */
     v.st_stride = round_up(v.NP, 128);
-    v.table_slot = round_up((long long)v.K * (v.S * v.S + 2) + (long long)(v.SU + 1) * v.B, 4);   /* + 2: padded matrices of the DNA traversal kernel */
+    v.table_slot = round_up((long long)v.K * (v.S * v.S + 2) + (long long)(v.SU + 1) * v.B + v.SU + 4, 4);   /* + 2: padded matrices of the DNA traversal kernel */
 
     cudaDeviceProp prop;
     rc = cudaGetDeviceProperties(&prop, cfg->device);
@@ -165,7 +165,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
 #define ALLOC(ptr, count) do { if (ok) { rc = dev_alloc(e, &(ptr), (size_t)(count)); if (rc != cudaSuccess) ok = false; } } while (0)
     if (ok) { rc = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking); ok = rc == cudaSuccess; e->own_stream = ok; }
     size_t nvec = (size_t)(cfg->nvec ? cfg->nvec : 1);
-    ALLOC(e->d_states, (size_t)cfg->ntaxa * v.st_stride);
+    ALLOC(e->d_states, (size_t)cfg->ntaxa * v.st_stride + 4096);   /* + slack: the traversal kernel bulk-copies whole tiles of a row */
     ALLOC(e->d_freq, v.P + 4); ALLOC(e->d_invar, v.NP + 4);
     ALLOC(e->d_eval, v.E * v.S); ALLOC(e->d_evec, (size_t)v.E * v.S * v.S); ALLOC(e->d_inv, (size_t)v.E * v.S * v.S);
     ALLOC(e->d_rate, v.K); ALLOC(e->d_weight, v.K); ALLOC(e->d_eigen, v.K);
@@ -183,7 +183,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     if (ok) { rc = cudaMemsetAsync(e->d_counter, 0, 4 * sizeof(unsigned int), e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMemsetAsync(e->d_result, 0, sizeof(double) * LKCUDA_NRESULT, e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMemsetAsync(e->d_theta_meta, 0, sizeof(double) * 8, e->stream); ok = rc == cudaSuccess; }
-    if (ok) { rc = cudaMemsetAsync(e->d_states, 0, (size_t)cfg->ntaxa * v.st_stride, e->stream); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMemsetAsync(e->d_states, 0, (size_t)cfg->ntaxa * v.st_stride + 4096, e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMemsetAsync(e->d_scale, 0, nvec * (size_t)v.sc_stride * sizeof(int16_t), e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaStreamSynchronize(e->stream); ok = rc == cudaSuccess; }
     if (!ok) {

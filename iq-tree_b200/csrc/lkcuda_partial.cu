@@ -69,6 +69,9 @@ __global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevCh
     if (!LKCUDA_IS_TIP(ch.id)) return;
     __syncthreads();
     const int SU = v.SU;
+    /* traversal layout (mpad != 0): row `st` is skewed by (st >> 1) 16-byte granules so that two lanes of a quarter-warp
+       that hold different states of {0,1} x {2,3} never meet in a bank (TRV_TAB_ROW below) */
+    const int skew = mpad ? 2 : 0;
     for (int idx = threadIdx.x; idx < (SU + 1) * B; idx += blockDim.x) {
         int st = idx / B, r = idx - st * B;
         double val = 1.0;
@@ -79,7 +82,7 @@ __global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevCh
             val = 0.0;
             for (int j = 0; j < S; j++) val += row[j] * tip[j];
         }
-        tab[idx] = val;
+        tab[idx + (st >> 1) * skew] = val;
     }
 }
 
@@ -113,19 +116,25 @@ __global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevCh
 #define TRV_CWARPS 11
 #define TRV_CTHREADS (TRV_CWARPS * 32)
 #define TRV_THREADS (TRV_CTHREADS + 32)
-#define TRV_STAGES 4
+#define TRV_MAX_STAGES 8
 #define TRV_R 4
 #define S4_MPAD 18  /* doubles per k of a staged 4x4 matrix: 16 + 2 keeps LDS.128 conflict-free across k */
 #define THR_HI 0x2FF00000   /* high word of 2^-256: |x| < 2^-256  <=>  (hi(x) & 0x7fffffff) < THR_HI */
 #define TRV_SLOT_PREV (-3)  /* child 1 is the result of the node executed immediately before: still in registers */
+/* doubles from the start of a staged tip table to the row of state st (K*4 doubles per row + the skew written by prep_tables_kernel) */
+#define TRV_TAB_ROW(st, K) ((st) * ((K) * 4) + ((st) >> 1) * 2)
+#define TRV_TAB_DOUBLES(SU, K) (((SU) + 1) * (K) * 4 + (((SU) >> 1) + 1) * 2)
 
+/* node descriptor, written by the host, streamed into the ring by the producer (64 bytes) */
 struct TravOp {
-    int32_t dst, dst_slot;      /* arena vector receiving the result; slot it is parked in (-1: not needed again in this launch or
-                                   consumed by the very next node from registers, -2: needed but no slot was free: the consumer
-                                   re-reads the arena vector) */
-    int32_t src0, slot0;        /* child 0: vector (>=0) or LKCUDA_TIP(taxon); slot holding it (-1: read the vector from global memory) */
-    int32_t src1, slot1;        /* child 1: likewise, or TRV_SLOT_PREV */
-    int32_t tab0, tab1;         /* table slots of the two children (prep_tables_kernel output) */
+    double *dst_lh; int16_t *dst_sc;    /* arena vector (partial_lh, scale_num) receiving the result */
+    const double *src0_lh, *src1_lh;    /* arena vectors of the children (NULL for a tip) */
+    int32_t src0, src1;                 /* child: vector (>= 0) or LKCUDA_TIP(taxon) */
+    int32_t slot0, slot1;               /* shared-memory slot holding the child (-1: read the arena vector; slot1 may be TRV_SLOT_PREV) */
+    int32_t dst_slot;                   /* slot the result is parked in (-1: not needed again in this launch or consumed by the next
+                                           node from registers, -2: needed but no slot was free: the consumer re-reads the arena) */
+    int32_t dst;
+    int32_t pad[2];
 };
 
 __device__ __forceinline__ d4 ld_coherent256(const double *p) { /* may have been written earlier by this very thread */
@@ -143,72 +152,89 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+__device__ __forceinline__ bool mbar_try(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
-        "LAB_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE;\n"
-        "bra LAB_WAIT;\n"
-        "DONE:\n"
-        "}\n" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
 }
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) { while (!mbar_try(bar, parity)) { } }
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t *bar, uint32_t parity) { while (!mbar_try(bar, parity)) __nanosleep(256); }
 __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  :: "r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-/* bytes of one ring stage: descriptor (32) + two child blocks of cbs doubles */
-__host__ __device__ __forceinline__ size_t trv_stage_bytes(int cbs) { return 32 + (size_t)2 * cbs * 8; }
+/* ring stage: descriptor (64) | child 0 block | child 1 block (cbs doubles each: padded matrices or tip lookup table) |
+   child 0 tip states | child 1 tip states (spad bytes each: the tile's patterns of that taxon) */
+__host__ __device__ __forceinline__ int trv_stage_bytes(int cbs, int spad) { return 64 + 2 * cbs * 8 + 2 * spad; }
 
-/* t = M * L for the staged 4x4 matrix M (row-major, 8 double2) */
+/* dst = M * L for a 4x4 row-major matrix held as 8 double2 */
 #define TRV_MATVEC(dst, m, L)                                                   \
     dst[0] = m[0].x * L.x + m[0].y * L.y + m[1].x * L.z + m[1].y * L.w;         \
     dst[1] = m[2].x * L.x + m[2].y * L.y + m[3].x * L.z + m[3].y * L.w;         \
     dst[2] = m[4].x * L.x + m[4].y * L.y + m[5].x * L.z + m[5].y * L.w;         \
     dst[3] = m[6].x * L.x + m[6].y * L.y + m[7].x * L.z + m[7].y * L.w;
 
+__device__ __forceinline__ void st_stream256_if(bool pred, double *p, const d4 &v) {
+    asm volatile("{\n.reg .pred q;\nsetp.ne.u32 q, %5, 0;\n@q st.global.L1::no_allocate.v4.f64 [%0], {%1,%2,%3,%4};\n}"
+                 :: "l"(p), "d"(v.x), "d"(v.y), "d"(v.z), "d"(v.w), "r"((unsigned)pred) : "memory");
+}
+__device__ __forceinline__ void st_s16_if(bool pred, int16_t *p, int val) {
+    asm volatile("{\n.reg .pred q;\nsetp.ne.u32 q, %2, 0;\n@q st.global.u16 [%0], %1;\n}" :: "l"(p), "h"((short)val), "r"((unsigned)pred) : "memory");
+}
+
 __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, const TravOp *__restrict__ ops, int nops, int upw, int nslots,
-                                                                     int cbs, long long total_units, long long ntiles) {
+                                                                     int cbs, int spad, int stage_shift, long long total_units, long long ntiles) {
     constexpr int R = TRV_R, CT = TRV_CTHREADS;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int K = v.K, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int stage_bytes = (int)trv_stage_bytes(cbs);
-    unsigned char *ring = smem_raw;                                                          /* [TRV_STAGES][stage_bytes] */
-    double2 *sl = reinterpret_cast<double2 *>(ring + TRV_STAGES * stage_bytes);              /* [nslots][R][2][CT] */
+    const int stage_bytes = trv_stage_bytes(cbs, spad);
+    const uint32_t nstages = 1u << stage_shift, stage_mask = nstages - 1;
+    unsigned char *ring = smem_raw;                                                          /* [nstages][stage_bytes] */
+    double2 *sl = reinterpret_cast<double2 *>(ring + nstages * stage_bytes);                 /* [nslots][R][2][CT] */
     int *ssc = reinterpret_cast<int *>(sl + nslots * R * 2 * CT);                            /* [nslots][R][CT] */
     double *sINV = reinterpret_cast<double *>(ssc + nslots * R * CT);                        /* [K][S4_MPAD] */
-    uint64_t *full = reinterpret_cast<uint64_t *>(sINV + K * S4_MPAD), *empty = full + TRV_STAGES;
+    uint64_t *full = reinterpret_cast<uint64_t *>(sINV + K * S4_MPAD), *empty = full + TRV_MAX_STAGES;
     for (int idx = tid; idx < K * 16; idx += TRV_THREADS) {
         int kk = idx >> 4, r = idx & 15;
         sINV[kk * S4_MPAD + r] = v.inv_evec[v.blk_eigen[kk] * 16 + r];
     }
     if (tid == 0) {
-        for (int s = 0; s < TRV_STAGES; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], TRV_CWARPS); }
+        for (uint32_t s = 0; s < nstages; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], TRV_CWARPS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    const int cta_units = TRV_CWARPS * upw;
+    const int tile_pats = cta_units * R / K;     /* upw is a multiple of K */
 
     if (warp == TRV_CWARPS) {
         /* ------------------------------ producer: one lane feeds the ring ------------------------------ */
         if (lane == 0) {
             uint32_t c = 0;
-            const uint32_t mat_bytes = (uint32_t)K * S4_MPAD * 8, tab_bytes = (uint32_t)(v.SU + 1) * K * 32;
+            const uint32_t mat_bytes = (uint32_t)K * S4_MPAD * 8, tab_bytes = (uint32_t)TRV_TAB_DOUBLES(v.SU, K) * 8;
             for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                const long long p0 = tile * tile_pats, a0 = p0 & ~15ll;           /* bulk copies start 16-byte aligned */
+                const uint32_t st_bytes = (uint32_t)((p0 - a0 + tile_pats + 15) & ~15ll);
                 for (int i = 0; i < nops; i++, c++) {
-                    const uint32_t s = c % TRV_STAGES, ph = (c / TRV_STAGES) & 1;
-                    const TravOp op = ops[i];
+                    const uint32_t s = c & stage_mask, ph = (c >> stage_shift) & 1;
+                    const int src0 = ops[i].src0, src1 = ops[i].src1;
                     unsigned char *st = ring + s * stage_bytes;
-                    const bool t0 = LKCUDA_IS_TIP(op.src0), t1 = LKCUDA_IS_TIP(op.src1);
+                    const bool t0 = LKCUDA_IS_TIP(src0), t1 = LKCUDA_IS_TIP(src1);
                     const uint32_t b0 = t0 ? tab_bytes : mat_bytes, b1 = t1 ? tab_bytes : mat_bytes;
-                    const double *g0 = v.tables + (long long)op.tab0 * v.table_slot + (t0 ? K * S4_MPAD : 0);
-                    const double *g1 = v.tables + (long long)op.tab1 * v.table_slot + (t1 ? K * S4_MPAD : 0);
-                    mbar_wait(&empty[s], ph ^ 1);
-                    mbar_expect_tx(&full[s], 32 + b0 + b1);
-                    bulk_g2s(st, ops + i, 32, &full[s]);
-                    bulk_g2s(st + 32, g0, b0, &full[s]);
-                    bulk_g2s(st + 32 + cbs * 8, g1, b1, &full[s]);
+                    const double *g0 = v.tables + (long long)(2 * i) * v.table_slot + (t0 ? K * S4_MPAD : 0);
+                    const double *g1 = v.tables + (long long)(2 * i + 1) * v.table_slot + (t1 ? K * S4_MPAD : 0);
+                    mbar_wait_backoff(&empty[s], ph ^ 1);
+                    mbar_expect_tx(&full[s], 64 + b0 + b1 + (t0 ? st_bytes : 0) + (t1 ? st_bytes : 0));
+                    bulk_g2s(st, ops + i, 64, &full[s]);
+                    bulk_g2s(st + 64, g0, b0, &full[s]);
+                    bulk_g2s(st + 64 + cbs * 8, g1, b1, &full[s]);
+                    if (t0) bulk_g2s(st + 64 + 2 * cbs * 8, tip_states(v, src0) + a0, st_bytes, &full[s]);
+                    if (t1) bulk_g2s(st + 64 + 2 * cbs * 8 + spad, tip_states(v, src1) + a0, st_bytes, &full[s]);
                 }
             }
         }
@@ -220,33 +246,27 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
     const int k = lane_on ? lane % K : 0;
     const int gbase = lane_on ? lane - k : lane;
     const unsigned gmask = K >= 32 ? 0xffffffffu : ((1u << K) - 1u);
-    const int cta_units = TRV_CWARPS * upw;
     const double2 *inv = reinterpret_cast<const double2 *>(sINV + k * S4_MPAD);
     const bool zero_guard = (v.flags & LKCUDA_FLAG_ZERO_GUARD) != 0, ignore_invar = (v.flags & LKCUDA_FLAG_SCALE_IGNORES_INVAR) != 0;
     double2 *const sl_t = sl + tid;
     int *const ssc_t = ssc + tid;
     const int B = v.B;
+    int q[R];           /* my units' pattern index inside a tile */
+#pragma unroll
+    for (int r = 0; r < R; r++) q[r] = (r * cta_units + warp * upw + (lane_on ? lane : 0)) / K;
     uint32_t c = 0;     /* ring position of the node being computed, continues across tiles */
 
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         long long p[R], off[R];     /* pattern, element offset of the unit inside a vector */
         bool valid[R];
-        const long long u0 = tile * ((long long)cta_units * R) + warp * upw + lane;
+        const long long p0 = tile * tile_pats;
+        const int sdelta = (int)(p0 & 15);
 #pragma unroll
         for (int r = 0; r < R; r++) {
-            long long u = u0 + (long long)r * cta_units;
-            valid[r] = lane_on && u < total_units;
-            p[r] = valid[r] ? u / K : v.NP - 1;      /* out-of-range units shadow the last pattern; only their stores are masked */
+            p[r] = p0 + q[r];
+            valid[r] = lane_on && p[r] < v.NP;
+            if (!valid[r]) p[r] = v.NP - 1;          /* out-of-range units shadow the last pattern; only their stores are masked */
             off[r] = p[r] * B + k * 4;
-        }
-        /* software pipeline: node i+1's descriptor is awaited, and its tip states requested, before node i is computed */
-        mbar_wait(&full[c % TRV_STAGES], (c / TRV_STAGES) & 1);
-        TravOp nxt = *reinterpret_cast<const TravOp *>(ring + (c % TRV_STAGES) * stage_bytes);
-        int st0n[R], st1n[R];
-        {
-            const uint8_t *s0 = tip_states(v, LKCUDA_IS_TIP(nxt.src0) ? nxt.src0 : -1), *s1 = tip_states(v, LKCUDA_IS_TIP(nxt.src1) ? nxt.src1 : -1);
-#pragma unroll
-            for (int r = 0; r < R; r++) { st0n[r] = s0[p[r]]; st1n[r] = s1[p[r]]; }
         }
         d4 pv[R];       /* result of the previous node (TRV_SLOT_PREV) */
         int pvsc[R];
@@ -254,22 +274,14 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
         for (int r = 0; r < R; r++) { pv[r].x = pv[r].y = pv[r].z = pv[r].w = 0.0; pvsc[r] = 0; }
 
         for (int i = 0; i < nops; i++, c++) {
-            const TravOp op = nxt;
-            const uint32_t s = c % TRV_STAGES;
-            int st0[R], st1[R];
-#pragma unroll
-            for (int r = 0; r < R; r++) { st0[r] = st0n[r]; st1[r] = st1n[r]; }
-            if (i + 1 < nops) {
-                const uint32_t c1 = c + 1;
-                mbar_wait(&full[c1 % TRV_STAGES], (c1 / TRV_STAGES) & 1);
-                nxt = *reinterpret_cast<const TravOp *>(ring + (c1 % TRV_STAGES) * stage_bytes);
-                /* a non-tip child prefetches taxon 0's row: a harmless, unused byte */
-                const uint8_t *s0 = tip_states(v, LKCUDA_IS_TIP(nxt.src0) ? nxt.src0 : -1), *s1 = tip_states(v, LKCUDA_IS_TIP(nxt.src1) ? nxt.src1 : -1);
-#pragma unroll
-                for (int r = 0; r < R; r++) { st0n[r] = s0[p[r]]; st1n[r] = s1[p[r]]; }
-            }
-            const bool tip0 = LKCUDA_IS_TIP(op.src0), tip1 = LKCUDA_IS_TIP(op.src1);
-            const double *blk0 = reinterpret_cast<const double *>(ring + s * stage_bytes + 32), *blk1 = blk0 + cbs;
+            const uint32_t s = c & stage_mask;
+            mbar_wait(&full[s], (c >> stage_shift) & 1);
+            const unsigned char *stage = ring + s * stage_bytes;
+            const TravOp *op = reinterpret_cast<const TravOp *>(stage);
+            const int src0 = op->src0, src1 = op->src1, slot0 = op->slot0, slot1 = op->slot1, dst_slot = op->dst_slot;
+            const bool tip0 = LKCUDA_IS_TIP(src0), tip1 = LKCUDA_IS_TIP(src1);
+            const double *blk0 = reinterpret_cast<const double *>(stage + 64), *blk1 = blk0 + cbs;
+            const unsigned char *sst0 = stage + 64 + 2 * cbs * 8 + sdelta, *sst1 = sst0 + spad;
             double t[R][4];
             int sc[R];
             /* ---- child 0: tip | slot | arena ---- */
@@ -277,16 +289,17 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                 const double *tab = blk0 + k * 4;
 #pragma unroll
                 for (int r = 0; r < R; r++) {
-                    const double2 *row = reinterpret_cast<const double2 *>(tab + st0[r] * (K * 4));
+                    const int st = sst0[q[r]];
+                    const double2 *row = reinterpret_cast<const double2 *>(tab + TRV_TAB_ROW(st, K));
                     const double2 a = row[0], b = row[1];
                     t[r][0] = a.x; t[r][1] = a.y; t[r][2] = b.x; t[r][3] = b.y; sc[r] = 0;
                 }
             } else {
                 const double2 *mp = reinterpret_cast<const double2 *>(blk0 + k * S4_MPAD);
                 const double2 m[8] = {mp[0], mp[1], mp[2], mp[3], mp[4], mp[5], mp[6], mp[7]};
-                if (op.slot0 >= 0) {
-                    const double2 *ps = sl_t + op.slot0 * (R * 2 * CT);
-                    const int *pc = ssc_t + op.slot0 * (R * CT);
+                if (slot0 >= 0) {
+                    const double2 *ps = sl_t + slot0 * (R * 2 * CT);
+                    const int *pc = ssc_t + slot0 * (R * CT);
 #pragma unroll
                     for (int r = 0; r < R; r++) {
                         const double2 a = ps[(r * 2) * CT], b = ps[(r * 2 + 1) * CT];
@@ -295,8 +308,8 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                         TRV_MATVEC(t[r], m, L)
                     }
                 } else {
-                    const double *g = vec_lh(v, op.src0);
-                    const int16_t *gs = vec_sc(v, op.src0);
+                    const double *g = op->src0_lh;
+                    const int16_t *gs = vec_sc(v, src0);
 #pragma unroll
                     for (int r = 0; r < R; r++) {
                         const d4 L = ld_coherent256(g + off[r]);
@@ -310,7 +323,8 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                 const double *tab = blk1 + k * 4;
 #pragma unroll
                 for (int r = 0; r < R; r++) {
-                    const double2 *row = reinterpret_cast<const double2 *>(tab + st1[r] * (K * 4));
+                    const int st = sst1[q[r]];
+                    const double2 *row = reinterpret_cast<const double2 *>(tab + TRV_TAB_ROW(st, K));
                     const double2 a = row[0], b = row[1];
                     t[r][0] *= a.x; t[r][1] *= a.y; t[r][2] *= b.x; t[r][3] *= b.y;
                 }
@@ -318,16 +332,16 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                 const double2 *mp = reinterpret_cast<const double2 *>(blk1 + k * S4_MPAD);
                 const double2 m[8] = {mp[0], mp[1], mp[2], mp[3], mp[4], mp[5], mp[6], mp[7]};
                 double u[4];
-                if (op.slot1 == TRV_SLOT_PREV) {
+                if (slot1 == TRV_SLOT_PREV) {
 #pragma unroll
                     for (int r = 0; r < R; r++) {
                         sc[r] += pvsc[r];
                         TRV_MATVEC(u, m, pv[r])
                         t[r][0] *= u[0]; t[r][1] *= u[1]; t[r][2] *= u[2]; t[r][3] *= u[3];
                     }
-                } else if (op.slot1 >= 0) {
-                    const double2 *ps = sl_t + op.slot1 * (R * 2 * CT);
-                    const int *pc = ssc_t + op.slot1 * (R * CT);
+                } else if (slot1 >= 0) {
+                    const double2 *ps = sl_t + slot1 * (R * 2 * CT);
+                    const int *pc = ssc_t + slot1 * (R * CT);
 #pragma unroll
                     for (int r = 0; r < R; r++) {
                         const double2 a = ps[(r * 2) * CT], b = ps[(r * 2 + 1) * CT];
@@ -337,8 +351,8 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                         t[r][0] *= u[0]; t[r][1] *= u[1]; t[r][2] *= u[2]; t[r][3] *= u[3];
                     }
                 } else {
-                    const double *g = vec_lh(v, op.src1);
-                    const int16_t *gs = vec_sc(v, op.src1);
+                    const double *g = op->src1_lh;
+                    const int16_t *gs = vec_sc(v, src1);
 #pragma unroll
                     for (int r = 0; r < R; r++) {
                         const d4 L = ld_coherent256(g + off[r]);
@@ -348,60 +362,65 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                     }
                 }
             }
-            /* the stage's tables are in registers now: hand the stage back to the producer */
+            double *const dst_lh = op->dst_lh;
+            int16_t *const dst_sc = op->dst_sc;
+            /* everything this node needs from the stage is in registers now: hand the stage back to the producer */
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[s]);
             /* ---- back to state space, scaling test, stores ---- */
             const double2 iv[8] = {inv[0], inv[1], inv[2], inv[3], inv[4], inv[5], inv[6], inv[7]};
             const bool may_scale = !(tip0 && tip1);   /* tip-tip never scales (phylokernel.h:246-281) */
-            double *dst_lh = vec_lh_w(v, op.dst);
-            int16_t *dst_sc = vec_sc_w(v, op.dst);
-            double2 *pd = sl_t + op.dst_slot * (R * 2 * CT);
-            int *pdc = ssc_t + op.dst_slot * (R * CT);
+            bool tiny = false;
 #pragma unroll
             for (int r = 0; r < R; r++) {
-                d4 o;
-                {
-                    const d4 T = {t[r][0], t[r][1], t[r][2], t[r][3]};
-                    double w[4];
-                    TRV_MATVEC(w, iv, T)
-                    o.x = w[0]; o.y = w[1]; o.z = w[2]; o.w = w[3];
-                }
-                if (may_scale) {
-                    /* lh_max < 2^-256 decided on the exponent words (integer pipe), agreed inside the pattern's lane group by a ballot */
-                    const int h0 = __double2hiint(o.x) & 0x7fffffff, h1 = __double2hiint(o.y) & 0x7fffffff,
-                              h2 = __double2hiint(o.z) & 0x7fffffff, h3 = __double2hiint(o.w) & 0x7fffffff;
+                const d4 T = {t[r][0], t[r][1], t[r][2], t[r][3]};
+                double w[4];
+                TRV_MATVEC(w, iv, T)
+                pv[r].x = w[0]; pv[r].y = w[1]; pv[r].z = w[2]; pv[r].w = w[3];
+                /* lh_max < 2^-256 is decided on the exponent words: integer pipe, not the FP64 pipe */
+                const int mx = max(max(__double2hiint(w[0]) & 0x7fffffff, __double2hiint(w[1]) & 0x7fffffff),
+                                   max(__double2hiint(w[2]) & 0x7fffffff, __double2hiint(w[3]) & 0x7fffffff));
+                tiny |= mx < THR_HI;
+            }
+            if (may_scale && __any_sync(0xffffffffu, tiny)) {
+                /* rare path: some unit of this warp is below the threshold; agree per pattern (lane group) with ballots */
+#pragma unroll
+                for (int r = 0; r < R; r++) {
+                    const int h0 = __double2hiint(pv[r].x) & 0x7fffffff, h1 = __double2hiint(pv[r].y) & 0x7fffffff,
+                              h2 = __double2hiint(pv[r].z) & 0x7fffffff, h3 = __double2hiint(pv[r].w) & 0x7fffffff;
                     const unsigned small = __ballot_sync(0xffffffffu, max(max(h0, h1), max(h2, h3)) < THR_HI);
+                    const bool nz = (h0 | h1 | h2 | h3 | __double2loint(pv[r].x) | __double2loint(pv[r].y) | __double2loint(pv[r].z) | __double2loint(pv[r].w)) != 0;
+                    const unsigned anynz = __ballot_sync(0xffffffffu, nz);
                     if (((small >> gbase) & gmask) == gmask) {
-                        bool refill = false;
-                        if (zero_guard) {
-                            const bool nz = (h0 | h1 | h2 | h3 | __double2loint(o.x) | __double2loint(o.y) | __double2loint(o.z) | __double2loint(o.w)) != 0;
-                            const unsigned anynz = __ballot_sync(__activemask(), nz);
-                            refill = ((anynz >> gbase) & gmask) == 0;
-                        }
-                        if (refill) {
+                        if (zero_guard && ((anynz >> gbase) & gmask) == 0) {
                             const double *tu = v.tip + ((long long)v.SU * v.E + v.blk_eigen[k]) * 4;
-                            o.x = tu[0]; o.y = tu[1]; o.z = tu[2]; o.w = tu[3];
+                            pv[r].x = tu[0]; pv[r].y = tu[1]; pv[r].z = tu[2]; pv[r].w = tu[3];
                             sc[r] += 4;
                         } else if (ignore_invar || v.invar[p[r]] == 0.0) {
-                            o.x *= LK_THR_INV; o.y *= LK_THR_INV; o.z *= LK_THR_INV; o.w *= LK_THR_INV;
+                            pv[r].x *= LK_THR_INV; pv[r].y *= LK_THR_INV; pv[r].z *= LK_THR_INV; pv[r].w *= LK_THR_INV;
                             sc[r] += 1;
                         }
                     }
                 }
-                if (valid[r]) {
-                    st_stream256(dst_lh + off[r], o);
-                    if (k == 0) dst_sc[p[r]] = (int16_t)sc[r];
-                }
-                if (op.dst_slot >= 0) {   /* parked for a later node of this launch */
-                    pd[(r * 2) * CT] = make_double2(o.x, o.y);
-                    pd[(r * 2 + 1) * CT] = make_double2(o.z, o.w);
+            }
+#pragma unroll
+            for (int r = 0; r < R; r++) {
+                pvsc[r] = sc[r];
+                st_stream256_if(valid[r], dst_lh + off[r], pv[r]);
+                st_s16_if(valid[r] && k == 0, dst_sc + p[r], sc[r]);
+            }
+            if (dst_slot >= 0) {   /* parked for a later node of this launch */
+                double2 *pd = sl_t + dst_slot * (R * 2 * CT);
+                int *pdc = ssc_t + dst_slot * (R * CT);
+#pragma unroll
+                for (int r = 0; r < R; r++) {
+                    pd[(r * 2) * CT] = make_double2(pv[r].x, pv[r].y);
+                    pd[(r * 2 + 1) * CT] = make_double2(pv[r].z, pv[r].w);
                     pdc[r * CT] = sc[r];
                 }
-                pv[r] = o; pvsc[r] = sc[r];
             }
             /* spilled result: its consumer re-reads scale_num, which lane k == 0 wrote for the whole lane group */
-            if (op.dst_slot == -2) { __threadfence_block(); __syncwarp(); }
+            if (dst_slot == -2) { __threadfence_block(); __syncwarp(); }
         }
     }
 }
@@ -524,7 +543,7 @@ static size_t generic_smem(const DevView &v) {
     return ((size_t)2 * v.S * v.S + (size_t)2 * GEN_TP * (v.S + 1)) * 8 + GEN_TP * 8 + GEN_TP * 4;
 }
 
-static_assert(sizeof(TravOp) == 2 * sizeof(DevOp), "the op ring is sized in TravOp units");
+static_assert(sizeof(TravOp) == 64 && sizeof(TravOp) >= sizeof(DevOp), "the op ring is sized in TravOp units");
 
 static bool use_traverse(const DevView &v) { return v.S == 4 && v.K <= 32; }
 
@@ -712,11 +731,17 @@ static int launch_ops(lkcuda_engine *e, int slot, int nops, int nchild_total, co
 static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops) {
     const DevView &v = e->v;
     /* child block of a ring stage: a padded matrix set or a tip lookup table, whichever is larger */
-    const int cbs_mat = v.K * S4_MPAD, cbs_tab = (v.SU + 1) * v.K * 4, cbs = cbs_mat > cbs_tab ? cbs_mat : cbs_tab;
+    const int cbs_mat = v.K * S4_MPAD, cbs_tab = TRV_TAB_DOUBLES(v.SU, v.K), cbs = cbs_mat > cbs_tab ? cbs_mat : cbs_tab;
     const size_t slot_bytes = (size_t)TRV_R * TRV_CTHREADS * (32 + 4);
-    const size_t fixed = TRV_STAGES * trv_stage_bytes(cbs) + (size_t)v.K * S4_MPAD * 8 + 2 * TRV_STAGES * 8;
-    if (fixed + 128 > 227 * 1024) return fail(e, LKCUDA_ERR_ARG, "too many categories for the DNA traversal kernel");
-    int maxslots = (int)((227 * 1024 - 128 - fixed) / slot_bytes);
+    const int upw = (32 / v.K) * v.K, tile_pats = TRV_CWARPS * upw * TRV_R / v.K, spad = (tile_pats + 15 + 15) & ~15;
+    /* ring depth: 8 stages when they fit beside the slots the schedule is likely to need, else 4, else 2 */
+    const size_t other = (size_t)v.K * S4_MPAD * 8 + 2 * TRV_MAX_STAGES * 8 + 128;
+    const size_t stage_b = (size_t)trv_stage_bytes(cbs, spad);
+    int stage_shift = 3;
+    while (stage_shift > 1 && (size_t)(1 << stage_shift) * stage_b + other + 3 * slot_bytes > 227 * 1024) stage_shift--;
+    const size_t fixed = (size_t)(1 << stage_shift) * stage_b + other;
+    if (fixed > 227 * 1024) return fail(e, LKCUDA_ERR_ARG, "too many categories for the DNA traversal kernel");
+    int maxslots = (int)((227 * 1024 - fixed) / slot_bytes);
     if (e->trav_maxslots >= 0 && e->trav_maxslots < maxslots) maxslots = e->trav_maxslots;   /* test knob: forces the spill path */
     TravSchedule sch;
     int rc = schedule_traverse(e, ops, nops, maxslots, sch);
@@ -730,9 +755,12 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
         const TravNode &n = sch.nodes[j];
         TravOp &t = h[j];
         t.dst = ops[n.op].dst; t.dst_slot = n.dst_slot;
+        t.dst_lh = e->d_arena + (size_t)t.dst * v.vec_stride; t.dst_sc = e->d_scale + (size_t)t.dst * v.sc_stride;
         t.src0 = n.src0; t.slot0 = n.slot0;
         t.src1 = n.src1; t.slot1 = n.slot1;
-        t.tab0 = 2 * j; t.tab1 = 2 * j + 1;
+        t.src0_lh = n.src0 >= 0 ? e->d_arena + (size_t)n.src0 * v.vec_stride : NULL;
+        t.src1_lh = n.src1 >= 0 ? e->d_arena + (size_t)n.src1 * v.vec_stride : NULL;
+        t.pad[0] = t.pad[1] = 0;
         DevChild &a = e->h_child[slot][2 * j], &b = e->h_child[slot][2 * j + 1];
         a.id = n.src0; a.pad = 0; a.len = n.len0;
         b.id = n.src1; b.pad = 0; b.len = n.len1;
@@ -753,18 +781,17 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
     rc = launch_end(e, KIND_PREP, 0, "prep_tables_kernel");
     if (rc) return rc;
 
-    const int upw = (32 / v.K) * v.K;
     const long long total_units = v.NP * v.K, tile_units = (long long)TRV_CWARPS * upw * TRV_R;
     const long long ntiles = (total_units + tile_units - 1) / tile_units;
-    const size_t sm = (size_t)sch.nslots * slot_bytes + fixed + 128;
+    const size_t sm = (size_t)sch.nslots * slot_bytes + fixed;
     if (sm > e->trav_smem_set) {
         LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         e->trav_smem_set = sm;
     }
-    long long grid = e->num_sms;      /* one persistent CTA per SM (512 threads, shared memory bound) */
+    long long grid = e->num_sms;      /* one persistent CTA per SM (384 threads, shared memory bound) */
     if (grid > ntiles) grid = ntiles;
     launch_begin(e, KIND_PARTIAL);
-    traverse_s4_kernel<<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, total_units, ntiles);
+    traverse_s4_kernel<<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, total_units, ntiles);
     return launch_end(e, KIND_PARTIAL, bytes, "traverse_s4_kernel");
 }
 
