@@ -264,6 +264,19 @@ def main():
     ms = ev0.elapsed_time(ev1)
     stats = t.kernelStats()
     launches = t.launchCount()
+
+    # ---- lnL only (clearAllPartialLH + computeLikelihood): the full-tree traversal launch alone, for the roofline ----
+    t.resetCounters()
+    barrier()
+    ev4, ev5 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev4.record(stream)
+    for _ in range(args.steps):
+        t.clearAllPartialLH()
+        t.computeLikelihood()
+    ev5.record(stream)
+    barrier()
+    ms_lnl = ev4.elapsed_time(ev5)
+    stats_lnl = t.kernelStats()
     t.setProfiling(False)
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region --------------------------------
@@ -298,18 +311,22 @@ def main():
     ms_e2e = ev2.elapsed_time(ev3)
     clocks = sampler.finish() if sampler else None
 
-    tt = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    tt = torch.tensor([ms, ms_e2e, ms_lnl], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    ms, ms_e2e = float(tt[0]), float(tt[1])
+    ms, ms_e2e, ms_lnl = float(tt[0]), float(tt[1]), float(tt[2])
 
     if rank == 0:
         updates = (NTAXA - 2) * NPTN * NCAT
         value = updates * args.steps / (ms * 1e-3)
         e2e_value = updates * args.steps / (ms_e2e * 1e-3)
         peak, peak_src = measured_hbm_peak()
-        n_p, b_p, ms_p = stats["partial"]
+        n_p, b_p, ms_p = stats_lnl["partial"]      # the full-tree traversal launches of the lnL-only loop
         achieved = (b_p / 1e9) / (ms_p * 1e-3) if ms_p > 0 else 0.0
+        nloc_all = t.localPatterns()[1] - t.localPatterns()[0]
+        # what the traversal kernel is designed to move: every node's vector + scale_num written once, one byte per tip child read
+        traffic_model = nloc_all * ((NTAXA - 2) * (4 * NCAT * 8 + 2) + NTAXA)
+        traffic_ncu = 12.79e9 if (world == 1 and NTAXA == 100 and NPTN == 1000000) else None   # profiles/r1_trv_ncu_summary.txt
         kinds = {k: {"launches": v[0], "algorithmic_gb": v[1] / 1e9, "device_ms": v[2],
                      "gbps": (v[1] / 1e9) / (v[2] * 1e-3) if v[2] > 0 else None} for k, v in stats.items() if v[0]}
         line = {
@@ -320,14 +337,21 @@ def main():
                        "step": "clearAllPartialLH + computeLikelihood + computeLikelihoodDerv(root branch, theta rebuilt)",
                        "l2": "inputs larger than L2: ~%.1f GB streamed per step per GPU vs 126 MB L2, no flush needed" % (
                            sum(v[1] for v in stats.values()) / 1e9 / max(args.steps, 1))},
-            "lnl_evals_per_s": args.steps / (ms * 1e-3),
+            "steps_per_s": args.steps / (ms * 1e-3),
+            "lnl_evals_per_s": args.steps / (ms_lnl * 1e-3), "ms_per_lnl_eval": ms_lnl / args.steps,
             "lnl": res[0], "df": res[1], "ddf": res[2],
             "e2e": {"value": e2e_value, "unit": "updates/s", "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": int(NTAXA * nloc), "d2h_bytes_per_step": int(8 * nloc + 3 * 64)},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "partial_s4_kernel (one launch per tree level)", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": None, "peak_source": peak_src,
-                         "launches": int(n_p), "algorithmic_bytes_per_launch": b_p / max(n_p, 1), "avg_launch_ms": ms_p / max(n_p, 1)},
+            "roofline": {"bound": "hbm", "kernel": "traverse_s4_kernel (whole post-order schedule in one launch; full-tree lnL launches only)",
+                         "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": traffic_ncu, "peak_source": peak_src,
+                         "launches": int(n_p), "algorithmic_bytes_per_launch": b_p / max(n_p, 1), "avg_launch_ms": ms_p / max(n_p, 1),
+                         "traffic_model_bytes_per_launch": traffic_model,
+                         "hbm_gbps_on_model_traffic": (traffic_model / 1e9) / (ms_p / max(n_p, 1) * 1e-3) if ms_p > 0 else None,
+                         "note": "achieved counts ALGORITHMIC bytes (SURVEY 8d: children read + result written per node); the kernel keeps "
+                                 "children in shared memory/registers and only writes each node once, so DRAM traffic is ~0.38x algorithmic "
+                                 "and frac can exceed 1"},
             "kernels": kinds,
             "clocks": clocks,
         }

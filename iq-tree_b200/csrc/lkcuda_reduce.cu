@@ -33,8 +33,9 @@ static GroupShape group_shape(const DevView &v) {
 }
 
 static int red_grid(const lkcuda_engine *e, long long NP, int G) {
-    long long groups_per_block = RED_THREADS / G;
-    long long need = (NP + groups_per_block - 1) / groups_per_block;
+    (void)G;
+    long long per_block = RED_THREADS;      /* a warp takes 32 patterns per outer step whatever G is */
+    long long need = (NP + per_block - 1) / per_block;
     long long cap = (long long)e->num_sms * 8;
     if (cap > e->red_blocks) cap = e->red_blocks;
     if (need < 1) need = 1;
@@ -123,40 +124,47 @@ __global__ void __launch_bounds__(RED_THREADS) branch_kernel(DevView v, int dad,
     const int nsec = v.B >> 2;
     double acc[4] = {0.0, 0.0, 0.0, 0.0};
 
-    for (long long base = warp_id * gpw; base < v.NP; base += nwarps * gpw) {
-        const long long p = base + gin;
-        const bool active = p < v.NP;
-        double s[1] = {0.0};
-        if (active) {
-            const int state = TIP ? st[p] : 0;
-            if (VEC) {
-                const double *a = lh_node + p * v.B;
-                for (int q = g; q < nsec; q += G) {
-                    d4 x = ld_stream256(a + 4 * q);
-                    if (TIP) {
-                        double t0, t1, t2, t3;
-                        if (use_tab) { const double *t = tipB + state * v.B + 4 * q; t0 = t[0]; t1 = t[1]; t2 = t[2]; t3 = t[3]; }
-                        else { t0 = tip_elem(v, state, 4 * q, val); t1 = tip_elem(v, state, 4 * q + 1, val); t2 = tip_elem(v, state, 4 * q + 2, val); t3 = tip_elem(v, state, 4 * q + 3, val); }
-                        s[0] = fma(t0, x.x, s[0]); s[0] = fma(t1, x.y, s[0]); s[0] = fma(t2, x.z, s[0]); s[0] = fma(t3, x.w, s[0]);
-                    } else {
-                        d4 y = ld_stream256(lh_dad + p * v.B + 4 * q);
-                        const double *w = val + 4 * q;
-                        s[0] = fma(w[0] * x.x, y.x, s[0]); s[0] = fma(w[1] * x.y, y.y, s[0]);
-                        s[0] = fma(w[2] * x.z, y.z, s[0]); s[0] = fma(w[3] * x.w, y.w, s[0]);
+    /* one outer step = 32 patterns per warp: G sub-steps of 32/G patterns, each summed inside its G-lane group;
+       lane (gin, g) keeps the total of sub-step g, so afterwards every lane owns one distinct pattern for the tail */
+    for (long long base = warp_id * 32; base < v.NP; base += nwarps * 32) {
+        double mine = 0.0;
+        for (int j = 0; j < G; j++) {
+            const long long p = base + (long long)j * gpw + gin;
+            double s0 = 0.0;
+            if (p < v.NP) {
+                const int state = TIP ? st[p] : 0;
+                if (VEC) {
+                    const double *a = lh_node + p * v.B;
+                    for (int q = g; q < nsec; q += G) {
+                        d4 x = ld_stream256(a + 4 * q);
+                        if (TIP) {
+                            double t0, t1, t2, t3;
+                            if (use_tab) { const double *t = tipB + state * v.B + 4 * q; t0 = t[0]; t1 = t[1]; t2 = t[2]; t3 = t[3]; }
+                            else { t0 = tip_elem(v, state, 4 * q, val); t1 = tip_elem(v, state, 4 * q + 1, val); t2 = tip_elem(v, state, 4 * q + 2, val); t3 = tip_elem(v, state, 4 * q + 3, val); }
+                            s0 = fma(t0, x.x, s0); s0 = fma(t1, x.y, s0); s0 = fma(t2, x.z, s0); s0 = fma(t3, x.w, s0);
+                        } else {
+                            d4 y = ld_stream256(lh_dad + p * v.B + 4 * q);
+                            const double *w = val + 4 * q;
+                            s0 = fma(w[0] * x.x, y.x, s0); s0 = fma(w[1] * x.y, y.y, s0);
+                            s0 = fma(w[2] * x.z, y.z, s0); s0 = fma(w[3] * x.w, y.w, s0);
+                        }
+                    }
+                } else {
+                    const double *a = lh_node + p * v.B;
+                    for (int jj = 0; jj < v.B; jj++) {
+                        if (TIP) s0 = fma(use_tab ? tipB[state * v.B + jj] : tip_elem(v, state, jj, val), a[jj], s0);
+                        else s0 = fma(val[jj] * a[jj], lh_dad[p * v.B + jj], s0);
                     }
                 }
-            } else {
-                const double *a = lh_node + p * v.B;
-                for (int j = 0; j < v.B; j++) {
-                    if (TIP) s[0] = fma(use_tab ? tipB[state * v.B + j] : tip_elem(v, state, j, val), a[j], s[0]);
-                    else s[0] = fma(val[j] * a[j], lh_dad[p * v.B + j], s[0]);
-                }
             }
+            double s[1] = {s0};
+            group_sum<1>(s, G);
+            if (j == g) mine = s[0];
         }
-        group_sum<1>(s, G);
-        if (active && g == 0) {
+        const long long p = base + (long long)g * gpw + gin;
+        if (p < v.NP) {
             int sc = sc_node[p] + (TIP ? 0 : sc_dad[p]);
-            lnl_tail(v, p, s[0], sc, acc);
+            lnl_tail(v, p, mine, sc, acc);
         }
     }
     if (grid_reduce<4>(acc, sred, v.red, v.counter)) lnl_finish(v, acc, acc[1]);
@@ -281,20 +289,25 @@ __device__ __forceinline__ bool derv_pass(const DevView &v, double len, int gshi
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
     const int gin = (threadIdx.x & 31) >> gshift;
     double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
-    for (long long base = warp_id * gpw; base < v.NP; base += nwarps * gpw) {
-        const long long p = base + gin;
-        const bool active = p < v.NP;
-        double s[3] = {0.0, 0.0, 0.0};
-        if (active) theta_dot<3, VEC>(v, p, g, G, val0, val1, val2, s);
-        group_sum<3>(s, G);
-        if (active && g == 0) {
-            double lh = fabs(s[0] + v.invar[p]);
+    /* 32 patterns per warp and outer step; after the G sub-steps every lane owns one distinct pattern (see branch_kernel) */
+    for (long long base = warp_id * 32; base < v.NP; base += nwarps * 32) {
+        double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+        for (int j = 0; j < G; j++) {
+            const long long p = base + (long long)j * gpw + gin;
+            double s[3] = {0.0, 0.0, 0.0};
+            if (p < v.NP) theta_dot<3, VEC>(v, p, g, G, val0, val1, val2, s);
+            group_sum<3>(s, G);
+            if (j == g) { m0 = s[0]; m1 = s[1]; m2 = s[2]; }
+        }
+        const long long p = base + (long long)g * gpw + gin;
+        if (p < v.NP) {
+            double lh = fabs(m0 + v.invar[p]);
             if (p < v.P) {      /* phylotreesse.cpp:1106-1132 */
-                double df_frac = s[1] / lh, ddf_frac = s[2] / lh, f = v.freq[p];
+                double df_frac = m1 / lh, ddf_frac = m2 / lh, f = v.freq[p];
                 double t1 = df_frac * f, t2 = ddf_frac * f;
                 acc[0] += t1;
                 acc[1] += t2 - t1 * df_frac;
-            } else { acc[2] += lh; acc[3] += s[1]; acc[4] += s[2]; }
+            } else { acc[2] += lh; acc[3] += m1; acc[4] += m2; }
         }
     }
     if (!grid_reduce<5>(acc, sred, v.red, v.counter)) return false;
@@ -334,14 +347,18 @@ __global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(DevView v, double 
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
     const int gin = (threadIdx.x & 31) >> gshift;
     double acc[4] = {0.0, 0.0, 0.0, 0.0};
-    for (long long base = warp_id * gpw; base < v.NP; base += nwarps * gpw) {
-        const long long p = base + gin;
-        const bool active = p < v.NP;
-        double s[1] = {0.0};
-        if (active) theta_dot<1, VEC>(v, p, g, G, sh, NULL, NULL, s);
-        group_sum<1>(s, G);
+    for (long long base = warp_id * 32; base < v.NP; base += nwarps * 32) {
+        double mine = 0.0;
+        for (int j = 0; j < G; j++) {
+            const long long p = base + (long long)j * gpw + gin;
+            double s[1] = {0.0};
+            if (p < v.NP) theta_dot<1, VEC>(v, p, g, G, sh, NULL, NULL, s);
+            group_sum<1>(s, G);
+            if (j == g) mine = s[0];
+        }
+        const long long p = base + (long long)g * gpw + gin;
         /* scale factors were folded into theta_meta[0] when theta_all was built: pass sc = 0 for observed patterns */
-        if (active && g == 0) lnl_tail(v, p, s[0], p < v.P ? 0 : (int)v.theta_sc[p - v.P], acc);
+        if (p < v.NP) lnl_tail(v, p, mine, p < v.P ? 0 : (int)v.theta_sc[p - v.P], acc);
     }
     if (grid_reduce<4>(acc, sred, v.red, v.counter)) lnl_finish(v, acc, v.theta_meta[0]);
 }
