@@ -150,7 +150,7 @@ def reference_arm(args):
     names, nwk, states, _ = make_inputs(min(CPU_SAMPLE_SITES, NPTN))
     ref = run_reference(names, nwk, states, args.steps + args.warmup, 0)
     if ref is None:
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_harness missing or failed"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/ref_harness missing or failed"})
         return 0
     v = ref["updates_per_s"]
     line = {
@@ -163,11 +163,32 @@ def reference_arm(args):
         "e2e": {"value": v, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """Everything libraries print to fd 1 (NCCL's version banner, torchrun notes) goes to stderr; the JSON line alone goes to stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -205,16 +226,18 @@ def main():
     t.setParams(0.1 / NPTN if NPTN >= 100000 else 1e-6, 100.0)
     t.setDevices([local])
     t.setProcessShard(rank, world)
-    stream = torch.cuda.current_stream()
+    # an explicit (non-default) stream: the engine, the CUDA events and NCCL's stream-ordering all refer to this one
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     t.setStream(stream.cuda_stream)
     t.initializeAllPartialLh()
 
-    class _DevBuf:
-        def __init__(self, ptr, n):
-            self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f8", "data": (ptr, False), "version": 3}
-
+    shard_check = None
     if world > 1:
-        cache = {}
+        # the engine keeps its 8-double result block inside this tensor; the only exchange of the path is one in-place NCCL sum of it
+        resbuf = torch.zeros(8, dtype=torch.float64, device=dev)
+        t.setResultBuffer(resbuf.data_ptr())
 
         def allreduce(host, dev_ptr, n):
             if host is not None:
@@ -222,11 +245,19 @@ def main():
                 dist.all_reduce(x)
                 host[:] = x.cpu().numpy()
                 return
-            if dev_ptr not in cache:
-                cache[dev_ptr] = torch.as_tensor(_DevBuf(dev_ptr, n), device=dev)
-            dist.all_reduce(cache[dev_ptr])
+            assert dev_ptr == resbuf.data_ptr()
+            dist.all_reduce(resbuf)
 
+        # sanity of the sharded sum: local lnL values summed by hand == the all-reduced lnL
+        t.clearAllPartialLH()
+        loc = torch.tensor([t.computeLikelihood()], dtype=torch.float64, device=dev)
+        dist.all_reduce(loc)
         t.setAllReduce(allreduce)
+        t.clearAllPartialLH()
+        glob = t.computeLikelihood()
+        shard_check = bool(abs(glob - float(loc[0])) <= 1e-12 * abs(glob))
+        if not shard_check:
+            raise SystemExit("sharded lnL %r != sum of shard lnLs %r" % (glob, float(loc[0])))
 
     root_leaf, root_nei = 0, None
     trav = t.getTraversal()
@@ -339,7 +370,7 @@ def main():
                            sum(v[1] for v in stats.values()) / 1e9 / max(args.steps, 1))},
             "steps_per_s": args.steps / (ms * 1e-3),
             "lnl_evals_per_s": args.steps / (ms_lnl * 1e-3), "ms_per_lnl_eval": ms_lnl / args.steps,
-            "lnl": res[0], "df": res[1], "ddf": res[2],
+            "lnl": res[0], "df": res[1], "ddf": res[2], "shard_sum_check": shard_check,
             "e2e": {"value": e2e_value, "unit": "updates/s", "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": int(NTAXA * nloc), "d2h_bytes_per_step": int(8 * nloc + 3 * 64)},
             "gpu_launches": int(launches),
@@ -362,7 +393,7 @@ def main():
                                         "sample": ref["sample"], "lnl_evals_per_s_on_sample": 1.0 / ref["lnl_s_mean"]}
             else:
                 line["cpu_baseline"] = None
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -163,6 +163,9 @@ int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, 
 /* results of the last enqueued reduction (synchronises) / their device address (for NCCL) */
 int lkcuda_read_result(lkcuda_engine *e, double *result);
 int lkcuda_result_device_ptr(lkcuda_engine *e, void **dev_ptr);
+/* keep the result block in caller-owned device memory (LKCUDA_NRESULT doubles, e.g. a buffer registered with NCCL or a
+   torch tensor) so that the caller's all-reduce runs in place on it; NULL = back to the engine's own block */
+int lkcuda_set_result_buffer(lkcuda_engine *e, void *dev_ptr);
 
 /* ---- host-visible mirrors (buffers host code reads or writes) ---- */
 int lkcuda_fetch_pattern_lh(lkcuda_engine *e, double *pattern_lh /*[P]*/);

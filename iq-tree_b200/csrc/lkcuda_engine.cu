@@ -310,7 +310,7 @@ int lkcuda_set_model(lkcuda_engine *e, const double *eval, const double *evec, c
 int lkcuda_read_result(lkcuda_engine *e, double *result) {
     LK_ENTER(e);
     if (!result) return fail(e, LKCUDA_ERR_ARG, "null result");
-    LK_CUDA(e, cudaMemcpyAsync(e->h_result, e->d_result, sizeof(double) * LKCUDA_NRESULT, cudaMemcpyDeviceToHost, e->stream));
+    LK_CUDA(e, cudaMemcpyAsync(e->h_result, e->v.result, sizeof(double) * LKCUDA_NRESULT, cudaMemcpyDeviceToHost, e->stream));
     LK_CUDA(e, cudaStreamSynchronize(e->stream));
     memcpy(result, e->h_result, sizeof(double) * LKCUDA_NRESULT);
     return LKCUDA_OK;
@@ -318,7 +318,14 @@ int lkcuda_read_result(lkcuda_engine *e, double *result) {
 
 int lkcuda_result_device_ptr(lkcuda_engine *e, void **p) {
     if (!e || !p) return LKCUDA_ERR_ARG;
-    *p = e->d_result;
+    *p = e->v.result;
+    return LKCUDA_OK;
+}
+
+int lkcuda_set_result_buffer(lkcuda_engine *e, void *dev_ptr) {
+    LK_ENTER(e);
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    e->v.result = dev_ptr ? (double *)dev_ptr : e->d_result;
     return LKCUDA_OK;
 }
 

@@ -566,7 +566,7 @@ int lkcuda_vector_scale_factor(lkcuda_engine *e, int32_t vec, double *out) {
     scale_factor_kernel<<<grid, RED_THREADS, 0, e->stream>>>(e->v, vec);
     int rc = launch_end(e, KIND_MISC, 0, "scale_factor_kernel");
     if (rc) return rc;
-    LK_CUDA(e, cudaMemcpyAsync(e->h_newton_out, e->d_result + 7, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    LK_CUDA(e, cudaMemcpyAsync(e->h_newton_out, e->v.result + 7, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
     LK_CUDA(e, cudaStreamSynchronize(e->stream));
     *out = e->h_newton_out[0];
     return LKCUDA_OK;

@@ -52,6 +52,7 @@ LKCUDA_SYMBOLS = {
     "lkcuda_newton_branch": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32, c_double_p]),
     "lkcuda_read_result": (C.c_int, [C.c_void_p, c_double_p]),
     "lkcuda_result_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "lkcuda_set_result_buffer": (C.c_int, [C.c_void_p, C.c_void_p]),
     "lkcuda_fetch_pattern_lh": (C.c_int, [C.c_void_p, c_double_p]),
     "lkcuda_fetch_pattern_lh_cat": (C.c_int, [C.c_void_p, c_double_p]),
     "lkcuda_fetch_vector": (C.c_int, [C.c_void_p, C.c_int32, c_double_p, c_int16_p]),
@@ -402,6 +403,11 @@ class PhyloTree:
             self._eck(e, self.lib.lkcuda_vector_scale_factor(e, vec, C.byref(v)))
             tot += v.value
         return tot
+
+    def setResultBuffer(self, dev_ptr, shard=0):
+        """keep the 8-double result block in caller-owned device memory (e.g. a torch tensor's data_ptr()) for an in-place all-reduce"""
+        e = self.engine(shard)
+        self._eck(e, self.lib.lkcuda_set_result_buffer(e, C.c_void_p(dev_ptr)))
 
     def launchCount(self, shard=0):
         e = self.engine(shard)

@@ -44,7 +44,8 @@ struct lkcuda_engine {
     int theta_ready, theta_dad_tip;
     double theta_scale_sum;
     int16_t *theta_scale_num;        /* [U] summed scale_num of the unobserved patterns */
-    double result[LKCUDA_NRESULT];
+    double result_own[LKCUDA_NRESULT];
+    double *result;                  /* result_own or a caller-supplied block (lkcuda_set_result_buffer) */
     uint64_t launches, bytes;
     char err[256];
 };
@@ -66,6 +67,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
         cfg->nunobs < 0 || cfg->nvec < 0 || cfg->state_unknown < cfg->nstates)
         return fail(NULL, LKCUDA_ERR_ARG, "invalid configuration");
     lkcuda_engine *e = (lkcuda_engine *)calloc(1, sizeof(*e));
+    if (e) e->result = e->result_own;
     if (!e) return fail(NULL, LKCUDA_ERR_NOMEM, "out of memory");
     e->cfg = *cfg;
     e->S = cfg->nstates; e->K = cfg->nblocks; e->E = cfg->neigen;
@@ -366,7 +368,7 @@ static void finish_lnl(lkcuda_engine *e, const double *lh_ptn_all, const int16_t
         for (size_t p = 0; p < P; p++) e->pattern_lh[p] -= lc;
         tree_lh -= (double)e->cfg.nsite * lc;
     }
-    memset(e->result, 0, sizeof(e->result));
+    memset(e->result, 0, sizeof(e->result_own));
     e->result[LKCUDA_R_LNL] = tree_lh;
     e->result[LKCUDA_R_PROB_CONST] = prob_const;
     e->result[LKCUDA_R_NREPAIRED] = nrep;
@@ -403,7 +405,7 @@ int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     finish_lnl(e, lh_all, ssn, scale_sum);
     free(val); free(lh_all); free(ssn);
     e->launches++;
-    if (result) memcpy(result, e->result, sizeof(e->result));
+    if (result) memcpy(result, e->result, sizeof(e->result_own));
     return LKCUDA_OK;
 }
 
@@ -496,9 +498,9 @@ int lkcuda_derv(lkcuda_engine *e, double len, double *result) {
     if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_derv: theta_all not built");
     double df, ddf;
     derv_at(e, len, &df, &ddf);
-    memset(e->result, 0, sizeof(e->result));
+    memset(e->result, 0, sizeof(e->result_own));
     e->result[LKCUDA_R_DF] = df; e->result[LKCUDA_R_DDF] = ddf;
-    if (result) memcpy(result, e->result, sizeof(e->result));
+    if (result) memcpy(result, e->result, sizeof(e->result_own));
     return LKCUDA_OK;
 }
 
@@ -518,7 +520,7 @@ int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result) {
     finish_lnl(e, lh_all, e->theta_scale_num, e->theta_scale_sum);
     free(val0); free(lh_all);
     e->launches++;
-    if (result) memcpy(result, e->result, sizeof(e->result));
+    if (result) memcpy(result, e->result, sizeof(e->result_own));
     return LKCUDA_OK;
 }
 
@@ -562,10 +564,11 @@ int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, 
 
 int lkcuda_read_result(lkcuda_engine *e, double *result) {
     if (!e || !result) return LKCUDA_ERR_ARG;
-    memcpy(result, e->result, sizeof(e->result));
+    memcpy(result, e->result, sizeof(e->result_own));
     return LKCUDA_OK;
 }
 int lkcuda_result_device_ptr(lkcuda_engine *e, void **p) { if (!e || !p) return LKCUDA_ERR_ARG; *p = e->result; return LKCUDA_OK; }
+int lkcuda_set_result_buffer(lkcuda_engine *e, void *ptr) { if (!e) return LKCUDA_ERR_ARG; e->result = ptr ? (double*)ptr : e->result_own; return LKCUDA_OK; }
 
 int lkcuda_fetch_pattern_lh(lkcuda_engine *e, double *dst) {
     if (!e || !dst) return LKCUDA_ERR_ARG;
