@@ -97,6 +97,8 @@ struct lkcuda_engine {
     int ring_cap_ops[RING], ring_cap_child[RING]; cudaEvent_t ring_ev[RING]; bool ring_used[RING]; int ring_next;
     int red_blocks;                         /* capacity of d_red in blocks */
     size_t trav_smem_set;                   /* dynamic shared memory the traversal kernel is currently allowed */
+    double *d_inv_frags;                    /* fragment-ordered inverse eigenvectors of the protein MMA kernel */
+    size_t mma_smem_set; bool trav_disable_mma;   /* LKCUDA_NO_MMA=1: protein falls back to the generic kernel (test knob) */
     int trav_maxslots;                      /* LKCUDA_TRV_MAXSLOTS: cap on shared-memory slots (-1 = what fits) */
     bool theta_ready; int theta_dad; int theta_node;
     bool model_set, states_set, weights_set;

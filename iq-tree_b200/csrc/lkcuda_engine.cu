@@ -140,6 +140,8 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
         e->ring_cap_ops[i] = e->ring_cap_child[i] = 0; e->ring_ev[i] = NULL; e->ring_used[i] = false;
     }
     e->ring_next = 0; e->red_blocks = 0; e->trav_smem_set = 48 * 1024;
+    e->d_inv_frags = NULL; e->mma_smem_set = 48 * 1024;
+    { const char *r = getenv("LKCUDA_NO_MMA"); e->trav_disable_mma = r && atoi(r) != 0; }
     { const char *r = getenv("LKCUDA_TRV_MAXSLOTS"); e->trav_maxslots = r ? atoi(r) : -1; }
     e->theta_ready = false; e->theta_dad = e->theta_node = 0;
     e->model_set = e->states_set = e->weights_set = false;
@@ -154,7 +156,11 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     v.vec_stride = round_up(v.NP * v.B, 32);     /* 256-byte multiple */
     v.sc_stride = round_up(v.NP, 64);            /* 128-byte multiple */
     v.st_stride = round_up(v.NP, 128);
-    v.table_slot = round_up((long long)v.K * (v.S * v.S + 2) + (long long)(v.SU + 1) * v.B + v.SU + 4, 4);   /* + 2: padded matrices of the DNA traversal kernel */
+    v.table_slot = round_up((long long)v.K * (v.S * v.S + 2) + (long long)(v.SU + 1) * v.B + v.SU + 4, 4);
+    if (v.S == 20 && v.K <= 4) {    /* protein MMA kernel: K fragment-ordered matrices (3*3*2*32 doubles each) + tip table with 24-double rows */
+        long long need = (long long)v.K * 576 + (long long)(v.SU + 1) * v.K * 24;
+        if (need > v.table_slot) v.table_slot = round_up(need, 4);
+    }   /* + 2: padded matrices of the DNA traversal kernel */
 
     cudaDeviceProp prop;
     rc = cudaGetDeviceProperties(&prop, cfg->device);
@@ -212,7 +218,7 @@ int lkcuda_destroy(lkcuda_engine *e) {
     cudaFree(e->d_eval); cudaFree(e->d_evec); cudaFree(e->d_inv); cudaFree(e->d_rate); cudaFree(e->d_weight); cudaFree(e->d_eigen);
     cudaFree(e->d_tip); cudaFree(e->d_arena); cudaFree(e->d_scale); cudaFree(e->d_theta); cudaFree(e->d_theta_sc); cudaFree(e->d_theta_meta);
     cudaFree(e->d_plh); cudaFree(e->d_plhcat); cudaFree(e->d_red); cudaFree(e->d_counter); cudaFree(e->d_result);
-    cudaFree(e->d_newton_out); cudaFree(e->d_tables);
+    cudaFree(e->d_newton_out); cudaFree(e->d_tables); cudaFree(e->d_inv_frags);
     if (e->h_result) cudaFreeHost(e->h_result);
     if (e->h_newton_out) cudaFreeHost(e->h_newton_out);
     for (int i = 0; i < lkcuda_engine::RING; i++) {

@@ -18,7 +18,7 @@
  *                          level (gridDim.y = nodes of the level), pattern tiles staged in shared memory;
  *                          correctness fallback for shapes without a tuned kernel.
  */
-#include "lkcuda_common.cuh"
+#include "lkcuda_traverse.cuh"
 
 using namespace lkc;
 
@@ -120,54 +120,9 @@ __global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevCh
 #define TRV_R 4
 #define S4_MPAD 18  /* doubles per k of a staged 4x4 matrix: 16 + 2 keeps LDS.128 conflict-free across k */
 #define THR_HI 0x2FF00000   /* high word of 2^-256: |x| < 2^-256  <=>  (hi(x) & 0x7fffffff) < THR_HI */
-#define TRV_SLOT_PREV (-3)  /* child 1 is the result of the node executed immediately before: still in registers */
 /* doubles from the start of a staged tip table to the row of state st (K*4 doubles per row + the skew written by prep_tables_kernel) */
 #define TRV_TAB_ROW(st, K) ((st) * ((K) * 4) + ((st) >> 1) * 2)
 #define TRV_TAB_DOUBLES(SU, K) (((SU) + 1) * (K) * 4 + (((SU) >> 1) + 1) * 2)
-
-/* node descriptor, written by the host, streamed into the ring by the producer (64 bytes) */
-struct TravOp {
-    double *dst_lh; int16_t *dst_sc;    /* arena vector (partial_lh, scale_num) receiving the result */
-    const double *src0_lh, *src1_lh;    /* arena vectors of the children (NULL for a tip) */
-    int32_t src0, src1;                 /* child: vector (>= 0) or LKCUDA_TIP(taxon) */
-    int32_t slot0, slot1;               /* shared-memory slot holding the child (-1: read the arena vector; slot1 may be TRV_SLOT_PREV) */
-    int32_t dst_slot;                   /* slot the result is parked in (-1: not needed again in this launch or consumed by the next
-                                           node from registers, -2: needed but no slot was free: the consumer re-reads the arena) */
-    int32_t dst;
-    int32_t pad[2];
-};
-
-__device__ __forceinline__ d4 ld_coherent256(const double *p) { /* may have been written earlier by this very thread */
-    d4 r;
-    asm volatile("ld.global.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p) : "memory");
-    return r;
-}
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ bool mbar_try(uint64_t *bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-        "selp.u32 %0, 1, 0, p;\n"
-        "}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-    return ok != 0;
-}
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) { while (!mbar_try(bar, parity)) { } }
-__device__ __forceinline__ void mbar_wait_backoff(uint64_t *bar, uint32_t parity) { while (!mbar_try(bar, parity)) __nanosleep(256); }
-__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 :: "r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
 
 /* ring stage: descriptor (64) | child 0 block | child 1 block (cbs doubles each: padded matrices or tip lookup table) |
    child 0 tip states | child 1 tip states (spad bytes each: the tile's patterns of that taxon) */
@@ -559,10 +514,7 @@ static bool use_traverse(const DevView &v) { return v.S == 4 && v.K <= 32; }
  *     its arena vector, like a child that was computed by an earlier launch.
  * Multiplication commutes exactly in IEEE arithmetic, so the two children may be swapped freely.
  */
-struct TravNode { int op; int32_t src0, slot0, src1, slot1, dst_slot; double len0, len1; };
-struct TravSchedule { std::vector<TravNode> nodes; int nslots; };
-
-static int schedule_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops, int maxslots, TravSchedule &sch) {
+int lkc::schedule_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops, int maxslots, bool use_prev, TravSchedule &sch) {
     std::vector<int> producer(e->cfg.nvec, -1);
     for (int i = 0; i < nops; i++) {
         if (producer[ops[i].dst] >= 0) return fail(e, LKCUDA_ERR_ARG, "partial ops %d and %d write the same vector", producer[ops[i].dst], i);
@@ -616,7 +568,7 @@ static int schedule_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int
                 if (second < 0) { second = first; first = -1; }
                 if (second >= 0 && first == second) first = -1;      /* both children are the same vector */
                 /* pushed in reverse: `first` is expanded (and finished) before `second`, which ends right before i */
-                if (second >= 0 && !state[second]) { stack.push_back(second); last_kid[second] = nconsumer[second] == 1; }
+                if (second >= 0 && !state[second]) { stack.push_back(second); last_kid[second] = use_prev && nconsumer[second] == 1; }
                 if (first >= 0 && !state[first]) stack.push_back(first);
             } else {
                 stack.pop_back();
@@ -663,7 +615,7 @@ static int schedule_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int
     return LKCUDA_OK;
 }
 
-static int ring_acquire(lkcuda_engine *e, int nops, int nchild, int *slot_out) {
+int lkc::ring_acquire(lkcuda_engine *e, int nops, int nchild, int *slot_out) {
     int s = e->ring_next;
     e->ring_next = (s + 1) % lkcuda_engine::RING;
     if (!e->ring_ev[s]) LK_CUDA(e, cudaEventCreateWithFlags(&e->ring_ev[s], cudaEventDisableTiming));
@@ -689,7 +641,7 @@ static int ring_acquire(lkcuda_engine *e, int nops, int nchild, int *slot_out) {
 }
 
 /* algorithmic bytes of one node: internal children are read, the result written, scale_num likewise */
-static uint64_t op_bytes(const DevView &v, int ntip, int nint) {
+uint64_t lkc::op_bytes(const DevView &v, int ntip, int nint) {
     uint64_t b = (uint64_t)v.B * 8;
     return (uint64_t)v.NP * ((uint64_t)(nint + 1) * b + (uint64_t)ntip * 1 + (uint64_t)(nint + 1) * 2);
 }
@@ -744,7 +696,7 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
     int maxslots = (int)((227 * 1024 - fixed) / slot_bytes);
     if (e->trav_maxslots >= 0 && e->trav_maxslots < maxslots) maxslots = e->trav_maxslots;   /* test knob: forces the spill path */
     TravSchedule sch;
-    int rc = schedule_traverse(e, ops, nops, maxslots, sch);
+    int rc = schedule_traverse(e, ops, nops, maxslots, true, sch);
     if (rc) return rc;
     int slot;
     rc = ring_acquire(e, nops, 2 * nops, &slot);
@@ -823,6 +775,10 @@ int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t
     if (use_traverse(e->v)) {
         e->theta_ready = false;
         return launch_traverse(e, ops, nops);
+    }
+    if (use_traverse_mma(e)) {
+        e->theta_ready = false;
+        return launch_traverse_mma(e, ops, nops);
     }
     int slot;
     int rc = ring_acquire(e, nops, 2 * nops, &slot);

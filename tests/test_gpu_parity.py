@@ -112,3 +112,51 @@ def test_traversal_kernel_slot_spill(case, maxslots, cuda_lib, monkeypatch):
     gu.check_partials(t, g)
     gu.check_derivatives(t, g)
     t.close()
+
+
+@pytest.mark.parametrize("maxslots", [-1, 0, 1])
+@pytest.mark.parametrize("case", ["aa_lg_g4", "aa_lg4x"])
+def test_protein_mma_kernel(case, maxslots, cuda_lib, monkeypatch):
+    """protein partials on the FP64 tensor cores (mma.sync m8n8k4), with all / no / one shared-memory slot"""
+    monkeypatch.setenv("LKCUDA_TRV_MAXSLOTS", str(maxslots))
+    g = gu.Golden(case)
+    t = gu.build_tree(g, cuda_lib)
+    t.initializeAllPartialLh()
+    gu.check_likelihood(t, g)
+    gu.check_partials(t, g)
+    gu.check_derivatives(t, g)
+    gu.check_optimize(t, g, full=False)
+    t.close()
+
+
+def test_protein_generic_kernel_still_covered(cuda_lib, monkeypatch):
+    """LKCUDA_NO_MMA=1 sends 20-state data through the generic kernel (the path every other state count takes)"""
+    monkeypatch.setenv("LKCUDA_NO_MMA", "1")
+    g = gu.Golden("aa_lg_g4")
+    t = gu.build_tree(g, cuda_lib)
+    t.initializeAllPartialLh()
+    gu.check_likelihood(t, g)
+    gu.check_partials(t, g)
+    t.close()
+
+
+def test_protein_mma_matches_oracle_large(cuda_lib, oracle_lib):
+    """more patterns than one tile per SM, ragged last tile, unknown states"""
+    a = _synthetic(cuda_lib, 30, 64 * 148 + 37, 20, 4, 5, 23)
+    b = _synthetic(oracle_lib, 30, 64 * 148 + 37, 20, 4, 5, 23)
+    for t in (a, b):
+        t.initializeAllPartialLh()
+    la, pa = a.computeLikelihood(pattern_lh=True)
+    lb, pb = b.computeLikelihood(pattern_lh=True)
+    assert abs(la - lb) <= gu.LNL_RTOL * abs(lb)
+    gu.rel_close(pa, pb, gu.PTN_RTOL, "pattern_lh")
+    trav = a.getTraversal()
+    for (n1, n2) in trav[::7]:
+        va, ca = a.branchVector(int(n1), int(n2))
+        vb, cb = b.branchVector(int(n1), int(n2))
+        assert va == vb and ca == cb
+        if va >= 0 and ca:
+            (lha, sca), (lhb, scb) = a.fetchVector(va), b.fetchVector(vb)
+            assert np.array_equal(sca, scb)
+            gu.block_close(lha, lhb, 1e-9, "partial_lh")
+    a.close(); b.close()
