@@ -8,7 +8,7 @@
  * (phylotree.cpp:667-716, 718-760, 834-987): one arena for all partial-likelihood vectors, one for the
  * scale_num rows, plus _pattern_lh, _pattern_lh_cat, theta_all, ptn_freq, ptn_invar.
  */
-#include "lkcuda_common.cuh"
+#include "lkcuda_traverse.cuh"
 #include <stdarg.h>
 #include <stdlib.h>
 #include <new>
@@ -161,6 +161,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
         long long need = (long long)v.K * 576 + (long long)(v.SU + 1) * v.K * 24;
         if (need > v.table_slot) v.table_slot = round_up(need, 4);
     }   /* + 2: padded matrices of the DNA traversal kernel */
+    { long long need = mmak_table_slot(v); if (need > v.table_slot) v.table_slot = round_up(need, 4); }   /* codon / wide-block protein MMA kernel */
 
     cudaDeviceProp prop;
     rc = cudaGetDeviceProperties(&prop, cfg->device);

@@ -780,6 +780,10 @@ int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t
         e->theta_ready = false;
         return launch_traverse_mma(e, ops, nops);
     }
+    if (use_traverse_mmak(e)) {
+        e->theta_ready = false;
+        return launch_traverse_mmak(e, ops, nops);
+    }
     int slot;
     int rc = ring_acquire(e, nops, 2 * nops, &slot);
     if (rc) return rc;

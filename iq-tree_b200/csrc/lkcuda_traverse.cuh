@@ -71,5 +71,10 @@ uint64_t op_bytes(const DevView &v, int ntip, int nint);
 bool use_traverse_mma(const lkcuda_engine *e);
 int launch_traverse_mma(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops);
 
+/* implemented in lkcuda_partial_mmak.cu (codon, wide-block protein) */
+long long mmak_table_slot(const DevView &v);
+bool use_traverse_mmak(const lkcuda_engine *e);
+int launch_traverse_mmak(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops);
+
 }  // namespace lkc
 #endif

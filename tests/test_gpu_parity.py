@@ -160,3 +160,53 @@ def test_protein_mma_matches_oracle_large(cuda_lib, oracle_lib):
             assert np.array_equal(sca, scb)
             gu.block_close(lha, lhb, 1e-9, "partial_lh")
     a.close(); b.close()
+
+
+@pytest.mark.parametrize("maxslots", [-1, 0])
+@pytest.mark.parametrize("case", ["codon_gy", "codon_mg_g4", "aa_lg_c20_g4"])
+def test_codon_mixture_mma_kernel(case, maxslots, cuda_lib, monkeypatch):
+    """64-state codon and wide-block protein mixtures on the FP64 tensor cores, one (node, block) pair per ring stage"""
+    monkeypatch.setenv("LKCUDA_TRV_MAXSLOTS", str(maxslots))
+    g = gu.Golden(case)
+    t = gu.build_tree(g, cuda_lib)
+    t.initializeAllPartialLh()
+    gu.check_likelihood(t, g)
+    gu.check_partials(t, g)
+    gu.check_derivatives(t, g)
+    gu.check_optimize(t, g, full=False)
+    t.close()
+
+
+@pytest.mark.parametrize("case", ["codon_gy", "aa_lg_c20_g4"])
+def test_codon_mixture_generic_kernel_still_covered(case, cuda_lib, monkeypatch):
+    monkeypatch.setenv("LKCUDA_NO_MMA", "1")
+    g = gu.Golden(case)
+    t = gu.build_tree(g, cuda_lib)
+    t.initializeAllPartialLh()
+    gu.check_likelihood(t, g)
+    gu.check_partials(t, g)
+    t.close()
+
+
+@pytest.mark.parametrize("shape", [(12, 64 * 148 + 37, 64, 1, 64), (8, 1500, 64, 4, 64), (10, 3000, 20, 8, 23)])
+def test_mmak_matches_oracle_large(shape, cuda_lib, oracle_lib):
+    """more patterns than one tile per SM, ragged last tile, unknown states, several blocks per pattern"""
+    ntaxa, nptn, S, C, SU = shape
+    a = _synthetic(cuda_lib, ntaxa, nptn, S, C, 5, SU)
+    b = _synthetic(oracle_lib, ntaxa, nptn, S, C, 5, SU)
+    for t in (a, b):
+        t.initializeAllPartialLh()
+    la, pa = a.computeLikelihood(pattern_lh=True)
+    lb, pb = b.computeLikelihood(pattern_lh=True)
+    assert abs(la - lb) <= gu.LNL_RTOL * abs(lb)
+    gu.rel_close(pa, pb, gu.PTN_RTOL, "pattern_lh")
+    trav = a.getTraversal()
+    for (n1, n2) in trav[::3]:
+        va, ca = a.branchVector(int(n1), int(n2))
+        vb, cb = b.branchVector(int(n1), int(n2))
+        assert va == vb and ca == cb
+        if va >= 0 and ca:
+            (lha, sca), (lhb, scb) = a.fetchVector(va), b.fetchVector(vb)
+            assert np.array_equal(sca, scb)
+            gu.block_close(lha, lhb, 1e-7 if S >= 64 else 1e-9, "partial_lh")
+    a.close(); b.close()

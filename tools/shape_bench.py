@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Time full-tree lnL / df-ddf / optimizeAllBranches(1) of the CUDA engine on a synthetic shape (tuning tool, not the headline bench).
-usage: python tools/shape_bench.py NTAXA NPTN NSTATES NCAT [reps] [--oab]"""
+usage: python tools/shape_bench.py NTAXA NPTN NSTATES NCAT [reps] [--oab] [--mix=M]   (--mix: M-component profile mixture, family 2)"""
 import json
 import os
 import sys
@@ -18,6 +18,10 @@ def main():
     ntaxa, nptn, S, C = [int(x) for x in sys.argv[1:5]]
     reps = int(sys.argv[5]) if len(sys.argv) > 5 and not sys.argv[5].startswith("-") else 5
     oab = "--oab" in sys.argv
+    nmix = 1
+    for a in sys.argv:
+        if a.startswith("--mix="):
+            nmix = int(a[6:])
     SU = {4: 18, 20: 23}.get(S, S)
     names = ["t%d" % i for i in range(ntaxa)]
     nwk = mi.random_tree_newick(ntaxa, 1, names)
@@ -27,7 +31,12 @@ def main():
     t = iqtree_b200.PhyloTree(lib=lib)
     t.setAlignment(st, np.ones(nptn), names=names, seq_type=0 if S == 4 else (1 if S == 20 else 4), nstates=S, state_unknown=SU)
     t.readTreeString(nwk)
-    t.setModel(0, C, 1, mdl["eval"], mdl["evec"], mdl["inv_evec"], mdl["rates"], mdl["props"], None, mdl["state_freq"], 0.0)
+    if nmix > 1:
+        comps = [mi.random_reversible_inputs(S, 100 + m, ncat=C) for m in range(nmix)]
+        t.setModel(2, C, nmix, np.concatenate([c["eval"].ravel() for c in comps]), np.concatenate([c["evec"].ravel() for c in comps]),
+                   np.concatenate([c["inv_evec"].ravel() for c in comps]), mdl["rates"], mdl["props"], np.full(nmix, 1.0 / nmix), mdl["state_freq"], 0.0)
+    else:
+        t.setModel(0, C, 1, mdl["eval"], mdl["evec"], mdl["inv_evec"], mdl["rates"], mdl["props"], None, mdl["state_freq"], 0.0)
     t.setParams(0.1 / nptn if nptn >= 100000 else 1e-6, 100.0)
     t.initializeAllPartialLh()
     for _ in range(2):
@@ -45,13 +54,13 @@ def main():
     for _ in range(reps * 4):
         d = t.computeLikelihoodDerv(a, b, reset_theta=False)
     dd = (time.time() - t0) / (reps * 4)
-    out = {"shape": [ntaxa, nptn, S, C], "lnl": lnl, "lnl_ms": dt * 1e3, "updates_per_s": (ntaxa - 2) * nptn * C / dt,
+    out = {"shape": [ntaxa, nptn, S, C, nmix], "lnl": lnl, "lnl_ms": dt * 1e3, "updates_per_s": (ntaxa - 2) * nptn * C * nmix / dt,
            "derv_ms": dd * 1e3, "mem_gb": t.memoryBytes() / 1e9,
            "kernels": {k: {"n": v[0], "ms": v[2], "alg_gbps": (v[1] / 1e9) / (v[2] * 1e-3) if v[2] > 0 else None} for k, v in stats.items() if v[0]}}
     flops = 0
     for k_ in ("partial",):
         pass
-    out["eff_tflops_internal_internal_equiv"] = (ntaxa - 2) * nptn * C * (6 * S * S + S) / dt / 1e12
+    out["eff_tflops_internal_internal_equiv"] = (ntaxa - 2) * nptn * C * nmix * (6 * S * S + S) / dt / 1e12
     if oab:
         t.clearAllPartialLH(); t.computeLikelihood()
         t0 = time.time(); l1 = t.optimizeAllBranches(1); out["oab1_s"] = time.time() - t0; out["oab1_lnl"] = l1
