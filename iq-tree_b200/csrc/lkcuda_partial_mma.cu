@@ -42,6 +42,11 @@ using namespace lkc;
 #define MM_ROW 24               /* doubles per (state, k) row of a staged tip table */
 #define MM_THR_HI 0x2FF00000
 
+/* fragment slot (tile t, column j) -> state / eigen index, -1 = padding.  The 4 entries of the last tile sit in its EVEN slots
+   (slot 2q <-> entry 16 + q), so its odd slots form one all-padding k-step that every contraction skips: 5 k-steps x 3 tiles =
+   15 DMMAs per 20x20 product instead of 18. */
+__host__ __device__ __forceinline__ int mm_index_of(int t, int j) { return t < 2 ? 8 * t + j : ((j & 1) ? -1 : 16 + (j >> 1)); }
+
 /* ------------------------------------------------------------------ operand preparation ------------------------------------------------------------------ */
 
 /* per child slot c (one CTA): K fragment-ordered matrices evec*exp(eval*rate*len) [K][MM_FRAGS][32] followed, for a tip
@@ -62,21 +67,21 @@ __global__ void __launch_bounds__(256) prep_frag_kernel(DevView v, const DevChil
         __syncthreads();
         for (int idx = threadIdx.x; idx < MM_FRAG_DOUBLES; idx += blockDim.x) {
             int lane = idx & 31, f = idx >> 5, cc = f & 1, ct = (f >> 1) % MM_NT, rt = (f >> 1) / MM_NT;
-            int r = 8 * rt + (lane >> 2), col = 8 * ct + 2 * (lane & 3) + cc;
-            out[(long long)k * MM_FRAG_DOUBLES + idx] = (r < MM_S && col < MM_S) ? sh_m[r * MM_S + col] : 0.0;
+            int r = mm_index_of(rt, lane >> 2), col = mm_index_of(ct, 2 * (lane & 3) + cc);
+            out[(long long)k * MM_FRAG_DOUBLES + idx] = (r >= 0 && col >= 0) ? sh_m[r * MM_S + col] : 0.0;
         }
         if (LKCUDA_IS_TIP(ch.id)) {
             for (int idx = threadIdx.x; idx < (v.SU + 1) * MM_ROW; idx += blockDim.x) {
-                int st = idx / MM_ROW, x = idx - st * MM_ROW;
+                int st = idx / MM_ROW, pos = idx - st * MM_ROW, x = mm_index_of(pos >> 3, pos & 7);   /* rows in fragment-slot order */
                 double val = 0.0;
-                if (x < MM_S) {
+                if (x >= 0) {
                     if (st == v.SU) val = 1.0;
                     else {
                         const double *tip = v.tip + ((long long)st * v.E + v.blk_eigen[k]) * MM_S;
                         for (int j = 0; j < MM_S; j++) val += sh_m[x * MM_S + j] * tip[j];
                     }
                 }
-                tab[((long long)st * K + k) * MM_ROW + x] = val;
+                tab[((long long)st * K + k) * MM_ROW + pos] = val;
             }
         }
     }
@@ -88,8 +93,8 @@ __global__ void __launch_bounds__(256) prep_inv_frag_kernel(DevView v, double *o
     const double *inv = v.inv_evec + (long long)v.blk_eigen[k] * MM_S * MM_S;
     for (int idx = threadIdx.x; idx < MM_FRAG_DOUBLES; idx += blockDim.x) {
         int lane = idx & 31, f = idx >> 5, cc = f & 1, ct = (f >> 1) % MM_NT, rt = (f >> 1) / MM_NT;
-        int r = 8 * rt + (lane >> 2), col = 8 * ct + 2 * (lane & 3) + cc;
-        out[(long long)k * MM_FRAG_DOUBLES + idx] = (r < MM_S && col < MM_S) ? inv[r * MM_S + col] : 0.0;
+        int r = mm_index_of(rt, lane >> 2), col = mm_index_of(ct, 2 * (lane & 3) + cc);
+        out[(long long)k * MM_FRAG_DOUBLES + idx] = (r >= 0 && col >= 0) ? inv[r * MM_S + col] : 0.0;
     }
 }
 
@@ -107,7 +112,10 @@ __device__ __forceinline__ void contract(double (&acc)[MM_NT][2], const double (
 #pragma unroll
         for (int ct = 0; ct < MM_NT; ct++) {
 #pragma unroll
-            for (int cc = 0; cc < 2; cc++) dmma(acc[rt][0], acc[rt][1], X[ct][cc], frag[((rt * MM_NT + ct) * 2 + cc) * 32]);
+            for (int cc = 0; cc < 2; cc++) {
+                if (ct == MM_NT - 1 && cc == 1) continue;       /* all-padding k-step */
+                dmma(acc[rt][0], acc[rt][1], X[ct][cc], frag[((rt * MM_NT + ct) * 2 + cc) * 32]);
+            }
         }
     }
 }
@@ -121,10 +129,28 @@ __device__ __forceinline__ void st_stream128(double *p, double x, double y) {
     asm volatile("st.global.L1::no_allocate.v2.f64 [%0], {%1,%2};" :: "l"(p), "d"(x), "d"(y) : "memory");
 }
 
-/* slot layout (doubles): [k][ tile 0: TP*8 | tile 1: TP*8 | tile 2: TP*4 ] — lane (g, q) of the warp owning patterns
-   8w..8w+7 reads/writes 16 bytes at tile*TP*8 + pat*8 + 2q (tile 2: pat*4 + 2q, q < 2): conflict-free LDS/STS.128 */
-__device__ __forceinline__ int slot_off(int k, int tile, int pat, int q) {
-    return k * (MM_TP * MM_S) + (tile < 2 ? tile * (MM_TP * 8) + pat * 8 : 2 * (MM_TP * 8) + pat * 4) + 2 * q;
+/* lane (g, q) holds slots 2q, 2q + 1 of every tile: entries 8t + 2q, 8t + 2q + 1 for t < 2, entry 16 + q (and padding) for t = 2.
+   blk: start of block k of one pattern in an arena vector (20 doubles, reference layout) */
+__device__ __forceinline__ double2 mm_g_ld(const double *blk, int nt, int q) {
+    if (nt < 2) return ld_coherent128(blk + 8 * nt + 2 * q);
+    double r;
+    asm volatile("ld.global.L1::no_allocate.f64 %0, [%1];" : "=d"(r) : "l"(blk + 16 + q) : "memory");
+    return make_double2(r, 0.0);
+}
+__device__ __forceinline__ void mm_g_st(double *blk, int nt, int q, double x, double y) {
+    if (nt < 2) st_stream128(blk + 8 * nt + 2 * q, x, y);
+    else asm volatile("st.global.L1::no_allocate.f64 [%0], %1;" :: "l"(blk + 16 + q), "d"(x) : "memory");
+}
+/* slot layout (doubles): [k][ tile 0: TP*8 | tile 1: TP*8 | tile 2: TP*4 ] - conflict-free LDS/STS.128 (tile 2: .64) */
+__device__ __forceinline__ double2 mm_s_ld(const double *slot, int k, int nt, int pat, int q) {
+    const double *b = slot + k * (MM_TP * MM_S) + nt * (MM_TP * 8);
+    if (nt < 2) return *reinterpret_cast<const double2 *>(b + pat * 8 + 2 * q);
+    return make_double2(b[pat * 4 + q], 0.0);
+}
+__device__ __forceinline__ void mm_s_st(double *slot, int k, int nt, int pat, int q, double x, double y) {
+    double *b = slot + k * (MM_TP * MM_S) + nt * (MM_TP * 8);
+    if (nt < 2) *reinterpret_cast<double2 *>(b + pat * 8 + 2 * q) = make_double2(x, y);
+    else b[pat * 4 + q] = x;
 }
 
 /* ring stage: descriptor (64) | child 0 block | child 1 block (cbs doubles each: K fragment matrices or tip table) | states 0 | states 1 */
@@ -215,19 +241,11 @@ __global__ void __launch_bounds__(MM_THREADS, 1) traverse_mma20_kernel(DevView v
                     if (slot0 >= 0) {
                         const double *ps = sl + (size_t)slot0 * K * MM_TP * MM_S;
 #pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) {
-                            double2 a = make_double2(0.0, 0.0);
-                            if (nt < 2 || q < 2) a = *reinterpret_cast<const double2 *>(ps + slot_off(k, nt, pat, q));
-                            X[nt][0] = a.x; X[nt][1] = a.y;
-                        }
+                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_s_ld(ps, k, nt, pat, q); X[nt][0] = a.x; X[nt][1] = a.y; }
                     } else {
-                        const double *gp = g0 + p * B + k * MM_S + 2 * q;
+                        const double *gp = g0 + p * B + k * MM_S;
 #pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) {
-                            double2 a = make_double2(0.0, 0.0);
-                            if (nt < 2 || q < 2) a = ld_coherent128(gp + 8 * nt);
-                            X[nt][0] = a.x; X[nt][1] = a.y;
-                        }
+                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_g_ld(gp, nt, q); X[nt][0] = a.x; X[nt][1] = a.y; }
                     }
                     contract(t, X, blk0 + (size_t)k * MM_FRAG_DOUBLES + lane);
                 }
@@ -241,19 +259,11 @@ __global__ void __launch_bounds__(MM_THREADS, 1) traverse_mma20_kernel(DevView v
                     if (slot1 >= 0) {
                         const double *ps = sl + (size_t)slot1 * K * MM_TP * MM_S;
 #pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) {
-                            double2 a = make_double2(0.0, 0.0);
-                            if (nt < 2 || q < 2) a = *reinterpret_cast<const double2 *>(ps + slot_off(k, nt, pat, q));
-                            X[nt][0] = a.x; X[nt][1] = a.y;
-                        }
+                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_s_ld(ps, k, nt, pat, q); X[nt][0] = a.x; X[nt][1] = a.y; }
                     } else {
-                        const double *gp = g1 + p * B + k * MM_S + 2 * q;
+                        const double *gp = g1 + p * B + k * MM_S;
 #pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) {
-                            double2 a = make_double2(0.0, 0.0);
-                            if (nt < 2 || q < 2) a = ld_coherent128(gp + 8 * nt);
-                            X[nt][0] = a.x; X[nt][1] = a.y;
-                        }
+                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_g_ld(gp, nt, q); X[nt][0] = a.x; X[nt][1] = a.y; }
                     }
                     contract(u, X, blk1 + (size_t)k * MM_FRAG_DOUBLES + lane);
 #pragma unroll
@@ -262,15 +272,15 @@ __global__ void __launch_bounds__(MM_THREADS, 1) traverse_mma20_kernel(DevView v
                 /* ---- back to state space ---- */
                 double o[MM_NT][2];
                 contract(o, t, sINV + (size_t)k * MM_FRAG_DOUBLES + lane);
-                double *gd = dst_lh + p * B + k * MM_S + 2 * q;
+                double *gd = dst_lh + p * B + k * MM_S;
 #pragma unroll
                 for (int nt = 0; nt < MM_NT; nt++) {
-                    if (nt < 2 || q < 2) {
+                    {
                         const int h0 = __double2hiint(o[nt][0]) & 0x7fffffff, h1 = __double2hiint(o[nt][1]) & 0x7fffffff;
                         mx = max(mx, max(h0, h1));
                         nz |= h0 | h1 | __double2loint(o[nt][0]) | __double2loint(o[nt][1]);
-                        if (valid) st_stream128(gd + 8 * nt, o[nt][0], o[nt][1]);
-                        if (dslot) *reinterpret_cast<double2 *>(dslot + slot_off(k, nt, pat, q)) = make_double2(o[nt][0], o[nt][1]);
+                        if (valid) mm_g_st(gd, nt, q, o[nt][0], o[nt][1]);
+                        if (dslot) mm_s_st(dslot, k, nt, pat, q, o[nt][0], o[nt][1]);
                     }
                 }
             }
@@ -287,17 +297,15 @@ __global__ void __launch_bounds__(MM_THREADS, 1) traverse_mma20_kernel(DevView v
                 const bool rescale = tiny && !refill && (ignore_invar || v.invar[p] == 0.0);
                 if (refill || rescale) {
                     for (int k = 0; k < K; k++) {
-                        double *gd = dst_lh + p * B + k * MM_S + 2 * q;
-                        const double *tu = v.tip + ((long long)v.SU * v.E + v.blk_eigen[k]) * MM_S + 2 * q;
+                        double *gd = dst_lh + p * B + k * MM_S;
+                        const double *tu = v.tip + ((long long)v.SU * v.E + v.blk_eigen[k]) * MM_S;
 #pragma unroll
                         for (int nt = 0; nt < MM_NT; nt++) {
-                            if (nt < 2 || q < 2) {
-                                double2 a;
-                                if (refill) a = make_double2(tu[8 * nt], tu[8 * nt + 1]);
-                                else { a = ld_coherent128(gd + 8 * nt); a.x *= LK_THR_INV; a.y *= LK_THR_INV; }
-                                if (valid) st_stream128(gd + 8 * nt, a.x, a.y);
-                                if (dslot) *reinterpret_cast<double2 *>(dslot + slot_off(k, nt, pat, q)) = a;
-                            }
+                            double2 a;
+                            if (refill) a = nt < 2 ? make_double2(tu[8 * nt + 2 * q], tu[8 * nt + 2 * q + 1]) : make_double2(tu[16 + q], 0.0);
+                            else { a = dslot ? mm_s_ld(dslot, k, nt, pat, q) : mm_g_ld(gd, nt, q); a.x *= LK_THR_INV; a.y *= LK_THR_INV; }
+                            if (valid) mm_g_st(gd, nt, q, a.x, a.y);
+                            if (dslot) mm_s_st(dslot, k, nt, pat, q, a.x, a.y);
                         }
                     }
                     sc += refill ? 4 : 1;

@@ -23,11 +23,7 @@
 
 using namespace lkc;
 
-#define MK_CWARPS 8
-#define MK_CTHREADS (MK_CWARPS * 32)
-#define MK_THREADS (MK_CTHREADS + 32)
-#define MK_TP (MK_CWARPS * 8)   /* patterns per tile: one 8-pattern group per consumer warp */
-#define MK_STAGES 2
+#define MK_MAX_STAGES 8
 #define MK_THR_HI 0x2FF00000    /* high word of 2^-256 */
 
 template <int S> struct MkShape {
@@ -36,7 +32,17 @@ template <int S> struct MkShape {
     static constexpr int FRAGS = NT * NT * 2;           /* B fragments of one matrix: (rt, ct, c) */
     static constexpr int FRAG_DOUBLES = FRAGS * 32;
     static constexpr int LASTW = S - 8 * (NT - 1);      /* valid entries of the last tile (even) */
-    static constexpr int LASTQ = LASTW / 2;             /* lanes q < LASTQ hold valid entries of the last tile */
+    /* HALF (S % 8 == 4, protein): the 4 entries of the last tile sit in its EVEN slots (slot 2q <-> entry 8(NT-1) + q), so that its
+       odd slots form one all-padding k-step that every contraction skips: 5 x 3 = 15 DMMAs per 20x20 product instead of 18 */
+    static constexpr bool HALF = LASTW == 4;
+    /* fragment slot (tile t, column j) -> state / eigen index, -1 = padding */
+    __host__ __device__ static constexpr int index_of(int t, int j) {
+        return t < NT - 1 ? 8 * t + j : (HALF ? ((j & 1) ? -1 : 8 * t + (j >> 1)) : (j < LASTW ? 8 * t + j : -1));
+    }
+    /* consumer warps per CTA (one 8-pattern group each): register budget allows 16 for the 3-tile protein shape */
+    static constexpr int CW = S <= 24 ? 16 : 8;
+    static constexpr int TP = CW * 8;                   /* patterns per round of a CTA */
+    static constexpr int THREADS = CW * 32 + 32;        /* + the producer warp */
 };
 
 /* ------------------------------------------------------------------ operand preparation ------------------------------------------------------------------ */
@@ -57,14 +63,14 @@ __global__ void __launch_bounds__(256) prep_fragk_kernel(DevView v, const DevChi
     __syncthreads();
     for (int idx = threadIdx.x; idx < Sh::FRAG_DOUBLES; idx += blockDim.x) {
         int lane = idx & 31, f = idx >> 5, cc = f & 1, ct = (f >> 1) % Sh::NT, rt = (f >> 1) / Sh::NT;
-        int r = 8 * rt + (lane >> 2), col = 8 * ct + 2 * (lane & 3) + cc;
-        out[idx] = (r < S && col < S) ? sh_m[r * S + col] : 0.0;
+        int r = Sh::index_of(rt, lane >> 2), col = Sh::index_of(ct, 2 * (lane & 3) + cc);
+        out[idx] = (r >= 0 && col >= 0) ? sh_m[r * S + col] : 0.0;
     }
     if (!LKCUDA_IS_TIP(ch.id)) return;
     for (int idx = threadIdx.x; idx < (v.SU + 1) * Sh::ROW; idx += blockDim.x) {
-        int st = idx / Sh::ROW, x = idx - st * Sh::ROW;
+        int st = idx / Sh::ROW, pos = idx - st * Sh::ROW, x = Sh::index_of(pos >> 3, pos & 7);   /* rows are stored in fragment-slot order */
         double val = 0.0;
-        if (x < S) {
+        if (x >= 0) {
             if (st == v.SU) val = 1.0;
             else {
                 const double *tip = v.tip + ((long long)st * v.E + v.blk_eigen[k]) * S;
@@ -83,8 +89,8 @@ __global__ void __launch_bounds__(256) prep_inv_fragk_kernel(DevView v, double *
     const double *inv = v.inv_evec + (long long)eg * S * S;
     for (int idx = threadIdx.x; idx < Sh::FRAG_DOUBLES; idx += blockDim.x) {
         int lane = idx & 31, f = idx >> 5, cc = f & 1, ct = (f >> 1) % Sh::NT, rt = (f >> 1) / Sh::NT;
-        int r = 8 * rt + (lane >> 2), col = 8 * ct + 2 * (lane & 3) + cc;
-        out[(long long)eg * Sh::FRAG_DOUBLES + idx] = (r < S && col < S) ? inv[r * S + col] : 0.0;
+        int r = Sh::index_of(rt, lane >> 2), col = Sh::index_of(ct, 2 * (lane & 3) + cc);
+        out[(long long)eg * Sh::FRAG_DOUBLES + idx] = (r >= 0 && col >= 0) ? inv[r * S + col] : 0.0;
     }
 }
 
@@ -95,7 +101,7 @@ __device__ __forceinline__ void mk_dmma(double &d0, double &d1, double a, double
 }
 
 /* acc[rt][c] = sum over k-steps (ct, cc) of X[ct][cc] * frag[rt][ct][cc]   (frag: this lane's column of a fragment-ordered matrix) */
-template <int NT>
+template <int NT, bool HALF>
 __device__ __forceinline__ void mk_contract(double (&acc)[NT][2], const double (&X)[NT][2], const double *frag) {
 #pragma unroll
     for (int rt = 0; rt < NT; rt++) { acc[rt][0] = 0.0; acc[rt][1] = 0.0; }
@@ -104,6 +110,7 @@ __device__ __forceinline__ void mk_contract(double (&acc)[NT][2], const double (
     for (int ct = 0; ct < NT; ct++) {
 #pragma unroll
         for (int cc = 0; cc < 2; cc++) {
+            if (HALF && ct == NT - 1 && cc == 1) continue;      /* all-padding k-step */
 #pragma unroll
             for (int rt = 0; rt < NT; rt++) mk_dmma(acc[rt][0], acc[rt][1], X[ct][cc], frag[((rt * NT + ct) * 2 + cc) * 32]);
         }
@@ -119,63 +126,108 @@ __device__ __forceinline__ void mk_st128(double *p, double x, double y) {
     asm volatile("st.global.L1::no_allocate.v2.f64 [%0], {%1,%2};" :: "l"(p), "d"(x), "d"(y) : "memory");
 }
 
-/* slot layout (doubles): [k][ tiles 0..NT-2: TP*8 each | last tile: TP*LASTW ]; lane (g, q) moves 16 bytes */
-template <int S>
-__device__ __forceinline__ int mk_slot_off(int k, int tile, int pat, int q) {
+/* lane (g, q) <-> the entries of tile nt it holds in a C / A fragment: slots 2q, 2q + 1 (see MkShape::index_of) */
+template <int S> __device__ __forceinline__ bool mk_lane_has(int nt, int q) {
     typedef MkShape<S> Sh;
-    return k * (MK_TP * S) + (tile < Sh::NT - 1 ? tile * (MK_TP * 8) + pat * 8 : (Sh::NT - 1) * (MK_TP * 8) + pat * Sh::LASTW) + 2 * q;
+    return nt < Sh::NT - 1 || Sh::HALF || q < Sh::LASTW / 2;
+}
+__device__ __forceinline__ double mk_ld64(const double *p) {
+    double r;
+    asm volatile("ld.global.L1::no_allocate.f64 %0, [%1];" : "=d"(r) : "l"(p) : "memory");
+    return r;
+}
+/* blk: start of block k of one pattern in an arena vector (S doubles, reference layout) */
+template <int S> __device__ __forceinline__ double2 mk_g_ld(const double *blk, int nt, int q) {
+    typedef MkShape<S> Sh;
+    if (Sh::HALF && nt == Sh::NT - 1) return make_double2(mk_ld64(blk + 8 * nt + q), 0.0);
+    return mk_lane_has<S>(nt, q) ? mk_ld128(blk + 8 * nt + 2 * q) : make_double2(0.0, 0.0);
+}
+template <int S> __device__ __forceinline__ void mk_g_st(double *blk, int nt, int q, double x, double y) {
+    typedef MkShape<S> Sh;
+    if (Sh::HALF && nt == Sh::NT - 1) asm volatile("st.global.L1::no_allocate.f64 [%0], %1;" :: "l"(blk + 8 * nt + q), "d"(x) : "memory");
+    else if (mk_lane_has<S>(nt, q)) mk_st128(blk + 8 * nt + 2 * q, x, y);
+}
+/* shared-memory slot (doubles): [k][ tiles 0..NT-2: TP*8 each | last tile: TP*LASTW ] */
+template <int S> __device__ __forceinline__ double2 mk_s_ld(const double *slot, int k, int nt, int pat, int q) {
+    typedef MkShape<S> Sh;
+    const double *b = slot + k * (Sh::TP * S) + nt * (Sh::TP * 8);
+    if (nt < Sh::NT - 1) return *reinterpret_cast<const double2 *>(b + pat * 8 + 2 * q);
+    if (Sh::HALF) return make_double2(b[pat * 4 + q], 0.0);
+    return mk_lane_has<S>(nt, q) ? *reinterpret_cast<const double2 *>(b + pat * Sh::LASTW + 2 * q) : make_double2(0.0, 0.0);
+}
+template <int S> __device__ __forceinline__ void mk_s_st(double *slot, int k, int nt, int pat, int q, double x, double y) {
+    typedef MkShape<S> Sh;
+    double *b = slot + k * (Sh::TP * S) + nt * (Sh::TP * 8);
+    if (nt < Sh::NT - 1) *reinterpret_cast<double2 *>(b + pat * 8 + 2 * q) = make_double2(x, y);
+    else if (Sh::HALF) b[pat * 4 + q] = x;
+    else if (mk_lane_has<S>(nt, q)) *reinterpret_cast<double2 *>(b + pat * Sh::LASTW + 2 * q) = make_double2(x, y);
+}
+template <int S>
+__device__ __forceinline__ void mk_load_x(double (&X)[MkShape<S>::NT][2], const double *blk, int q) {
+#pragma unroll
+    for (int nt = 0; nt < MkShape<S>::NT; nt++) { const double2 a = mk_g_ld<S>(blk, nt, q); X[nt][0] = a.x; X[nt][1] = a.y; }
 }
 
 /* ring stage: descriptor (64) | child 0 block | child 1 block | [inverse eigenvectors of block k] (cbs doubles each) | states 0 | states 1 */
-__host__ __device__ __forceinline__ int mk_stage_bytes(int cbs, int nblk) { return 64 + nblk * cbs * 8 + 2 * (MK_TP + 16); }
+__host__ __device__ __forceinline__ int mk_stage_bytes(int cbs, int nblk, int tp) { return 64 + nblk * cbs * 8 + 2 * (tp + 16); }
 
-template <int S>
-__global__ void __launch_bounds__(MK_THREADS, 1) traverse_mmak_kernel(DevView v, const TravOp *__restrict__ ops, int nops, int nslots, int cbs,
-                                                                     int inv_streamed, const double *__restrict__ inv_frags, long long ntiles) {
+/* the 8-pattern groups [g0, g1) of CTA b: an even split of all groups over the grid (the last round of a CTA may run with idle warps) */
+__device__ __forceinline__ void mk_cta_groups(long long ngroups, long long &g0, long long &g1) {
+    g0 = ngroups * blockIdx.x / gridDim.x; g1 = ngroups * (blockIdx.x + 1) / gridDim.x;
+}
+
+/* KONE: one block per pattern (codon without rate heterogeneity): the previous node's result stays in registers
+   (TRV_SLOT_PREV) like in the DNA kernel.  Otherwise the next block's child entries are loaded while the current
+   block's contractions run. */
+template <int S, bool KONE>
+__global__ void __launch_bounds__(MkShape<S>::THREADS, 1) traverse_mmak_kernel(DevView v, const TravOp *__restrict__ ops, int nops, int nslots, int cbs,
+                                                                              int inv_streamed, int nstages, const double *__restrict__ inv_frags, long long ngroups) {
     typedef MkShape<S> Sh;
-    constexpr int NT = Sh::NT, FD = Sh::FRAG_DOUBLES, ROW = Sh::ROW, LASTQ = Sh::LASTQ;
+    constexpr int NT = Sh::NT, FD = Sh::FRAG_DOUBLES, ROW = Sh::ROW, CW = Sh::CW, TP = Sh::TP, THREADS = Sh::THREADS;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int K = v.K, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int K = KONE ? 1 : v.K, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nblk = inv_streamed ? 3 : 2;
-    const int stage_bytes = mk_stage_bytes(cbs, nblk);
-    unsigned char *ring = smem_raw;                                                         /* [MK_STAGES][stage_bytes] */
-    double *sINV = reinterpret_cast<double *>(ring + MK_STAGES * stage_bytes);              /* [FD] when resident (one eigensystem) */
+    const int stage_bytes = mk_stage_bytes(cbs, nblk, TP);
+    unsigned char *ring = smem_raw;                                                         /* [nstages][stage_bytes] */
+    double *sINV = reinterpret_cast<double *>(ring + nstages * stage_bytes);                /* [FD] when resident (one eigensystem) */
     double *sl = sINV + (inv_streamed ? 0 : FD);                                            /* [nslots][K*TP*S] */
-    int *ssc = reinterpret_cast<int *>(sl + (size_t)nslots * K * MK_TP * S);                /* [nslots + 1][TP]; the last row is scratch */
-    uint64_t *full = reinterpret_cast<uint64_t *>(ssc + (nslots + 1) * MK_TP), *empty = full + MK_STAGES;
-    if (!inv_streamed) for (int idx = tid; idx < FD; idx += MK_THREADS) sINV[idx] = inv_frags[idx];
+    int *ssc = reinterpret_cast<int *>(sl + (size_t)nslots * K * TP * S);                   /* [nslots + 1][TP] */
+    uint64_t *full = reinterpret_cast<uint64_t *>(ssc + (nslots + 1) * TP), *empty = full + MK_MAX_STAGES;
+    if (!inv_streamed) for (int idx = tid; idx < FD; idx += THREADS) sINV[idx] = inv_frags[idx];
     if (tid == 0) {
-        for (int s = 0; s < MK_STAGES; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], MK_CWARPS); }
+        for (int s = 0; s < nstages; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], CW); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     const int states_off = 64 + nblk * cbs * 8;
+    long long g0, g1;
+    mk_cta_groups(ngroups, g0, g1);
 
-    if (warp == MK_CWARPS) {
+    if (warp == CW) {
         /* ------------------------------ producer: one stage per (node, block k) ------------------------------ */
         if (lane == 0) {
-            uint32_t c = 0;
+            uint32_t s = 0, ph = 0;
             const uint32_t mat_bytes = (uint32_t)FD * 8, tab_bytes = (uint32_t)(v.SU + 1) * ROW * 8;
-            for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-                const long long p0 = tile * MK_TP;          /* MK_TP is a multiple of 16: bulk copies stay 16-byte aligned */
+            for (long long gr = g0; gr < g1; gr += CW) {
+                const long long p0 = gr * 8, a0 = p0 & ~15ll;               /* bulk copies start 16-byte aligned */
                 for (int i = 0; i < nops; i++) {
                     const int src0 = ops[i].src0, src1 = ops[i].src1;
                     const bool t0 = LKCUDA_IS_TIP(src0), t1 = LKCUDA_IS_TIP(src1);
                     const uint32_t b0 = t0 ? tab_bytes : mat_bytes, b1 = t1 ? tab_bytes : mat_bytes;
                     const double *s0 = v.tables + (long long)(2 * i) * v.table_slot, *s1 = s0 + v.table_slot;
-                    for (int k = 0; k < K; k++, c++) {
-                        const uint32_t s = c % MK_STAGES, ph = (c / MK_STAGES) & 1;
+                    for (int k = 0; k < K; k++) {
                         unsigned char *st = ring + s * stage_bytes;
-                        const double *g0 = t0 ? s0 + (long long)K * FD + (long long)k * (v.SU + 1) * ROW : s0 + (long long)k * FD;
-                        const double *g1 = t1 ? s1 + (long long)K * FD + (long long)k * (v.SU + 1) * ROW : s1 + (long long)k * FD;
+                        const double *q0 = t0 ? s0 + (long long)K * FD + (long long)k * (v.SU + 1) * ROW : s0 + (long long)k * FD;
+                        const double *q1 = t1 ? s1 + (long long)K * FD + (long long)k * (v.SU + 1) * ROW : s1 + (long long)k * FD;
                         mbar_wait_backoff(&empty[s], ph ^ 1);
-                        mbar_expect_tx(&full[s], 64 + b0 + b1 + (inv_streamed ? mat_bytes : 0) + (t0 ? MK_TP : 0) + (t1 ? MK_TP : 0));
+                        mbar_expect_tx(&full[s], 64 + b0 + b1 + (inv_streamed ? mat_bytes : 0) + (t0 ? TP + 16 : 0) + (t1 ? TP + 16 : 0));
                         bulk_g2s(st, ops + i, 64, &full[s]);
-                        bulk_g2s(st + 64, g0, b0, &full[s]);
-                        bulk_g2s(st + 64 + cbs * 8, g1, b1, &full[s]);
+                        bulk_g2s(st + 64, q0, b0, &full[s]);
+                        bulk_g2s(st + 64 + cbs * 8, q1, b1, &full[s]);
                         if (inv_streamed) bulk_g2s(st + 64 + 2 * cbs * 8, inv_frags + (long long)v.blk_eigen[k] * FD, mat_bytes, &full[s]);
-                        if (t0) bulk_g2s(st + states_off, tip_states(v, src0) + p0, MK_TP, &full[s]);
-                        if (t1) bulk_g2s(st + states_off + MK_TP + 16, tip_states(v, src1) + p0, MK_TP, &full[s]);
+                        if (t0) bulk_g2s(st + states_off, tip_states(v, src0) + a0, TP + 16, &full[s]);
+                        if (t1) bulk_g2s(st + states_off + TP + 16, tip_states(v, src1) + a0, TP + 16, &full[s]);
+                        if (++s == (uint32_t)nstages) { s = 0; ph ^= 1; }
                     }
                 }
             }
@@ -183,108 +235,109 @@ __global__ void __launch_bounds__(MK_THREADS, 1) traverse_mmak_kernel(DevView v,
         return;
     }
 
-    /* ------------------------------ consumers: warp w owns patterns 8w..8w+7 of the tile ------------------------------ */
+    /* ------------------------------ consumers: warp w owns group gr + w of the round ------------------------------ */
     const int g = lane >> 2, q = lane & 3, pat = warp * 8 + g;
     const bool zero_guard = (v.flags & LKCUDA_FLAG_ZERO_GUARD) != 0, ignore_invar = (v.flags & LKCUDA_FLAG_SCALE_IGNORES_INVAR) != 0;
     const int B = v.B;
-    uint32_t c = 0;
+    uint32_t s = 0, ph = 0;
 
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        long long p = tile * MK_TP + pat;
-        const bool valid = p < v.NP;
-        if (!valid) p = v.NP - 1;
+    for (long long gr = g0; gr < g1; gr += CW) {
+        long long p = (gr + warp) * 8 + g;
+        const bool valid = gr + warp < g1 && p < v.NP;
+        if (!valid) p = v.NP - 1;                   /* idle lanes shadow the last pattern; only their stores are masked */
+        const int sdelta = (int)((gr * 8) & 15);
+        double pv[NT][2];                           /* KONE: result of the previous node */
+        int pvsc = 0;
+#pragma unroll
+        for (int nt = 0; nt < NT; nt++) { pv[nt][0] = 0.0; pv[nt][1] = 0.0; }
+        if (gr + warp >= g1) {
+            /* this warp has no group in the CTA's last round: keep the ring protocol going, leave the tensor pipe to the others */
+            for (int n = nops * K; n > 0; n--) {
+                mbar_wait(&full[s], ph);
+                if (lane == 0) mbar_arrive(&empty[s]);
+                if (++s == (uint32_t)nstages) { s = 0; ph ^= 1; }
+            }
+            continue;
+        }
         for (int i = 0; i < nops; i++) {
             int sc = 0, mx = 0, nz = 0, dst_slot = -1;
             bool tip0 = false, tip1 = false;
             double *dst_lh = NULL, *dslot = NULL;
             int16_t *dst_sc = NULL;
-            for (int k = 0; k < K; k++, c++) {
-                const uint32_t s = c % MK_STAGES;
-                mbar_wait(&full[s], (c / MK_STAGES) & 1);
+            double X0[NT][2], X1[NT][2];
+            for (int k = 0; k < K; k++) {
+                mbar_wait(&full[s], ph);
                 const unsigned char *stage = ring + s * stage_bytes;
                 const TravOp *op = reinterpret_cast<const TravOp *>(stage);
                 const int src0 = op->src0, src1 = op->src1, slot0 = op->slot0, slot1 = op->slot1;
                 tip0 = LKCUDA_IS_TIP(src0); tip1 = LKCUDA_IS_TIP(src1);
+                const bool arena0 = !tip0 && slot0 < 0, arena1 = !tip1 && slot1 < 0 && slot1 != TRV_SLOT_PREV;
                 const double *blk0 = reinterpret_cast<const double *>(stage + 64), *blk1 = blk0 + cbs;
                 const double *invf = inv_streamed ? blk1 + cbs : sINV;
+                const double *gp0 = op->src0_lh + p * B, *gp1 = op->src1_lh + p * B;
                 if (k == 0) {
+                    if (arena0) mk_load_x<S>(X0, gp0, q);
+                    if (arena1) mk_load_x<S>(X1, gp1, q);
                     dst_slot = op->dst_slot; dst_lh = op->dst_lh; dst_sc = op->dst_sc;
-                    dslot = dst_slot >= 0 ? sl + (size_t)dst_slot * K * MK_TP * S : NULL;
-                    if (!tip0) sc += slot0 >= 0 ? ssc[slot0 * MK_TP + pat] : (int)vec_sc(v, src0)[p];
-                    if (!tip1) sc += slot1 >= 0 ? ssc[slot1 * MK_TP + pat] : (int)vec_sc(v, src1)[p];
+                    dslot = dst_slot >= 0 ? sl + (size_t)dst_slot * K * TP * S : NULL;
+                    if (!tip0) sc += slot0 >= 0 ? ssc[slot0 * TP + pat] : (int)vec_sc(v, src0)[p];
+                    if (!tip1) sc += slot1 == TRV_SLOT_PREV ? pvsc : (slot1 >= 0 ? ssc[slot1 * TP + pat] : (int)vec_sc(v, src1)[p]);
                 }
                 double t[NT][2];
                 /* ---- child 0 ---- */
                 if (tip0) {
-                    const int st0 = stage[states_off + pat];
+                    const int st0 = stage[states_off + sdelta + pat];
                     const double *row = blk0 + (size_t)st0 * ROW + 2 * q;
 #pragma unroll
                     for (int nt = 0; nt < NT; nt++) { const double2 a = *reinterpret_cast<const double2 *>(row + 8 * nt); t[nt][0] = a.x; t[nt][1] = a.y; }
                 } else {
-                    double X[NT][2];
                     if (slot0 >= 0) {
-                        const double *ps = sl + (size_t)slot0 * K * MK_TP * S;
+                        const double *ps = sl + (size_t)slot0 * K * TP * S;
 #pragma unroll
-                        for (int nt = 0; nt < NT; nt++) {
-                            double2 a = make_double2(0.0, 0.0);
-                            if (nt < NT - 1 || q < LASTQ) a = *reinterpret_cast<const double2 *>(ps + mk_slot_off<S>(k, nt, pat, q));
-                            X[nt][0] = a.x; X[nt][1] = a.y;
-                        }
-                    } else {
-                        const double *gp = op->src0_lh + p * B + k * S + 2 * q;
-#pragma unroll
-                        for (int nt = 0; nt < NT; nt++) {
-                            double2 a = make_double2(0.0, 0.0);
-                            if (nt < NT - 1 || q < LASTQ) a = mk_ld128(gp + 8 * nt);
-                            X[nt][0] = a.x; X[nt][1] = a.y;
-                        }
+                        for (int nt = 0; nt < NT; nt++) { const double2 a = mk_s_ld<S>(ps, k, nt, pat, q); X0[nt][0] = a.x; X0[nt][1] = a.y; }
                     }
-                    mk_contract<NT>(t, X, blk0 + lane);
+                    mk_contract<NT, Sh::HALF>(t, X0, blk0 + lane);
+                    if (!KONE && arena0 && k + 1 < K) mk_load_x<S>(X0, gp0 + (k + 1) * S, q);     /* next block, in flight during the other contractions */
                 }
                 /* ---- child 1 ---- */
                 if (tip1) {
-                    const int st1 = stage[states_off + MK_TP + 16 + pat];
+                    const int st1 = stage[states_off + TP + 16 + sdelta + pat];
                     const double *row = blk1 + (size_t)st1 * ROW + 2 * q;
 #pragma unroll
                     for (int nt = 0; nt < NT; nt++) { const double2 a = *reinterpret_cast<const double2 *>(row + 8 * nt); t[nt][0] *= a.x; t[nt][1] *= a.y; }
                 } else {
-                    double X[NT][2], u[NT][2];
-                    if (slot1 >= 0) {
-                        const double *ps = sl + (size_t)slot1 * K * MK_TP * S;
-#pragma unroll
-                        for (int nt = 0; nt < NT; nt++) {
-                            double2 a = make_double2(0.0, 0.0);
-                            if (nt < NT - 1 || q < LASTQ) a = *reinterpret_cast<const double2 *>(ps + mk_slot_off<S>(k, nt, pat, q));
-                            X[nt][0] = a.x; X[nt][1] = a.y;
-                        }
+                    double u[NT][2];
+                    if (KONE && slot1 == TRV_SLOT_PREV) {
+                        mk_contract<NT, Sh::HALF>(u, pv, blk1 + lane);
                     } else {
-                        const double *gp = op->src1_lh + p * B + k * S + 2 * q;
+                        if (slot1 >= 0) {
+                            const double *ps = sl + (size_t)slot1 * K * TP * S;
 #pragma unroll
-                        for (int nt = 0; nt < NT; nt++) {
-                            double2 a = make_double2(0.0, 0.0);
-                            if (nt < NT - 1 || q < LASTQ) a = mk_ld128(gp + 8 * nt);
-                            X[nt][0] = a.x; X[nt][1] = a.y;
+                        for (int nt = 0; nt < NT; nt++) { const double2 a = mk_s_ld<S>(ps, k, nt, pat, q); X1[nt][0] = a.x; X1[nt][1] = a.y; }
                         }
+                        mk_contract<NT, Sh::HALF>(u, X1, blk1 + lane);
+                        if (!KONE && arena1 && k + 1 < K) mk_load_x<S>(X1, gp1 + (k + 1) * S, q);
                     }
-                    mk_contract<NT>(u, X, blk1 + lane);
 #pragma unroll
                     for (int nt = 0; nt < NT; nt++) { t[nt][0] *= u[nt][0]; t[nt][1] *= u[nt][1]; }
                 }
                 /* ---- back to state space ---- */
                 double o[NT][2];
-                mk_contract<NT>(o, t, invf + lane);
+                mk_contract<NT, Sh::HALF>(o, t, invf + lane);
                 /* every operand of this (node, k) has been consumed: hand the stage back */
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&empty[s]);
-                double *gd = dst_lh + p * B + k * S + 2 * q;
+                if (++s == (uint32_t)nstages) { s = 0; ph ^= 1; }
+                double *gd = dst_lh + p * B + k * S;
 #pragma unroll
                 for (int nt = 0; nt < NT; nt++) {
-                    if (nt < NT - 1 || q < LASTQ) {
+                    if (KONE) { pv[nt][0] = o[nt][0]; pv[nt][1] = o[nt][1]; }
+                    if (mk_lane_has<S>(nt, q)) {
                         const int h0 = __double2hiint(o[nt][0]) & 0x7fffffff, h1 = __double2hiint(o[nt][1]) & 0x7fffffff;
                         mx = max(mx, max(h0, h1));
                         nz |= h0 | h1 | __double2loint(o[nt][0]) | __double2loint(o[nt][1]);
-                        if (valid) mk_st128(gd + 8 * nt, o[nt][0], o[nt][1]);
-                        if (dslot) *reinterpret_cast<double2 *>(dslot + mk_slot_off<S>(k, nt, pat, q)) = make_double2(o[nt][0], o[nt][1]);
+                        if (valid) mk_g_st<S>(gd, nt, q, o[nt][0], o[nt][1]);
+                        if (dslot) mk_s_st<S>(dslot, k, nt, pat, q, o[nt][0], o[nt][1]);
                     }
                 }
             }
@@ -298,29 +351,34 @@ __global__ void __launch_bounds__(MK_THREADS, 1) traverse_mmak_kernel(DevView v,
                 const bool rescale = tiny && !refill && (ignore_invar || v.invar[p] == 0.0);
                 if (refill || rescale) {
                     for (int k = 0; k < K; k++) {
-                        double *gd = dst_lh + p * B + k * S + 2 * q;
-                        const double *tu = v.tip + ((long long)v.SU * v.E + v.blk_eigen[k]) * S + 2 * q;
+                        double *gd = dst_lh + p * B + k * S;
+                        const double *tu = v.tip + ((long long)v.SU * v.E + v.blk_eigen[k]) * S;
 #pragma unroll
                         for (int nt = 0; nt < NT; nt++) {
-                            if (nt < NT - 1 || q < LASTQ) {
+                            if (mk_lane_has<S>(nt, q)) {
                                 double2 a;
-                                if (refill) a = make_double2(tu[8 * nt], tu[8 * nt + 1]);
-                                else {
-                                    if (dslot) a = *reinterpret_cast<double2 *>(dslot + mk_slot_off<S>(k, nt, pat, q));
-                                    else a = mk_ld128(gd + 8 * nt);
+                                if (refill) {
+                                    const int i0 = Sh::index_of(nt, 2 * q), i1 = Sh::index_of(nt, 2 * q + 1);
+                                    a = make_double2(i0 >= 0 ? tu[i0] : 0.0, i1 >= 0 ? tu[i1] : 0.0);
+                                } else {
+                                    if (KONE) a = make_double2(pv[nt][0], pv[nt][1]);
+                                    else if (dslot) a = mk_s_ld<S>(dslot, k, nt, pat, q);
+                                    else a = mk_g_ld<S>(gd, nt, q);
                                     a.x *= LK_THR_INV; a.y *= LK_THR_INV;
                                 }
-                                if (valid) mk_st128(gd + 8 * nt, a.x, a.y);
-                                if (dslot) *reinterpret_cast<double2 *>(dslot + mk_slot_off<S>(k, nt, pat, q)) = a;
+                                if (KONE) { pv[nt][0] = a.x; pv[nt][1] = a.y; }
+                                if (valid) mk_g_st<S>(gd, nt, q, a.x, a.y);
+                                if (dslot) mk_s_st<S>(dslot, k, nt, pat, q, a.x, a.y);
                             }
                         }
                     }
                     sc += refill ? 4 : 1;
                 }
             }
+            pvsc = sc;
             if (q == 0) {
                 if (valid) dst_sc[p] = (int16_t)sc;
-                if (dst_slot >= 0) ssc[dst_slot * MK_TP + pat] = sc;
+                if (dst_slot >= 0) ssc[dst_slot * TP + pat] = sc;
             }
             /* a parked result is read back by the other lanes of the quad (scale count) and, when spilled, from the arena */
             __syncwarp();
@@ -348,18 +406,23 @@ template <int S>
 static int launch_mmak(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops) {
     typedef MkShape<S> Sh;
     const DevView &v = e->v;
-    const int K = v.K;
+    const int K = v.K, TP = Sh::TP;
+    const bool kone = K == 1;
     const int cbs_mat = Sh::FRAG_DOUBLES, cbs_tab = (v.SU + 1) * Sh::ROW, cbs = cbs_mat > cbs_tab ? cbs_mat : cbs_tab;
     if (mmak_table_slot(v) > v.table_slot) return fail(e, LKCUDA_ERR_STATE, "table slot too small for the MMA layout");
     const int inv_streamed = v.E > 1 ? 1 : 0;
-    const size_t slot_bytes = (size_t)K * MK_TP * S * 8 + (size_t)MK_TP * 4;
-    const size_t fixed = (size_t)MK_STAGES * mk_stage_bytes(cbs, inv_streamed ? 3 : 2) + (inv_streamed ? 0 : (size_t)Sh::FRAG_DOUBLES * 8) +
-                         (size_t)MK_TP * 4 + 2 * MK_STAGES * 8 + 128;
+    const size_t stage_b = (size_t)mk_stage_bytes(cbs, inv_streamed ? 3 : 2, TP);
+    const size_t slot_bytes = (size_t)K * TP * S * 8 + (size_t)TP * 4;
+    const size_t other = (inv_streamed ? 0 : (size_t)Sh::FRAG_DOUBLES * 8) + (size_t)TP * 4 + 2 * MK_MAX_STAGES * 8 + 128;
+    /* ring depth: up to 8 stages (small protein stages), at least 2 (codon: 67 KB per stage) */
+    int nstages = MK_MAX_STAGES;
+    while (nstages > 2 && nstages * stage_b + other > 160 * 1024) nstages--;
+    const size_t fixed = nstages * stage_b + other;
     if (fixed > 227 * 1024) return fail(e, LKCUDA_ERR_ARG, "state space too large for the MMA traversal kernel");
     int maxslots = (int)((227 * 1024 - fixed) / slot_bytes);
     if (e->trav_maxslots >= 0 && e->trav_maxslots < maxslots) maxslots = e->trav_maxslots;
     TravSchedule sch;
-    int rc = schedule_traverse(e, ops, nops, maxslots, false, sch);
+    int rc = schedule_traverse(e, ops, nops, maxslots, kone, sch);
     if (rc) return rc;
     int slot;
     rc = ring_acquire(e, nops, 2 * nops, &slot);
@@ -402,16 +465,18 @@ static int launch_mmak(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops)
     rc = launch_end(e, KIND_PREP, 0, "prep_inv_fragk_kernel");
     if (rc) return rc;
 
-    const long long ntiles = (v.NP + MK_TP - 1) / MK_TP;
+    const long long ngroups = (v.NP + 7) / 8;
     const size_t sm = (size_t)sch.nslots * slot_bytes + fixed;
     if (sm > e->mma_smem_set) {
-        LK_CUDA(e, cudaFuncSetAttribute(traverse_mmak_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        LK_CUDA(e, cudaFuncSetAttribute(traverse_mmak_kernel<S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        LK_CUDA(e, cudaFuncSetAttribute(traverse_mmak_kernel<S, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         e->mma_smem_set = sm;
     }
-    long long grid = e->num_sms;
-    if (grid > ntiles) grid = ntiles;
+    long long grid = e->num_sms;      /* one persistent CTA per SM; every CTA gets at least one 8-pattern group */
+    if (grid > ngroups) grid = ngroups;
     launch_begin(e, KIND_PARTIAL);
-    traverse_mmak_kernel<S><<<(unsigned)grid, MK_THREADS, sm, e->stream>>>(e->v, d, nops, sch.nslots, cbs, inv_streamed, e->d_inv_frags, ntiles);
+    if (kone) traverse_mmak_kernel<S, true><<<(unsigned)grid, Sh::THREADS, sm, e->stream>>>(e->v, d, nops, sch.nslots, cbs, inv_streamed, nstages, e->d_inv_frags, ngroups);
+    else traverse_mmak_kernel<S, false><<<(unsigned)grid, Sh::THREADS, sm, e->stream>>>(e->v, d, nops, sch.nslots, cbs, inv_streamed, nstages, e->d_inv_frags, ngroups);
     return launch_end(e, KIND_PARTIAL, bytes, "traverse_mmak_kernel");
 }
 
