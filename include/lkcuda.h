@@ -117,6 +117,12 @@ int lkcuda_synchronize(lkcuda_engine *e);
 /* ---- inputs ---- */
 /* states[taxon][ptn], ptn < P+U: aln->at(ptn)[taxon] then model_factory->unobserved_ptns (phylokernel.h:237-244) */
 int lkcuda_set_tip_states(lkcuda_engine *e, const uint8_t *states);
+/* the same upload, pipelined: returns as soon as the copies are queued.  `states` must be page-locked host memory and stay valid
+   until the next synchronising call.  The matrix goes up in `nchunks` pattern ranges on a copy stream; the DNA traversal kernel
+   starts on the first range while the rest is still in flight (its producer warp polls a per-chunk counter), every other
+   kernel that reads tip states is ordered after the whole upload.  A state out of range is reported by the next
+   lkcuda_read_result / lkcuda_synchronize / lkcuda_fetch_* (LKCUDA_ERR_ARG), the engine computes on clamped states until then. */
+int lkcuda_set_tip_states_async(lkcuda_engine *e, const uint8_t *states, int32_t nchunks);
 /* PhyloTree::computePtnFreq / computePtnInvar outputs (phylotreesse.cpp:531-569): ptn_freq[P], ptn_invar[P+U] */
 int lkcuda_set_pattern_weights(lkcuda_engine *e, const double *ptn_freq, const double *ptn_invar);
 /* model->getEigenvalues/getEigenvectors/getInverseEigenvectors (model/modelsubst.h:248-258; mixtures
@@ -170,6 +176,10 @@ int lkcuda_set_result_buffer(lkcuda_engine *e, void *dev_ptr);
 /* ---- host-visible mirrors (buffers host code reads or writes) ---- */
 int lkcuda_fetch_pattern_lh(lkcuda_engine *e, double *pattern_lh /*[P]*/);
 int lkcuda_fetch_pattern_lh_cat(lkcuda_engine *e, double *pattern_lh_cat /*[P][K]*/);
+/* the tail of PhyloTree::computeLikelihood(double *pattern_lh) (phylotree.cpp:1055-1069) done on the device:
+   dst[p] = _pattern_lh[p] + max(scale_num(vec)[p], 0) * LOG_SCALING_THRESHOLD; vec < 0 (a tip end): plain copy.
+   _pattern_lh itself is left untouched. */
+int lkcuda_fetch_pattern_lh_corrected(lkcuda_engine *e, int32_t vec, double *pattern_lh /*[P]*/);
 int lkcuda_fetch_vector(lkcuda_engine *e, int32_t vec, double *partial_lh /*[(P+U)*K*S] or NULL*/,
                         int16_t *scale_num /*[P+U] or NULL*/);
 int lkcuda_store_vector(lkcuda_engine *e, int32_t vec, const double *partial_lh, const int16_t *scale_num);

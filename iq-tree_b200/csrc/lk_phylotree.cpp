@@ -667,18 +667,10 @@ double PhyloTree::computeLikelihood(double *pattern_lh) {   // phylotree.cpp:103
     double score = computeLikelihoodBranch(current_it, current_it_back->node);
     if (pattern_lh) {
         // _pattern_lh + max(scale_num,0)*LOG_SCALING_THRESHOLD of current_it (phylotree.cpp:1055-1069)
-        const double LOG_THR = std::log(1.0 / 115792089237316195423570985008687907853269984665640564039457584007913129639936.0);
         for (size_t d = 0; d < engines_.size(); d++) {
             int64_t b = shard_begin_[d] - ptn_begin_, np = shard_begin_[d + 1] - shard_begin_[d];
             if (!np) continue;
-            check(lkcuda_fetch_pattern_lh(engines_[d], pattern_lh + b), engines_[d], "lkcuda_fetch_pattern_lh");
-            if (current_it->vec >= 0) {
-                std::vector<int16_t> sc((size_t)(np + nunobs));
-                check(lkcuda_fetch_vector(engines_[d], current_it->vec, NULL, &sc[0]), engines_[d], "lkcuda_fetch_vector");
-                bool any = false;
-                for (int64_t i = 0; i < np; i++) if (sc[i] > 0) { any = true; break; }
-                if (any) for (int64_t i = 0; i < np; i++) pattern_lh[b + i] += std::max<int16_t>(sc[i], 0) * LOG_THR;
-            }
+            check(lkcuda_fetch_pattern_lh_corrected(engines_[d], current_it->vec, pattern_lh + b), engines_[d], "lkcuda_fetch_pattern_lh_corrected");
         }
     }
     return score;

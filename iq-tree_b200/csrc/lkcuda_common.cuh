@@ -85,7 +85,7 @@ struct lkcuda_engine {
     double *d_eval, *d_evec, *d_inv, *d_rate, *d_weight, *d_tip; int32_t *d_eigen;
     double *d_arena; int16_t *d_scale;
     double *d_theta; int16_t *d_theta_sc; double *d_theta_meta;
-    double *d_plh, *d_plhcat;
+    double *d_plh, *d_plhcat, *d_plh_out;   /* d_plh_out: scale-corrected copy of _pattern_lh on its way to the host (lazy) */
     double *d_red; unsigned int *d_counter; double *d_result;
     double *h_result;                       /* pinned */
     double *d_newton_out; double *h_newton_out;
@@ -100,6 +100,14 @@ struct lkcuda_engine {
     double *d_inv_frags;                    /* fragment-ordered inverse eigenvectors of the protein MMA kernel */
     size_t mma_smem_set; bool trav_disable_mma;   /* LKCUDA_NO_MMA=1: protein falls back to the generic kernel (test knob) */
     int trav_maxslots;                      /* LKCUDA_TRV_MAXSLOTS: cap on shared-memory slots (-1 = what fits) */
+    /* pipelined tip-state upload (lkcuda_set_tip_states_async): chunks of patterns go up on `cstream`; after each chunk the copy
+       engine bumps *d_upload_flag, which the DNA traversal kernel's producer warp polls before it stages a tile's tip states */
+    enum { UPLOAD_MAX_CHUNKS = 64 };
+    cudaStream_t cstream; cudaEvent_t ev_upload_done, ev_main_mark;
+    unsigned int *d_upload_flag, *h_upload_vals, *h_upload_bad;    /* device counter; pinned sources of its values; pinned validation result */
+    unsigned int upload_base; int upload_chunks; long long upload_chunk_pat;
+    bool upload_pending;        /* the main stream has not yet been ordered after the upload */
+    bool upload_check;          /* the range check of the uploaded states has not been examined yet */
     bool theta_ready; int theta_dad; int theta_node;
     bool model_set, states_set, weights_set;
     int num_sms;
@@ -133,6 +141,10 @@ inline bool valid_end(const lkcuda_engine *e, int32_t id) {
 
 /* implemented in lkcuda_partial.cu / lkcuda_reduce.cu */
 int ensure_tables(lkcuda_engine *e, long long slots);
+/* order the engine stream after a pipelined tip-state upload (every kernel that reads tip states without polling calls this) */
+int states_barrier(lkcuda_engine *e);
+/* after a synchronisation point: report a failed range check of an asynchronous upload */
+int upload_verdict(lkcuda_engine *e);
 
 }  // namespace lkc
 

@@ -66,6 +66,21 @@ void drain_events(lkcuda_engine *e) {
     e->pending.clear();
 }
 
+int states_barrier(lkcuda_engine *e) {
+    if (!e->upload_pending) return LKCUDA_OK;
+    LK_CUDA(e, cudaStreamWaitEvent(e->stream, e->ev_upload_done, 0));
+    e->upload_pending = false;
+    return LKCUDA_OK;
+}
+
+int upload_verdict(lkcuda_engine *e) {
+    if (!e->upload_check) return LKCUDA_OK;
+    LK_CUDA(e, cudaEventSynchronize(e->ev_upload_done));
+    e->upload_check = false;
+    if (e->h_upload_bad[0] != 0) { e->states_set = false; return fail(e, LKCUDA_ERR_ARG, "tip state out of range"); }
+    return LKCUDA_OK;
+}
+
 }  // namespace lkc
 
 using namespace lkc;
@@ -80,20 +95,29 @@ static cudaError_t dev_alloc(lkcuda_engine *e, T **p, size_t count) {
     return rc;
 }
 
-/* flags any state code above state_unknown (16 bytes per thread per step) */
-__global__ void validate_states_kernel(const uint8_t *states, long long total, long long stride, long long np, int su, unsigned int *flag) {
+/* flags any state code above state_unknown: gridDim.y = taxa (rows of the matrix), 16 bytes per thread and step, byte-wise SIMD compare */
+__global__ void validate_states_kernel(const uint8_t *states, int ntaxa, long long stride, long long np, int su, unsigned int *flag) {
+    const unsigned int su4 = (unsigned int)su * 0x01010101u;
     bool bad = false;
-    for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 16; i < total; i += (long long)gridDim.x * blockDim.x * 16) {
-        uint4 w = *reinterpret_cast<const uint4 *>(states + i);
-        unsigned int x[4] = {w.x, w.y, w.z, w.w};
-#pragma unroll
-        for (int k = 0; k < 16; k++) {
-            long long col = (i + k) % stride;
-            int b = (x[k >> 2] >> ((k & 3) * 8)) & 0xff;
-            if (col < np && b > su) bad = true;
+    for (int t = blockIdx.y; t < ntaxa; t += gridDim.y) {
+    const uint8_t *row = states + (long long)t * stride;
+    for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 16; i < np; i += (long long)gridDim.x * blockDim.x * 16) {
+        const uint4 w = *reinterpret_cast<const uint4 *>(row + i);
+        if (i + 16 <= np) bad |= (__vcmpgtu4(w.x, su4) | __vcmpgtu4(w.y, su4) | __vcmpgtu4(w.z, su4) | __vcmpgtu4(w.w, su4)) != 0u;
+        else {
+            const unsigned int x[4] = {w.x, w.y, w.z, w.w};
+            for (int k = 0; k < (int)(np - i); k++) bad |= (int)((x[k >> 2] >> ((k & 3) * 8)) & 0xff) > su;
         }
     }
+    }
     if (bad) atomicOr(flag, 1u);
+}
+
+static void launch_validate(lkcuda_engine *e, cudaStream_t s, unsigned int *flag) {
+    const DevView &v = e->v;
+    long long per_row = (v.NP / 16 + 255) / 256;
+    int gx = (int)(per_row < 1 ? 1 : (per_row > 64 ? 64 : per_row));
+    validate_states_kernel<<<dim3(gx, e->cfg.ntaxa < 65535 ? e->cfg.ntaxa : 65535), 256, 0, s>>>(e->d_states, e->cfg.ntaxa, v.st_stride, v.NP, e->cfg.state_unknown, flag);
 }
 
 extern "C" {
@@ -132,7 +156,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     e->d_states = NULL; e->d_freq = e->d_invar = NULL;
     e->d_eval = e->d_evec = e->d_inv = e->d_rate = e->d_weight = e->d_tip = NULL; e->d_eigen = NULL;
     e->d_arena = NULL; e->d_scale = NULL; e->d_theta = NULL; e->d_theta_sc = NULL; e->d_theta_meta = NULL;
-    e->d_plh = e->d_plhcat = NULL; e->d_red = NULL; e->d_counter = NULL; e->d_result = NULL; e->h_result = NULL;
+    e->d_plh = e->d_plhcat = e->d_plh_out = NULL; e->d_red = NULL; e->d_counter = NULL; e->d_result = NULL; e->h_result = NULL;
     e->d_newton_out = NULL; e->h_newton_out = NULL;
     e->d_tables = NULL; e->table_slots_cap = 0;
     for (int i = 0; i < lkcuda_engine::RING; i++) {
@@ -144,6 +168,8 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     { const char *r = getenv("LKCUDA_NO_MMA"); e->trav_disable_mma = r && atoi(r) != 0; }
     { const char *r = getenv("LKCUDA_TRV_MAXSLOTS"); e->trav_maxslots = r ? atoi(r) : -1; }
     e->theta_ready = false; e->theta_dad = e->theta_node = 0;
+    e->cstream = NULL; e->ev_upload_done = e->ev_main_mark = NULL; e->d_upload_flag = NULL; e->h_upload_vals = e->h_upload_bad = NULL;
+    e->upload_base = 0; e->upload_chunks = 0; e->upload_chunk_pat = 0; e->upload_pending = e->upload_check = false;
     e->model_set = e->states_set = e->weights_set = false;
     e->launches = e->bytes = 0; e->profiling = false; e->total_dev_bytes = 0;
     memset(e->kind_ms, 0, sizeof(e->kind_ms)); memset(e->kind_launches, 0, sizeof(e->kind_launches)); memset(e->kind_bytes, 0, sizeof(e->kind_bytes));
@@ -184,9 +210,16 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     ALLOC(e->d_plh, v.NP + 4); ALLOC(e->d_plhcat, (size_t)v.P * v.K + 4);
     ALLOC(e->d_red, (size_t)e->red_blocks * RED_SLOTS); ALLOC(e->d_counter, 4); ALLOC(e->d_result, LKCUDA_NRESULT);
     ALLOC(e->d_newton_out, 8);
+    ALLOC(e->d_upload_flag, 4);
 #undef ALLOC
     if (ok) { rc = cudaMallocHost((void **)&e->h_result, sizeof(double) * LKCUDA_NRESULT); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMallocHost((void **)&e->h_newton_out, sizeof(double) * 8); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMallocHost((void **)&e->h_upload_vals, sizeof(unsigned int) * (lkcuda_engine::UPLOAD_MAX_CHUNKS + 1)); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMallocHost((void **)&e->h_upload_bad, sizeof(unsigned int) * 4); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaStreamCreateWithFlags(&e->cstream, cudaStreamNonBlocking); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaEventCreateWithFlags(&e->ev_upload_done, cudaEventDisableTiming); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaEventCreateWithFlags(&e->ev_main_mark, cudaEventDisableTiming); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMemsetAsync(e->d_upload_flag, 0, 4 * sizeof(unsigned int), e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMemsetAsync(e->d_counter, 0, 4 * sizeof(unsigned int), e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMemsetAsync(e->d_result, 0, sizeof(double) * LKCUDA_NRESULT, e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMemsetAsync(e->d_theta_meta, 0, sizeof(double) * 8, e->stream); ok = rc == cudaSuccess; }
@@ -213,12 +246,18 @@ int lkcuda_destroy(lkcuda_engine *e) {
     if (!e) return LKCUDA_OK;
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
+    if (e->cstream) { cudaStreamSynchronize(e->cstream); cudaStreamDestroy(e->cstream); }
+    if (e->ev_upload_done) cudaEventDestroy(e->ev_upload_done);
+    if (e->ev_main_mark) cudaEventDestroy(e->ev_main_mark);
+    cudaFree(e->d_upload_flag);
+    if (e->h_upload_vals) cudaFreeHost(e->h_upload_vals);
+    if (e->h_upload_bad) cudaFreeHost(e->h_upload_bad);
     drain_events(e);
     for (size_t i = 0; i < e->event_pool.size(); i++) cudaEventDestroy(e->event_pool[i]);
     cudaFree(e->d_states); cudaFree(e->d_freq); cudaFree(e->d_invar);
     cudaFree(e->d_eval); cudaFree(e->d_evec); cudaFree(e->d_inv); cudaFree(e->d_rate); cudaFree(e->d_weight); cudaFree(e->d_eigen);
     cudaFree(e->d_tip); cudaFree(e->d_arena); cudaFree(e->d_scale); cudaFree(e->d_theta); cudaFree(e->d_theta_sc); cudaFree(e->d_theta_meta);
-    cudaFree(e->d_plh); cudaFree(e->d_plhcat); cudaFree(e->d_red); cudaFree(e->d_counter); cudaFree(e->d_result);
+    cudaFree(e->d_plh); cudaFree(e->d_plhcat); cudaFree(e->d_plh_out); cudaFree(e->d_red); cudaFree(e->d_counter); cudaFree(e->d_result);
     cudaFree(e->d_newton_out); cudaFree(e->d_tables); cudaFree(e->d_inv_frags);
     if (e->h_result) cudaFreeHost(e->h_result);
     if (e->h_newton_out) cudaFreeHost(e->h_newton_out);
@@ -253,6 +292,44 @@ int lkcuda_set_stream(lkcuda_engine *e, void *s) {
 int lkcuda_synchronize(lkcuda_engine *e) {
     LK_ENTER(e);
     LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    return upload_verdict(e);
+}
+
+int lkcuda_set_tip_states_async(lkcuda_engine *e, const uint8_t *states, int32_t nchunks) {
+    LK_ENTER(e);
+    if (!states) return fail(e, LKCUDA_ERR_ARG, "null tip states");
+    const DevView &v = e->v;
+    if (nchunks < 1) nchunks = 1;
+    if (nchunks > lkcuda_engine::UPLOAD_MAX_CHUNKS) nchunks = lkcuda_engine::UPLOAD_MAX_CHUNKS;
+    /* the previous upload's flag sources and verdict are reused: it must be over (it is, unless uploads are issued back to back) */
+    if (e->upload_check || e->upload_pending) LK_CUDA(e, cudaEventSynchronize(e->ev_upload_done));
+    if (e->upload_check) { int rc = upload_verdict(e); if (rc) return rc; }
+    /* chunk boundaries on 128-pattern multiples: whole 16-byte granules for the kernel's bulk copies */
+    long long chunk = ((v.NP + nchunks - 1) / nchunks + 127) / 128 * 128;
+    if (chunk < 128) chunk = 128;
+    nchunks = v.NP > 0 ? (int)((v.NP + chunk - 1) / chunk) : 0;
+    /* kernels already queued on the engine stream still read the old matrix */
+    LK_CUDA(e, cudaEventRecord(e->ev_main_mark, e->stream));
+    LK_CUDA(e, cudaStreamWaitEvent(e->cstream, e->ev_main_mark, 0));
+    e->upload_base += (unsigned int)e->upload_chunks;       /* the counter only ever grows: no reset to race with */
+    e->upload_chunks = nchunks; e->upload_chunk_pat = chunk;
+    for (int c = 0; c < nchunks; c++) {
+        const long long b = (long long)c * chunk, w = (b + chunk <= v.NP ? chunk : v.NP - b);
+        LK_CUDA(e, cudaMemcpy2DAsync(e->d_states + b, (size_t)v.st_stride, states + b, (size_t)v.NP, (size_t)w, (size_t)e->cfg.ntaxa,
+                                     cudaMemcpyHostToDevice, e->cstream));
+        e->h_upload_vals[c] = e->upload_base + (unsigned int)(c + 1);
+        LK_CUDA(e, cudaMemcpyAsync(e->d_upload_flag, &e->h_upload_vals[c], sizeof(unsigned int), cudaMemcpyHostToDevice, e->cstream));
+    }
+    if (v.NP > 0) {
+        LK_CUDA(e, cudaMemsetAsync(e->d_upload_flag + 1, 0, sizeof(unsigned int), e->cstream));
+        launch_validate(e, e->cstream, e->d_upload_flag + 1);
+        e->launches++; e->kind_launches[KIND_MISC]++;
+        LK_CUDA(e, cudaGetLastError());
+        LK_CUDA(e, cudaMemcpyAsync(e->h_upload_bad, e->d_upload_flag + 1, sizeof(unsigned int), cudaMemcpyDeviceToHost, e->cstream));
+    } else e->h_upload_bad[0] = 0;
+    LK_CUDA(e, cudaEventRecord(e->ev_upload_done, e->cstream));
+    e->upload_pending = true; e->upload_check = v.NP > 0;
+    e->states_set = true; e->theta_ready = false;
     return LKCUDA_OK;
 }
 
@@ -260,17 +337,18 @@ int lkcuda_set_tip_states(lkcuda_engine *e, const uint8_t *states) {
     LK_ENTER(e);
     if (!states) return fail(e, LKCUDA_ERR_ARG, "null tip states");
     const DevView &v = e->v;
+    if (e->upload_pending || e->upload_check) {      /* a pipelined upload is still in flight: finish it first */
+        LK_CUDA(e, cudaEventSynchronize(e->ev_upload_done));
+        e->upload_pending = false; e->upload_check = false;
+    }
     if (v.NP > 0) {
         /* `states` may be pinned (then this is one DMA at link speed) or pageable caller memory */
         LK_CUDA(e, cudaMemcpy2DAsync(e->d_states, (size_t)v.st_stride, states, (size_t)v.NP, (size_t)v.NP, (size_t)e->cfg.ntaxa,
                                      cudaMemcpyHostToDevice, e->stream));
         /* range check on the device: the matrix is 100 MB at the BASELINE shape, a host scan would cost more than the copy */
         LK_CUDA(e, cudaMemsetAsync(e->d_counter + 2, 0, sizeof(unsigned int), e->stream));
-        long long total = (long long)e->cfg.ntaxa * v.st_stride;
-        int grid = (int)((total / 16 + 255) / 256 < (long long)e->num_sms * 8 ? (total / 16 + 255) / 256 : (long long)e->num_sms * 8);
-        if (grid < 1) grid = 1;
         launch_begin(e, KIND_MISC);
-        validate_states_kernel<<<grid, 256, 0, e->stream>>>(e->d_states, total, v.st_stride, v.NP, e->cfg.state_unknown, e->d_counter + 2);
+        launch_validate(e, e->stream, e->d_counter + 2);
         int rc = launch_end(e, KIND_MISC, 0, "validate_states_kernel");
         if (rc) return rc;
         LK_CUDA(e, cudaMemcpyAsync(e->h_newton_out, e->d_counter + 2, sizeof(unsigned int), cudaMemcpyDeviceToHost, e->stream));
@@ -320,7 +398,7 @@ int lkcuda_read_result(lkcuda_engine *e, double *result) {
     LK_CUDA(e, cudaMemcpyAsync(e->h_result, e->v.result, sizeof(double) * LKCUDA_NRESULT, cudaMemcpyDeviceToHost, e->stream));
     LK_CUDA(e, cudaStreamSynchronize(e->stream));
     memcpy(result, e->h_result, sizeof(double) * LKCUDA_NRESULT);
-    return LKCUDA_OK;
+    return upload_verdict(e);
 }
 
 int lkcuda_result_device_ptr(lkcuda_engine *e, void **p) {
@@ -341,7 +419,7 @@ int lkcuda_fetch_pattern_lh(lkcuda_engine *e, double *dst) {
     if (!dst) return fail(e, LKCUDA_ERR_ARG, "null destination");
     if (e->v.P) LK_CUDA(e, cudaMemcpyAsync(dst, e->d_plh, (size_t)e->v.P * 8, cudaMemcpyDeviceToHost, e->stream));
     LK_CUDA(e, cudaStreamSynchronize(e->stream));
-    return LKCUDA_OK;
+    return upload_verdict(e);
 }
 
 int lkcuda_fetch_pattern_lh_cat(lkcuda_engine *e, double *dst) {

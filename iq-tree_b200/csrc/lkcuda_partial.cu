@@ -144,7 +144,8 @@ __device__ __forceinline__ void st_s16_if(bool pred, int16_t *p, int val) {
 }
 
 __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, const TravOp *__restrict__ ops, int nops, int upw, int nslots,
-                                                                     int cbs, int spad, int stage_shift, long long total_units, long long ntiles) {
+                                                                     int cbs, int spad, int stage_shift, int tile_stride, long long ntiles,
+                                                                     const unsigned int *upload_flag, unsigned int upload_base, long long upload_chunk_pat) {
     constexpr int R = TRV_R, CT = TRV_CTHREADS;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int K = v.K, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -171,9 +172,20 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
         /* ------------------------------ producer: one lane feeds the ring ------------------------------ */
         if (lane == 0) {
             uint32_t c = 0;
+            unsigned int seen = upload_base;
             const uint32_t mat_bytes = (uint32_t)K * S4_MPAD * 8, tab_bytes = (uint32_t)TRV_TAB_DOUBLES(v.SU, K) * 8;
             for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-                const long long p0 = tile * tile_pats, a0 = p0 & ~15ll;           /* bulk copies start 16-byte aligned */
+                const long long p0 = tile * tile_stride, a0 = p0 & ~15ll;         /* bulk copies start 16-byte aligned */
+                if (upload_flag) {
+                    /* pipelined upload (lkcuda_set_tip_states_async): wait until the copy engine has delivered this tile's pattern range */
+                    long long last = p0 + tile_stride - 1;
+                    if (last > v.NP - 1) last = v.NP - 1;
+                    const unsigned int need = upload_base + (unsigned int)(last / upload_chunk_pat) + 1u;
+                    while ((int)(seen - need) < 0) {
+                        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(upload_flag) : "memory");
+                        if ((int)(seen - need) < 0) __nanosleep(500);
+                    }
+                }
                 const uint32_t st_bytes = (uint32_t)((p0 - a0 + tile_pats + 15) & ~15ll);
                 for (int i = 0; i < nops; i++, c++) {
                     const uint32_t s = c & stage_mask, ph = (c >> stage_shift) & 1;
@@ -214,12 +226,12 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         long long p[R], off[R];     /* pattern, element offset of the unit inside a vector */
         bool valid[R];
-        const long long p0 = tile * tile_pats;
+        const long long p0 = tile * tile_stride;
         const int sdelta = (int)(p0 & 15);
 #pragma unroll
         for (int r = 0; r < R; r++) {
             p[r] = p0 + q[r];
-            valid[r] = lane_on && p[r] < v.NP;
+            valid[r] = lane_on && q[r] < tile_stride && p[r] < v.NP;
             if (!valid[r]) p[r] = v.NP - 1;          /* out-of-range units shadow the last pattern; only their stores are masked */
             off[r] = p[r] * B + k * 4;
         }
@@ -244,7 +256,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                 const double *tab = blk0 + k * 4;
 #pragma unroll
                 for (int r = 0; r < R; r++) {
-                    const int st = sst0[q[r]];
+                    const int st = min((int)sst0[q[r]], v.SU);      /* clamped: an out-of-range code is reported by the upload's range check */
                     const double2 *row = reinterpret_cast<const double2 *>(tab + TRV_TAB_ROW(st, K));
                     const double2 a = row[0], b = row[1];
                     t[r][0] = a.x; t[r][1] = a.y; t[r][2] = b.x; t[r][3] = b.y; sc[r] = 0;
@@ -278,7 +290,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                 const double *tab = blk1 + k * 4;
 #pragma unroll
                 for (int r = 0; r < R; r++) {
-                    const int st = sst1[q[r]];
+                    const int st = min((int)sst1[q[r]], v.SU);
                     const double2 *row = reinterpret_cast<const double2 *>(tab + TRV_TAB_ROW(st, K));
                     const double2 a = row[0], b = row[1];
                     t[r][0] *= a.x; t[r][1] *= a.y; t[r][2] *= b.x; t[r][3] *= b.y;
@@ -655,6 +667,8 @@ static int launch_ops(lkcuda_engine *e, int slot, int nops, int nchild_total, co
     LK_CUDA(e, cudaEventRecord(e->ring_ev[slot], e->stream));
     e->ring_used[slot] = true;
     if (v.NP == 0) return LKCUDA_OK;
+    rc = states_barrier(e);
+    if (rc) return rc;
 
     launch_begin(e, KIND_PREP);
     prep_tables_kernel<<<nchild_total, 256, (size_t)v.B * 8, e->stream>>>(e->v, e->d_child[slot], 0);
@@ -733,8 +747,13 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
     rc = launch_end(e, KIND_PREP, 0, "prep_tables_kernel");
     if (rc) return rc;
 
-    const long long total_units = v.NP * v.K, tile_units = (long long)TRV_CWARPS * upw * TRV_R;
-    const long long ntiles = (total_units + tile_units - 1) / tile_units;
+    /* a CTA takes tile_pats patterns per round at most; the rounds are evened out (tile_stride <= tile_pats patterns per tile, the
+       same for every tile) so that no CTA runs a whole round more than the others - it matters for small shards (8-GPU runs) */
+    long long ntiles = (v.NP + tile_pats - 1) / tile_pats;
+    const long long nrounds = (ntiles + e->num_sms - 1) / e->num_sms;
+    long long tile_stride = ((v.NP + nrounds * e->num_sms - 1) / (nrounds * e->num_sms) + 31) / 32 * 32;
+    if (tile_stride > tile_pats) tile_stride = tile_pats;
+    ntiles = (v.NP + tile_stride - 1) / tile_stride;
     const size_t sm = (size_t)sch.nslots * slot_bytes + fixed;
     if (sm > e->trav_smem_set) {
         LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
@@ -743,7 +762,10 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
     long long grid = e->num_sms;      /* one persistent CTA per SM (384 threads, shared memory bound) */
     if (grid > ntiles) grid = ntiles;
     launch_begin(e, KIND_PARTIAL);
-    traverse_s4_kernel<<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, total_units, ntiles);
+    /* with a pipelined upload in flight the kernel is NOT ordered after it: its producer polls the per-chunk counter instead */
+    const unsigned int *flag = e->upload_pending ? e->d_upload_flag : NULL;
+    traverse_s4_kernel<<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, (int)tile_stride, ntiles,
+                                                                      flag, e->upload_base, e->upload_chunk_pat > 0 ? e->upload_chunk_pat : 1);
     return launch_end(e, KIND_PARTIAL, bytes, "traverse_s4_kernel");
 }
 
@@ -830,6 +852,8 @@ int lkcuda_partial_multi(lkcuda_engine *e, int32_t dst, int32_t nchild, const in
     LK_CUDA(e, cudaEventRecord(e->ring_ev[slot], e->stream));
     e->ring_used[slot] = true;
     if (v.NP == 0) return LKCUDA_OK;
+    rc = states_barrier(e);
+    if (rc) return rc;
     launch_begin(e, KIND_PREP);
     prep_tables_kernel<<<nchild, 256, (size_t)v.B * 8, e->stream>>>(e->v, e->d_child[slot], 0);
     rc = launch_end(e, KIND_PREP, 0, "prep_tables_kernel");

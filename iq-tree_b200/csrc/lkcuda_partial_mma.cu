@@ -376,6 +376,8 @@ int launch_traverse_mma(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops
     LK_CUDA(e, cudaEventRecord(e->ring_ev[slot], e->stream));
     e->ring_used[slot] = true;
     if (v.NP == 0) return LKCUDA_OK;
+    rc = states_barrier(e);
+    if (rc) return rc;
 
     launch_begin(e, KIND_PREP);
     prep_frag_kernel<<<2 * nops, 256, 0, e->stream>>>(e->v, e->d_child[slot]);

@@ -454,6 +454,8 @@ static int launch_mmak(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops)
     LK_CUDA(e, cudaEventRecord(e->ring_ev[slot], e->stream));
     e->ring_used[slot] = true;
     if (v.NP == 0) return LKCUDA_OK;
+    rc = states_barrier(e);
+    if (rc) return rc;
 
     if ((size_t)S * S * 8 > 48 * 1024) return fail(e, LKCUDA_ERR_ARG, "state space too large for prep_fragk_kernel");
     launch_begin(e, KIND_PREP);

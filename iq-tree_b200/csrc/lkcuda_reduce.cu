@@ -363,6 +363,15 @@ __global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(DevView v, double 
     if (grid_reduce<4>(acc, sred, v.red, v.counter)) lnl_finish(v, acc, v.theta_meta[0]);
 }
 
+/* out[p] = _pattern_lh[p] + max(scale_num[p], 0) * LOG_SCALING_THRESHOLD (phylotree.cpp:1058-1064) */
+__global__ void __launch_bounds__(RED_THREADS) pattern_lh_corrected_kernel(DevView v, int vec, double *out) {
+    const int16_t *sc = vec_sc(v, vec);
+    for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < v.P; p += (long long)gridDim.x * blockDim.x) {
+        const int s = sc[p];
+        out[p] = s > 0 ? v.pattern_lh[p] + (double)s * LK_LOG_THR : v.pattern_lh[p];
+    }
+}
+
 /* lh_scale_factor of one vector = sum_p LOG_SCALING_THRESHOLD * ptn_freq[p] * scale_num[p] */
 __global__ void __launch_bounds__(RED_THREADS) scale_factor_kernel(DevView v, int vec) {
     __shared__ double sred[32];
@@ -417,6 +426,8 @@ int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     if (node < 0 || node >= e->cfg.nvec || !valid_end(e, dad) || dad == node) return fail(e, LKCUDA_ERR_ARG, "lkcuda_branch_lnl: bad vector / taxon id");
     int rc = check_ready(e, "lkcuda_branch_lnl");
     if (rc) return rc;
+    rc = states_barrier(e);
+    if (rc) return rc;
     const DevView &v = e->v;
     GroupShape gs = group_shape(v);
     const bool tip = LKCUDA_IS_TIP(dad);
@@ -453,6 +464,8 @@ int lkcuda_pattern_lh_cat(lkcuda_engine *e, int32_t dad, int32_t node, double le
     if (node < 0 || node >= e->cfg.nvec || !valid_end(e, dad) || dad == node) return fail(e, LKCUDA_ERR_ARG, "lkcuda_pattern_lh_cat: bad vector / taxon id");
     int rc = check_ready(e, "lkcuda_pattern_lh_cat");
     if (rc) return rc;
+    rc = states_barrier(e);
+    if (rc) return rc;
     const DevView &v = e->v;
     if (v.P == 0) return LKCUDA_OK;
     long long total = v.P * v.K;
@@ -466,6 +479,8 @@ int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node) {
     LK_ENTER(e);
     if (node < 0 || node >= e->cfg.nvec || !valid_end(e, dad) || dad == node) return fail(e, LKCUDA_ERR_ARG, "lkcuda_theta_build: bad vector / taxon id");
     int rc = check_ready(e, "lkcuda_theta_build");
+    if (rc) return rc;
+    rc = states_barrier(e);
     if (rc) return rc;
     const DevView &v = e->v;
     GroupShape gs = group_shape(v);
@@ -554,6 +569,27 @@ int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, 
     return fail(e, LKCUDA_ERR_STATE, "Maximum number of iterations exceeded in minimizeNewton");
 #undef FUNC_DERV
 #undef NR_RETURN
+}
+
+int lkcuda_fetch_pattern_lh_corrected(lkcuda_engine *e, int32_t vec, double *dst) {
+    LK_ENTER(e);
+    if (!dst || vec >= e->cfg.nvec) return fail(e, LKCUDA_ERR_ARG, "lkcuda_fetch_pattern_lh_corrected: bad argument");
+    if (vec < 0) return lkcuda_fetch_pattern_lh(e, dst);
+    const DevView &v = e->v;
+    if (v.P) {
+        if (!e->d_plh_out) {
+            LK_CUDA(e, cudaMalloc((void **)&e->d_plh_out, (size_t)v.P * 8));
+            e->total_dev_bytes += (uint64_t)v.P * 8;
+        }
+        int grid = red_grid(e, v.P, 1);
+        launch_begin(e, KIND_MISC);
+        pattern_lh_corrected_kernel<<<grid, RED_THREADS, 0, e->stream>>>(e->v, vec, e->d_plh_out);
+        int rc = launch_end(e, KIND_MISC, 0, "pattern_lh_corrected_kernel");
+        if (rc) return rc;
+        LK_CUDA(e, cudaMemcpyAsync(dst, e->d_plh_out, (size_t)v.P * 8, cudaMemcpyDeviceToHost, e->stream));
+    }
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    return upload_verdict(e);
 }
 
 int lkcuda_vector_scale_factor(lkcuda_engine *e, int32_t vec, double *out) {

@@ -40,6 +40,7 @@ LKCUDA_SYMBOLS = {
     "lkcuda_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "lkcuda_synchronize": (C.c_int, [C.c_void_p]),
     "lkcuda_set_tip_states": (C.c_int, [C.c_void_p, c_uint8_p]),
+    "lkcuda_set_tip_states_async": (C.c_int, [C.c_void_p, c_uint8_p, C.c_int32]),
     "lkcuda_set_pattern_weights": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
     "lkcuda_set_model": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p, c_int32_p, c_double_p, c_double_p, c_double_p]),
     "lkcuda_partial_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, c_int32_p, C.c_int32]),
@@ -55,6 +56,7 @@ LKCUDA_SYMBOLS = {
     "lkcuda_set_result_buffer": (C.c_int, [C.c_void_p, C.c_void_p]),
     "lkcuda_fetch_pattern_lh": (C.c_int, [C.c_void_p, c_double_p]),
     "lkcuda_fetch_pattern_lh_cat": (C.c_int, [C.c_void_p, c_double_p]),
+    "lkcuda_fetch_pattern_lh_corrected": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),
     "lkcuda_fetch_vector": (C.c_int, [C.c_void_p, C.c_int32, c_double_p, c_int16_p]),
     "lkcuda_store_vector": (C.c_int, [C.c_void_p, C.c_int32, c_double_p, c_int16_p]),
     "lkcuda_fetch_theta": (C.c_int, [C.c_void_p, c_double_p]),

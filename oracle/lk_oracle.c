@@ -118,6 +118,9 @@ int lkcuda_set_tip_states(lkcuda_engine *e, const uint8_t *states) {
     return LKCUDA_OK;
 }
 
+/* the oracle has no copy engine: the pipelined upload is the plain one */
+int lkcuda_set_tip_states_async(lkcuda_engine *e, const uint8_t *states, int32_t nchunks) { (void)nchunks; return lkcuda_set_tip_states(e, states); }
+
 int lkcuda_set_pattern_weights(lkcuda_engine *e, const double *ptn_freq, const double *ptn_invar) {
     if (!e || !ptn_freq || !ptn_invar) return LKCUDA_ERR_ARG;
     memcpy(e->ptn_freq, ptn_freq, (size_t)e->cfg.nptn * 8);
@@ -575,6 +578,18 @@ int lkcuda_fetch_pattern_lh(lkcuda_engine *e, double *dst) {
     memcpy(dst, e->pattern_lh, (size_t)e->cfg.nptn * 8);
     return LKCUDA_OK;
 }
+int lkcuda_fetch_pattern_lh_corrected(lkcuda_engine *e, int32_t vec, double *dst) {   /* phylotree.cpp:1055-1069 */
+    int rc = lkcuda_fetch_pattern_lh(e, dst);
+    if (rc || vec < 0) return rc;
+    if (vec >= e->cfg.nvec) return LKCUDA_ERR_ARG;
+    {
+        const int16_t *sc = e->scale + (size_t)vec * e->nptn_all;
+        int64_t p;
+        for (p = 0; p < e->cfg.nptn; p++) if (sc[p] > 0) dst[p] += (double)sc[p] * LOG_SCALING_THRESHOLD;
+    }
+    return LKCUDA_OK;
+}
+
 int lkcuda_fetch_pattern_lh_cat(lkcuda_engine *e, double *dst) {
     if (!e || !dst) return LKCUDA_ERR_ARG;
     memcpy(dst, e->pattern_lh_cat, (size_t)e->cfg.nptn * e->K * 8);

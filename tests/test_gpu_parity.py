@@ -210,3 +210,48 @@ def test_mmak_matches_oracle_large(shape, cuda_lib, oracle_lib):
             assert np.array_equal(sca, scb)
             gu.block_close(lha, lhb, 1e-7 if S >= 64 else 1e-9, "partial_lh")
     a.close(); b.close()
+
+
+@pytest.mark.parametrize("nchunks", [1, 3, 8])
+def test_pipelined_tip_state_upload(nchunks, cuda_lib, oracle_lib):
+    """lkcuda_set_tip_states_async: the traversal kernel polls the per-chunk counter; results equal the plain upload's and the
+    oracle's; a second upload with different states is picked up; an out-of-range state is reported at the next read-back"""
+    import ctypes
+    import torch
+    ntaxa, nptn = 40, 148 * 352 * 2 + 77
+    a = _synthetic(cuda_lib, ntaxa, nptn, 4, 4, 11, 18)
+    b = _synthetic(oracle_lib, ntaxa, nptn, 4, 4, 11, 18)
+    for t in (a, b):
+        t.initializeAllPartialLh()
+    l0 = a.computeLikelihood()
+    lb = b.computeLikelihood()
+    assert abs(l0 - lb) <= gu.LNL_RTOL * abs(lb)
+    names = ["t%d" % i for i in range(ntaxa)]
+    st = mi.simulate_patterns(mi.random_tree_newick(ntaxa, 11, names), names, nptn, 4, 11)
+    rng = np.random.default_rng(11)
+    st[rng.integers(0, ntaxa, nptn // 50), rng.integers(0, nptn, nptn // 50)] = 18
+    pinned = torch.from_numpy(np.ascontiguousarray(st)).pin_memory()
+    eng = a.engine(0)
+    u8p = ctypes.POINTER(ctypes.c_uint8)
+    for rep in range(3):
+        assert cuda_lib.lkcuda_set_tip_states_async(eng, ctypes.cast(pinned.data_ptr(), u8p), nchunks) == 0
+        a.clearAllPartialLH()
+        l1, p1 = a.computeLikelihood(pattern_lh=True)
+        assert l1 == l0
+    # different data: every state rotated
+    st2 = np.where(st < 4, (st + 1) % 4, st).astype(np.uint8)
+    pinned2 = torch.from_numpy(np.ascontiguousarray(st2)).pin_memory()
+    assert cuda_lib.lkcuda_set_tip_states_async(eng, ctypes.cast(pinned2.data_ptr(), u8p), nchunks) == 0
+    a.clearAllPartialLH()
+    l2 = a.computeLikelihood()
+    assert l2 != l0
+    assert cuda_lib.lkcuda_set_tip_states(eng, ctypes.cast(pinned2.data_ptr(), u8p)) == 0
+    a.clearAllPartialLH()
+    assert a.computeLikelihood() == l2
+    # range check of the pipelined upload
+    bad = st.copy(); bad[3, nptn - 5] = 19
+    pinned3 = torch.from_numpy(np.ascontiguousarray(bad)).pin_memory()
+    assert cuda_lib.lkcuda_set_tip_states_async(eng, ctypes.cast(pinned3.data_ptr(), u8p), nchunks) == 0
+    assert cuda_lib.lkcuda_synchronize(eng) == 1      # LKCUDA_ERR_ARG
+    assert b"out of range" in cuda_lib.lkcuda_last_error(eng)
+    a.close(); b.close()
