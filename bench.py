@@ -37,7 +37,7 @@ NTAXA = int(os.environ.get("LK_BENCH_TAXA", 100))
 NPTN = int(os.environ.get("LK_BENCH_PATTERNS", 1000000))
 NCAT = 4
 SEED = 1
-UPLOAD_CHUNKS = int(os.environ.get("LK_BENCH_UPLOAD_CHUNKS", 8))
+UPLOAD_CHUNKS = int(os.environ.get("LK_BENCH_UPLOAD_CHUNKS", 16))
 CPU_SAMPLE_SITES = int(os.environ.get("LK_BENCH_CPU_SITES", 200000))
 WORKLOAD = "synthetic DNA %d taxa x %d patterns, GTR+G4 (BASELINE configs[1])" % (NTAXA, NPTN)
 

@@ -20,14 +20,17 @@
 using namespace lkc;
 
 #define RED_THREADS 256
+#define RED_BLOCKS_PER_SM 3     /* __launch_bounds__(256, 4): <= 64 registers, 1024 threads per SM with 4 x 32-byte loads each in flight */
 
 struct GroupShape { int G, gshift, vec; };
 
 static GroupShape group_shape(const DevView &v) {
     GroupShape s;
     if (v.B % 4 != 0) { s.G = 1; s.gshift = 0; s.vec = 0; return s; }
+    /* lanes per pattern: a power of two dividing the sector count that leaves every lane at least 4 sectors (4 independent
+       32-byte loads in flight per lane); DNA+G4 (4 sectors): one lane per pattern, no shuffles at all */
     int nsec = v.B / 4, g = 1, sh = 0;
-    while (g < 32 && nsec % (g * 2) == 0) { g *= 2; sh++; }
+    while (g < 32 && nsec % (g * 2) == 0 && nsec / (g * 2) >= 4) { g *= 2; sh++; }
     s.G = g; s.gshift = sh; s.vec = 1;
     return s;
 }
@@ -36,7 +39,7 @@ static int red_grid(const lkcuda_engine *e, long long NP, int G) {
     (void)G;
     long long per_block = RED_THREADS;      /* a warp takes 32 patterns per outer step whatever G is */
     long long need = (NP + per_block - 1) / per_block;
-    long long cap = (long long)e->num_sms * 8;
+    long long cap = (long long)e->num_sms * RED_BLOCKS_PER_SM;      /* one resident wave, grid-stride inside */
     if (cap > e->red_blocks) cap = e->red_blocks;
     if (need < 1) need = 1;
     return (int)(need < cap ? need : cap);
@@ -79,18 +82,20 @@ __device__ __forceinline__ void group_sum(double (&a)[N], int G) {
 
 /* log, NaN repair, pattern_lh, frequency weighting, +ASC accumulation: the common tail of branch lnL and
    lnL-from-buffer (phylokernel.h:828-866, 895-900, 1009-1016). acc[0..3] = {sum freq*log, scale sum, prob_const, repaired} */
-__device__ __forceinline__ void lnl_tail(const DevView &v, long long p, double lh, int sc, double (&acc)[4]) {
+__device__ __forceinline__ void lnl_tail_vals(const DevView &v, long long p, double lh, int sc, double inv, double f, double (&acc)[4]) {
     if (p < v.P) {
-        double l = log(fabs(lh + v.invar[p]));
+        double l = log(fabs(lh + inv));
         if (isnan(l) || isinf(l)) { l = LK_LOG_THR * 4.0; acc[3] += 1.0; }
         v.pattern_lh[p] = l;
-        double f = v.freq[p];
         acc[0] += l * f;
         if (sc) acc[1] += LK_LOG_THR * f * (double)sc;
     } else {
         if (sc >= 1) lh *= LK_THR;
-        acc[2] += lh + v.invar[p];
+        acc[2] += lh + inv;
     }
+}
+__device__ __forceinline__ void lnl_tail(const DevView &v, long long p, double lh, int sc, double (&acc)[4]) {
+    lnl_tail_vals(v, p, lh, sc, v.invar[p], p < v.P ? v.freq[p] : 0.0, acc);
 }
 
 __device__ __forceinline__ void lnl_finish(const DevView &v, const double (&acc)[4], double scale_sum) {
@@ -104,7 +109,7 @@ __device__ __forceinline__ void lnl_finish(const DevView &v, const double (&acc)
 /* ------------------------------------------------------------------ branch lnL ------------------------------------------------------------------ */
 
 template <bool TIP, bool VEC>
-__global__ void __launch_bounds__(RED_THREADS) branch_kernel(DevView v, int dad, int node, double len, int gshift, int use_tab) {
+__global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) branch_kernel(DevView v, int dad, int node, double len, int gshift, int use_tab) {
     extern __shared__ __align__(32) double sh[];
     __shared__ double sred[4 * 32];
     double *val = sh, *tipB = sh + ((v.B + 3) & ~3);
@@ -135,18 +140,30 @@ __global__ void __launch_bounds__(RED_THREADS) branch_kernel(DevView v, int dad,
                 const int state = TIP ? st[p] : 0;
                 if (VEC) {
                     const double *a = lh_node + p * v.B;
-                    for (int q = g; q < nsec; q += G) {
-                        d4 x = ld_stream256(a + 4 * q);
-                        if (TIP) {
-                            double t0, t1, t2, t3;
-                            if (use_tab) { const double *t = tipB + state * v.B + 4 * q; t0 = t[0]; t1 = t[1]; t2 = t[2]; t3 = t[3]; }
-                            else { t0 = tip_elem(v, state, 4 * q, val); t1 = tip_elem(v, state, 4 * q + 1, val); t2 = tip_elem(v, state, 4 * q + 2, val); t3 = tip_elem(v, state, 4 * q + 3, val); }
-                            s0 = fma(t0, x.x, s0); s0 = fma(t1, x.y, s0); s0 = fma(t2, x.z, s0); s0 = fma(t3, x.w, s0);
-                        } else {
-                            d4 y = ld_stream256(lh_dad + p * v.B + 4 * q);
-                            const double *w = val + 4 * q;
-                            s0 = fma(w[0] * x.x, y.x, s0); s0 = fma(w[1] * x.y, y.y, s0);
-                            s0 = fma(w[2] * x.z, y.z, s0); s0 = fma(w[3] * x.w, y.w, s0);
+                    constexpr int NB = TIP ? 4 : 2;     /* sectors per vector in flight before the first is used */
+                    for (int q0 = g; q0 < nsec; q0 += NB * G) {
+                        d4 xs[NB], ys[NB];
+#pragma unroll
+                        for (int u = 0; u < NB; u++) if (q0 + u * G < nsec) {
+                            xs[u] = ld_stream256(a + 4 * (q0 + u * G));
+                            if (!TIP) ys[u] = ld_stream256(lh_dad + p * v.B + 4 * (q0 + u * G));
+                        }
+#pragma unroll
+                        for (int u = 0; u < NB; u++) {
+                            const int q = q0 + u * G;
+                            if (q >= nsec) break;
+                            const d4 x = xs[u];
+                            if (TIP) {
+                                double t0, t1, t2, t3;
+                                if (use_tab) { const double *t = tipB + state * v.B + 4 * q; t0 = t[0]; t1 = t[1]; t2 = t[2]; t3 = t[3]; }
+                                else { t0 = tip_elem(v, state, 4 * q, val); t1 = tip_elem(v, state, 4 * q + 1, val); t2 = tip_elem(v, state, 4 * q + 2, val); t3 = tip_elem(v, state, 4 * q + 3, val); }
+                                s0 = fma(t0, x.x, s0); s0 = fma(t1, x.y, s0); s0 = fma(t2, x.z, s0); s0 = fma(t3, x.w, s0);
+                            } else {
+                                const d4 y = ys[u];
+                                const double *w = val + 4 * q;
+                                s0 = fma(w[0] * x.x, y.x, s0); s0 = fma(w[1] * x.y, y.y, s0);
+                                s0 = fma(w[2] * x.z, y.z, s0); s0 = fma(w[3] * x.w, y.w, s0);
+                            }
                         }
                     }
                 } else {
@@ -166,6 +183,55 @@ __global__ void __launch_bounds__(RED_THREADS) branch_kernel(DevView v, int dad,
             int sc = sc_node[p] + (TIP ? 0 : sc_dad[p]);
             lnl_tail(v, p, mine, sc, acc);
         }
+    }
+    if (grid_reduce<4>(acc, sred, v.red, v.counter)) lnl_finish(v, acc, acc[1]);
+}
+
+/* DNA + 4 categories, tip end (the root branch of every full-tree lnL): one lane per pattern, next pattern's operands requested
+   before the current one is reduced.  tipB rows are 18 doubles apart: lanes with different states read different banks. */
+#define B16_TIPROW 18
+__global__ void __launch_bounds__(RED_THREADS, 2) branch_tip_b16_kernel(DevView v, int dad, int node, double len) {
+    __shared__ __align__(32) double val[16];
+    __shared__ __align__(32) double tipB[32 * B16_TIPROW];
+    __shared__ double sred[4 * 32];
+    build_val(v, len, val, NULL, NULL);
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < (v.SU + 1) * 16; idx += blockDim.x) {
+        const int st = idx >> 4, j = idx & 15;
+        tipB[st * B16_TIPROW + j] = val[j] * v.tip[((long long)st * v.E + v.blk_eigen[j >> 2]) * 4 + (j & 3)];
+    }
+    __syncthreads();
+    const double *lh_node = vec_lh(v, node);
+    const int16_t *sc_node = vec_sc(v, node);
+    const uint8_t *st = tip_states(v, dad);
+    const long long nthr = (long long)gridDim.x * blockDim.x;
+    long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    d4 n[4]; double ninv = 0.0, nf = 0.0; int nst = 0, nsc = 0;
+    if (p < v.NP) {
+#pragma unroll
+        for (int u = 0; u < 4; u++) n[u] = ld_stream256(lh_node + p * 16 + 4 * u);
+        ninv = v.invar[p]; nf = p < v.P ? v.freq[p] : 0.0; nst = st[p]; nsc = sc_node[p];
+    }
+    while (p < v.NP) {
+        const d4 x[4] = {n[0], n[1], n[2], n[3]};
+        const double inv = ninv, f = nf;
+        const int state = nst, sc = nsc;
+        const long long pc = p;
+        p += nthr;
+        if (p < v.NP) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) n[u] = ld_stream256(lh_node + p * 16 + 4 * u);
+            ninv = v.invar[p]; nf = p < v.P ? v.freq[p] : 0.0; nst = st[p]; nsc = sc_node[p];
+        }
+        const double2 *t = reinterpret_cast<const double2 *>(tipB + state * B16_TIPROW);
+        double s0 = 0.0;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const double2 a = t[2 * u], b = t[2 * u + 1];
+            s0 = fma(a.x, x[u].x, s0); s0 = fma(a.y, x[u].y, s0); s0 = fma(b.x, x[u].z, s0); s0 = fma(b.y, x[u].w, s0);
+        }
+        lnl_tail_vals(v, pc, s0, sc, inv, f, acc);
     }
     if (grid_reduce<4>(acc, sred, v.red, v.counter)) lnl_finish(v, acc, acc[1]);
 }
@@ -257,14 +323,22 @@ __device__ __forceinline__ void theta_dot(const DevView &v, long long p, int g, 
     const double *th = v.theta + p * v.B;
     if (VEC) {
         const int nsec = v.B >> 2;
-        for (int q = g; q < nsec; q += G) {
-            d4 x = ld_stream256(th + 4 * q);
-            const double *w0 = val0 + 4 * q;
-            s[0] = fma(x.x, w0[0], s[0]); s[0] = fma(x.y, w0[1], s[0]); s[0] = fma(x.z, w0[2], s[0]); s[0] = fma(x.w, w0[3], s[0]);
-            if (NV == 3) {
-                const double *w1 = val1 + 4 * q, *w2 = val2 + 4 * q;
-                s[1] = fma(x.x, w1[0], s[1]); s[1] = fma(x.y, w1[1], s[1]); s[1] = fma(x.z, w1[2], s[1]); s[1] = fma(x.w, w1[3], s[1]);
-                s[2] = fma(x.x, w2[0], s[2]); s[2] = fma(x.y, w2[1], s[2]); s[2] = fma(x.z, w2[2], s[2]); s[2] = fma(x.w, w2[3], s[2]);
+        for (int q0 = g; q0 < nsec; q0 += 4 * G) {
+            d4 xs[4];       /* up to 4 sectors in flight before the first is used */
+#pragma unroll
+            for (int u = 0; u < 4; u++) if (q0 + u * G < nsec) xs[u] = ld_stream256(th + 4 * (q0 + u * G));
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int q = q0 + u * G;
+                if (q >= nsec) break;
+                const d4 x = xs[u];
+                const double *w0 = val0 + 4 * q;
+                s[0] = fma(x.x, w0[0], s[0]); s[0] = fma(x.y, w0[1], s[0]); s[0] = fma(x.z, w0[2], s[0]); s[0] = fma(x.w, w0[3], s[0]);
+                if (NV == 3) {
+                    const double *w1 = val1 + 4 * q, *w2 = val2 + 4 * q;
+                    s[1] = fma(x.x, w1[0], s[1]); s[1] = fma(x.y, w1[1], s[1]); s[1] = fma(x.z, w1[2], s[1]); s[1] = fma(x.w, w1[3], s[1]);
+                    s[2] = fma(x.x, w2[0], s[2]); s[2] = fma(x.y, w2[1], s[2]); s[2] = fma(x.z, w2[2], s[2]); s[2] = fma(x.w, w2[3], s[2]);
+                }
             }
         }
     } else {
@@ -322,8 +396,70 @@ __device__ __forceinline__ bool derv_pass(const DevView &v, double len, int gshi
     return true;
 }
 
+/* ---- DNA + 4 categories (B = 16, 128 bytes per pattern): dedicated streaming kernels ---- */
+
+/* finish df/ddf from the five grid sums (phylokernel.h:647-651, 719-724) */
+__device__ __forceinline__ void derv_finish(const DevView &v, const double (&acc)[5]) {
+    double df = acc[0], ddf = acc[1];
+    if (isnan(df) || isinf(df)) { df = 0.0; ddf = 0.0; }
+    if (v.U > 0) {
+        double pc = 1.0 - acc[2], df_frac = acc[3] / pc, ddf_frac = acc[4] / pc;
+        df += v.nsite * df_frac;
+        ddf += v.nsite * (ddf_frac + df_frac * df_frac);
+    }
+    v.result[LKCUDA_R_LNL] = 0.0; v.result[LKCUDA_R_DF] = df; v.result[LKCUDA_R_DDF] = ddf;
+    v.result[LKCUDA_R_PROB_CONST] = 0.0; v.result[LKCUDA_R_NREPAIRED] = 0.0; v.result[LKCUDA_R_SCALE_SUM] = 0.0;
+    v.result[6] = 0.0; v.result[7] = 0.0;
+}
+
+__global__ void __launch_bounds__(RED_THREADS, 2) derv_b16_kernel(DevView v, double len) {
+    __shared__ __align__(32) double val0[16], val1[16], val2[16];
+    __shared__ double sred[5 * 32];
+    build_val(v, len, val0, val1, val2);
+    __syncthreads();
+    double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+    {
+        /* DNA + 4 categories (128 bytes per pattern): one lane per pattern, the NEXT pattern's four sectors are requested before the
+           current one is reduced, so every lane always has 128 bytes in flight */
+        const long long nthr = (long long)gridDim.x * blockDim.x;
+        long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+        d4 n[4]; double ninv = 0.0, nf = 0.0;
+        if (p < v.NP) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) n[u] = ld_stream256(v.theta + p * 16 + 4 * u);
+            ninv = v.invar[p]; nf = p < v.P ? v.freq[p] : 0.0;
+        }
+        while (p < v.NP) {
+            const d4 x[4] = {n[0], n[1], n[2], n[3]};
+            const double inv = ninv, f = nf;
+            const bool observed = p < v.P;
+            p += nthr;
+            if (p < v.NP) {
+#pragma unroll
+                for (int u = 0; u < 4; u++) n[u] = ld_stream256(v.theta + p * 16 + 4 * u);
+                ninv = v.invar[p]; nf = p < v.P ? v.freq[p] : 0.0;
+            }
+            double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const double *w0 = val0 + 4 * u, *w1 = val1 + 4 * u, *w2 = val2 + 4 * u;
+                m0 = fma(x[u].x, w0[0], m0); m0 = fma(x[u].y, w0[1], m0); m0 = fma(x[u].z, w0[2], m0); m0 = fma(x[u].w, w0[3], m0);
+                m1 = fma(x[u].x, w1[0], m1); m1 = fma(x[u].y, w1[1], m1); m1 = fma(x[u].z, w1[2], m1); m1 = fma(x[u].w, w1[3], m1);
+                m2 = fma(x[u].x, w2[0], m2); m2 = fma(x[u].y, w2[1], m2); m2 = fma(x[u].z, w2[2], m2); m2 = fma(x[u].w, w2[3], m2);
+            }
+            const double lh = fabs(m0 + inv);
+            if (observed) {
+                const double df_frac = m1 / lh, ddf_frac = m2 / lh, t1 = df_frac * f, t2 = ddf_frac * f;
+                acc[0] += t1;
+                acc[1] += t2 - t1 * df_frac;
+            } else { acc[2] += lh; acc[3] += m1; acc[4] += m2; }
+        }
+    }
+    if (grid_reduce<5>(acc, sred, v.red, v.counter)) derv_finish(v, acc);
+}
+
 template <bool VEC>
-__global__ void __launch_bounds__(RED_THREADS) derv_kernel(DevView v, double len, int gshift) {
+__global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) derv_kernel(DevView v, double len, int gshift) {
     extern __shared__ __align__(32) double sh[];
     __shared__ double sred[5 * 32];
     const int Bp = (v.B + 3) & ~3;
@@ -336,7 +472,7 @@ __global__ void __launch_bounds__(RED_THREADS) derv_kernel(DevView v, double len
 }
 
 template <bool VEC>
-__global__ void __launch_bounds__(RED_THREADS) frombuf_kernel(DevView v, double len, int gshift) {
+__global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) frombuf_kernel(DevView v, double len, int gshift) {
     extern __shared__ __align__(32) double sh[];
     __shared__ double sred[4 * 32];
     build_val(v, len, sh, NULL, NULL);
@@ -414,7 +550,11 @@ static int enqueue_derv(lkcuda_engine *e, double len) {
     int grid = red_grid(e, v.NP, gs.G);
     size_t sm = (size_t)3 * ((v.B + 3) & ~3) * 8;
     launch_begin(e, KIND_DERV);
-    if (gs.vec) derv_kernel<true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
+    if (gs.vec && v.B == 16) {      /* two resident blocks per SM, each lane keeps 2 x 128 bytes in flight */
+        int g2 = e->num_sms * 2 < grid ? e->num_sms * 2 : grid;
+        derv_b16_kernel<<<g2, RED_THREADS, 0, e->stream>>>(e->v, len);
+    }
+    else if (gs.vec) derv_kernel<true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
     else derv_kernel<false><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
     return launch_end(e, KIND_DERV, (uint64_t)v.NP * ((uint64_t)v.B * 8 + 16), "derv_kernel");
 }
@@ -437,7 +577,10 @@ int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     int use_tab = tip && (Bp * 8 + tabsz <= TAB_SMEM_LIMIT);
     size_t sm = Bp * 8 + (use_tab ? tabsz : 0);
     launch_begin(e, KIND_BRANCH);
-    if (tip) launch_branch<true>(e, gs, grid, sm, dad, node, len, use_tab);
+    if (tip && gs.vec && v.B == 16 && v.S == 4 && v.SU < 32) {
+        int g2 = e->num_sms * 2 < grid ? e->num_sms * 2 : grid;
+        branch_tip_b16_kernel<<<g2, RED_THREADS, 0, e->stream>>>(e->v, dad, node, len);
+    } else if (tip) launch_branch<true>(e, gs, grid, sm, dad, node, len, use_tab);
     else launch_branch<false>(e, gs, grid, sm, dad, node, len, use_tab);
     uint64_t b = (uint64_t)v.B * 8;
     rc = launch_end(e, KIND_BRANCH, (uint64_t)v.NP * (tip ? b + 1 + 24 : 2 * b + 24), "branch_kernel");
