@@ -108,6 +108,19 @@ int lkcuda_device_count(int32_t *count);
 int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out);
 int lkcuda_destroy(lkcuda_engine *e);
 const char *lkcuda_last_error(const lkcuda_engine *e);   /* e may be NULL: error of the last failed create */
+/* Caller-owned arenas.  PhyloSuperTreePlen::initializeAllPartialLh (phylosupertreeplen.cpp:1742-1871) sub-allocates all partitions'
+   vectors from ONE central_partial_lh / central_scale_num with per-partition strides block_size[part] / scale_block_size[part]
+   (:1766-1768, 1834-1855), and ModelMixture::optimizeWithEM aliases a tree's arena into a temporary tree and NULLs it before
+   delete (model/modelmixture.cpp:1427-1429, 1524-1526).  lkcuda_device_malloc gives the shim (host C++, no CUDA headers) zeroed
+   device memory; lkcuda_attach_arena makes the engine use `nvec` vectors at partial_lh + i*vec_stride (doubles) and
+   scale_num + i*scale_stride (int16) instead of its own arena - create the engine with cfg.nvec = 0 then.  The memory is
+   BORROWED: lkcuda_destroy never frees it.  Passing NULL, NULL detaches.  Requirements: 32-byte aligned base, vec_stride a
+   multiple of 4 doubles and >= (P+U)*K*S, scale_stride >= P+U.  lkcuda_arena_layout returns the strides the engine uses for its
+   own arena (what PhyloTree::initializeAllPartialLh's block_size / scale_block_size become, phylotree.cpp:845, 863-914). */
+int lkcuda_device_malloc(int32_t device, uint64_t bytes, void **ptr);
+int lkcuda_device_free(int32_t device, void *ptr);
+int lkcuda_arena_layout(const lkcuda_engine *e, int64_t *vec_stride, int64_t *scale_stride);
+int lkcuda_attach_arena(lkcuda_engine *e, void *partial_lh, int64_t vec_stride, void *scale_num, int64_t scale_stride, int32_t nvec);
 /* bytes of device memory the engine holds (getMemoryRequired analogue, phylotree.cpp:995-1024) */
 int lkcuda_memory_bytes(const lkcuda_engine *e, uint64_t *bytes);
 /* run on the caller's CUDA stream (cudaStream_t as void*); NULL = the engine's own stream */

@@ -33,6 +33,11 @@ enum KernelKind {
     KIND_NEWTON = 6, KIND_MISC = 7, KIND_COUNT = 8
 };
 
+/* cudaFuncAttributeMaxDynamicSharedMemorySize is a property of the FUNCTION (per context), not of an engine: every engine sets the
+   same value - the device maximum - so that engines of different shapes, driven from different host threads, never lower it
+   under each other's launches */
+#define LK_MAX_DYN_SMEM (227 * 1024)
+
 /* slots of the cross-block reduction buffer */
 enum { RED_SLOTS = 8 };
 
@@ -83,7 +88,8 @@ struct lkcuda_engine {
     /* owned device allocations */
     uint8_t *d_states; double *d_freq, *d_invar;
     double *d_eval, *d_evec, *d_inv, *d_rate, *d_weight, *d_tip; int32_t *d_eigen;
-    double *d_arena; int16_t *d_scale;
+    double *d_arena; int16_t *d_scale;      /* the engine's OWN arena; v.arena / v.scale may point at a caller-owned one (lkcuda_attach_arena) */
+    long long own_vec_stride, own_sc_stride; int own_nvec;
     double *d_theta; int16_t *d_theta_sc; double *d_theta_meta;
     double *d_plh, *d_plhcat, *d_plh_out;   /* d_plh_out: scale-corrected copy of _pattern_lh on its way to the host (lazy) */
     double *d_red; unsigned int *d_counter; double *d_result;

@@ -234,6 +234,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     v.states = e->d_states; v.freq = e->d_freq; v.invar = e->d_invar;
     v.eval = e->d_eval; v.evec = e->d_evec; v.inv_evec = e->d_inv; v.blk_rate = e->d_rate; v.blk_weight = e->d_weight;
     v.tip = e->d_tip; v.blk_eigen = e->d_eigen;
+    e->own_vec_stride = v.vec_stride; e->own_sc_stride = v.sc_stride; e->own_nvec = cfg->nvec;
     v.arena = e->d_arena; v.scale = e->d_scale; v.theta = e->d_theta; v.theta_sc = e->d_theta_sc; v.theta_meta = e->d_theta_meta;
     v.pattern_lh = e->d_plh; v.pattern_lh_cat = e->d_plhcat;
     v.red = e->d_red; v.counter = e->d_counter; v.result = e->d_result;
@@ -270,6 +271,65 @@ int lkcuda_destroy(lkcuda_engine *e) {
     if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
     cudaGetLastError();
     delete e;
+    return LKCUDA_OK;
+}
+
+/* ---- externally owned arenas (PhyloSuperTreePlen::initializeAllPartialLh, phylosupertreeplen.cpp:1742-1871, hands every
+   partition a window of ONE shared arena; ModelMixture::optimizeWithEM aliases a tree's arena into a temporary tree,
+   model/modelmixture.cpp:1427-1429, 1524-1526) ---- */
+int lkcuda_device_malloc(int32_t device, uint64_t bytes, void **ptr) {
+    if (!ptr) return LKCUDA_ERR_ARG;
+    *ptr = NULL;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { cudaGetLastError(); return fail(NULL, LKCUDA_ERR_NODEVICE, "no CUDA device available"); }
+    if (device < 0 || device >= ndev) return fail(NULL, LKCUDA_ERR_ARG, "device ordinal %d out of range", device);
+    cudaError_t rc = cudaSetDevice(device);
+    if (rc == cudaSuccess) rc = cudaMalloc(ptr, bytes ? (size_t)bytes : 1);
+    if (rc == cudaSuccess) rc = cudaMemset(*ptr, 0, bytes ? (size_t)bytes : 1);
+    if (rc != cudaSuccess) return cuda_fail(NULL, rc, "lkcuda_device_malloc");
+    return LKCUDA_OK;
+}
+
+int lkcuda_device_free(int32_t device, void *ptr) {
+    if (!ptr) return LKCUDA_OK;
+    cudaError_t rc = cudaSetDevice(device);
+    if (rc == cudaSuccess) rc = cudaDeviceSynchronize();
+    if (rc == cudaSuccess) rc = cudaFree(ptr);
+    if (rc != cudaSuccess) return cuda_fail(NULL, rc, "lkcuda_device_free");
+    return LKCUDA_OK;
+}
+
+int lkcuda_arena_layout(const lkcuda_engine *e, int64_t *vec_stride, int64_t *scale_stride) {
+    if (!e) return LKCUDA_ERR_ARG;
+    if (vec_stride) *vec_stride = e->v.vec_stride;
+    if (scale_stride) *scale_stride = e->v.sc_stride;
+    return LKCUDA_OK;
+}
+
+int lkcuda_attach_arena(lkcuda_engine *e, void *partial_lh, int64_t vec_stride, void *scale_num, int64_t scale_stride, int32_t nvec) {
+    LK_ENTER(e);
+    DevView &v = e->v;
+    if (!partial_lh && !scale_num) {            /* detach: back to the engine's own arena (sized by cfg.nvec at creation) */
+        LK_CUDA(e, cudaStreamSynchronize(e->stream));
+        v.arena = e->d_arena; v.scale = e->d_scale;
+        v.vec_stride = e->own_vec_stride; v.sc_stride = e->own_sc_stride; e->cfg.nvec = e->own_nvec;
+        e->theta_ready = false;
+        return LKCUDA_OK;
+    }
+    if (!partial_lh || !scale_num || nvec < 0) return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_arena: null base address");
+    if (vec_stride < v.NP * v.B || scale_stride < v.NP) return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_arena: stride shorter than one vector");
+    /* the kernels move whole 32-byte sectors: vectors must start on 32-byte boundaries */
+    if (((uintptr_t)partial_lh & 31) || (v.B % 4 == 0 && vec_stride % 4 != 0) || ((uintptr_t)scale_num & 1))
+        return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_arena: base must be 32-byte aligned and the stride a multiple of 4 doubles");
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, partial_lh) != cudaSuccess || at.type != cudaMemoryTypeDevice || at.device != e->device) {
+        cudaGetLastError();
+        return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_arena: not device memory of device %d", e->device);
+    }
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    v.arena = (double *)partial_lh; v.scale = (int16_t *)scale_num;
+    v.vec_stride = vec_stride; v.sc_stride = scale_stride; e->cfg.nvec = nvec;
+    e->theta_ready = false;
     return LKCUDA_OK;
 }
 
@@ -434,8 +494,8 @@ int lkcuda_fetch_vector(lkcuda_engine *e, int32_t vec, double *partial_lh, int16
     LK_ENTER(e);
     if (vec < 0 || vec >= e->cfg.nvec) return fail(e, LKCUDA_ERR_ARG, "vector index out of range");
     const DevView &v = e->v;
-    if (partial_lh && v.NP) LK_CUDA(e, cudaMemcpyAsync(partial_lh, e->d_arena + (size_t)vec * v.vec_stride, (size_t)v.NP * v.B * 8, cudaMemcpyDeviceToHost, e->stream));
-    if (scale_num && v.NP) LK_CUDA(e, cudaMemcpyAsync(scale_num, e->d_scale + (size_t)vec * v.sc_stride, (size_t)v.NP * 2, cudaMemcpyDeviceToHost, e->stream));
+    if (partial_lh && v.NP) LK_CUDA(e, cudaMemcpyAsync(partial_lh, e->v.arena + (size_t)vec * v.vec_stride, (size_t)v.NP * v.B * 8, cudaMemcpyDeviceToHost, e->stream));
+    if (scale_num && v.NP) LK_CUDA(e, cudaMemcpyAsync(scale_num, e->v.scale + (size_t)vec * v.sc_stride, (size_t)v.NP * 2, cudaMemcpyDeviceToHost, e->stream));
     LK_CUDA(e, cudaStreamSynchronize(e->stream));
     return LKCUDA_OK;
 }
@@ -444,8 +504,8 @@ int lkcuda_store_vector(lkcuda_engine *e, int32_t vec, const double *partial_lh,
     LK_ENTER(e);
     if (vec < 0 || vec >= e->cfg.nvec) return fail(e, LKCUDA_ERR_ARG, "vector index out of range");
     const DevView &v = e->v;
-    if (partial_lh && v.NP) LK_CUDA(e, cudaMemcpyAsync(e->d_arena + (size_t)vec * v.vec_stride, partial_lh, (size_t)v.NP * v.B * 8, cudaMemcpyHostToDevice, e->stream));
-    if (scale_num && v.NP) LK_CUDA(e, cudaMemcpyAsync(e->d_scale + (size_t)vec * v.sc_stride, scale_num, (size_t)v.NP * 2, cudaMemcpyHostToDevice, e->stream));
+    if (partial_lh && v.NP) LK_CUDA(e, cudaMemcpyAsync(e->v.arena + (size_t)vec * v.vec_stride, partial_lh, (size_t)v.NP * v.B * 8, cudaMemcpyHostToDevice, e->stream));
+    if (scale_num && v.NP) LK_CUDA(e, cudaMemcpyAsync(e->v.scale + (size_t)vec * v.sc_stride, scale_num, (size_t)v.NP * 2, cudaMemcpyHostToDevice, e->stream));
     LK_CUDA(e, cudaStreamSynchronize(e->stream));
     e->theta_ready = false;
     return LKCUDA_OK;
@@ -461,8 +521,8 @@ int lkcuda_fetch_theta(lkcuda_engine *e, double *theta) {
 
 int lkcuda_vector_device_ptr(lkcuda_engine *e, int32_t vec, void **partial_lh, void **scale_num) {
     if (!e || vec < 0 || vec >= e->cfg.nvec) return LKCUDA_ERR_ARG;
-    if (partial_lh) *partial_lh = e->d_arena + (size_t)vec * e->v.vec_stride;
-    if (scale_num) *scale_num = e->d_scale + (size_t)vec * e->v.sc_stride;
+    if (partial_lh) *partial_lh = e->v.arena + (size_t)vec * e->v.vec_stride;
+    if (scale_num) *scale_num = e->v.scale + (size_t)vec * e->v.sc_stride;
     return LKCUDA_OK;
 }
 

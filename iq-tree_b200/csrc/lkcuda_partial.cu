@@ -678,7 +678,7 @@ static int launch_ops(lkcuda_engine *e, int slot, int nops, int nchild_total, co
     size_t gsm = generic_smem(v);
     if (gsm > 48 * 1024) {
         if (gsm > 227 * 1024) return fail(e, LKCUDA_ERR_ARG, "state space too large for the generic kernel (%d states)", v.S);
-        LK_CUDA(e, cudaFuncSetAttribute(partial_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm));
+        LK_CUDA(e, cudaFuncSetAttribute(partial_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
     }
     for (int l = 0; l < nlevels; l++) {
         int b = level_start[l], n = level_start[l + 1] - b;
@@ -721,11 +721,11 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
         const TravNode &n = sch.nodes[j];
         TravOp &t = h[j];
         t.dst = ops[n.op].dst; t.dst_slot = n.dst_slot;
-        t.dst_lh = e->d_arena + (size_t)t.dst * v.vec_stride; t.dst_sc = e->d_scale + (size_t)t.dst * v.sc_stride;
+        t.dst_lh = e->v.arena + (size_t)t.dst * v.vec_stride; t.dst_sc = e->v.scale + (size_t)t.dst * v.sc_stride;
         t.src0 = n.src0; t.slot0 = n.slot0;
         t.src1 = n.src1; t.slot1 = n.slot1;
-        t.src0_lh = n.src0 >= 0 ? e->d_arena + (size_t)n.src0 * v.vec_stride : NULL;
-        t.src1_lh = n.src1 >= 0 ? e->d_arena + (size_t)n.src1 * v.vec_stride : NULL;
+        t.src0_lh = n.src0 >= 0 ? e->v.arena + (size_t)n.src0 * v.vec_stride : NULL;
+        t.src1_lh = n.src1 >= 0 ? e->v.arena + (size_t)n.src1 * v.vec_stride : NULL;
         t.pad[0] = t.pad[1] = 0;
         DevChild &a = e->h_child[slot][2 * j], &b = e->h_child[slot][2 * j + 1];
         a.id = n.src0; a.pad = 0; a.len = n.len0;
@@ -755,9 +755,9 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
     if (tile_stride > tile_pats) tile_stride = tile_pats;
     ntiles = (v.NP + tile_stride - 1) / tile_stride;
     const size_t sm = (size_t)sch.nslots * slot_bytes + fixed;
-    if (sm > e->trav_smem_set) {
-        LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-        e->trav_smem_set = sm;
+    if (e->trav_smem_set != LK_MAX_DYN_SMEM) {
+        LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
+        e->trav_smem_set = LK_MAX_DYN_SMEM;
     }
     long long grid = e->num_sms;      /* one persistent CTA per SM (384 threads, shared memory bound) */
     if (grid > ntiles) grid = ntiles;
@@ -860,7 +860,7 @@ int lkcuda_partial_multi(lkcuda_engine *e, int32_t dst, int32_t nchild, const in
     if (rc) return rc;
     size_t gsm = generic_smem(v);
     if (gsm > 227 * 1024) return fail(e, LKCUDA_ERR_ARG, "state space too large for the generic kernel (%d states)", v.S);
-    if (gsm > 48 * 1024) LK_CUDA(e, cudaFuncSetAttribute(partial_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm));
+    if (gsm > 48 * 1024) LK_CUDA(e, cudaFuncSetAttribute(partial_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
     launch_begin(e, KIND_PARTIAL);
     dim3 grid((unsigned)((v.NP + GEN_TP - 1) / GEN_TP), 1);
     partial_generic_kernel<<<grid, GEN_THREADS, gsm, e->stream>>>(e->v, e->d_ops[slot], e->d_child[slot], 0);

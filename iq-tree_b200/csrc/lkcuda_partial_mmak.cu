@@ -433,11 +433,11 @@ static int launch_mmak(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops)
         const TravNode &n = sch.nodes[j];
         TravOp &t = h[j];
         t.dst = ops[n.op].dst; t.dst_slot = n.dst_slot;
-        t.dst_lh = e->d_arena + (size_t)t.dst * v.vec_stride; t.dst_sc = e->d_scale + (size_t)t.dst * v.sc_stride;
+        t.dst_lh = e->v.arena + (size_t)t.dst * v.vec_stride; t.dst_sc = e->v.scale + (size_t)t.dst * v.sc_stride;
         t.src0 = n.src0; t.slot0 = n.slot0;
         t.src1 = n.src1; t.slot1 = n.slot1;
-        t.src0_lh = n.src0 >= 0 ? e->d_arena + (size_t)n.src0 * v.vec_stride : NULL;
-        t.src1_lh = n.src1 >= 0 ? e->d_arena + (size_t)n.src1 * v.vec_stride : NULL;
+        t.src0_lh = n.src0 >= 0 ? e->v.arena + (size_t)n.src0 * v.vec_stride : NULL;
+        t.src1_lh = n.src1 >= 0 ? e->v.arena + (size_t)n.src1 * v.vec_stride : NULL;
         t.pad[0] = t.pad[1] = 0;
         DevChild &a = e->h_child[slot][2 * j], &b = e->h_child[slot][2 * j + 1];
         a.id = n.src0; a.pad = 0; a.len = n.len0;
@@ -469,10 +469,10 @@ static int launch_mmak(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops)
 
     const long long ngroups = (v.NP + 7) / 8;
     const size_t sm = (size_t)sch.nslots * slot_bytes + fixed;
-    if (sm > e->mma_smem_set) {
-        LK_CUDA(e, cudaFuncSetAttribute(traverse_mmak_kernel<S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-        LK_CUDA(e, cudaFuncSetAttribute(traverse_mmak_kernel<S, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-        e->mma_smem_set = sm;
+    if (e->mma_smem_set != LK_MAX_DYN_SMEM) {
+        LK_CUDA(e, cudaFuncSetAttribute(traverse_mmak_kernel<S, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
+        LK_CUDA(e, cudaFuncSetAttribute(traverse_mmak_kernel<S, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
+        e->mma_smem_set = LK_MAX_DYN_SMEM;
     }
     long long grid = e->num_sms;      /* one persistent CTA per SM; every CTA gets at least one 8-pattern group */
     if (grid > ngroups) grid = ngroups;

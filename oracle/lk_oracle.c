@@ -37,8 +37,9 @@ struct lkcuda_engine {
     double *eval, *evec, *inv_evec;  /* [E*S], [E*S*S], [E*S*S] */
     int32_t *blk_eigen; double *blk_rate, *blk_weight;
     double *tip_lh;                  /* [(SU+1)][E][S] */
-    double *arena;                   /* [nvec][(P+U)*block] */
-    int16_t *scale;                  /* [nvec][P+U] */
+    double *arena;                   /* [nvec][vec_stride], own: vec_stride = (P+U)*block */
+    int16_t *scale;                  /* [nvec][sc_stride], own: sc_stride = P+U */
+    double *own_arena; int16_t *own_scale; size_t vec_stride, sc_stride; int32_t own_nvec;   /* lkcuda_attach_arena borrows */
     double *theta;                   /* [(P+U)*block] */
     double *pattern_lh, *pattern_lh_cat;
     int theta_ready, theta_dad_tip;
@@ -84,6 +85,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     e->theta = (double *)calloc(n * e->block, 8);
     e->pattern_lh = (double *)calloc(n, 8); e->pattern_lh_cat = (double *)calloc(n * e->K, 8);
     e->theta_scale_num = (int16_t *)calloc((size_t)cfg->nunobs + 1, 2);
+    e->own_arena = e->arena; e->own_scale = e->scale; e->vec_stride = n * e->block; e->sc_stride = n; e->own_nvec = cfg->nvec;
     if (!e->states || !e->arena || !e->scale || !e->theta || !e->pattern_lh_cat) {
         lkcuda_destroy(e);
         return fail(NULL, LKCUDA_ERR_NOMEM, "out of memory");
@@ -95,7 +97,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
 int lkcuda_destroy(lkcuda_engine *e) {
     if (!e) return LKCUDA_OK;
     free(e->states); free(e->ptn_freq); free(e->ptn_invar); free(e->eval); free(e->evec); free(e->inv_evec);
-    free(e->blk_eigen); free(e->blk_rate); free(e->blk_weight); free(e->tip_lh); free(e->arena); free(e->scale);
+    free(e->blk_eigen); free(e->blk_rate); free(e->blk_weight); free(e->tip_lh); free(e->own_arena); free(e->own_scale);
     free(e->theta); free(e->pattern_lh); free(e->pattern_lh_cat); free(e->theta_scale_num);
     free(e);
     return LKCUDA_OK;
@@ -106,6 +108,39 @@ int lkcuda_memory_bytes(const lkcuda_engine *e, uint64_t *bytes) {
     *bytes = 0;
     return LKCUDA_OK;
 }
+/* caller-owned arenas: plain host memory here */
+int lkcuda_device_malloc(int32_t device, uint64_t bytes, void **ptr) {
+    (void)device;
+    if (!ptr) return LKCUDA_ERR_ARG;
+    *ptr = aligned_alloc(256, ((bytes ? (size_t)bytes : 1) + 255) / 256 * 256);
+    if (!*ptr) return LKCUDA_ERR_NOMEM;
+    memset(*ptr, 0, bytes ? (size_t)bytes : 1);
+    return LKCUDA_OK;
+}
+int lkcuda_device_free(int32_t device, void *ptr) { (void)device; free(ptr); return LKCUDA_OK; }
+int lkcuda_arena_layout(const lkcuda_engine *e, int64_t *vec_stride, int64_t *scale_stride) {
+    if (!e) return LKCUDA_ERR_ARG;
+    if (vec_stride) *vec_stride = (int64_t)e->vec_stride;
+    if (scale_stride) *scale_stride = (int64_t)e->sc_stride;
+    return LKCUDA_OK;
+}
+int lkcuda_attach_arena(lkcuda_engine *e, void *partial_lh, int64_t vec_stride, void *scale_num, int64_t scale_stride, int32_t nvec) {
+    if (!e) return LKCUDA_ERR_ARG;
+    if (!partial_lh && !scale_num) {
+        e->arena = e->own_arena; e->scale = e->own_scale; e->vec_stride = e->nptn_all * e->block; e->sc_stride = e->nptn_all;
+        e->cfg.nvec = e->own_nvec; e->theta_ready = 0;
+        return LKCUDA_OK;
+    }
+    if (!partial_lh || !scale_num || nvec < 0 || vec_stride < (int64_t)(e->nptn_all * e->block) || scale_stride < (int64_t)e->nptn_all)
+        return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_arena: bad arena");
+    /* same contract as the CUDA engine (whole 32-byte sectors) */
+    if (((uintptr_t)partial_lh & 31) || (e->block % 4 == 0 && vec_stride % 4 != 0) || ((uintptr_t)scale_num & 1))
+        return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_arena: base must be 32-byte aligned and the stride a multiple of 4 doubles");
+    e->arena = (double *)partial_lh; e->scale = (int16_t *)scale_num;
+    e->vec_stride = (size_t)vec_stride; e->sc_stride = (size_t)scale_stride; e->cfg.nvec = nvec; e->theta_ready = 0;
+    return LKCUDA_OK;
+}
+
 int lkcuda_set_stream(lkcuda_engine *e, void *s) { (void)s; return e ? LKCUDA_OK : LKCUDA_ERR_ARG; }
 int lkcuda_synchronize(lkcuda_engine *e) { return e ? LKCUDA_OK : LKCUDA_ERR_ARG; }
 
@@ -146,8 +181,8 @@ int lkcuda_set_model(lkcuda_engine *e, const double *eval, const double *evec, c
     return LKCUDA_OK;
 }
 
-static double *vec_lh(lkcuda_engine *e, int32_t v) { return e->arena + (size_t)v * e->nptn_all * e->block; }
-static int16_t *vec_sc(lkcuda_engine *e, int32_t v) { return e->scale + (size_t)v * e->nptn_all; }
+static double *vec_lh(lkcuda_engine *e, int32_t v) { return e->arena + (size_t)v * e->vec_stride; }
+static int16_t *vec_sc(lkcuda_engine *e, int32_t v) { return e->scale + (size_t)v * e->sc_stride; }
 static int bad_end(lkcuda_engine *e, int32_t id) {
     return id >= 0 ? id >= e->cfg.nvec : LKCUDA_TIP_TAXON(id) >= e->cfg.ntaxa;
 }
@@ -583,7 +618,7 @@ int lkcuda_fetch_pattern_lh_corrected(lkcuda_engine *e, int32_t vec, double *dst
     if (rc || vec < 0) return rc;
     if (vec >= e->cfg.nvec) return LKCUDA_ERR_ARG;
     {
-        const int16_t *sc = e->scale + (size_t)vec * e->nptn_all;
+        const int16_t *sc = e->scale + (size_t)vec * e->sc_stride;
         int64_t p;
         for (p = 0; p < e->cfg.nptn; p++) if (sc[p] > 0) dst[p] += (double)sc[p] * LOG_SCALING_THRESHOLD;
     }
