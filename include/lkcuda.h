@@ -168,6 +168,9 @@ int lkcuda_pattern_lh_cat(lkcuda_engine *e, int32_t dad, int32_t node, double le
 /* ---- derivatives: PhyloTree::computeLikelihoodDerv (phylotreesse.cpp:344) split at its theta_computed flag ---- */
 /* theta_all = L_node * L_dad (phylokernel.h:535-579) */
 int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node);
+/* both halves of one PhyloTree::computeLikelihoodDerv call with theta_computed == false (phylokernel.h:535-635): builds theta_all
+   AND returns df, ddf at `len` in the same pass over the two vectors (one read of theta_all saved per branch) */
+int lkcuda_theta_derv(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result);
 /* df, ddf at branch length len from theta_all (phylokernel.h:521-532, 599-725) */
 int lkcuda_derv(lkcuda_engine *e, double len, double *result);
 /* PhyloTree::computeLikelihoodFromBuffer (phylotreesse.cpp:349; phylokernel.h:1023-1192) */

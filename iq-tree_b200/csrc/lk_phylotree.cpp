@@ -605,11 +605,12 @@ void PhyloTree::computeLikelihoodDerv(Neighbor *dad_branch, Node *dad, double &d
     if (!theta_computed) {
         theta_computed = true;
         int32_t dad_end = dad->isLeaf() ? LKCUDA_TIP(dad->id) : node_branch->vec;
+        for (size_t d = 0; d < engines_.size(); d++)      // theta_all and the first df/ddf in one pass
+            check(lkcuda_theta_derv(engines_[d], dad_end, dad_branch->vec, dad_branch->length, NULL), engines_[d], "lkcuda_theta_derv");
+    } else {
         for (size_t d = 0; d < engines_.size(); d++)
-            check(lkcuda_theta_build(engines_[d], dad_end, dad_branch->vec), engines_[d], "lkcuda_theta_build");
+            check(lkcuda_derv(engines_[d], dad_branch->length, NULL), engines_[d], "lkcuda_derv");
     }
-    for (size_t d = 0; d < engines_.size(); d++)
-        check(lkcuda_derv(engines_[d], dad_branch->length, NULL), engines_[d], "lkcuda_derv");
     double r[LKCUDA_NRESULT];
     reduceResult(r);
     df = r[LKCUDA_R_DF]; ddf = r[LKCUDA_R_DDF];

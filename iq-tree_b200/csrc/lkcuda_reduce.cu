@@ -458,6 +458,66 @@ __global__ void __launch_bounds__(RED_THREADS, 2) derv_b16_kernel(DevView v, dou
     if (grid_reduce<5>(acc, sred, v.red, v.counter)) derv_finish(v, acc);
 }
 
+/* theta_all build + first df/ddf in one pass (B = 16): lane = pattern; reads the node vector and the dad vector (or the dad
+   tip's state), writes theta_all, keeps the three dot products.  acc[5] carries the scale sum that theta_kernel leaves in theta_meta. */
+template <bool TIP>
+__global__ void __launch_bounds__(RED_THREADS, 2) theta_derv_b16_kernel(DevView v, int dad, int node, double len) {
+    __shared__ __align__(32) double val0[16], val1[16], val2[16];
+    __shared__ __align__(32) double tipT[32 * B16_TIPROW];
+    __shared__ double sred[6 * 32];
+    build_val(v, len, val0, val1, val2);
+    if (TIP) {
+        for (int idx = threadIdx.x; idx < (v.SU + 1) * 16; idx += blockDim.x) {
+            const int st = idx >> 4, j = idx & 15;
+            tipT[st * B16_TIPROW + j] = v.tip[((long long)st * v.E + v.blk_eigen[j >> 2]) * 4 + (j & 3)];
+        }
+    }
+    __syncthreads();
+    const double *lh_node = vec_lh(v, node), *lh_dad = TIP ? NULL : vec_lh(v, dad);
+    const int16_t *sc_node = vec_sc(v, node), *sc_dad = TIP ? NULL : vec_sc(v, dad);
+    const uint8_t *st = TIP ? tip_states(v, dad) : NULL;
+    const long long nthr = (long long)gridDim.x * blockDim.x;
+    double acc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < v.NP; p += nthr) {
+        d4 x[4], y[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) x[u] = ld_stream256(lh_node + p * 16 + 4 * u);
+        if (TIP) {
+            const double2 *t = reinterpret_cast<const double2 *>(tipT + (int)st[p] * B16_TIPROW);
+#pragma unroll
+            for (int u = 0; u < 4; u++) { const double2 a = t[2 * u], b = t[2 * u + 1]; y[u].x = a.x; y[u].y = a.y; y[u].z = b.x; y[u].w = b.y; }
+        } else {
+#pragma unroll
+            for (int u = 0; u < 4; u++) y[u] = ld_stream256(lh_dad + p * 16 + 4 * u);
+        }
+        const double inv = v.invar[p], f = p < v.P ? v.freq[p] : 0.0;
+        const int sc = sc_node[p] + (TIP ? 0 : sc_dad[p]);
+        double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            d4 r;
+            r.x = x[u].x * y[u].x; r.y = x[u].y * y[u].y; r.z = x[u].z * y[u].z; r.w = x[u].w * y[u].w;
+            st_stream256(v.theta + p * 16 + 4 * u, r);
+            const double *w0 = val0 + 4 * u, *w1 = val1 + 4 * u, *w2 = val2 + 4 * u;
+            m0 = fma(r.x, w0[0], m0); m0 = fma(r.y, w0[1], m0); m0 = fma(r.z, w0[2], m0); m0 = fma(r.w, w0[3], m0);
+            m1 = fma(r.x, w1[0], m1); m1 = fma(r.y, w1[1], m1); m1 = fma(r.z, w1[2], m1); m1 = fma(r.w, w1[3], m1);
+            m2 = fma(r.x, w2[0], m2); m2 = fma(r.y, w2[1], m2); m2 = fma(r.z, w2[2], m2); m2 = fma(r.w, w2[3], m2);
+        }
+        const double lh = fabs(m0 + inv);
+        if (p < v.P) {
+            const double df_frac = m1 / lh, ddf_frac = m2 / lh, t1 = df_frac * f, t2 = ddf_frac * f;
+            acc[0] += t1;
+            acc[1] += t2 - t1 * df_frac;
+            if (sc) acc[5] += LK_LOG_THR * f * (double)sc;
+        } else { acc[2] += lh; acc[3] += m1; acc[4] += m2; v.theta_sc[p - v.P] = (int16_t)sc; }
+    }
+    if (grid_reduce<6>(acc, sred, v.red, v.counter)) {
+        v.theta_meta[0] = acc[5];
+        const double a5[5] = {acc[0], acc[1], acc[2], acc[3], acc[4]};
+        derv_finish(v, a5);
+    }
+}
+
 template <bool VEC>
 __global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) derv_kernel(DevView v, double len, int gshift) {
     extern __shared__ __align__(32) double sh[];
@@ -643,6 +703,32 @@ int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node) {
     if (rc) return rc;
     e->theta_ready = true; e->theta_dad = dad; e->theta_node = node;
     return LKCUDA_OK;
+}
+
+int lkcuda_theta_derv(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result) {
+    LK_ENTER(e);
+    const DevView &v = e->v;
+    GroupShape gs = group_shape(v);
+    if (!(gs.vec && v.B == 16 && v.S == 4 && v.SU < 32)) {      /* other shapes: the two passes */
+        int rc = lkcuda_theta_build(e, dad, node);
+        return rc ? rc : lkcuda_derv(e, len, result);
+    }
+    if (node < 0 || node >= e->cfg.nvec || !valid_end(e, dad) || dad == node) return fail(e, LKCUDA_ERR_ARG, "lkcuda_theta_derv: bad vector / taxon id");
+    int rc = check_ready(e, "lkcuda_theta_derv");
+    if (rc) return rc;
+    rc = states_barrier(e);
+    if (rc) return rc;
+    const bool tip = LKCUDA_IS_TIP(dad);
+    int grid = red_grid(e, v.NP, 1);
+    if (grid > e->num_sms * 2) grid = e->num_sms * 2;
+    launch_begin(e, KIND_THETA);
+    if (tip) theta_derv_b16_kernel<true><<<grid, RED_THREADS, 0, e->stream>>>(e->v, dad, node, len);
+    else theta_derv_b16_kernel<false><<<grid, RED_THREADS, 0, e->stream>>>(e->v, dad, node, len);
+    uint64_t b = (uint64_t)v.B * 8;
+    rc = launch_end(e, KIND_THETA, (uint64_t)v.NP * ((tip ? 2 * b + 1 : 3 * b) + 16), "theta_derv_b16_kernel");
+    if (rc) return rc;
+    e->theta_ready = true; e->theta_dad = dad; e->theta_node = node;
+    return finish_result(e, result);
 }
 
 int lkcuda_derv(lkcuda_engine *e, double len, double *result) {

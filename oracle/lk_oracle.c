@@ -472,6 +472,13 @@ int lkcuda_pattern_lh_cat(lkcuda_engine *e, int32_t dad, int32_t node, double le
     return LKCUDA_OK;
 }
 
+int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node);
+int lkcuda_derv(lkcuda_engine *e, double len, double *result);
+int lkcuda_theta_derv(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result) {
+    int rc = lkcuda_theta_build(e, dad, node);
+    return rc ? rc : lkcuda_derv(e, len, result);
+}
+
 int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node) {
     if (!e || node < 0 || node >= e->cfg.nvec || bad_end(e, dad)) return LKCUDA_ERR_ARG;
     size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all, P = (size_t)e->cfg.nptn;
