@@ -236,8 +236,9 @@ def main():
     t.initializeAllPartialLh()
 
     shard_check = None
+    exchange = "none"
     if world > 1:
-        # the engine keeps its 8-double result block inside this tensor; the only exchange of the path is one in-place NCCL sum of it
+        # the engine keeps its 8-double result block inside this tensor; the NCCL variant of the exchange is one in-place sum of it
         resbuf = torch.zeros(8, dtype=torch.float64, device=dev)
         t.setResultBuffer(resbuf.data_ptr())
 
@@ -254,7 +255,26 @@ def main():
         t.clearAllPartialLH()
         loc = torch.tensor([t.computeLikelihood()], dtype=torch.float64, device=dev)
         dist.all_reduce(loc)
-        t.setAllReduce(allreduce)
+        # default exchange: fused into the reduction kernels over NVLink peer memory (lkcuda_attach_peers) - the mailbox handles
+        # travel once through torch.distributed; LK_BENCH_EXCHANGE=nccl keeps one NCCL all-reduce per evaluation instead
+        exchange = "nccl"
+        if os.environ.get("LK_BENCH_EXCHANGE", "peer") == "peer":
+            mine = torch.from_numpy(t.peerHandle()).to(dev)
+            allh = [torch.zeros(64, dtype=torch.uint8, device=dev) for _ in range(world)]
+            dist.all_gather(allh, mine)
+            ok = torch.ones(1, dtype=torch.int32, device=dev)
+            try:
+                t.attachPeers(torch.stack(allh).cpu().numpy())
+            except RuntimeError as ex:
+                sys.stderr.write("rank %d: peer attach failed (%s); falling back to NCCL\n" % (rank, ex))
+                ok[0] = 0
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok[0]) == 1:
+                exchange = "peer"
+            else:
+                raise SystemExit("peer attach failed on some rank; rerun with LK_BENCH_EXCHANGE=nccl")
+        if exchange == "nccl":
+            t.setAllReduce(allreduce)
         t.clearAllPartialLH()
         glob = t.computeLikelihood()
         shard_check = bool(abs(glob - float(loc[0])) <= 1e-12 * abs(glob))
@@ -282,7 +302,6 @@ def main():
     for _ in range(args.warmup):
         res = step()
     t.resetCounters()
-    t.setProfiling(True)
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
@@ -295,8 +314,16 @@ def main():
     ev1.record(stream)
     barrier()
     ms = ev0.elapsed_time(ev1)
-    stats = t.kernelStats()
     launches = t.launchCount()
+
+    # ---- the same steps once more with every launch bracketed by CUDA events: per-kernel device times (not the headline) ----
+    t.resetCounters()
+    t.setProfiling(True)
+    barrier()
+    for _ in range(args.steps):
+        step()
+    barrier()
+    stats = t.kernelStats()
 
     # ---- lnL only (clearAllPartialLH + computeLikelihood): the full-tree traversal launch alone, for the roofline ----
     t.resetCounters()
@@ -368,7 +395,7 @@ def main():
             "metric": "partial-LH updates/s (patterns x cats x nodes)", "value": value, "unit": "updates/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "ntaxa": NTAXA, "patterns": NPTN, "ncat": NCAT, "sharding": "patterns x%d" % world,
+            "config": {"workload": WORKLOAD, "ntaxa": NTAXA, "patterns": NPTN, "ncat": NCAT, "sharding": "patterns x%d" % world, "exchange": exchange,
                        "step": "clearAllPartialLH + computeLikelihood + computeLikelihoodDerv(root branch, theta rebuilt)",
                        "l2": "inputs larger than L2: ~%.1f GB streamed per step per GPU vs 126 MB L2, no flush needed" % (
                            sum(v[1] for v in stats.values()) / 1e9 / max(args.steps, 1))},

@@ -102,6 +102,7 @@ enum {
     LKCUDA_R_SCALE_SUM = 5,  /* lh_scale_factor(node)+lh_scale_factor(dad) of the shard      */
     LKCUDA_NRESULT = 8
 };
+enum { LKCUDA_MAX_PEERS = 16, LKCUDA_PEER_HANDLE_BYTES = 64 };
 
 /* ---- life cycle : PhyloTree::initializeAllPartialLh / deleteAllPartialLh (phylotree.cpp:667-987, 718) ---- */
 int lkcuda_device_count(int32_t *count);
@@ -188,6 +189,25 @@ int lkcuda_result_device_ptr(lkcuda_engine *e, void **dev_ptr);
 /* keep the result block in caller-owned device memory (LKCUDA_NRESULT doubles, e.g. a buffer registered with NCCL or a
    torch tensor) so that the caller's all-reduce runs in place on it; NULL = back to the engine's own block */
 int lkcuda_set_result_buffer(lkcuda_engine *e, void *dev_ptr);
+/* Results of the last enqueued reduction WITHOUT a copy or a stream synchronisation: every reduction kernel ends by writing its
+   result block and a sequence number into host-mapped memory, which this call polls (the wrappers at phylotreesse.cpp:335-357 return
+   a double, so each evaluation ends in exactly one such wait).  With peers attached the block already holds the sums over all
+   ranks.  lkcuda_read_result stays the path to use after the caller changed the block behind the engine's back (NCCL in place). */
+int lkcuda_wait_result(lkcuda_engine *e, double *result);
+
+/* ---- fused reduction + cross-GPU all-reduce over NVLink peer memory (only the scalar lnL/df/ddf sums are exchanged) ----
+   Each engine (= one pattern shard on one GPU, normally one process per GPU) owns a small mailbox in device memory.
+   lkcuda_peer_handle exports it: `handle` receives a CUDA IPC handle (LKCUDA_PEER_HANDLE_BYTES) for engines in OTHER processes,
+   `local_ptr` the raw device address for engines in the SAME process.  After the ranks exchanged them (any transport: MPI,
+   torch.distributed, a pipe) lkcuda_attach_peers installs the table; from then on every reduction kernel (branch lnL, df/ddf, lnL from
+   buffer) deposits its result block in all peers' mailboxes with P2P stores and sums the deposits in rank order before it exits, so
+   that lkcuda_wait_result returns the GLOBAL sums on every rank (bit-identical across ranks).  All ranks must enqueue the same
+   sequence of reductions (they do: tree, model and host control flow are replicated).  `handles`: [world][LKCUDA_PEER_HANDLE_BYTES]
+   or NULL; `raw_ptrs`: [world] device addresses or NULL; entry `rank` of either is ignored.  A peer that never shows up makes the
+   kernel give up after 10 s and the next lkcuda_wait_result fail with LKCUDA_ERR_STATE. */
+int lkcuda_peer_handle(lkcuda_engine *e, uint8_t *handle /*[LKCUDA_PEER_HANDLE_BYTES] or NULL*/, void **local_ptr /*or NULL*/);
+int lkcuda_attach_peers(lkcuda_engine *e, int32_t rank, int32_t world, const uint8_t *handles, void *const *raw_ptrs);
+int lkcuda_detach_peers(lkcuda_engine *e);
 
 /* ---- host-visible mirrors (buffers host code reads or writes) ---- */
 int lkcuda_fetch_pattern_lh(lkcuda_engine *e, double *pattern_lh /*[P]*/);

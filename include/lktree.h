@@ -47,6 +47,11 @@ int lktree_get_tree_string(lktree *h, char *buf, size_t buflen);
 int lktree_set_devices(lktree *h, const int32_t *devices, int32_t n);        /* in-process shards, one per device */
 int lktree_set_process_shard(lktree *h, int32_t rank, int32_t world);        /* one process per GPU */
 int lktree_set_allreduce(lktree *h, lktree_allreduce_fn fn, void *user);
+/* fused cross-GPU all-reduce inside the reduction kernels (lkcuda_peer_handle / lkcuda_attach_peers), one process per GPU:
+   every rank exports its handle (LKCUDA_PEER_HANDLE_BYTES), the host exchanges them and passes all `world` of them in rank order */
+int lktree_peer_handle(lktree *h, uint8_t *handle);
+int lktree_attach_peers(lktree *h, const uint8_t *handles);
+int lktree_peers_attached(lktree *h);
 int lktree_set_stream(lktree *h, void *cuda_stream);
 int lktree_set_params(lktree *h, double min_branch_length, double max_branch_length, int32_t device_newton, int32_t generic_kernel);
 

@@ -70,6 +70,9 @@ int lktree_set_devices(lktree *h, const int32_t *devices, int32_t n) {
 }
 int lktree_set_process_shard(lktree *h, int32_t rank, int32_t world) { LK_TRY(h) h->tree.setProcessShard(rank, world); LK_CATCH(h) }
 int lktree_set_allreduce(lktree *h, lktree_allreduce_fn fn, void *user) { LK_TRY(h) h->tree.setAllReduce(fn, user); LK_CATCH(h) }
+int lktree_peer_handle(lktree *h, uint8_t *handle) { LK_TRY(h) h->tree.peerHandle(handle); LK_CATCH(h) }
+int lktree_attach_peers(lktree *h, const uint8_t *handles) { LK_TRY(h) h->tree.attachPeers(handles); LK_CATCH(h) }
+int lktree_peers_attached(lktree *h) { return h && h->tree.peersAttached() ? 1 : 0; }
 int lktree_set_stream(lktree *h, void *stream) { LK_TRY(h) h->tree.setStream(stream); LK_CATCH(h) }
 
 int lktree_set_params(lktree *h, double min_branch_length, double max_branch_length, int32_t device_newton, int32_t generic_kernel) {

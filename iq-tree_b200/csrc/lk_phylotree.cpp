@@ -13,6 +13,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <sstream>
 
@@ -27,7 +28,7 @@ PhyloTree::PhyloTree()
       device_newton(false), generic_kernel(false), current_it(NULL), current_it_back(NULL),
       theta_computed(false), num_partial_lh_computations(0), nstates(0), ncat(1), nmix(1), family(FAMILY_PLAIN),
       state_unknown(0), seq_type(SEQ_DNA), ntaxa(0), nptn(0), nunobs(0), nsite(0), p_invar_(0.0),
-      proc_rank_(0), proc_world_(1), allreduce_(NULL), allreduce_user_(NULL), stream_(NULL),
+      proc_rank_(0), proc_world_(1), allreduce_(NULL), allreduce_user_(NULL), stream_(NULL), peers_attached_(false),
       ptn_begin_(0), ptn_end_(0), tip_partial_lh_computed_(false), weights_uploaded_(false), model_uploaded_(false),
       freq_dirty_(true), invar_dirty_(true), model_dirty_(true), nvec_(0) {}
 
@@ -416,6 +417,19 @@ void PhyloTree::initializeAllPartialLh() {
         }
         check(lkcuda_set_tip_states(e, na ? &st[0] : (const uint8_t*)""), e, "lkcuda_set_tip_states");
     }
+    // several engines in ONE process, each on its own stream: their reduction kernels exchange and add the result blocks among
+    // themselves (raw device addresses; peer access across devices), the host no longer sums anything.  With a caller-supplied
+    // common stream the kernels would serialise behind each other and could not wait for one another: host sum then.
+    peers_attached_ = false;
+    if (engines_.size() > 1 && engines_.size() <= (size_t)LKCUDA_MAX_PEERS && proc_world_ == 1 && !stream_ && !getenv("LKTREE_NO_PEERS")) {
+        std::vector<void*> ptrs(engines_.size(), (void*)NULL);
+        bool ok = true;
+        for (size_t d = 0; d < engines_.size() && ok; d++) ok = lkcuda_peer_handle(engines_[d], NULL, &ptrs[d]) == LKCUDA_OK;
+        for (size_t d = 0; d < engines_.size() && ok; d++)
+            ok = lkcuda_attach_peers(engines_[d], (int32_t)d, (int32_t)engines_.size(), NULL, &ptrs[0]) == LKCUDA_OK;
+        if (!ok) for (size_t d = 0; d < engines_.size(); d++) lkcuda_detach_peers(engines_[d]);
+        peers_attached_ = ok;
+    }
     weights_uploaded_ = model_uploaded_ = false;
     freq_dirty_ = invar_dirty_ = model_dirty_ = true;
     tip_partial_lh_computed_ = false;
@@ -423,9 +437,22 @@ void PhyloTree::initializeAllPartialLh() {
     clearAllPartialLH();
 }
 
+void PhyloTree::peerHandle(uint8_t *handle) {
+    if (engines_.empty()) initializeAllPartialLh();
+    if (engines_.size() != 1) throw std::runtime_error("peerHandle: one engine per process expected");
+    check(lkcuda_peer_handle(engines_[0], handle, NULL), engines_[0], "lkcuda_peer_handle");
+}
+
+void PhyloTree::attachPeers(const uint8_t *handles) {
+    if (engines_.size() != 1) throw std::runtime_error("attachPeers: one engine per process expected");
+    check(lkcuda_attach_peers(engines_[0], proc_rank_, proc_world_, handles, NULL), engines_[0], "lkcuda_attach_peers");
+    peers_attached_ = proc_world_ > 1;
+}
+
 void PhyloTree::deleteAllPartialLh() {
     for (size_t i = 0; i < engines_.size(); i++) lkcuda_destroy(engines_[i]);
     engines_.clear();
+    peers_attached_ = false;
     pending_ops_.clear(); pending_level_.clear();
     theta_computed = false;
 }
@@ -559,7 +586,11 @@ void PhyloTree::flushPartialOps() {
 void PhyloTree::reduceResult(double *result) {
     double tot[LKCUDA_NRESULT];
     memset(tot, 0, sizeof(tot));
-    if (allreduce_ && engines_.size() == 1) {
+    if (peers_attached_) {
+        // the kernels already exchanged and added their blocks: every engine holds the same global sums
+        for (size_t d = 0; d < engines_.size(); d++)
+            check(lkcuda_wait_result(engines_[d], tot), engines_[d], "lkcuda_wait_result");
+    } else if (allreduce_ && engines_.size() == 1) {
         void *dev = NULL;
         check(lkcuda_result_device_ptr(engines_[0], &dev), engines_[0], "lkcuda_result_device_ptr");
         allreduce_(allreduce_user_, NULL, dev, LKCUDA_NRESULT);
@@ -567,7 +598,7 @@ void PhyloTree::reduceResult(double *result) {
     } else {
         for (size_t d = 0; d < engines_.size(); d++) {
             double r[LKCUDA_NRESULT];
-            check(lkcuda_read_result(engines_[d], r), engines_[d], "lkcuda_read_result");
+            check(lkcuda_wait_result(engines_[d], r), engines_[d], "lkcuda_wait_result");
             for (int i = 0; i < LKCUDA_NRESULT; i++) tot[i] += r[i];
         }
         if (allreduce_) allreduce_(allreduce_user_, tot, NULL, LKCUDA_NRESULT);

@@ -98,6 +98,11 @@ public:
     void setProcessShard(int rank, int world) { proc_rank_ = rank; proc_world_ = world; }
     void setAllReduce(AllReduceFn fn, void *user) { allreduce_ = fn; allreduce_user_ = user; }
     void setStream(void *cuda_stream);
+    // fused cross-GPU all-reduce inside the reduction kernels (lkcuda_attach_peers), one engine per process: every rank
+    // exports peerHandle(), the host exchanges the handles by any transport and gives all of them to attachPeers()
+    void peerHandle(uint8_t *handle /*[LKCUDA_PEER_HANDLE_BYTES]*/);
+    void attachPeers(const uint8_t *handles /*[world][LKCUDA_PEER_HANDLE_BYTES]*/);
+    bool peersAttached() const { return peers_attached_; }
     void initializeAllPartialLh();
     void deleteAllPartialLh();
     int64_t localPatternBegin() const { return ptn_begin_; }
@@ -166,6 +171,7 @@ private:
     AllReduceFn allreduce_;
     void *allreduce_user_;
     void *stream_;
+    bool peers_attached_;                  // the engines' reduction kernels already return sums over all shards / ranks
     std::vector<lkcuda_engine*> engines_;
     std::vector<int64_t> shard_begin_;     // per engine, global pattern offsets (size engines+1)
     int64_t ptn_begin_, ptn_end_;

@@ -57,6 +57,8 @@ struct DevChild {
     double  len;
 };
 
+struct PeerMbox;
+
 /* everything a kernel needs to know about the engine, passed by value */
 struct DevView {
     int S, K, E, B;             /* states, blocks per pattern, eigensystems, B = S*K        */
@@ -76,6 +78,18 @@ struct DevView {
     /* per-child transition tables built by the prep kernel:
        slot c: ech[K*S*S] then tab[(SU+1)*B]                                                   */
     double *tables; long long table_slot;   /* doubles per slot */
+    /* result publication (publish_result): the host-mapped copy of the result block + the sequence number of this launch, and the
+       peer mailboxes of the fused cross-GPU all-reduce (lkcuda_attach_peers) */
+    double *host_result; unsigned int seq;
+    int peer_world, peer_rank; unsigned int peer_seq;
+    PeerMbox *const *peer_mbox;
+};
+
+/* one per engine, in cudaMalloc'ed (IPC-exportable) device memory: rank r writes its 8 sums into data[parity][r] of EVERY rank's
+   mailbox, then flag[parity][r] = sequence number; the owner adds the deposits in rank order once all flags show the number */
+struct PeerMbox {
+    double data[2][LKCUDA_MAX_PEERS][LKCUDA_NRESULT];
+    unsigned int flag[2][LKCUDA_MAX_PEERS];
 };
 
 }  // namespace lkc
@@ -94,6 +108,9 @@ struct lkcuda_engine {
     double *d_plh, *d_plhcat, *d_plh_out;   /* d_plh_out: scale-corrected copy of _pattern_lh on its way to the host (lazy) */
     double *d_red; unsigned int *d_counter; double *d_result;
     double *h_result;                       /* pinned */
+    double *h_mapped;                       /* pinned + mapped: [0..7] result block, [8] (as uint64) sequence number | error << 32, written by publish_result */
+    unsigned int result_seq;                /* sequence number of the last publishing launch */
+    lkc::PeerMbox *d_mbox; lkc::PeerMbox **d_peer_tab; void *peer_opened[LKCUDA_MAX_PEERS]; unsigned int peer_seq;
     double *d_newton_out; double *h_newton_out;
     /* transition tables */
     double *d_tables; long long table_slots_cap;
@@ -143,6 +160,12 @@ void drain_events(lkcuda_engine *e);
 
 inline bool valid_end(const lkcuda_engine *e, int32_t id) {
     return id >= 0 ? id < e->cfg.nvec : LKCUDA_TIP_TAXON(id) < e->cfg.ntaxa;
+}
+
+/* call right before launching a kernel that ends in publish_result(): stamps e->v with the launch's sequence numbers */
+inline void next_result(lkcuda_engine *e) {
+    e->v.seq = ++e->result_seq;
+    if (e->v.peer_world > 1) e->v.peer_seq = ++e->peer_seq;
 }
 
 /* implemented in lkcuda_partial.cu / lkcuda_reduce.cu */
@@ -233,6 +256,67 @@ __device__ __forceinline__ bool grid_reduce(double (&val)[N], double *sh, double
         *counter = 0u;
     }
     return threadIdx.x == 0;
+}
+
+/* ---- publication of a reduction's result block (called by ONE thread: the one grid_reduce returned true in) ----
+   1. fused cross-GPU all-reduce (only the scalar sums cross NVLink): the block goes straight into every peer's mailbox with
+      plain P2P stores, a release-store of the sequence number follows; the thread then waits for all ranks' numbers in its OWN mailbox
+      and adds the deposits in rank order - every rank gets bit-identical sums, no NCCL launch, no host round trip.  Slot 6
+      (log(1 - prob_const), read by asc_adjust_kernel) is replicated, not additive: it stays local.
+   2. the block is written to device memory (v.result) and to host-mapped memory followed by the sequence number, which
+      lkcuda_wait_result() polls instead of issuing a copy and a stream synchronisation. */
+__device__ __forceinline__ unsigned long long lk_globaltimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+static __device__ __noinline__ void publish_result(const DevView &v, double (&r)[LKCUDA_NRESULT]) {
+    unsigned int err = 0;
+    if (v.peer_world > 1) {
+        const int par = (int)(v.peer_seq & 1u);
+        for (int q = 0; q < v.peer_world; q++) {
+            volatile double *dst = v.peer_mbox[q]->data[par][v.peer_rank];
+#pragma unroll
+            for (int i = 0; i < LKCUDA_NRESULT; i++) dst[i] = r[i];
+        }
+        __threadfence_system();
+        for (int q = 0; q < v.peer_world; q++) {
+            unsigned int *f = &v.peer_mbox[q]->flag[par][v.peer_rank];
+            asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(f), "r"(v.peer_seq) : "memory");
+        }
+        PeerMbox *me = v.peer_mbox[v.peer_rank];
+        const unsigned long long t0 = lk_globaltimer();
+        for (int q = 0; q < v.peer_world && !err; q++) {
+            const unsigned int *f = &me->flag[par][q];
+            unsigned int seen;
+            for (;;) {
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
+                if (seen == v.peer_seq) break;
+                if (lk_globaltimer() - t0 > 10000000000ull) { err = 1; break; }      /* 10 s: a peer never launched its reduction */
+            }
+        }
+        if (!err) {
+            const double own6 = r[6];
+#pragma unroll
+            for (int i = 0; i < LKCUDA_NRESULT; i++) r[i] = 0.0;
+            for (int q = 0; q < v.peer_world; q++) {
+                const volatile double *src = me->data[par][q];
+#pragma unroll
+                for (int i = 0; i < LKCUDA_NRESULT; i++) r[i] += src[i];
+            }
+            r[6] = own6;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < LKCUDA_NRESULT; i++) v.result[i] = r[i];
+    if (v.host_result) {
+        volatile double *h = v.host_result;
+#pragma unroll
+        for (int i = 0; i < LKCUDA_NRESULT; i++) h[i] = r[i];
+        __threadfence_system();
+        *reinterpret_cast<volatile unsigned long long *>(v.host_result + LKCUDA_NRESULT) = (unsigned long long)v.seq | ((unsigned long long)err << 32);
+    }
 }
 
 }  // namespace lkc

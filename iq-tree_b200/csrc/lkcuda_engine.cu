@@ -11,6 +11,7 @@
 #include "lkcuda_traverse.cuh"
 #include <stdarg.h>
 #include <stdlib.h>
+#include <chrono>
 #include <new>
 
 static char g_create_err[512] = "";
@@ -158,6 +159,8 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     e->d_arena = NULL; e->d_scale = NULL; e->d_theta = NULL; e->d_theta_sc = NULL; e->d_theta_meta = NULL;
     e->d_plh = e->d_plhcat = e->d_plh_out = NULL; e->d_red = NULL; e->d_counter = NULL; e->d_result = NULL; e->h_result = NULL;
     e->d_newton_out = NULL; e->h_newton_out = NULL;
+    e->h_mapped = NULL; e->result_seq = 0; e->d_mbox = NULL; e->d_peer_tab = NULL; e->peer_seq = 0;
+    memset(e->peer_opened, 0, sizeof(e->peer_opened));
     e->d_tables = NULL; e->table_slots_cap = 0;
     for (int i = 0; i < lkcuda_engine::RING; i++) {
         e->h_ops[i] = e->d_ops[i] = NULL; e->h_child[i] = e->d_child[i] = NULL;
@@ -214,6 +217,8 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
 #undef ALLOC
     if (ok) { rc = cudaMallocHost((void **)&e->h_result, sizeof(double) * LKCUDA_NRESULT); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMallocHost((void **)&e->h_newton_out, sizeof(double) * 8); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaHostAlloc((void **)&e->h_mapped, sizeof(double) * (LKCUDA_NRESULT + 8), cudaHostAllocMapped); ok = rc == cudaSuccess; }
+    if (ok) memset(e->h_mapped, 0, sizeof(double) * (LKCUDA_NRESULT + 8));
     if (ok) { rc = cudaMallocHost((void **)&e->h_upload_vals, sizeof(unsigned int) * (lkcuda_engine::UPLOAD_MAX_CHUNKS + 1)); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMallocHost((void **)&e->h_upload_bad, sizeof(unsigned int) * 4); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaStreamCreateWithFlags(&e->cstream, cudaStreamNonBlocking); ok = rc == cudaSuccess; }
@@ -239,6 +244,12 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     v.pattern_lh = e->d_plh; v.pattern_lh_cat = e->d_plhcat;
     v.red = e->d_red; v.counter = e->d_counter; v.result = e->d_result;
     v.tables = NULL;
+    {   /* device-side address of the host-mapped result block (identical under UVA; asked for all the same) */
+        void *dp = NULL;
+        if (cudaHostGetDevicePointer(&dp, e->h_mapped, 0) == cudaSuccess) v.host_result = (double *)dp;
+        else { cudaGetLastError(); v.host_result = NULL; }
+    }
+    v.seq = 0; v.peer_world = 1; v.peer_rank = 0; v.peer_seq = 0; v.peer_mbox = NULL;
     *out = e;
     return LKCUDA_OK;
 }
@@ -262,6 +273,9 @@ int lkcuda_destroy(lkcuda_engine *e) {
     cudaFree(e->d_newton_out); cudaFree(e->d_tables); cudaFree(e->d_inv_frags);
     if (e->h_result) cudaFreeHost(e->h_result);
     if (e->h_newton_out) cudaFreeHost(e->h_newton_out);
+    if (e->h_mapped) cudaFreeHost(e->h_mapped);
+    for (int q = 0; q < LKCUDA_MAX_PEERS; q++) if (e->peer_opened[q]) cudaIpcCloseMemHandle(e->peer_opened[q]);
+    cudaFree(e->d_mbox); cudaFree(e->d_peer_tab);
     for (int i = 0; i < lkcuda_engine::RING; i++) {
         if (e->h_ops[i]) cudaFreeHost(e->h_ops[i]);
         if (e->h_child[i]) cudaFreeHost(e->h_child[i]);
@@ -459,6 +473,109 @@ int lkcuda_read_result(lkcuda_engine *e, double *result) {
     LK_CUDA(e, cudaStreamSynchronize(e->stream));
     memcpy(result, e->h_result, sizeof(double) * LKCUDA_NRESULT);
     return upload_verdict(e);
+}
+
+int lkcuda_wait_result(lkcuda_engine *e, double *result) {
+    LK_ENTER(e);
+    if (!result) return fail(e, LKCUDA_ERR_ARG, "null result");
+    if (!e->v.host_result || e->result_seq == 0) return lkcuda_read_result(e, result);
+    volatile unsigned long long *flag = reinterpret_cast<volatile unsigned long long *>(e->h_mapped + LKCUDA_NRESULT);
+    unsigned long long f = *flag;
+    if ((unsigned int)f != e->result_seq) {
+        auto next_query = std::chrono::steady_clock::now() + std::chrono::microseconds(200);
+        for (unsigned int spin = 0;; spin++) {
+            f = *flag;
+            if ((unsigned int)f == e->result_seq) break;
+#if defined(__x86_64__) || defined(__i386__)
+            __builtin_ia32_pause();
+#endif
+            if ((spin & 63u) == 63u && std::chrono::steady_clock::now() >= next_query) {
+                /* the stream drained (or died) without the number showing up: take the slow path, which also reports CUDA errors */
+                cudaError_t q = cudaStreamQuery(e->stream);
+                if (q != cudaErrorNotReady) {
+                    f = *flag;
+                    if (q == cudaSuccess && (unsigned int)f == e->result_seq) break;
+                    if (q != cudaSuccess) return cuda_fail(e, q, "reduction kernel");
+                    return lkcuda_read_result(e, result);
+                }
+                next_query = std::chrono::steady_clock::now() + std::chrono::microseconds(200);
+            }
+        }
+    }
+    __atomic_thread_fence(__ATOMIC_ACQUIRE);
+    for (int i = 0; i < LKCUDA_NRESULT; i++) result[i] = ((volatile double *)e->h_mapped)[i];
+    if ((f >> 32) & 1ull) return fail(e, LKCUDA_ERR_STATE, "cross-GPU all-reduce timed out: a peer never enqueued its reduction");
+    return upload_verdict(e);
+}
+
+int lkcuda_peer_handle(lkcuda_engine *e, uint8_t *handle, void **local_ptr) {
+    LK_ENTER(e);
+    if (!e->d_mbox) {
+        LK_CUDA(e, cudaMalloc((void **)&e->d_mbox, sizeof(PeerMbox)));     /* plain cudaMalloc: exportable through CUDA IPC */
+        LK_CUDA(e, cudaMemset(e->d_mbox, 0, sizeof(PeerMbox)));
+        LK_CUDA(e, cudaDeviceSynchronize());
+        e->peer_seq = 0;
+    }
+    if (handle) {
+        cudaIpcMemHandle_t h;
+        static_assert(sizeof(h) == LKCUDA_PEER_HANDLE_BYTES, "CUDA IPC handle size");
+        LK_CUDA(e, cudaIpcGetMemHandle(&h, e->d_mbox));
+        memcpy(handle, &h, sizeof(h));
+    }
+    if (local_ptr) *local_ptr = e->d_mbox;
+    return LKCUDA_OK;
+}
+
+int lkcuda_detach_peers(lkcuda_engine *e) {
+    LK_ENTER(e);
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    e->v.peer_world = 1; e->v.peer_rank = 0; e->v.peer_mbox = NULL;
+    for (int q = 0; q < LKCUDA_MAX_PEERS; q++)
+        if (e->peer_opened[q]) { cudaIpcCloseMemHandle(e->peer_opened[q]); e->peer_opened[q] = NULL; }
+    return LKCUDA_OK;
+}
+
+int lkcuda_attach_peers(lkcuda_engine *e, int32_t rank, int32_t world, const uint8_t *handles, void *const *raw_ptrs) {
+    LK_ENTER(e);
+    if (world < 1 || world > LKCUDA_MAX_PEERS || rank < 0 || rank >= world) return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_peers: bad rank / world (at most %d peers)", LKCUDA_MAX_PEERS);
+    if (!e->d_mbox) return fail(e, LKCUDA_ERR_STATE, "lkcuda_attach_peers: call lkcuda_peer_handle first");
+    if (world > 1 && !handles && !raw_ptrs) return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_peers: no peer addresses");
+    if (e->peer_seq != 0) return fail(e, LKCUDA_ERR_STATE, "lkcuda_attach_peers: the mailbox has already been used");
+    int rc0 = lkcuda_detach_peers(e);
+    if (rc0) return rc0;
+    PeerMbox *tab[LKCUDA_MAX_PEERS];
+    memset(tab, 0, sizeof(tab));
+    for (int q = 0; q < world; q++) {
+        if (q == rank) { tab[q] = e->d_mbox; continue; }
+        if (raw_ptrs && raw_ptrs[q]) {
+            cudaPointerAttributes at;
+            if (cudaPointerGetAttributes(&at, raw_ptrs[q]) != cudaSuccess || at.type != cudaMemoryTypeDevice) {
+                cudaGetLastError();
+                return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_peers: peer %d is not device memory", q);
+            }
+            if (at.device != e->device) {
+                int can = 0;
+                cudaDeviceCanAccessPeer(&can, e->device, at.device);
+                if (!can) return fail(e, LKCUDA_ERR_STATE, "lkcuda_attach_peers: device %d cannot access device %d", e->device, at.device);
+                cudaError_t pe = cudaDeviceEnablePeerAccess(at.device, 0);
+                if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(e, pe, "cudaDeviceEnablePeerAccess");
+                cudaGetLastError();
+            }
+            tab[q] = (PeerMbox *)raw_ptrs[q];
+        } else if (handles) {
+            cudaIpcMemHandle_t h;
+            memcpy(&h, handles + (size_t)q * LKCUDA_PEER_HANDLE_BYTES, sizeof(h));
+            void *p = NULL;
+            cudaError_t ie = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+            if (ie != cudaSuccess) { cudaGetLastError(); lkcuda_detach_peers(e); return cuda_fail(e, ie, "cudaIpcOpenMemHandle (peer mailbox)"); }
+            e->peer_opened[q] = p;
+            tab[q] = (PeerMbox *)p;
+        } else return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_peers: no address for peer %d", q);
+    }
+    if (!e->d_peer_tab) LK_CUDA(e, cudaMalloc((void **)&e->d_peer_tab, sizeof(tab)));
+    LK_CUDA(e, cudaMemcpy(e->d_peer_tab, tab, sizeof(tab), cudaMemcpyHostToDevice));
+    if (world > 1) { e->v.peer_world = world; e->v.peer_rank = rank; e->v.peer_mbox = e->d_peer_tab; }
+    return LKCUDA_OK;
 }
 
 int lkcuda_result_device_ptr(lkcuda_engine *e, void **p) {

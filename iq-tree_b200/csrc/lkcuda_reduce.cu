@@ -101,9 +101,8 @@ __device__ __forceinline__ void lnl_tail(const DevView &v, long long p, double l
 __device__ __forceinline__ void lnl_finish(const DevView &v, const double (&acc)[4], double scale_sum) {
     double lnl = acc[0] + scale_sum, lc = 0.0;
     if (v.U > 0) { lc = log(1.0 - acc[2]); lnl -= v.nsite * lc; }
-    v.result[LKCUDA_R_LNL] = lnl; v.result[LKCUDA_R_DF] = 0.0; v.result[LKCUDA_R_DDF] = 0.0;
-    v.result[LKCUDA_R_PROB_CONST] = acc[2]; v.result[LKCUDA_R_NREPAIRED] = acc[3]; v.result[LKCUDA_R_SCALE_SUM] = scale_sum;
-    v.result[6] = lc; v.result[7] = 0.0;
+    double r[LKCUDA_NRESULT] = {lnl, 0.0, 0.0, acc[2], acc[3], scale_sum, lc, 0.0};
+    publish_result(v, r);
 }
 
 /* ------------------------------------------------------------------ branch lnL ------------------------------------------------------------------ */
@@ -407,9 +406,8 @@ __device__ __forceinline__ void derv_finish(const DevView &v, const double (&acc
         df += v.nsite * df_frac;
         ddf += v.nsite * (ddf_frac + df_frac * df_frac);
     }
-    v.result[LKCUDA_R_LNL] = 0.0; v.result[LKCUDA_R_DF] = df; v.result[LKCUDA_R_DDF] = ddf;
-    v.result[LKCUDA_R_PROB_CONST] = 0.0; v.result[LKCUDA_R_NREPAIRED] = 0.0; v.result[LKCUDA_R_SCALE_SUM] = 0.0;
-    v.result[6] = 0.0; v.result[7] = 0.0;
+    double r[LKCUDA_NRESULT] = {0.0, df, ddf, 0.0, 0.0, 0.0, 0.0, 0.0};
+    publish_result(v, r);
 }
 
 __global__ void __launch_bounds__(RED_THREADS, 2) derv_b16_kernel(DevView v, double len) {
@@ -525,9 +523,8 @@ __global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) derv_kernel(De
     const int Bp = (v.B + 3) & ~3;
     DervOut o;
     if (derv_pass<VEC>(v, len, gshift, sh, sh + Bp, sh + 2 * Bp, sred, &o)) {
-        v.result[LKCUDA_R_LNL] = 0.0; v.result[LKCUDA_R_DF] = o.df; v.result[LKCUDA_R_DDF] = o.ddf;
-        v.result[LKCUDA_R_PROB_CONST] = 0.0; v.result[LKCUDA_R_NREPAIRED] = 0.0; v.result[LKCUDA_R_SCALE_SUM] = 0.0;
-        v.result[6] = 0.0; v.result[7] = 0.0;
+        double r[LKCUDA_NRESULT] = {0.0, o.df, o.ddf, 0.0, 0.0, 0.0, 0.0, 0.0};
+        publish_result(v, r);
     }
 }
 
@@ -589,7 +586,7 @@ static int check_ready(lkcuda_engine *e, const char *who) {
 
 static int finish_result(lkcuda_engine *e, double *result) {
     if (!result) return LKCUDA_OK;
-    return lkcuda_read_result(e, result);
+    return lkcuda_wait_result(e, result);
 }
 
 template <bool TIP>
@@ -609,6 +606,7 @@ static int enqueue_derv(lkcuda_engine *e, double len) {
     GroupShape gs = group_shape(v);
     int grid = red_grid(e, v.NP, gs.G);
     size_t sm = (size_t)3 * ((v.B + 3) & ~3) * 8;
+    next_result(e);
     launch_begin(e, KIND_DERV);
     if (gs.vec && v.B == 16) {      /* two resident blocks per SM, each lane keeps 2 x 128 bytes in flight */
         int g2 = e->num_sms * 2 < grid ? e->num_sms * 2 : grid;
@@ -636,6 +634,7 @@ int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     size_t tabsz = (size_t)(v.SU + 1) * v.B * 8;
     int use_tab = tip && (Bp * 8 + tabsz <= TAB_SMEM_LIMIT);
     size_t sm = Bp * 8 + (use_tab ? tabsz : 0);
+    next_result(e);
     launch_begin(e, KIND_BRANCH);
     if (tip && gs.vec && v.B == 16 && v.S == 4 && v.SU < 32) {
         int g2 = e->num_sms * 2 < grid ? e->num_sms * 2 : grid;
@@ -721,6 +720,7 @@ int lkcuda_theta_derv(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     const bool tip = LKCUDA_IS_TIP(dad);
     int grid = red_grid(e, v.NP, 1);
     if (grid > e->num_sms * 2) grid = e->num_sms * 2;
+    next_result(e);
     launch_begin(e, KIND_THETA);
     if (tip) theta_derv_b16_kernel<true><<<grid, RED_THREADS, 0, e->stream>>>(e->v, dad, node, len);
     else theta_derv_b16_kernel<false><<<grid, RED_THREADS, 0, e->stream>>>(e->v, dad, node, len);
@@ -746,6 +746,7 @@ int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result) {
     GroupShape gs = group_shape(v);
     int grid = red_grid(e, v.NP, gs.G);
     size_t sm = (size_t)((v.B + 3) & ~3) * 8;
+    next_result(e);
     launch_begin(e, KIND_FROMBUF);
     if (gs.vec) frombuf_kernel<true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
     else frombuf_kernel<false><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
@@ -768,7 +769,7 @@ int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, 
     if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_newton_branch: theta_all not built");
     int j, nev = 0, rc;
     double df, dx, f, temp, xh, xl, rts, rts_old, d2l, r[LKCUDA_NRESULT];
-#define FUNC_DERV(x) do { rc = enqueue_derv(e, (x)); if (rc) return rc; rc = lkcuda_read_result(e, r); if (rc) return rc; \
+#define FUNC_DERV(x) do { rc = enqueue_derv(e, (x)); if (rc) return rc; rc = lkcuda_wait_result(e, r); if (rc) return rc; \
                           f = -r[LKCUDA_R_DF]; df = -r[LKCUDA_R_DDF]; nev++; out[3] = (x); } while (0)
 #define NR_RETURN(x) do { out[0] = (x); out[1] = d2l; out[2] = (double)nev; return LKCUDA_OK; } while (0)
     rts = xguess;

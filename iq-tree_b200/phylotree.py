@@ -57,6 +57,10 @@ LKCUDA_SYMBOLS = {
     "lkcuda_lnl_from_buffer": (C.c_int, [C.c_void_p, C.c_double, c_double_p]),
     "lkcuda_newton_branch": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32, c_double_p]),
     "lkcuda_read_result": (C.c_int, [C.c_void_p, c_double_p]),
+    "lkcuda_wait_result": (C.c_int, [C.c_void_p, c_double_p]),
+    "lkcuda_peer_handle": (C.c_int, [C.c_void_p, c_uint8_p, C.POINTER(C.c_void_p)]),
+    "lkcuda_attach_peers": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_uint8_p, C.POINTER(C.c_void_p)]),
+    "lkcuda_detach_peers": (C.c_int, [C.c_void_p]),
     "lkcuda_result_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "lkcuda_set_result_buffer": (C.c_int, [C.c_void_p, C.c_void_p]),
     "lkcuda_fetch_pattern_lh": (C.c_int, [C.c_void_p, c_double_p]),
@@ -88,6 +92,9 @@ LKTREE_SYMBOLS = {
     "lktree_set_devices": (C.c_int, [C.c_void_p, c_int32_p, C.c_int32]),
     "lktree_set_process_shard": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
     "lktree_set_allreduce": (C.c_int, [C.c_void_p, ALLREDUCE_FN, C.c_void_p]),
+    "lktree_peer_handle": (C.c_int, [C.c_void_p, c_uint8_p]),
+    "lktree_attach_peers": (C.c_int, [C.c_void_p, c_uint8_p]),
+    "lktree_peers_attached": (C.c_int, [C.c_void_p]),
     "lktree_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "lktree_set_params": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_int32, C.c_int32]),
     "lktree_initialize_all_partial_lh": (C.c_int, [C.c_void_p]),
@@ -251,6 +258,20 @@ class PhyloTree:
 
         self._cb = ALLREDUCE_FN(tramp)
         self._ck(self.lib.lktree_set_allreduce(self.h, self._cb, None))
+
+    def peerHandle(self):
+        """CUDA IPC handle (64 bytes, numpy uint8) of this rank's all-reduce mailbox; exchange with every rank, then attachPeers()."""
+        h = np.zeros(64, dtype=np.uint8)
+        self._ck(self.lib.lktree_peer_handle(self.h, h.ctypes.data_as(c_uint8_p)))
+        return h
+
+    def attachPeers(self, handles):
+        """handles: uint8[world][64] in rank order. From now on every reduction kernel returns the sums over all ranks."""
+        a = np.ascontiguousarray(handles, dtype=np.uint8)
+        self._ck(self.lib.lktree_attach_peers(self.h, a.ctypes.data_as(c_uint8_p)))
+
+    def peersAttached(self):
+        return bool(self.lib.lktree_peers_attached(self.h))
 
     def setStream(self, cuda_stream):
         self._ck(self.lib.lktree_set_stream(self.h, C.c_void_p(cuda_stream)))

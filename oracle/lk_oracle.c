@@ -612,6 +612,14 @@ int lkcuda_read_result(lkcuda_engine *e, double *result) {
     memcpy(result, e->result, sizeof(e->result_own));
     return LKCUDA_OK;
 }
+int lkcuda_wait_result(lkcuda_engine *e, double *result) { return lkcuda_read_result(e, result); }
+/* the oracle has no devices and no peers: shards are summed by the host (lk_phylotree.cpp reduceResult) */
+int lkcuda_peer_handle(lkcuda_engine *e, uint8_t *handle, void **local_ptr) { (void)handle; (void)local_ptr; return e ? fail(e, LKCUDA_ERR_STATE, "the CPU oracle has no peer mailboxes") : LKCUDA_ERR_ARG; }
+int lkcuda_attach_peers(lkcuda_engine *e, int32_t rank, int32_t world, const uint8_t *handles, void *const *raw_ptrs) {
+    (void)rank; (void)world; (void)handles; (void)raw_ptrs;
+    return e ? fail(e, LKCUDA_ERR_STATE, "the CPU oracle has no peer mailboxes") : LKCUDA_ERR_ARG;
+}
+int lkcuda_detach_peers(lkcuda_engine *e) { return e ? LKCUDA_OK : LKCUDA_ERR_ARG; }
 int lkcuda_result_device_ptr(lkcuda_engine *e, void **p) { if (!e || !p) return LKCUDA_ERR_ARG; *p = e->result; return LKCUDA_OK; }
 int lkcuda_set_result_buffer(lkcuda_engine *e, void *ptr) { if (!e) return LKCUDA_ERR_ARG; e->result = ptr ? (double*)ptr : e->result_own; return LKCUDA_OK; }
 

@@ -89,14 +89,55 @@ def test_cuda_matches_oracle_synthetic(shape, cuda_lib, oracle_lib):
     a.close(); b.close()
 
 
-def test_two_shards_one_device(cuda_lib):
-    """pattern sharding: two engines on the same device give the sums of one (host-side reduction of the shards)"""
-    g = gu.Golden("dna_example_gtr_i_g4")
-    t = gu.build_tree(g, cuda_lib, devices=[0, 0])
+@pytest.mark.parametrize("host_sum", [False, True])
+@pytest.mark.parametrize("case,nshard", [("dna_example_gtr_i_g4", 2), ("dna_example_gtr_g4", 4), ("morph_mk_asc", 3), ("aa_lg_g4", 2)])
+def test_shards_one_device(case, nshard, host_sum, cuda_lib, monkeypatch):
+    """pattern sharding: N engines on the same device (each on its own stream) give the sums of one.  Default: the reduction kernels
+    exchange and add their result blocks among themselves through the peer mailboxes (fused all-reduce, lkcuda_attach_peers);
+    LKTREE_NO_PEERS=1: host-side sum of the shards."""
+    if host_sum:
+        monkeypatch.setenv("LKTREE_NO_PEERS", "1")
+    g = gu.Golden(case)
+    t = gu.build_tree(g, cuda_lib, devices=[0] * nshard)
     t.initializeAllPartialLh()
+    assert t.peersAttached() == (not host_sum)
     gu.check_likelihood(t, g)
     gu.check_derivatives(t, g)
     gu.check_optimize(t, g, full=False)
+    t.close()
+
+
+def test_wait_result_matches_read_result(cuda_lib):
+    """lkcuda_wait_result (host-mapped block + sequence number, no copy) returns what lkcuda_read_result copies back"""
+    import ctypes
+    g = gu.Golden("dna_example_gtr_g4")
+    t = gu.build_tree(g, cuda_lib)
+    t.initializeAllPartialLh()
+    lnl = t.computeLikelihood()
+    e = t.engine(0)
+    a = (ctypes.c_double * 8)(); b = (ctypes.c_double * 8)()
+    for _ in range(3):
+        assert cuda_lib.lkcuda_wait_result(e, a) == 0
+        assert cuda_lib.lkcuda_read_result(e, b) == 0
+        assert list(a) == list(b) and a[0] == lnl
+    t.close()
+
+
+def test_peer_attach_argument_checks(cuda_lib):
+    import ctypes
+    g = gu.Golden("dna_example_gtr_g4")
+    t = gu.build_tree(g, cuda_lib)
+    t.initializeAllPartialLh()
+    e = t.engine(0)
+    assert cuda_lib.lkcuda_attach_peers(e, 0, 2, None, None) != 0          # no mailbox yet
+    h = (ctypes.c_uint8 * 64)(); p = ctypes.c_void_p()
+    assert cuda_lib.lkcuda_peer_handle(e, h, ctypes.byref(p)) == 0 and p.value
+    assert any(h)
+    assert cuda_lib.lkcuda_attach_peers(e, 0, 17, None, None) != 0         # more than LKCUDA_MAX_PEERS
+    assert cuda_lib.lkcuda_attach_peers(e, 2, 2, None, None) != 0          # rank out of range
+    assert cuda_lib.lkcuda_attach_peers(e, 0, 2, None, None) != 0          # no addresses
+    assert cuda_lib.lkcuda_attach_peers(e, 0, 1, None, None) == 0          # a world of one: nothing to exchange
+    assert abs(t.computeLikelihood() - g.meta["lnl"]) <= gu.LNL_RTOL * abs(g.meta["lnl"])
     t.close()
 
 
