@@ -225,6 +225,34 @@ int lkcuda_vector_scale_factor(lkcuda_engine *e, int32_t vec, double *lh_scale_f
 /* raw device addresses of a vector (PhyloNeighbor::partial_lh / scale_num become these) */
 int lkcuda_vector_device_ptr(lkcuda_engine *e, int32_t vec, void **partial_lh, void **scale_num);
 
+/* ---- UFBoot RELL (IQTree::saveCurrentTree, iqtree.cpp:2676-2786; dotProductSIMD, phylokernel.h:55-61) ----
+   lkcuda_set_boot_samples: boot_samples[s][ptn] (float pattern frequencies of bootstrap replicate s, iqtree.cpp:300-340) of THIS
+   shard's patterns, row s at samples + s*stride; kept in HBM for the whole search, stored losslessly as uint8 / uint16 when all
+   entries are small non-negative integers (lkcuda_boot_storage tells which).
+   lkcuda_rell: rell[s] = sum_ptn boot_samples[s][ptn] * (float)ptn_lh[ptn], ptn_lh = _pattern_lh of the last branch-lnL plus the
+   scale_num correction of computePatternLikelihood (phylotree.cpp:1213-1259) taken from vectors vec_a / vec_b (-1 = a tip end).
+   Additive over shards; lkcuda_rell_device_ptr gives the device copy (double[nsamples]) for an NCCL sum.  rell may be NULL. */
+int lkcuda_set_boot_samples(lkcuda_engine *e, const float *samples, int32_t nsamples, int64_t stride);
+int lkcuda_boot_storage(lkcuda_engine *e, int32_t *bytes_per_entry, uint64_t *bytes);
+int lkcuda_rell(lkcuda_engine *e, int32_t vec_a, int32_t vec_b, double *rell /*[nsamples]*/);
+int lkcuda_rell_fetch(lkcuda_engine *e, double *rell /*[nsamples]*/);      /* the sums of the last lkcuda_rell (synchronises) */
+int lkcuda_rell_device_ptr(lkcuda_engine *e, void **dev_ptr);
+
+/* ---- consumers of _pattern_lh_cat (filled by lkcuda_pattern_lh_cat or a generic-kernel branch lnL) ----
+   lkcuda_lh_cat_collapse: the tail of PhyloTree::computePatternLhCat (phylotree.cpp:1133-1158) into a work matrix w[P][ncol]:
+     mode 0 = as is (ncol = ncat*nmix), 1 = per mixture class (WSL_MIXTURE, ncol = nmix), 2 = per rate category (WSL_RATECAT, ncol = ncat);
+     blocks are ordered m*ncat + c (phylokernelmixture.h:121); for plain / fused models pass nmix = 1.
+   lkcuda_lh_cat_em: one EM pass (ModelMixture::optimizeWeights, model/modelmixture.cpp:1369-1388; RateFree::optimizeWithEM,
+     model/ratefree.cpp:499-520): w[p][c] *= ratio[c] (ratio may be NULL), sums[c] = sum_p w[p][c] * ptn_freq[p] / (ptn_invar[p] + sum_c w[p][c]).
+     Additive over shards.  ncol <= 96.
+   lkcuda_lh_cat_pattern_rates: RateGamma::computePatternRates (model/rategamma.cpp:235-257): posterior mean rate and most likely
+     category of every pattern (exact ties: first maximum; the reference tosses a coin).  invar_class != 0: RateGammaInvar's variant
+     (model/rategammainvar.cpp:193-221) - ptn_invar joins the denominator and competes as category 0, the others become c + 1. */
+int lkcuda_lh_cat_collapse(lkcuda_engine *e, int32_t mode, int32_t ncat, int32_t nmix, int32_t *ncol);
+int lkcuda_lh_cat_em(lkcuda_engine *e, const double *ratio /*[ncol] or NULL*/, double *sums /*[ncol]*/);
+int lkcuda_lh_cat_pattern_rates(lkcuda_engine *e, const double *rates /*[ncol]*/, int32_t invar_class, double *ptn_rates /*[P]*/, int32_t *ptn_cat /*[P]*/);
+int lkcuda_fetch_lh_cat_collapsed(lkcuda_engine *e, double *w /*[P][ncol]*/);
+
 /* ---- instrumentation ---- */
 /* kernels launched by this engine since creation (bench.py's gpu_launches) */
 int lkcuda_launch_count(const lkcuda_engine *e, uint64_t *count);
@@ -236,7 +264,8 @@ int lkcuda_reset_counters(lkcuda_engine *e);
    getRealTime instrumentation, phylokernel.h:85, timeutil.h:134) */
 enum {
     LKCUDA_KIND_PREP = 0, LKCUDA_KIND_PARTIAL = 1, LKCUDA_KIND_BRANCH = 2, LKCUDA_KIND_THETA = 3,
-    LKCUDA_KIND_DERV = 4, LKCUDA_KIND_FROMBUF = 5, LKCUDA_KIND_NEWTON = 6, LKCUDA_KIND_MISC = 7, LKCUDA_NKIND = 8
+    LKCUDA_KIND_DERV = 4, LKCUDA_KIND_FROMBUF = 5, LKCUDA_KIND_NEWTON = 6, LKCUDA_KIND_MISC = 7, LKCUDA_KIND_RELL = 8,
+    LKCUDA_KIND_EM = 9, LKCUDA_NKIND = 10
 };
 int lkcuda_set_profiling(lkcuda_engine *e, int32_t on);
 int lkcuda_kernel_stats(lkcuda_engine *e, int32_t kind, uint64_t *launches, uint64_t *bytes, double *device_ms);

@@ -47,6 +47,16 @@ int lktree_get_tree_string(lktree *h, char *buf, size_t buflen);
 int lktree_set_devices(lktree *h, const int32_t *devices, int32_t n);        /* in-process shards, one per device */
 int lktree_set_process_shard(lktree *h, int32_t rank, int32_t world);        /* one process per GPU */
 int lktree_set_allreduce(lktree *h, lktree_allreduce_fn fn, void *user);
+/* consumers of the kernels' per-pattern outputs, on the device.
+   lktree_set_boot_samples / lktree_compute_rell: IQTree::saveCurrentTree's RELL dot products (iqtree.cpp:2689-2735), samples = boot_samples
+   [nsamples][nptn] float; rell[nsamples] for the branch of the last computeLikelihood.
+   lktree_optimize_mixture_weights: ModelMixture::optimizeWeights (model/modelmixture.cpp:1356-1416): EM on the class weights, returns
+   the new lnL and (optionally) the nmix weights.
+   lktree_compute_pattern_rates: RateGamma::computePatternRates (model/rategamma.cpp:235-257), outputs for this process' patterns. */
+int lktree_set_boot_samples(lktree *h, const float *samples, int32_t nsamples);
+int lktree_compute_rell(lktree *h, double *rell);
+int lktree_optimize_mixture_weights(lktree *h, double *lnl, double *weights);
+int lktree_compute_pattern_rates(lktree *h, double *pattern_rates, int32_t *pattern_cat);
 /* fused cross-GPU all-reduce inside the reduction kernels (lkcuda_peer_handle / lkcuda_attach_peers), one process per GPU:
    every rank exports its handle (LKCUDA_PEER_HANDLE_BYTES), the host exchanges them and passes all `world` of them in rank order */
 int lktree_peer_handle(lktree *h, uint8_t *handle);

@@ -70,6 +70,17 @@ int lktree_set_devices(lktree *h, const int32_t *devices, int32_t n) {
 }
 int lktree_set_process_shard(lktree *h, int32_t rank, int32_t world) { LK_TRY(h) h->tree.setProcessShard(rank, world); LK_CATCH(h) }
 int lktree_set_allreduce(lktree *h, lktree_allreduce_fn fn, void *user) { LK_TRY(h) h->tree.setAllReduce(fn, user); LK_CATCH(h) }
+int lktree_set_boot_samples(lktree *h, const float *samples, int32_t nsamples) { LK_TRY(h) h->tree.setBootSamples(samples, nsamples); LK_CATCH(h) }
+int lktree_compute_rell(lktree *h, double *rell) { LK_TRY(h) h->tree.computeRell(rell); LK_CATCH(h) }
+int lktree_optimize_mixture_weights(lktree *h, double *lnl, double *weights) {
+    LK_TRY(h)
+    *lnl = h->tree.optimizeMixtureWeights();
+    if (weights) memcpy(weights, &h->tree.mixtureWeights()[0], h->tree.mixtureWeights().size() * sizeof(double));
+    LK_CATCH(h)
+}
+int lktree_compute_pattern_rates(lktree *h, double *pattern_rates, int32_t *pattern_cat) {
+    LK_TRY(h) h->tree.computePatternRates(pattern_rates, pattern_cat); LK_CATCH(h)
+}
 int lktree_peer_handle(lktree *h, uint8_t *handle) { LK_TRY(h) h->tree.peerHandle(handle); LK_CATCH(h) }
 int lktree_attach_peers(lktree *h, const uint8_t *handles) { LK_TRY(h) h->tree.attachPeers(handles); LK_CATCH(h) }
 int lktree_peers_attached(lktree *h) { return h && h->tree.peersAttached() ? 1 : 0; }

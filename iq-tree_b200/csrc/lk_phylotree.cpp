@@ -28,7 +28,7 @@ PhyloTree::PhyloTree()
       device_newton(false), generic_kernel(false), current_it(NULL), current_it_back(NULL),
       theta_computed(false), num_partial_lh_computations(0), nstates(0), ncat(1), nmix(1), family(FAMILY_PLAIN),
       state_unknown(0), seq_type(SEQ_DNA), ntaxa(0), nptn(0), nunobs(0), nsite(0), p_invar_(0.0),
-      proc_rank_(0), proc_world_(1), allreduce_(NULL), allreduce_user_(NULL), stream_(NULL), peers_attached_(false),
+      proc_rank_(0), proc_world_(1), allreduce_(NULL), allreduce_user_(NULL), stream_(NULL), peers_attached_(false), boot_nsamples_(0),
       ptn_begin_(0), ptn_end_(0), tip_partial_lh_computed_(false), weights_uploaded_(false), model_uploaded_(false),
       freq_dirty_(true), invar_dirty_(true), model_dirty_(true), nvec_(0) {}
 
@@ -710,7 +710,7 @@ double PhyloTree::computeLikelihood(double *pattern_lh) {   // phylotree.cpp:103
 
 /* phylotree.cpp:1108-1160: per-category pattern likelihoods on current_it (picked like the reference when unset);
    wsl: 2 = WSL_RATECAT, 3 = WSL_MIXTURE, 4 = WSL_MIXTURE_RATECAT (tools.h:406). Returns the entries per pattern. */
-int PhyloTree::computePatternLhCat(double *out, int wsl) {
+void PhyloTree::enqueuePatternLhCat() {
     if (engines_.empty()) initializeAllPartialLh();
     if (!current_it) {
         Node *leaf = findFarthestLeaf();   // findFirstFarLeaf (phylotree.cpp:1018) picks the same leaf: first maximal height
@@ -725,11 +725,16 @@ int PhyloTree::computePatternLhCat(double *out, int wsl) {
     if ((node_branch->partial_lh_computed & 1) == 0) computePartialLikelihood(node_branch, node);
     flushPartialOps();
     int32_t dad_end = dad->isLeaf() ? LKCUDA_TIP(dad->id) : node_branch->vec;
+    for (size_t d = 0; d < engines_.size(); d++)
+        check(lkcuda_pattern_lh_cat(engines_[d], dad_end, dad_branch->vec, dad_branch->length), engines_[d], "lkcuda_pattern_lh_cat");
+}
+
+int PhyloTree::computePatternLhCat(double *out, int wsl) {
+    enqueuePatternLhCat();
     int K = family == FAMILY_MIXTURE ? ncat * nmix : ncat;
     std::vector<double> raw((size_t)(ptn_end_ - ptn_begin_) * K + 1);
     for (size_t d = 0; d < engines_.size(); d++) {
         int64_t b = shard_begin_[d] - ptn_begin_;
-        check(lkcuda_pattern_lh_cat(engines_[d], dad_end, dad_branch->vec, dad_branch->length), engines_[d], "lkcuda_pattern_lh_cat");
         check(lkcuda_fetch_pattern_lh_cat(engines_[d], &raw[b * K]), engines_[d], "lkcuda_fetch_pattern_lh_cat");
     }
     int64_t np = ptn_end_ - ptn_begin_;
@@ -754,6 +759,102 @@ int PhyloTree::computePatternLhCat(double *out, int wsl) {
     }
     memcpy(out, &raw[0], (size_t)np * K * 8);
     return K;
+}
+
+/* ---- the consumers of _pattern_lh_cat, run on the device (only ncol sums / P rates come back) ---- */
+
+/* the collapse of computePatternLhCat (phylotree.cpp:1133-1158) on every engine; returns the columns per pattern */
+int PhyloTree::collapsePatternLhCat(int wsl) {
+    int mode = 0, inner = ncat, outer = 1;
+    if (family == FAMILY_MIXTURE) {
+        outer = nmix;
+        if (wsl == 3 && ncat > 1) mode = 1; else if (wsl == 2 && nmix > 1) mode = 2;
+        if (wsl == 3 && ncat == 1) mode = 0;
+    }
+    int32_t ncol = 0;
+    for (size_t d = 0; d < engines_.size(); d++)
+        check(lkcuda_lh_cat_collapse(engines_[d], mode, inner, outer, &ncol), engines_[d], "lkcuda_lh_cat_collapse");
+    return ncol;
+}
+
+/* ModelMixture::optimizeWeights (model/modelmixture.cpp:1356-1416), statement for statement; the two passes over the patterns
+   (:1369-1388) are one kernel per EM step */
+double PhyloTree::optimizeMixtureWeights() {
+    if (family != FAMILY_MIXTURE) throw std::runtime_error("optimizeMixtureWeights: not a mixture model");
+    enqueuePatternLhCat();                               // phylo_tree->computePatternLhCat(WSL_MIXTURE)
+    int ncol = collapsePatternLhCat(3);
+    if (ncol != nmix) throw std::runtime_error("optimizeMixtureWeights: unexpected column count");
+    std::vector<double> new_prop(nmix), ratio_prop(nmix), part(nmix);
+    std::vector<double> &prop = mixprops_;
+    const bool has_invar = p_invar_ != 0.0;             // RateHeterogeneity::setPInvar is a no-op without an invariant class
+    for (int step = 0; step < nmix; step++) {
+        std::fill(new_prop.begin(), new_prop.end(), 0.0);
+        for (size_t d = 0; d < engines_.size(); d++) {
+            check(lkcuda_lh_cat_em(engines_[d], step > 0 ? &ratio_prop[0] : NULL, &part[0]), engines_[d], "lkcuda_lh_cat_em");
+            for (int c = 0; c < nmix; c++) new_prop[c] += part[c];
+        }
+        if (allreduce_) allreduce_(allreduce_user_, &new_prop[0], NULL, nmix);
+        bool converged = true;
+        double new_pinvar = 0.0;
+        for (int c = 0; c < nmix; c++) {
+            new_prop[c] /= (double)nsite;
+            converged = converged && (fabs(prop[c] - new_prop[c]) < 1e-4);
+            ratio_prop[c] = new_prop[c] / prop[c];
+            prop[c] = new_prop[c];
+            new_pinvar += prop[c];
+        }
+        new_pinvar = 1.0 - new_pinvar;
+        if (new_pinvar != 0.0) {
+            converged = converged && (fabs((has_invar ? p_invar_ : 0.0) - new_pinvar) < 1e-4);
+            if (has_invar) {
+                p_invar_ = new_pinvar;
+                computePtnInvar();
+                weights_uploaded_ = false;
+                ensureInputs();
+            }
+        }
+        if (converged) break;
+    }
+    // the weights only enter the branch reductions (val = exp(eval*rate*t)*prop): partials stay valid, the model goes up again
+    tip_partial_lh_computed_ = false; model_dirty_ = true;
+    return computeLikelihood();
+}
+
+/* RateGamma::computePatternRates (model/rategamma.cpp:235-257); with an invariant class (+I+G, p_invar != 0) RateGammaInvar's
+   variant (model/rategammainvar.cpp:193-221), whose categories are 0 = invariant, c + 1 = Gamma category c */
+int PhyloTree::computePatternRates(double *pattern_rates, int32_t *pattern_cat) {
+    enqueuePatternLhCat();                               // phylo_tree->computePatternLhCat(WSL_RATECAT)
+    int ncol = collapsePatternLhCat(2);
+    if (ncol != ncat) throw std::runtime_error("computePatternRates: unexpected column count");
+    for (size_t d = 0; d < engines_.size(); d++) {
+        int64_t b = shard_begin_[d] - ptn_begin_;
+        check(lkcuda_lh_cat_pattern_rates(engines_[d], &rates_[0], p_invar_ != 0.0 ? 1 : 0, pattern_rates + b, pattern_cat + b), engines_[d], "lkcuda_lh_cat_pattern_rates");
+    }
+    return p_invar_ != 0.0 ? ncat + 1 : ncat;
+}
+
+/* ---- UFBoot RELL (IQTree::saveCurrentTree, iqtree.cpp:2676-2786) ---- */
+void PhyloTree::setBootSamples(const float *samples, int nsamples) {     // boot_samples (iqtree.cpp:300-340), [nsamples][nptn]
+    if (engines_.empty()) initializeAllPartialLh();
+    boot_nsamples_ = nsamples;
+    for (size_t d = 0; d < engines_.size(); d++)
+        check(lkcuda_set_boot_samples(engines_[d], samples + shard_begin_[d], nsamples, nptn), engines_[d], "lkcuda_set_boot_samples");
+}
+
+/* rell[s] = dotProduct((float)computePatternLikelihood(), boot_samples[s]) (iqtree.cpp:2689-2735); the branch is current_it, whose
+   _pattern_lh the last computeLikelihood / computeLikelihoodBranch left behind */
+void PhyloTree::computeRell(double *rell) {
+    if (!current_it || !current_it_back) throw std::runtime_error("computeRell: no current branch (computeLikelihood first)");
+    if (boot_nsamples_ <= 0) throw std::runtime_error("computeRell: no bootstrap samples");
+    for (size_t d = 0; d < engines_.size(); d++)
+        check(lkcuda_rell(engines_[d], current_it->vec, current_it_back->vec, NULL), engines_[d], "lkcuda_rell");
+    std::vector<double> part(boot_nsamples_);
+    std::fill(rell, rell + boot_nsamples_, 0.0);
+    for (size_t d = 0; d < engines_.size(); d++) {
+        check(lkcuda_rell_fetch(engines_[d], &part[0]), engines_[d], "lkcuda_rell_fetch");
+        for (int s = 0; s < boot_nsamples_; s++) rell[s] += part[s];
+    }
+    if (allreduce_) allreduce_(allreduce_user_, rell, NULL, boot_nsamples_);
 }
 
 void PhyloTree::computeFuncDerv(double value, double &df, double &ddf) {   // phylotree.cpp:2135-2146

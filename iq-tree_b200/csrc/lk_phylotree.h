@@ -122,6 +122,12 @@ public:
     double computeLikelihoodFromBuffer();
     double computeLikelihood(double *pattern_lh = NULL);
     int computePatternLhCat(double *pattern_lh_cat, int wsl = 4);    // phylotree.cpp:1108-1160; returns entries per pattern
+    /* the consumers of _pattern_lh_cat and _pattern_lh on the device */
+    double optimizeMixtureWeights();                                 // ModelMixture::optimizeWeights, model/modelmixture.cpp:1356-1416
+    const std::vector<double> &mixtureWeights() const { return mixprops_; }
+    int computePatternRates(double *pattern_rates, int32_t *pattern_cat);   // RateGamma::computePatternRates, model/rategamma.cpp:235-257
+    void setBootSamples(const float *samples, int nsamples);         // boot_samples, iqtree.cpp:300-340
+    void computeRell(double *rell);                                  // IQTree::saveCurrentTree's dot products, iqtree.cpp:2689-2735
     void computeFuncDerv(double value, double &df, double &ddf);
     double minimizeNewton(double x1, double xguess, double x2, double xacc, double &d2l, int maxNRStep = 100);
     void optimizeOneBranch(Node *node1, Node *node2, bool clearLH = true, int maxNRStep = 100);
@@ -150,6 +156,8 @@ public:
 
 private:
     void flushPartialOps();
+    void enqueuePatternLhCat();
+    int collapsePatternLhCat(int wsl);
     void check(int rc, lkcuda_engine *e, const char *what);
     void reduceResult(double *result);
     Node *newNode();
@@ -171,6 +179,7 @@ private:
     AllReduceFn allreduce_;
     void *allreduce_user_;
     void *stream_;
+    int boot_nsamples_;
     bool peers_attached_;                  // the engines' reduction kernels already return sums over all shards / ranks
     std::vector<lkcuda_engine*> engines_;
     std::vector<int64_t> shard_begin_;     // per engine, global pattern offsets (size engines+1)

@@ -30,7 +30,7 @@ namespace lkc {
 
 enum KernelKind {
     KIND_PREP = 0, KIND_PARTIAL = 1, KIND_BRANCH = 2, KIND_THETA = 3, KIND_DERV = 4, KIND_FROMBUF = 5,
-    KIND_NEWTON = 6, KIND_MISC = 7, KIND_COUNT = 8
+    KIND_NEWTON = 6, KIND_MISC = 7, KIND_RELL = 8, KIND_EM = 9, KIND_COUNT = 10
 };
 
 /* cudaFuncAttributeMaxDynamicSharedMemorySize is a property of the FUNCTION (per context), not of an engine: every engine sets the
@@ -94,8 +94,11 @@ struct PeerMbox {
 
 }  // namespace lkc
 
+struct lkcuda_aux;      /* lkcuda_aux.cu: RELL matrix and _pattern_lh_cat work buffers (allocated on first use) */
+
 struct lkcuda_engine {
     lkcuda_config cfg;
+    lkcuda_aux *aux;
     lkc::DevView v;
     int device;
     cudaStream_t stream; bool own_stream;
@@ -157,6 +160,7 @@ int cuda_fail(lkcuda_engine *e, cudaError_t rc, const char *what);
 void launch_begin(lkcuda_engine *e, int kind);
 int launch_end(lkcuda_engine *e, int kind, uint64_t algorithmic_bytes, const char *what);
 void drain_events(lkcuda_engine *e);
+void aux_destroy(lkcuda_engine *e);
 
 inline bool valid_end(const lkcuda_engine *e, int32_t id) {
     return id >= 0 ? id < e->cfg.nvec : LKCUDA_TIP_TAXON(id) < e->cfg.ntaxa;

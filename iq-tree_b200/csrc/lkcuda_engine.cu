@@ -153,6 +153,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     lkcuda_engine *e = new (std::nothrow) lkcuda_engine();
     if (!e) return fail(NULL, LKCUDA_ERR_NOMEM, "out of host memory");
     /* lkcuda_engine holds std::vector members: value-initialise the POD part by hand */
+    e->aux = NULL;
     e->cfg = *cfg; e->device = cfg->device; e->stream = NULL; e->own_stream = false;
     e->d_states = NULL; e->d_freq = e->d_invar = NULL;
     e->d_eval = e->d_evec = e->d_inv = e->d_rate = e->d_weight = e->d_tip = NULL; e->d_eigen = NULL;
@@ -265,6 +266,7 @@ int lkcuda_destroy(lkcuda_engine *e) {
     if (e->h_upload_vals) cudaFreeHost(e->h_upload_vals);
     if (e->h_upload_bad) cudaFreeHost(e->h_upload_bad);
     drain_events(e);
+    aux_destroy(e);
     for (size_t i = 0; i < e->event_pool.size(); i++) cudaEventDestroy(e->event_pool[i]);
     cudaFree(e->d_states); cudaFree(e->d_freq); cudaFree(e->d_invar);
     cudaFree(e->d_eval); cudaFree(e->d_evec); cudaFree(e->d_inv); cudaFree(e->d_rate); cudaFree(e->d_weight); cudaFree(e->d_eigen);

@@ -25,7 +25,7 @@ ALLREDUCE_FN = C.CFUNCTYPE(None, C.c_void_p, c_double_p, C.c_void_p, C.c_int)
 NRESULT = 8
 R_LNL, R_DF, R_DDF, R_PROB_CONST, R_NREPAIRED, R_SCALE_SUM = 0, 1, 2, 3, 4, 5
 KIND_PREP, KIND_PARTIAL, KIND_BRANCH, KIND_THETA, KIND_DERV, KIND_FROMBUF, KIND_NEWTON, KIND_MISC = range(8)
-KIND_NAMES = ["prep", "partial", "branch", "theta", "derv", "frombuf", "newton", "misc"]
+KIND_NAMES = ["prep", "partial", "branch", "theta", "derv", "frombuf", "newton", "misc", "rell", "em"]
 FAMILY_PLAIN, FAMILY_MIXRATE, FAMILY_MIXTURE = 0, 1, 2
 SEQ_DNA, SEQ_PROTEIN, SEQ_BINARY, SEQ_MORPH, SEQ_MULTISTATE, SEQ_CODON = range(6)
 WSL_RATECAT, WSL_MIXTURE, WSL_MIXTURE_RATECAT = 2, 3, 4
@@ -62,6 +62,15 @@ LKCUDA_SYMBOLS = {
     "lkcuda_attach_peers": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_uint8_p, C.POINTER(C.c_void_p)]),
     "lkcuda_detach_peers": (C.c_int, [C.c_void_p]),
     "lkcuda_result_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "lkcuda_set_boot_samples": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.c_int32, C.c_int64]),
+    "lkcuda_boot_storage": (C.c_int, [C.c_void_p, c_int32_p, c_uint64_p]),
+    "lkcuda_rell": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_double_p]),
+    "lkcuda_rell_fetch": (C.c_int, [C.c_void_p, c_double_p]),
+    "lkcuda_rell_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "lkcuda_lh_cat_collapse": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_int32_p]),
+    "lkcuda_lh_cat_em": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
+    "lkcuda_lh_cat_pattern_rates": (C.c_int, [C.c_void_p, c_double_p, C.c_int32, c_double_p, c_int32_p]),
+    "lkcuda_fetch_lh_cat_collapsed": (C.c_int, [C.c_void_p, c_double_p]),
     "lkcuda_set_result_buffer": (C.c_int, [C.c_void_p, C.c_void_p]),
     "lkcuda_fetch_pattern_lh": (C.c_int, [C.c_void_p, c_double_p]),
     "lkcuda_fetch_pattern_lh_cat": (C.c_int, [C.c_void_p, c_double_p]),
@@ -92,6 +101,10 @@ LKTREE_SYMBOLS = {
     "lktree_set_devices": (C.c_int, [C.c_void_p, c_int32_p, C.c_int32]),
     "lktree_set_process_shard": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
     "lktree_set_allreduce": (C.c_int, [C.c_void_p, ALLREDUCE_FN, C.c_void_p]),
+    "lktree_set_boot_samples": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.c_int32]),
+    "lktree_compute_rell": (C.c_int, [C.c_void_p, c_double_p]),
+    "lktree_optimize_mixture_weights": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
+    "lktree_compute_pattern_rates": (C.c_int, [C.c_void_p, c_double_p, c_int32_p]),
     "lktree_peer_handle": (C.c_int, [C.c_void_p, c_uint8_p]),
     "lktree_attach_peers": (C.c_int, [C.c_void_p, c_uint8_p]),
     "lktree_peers_attached": (C.c_int, [C.c_void_p]),
@@ -258,6 +271,32 @@ class PhyloTree:
 
         self._cb = ALLREDUCE_FN(tramp)
         self._ck(self.lib.lktree_set_allreduce(self.h, self._cb, None))
+
+    # ---- RELL and the _pattern_lh_cat consumers --------------------------------------------------
+    def setBootSamples(self, samples):
+        """samples: float32[nsamples][nptn] bootstrap pattern frequencies (IQTree::boot_samples, iqtree.cpp:300-340)"""
+        a = np.ascontiguousarray(samples, dtype=np.float32)
+        self._nboot = a.shape[0]
+        self._ck(self.lib.lktree_set_boot_samples(self.h, a.ctypes.data_as(C.POINTER(C.c_float)), a.shape[0]))
+
+    def computeRell(self):
+        out = np.zeros(self._nboot, dtype=np.float64)
+        self._ck(self.lib.lktree_compute_rell(self.h, out.ctypes.data_as(c_double_p)))
+        return out
+
+    def optimizeMixtureWeights(self, nmix):
+        """ModelMixture::optimizeWeights: (lnL after the EM, new class weights)"""
+        lnl = C.c_double()
+        w = np.zeros(nmix, dtype=np.float64)
+        self._ck(self.lib.lktree_optimize_mixture_weights(self.h, C.byref(lnl), w.ctypes.data_as(c_double_p)))
+        return lnl.value, w
+
+    def computePatternRates(self):
+        b0, b1 = self.localPatterns()
+        r = np.zeros(b1 - b0, dtype=np.float64)
+        c = np.zeros(b1 - b0, dtype=np.int32)
+        self._ck(self.lib.lktree_compute_pattern_rates(self.h, r.ctypes.data_as(c_double_p), c.ctypes.data_as(c_int32_p)))
+        return r, c
 
     def peerHandle(self):
         """CUDA IPC handle (64 bytes, numpy uint8) of this rank's all-reduce mailbox; exchange with every rank, then attachPeers()."""

@@ -48,6 +48,8 @@ struct lkcuda_engine {
     double result_own[LKCUDA_NRESULT];
     double *result;                  /* result_own or a caller-supplied block (lkcuda_set_result_buffer) */
     uint64_t launches, bytes;
+    /* RELL matrix and the collapsed _pattern_lh_cat work matrix */
+    float *boot; int32_t nboot; double *rell; double *w; int32_t ncol;
     char err[256];
 };
 
@@ -99,6 +101,7 @@ int lkcuda_destroy(lkcuda_engine *e) {
     free(e->states); free(e->ptn_freq); free(e->ptn_invar); free(e->eval); free(e->evec); free(e->inv_evec);
     free(e->blk_eigen); free(e->blk_rate); free(e->blk_weight); free(e->tip_lh); free(e->own_arena); free(e->own_scale);
     free(e->theta); free(e->pattern_lh); free(e->pattern_lh_cat); free(e->theta_scale_num);
+    free(e->boot); free(e->rell); free(e->w);
     free(e);
     return LKCUDA_OK;
 }
@@ -645,6 +648,132 @@ int lkcuda_fetch_pattern_lh_cat(lkcuda_engine *e, double *dst) {
     memcpy(dst, e->pattern_lh_cat, (size_t)e->cfg.nptn * e->K * 8);
     return LKCUDA_OK;
 }
+/* ---- UFBoot RELL.  IQTree::saveCurrentTree (iqtree.cpp:2676-2786): pattern_lh[i] = (float)pattern_lh_orig[i] with
+   pattern_lh_orig from computePatternLikelihood (phylotree.cpp:1213-1259); rell = dotProduct(pattern_lh, boot_sample, nptn)
+   (iqtree.cpp:2733).  dotProductSIMD<float, Vec8f, 8> (phylokernel.h:55-61; AVX binding phylotreeavx.cpp:26) keeps 8 float lanes, lane j
+   accumulating entries j, j+8, j+16, ... with mul_add (a separate multiply and add without FMA hardware flags, vectorclass), and
+   ends with horizontal_add.  Restated lane by lane in float. ---- */
+int lkcuda_set_boot_samples(lkcuda_engine *e, const float *samples, int32_t nsamples, int64_t stride) {
+    if (!e || nsamples < 0 || (nsamples && !samples) || stride < e->cfg.nptn) return LKCUDA_ERR_ARG;
+    size_t P = (size_t)e->cfg.nptn;
+    free(e->boot); free(e->rell);
+    e->boot = (float *)calloc((size_t)nsamples * P + 1, sizeof(float));
+    e->rell = (double *)calloc((size_t)nsamples + 1, sizeof(double));
+    e->nboot = nsamples;
+    for (int32_t s = 0; s < nsamples; s++) memcpy(e->boot + (size_t)s * P, samples + (size_t)s * (size_t)stride, P * sizeof(float));
+    return LKCUDA_OK;
+}
+int lkcuda_boot_storage(lkcuda_engine *e, int32_t *bytes_per_entry, uint64_t *bytes) {
+    if (!e || !e->boot) return LKCUDA_ERR_STATE;
+    if (bytes_per_entry) *bytes_per_entry = 4;
+    if (bytes) *bytes = (uint64_t)e->nboot * (uint64_t)e->cfg.nptn * 4;
+    return LKCUDA_OK;
+}
+int lkcuda_rell(lkcuda_engine *e, int32_t vec_a, int32_t vec_b, double *rell) {
+    if (!e || vec_a >= e->cfg.nvec || vec_b >= e->cfg.nvec) return LKCUDA_ERR_ARG;
+    if (!e->boot) return fail(e, LKCUDA_ERR_STATE, "lkcuda_rell: no bootstrap samples");
+    size_t P = (size_t)e->cfg.nptn, Ppad = (P + 7) / 8 * 8;
+    float *x = (float *)calloc(Ppad + 8, sizeof(float)), *y = (float *)calloc(Ppad + 8, sizeof(float));
+    const int16_t *sa = vec_a >= 0 ? vec_sc(e, vec_a) : NULL, *sb = vec_b >= 0 ? vec_sc(e, vec_b) : NULL;
+    for (size_t p = 0; p < P; p++) {       /* phylotree.cpp:1216-1233 */
+        int sc = (sa && sa[p] > 0 ? sa[p] : 0) + (sb && sb[p] > 0 ? sb[p] : 0);
+        x[p] = (float)(sc ? e->pattern_lh[p] + sc * LOG_SCALING_THRESHOLD : e->pattern_lh[p]);
+    }
+    for (int32_t s = 0; s < e->nboot; s++) {
+        memcpy(y, e->boot + (size_t)s * P, P * sizeof(float));
+        volatile float lane[8];
+        for (int j = 0; j < 8; j++) lane[j] = x[j] * y[j];
+        for (size_t i = 8; i < Ppad; i += 8)
+            for (int j = 0; j < 8; j++) { volatile float pr = x[i + j] * y[i + j]; lane[j] = pr + lane[j]; }
+        /* horizontal_add(Vec8f) (vectorclass/vectorf256.h): hadd within 128-bit halves twice, then low + high */
+        volatile float h0 = lane[0] + lane[1], h1 = lane[2] + lane[3], h2 = lane[4] + lane[5], h3 = lane[6] + lane[7];
+        volatile float g0 = h0 + h1, g1 = h2 + h3;
+        volatile float r = g0 + g1;
+        e->rell[s] = (double)r;
+    }
+    free(x); free(y);
+    if (rell) memcpy(rell, e->rell, (size_t)e->nboot * 8);
+    return LKCUDA_OK;
+}
+int lkcuda_rell_fetch(lkcuda_engine *e, double *rell) { if (!e || !rell || !e->rell) return LKCUDA_ERR_STATE; memcpy(rell, e->rell, (size_t)e->nboot * 8); return LKCUDA_OK; }
+int lkcuda_rell_device_ptr(lkcuda_engine *e, void **p) { if (!e || !p || !e->rell) return LKCUDA_ERR_STATE; *p = e->rell; return LKCUDA_OK; }
+
+/* ---- consumers of _pattern_lh_cat ---- */
+int lkcuda_lh_cat_collapse(lkcuda_engine *e, int32_t mode, int32_t ncat, int32_t nmix, int32_t *ncol_out) {
+    if (!e || mode < 0 || mode > 2 || ncat < 1 || nmix < 1 || (size_t)ncat * (size_t)nmix != e->K) return LKCUDA_ERR_ARG;
+    size_t P = (size_t)e->cfg.nptn;
+    if (!e->w) e->w = (double *)calloc(P * e->K + 1, 8);
+    e->ncol = mode == 1 ? nmix : (mode == 2 ? ncat : ncat * nmix);
+    if (ncol_out) *ncol_out = e->ncol;
+    const double *lh_cat = e->pattern_lh_cat;
+    double *lh_res = e->w;
+    for (size_t ptn = 0; ptn < P; ptn++) {          /* phylotree.cpp:1133-1158 */
+        if (mode == 1) {
+            for (int m = 0; m < nmix; m++) {
+                double lh = lh_cat[0];
+                for (int c = 1; c < ncat; c++) lh += lh_cat[c];
+                lh_res[m] = lh;
+                lh_cat += ncat;
+            }
+            lh_res += nmix;
+        } else if (mode == 2) {
+            memcpy(lh_res, lh_cat, (size_t)ncat * 8);
+            lh_cat += ncat;
+            for (int m = 1; m < nmix; m++) {
+                for (int c = 0; c < ncat; c++) lh_res[c] += lh_cat[c];
+                lh_cat += ncat;
+            }
+            lh_res += ncat;
+        } else {
+            memcpy(lh_res, lh_cat, e->K * 8);
+            lh_cat += e->K; lh_res += e->K;
+        }
+    }
+    return LKCUDA_OK;
+}
+int lkcuda_lh_cat_em(lkcuda_engine *e, const double *ratio, double *sums) {
+    if (!e || !sums) return LKCUDA_ERR_ARG;
+    if (!e->w || e->ncol < 1) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lh_cat_em: call lkcuda_lh_cat_collapse first");
+    size_t P = (size_t)e->cfg.nptn, n = (size_t)e->ncol;
+    if (ratio)                                   /* modelmixture.cpp:1369-1377 */
+        for (size_t ptn = 0; ptn < P; ptn++)
+            for (size_t c = 0; c < n; c++) e->w[ptn * n + c] *= ratio[c];
+    memset(sums, 0, n * 8);
+    for (size_t ptn = 0; ptn < P; ptn++) {       /* modelmixture.cpp:1379-1388 */
+        const double *this_lk_cat = e->w + ptn * n;
+        double lk_ptn = e->ptn_invar[ptn];
+        for (size_t c = 0; c < n; c++) lk_ptn += this_lk_cat[c];
+        lk_ptn = e->ptn_freq[ptn] / lk_ptn;
+        for (size_t c = 0; c < n; c++) sums[c] += this_lk_cat[c] * lk_ptn;
+    }
+    return LKCUDA_OK;
+}
+int lkcuda_lh_cat_pattern_rates(lkcuda_engine *e, const double *rates, int32_t invar_class, double *ptn_rates, int32_t *ptn_cat) {
+    if (!e || !rates || !ptn_rates || !ptn_cat) return LKCUDA_ERR_ARG;
+    if (!e->w || e->ncol < 1) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lh_cat_pattern_rates: call lkcuda_lh_cat_collapse first");
+    size_t P = (size_t)e->cfg.nptn, n = (size_t)e->ncol;
+    for (size_t i = 0; i < P; i++) {             /* rategamma.cpp:244-257 / rategammainvar.cpp:202-219, ties: first maximum */
+        const double *lh_cat = e->w + i * n;
+        double sum_rate = 0.0, sum_lh = invar_class ? e->ptn_invar[i] : 0.0;
+        double best_lh = invar_class ? e->ptn_invar[i] : lh_cat[0];
+        size_t best = 0;
+        for (size_t c = 0; c < n; c++) {
+            sum_rate += rates[c] * lh_cat[c];
+            sum_lh += lh_cat[c];
+            if (lh_cat[c] > best_lh) { best = c + (invar_class ? 1 : 0); best_lh = lh_cat[c]; }
+        }
+        ptn_rates[i] = sum_rate / sum_lh;
+        ptn_cat[i] = (int32_t)best;
+    }
+    return LKCUDA_OK;
+}
+int lkcuda_fetch_lh_cat_collapsed(lkcuda_engine *e, double *dst) {
+    if (!e || !dst) return LKCUDA_ERR_ARG;
+    if (!e->w || e->ncol < 1) return fail(e, LKCUDA_ERR_STATE, "lkcuda_fetch_lh_cat_collapsed: call lkcuda_lh_cat_collapse first");
+    memcpy(dst, e->w, (size_t)e->cfg.nptn * (size_t)e->ncol * 8);
+    return LKCUDA_OK;
+}
+
 int lkcuda_fetch_vector(lkcuda_engine *e, int32_t vec, double *partial_lh, int16_t *scale_num) {
     if (!e || vec < 0 || vec >= e->cfg.nvec) return LKCUDA_ERR_ARG;
     if (partial_lh) memcpy(partial_lh, vec_lh(e, vec), e->nptn_all * e->block * 8);

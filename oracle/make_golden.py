@@ -8,6 +8,7 @@ runs only in the build container; the resulting fixtures are committed and trave
 
     python oracle/make_golden.py            # all cases
     python oracle/make_golden.py dna_example_gtr_g4 ...
+    python oracle/make_golden.py --aux      # tests/golden/aux/*.npz: RELL, pattern rates, mixture-weight EM of AUX_CASES
 
 Synthetic alignments (codon, deep DNA tree, morphological, multifurcating) are generated here with fixed seeds.
 """
@@ -204,6 +205,31 @@ def pack(case, d):
         case, meta["lnl"], P, U, B, n, len(keep), int((sc > 0).any(axis=0).sum()), os.path.getsize(path) / 1024))
 
 
+AUX_CASES = ["dna_example_gtr_g4", "dna_example_gtr_i_g4", "dna_deep_scaling", "aa_lg_g4", "aa_lg_c20_g4", "codon_mg_g4"]
+AUX_SAMPLES = 24
+
+
+def pack_aux(case, d):
+    m = json.load(open(os.path.join(d, "metax.json")))
+    P, ns = m["nptn"], m["nsamples"]
+    z = {"meta": json.dumps(m)}
+    z["boot_samples"] = rd(d, "boot_samples.f32", np.float32).reshape(ns, P)
+    z["rell"] = rd(d, "rell.f64", np.float64)
+    z["ptn_lh_full"] = rd(d, "ptn_lh_full.f64", np.float64)
+    if m["nrate_cat"]:
+        z["pattern_rates"] = rd(d, "pattern_rates.f64", np.float64)
+        z["pattern_cat"] = rd(d, "pattern_cat.i32", np.int32)
+    if m["has_em"]:
+        z["lhcat_mixture"] = rd(d, "lhcat_mixture.f64", np.float64).reshape(P, m["nmix"])
+        z["em_props_before"] = rd(d, "em_props_before.f64", np.float64)
+        z["em_props"] = rd(d, "em_props.f64", np.float64)
+    os.makedirs(os.path.join(OUT, "aux"), exist_ok=True)
+    path = os.path.join(OUT, "aux", case + ".npz")
+    np.savez_compressed(path, **z)
+    print("%-28s aux: lnl %.10f rell[0] %.6f rates %d em %d (em lnl %.10f)  %.0f KB" % (
+        case, m["lnl"], z["rell"][0], m["nrate_cat"], m["has_em"], m["em_lnl"], os.path.getsize(path) / 1024))
+
+
 def main():
     if not os.path.exists(HARNESS):
         raise SystemExit("build the reference first: make -f oracle/Makefile.ref -j8")
@@ -241,6 +267,17 @@ def main():
         "morph_mk_asc": ["-s", asc_aln, "-st", "MORPH", "-m", "MK+ASC", "-te", asc_tree],
         "bin_jc2_g4": ["-s", bin_aln, "-st", "BIN", "-m", "JC2+G4", "-te", bin_tree],
     }
+    if sys.argv[1:2] == ["--aux"]:
+        for case in (sys.argv[2:] or AUX_CASES):
+            d = os.path.join(tmp, "outx_" + case)
+            cmd = [HARNESS, "dumpx", d, str(AUX_SAMPLES)] + cases[case] + ["-nt", "1", "-seed", "1", "-pre", os.path.join(tmp, "runx_" + case)]
+            r = subprocess.run(cmd, cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            if r.returncode != 0:
+                print("%-28s aux FAILED:\n%s" % (case, r.stdout[-1500:]))
+                continue
+            pack_aux(case, d)
+        shutil.rmtree(tmp, ignore_errors=True)
+        return
     want = sys.argv[1:] or list(cases)
     for case in want:
         d = os.path.join(tmp, "out_" + case)

@@ -11,7 +11,11 @@
  *
  * The set-up sequence mirrors runTreeReconstruction (phyloanalysis.cpp:1611-1726).
  *
+ *   (3) dumps the SURVEY 8(f) consumers' golden values (dumpx): UFBoot RELL dot products of IQTree::saveCurrentTree, RateGamma::
+ *       computePatternRates and ModelMixture::optimizeWeights, all computed by the reference's own functions.
+ *
  * usage: ref_harness dump <outdir> <iqtree args: -s aln -m MODEL -te tree -nt N ...>
+ *        ref_harness dumpx <outdir> <nsamples> <iqtree args ...>
  *        ref_harness time <lnl_reps> <derv_reps> <oab_reps> <iqtree args ...>
  */
 #include <cstdio>
@@ -271,6 +275,87 @@ static int do_dump(int argc, char **argv) {
     return 0;
 }
 
+/* golden values of the consumers of _pattern_lh / _pattern_lh_cat from the reference's own functions */
+static int do_dumpx(int argc, char **argv) {
+    g_out = argv[2];
+    mkdir(g_out.c_str(), 0755);
+    int nsamples = atoi(argv[3]);
+    std::vector<char*> args; args.push_back(argv[0]);
+    for (int i = 4; i < argc; i++) args.push_back(argv[i]);
+    Params &params = Params::getInstance();
+    IQTree *tree = setup((int)args.size(), &args[0], params);
+    Alignment *aln = tree->aln;
+    ModelSubst *model = tree->getModel();
+    RateHeterogeneity *rate = tree->getRate();
+    bool fused = tree->getModelFactory()->fused_mix_rate;
+    size_t P = aln->size(), C = rate->getNRate(), M = model->getNMixtures();
+
+    tree->clearAllPartialLH();
+    double lnl = tree->computeLikelihood();
+
+    /* ---- RELL: the statements of IQTree::saveCurrentTree (iqtree.cpp:2689-2735) and of the boot_samples set-up (iqtree.cpp:300-338) ---- */
+    size_t maxnptn = get_safe_upper_limit_float(P);
+    BootValType *pattern_lh = aligned_alloc<BootValType>(maxnptn);
+    memset(pattern_lh, 0, maxnptn * sizeof(BootValType));
+    double *pattern_lh_orig = aligned_alloc<double>(P);
+    double cur_logl = lnl;
+    tree->computePatternLikelihood(pattern_lh_orig, &cur_logl);
+    for (size_t i = 0; i < P; i++) pattern_lh[i] = (float)pattern_lh_orig[i];
+    BootValType *mem = aligned_alloc<BootValType>(maxnptn * (size_t)nsamples);
+    memset(mem, 0, maxnptn * (size_t)nsamples * sizeof(BootValType));
+    std::vector<float> samples((size_t)nsamples * P);
+    std::vector<double> rell(nsamples);
+    VerboseMode saved_mode = verbose_mode;
+    verbose_mode = VB_QUIET;
+    for (int s = 0; s < nsamples; s++) {
+        IntVector this_sample;
+        aln->createBootstrapAlignment(this_sample, params.bootstrap_spec);
+        for (size_t j = 0; j < P; j++) { mem[s * maxnptn + j] = this_sample[j]; samples[s * P + j] = (float)this_sample[j]; }
+    }
+    verbose_mode = saved_mode;
+    for (int s = 0; s < nsamples; s++)
+        rell[s] = (tree->*(tree->dotProduct))(pattern_lh, mem + s * maxnptn, (int)P);
+    wbin("boot_samples.f32", &samples[0], samples.size() * sizeof(float));
+    wbin("rell.f64", &rell[0], rell.size() * 8);
+    wbin("ptn_lh_full.f64", pattern_lh_orig, P * 8);
+    int root_from = tree->current_it_back->node->id, root_to = tree->current_it->node->id;
+
+    /* ---- RateGamma::computePatternRates (model/rategamma.cpp:235-257); other rate models return 0 or their own estimate ---- */
+    int nrate_cat = 0;
+    {
+        DoubleVector pr; IntVector pc;
+        nrate_cat = rate->computePatternRates(pr, pc);
+        if (nrate_cat > 0 && pr.size() == P) {
+            std::vector<int> pci(pc.begin(), pc.end());
+            wbin("pattern_rates.f64", &pr[0], P * 8);
+            wbin("pattern_cat.i32", &pci[0], P * sizeof(int));
+        } else nrate_cat = 0;
+    }
+
+    /* ---- ModelMixture::optimizeWeights (model/modelmixture.cpp:1356-1416) ---- */
+    double em_lnl = 0.0; int has_em = 0;
+    if (model->isMixture() && !fused) {
+        ModelMixture *mm = (ModelMixture*)model;
+        tree->computePatternLhCat(WSL_MIXTURE);
+        wbin("lhcat_mixture.f64", tree->_pattern_lh_cat, P * M * 8);
+        std::vector<double> before(mm->prop, mm->prop + M);
+        em_lnl = mm->optimizeWeights();
+        wbin("em_props_before.f64", &before[0], M * 8);
+        wbin("em_props.f64", mm->prop, M * 8);
+        has_em = 1;
+    }
+    {
+        std::ofstream f((g_out + "/metax.json").c_str());
+        f << std::setprecision(17);
+        f << "{ \"nptn\": " << P << ", \"ncat\": " << C << ", \"nmix\": " << M << ", \"nsamples\": " << nsamples
+          << ", \"lnl\": " << lnl << ", \"root_branch\": [" << root_from << ", " << root_to << "]"
+          << ", \"nrate_cat\": " << nrate_cat << ", \"has_em\": " << has_em << ", \"em_lnl\": " << em_lnl
+          << ", \"dot_kernel\": \"" << (tree->sse == LK_EIGEN_SSE ? (instruction_set >= 7 ? "AVX" : "SSE") : "generic") << "\" }\n";
+    }
+    printf("dumpx lnl %.10f rell0 %.6f nrate_cat %d em %d em_lnl %.10f\n", lnl, rell[0], nrate_cat, has_em, em_lnl);
+    return 0;
+}
+
 static int do_time(int argc, char **argv) {
     int lnl_reps = atoi(argv[2]), derv_reps = atoi(argv[3]), oab_reps = atoi(argv[4]);
     std::vector<char*> args; args.push_back(argv[0]);
@@ -334,6 +419,7 @@ static int do_time(int argc, char **argv) {
 int main(int argc, char **argv) {
     if (argc >= 4 && !strcmp(argv[1], "dump")) return do_dump(argc, argv);
     if (argc >= 6 && !strcmp(argv[1], "time")) return do_time(argc, argv);
+    if (argc >= 5 && !strcmp(argv[1], "dumpx")) return do_dumpx(argc, argv);
     fprintf(stderr, "usage: %s dump <outdir> <iqtree args>\n       %s time <lnl_reps> <derv_reps> <oab_reps> <iqtree args>\n", argv[0], argv[0]);
     return 2;
 }
