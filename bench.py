@@ -37,7 +37,7 @@ NTAXA = int(os.environ.get("LK_BENCH_TAXA", 100))
 NPTN = int(os.environ.get("LK_BENCH_PATTERNS", 1000000))
 NCAT = 4
 SEED = 1
-UPLOAD_CHUNKS = int(os.environ.get("LK_BENCH_UPLOAD_CHUNKS", 16))
+UPLOAD_CHUNKS = int(os.environ.get("LK_BENCH_UPLOAD_CHUNKS", 0))     # 0 = about 2 MB per chunk, 2..16 chunks
 CPU_SAMPLE_SITES = int(os.environ.get("LK_BENCH_CPU_SITES", 200000))
 WORKLOAD = "synthetic DNA %d taxa x %d patterns, GTR+G4 (BASELINE configs[1])" % (NTAXA, NPTN)
 
@@ -265,14 +265,17 @@ def main():
             ok = torch.ones(1, dtype=torch.int32, device=dev)
             try:
                 t.attachPeers(torch.stack(allh).cpu().numpy())
-            except RuntimeError as ex:
+            except Exception as ex:
                 sys.stderr.write("rank %d: peer attach failed (%s); falling back to NCCL\n" % (rank, ex))
                 ok[0] = 0
             dist.all_reduce(ok, op=dist.ReduceOp.MIN)
             if int(ok[0]) == 1:
                 exchange = "peer"
-            else:
-                raise SystemExit("peer attach failed on some rank; rerun with LK_BENCH_EXCHANGE=nccl")
+            else:       # CUDA IPC unavailable on some rank: every rank goes back to the NCCL exchange
+                try:
+                    t.detachPeers()
+                except Exception:
+                    pass
         if exchange == "nccl":
             t.setAllReduce(allreduce)
         t.clearAllPartialLH()
@@ -349,10 +352,12 @@ def main():
     c_dp = ctypes.POINTER(ctypes.c_double)
     lnl_c = ctypes.c_double()
 
+    nchunks = UPLOAD_CHUNKS if UPLOAD_CHUNKS > 0 else max(2, min(16, (NTAXA * nloc) // (2 << 20)))
+
     def e2e_step():
-        # pipelined upload: the matrix goes up in 8 pattern ranges on the engine's copy stream while the traversal kernel already works
+        # pipelined upload: the matrix goes up in `nchunks` pattern ranges on the engine's copy stream while the traversal kernel already works
         # on the ranges that have arrived (its producer warp polls a per-chunk counter); nothing is pre-loaded, every byte is re-sent
-        rc = lib.lkcuda_set_tip_states_async(eng, ctypes.cast(pinned_states.data_ptr(), c_u8p), UPLOAD_CHUNKS)
+        rc = lib.lkcuda_set_tip_states_async(eng, ctypes.cast(pinned_states.data_ptr(), c_u8p), nchunks)
         if rc:
             raise RuntimeError(lib.lkcuda_last_error(eng).decode())
         t.clearAllPartialLH()

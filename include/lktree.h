@@ -61,6 +61,7 @@ int lktree_compute_pattern_rates(lktree *h, double *pattern_rates, int32_t *patt
    every rank exports its handle (LKCUDA_PEER_HANDLE_BYTES), the host exchanges them and passes all `world` of them in rank order */
 int lktree_peer_handle(lktree *h, uint8_t *handle);
 int lktree_attach_peers(lktree *h, const uint8_t *handles);
+int lktree_detach_peers(lktree *h);
 int lktree_peers_attached(lktree *h);
 int lktree_set_stream(lktree *h, void *cuda_stream);
 int lktree_set_params(lktree *h, double min_branch_length, double max_branch_length, int32_t device_newton, int32_t generic_kernel);

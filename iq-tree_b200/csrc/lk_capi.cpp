@@ -83,6 +83,7 @@ int lktree_compute_pattern_rates(lktree *h, double *pattern_rates, int32_t *patt
 }
 int lktree_peer_handle(lktree *h, uint8_t *handle) { LK_TRY(h) h->tree.peerHandle(handle); LK_CATCH(h) }
 int lktree_attach_peers(lktree *h, const uint8_t *handles) { LK_TRY(h) h->tree.attachPeers(handles); LK_CATCH(h) }
+int lktree_detach_peers(lktree *h) { LK_TRY(h) h->tree.detachPeers(); LK_CATCH(h) }
 int lktree_peers_attached(lktree *h) { return h && h->tree.peersAttached() ? 1 : 0; }
 int lktree_set_stream(lktree *h, void *stream) { LK_TRY(h) h->tree.setStream(stream); LK_CATCH(h) }
 

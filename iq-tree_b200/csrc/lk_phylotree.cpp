@@ -443,6 +443,11 @@ void PhyloTree::peerHandle(uint8_t *handle) {
     check(lkcuda_peer_handle(engines_[0], handle, NULL), engines_[0], "lkcuda_peer_handle");
 }
 
+void PhyloTree::detachPeers() {
+    for (size_t d = 0; d < engines_.size(); d++) check(lkcuda_detach_peers(engines_[d]), engines_[d], "lkcuda_detach_peers");
+    peers_attached_ = false;
+}
+
 void PhyloTree::attachPeers(const uint8_t *handles) {
     if (engines_.size() != 1) throw std::runtime_error("attachPeers: one engine per process expected");
     check(lkcuda_attach_peers(engines_[0], proc_rank_, proc_world_, handles, NULL), engines_[0], "lkcuda_attach_peers");

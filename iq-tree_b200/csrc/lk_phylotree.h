@@ -102,6 +102,7 @@ public:
     // exports peerHandle(), the host exchanges the handles by any transport and gives all of them to attachPeers()
     void peerHandle(uint8_t *handle /*[LKCUDA_PEER_HANDLE_BYTES]*/);
     void attachPeers(const uint8_t *handles /*[world][LKCUDA_PEER_HANDLE_BYTES]*/);
+    void detachPeers();
     bool peersAttached() const { return peers_attached_; }
     void initializeAllPartialLh();
     void deleteAllPartialLh();

@@ -107,6 +107,7 @@ LKTREE_SYMBOLS = {
     "lktree_compute_pattern_rates": (C.c_int, [C.c_void_p, c_double_p, c_int32_p]),
     "lktree_peer_handle": (C.c_int, [C.c_void_p, c_uint8_p]),
     "lktree_attach_peers": (C.c_int, [C.c_void_p, c_uint8_p]),
+    "lktree_detach_peers": (C.c_int, [C.c_void_p]),
     "lktree_peers_attached": (C.c_int, [C.c_void_p]),
     "lktree_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "lktree_set_params": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_int32, C.c_int32]),
@@ -308,6 +309,9 @@ class PhyloTree:
         """handles: uint8[world][64] in rank order. From now on every reduction kernel returns the sums over all ranks."""
         a = np.ascontiguousarray(handles, dtype=np.uint8)
         self._ck(self.lib.lktree_attach_peers(self.h, a.ctypes.data_as(c_uint8_p)))
+
+    def detachPeers(self):
+        self._ck(self.lib.lktree_detach_peers(self.h))
 
     def peersAttached(self):
         return bool(self.lib.lktree_peers_attached(self.h))

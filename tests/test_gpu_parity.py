@@ -296,3 +296,46 @@ def test_pipelined_tip_state_upload(nchunks, cuda_lib, oracle_lib):
     assert cuda_lib.lkcuda_synchronize(eng) == 1      # LKCUDA_ERR_ARG
     assert b"out of range" in cuda_lib.lkcuda_last_error(eng)
     a.close(); b.close()
+
+
+def _subset_tree(g, lib, npat, devices=None):
+    """the fixture's tree and model on its first `npat` patterns only"""
+    from iqtree_b200 import PhyloTree
+    m = g.meta
+    t = PhyloTree(lib=lib)
+    st = g["tip_states"]
+    t.setAlignment(st[:, :npat], g["ptn_freq"][:npat], names=[str(x) for x in g["taxa"]], seq_type=m["seq_type"],
+                   nstates=m["nstates"], state_unknown=m["state_unknown"])
+    t.setConstChar(g["const_char"][:npat])
+    t.readAdjacency(str(g["tree_adj"]))
+    t.setModel(gu.FAMILY[m["family"]], m["ncat"], m["nmix"], g["eval"], g["evec"], g["inv_evec"], g["rates"], g["props"],
+               g["mixprops"], g["state_freq"], m["p_invar"])
+    t.setParams(m["min_branch_length"], m["max_branch_length"])
+    if devices is not None:
+        t.setDevices(devices)
+    return t
+
+
+@pytest.mark.parametrize("npat,nshard", [(1, 1), (3, 5), (33, 2), (257, 4)])
+def test_ragged_and_empty_shards(npat, nshard, cuda_lib, oracle_lib):
+    """edge sizes: a single pattern, fewer patterns than shards (EMPTY shards still take part in the fused all-reduce), sizes that are
+    not multiples of the kernels' tiles; checked against the oracle on the same truncated alignment"""
+    g = gu.Golden("dna_example_gtr_i_g4")
+    a = _subset_tree(g, cuda_lib, npat, devices=[0] * nshard)
+    b = _subset_tree(g, oracle_lib, npat)
+    a.initializeAllPartialLh(); b.initializeAllPartialLh()
+    la, lb = a.computeLikelihood(), b.computeLikelihood()
+    assert abs(la - lb) <= gu.LNL_RTOL * abs(lb)
+    _, pa = a.computeLikelihood(pattern_lh=True)
+    _, pb = b.computeLikelihood(pattern_lh=True)
+    gu.rel_close(pa, pb, gu.PTN_RTOL, "pattern_lh")
+    for (n1, n2) in a.getTraversal()[::7]:
+        da = a.computeLikelihoodDerv(int(n1), int(n2), reset_theta=True)
+        db = b.computeLikelihoodDerv(int(n1), int(n2), reset_theta=True)
+        tol = 1e-9 * max(abs(db[0]), abs(db[1]), 1.0)
+        assert abs(da[0] - db[0]) <= tol and abs(da[1] - db[1]) <= tol
+        fa, fb = a.computeLikelihoodFromBuffer(), b.computeLikelihoodFromBuffer()
+        assert abs(fa - fb) <= gu.LNL_RTOL * abs(fb)
+    oa, ob = a.optimizeAllBranches(1), b.optimizeAllBranches(1)
+    assert abs(oa - ob) <= gu.LNL_RTOL * abs(ob)
+    a.close(); b.close()

@@ -37,7 +37,7 @@ def main():
                    np.concatenate([c["inv_evec"].ravel() for c in comps]), mdl["rates"], mdl["props"], np.full(nmix, 1.0 / nmix), mdl["state_freq"], 0.0)
     else:
         t.setModel(0, C, 1, mdl["eval"], mdl["evec"], mdl["inv_evec"], mdl["rates"], mdl["props"], None, mdl["state_freq"], 0.0)
-    t.setParams(0.1 / nptn if nptn >= 100000 else 1e-6, 100.0)
+    t.setParams(0.1 / nptn if nptn >= 100000 else 1e-6, 100.0, device_newton="--devnewton" in sys.argv)
     t.initializeAllPartialLh()
     for _ in range(2):
         t.clearAllPartialLH(); lnl = t.computeLikelihood()
@@ -64,6 +64,9 @@ def main():
     if oab:
         t.clearAllPartialLH(); t.computeLikelihood()
         t0 = time.time(); l1 = t.optimizeAllBranches(1); out["oab1_s"] = time.time() - t0; out["oab1_lnl"] = l1
+        t.resetCounters()
+        t0 = time.time(); l2 = t.optimizeAllBranches(1); out["oab1_second_s"] = time.time() - t0; out["oab1_second_lnl"] = l2
+        out["oab_kernels"] = {k: {"n": v[0], "ms": v[2]} for k, v in t.kernelStats().items() if v[0]}
     print(json.dumps(out))
     t.close()
 
