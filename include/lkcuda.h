@@ -56,7 +56,12 @@ enum {
     LKCUDA_FLAG_ZERO_GUARD = 2,
     /* also fill _pattern_lh_cat in every branch-lnL call (the generic kernels always do,
        phylotreesse.cpp:1198,1225-1237; the SIMD kernels never do) */
-    LKCUDA_FLAG_PATTERN_LH_CAT = 4
+    LKCUDA_FLAG_PATTERN_LH_CAT = 4,
+    /* site-specific frequency models (-fs / PMSF; phylokernelsitemodel.cpp): every pattern has its own eigensystem
+       (ModelSet, models->at(ptn)).  neigen = number of DISTINCT site models, lkcuda_set_site_models maps patterns to them; blocks are
+       the rate categories; the scaling test has no ptn_invar condition and the lh_max == 0 branch refills with taxon 0's tip vector
+       (phylokernelsitemodel.cpp:306-335, 404-430).  nstates <= 32. */
+    LKCUDA_FLAG_SITEMODEL = 8
 };
 
 #define LKCUDA_TIP(taxon) (-1 - (int32_t)(taxon))
@@ -224,6 +229,14 @@ int lkcuda_fetch_theta(lkcuda_engine *e, double *theta /*[(P+U)*K*S]*/);
 int lkcuda_vector_scale_factor(lkcuda_engine *e, int32_t vec, double *lh_scale_factor);
 /* raw device addresses of a vector (PhyloNeighbor::partial_lh / scale_num become these) */
 int lkcuda_vector_device_ptr(lkcuda_engine *e, int32_t vec, void **partial_lh, void **scale_num);
+
+/* ---- site-specific frequency models (LKCUDA_FLAG_SITEMODEL) ----
+   ptn_model[p] = index of pattern p's eigensystem among the `neigen` given to lkcuda_set_model (ModelSet::pattern_model_map,
+   model/modelfactory.cpp:316-320); state_mask[s] = bit set of the plain states tip code s stands for (bit x set <=> state x
+   contributes): 1 << s for s < nstates, all ones for STATE_UNKNOWN, the ambiguity sets of phylotreesse.cpp:398-440 otherwise.  The
+   per-taxon, per-pattern tip vectors the reference precomputes (tip_partial_lh[taxon][ptn][S], phylotreesse.cpp:373-456) are
+   formed on the fly as sum over the set of inv_evec[i][x].  With this flag lkcuda_set_model ignores blk_eigen and tip_partial_lh. */
+int lkcuda_set_site_models(lkcuda_engine *e, const int32_t *ptn_model /*[P+U]*/, const uint64_t *state_mask /*[state_unknown+1]*/);
 
 /* ---- UFBoot RELL (IQTree::saveCurrentTree, iqtree.cpp:2676-2786; dotProductSIMD, phylokernel.h:55-61) ----
    lkcuda_set_boot_samples: boot_samples[s][ptn] (float pattern frequencies of bootstrap replicate s, iqtree.cpp:300-340) of THIS

@@ -39,6 +39,9 @@ int lktree_set_unobserved(lktree *h, const uint8_t *unobs, int32_t n);       /* 
 int lktree_set_model(lktree *h, int32_t family, int32_t ncat, int32_t nmix, const double *eval, const double *evec,
                      const double *inv_evec, const double *rates, const double *props, const double *mixprops,
                      const double *state_freq, double p_invar);
+/* family 3 = site-specific frequency models (-fs / PMSF, phylokernelsitemodel.cpp): nmix = number of distinct site models whose
+   eigensystems lktree_set_model receives; ptn_model[nptn] maps every pattern to one (ModelSet::pattern_model_map) */
+int lktree_set_site_models(lktree *h, const int32_t *ptn_model);
 int lktree_read_newick(lktree *h, const char *newick);
 int lktree_read_adjacency(lktree *h, const char *text);
 int lktree_get_tree_string(lktree *h, char *buf, size_t buflen);

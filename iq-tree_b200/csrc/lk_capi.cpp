@@ -54,6 +54,8 @@ int lktree_set_model(lktree *h, int32_t family, int32_t ncat, int32_t nmix, cons
     LK_TRY(h) h->tree.setModel(family, ncat, nmix, eval, evec, inv_evec, rates, props, mixprops, state_freq, p_invar); LK_CATCH(h)
 }
 
+int lktree_set_site_models(lktree *h, const int32_t *ptn_model) { LK_TRY(h) h->tree.setSiteModels(ptn_model); LK_CATCH(h) }
+
 int lktree_read_newick(lktree *h, const char *newick) { LK_TRY(h) h->tree.readTreeString(newick); LK_CATCH(h) }
 int lktree_read_adjacency(lktree *h, const char *text) { LK_TRY(h) h->tree.readAdjacency(text); LK_CATCH(h) }
 

@@ -286,6 +286,11 @@ void PhyloTree::setModel(int family_, int ncat_, int nmix_, const double *eval, 
     model_dirty_ = true;
 }
 
+void PhyloTree::setSiteModels(const int32_t *ptn_model) {
+    ptn_model_.assign(ptn_model, ptn_model + nptn);
+    if (!engines_.empty()) deleteAllPartialLh();
+}
+
 /* phylotreesse.cpp:459-527 */
 void PhyloTree::computeTipPartialLikelihood() {
     if (tip_partial_lh_computed_) return;
@@ -296,6 +301,7 @@ void PhyloTree::computeTipPartialLikelihood() {
     if (invar_dirty_) { computePtnInvar(); invar_dirty_ = false; weights_uploaded_ = false; }
     if (!model_dirty_) return;
     model_dirty_ = false; model_uploaded_ = false;
+    if (family == FAMILY_SITEMODEL) { tip_partial_lh.clear(); return; }   // per-pattern tip vectors are formed on the device (phylotreesse.cpp:373-456)
     int S = nstates, M = nmix;
     tip_partial_lh.assign((size_t)(state_unknown + 1) * S * M, 0.0);
     const double *all_inv_evec = &inv_evec_[0];
@@ -392,7 +398,8 @@ void PhyloTree::initializeAllPartialLh() {
         cfg.device = devs[d];
         cfg.nstates = nstates; cfg.nblocks = K; cfg.neigen = nmix; cfg.ntaxa = ntaxa;
         cfg.state_unknown = state_unknown; cfg.nvec = nvec_;
-        cfg.flags = (family != FAMILY_PLAIN ? LKCUDA_FLAG_SCALE_IGNORES_INVAR : 0) |
+        cfg.flags = (family == FAMILY_SITEMODEL ? LKCUDA_FLAG_SITEMODEL : 0) |
+                    (family != FAMILY_PLAIN ? LKCUDA_FLAG_SCALE_IGNORES_INVAR : 0) |
                     (generic_kernel ? (LKCUDA_FLAG_ZERO_GUARD | LKCUDA_FLAG_PATTERN_LH_CAT) : 0);
         cfg.nptn = shard_begin_[d + 1] - shard_begin_[d];
         cfg.nunobs = nunobs;
@@ -416,6 +423,21 @@ void PhyloTree::initializeAllPartialLh() {
             for (int64_t u = 0; u < nunobs; u++) st[(size_t)t * na + np + u] = unobs_[u];
         }
         check(lkcuda_set_tip_states(e, na ? &st[0] : (const uint8_t*)""), e, "lkcuda_set_tip_states");
+        if (family == FAMILY_SITEMODEL) {
+            if ((int64_t)ptn_model_.size() != nptn) throw std::runtime_error("site-specific model: setSiteModels first");
+            if (nunobs) throw std::runtime_error("site-specific models do not combine with +ASC");
+            // the states each tip code stands for (phylotreesse.cpp:386-440): plain, unknown, DNA / protein ambiguity codes
+            std::vector<uint64_t> mask((size_t)state_unknown + 1, 0);
+            const uint64_t all = nstates >= 64 ? ~0ull : ((1ull << nstates) - 1);
+            for (int s = 0; s <= state_unknown; s++) {
+                if (s < nstates) mask[s] = 1ull << s;
+                else if (s == state_unknown) mask[s] = all;
+                else if (seq_type == SEQ_DNA && nstates == 4) mask[s] = (uint64_t)(s - nstates + 1);
+                else if (seq_type == SEQ_PROTEIN && nstates == 20 && s < 23) { static const uint64_t ambi_aa[] = {4 + 8, 32 + 64, 512 + 1024}; mask[s] = ambi_aa[s - 20]; }
+            }
+            static const int32_t zero_model = 0;
+            check(lkcuda_set_site_models(e, np ? &ptn_model_[shard_begin_[d]] : &zero_model, &mask[0]), e, "lkcuda_set_site_models");
+        }
     }
     // several engines in ONE process, each on its own stream: their reduction kernels exchange and add the result blocks among
     // themselves (raw device addresses; peer access across devices), the host no longer sums anything.  With a caller-supplied
@@ -489,7 +511,7 @@ void PhyloTree::ensureInputs() {
             check(lkcuda_set_pattern_weights(e, np ? &ptn_freq[shard_begin_[d]] : &zero, &inv[0]), e, "lkcuda_set_pattern_weights");
         if (!model_uploaded_)
             check(lkcuda_set_model(e, &eval_[0], &evec_[0], &inv_evec_[0], &blk_eigen[0], &blk_rate[0], &blk_weight[0],
-                                   &tip_partial_lh[0]), e, "lkcuda_set_model");
+                                   tip_partial_lh.empty() ? NULL : &tip_partial_lh[0]), e, "lkcuda_set_model");
     }
     weights_uploaded_ = model_uploaded_ = true;
 }

@@ -62,7 +62,8 @@ struct Node {
 };
 
 enum SeqType { SEQ_DNA = 0, SEQ_PROTEIN = 1, SEQ_BINARY = 2, SEQ_MORPH = 3, SEQ_MULTISTATE = 4, SEQ_CODON = 5 };
-enum ModelFamily { FAMILY_PLAIN = 0, FAMILY_MIXRATE = 1, FAMILY_MIXTURE = 2 };
+enum ModelFamily { FAMILY_PLAIN = 0, FAMILY_MIXRATE = 1, FAMILY_MIXTURE = 2,
+                   FAMILY_SITEMODEL = 3 /* -fs / PMSF (phylokernelsitemodel.cpp): nmix = number of distinct site models, setSiteModels maps patterns to them */ };
 
 typedef void (*AllReduceFn)(void *user, double *host_buf /*may be NULL*/, void *dev_buf, int n);
 
@@ -90,6 +91,8 @@ public:
     void setModel(int family, int ncat, int nmix, const double *eval, const double *evec, const double *inv_evec,
                   const double *rates, const double *props, const double *mixprops,
                   const double *state_freq, double p_invar);
+
+    void setSiteModels(const int32_t *ptn_model);                   // ModelSet::pattern_model_map (model/modelfactory.cpp:316-320), [nptn]
 
     /* ---- engine / shards ---- */
     // devices: CUDA ordinals, one pattern shard per entry; shard_rank/shard_world further restrict this
@@ -171,7 +174,7 @@ private:
 
     std::vector<uint8_t> states_;          // [ntaxa][nptn] global
     std::vector<uint8_t> unobs_;
-    std::vector<int32_t> const_char_;
+    std::vector<int32_t> const_char_, ptn_model_;
     std::vector<double> freq_global_;
     std::vector<double> eval_, evec_, inv_evec_, rates_, props_, mixprops_, state_freq_;
     double p_invar_;

@@ -83,6 +83,8 @@ struct DevView {
     double *host_result; unsigned int seq;
     int peer_world, peer_rank; unsigned int peer_seq;
     PeerMbox *const *peer_mbox;
+    /* site-specific frequency models (LKCUDA_FLAG_SITEMODEL): pattern -> eigensystem, tip code -> set of plain states */
+    const int32_t *ptn_model; const unsigned long long *state_mask;
 };
 
 /* one per engine, in cudaMalloc'ed (IPC-exportable) device memory: rank r writes its 8 sums into data[parity][r] of EVERY rank's
@@ -108,6 +110,7 @@ struct lkcuda_engine {
     double *d_arena; int16_t *d_scale;      /* the engine's OWN arena; v.arena / v.scale may point at a caller-owned one (lkcuda_attach_arena) */
     long long own_vec_stride, own_sc_stride; int own_nvec;
     double *d_theta; int16_t *d_theta_sc; double *d_theta_meta;
+    int32_t *d_ptn_model; unsigned long long *d_state_mask;     /* LKCUDA_FLAG_SITEMODEL */
     double *d_plh, *d_plhcat, *d_plh_out;   /* d_plh_out: scale-corrected copy of _pattern_lh on its way to the host (lazy) */
     double *d_red; unsigned int *d_counter; double *d_result;
     double *h_result;                       /* pinned */
@@ -161,6 +164,7 @@ void launch_begin(lkcuda_engine *e, int kind);
 int launch_end(lkcuda_engine *e, int kind, uint64_t algorithmic_bytes, const char *what);
 void drain_events(lkcuda_engine *e);
 void aux_destroy(lkcuda_engine *e);
+void preload_reduce_kernels();      /* lkcuda_reduce.cu: force-load every reduction kernel (called when peers are attached) */
 
 inline bool valid_end(const lkcuda_engine *e, int32_t id) {
     return id >= 0 ? id < e->cfg.nvec : LKCUDA_TIP_TAXON(id) < e->cfg.ntaxa;

@@ -137,6 +137,8 @@ const char *lkcuda_last_error(const lkcuda_engine *e) { return e ? e->err : g_cr
 int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     if (!cfg || !out) return fail(NULL, LKCUDA_ERR_ARG, "null argument");
     *out = NULL;
+    if ((cfg->flags & LKCUDA_FLAG_SITEMODEL) && (cfg->nstates > 32 || cfg->nunobs > 0))
+        return fail(NULL, LKCUDA_ERR_ARG, "site-specific models: at most 32 states, no +ASC");
     if (cfg->nstates < 1 || cfg->nblocks < 1 || cfg->neigen < 1 || cfg->ntaxa < 1 || cfg->nptn < 0 ||
         cfg->nunobs < 0 || cfg->nvec < 0 || cfg->state_unknown < cfg->nstates || cfg->state_unknown > 255)
         return fail(NULL, LKCUDA_ERR_ARG, "invalid configuration");
@@ -160,6 +162,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     e->d_arena = NULL; e->d_scale = NULL; e->d_theta = NULL; e->d_theta_sc = NULL; e->d_theta_meta = NULL;
     e->d_plh = e->d_plhcat = e->d_plh_out = NULL; e->d_red = NULL; e->d_counter = NULL; e->d_result = NULL; e->h_result = NULL;
     e->d_newton_out = NULL; e->h_newton_out = NULL;
+    e->d_ptn_model = NULL; e->d_state_mask = NULL;
     e->h_mapped = NULL; e->result_seq = 0; e->d_mbox = NULL; e->d_peer_tab = NULL; e->peer_seq = 0;
     memset(e->peer_opened, 0, sizeof(e->peer_opened));
     e->d_tables = NULL; e->table_slots_cap = 0;
@@ -206,7 +209,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     ALLOC(e->d_freq, v.P + 4); ALLOC(e->d_invar, v.NP + 4);
     ALLOC(e->d_eval, v.E * v.S); ALLOC(e->d_evec, (size_t)v.E * v.S * v.S); ALLOC(e->d_inv, (size_t)v.E * v.S * v.S);
     ALLOC(e->d_rate, v.K); ALLOC(e->d_weight, v.K); ALLOC(e->d_eigen, v.K);
-    ALLOC(e->d_tip, (size_t)(v.SU + 1) * v.E * v.S);
+    ALLOC(e->d_tip, (cfg->flags & LKCUDA_FLAG_SITEMODEL) ? 4 : (size_t)(v.SU + 1) * v.E * v.S);
     ALLOC(e->d_arena, nvec * (size_t)v.vec_stride);
     ALLOC(e->d_scale, nvec * (size_t)v.sc_stride);
     ALLOC(e->d_theta, (size_t)v.vec_stride);
@@ -277,7 +280,7 @@ int lkcuda_destroy(lkcuda_engine *e) {
     if (e->h_newton_out) cudaFreeHost(e->h_newton_out);
     if (e->h_mapped) cudaFreeHost(e->h_mapped);
     for (int q = 0; q < LKCUDA_MAX_PEERS; q++) if (e->peer_opened[q]) cudaIpcCloseMemHandle(e->peer_opened[q]);
-    cudaFree(e->d_mbox); cudaFree(e->d_peer_tab);
+    cudaFree(e->d_mbox); cudaFree(e->d_peer_tab); cudaFree(e->d_ptn_model); cudaFree(e->d_state_mask);
     for (int i = 0; i < lkcuda_engine::RING; i++) {
         if (e->h_ops[i]) cudaFreeHost(e->h_ops[i]);
         if (e->h_child[i]) cudaFreeHost(e->h_child[i]);
@@ -450,19 +453,20 @@ int lkcuda_set_model(lkcuda_engine *e, const double *eval, const double *evec, c
                      const int32_t *blk_eigen, const double *blk_rate, const double *blk_weight,
                      const double *tip_partial_lh) {
     LK_ENTER(e);
-    if (!eval || !evec || !inv_evec || !blk_eigen || !blk_rate || !blk_weight || !tip_partial_lh)
-        return fail(e, LKCUDA_ERR_ARG, "null model argument");
     const DevView &v = e->v;
-    for (int k = 0; k < v.K; k++)
+    const bool sm = (v.flags & LKCUDA_FLAG_SITEMODEL) != 0;     /* blk_eigen and the tip table are not used: one eigensystem per pattern */
+    if (!eval || !evec || !inv_evec || !blk_rate || !blk_weight || (!sm && (!blk_eigen || !tip_partial_lh)))
+        return fail(e, LKCUDA_ERR_ARG, "null model argument");
+    for (int k = 0; k < v.K && !sm; k++)
         if (blk_eigen[k] < 0 || blk_eigen[k] >= v.E) return fail(e, LKCUDA_ERR_ARG, "blk_eigen out of range");
     size_t S = (size_t)v.S, E = (size_t)v.E, K = (size_t)v.K;
     LK_CUDA(e, cudaMemcpyAsync(e->d_eval, eval, E * S * 8, cudaMemcpyHostToDevice, e->stream));
     LK_CUDA(e, cudaMemcpyAsync(e->d_evec, evec, E * S * S * 8, cudaMemcpyHostToDevice, e->stream));
     LK_CUDA(e, cudaMemcpyAsync(e->d_inv, inv_evec, E * S * S * 8, cudaMemcpyHostToDevice, e->stream));
-    LK_CUDA(e, cudaMemcpyAsync(e->d_eigen, blk_eigen, K * 4, cudaMemcpyHostToDevice, e->stream));
+    if (!sm) LK_CUDA(e, cudaMemcpyAsync(e->d_eigen, blk_eigen, K * 4, cudaMemcpyHostToDevice, e->stream));
     LK_CUDA(e, cudaMemcpyAsync(e->d_rate, blk_rate, K * 8, cudaMemcpyHostToDevice, e->stream));
     LK_CUDA(e, cudaMemcpyAsync(e->d_weight, blk_weight, K * 8, cudaMemcpyHostToDevice, e->stream));
-    LK_CUDA(e, cudaMemcpyAsync(e->d_tip, tip_partial_lh, (size_t)(v.SU + 1) * E * S * 8, cudaMemcpyHostToDevice, e->stream));
+    if (!sm) LK_CUDA(e, cudaMemcpyAsync(e->d_tip, tip_partial_lh, (size_t)(v.SU + 1) * E * S * 8, cudaMemcpyHostToDevice, e->stream));
     LK_CUDA(e, cudaStreamSynchronize(e->stream));   /* the sources are pageable caller memory */
     e->model_set = true; e->theta_ready = false;
     return LKCUDA_OK;
@@ -576,7 +580,7 @@ int lkcuda_attach_peers(lkcuda_engine *e, int32_t rank, int32_t world, const uin
     }
     if (!e->d_peer_tab) LK_CUDA(e, cudaMalloc((void **)&e->d_peer_tab, sizeof(tab)));
     LK_CUDA(e, cudaMemcpy(e->d_peer_tab, tab, sizeof(tab), cudaMemcpyHostToDevice));
-    if (world > 1) { e->v.peer_world = world; e->v.peer_rank = rank; e->v.peer_mbox = e->d_peer_tab; }
+    if (world > 1) { preload_reduce_kernels(); e->v.peer_world = world; e->v.peer_rank = rank; e->v.peer_mbox = e->d_peer_tab; }
     return LKCUDA_OK;
 }
 

@@ -794,15 +794,16 @@ int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t
             return fail(e, LKCUDA_ERR_ARG, "partial op %d: a leaf child must be 'left' (phylokernel.h:116-121)", i);
         if (op.dst == op.left || op.dst == op.right) return fail(e, LKCUDA_ERR_ARG, "partial op %d: destination aliases a child", i);
     }
-    if (use_traverse(e->v)) {
+    const bool sitemodel = (e->v.flags & LKCUDA_FLAG_SITEMODEL) != 0;
+    if (!sitemodel && use_traverse(e->v)) {
         e->theta_ready = false;
         return launch_traverse(e, ops, nops);
     }
-    if (use_traverse_mma(e)) {
+    if (!sitemodel && use_traverse_mma(e)) {
         e->theta_ready = false;
         return launch_traverse_mma(e, ops, nops);
     }
-    if (use_traverse_mmak(e)) {
+    if (!sitemodel && use_traverse_mmak(e)) {
         e->theta_ready = false;
         return launch_traverse_mmak(e, ops, nops);
     }
@@ -822,6 +823,7 @@ int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t
         lbytes[l] += op_bytes(e->v, ntip, 2 - ntip);
     }
     e->theta_ready = false;
+    if (sitemodel) return launch_traverse_sitemodel(e, slot, nops);
     return launch_ops(e, slot, nops, 2 * nops, level_start, nlevels, &lbytes[0]);
 }
 
@@ -830,6 +832,7 @@ int lkcuda_partial_multi(lkcuda_engine *e, int32_t dst, int32_t nchild, const in
     if (!child || !child_len || nchild < 2 || dst < 0 || dst >= e->cfg.nvec) return fail(e, LKCUDA_ERR_ARG, "bad multifurcation arguments");
     if (!e->model_set || !e->states_set || !e->weights_set) return fail(e, LKCUDA_ERR_STATE, "lkcuda_partial_multi: inputs not set");
     for (int c = 0; c < nchild; c++) if (!valid_end(e, child[c]) || child[c] == dst) return fail(e, LKCUDA_ERR_ARG, "bad child");
+    if (e->v.flags & LKCUDA_FLAG_SITEMODEL) return fail(e, LKCUDA_ERR_ARG, "site-specific models need a bifurcating tree (phylokernelsitemodel.cpp:86)");
     int slot;
     int rc = ring_acquire(e, 1, nchild, &slot);
     if (rc) return rc;

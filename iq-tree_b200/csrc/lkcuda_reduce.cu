@@ -575,6 +575,114 @@ __global__ void __launch_bounds__(RED_THREADS) scale_factor_kernel(DevView v, in
     if (grid_reduce<1>(acc, sred, v.red, v.counter)) v.result[7] = acc[0];
 }
 
+
+/* ------------------------------------------------------------------ site-specific frequency models ------------------------------------------------------------------
+   SURVEY 8(f).3: computeSitemodelLikelihoodBranchEigen / DervEigen / FromBufferEigen (phylokernelsitemodel.cpp:548-660, 438-546, 663-703).
+   The eigenvalues differ per pattern, so there is no shared val[] table: a warp takes a pattern, lane i owns state i and forms
+   exp(eval_i * rate_c * len) itself; category sums by warp shuffles.  MODE 0: branch lnL (also fills _pattern_lh_cat, like the
+   reference's generic kernel), 1: theta_all, 2: df/ddf from theta_all, 3: lnL from theta_all. */
+template <int MODE>
+__global__ void __launch_bounds__(RED_THREADS) sitemodel_reduce_kernel(DevView v, int dad, int node, double len) {
+    __shared__ double sred[5 * 32];
+    const int lane = threadIdx.x & 31, ns = v.S;
+    const bool on = lane < ns;
+    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    const bool tip = (MODE <= 1) && LKCUDA_IS_TIP(dad);
+    const double *lh_node = MODE <= 1 ? vec_lh(v, node) : NULL, *lh_dad = (MODE <= 1 && !tip) ? vec_lh(v, dad) : NULL;
+    double acc4[4] = {0.0, 0.0, 0.0, 0.0}, acc5[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+    double theta_sc = 0.0;
+    for (long long p = warp0; p < v.NP; p += nwarps) {
+        const long long m = v.ptn_model[p];
+        const double ev = on ? v.eval[m * ns + lane] : 0.0;
+        double t = 0.0;
+        if (tip && on) {
+            const int state = tip_states(v, dad)[p];
+            const double *ivrow = v.inv_evec + m * ns * ns + lane * ns;
+            if (state < ns) t = ivrow[state];
+            else { const unsigned long long mask = v.state_mask[state]; for (int x = 0; x < ns; x++) if ((mask >> x) & 1ull) t += ivrow[x]; }
+        }
+        double lh_ptn = 0.0, df_ptn = 0.0, ddf_ptn = 0.0;
+        for (int c = 0; c < v.K; c++) {
+            const long long j = p * v.B + c * ns + lane;
+            double th = 0.0;
+            if (on) th = MODE <= 1 ? (tip ? t : lh_dad[j]) * lh_node[j] : v.theta[j];
+            if (MODE == 1) { if (on) v.theta[j] = th; continue; }
+            const double cof = ev * v.blk_rate[c];
+            double val = on ? exp(cof * len) * th : 0.0, val1 = cof * val, val2 = cof * val1;
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                val += __shfl_xor_sync(0xffffffffu, val, off);
+                if (MODE == 2) { val1 += __shfl_xor_sync(0xffffffffu, val1, off); val2 += __shfl_xor_sync(0xffffffffu, val2, off); }
+            }
+            const double prop = v.blk_weight[c];
+            if (MODE == 0 && lane == 0 && p < v.P) v.pattern_lh_cat[p * v.K + c] = val * prop;
+            lh_ptn += val * prop; df_ptn += val1 * prop; ddf_ptn += val2 * prop;
+        }
+        if (lane != 0) continue;
+        if (MODE == 1) {
+            const int sc = vec_sc(v, node)[p] + (tip ? 0 : vec_sc(v, dad)[p]);
+            if (sc && p < v.P) theta_sc += LK_LOG_THR * v.freq[p] * (double)sc;
+        } else if (MODE == 2) {
+            const double lh = 1.0 / fabs(lh_ptn + v.invar[p]);
+            const double df_frac = df_ptn * lh, ddf_frac = ddf_ptn * lh, f = v.freq[p], t1 = df_frac * f, t2 = ddf_frac * f;
+            acc5[0] += t1; acc5[1] += t2 - t1 * df_frac;
+        } else {
+            const int sc = MODE == 0 ? vec_sc(v, node)[p] + (tip ? 0 : vec_sc(v, dad)[p]) : 0;
+            lnl_tail(v, p, lh_ptn, sc, acc4);
+        }
+    }
+    if (MODE == 1) { double a[1] = {theta_sc}; if (grid_reduce<1>(a, sred, v.red, v.counter)) v.theta_meta[0] = a[0]; }
+    else if (MODE == 2) { if (grid_reduce<5>(acc5, sred, v.red, v.counter)) derv_finish(v, acc5); }
+    else if (grid_reduce<4>(acc4, sred, v.red, v.counter)) lnl_finish(v, acc4, MODE == 0 ? acc4[1] : v.theta_meta[0]);
+}
+
+/* With peers attached a reduction kernel waits, inside the kernel, for the other ranks' kernels.  When several engines are driven by ONE
+   host thread, nothing the host does between launching engine A's reduction and engine B's may wait for the device - and the FIRST launch
+   of a kernel does exactly that under CUDA's lazy module loading (the load synchronises with running kernels: A spins, the host is stuck
+   loading the follow-up kernel, B is never launched).  So every kernel of this file is loaded when peers are attached. */
+void lkc::preload_reduce_kernels() {
+    cudaFuncAttributes fa;
+#define PRELOAD(k) cudaFuncGetAttributes(&fa, k)
+    PRELOAD((branch_kernel<true, true>)); PRELOAD((branch_kernel<true, false>)); PRELOAD((branch_kernel<false, true>)); PRELOAD((branch_kernel<false, false>));
+    PRELOAD(branch_tip_b16_kernel); PRELOAD(asc_adjust_kernel); PRELOAD(pattern_lh_cat_kernel);
+    PRELOAD((theta_kernel<true, true>)); PRELOAD((theta_kernel<true, false>)); PRELOAD((theta_kernel<false, true>)); PRELOAD((theta_kernel<false, false>));
+    PRELOAD(derv_b16_kernel); PRELOAD(theta_derv_b16_kernel<true>); PRELOAD(theta_derv_b16_kernel<false>);
+    PRELOAD(derv_kernel<true>); PRELOAD(derv_kernel<false>); PRELOAD(frombuf_kernel<true>); PRELOAD(frombuf_kernel<false>);
+    PRELOAD(pattern_lh_corrected_kernel); PRELOAD(scale_factor_kernel);
+    PRELOAD(sitemodel_reduce_kernel<0>); PRELOAD(sitemodel_reduce_kernel<1>); PRELOAD(sitemodel_reduce_kernel<2>); PRELOAD(sitemodel_reduce_kernel<3>);
+#undef PRELOAD
+    cudaGetLastError();
+}
+
+static int sitemodel_reduce(lkcuda_engine *e, int mode, int dad, int node, double len) {
+    const DevView &v = e->v;
+    if (!v.ptn_model) return fail(e, LKCUDA_ERR_STATE, "site-specific model: lkcuda_set_site_models first");
+    long long need = (v.NP * 32 + RED_THREADS - 1) / RED_THREADS;
+    long long cap = (long long)e->num_sms * 4 < e->red_blocks ? (long long)e->num_sms * 4 : e->red_blocks;
+    int grid = (int)(need < 1 ? 1 : (need < cap ? need : cap));
+    const uint64_t b = (uint64_t)v.B * 8, tipd = LKCUDA_IS_TIP(dad) ? 1 : 0;
+    if (mode != 1) next_result(e);
+    if (mode == 0) {
+        launch_begin(e, KIND_BRANCH);
+        sitemodel_reduce_kernel<0><<<grid, RED_THREADS, 0, e->stream>>>(e->v, dad, node, len);
+        return launch_end(e, KIND_BRANCH, (uint64_t)v.NP * (tipd ? b + 1 + 24 : 2 * b + 24), "sitemodel_reduce_kernel<branch>");
+    }
+    if (mode == 1) {
+        launch_begin(e, KIND_THETA);
+        sitemodel_reduce_kernel<1><<<grid, RED_THREADS, 0, e->stream>>>(e->v, dad, node, len);
+        return launch_end(e, KIND_THETA, (uint64_t)v.NP * (tipd ? 2 * b + 1 : 3 * b), "sitemodel_reduce_kernel<theta>");
+    }
+    if (mode == 2) {
+        launch_begin(e, KIND_DERV);
+        sitemodel_reduce_kernel<2><<<grid, RED_THREADS, 0, e->stream>>>(e->v, dad, node, len);
+        return launch_end(e, KIND_DERV, (uint64_t)v.NP * (b + 16), "sitemodel_reduce_kernel<derv>");
+    }
+    launch_begin(e, KIND_FROMBUF);
+    sitemodel_reduce_kernel<3><<<grid, RED_THREADS, 0, e->stream>>>(e->v, dad, node, len);
+    return launch_end(e, KIND_FROMBUF, (uint64_t)v.NP * (b + 24), "sitemodel_reduce_kernel<frombuf>");
+}
+#define IS_SITEMODEL(e) (((e)->v.flags & LKCUDA_FLAG_SITEMODEL) != 0)
+
 /* ------------------------------------------------------------------ host side ------------------------------------------------------------------ */
 
 #define TAB_SMEM_LIMIT (44 * 1024)
@@ -602,6 +710,7 @@ static void launch_theta(lkcuda_engine *e, const GroupShape &gs, int grid, size_
 }
 
 static int enqueue_derv(lkcuda_engine *e, double len) {
+    if (IS_SITEMODEL(e)) return sitemodel_reduce(e, 2, 0, 0, len);
     const DevView &v = e->v;
     GroupShape gs = group_shape(v);
     int grid = red_grid(e, v.NP, gs.G);
@@ -626,6 +735,7 @@ int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     if (rc) return rc;
     rc = states_barrier(e);
     if (rc) return rc;
+    if (IS_SITEMODEL(e)) { rc = sitemodel_reduce(e, 0, dad, node, len); return rc ? rc : finish_result(e, result); }
     const DevView &v = e->v;
     GroupShape gs = group_shape(v);
     const bool tip = LKCUDA_IS_TIP(dad);
@@ -668,6 +778,7 @@ int lkcuda_pattern_lh_cat(lkcuda_engine *e, int32_t dad, int32_t node, double le
     if (rc) return rc;
     rc = states_barrier(e);
     if (rc) return rc;
+    if (IS_SITEMODEL(e)) return sitemodel_reduce(e, 0, dad, node, len);     /* the site-model branch kernel is what fills it */
     const DevView &v = e->v;
     if (v.P == 0) return LKCUDA_OK;
     long long total = v.P * v.K;
@@ -684,6 +795,12 @@ int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node) {
     if (rc) return rc;
     rc = states_barrier(e);
     if (rc) return rc;
+    if (IS_SITEMODEL(e)) {
+        rc = sitemodel_reduce(e, 1, dad, node, 0.0);
+        if (rc) return rc;
+        e->theta_ready = true; e->theta_dad = dad; e->theta_node = node;
+        return LKCUDA_OK;
+    }
     const DevView &v = e->v;
     GroupShape gs = group_shape(v);
     const bool tip = LKCUDA_IS_TIP(dad);
@@ -708,7 +825,7 @@ int lkcuda_theta_derv(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     LK_ENTER(e);
     const DevView &v = e->v;
     GroupShape gs = group_shape(v);
-    if (!(gs.vec && v.B == 16 && v.S == 4 && v.SU < 32)) {      /* other shapes: the two passes */
+    if (IS_SITEMODEL(e) || !(gs.vec && v.B == 16 && v.S == 4 && v.SU < 32)) {      /* other shapes: the two passes */
         int rc = lkcuda_theta_build(e, dad, node);
         return rc ? rc : lkcuda_derv(e, len, result);
     }
@@ -742,6 +859,7 @@ int lkcuda_derv(lkcuda_engine *e, double len, double *result) {
 int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result) {
     LK_ENTER(e);
     if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lnl_from_buffer: theta_all not built");
+    if (IS_SITEMODEL(e)) { int rcs = sitemodel_reduce(e, 3, 0, 0, len); return rcs ? rcs : finish_result(e, result); }
     const DevView &v = e->v;
     GroupShape gs = group_shape(v);
     int grid = red_grid(e, v.NP, gs.G);

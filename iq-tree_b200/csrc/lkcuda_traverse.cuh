@@ -76,5 +76,8 @@ long long mmak_table_slot(const DevView &v);
 bool use_traverse_mmak(const lkcuda_engine *e);
 int launch_traverse_mmak(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops);
 
+/* implemented in lkcuda_sitemodel.cu (site-specific frequency models): ops / children already written to ring slot `slot` */
+int launch_traverse_sitemodel(lkcuda_engine *e, int slot, int nops);
+
 }  // namespace lkc
 #endif

@@ -62,6 +62,7 @@ LKCUDA_SYMBOLS = {
     "lkcuda_attach_peers": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_uint8_p, C.POINTER(C.c_void_p)]),
     "lkcuda_detach_peers": (C.c_int, [C.c_void_p]),
     "lkcuda_result_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "lkcuda_set_site_models": (C.c_int, [C.c_void_p, c_int32_p, C.POINTER(C.c_uint64)]),
     "lkcuda_set_boot_samples": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.c_int32, C.c_int64]),
     "lkcuda_boot_storage": (C.c_int, [C.c_void_p, c_int32_p, c_uint64_p]),
     "lkcuda_rell": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_double_p]),
@@ -95,6 +96,7 @@ LKTREE_SYMBOLS = {
     "lktree_set_const_char": (C.c_int, [C.c_void_p, c_int32_p]),
     "lktree_set_unobserved": (C.c_int, [C.c_void_p, c_uint8_p, C.c_int32]),
     "lktree_set_model": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, C.c_double]),
+    "lktree_set_site_models": (C.c_int, [C.c_void_p, c_int32_p]),
     "lktree_read_newick": (C.c_int, [C.c_void_p, C.c_char_p]),
     "lktree_read_adjacency": (C.c_int, [C.c_void_p, C.c_char_p]),
     "lktree_get_tree_string": (C.c_int, [C.c_void_p, C.c_char_p, C.c_size_t]),
@@ -298,6 +300,11 @@ class PhyloTree:
         c = np.zeros(b1 - b0, dtype=np.int32)
         self._ck(self.lib.lktree_compute_pattern_rates(self.h, r.ctypes.data_as(c_double_p), c.ctypes.data_as(c_int32_p)))
         return r, c
+
+    def setSiteModels(self, ptn_model):
+        """family 3 (site-specific frequency models): ptn_model[nptn] -> index of the pattern's eigensystem"""
+        a = np.ascontiguousarray(ptn_model, dtype=np.int32)
+        self._ck(self.lib.lktree_set_site_models(self.h, a.ctypes.data_as(c_int32_p)))
 
     def peerHandle(self):
         """CUDA IPC handle (64 bytes, numpy uint8) of this rank's all-reduce mailbox; exchange with every rank, then attachPeers()."""

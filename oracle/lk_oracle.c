@@ -50,6 +50,8 @@ struct lkcuda_engine {
     uint64_t launches, bytes;
     /* RELL matrix and the collapsed _pattern_lh_cat work matrix */
     float *boot; int32_t nboot; double *rell; double *w; int32_t ncol;
+    /* site-specific models */
+    int32_t *ptn_model; uint64_t *state_mask;
     char err[256];
 };
 
@@ -81,7 +83,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     e->eval = (double *)calloc(e->E * e->S, 8);
     e->evec = (double *)calloc(e->E * e->S * e->S, 8); e->inv_evec = (double *)calloc(e->E * e->S * e->S, 8);
     e->blk_eigen = (int32_t *)calloc(e->K, 4); e->blk_rate = (double *)calloc(e->K, 8); e->blk_weight = (double *)calloc(e->K, 8);
-    e->tip_lh = (double *)calloc((size_t)(cfg->state_unknown + 1) * e->E * e->S, 8);
+    e->tip_lh = (double *)calloc((cfg->flags & LKCUDA_FLAG_SITEMODEL) ? 1 : (size_t)(cfg->state_unknown + 1) * e->E * e->S, 8);
     e->arena = (double *)calloc((size_t)(cfg->nvec ? cfg->nvec : 1) * n * e->block, 8);
     e->scale = (int16_t *)calloc((size_t)(cfg->nvec ? cfg->nvec : 1) * n, 2);
     e->theta = (double *)calloc(n * e->block, 8);
@@ -101,7 +103,7 @@ int lkcuda_destroy(lkcuda_engine *e) {
     free(e->states); free(e->ptn_freq); free(e->ptn_invar); free(e->eval); free(e->evec); free(e->inv_evec);
     free(e->blk_eigen); free(e->blk_rate); free(e->blk_weight); free(e->tip_lh); free(e->own_arena); free(e->own_scale);
     free(e->theta); free(e->pattern_lh); free(e->pattern_lh_cat); free(e->theta_scale_num);
-    free(e->boot); free(e->rell); free(e->w);
+    free(e->boot); free(e->rell); free(e->w); free(e->ptn_model); free(e->state_mask);
     free(e);
     return LKCUDA_OK;
 }
@@ -169,17 +171,19 @@ int lkcuda_set_pattern_weights(lkcuda_engine *e, const double *ptn_freq, const d
 int lkcuda_set_model(lkcuda_engine *e, const double *eval, const double *evec, const double *inv_evec,
                      const int32_t *blk_eigen, const double *blk_rate, const double *blk_weight,
                      const double *tip_partial_lh) {
-    if (!e || !eval || !evec || !inv_evec || !blk_eigen || !blk_rate || !blk_weight || !tip_partial_lh)
+    const int sm = e && (e->cfg.flags & LKCUDA_FLAG_SITEMODEL);
+    if (!e || !eval || !evec || !inv_evec || !blk_rate || !blk_weight || (!sm && (!blk_eigen || !tip_partial_lh)))
         return LKCUDA_ERR_ARG;
-    for (size_t k = 0; k < e->K; k++)
-        if (blk_eigen[k] < 0 || (size_t)blk_eigen[k] >= e->E) return fail(e, LKCUDA_ERR_ARG, "blk_eigen out of range");
+    if (!sm)
+        for (size_t k = 0; k < e->K; k++)
+            if (blk_eigen[k] < 0 || (size_t)blk_eigen[k] >= e->E) return fail(e, LKCUDA_ERR_ARG, "blk_eigen out of range");
     memcpy(e->eval, eval, e->E * e->S * 8);
     memcpy(e->evec, evec, e->E * e->S * e->S * 8);
     memcpy(e->inv_evec, inv_evec, e->E * e->S * e->S * 8);
-    memcpy(e->blk_eigen, blk_eigen, e->K * 4);
+    if (!sm) memcpy(e->blk_eigen, blk_eigen, e->K * 4);
     memcpy(e->blk_rate, blk_rate, e->K * 8);
     memcpy(e->blk_weight, blk_weight, e->K * 8);
-    memcpy(e->tip_lh, tip_partial_lh, (size_t)(e->cfg.state_unknown + 1) * e->E * e->S * 8);
+    if (!sm) memcpy(e->tip_lh, tip_partial_lh, (size_t)(e->cfg.state_unknown + 1) * e->E * e->S * 8);
     e->theta_ready = 0;
     return LKCUDA_OK;
 }
@@ -235,7 +239,15 @@ static void scale_pattern(lkcuda_engine *e, double *partial_lh, int16_t *scale_n
     }
 }
 
+static int sm_partial_one(lkcuda_engine *e, const lkcuda_partial_op *op);
+static int sm_branch(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result);
+static int sm_theta(lkcuda_engine *e, int32_t dad, int32_t node);
+static int sm_derv(lkcuda_engine *e, double len, double *df_out, double *ddf_out);
+static int sm_frombuf(lkcuda_engine *e, double len, double *result);
+#define IS_SM(e) ((e)->cfg.flags & LKCUDA_FLAG_SITEMODEL)
+
 static int partial_one(lkcuda_engine *e, const lkcuda_partial_op *op) {
+    if (IS_SM(e)) return sm_partial_one(e, op);
     size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all, SU = (size_t)e->cfg.state_unknown;
     if (op->dst < 0 || op->dst >= e->cfg.nvec || bad_end(e, op->left) || bad_end(e, op->right))
         return fail(e, LKCUDA_ERR_ARG, "partial op: bad vector / taxon id");
@@ -418,6 +430,7 @@ static void finish_lnl(lkcuda_engine *e, const double *lh_ptn_all, const int16_t
 
 int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result) {
     if (!e || node < 0 || node >= e->cfg.nvec || bad_end(e, dad)) return LKCUDA_ERR_ARG;
+    if (IS_SM(e)) return sm_branch(e, dad, node, len, result);
     size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all, P = (size_t)e->cfg.nptn;
     double *val = (double *)malloc(block * 8);
     double *lh_all = (double *)malloc((nptn + 1) * 8);
@@ -453,6 +466,7 @@ int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
 /* _pattern_lh_cat only (phylotreesse.cpp:1194-1237) */
 int lkcuda_pattern_lh_cat(lkcuda_engine *e, int32_t dad, int32_t node, double len) {
     if (!e || node < 0 || node >= e->cfg.nvec || bad_end(e, dad)) return LKCUDA_ERR_ARG;
+    if (IS_SM(e)) return sm_branch(e, dad, node, len, NULL);    /* the site-model branch kernel is what fills it (phylokernelsitemodel.cpp:579-603) */
     size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all, P = (size_t)e->cfg.nptn;
     double *val = (double *)malloc(block * 8);
     build_val(e, len, val, NULL, NULL);
@@ -484,6 +498,7 @@ int lkcuda_theta_derv(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
 
 int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node) {
     if (!e || node < 0 || node >= e->cfg.nvec || bad_end(e, dad)) return LKCUDA_ERR_ARG;
+    if (IS_SM(e)) return sm_theta(e, dad, node);
     size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all, P = (size_t)e->cfg.nptn;
     const double *lh_node = vec_lh(e, node);
     if (LKCUDA_IS_TIP(dad)) {   /* phylotreesse.cpp:1046-1063 */
@@ -506,6 +521,7 @@ int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node) {
 }
 
 static int derv_at(lkcuda_engine *e, double len, double *df_out, double *ddf_out) {
+    if (IS_SM(e)) return sm_derv(e, len, df_out, ddf_out);
     size_t block = e->block, nptn = e->nptn_all, P = (size_t)e->cfg.nptn;
     double *val0 = (double *)malloc(block * 8), *val1 = (double *)malloc(block * 8), *val2 = (double *)malloc(block * 8);
     build_val(e, len, val0, val1, val2);
@@ -555,6 +571,7 @@ int lkcuda_derv(lkcuda_engine *e, double len, double *result) {
 int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result) {
     if (!e) return LKCUDA_ERR_ARG;
     if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lnl_from_buffer: theta_all not built");
+    if (IS_SM(e)) return sm_frombuf(e, len, result);
     size_t block = e->block, nptn = e->nptn_all;
     double *val0 = (double *)malloc(block * 8);
     double *lh_all = (double *)malloc((nptn + 1) * 8);
@@ -804,5 +821,206 @@ int lkcuda_set_profiling(lkcuda_engine *e, int32_t on) { (void)on; return e ? LK
 int lkcuda_kernel_stats(lkcuda_engine *e, int32_t kind, uint64_t *launches, uint64_t *bytes, double *device_ms) {
     if (!e || kind < 0 || kind >= LKCUDA_NKIND) return LKCUDA_ERR_ARG;
     if (launches) *launches = 0; if (bytes) *bytes = 0; if (device_ms) *device_ms = 0.0;
+    return LKCUDA_OK;
+}
+
+
+/* ================================================================================================================================
+ * site-specific frequency models, restated from phylokernelsitemodel.cpp (the generic, non-SIMD versions):
+ * computeSitemodelPartialLikelihoodEigen :20-436, ...DervEigen :438-546, ...BranchEigen :548-660, ...FromBufferEigen :663-703.
+ * eval / evec / inv_evec of pattern ptn = those of model ptn_model[ptn] (models->at(ptn)).  No +ASC (the reference never combines them).
+ * ================================================================================================================================ */
+int lkcuda_set_site_models(lkcuda_engine *e, const int32_t *ptn_model, const uint64_t *state_mask) {
+    if (!e || !ptn_model || !state_mask) return LKCUDA_ERR_ARG;
+    if (!IS_SM(e)) return fail(e, LKCUDA_ERR_STATE, "lkcuda_set_site_models: engine created without LKCUDA_FLAG_SITEMODEL");
+    for (size_t p = 0; p < e->nptn_all; p++)
+        if (ptn_model[p] < 0 || (size_t)ptn_model[p] >= e->E) return fail(e, LKCUDA_ERR_ARG, "ptn_model out of range");
+    free(e->ptn_model); free(e->state_mask);
+    e->ptn_model = (int32_t *)malloc((e->nptn_all + 1) * 4);
+    e->state_mask = (uint64_t *)malloc((size_t)(e->cfg.state_unknown + 1) * 8);
+    memcpy(e->ptn_model, ptn_model, e->nptn_all * 4);
+    memcpy(e->state_mask, state_mask, (size_t)(e->cfg.state_unknown + 1) * 8);
+    e->theta_ready = 0;
+    return LKCUDA_OK;
+}
+
+/* tip_partial_lh[taxon][ptn][i] (phylotreesse.cpp:373-456): sum over the states the code stands for of inv_evec[i][x], x ascending */
+static void sm_tip(lkcuda_engine *e, size_t ptn, int state, double *out) {
+    size_t S = e->S;
+    const double *inv_evec = e->inv_evec + (size_t)e->ptn_model[ptn] * S * S;
+    uint64_t mask = e->state_mask[state];
+    if (state < (int)S) { for (size_t i = 0; i < S; i++) out[i] = inv_evec[i * S + (size_t)state]; return; }
+    for (size_t i = 0; i < S; i++) {
+        double lh = 0.0;
+        for (size_t x = 0; x < S; x++) if (mask & (1ull << x)) lh += inv_evec[i * S + x];
+        out[i] = lh;
+    }
+}
+
+static int sm_partial_one(lkcuda_engine *e, const lkcuda_partial_op *op) {
+    size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all;
+    if (!e->ptn_model) return fail(e, LKCUDA_ERR_STATE, "site models not set");
+    if (op->dst < 0 || op->dst >= e->cfg.nvec || bad_end(e, op->left) || bad_end(e, op->right))
+        return fail(e, LKCUDA_ERR_ARG, "partial op: bad vector / taxon id");
+    if (!LKCUDA_IS_TIP(op->left) && LKCUDA_IS_TIP(op->right))
+        return fail(e, LKCUDA_ERR_ARG, "partial op: a leaf child must be 'left'");
+    double *dst = vec_lh(e, op->dst);
+    int16_t *dsc = vec_sc(e, op->dst);
+    const uint8_t *st_l = LKCUDA_IS_TIP(op->left) ? e->states + (size_t)LKCUDA_TIP_TAXON(op->left) * nptn : NULL;
+    const uint8_t *st_r = LKCUDA_IS_TIP(op->right) ? e->states + (size_t)LKCUDA_TIP_TAXON(op->right) * nptn : NULL;
+    const double *lh_l = st_l ? NULL : vec_lh(e, op->left), *lh_r = st_r ? NULL : vec_lh(e, op->right);
+    const int16_t *sc_l = st_l ? NULL : vec_sc(e, op->left), *sc_r = st_r ? NULL : vec_sc(e, op->right);
+    double *tmp = (double *)malloc(S * 8), *expleft = (double *)malloc(S * 8), *expright = (double *)malloc(S * 8);
+    double *tipl = (double *)malloc(S * 8), *tipr = (double *)malloc(S * 8), *tip0 = (double *)malloc(S * 8);
+    for (size_t ptn = 0; ptn < nptn; ptn++) {
+        const size_t m = (size_t)e->ptn_model[ptn];
+        const double *eval = e->eval + m * S, *evec = e->evec + m * S * S, *inv_evec = e->inv_evec + m * S * S;
+        double *partial_lh = dst + ptn * block;
+        double lh_max = 0.0;
+        dsc[ptn] = (int16_t)((sc_l ? sc_l[ptn] : 0) + (sc_r ? sc_r[ptn] : 0));      /* :233, :267, :351 */
+        if (st_l) sm_tip(e, ptn, st_l[ptn], tipl);
+        if (st_r) sm_tip(e, ptn, st_r[ptn], tipr);
+        for (size_t c = 0; c < K; c++) {
+            const double len_left = e->blk_rate[c] * op->len_left, len_right = e->blk_rate[c] * op->len_right;
+            const double *pl = st_l ? tipl : lh_l + ptn * block + c * S, *pr = st_r ? tipr : lh_r + ptn * block + c * S;
+            for (size_t i = 0; i < S; i++) {
+                expleft[i] = exp(eval[i] * len_left) * pl[i];
+                expright[i] = exp(eval[i] * len_right) * pr[i];
+            }
+            for (size_t x = 0; x < S; x++) {
+                double vleft = 0.0, vright = 0.0;
+                const double *this_evec = evec + x * S;
+                for (size_t i = 0; i < S; i++) { vleft += this_evec[i] * expleft[i]; vright += this_evec[i] * expright[i]; }
+                tmp[x] = vleft * vright;
+            }
+            for (size_t i = 0; i < S; i++) {
+                double res = 0.0;
+                for (size_t x = 0; x < S; x++) res += tmp[x] * inv_evec[i * S + x];
+                partial_lh[c * S + i] = res;
+                if (fabs(res) > lh_max) lh_max = fabs(res);
+            }
+        }
+        if (!(st_l && st_r) && lh_max < SCALING_THRESHOLD) {       /* the cherry case never scales (:222-262) */
+            if (lh_max == 0.0) {                                    /* :308-320: &tip_partial_lh[ptn*nstates] is taxon 0's vector */
+                sm_tip(e, ptn, e->states[ptn], tip0);
+                for (size_t c = 0; c < K; c++) memcpy(&partial_lh[c * S], tip0, S * 8);
+                dsc[ptn] += 4;
+            } else {
+                for (size_t i = 0; i < block; i++) partial_lh[i] *= SCALING_THRESHOLD_INVER;
+                dsc[ptn] += 1;
+            }
+        }
+    }
+    free(tmp); free(expleft); free(expright); free(tipl); free(tipr); free(tip0);
+    e->launches++;
+    return LKCUDA_OK;
+}
+
+static int sm_branch(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result) {
+    size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all, P = (size_t)e->cfg.nptn;
+    if (!e->ptn_model) return fail(e, LKCUDA_ERR_STATE, "site models not set");
+    double *lh_all = (double *)malloc((nptn + 1) * 8), *tip = (double *)malloc(S * 8);
+    int16_t *ssn = (int16_t *)calloc((size_t)e->cfg.nunobs + 1, 2);
+    const double *lh_node = vec_lh(e, node);
+    const uint8_t *st = LKCUDA_IS_TIP(dad) ? e->states + (size_t)LKCUDA_TIP_TAXON(dad) * nptn : NULL;
+    const double *lh_dad = st ? NULL : vec_lh(e, dad);
+    for (size_t ptn = 0; ptn < nptn; ptn++) {       /* :583-606 (tip), :612-636 (internal) */
+        const double *eval = e->eval + (size_t)e->ptn_model[ptn] * S;
+        double lh_ptn = e->ptn_invar[ptn];
+        if (st) sm_tip(e, ptn, st[ptn], tip);
+        for (size_t c = 0; c < K; c++) {
+            double lh_cat = 0.0;
+            const double l = e->blk_rate[c] * len, prop = e->blk_weight[c];
+            const double *a = st ? tip : lh_dad + ptn * block + c * S, *b = lh_node + ptn * block + c * S;
+            for (size_t i = 0; i < S; i++) lh_cat += exp(eval[i] * l) * a[i] * b[i];
+            lh_cat *= prop;
+            if (ptn < P) e->pattern_lh_cat[ptn * K + c] = lh_cat;
+            lh_ptn += lh_cat;
+        }
+        lh_all[ptn] = lh_ptn;
+    }
+    double scale_sum = vec_scale_factor(e, node) + (st ? 0.0 : vec_scale_factor(e, dad));
+    finish_lnl(e, lh_all, ssn, scale_sum);
+    free(lh_all); free(tip); free(ssn);
+    e->launches++;
+    if (result) memcpy(result, e->result, sizeof(e->result_own));
+    return LKCUDA_OK;
+}
+
+static int sm_theta(lkcuda_engine *e, int32_t dad, int32_t node) {
+    size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all;
+    if (!e->ptn_model) return fail(e, LKCUDA_ERR_STATE, "site models not set");
+    const double *lh_node = vec_lh(e, node);
+    if (LKCUDA_IS_TIP(dad)) {       /* :463-482 */
+        const uint8_t *st = e->states + (size_t)LKCUDA_TIP_TAXON(dad) * nptn;
+        double *tip = (double *)malloc(S * 8);
+        for (size_t ptn = 0; ptn < nptn; ptn++) {
+            sm_tip(e, ptn, st[ptn], tip);
+            for (size_t c = 0; c < K; c++)
+                for (size_t i = 0; i < S; i++) e->theta[ptn * block + c * S + i] = tip[i] * lh_node[ptn * block + c * S + i];
+        }
+        free(tip);
+    } else {                        /* :484-497 */
+        const double *lh_dad = vec_lh(e, dad);
+        for (size_t i = 0; i < nptn * block; i++) e->theta[i] = lh_dad[i] * lh_node[i];
+    }
+    e->theta_scale_sum = vec_scale_factor(e, node) + (LKCUDA_IS_TIP(dad) ? 0.0 : vec_scale_factor(e, dad));
+    e->theta_ready = 1;
+    e->launches++;
+    return LKCUDA_OK;
+}
+
+static int sm_derv(lkcuda_engine *e, double len, double *df_out, double *ddf_out) {
+    size_t S = e->S, K = e->K, block = e->block, P = (size_t)e->cfg.nptn;
+    double my_df = 0.0, my_ddf = 0.0;
+    for (size_t ptn = 0; ptn < P; ptn++) {      /* :505-538 */
+        double lh_ptn = e->ptn_invar[ptn], df_ptn = 0.0, ddf_ptn = 0.0;
+        const double *theta = e->theta + ptn * block;
+        const double *eval = e->eval + (size_t)e->ptn_model[ptn] * S;
+        for (size_t c = 0; c < K; c++) {
+            double lh_cat = 0.0, df_cat = 0.0, ddf_cat = 0.0;
+            for (size_t i = 0; i < S; i++) {
+                double cof = eval[i] * e->blk_rate[c];
+                double val = exp(cof * len) * theta[i];
+                double val1 = cof * val;
+                lh_cat += val; df_cat += val1; ddf_cat += cof * val1;
+            }
+            double prop = e->blk_weight[c];
+            lh_ptn += prop * lh_cat; df_ptn += prop * df_cat; ddf_ptn += prop * ddf_cat;
+            theta += S;
+        }
+        lh_ptn = 1.0 / fabs(lh_ptn);
+        double df_frac = df_ptn * lh_ptn, ddf_frac = ddf_ptn * lh_ptn, freq = e->ptn_freq[ptn];
+        double tmp1 = df_frac * freq, tmp2 = ddf_frac * freq;
+        my_df += tmp1;
+        my_ddf += tmp2 - tmp1 * df_frac;
+    }
+    if (isnan(my_df) || isinf(my_df)) { my_df = 0.0; my_ddf = 0.0; }
+    *df_out = my_df; *ddf_out = my_ddf;
+    e->launches++;
+    return LKCUDA_OK;
+}
+
+static int sm_frombuf(lkcuda_engine *e, double len, double *result) {
+    size_t S = e->S, K = e->K, block = e->block, nptn = e->nptn_all;
+    double *lh_all = (double *)malloc((nptn + 1) * 8);
+    int16_t *ssn = (int16_t *)calloc((size_t)e->cfg.nunobs + 1, 2);
+    for (size_t ptn = 0; ptn < nptn; ptn++) {   /* :680-699 */
+        double lh_ptn = e->ptn_invar[ptn];
+        const double *theta = e->theta + ptn * block;
+        const double *eval = e->eval + (size_t)e->ptn_model[ptn] * S;
+        for (size_t c = 0; c < K; c++) {
+            double lh_cat = 0.0;
+            const double l = e->blk_rate[c] * len;
+            for (size_t i = 0; i < S; i++) lh_cat += exp(eval[i] * l) * theta[i];
+            lh_ptn += lh_cat * e->blk_weight[c];
+            theta += S;
+        }
+        lh_all[ptn] = lh_ptn;
+    }
+    finish_lnl(e, lh_all, ssn, e->theta_scale_sum);
+    free(lh_all); free(ssn);
+    e->launches++;
+    if (result) memcpy(result, e->result, sizeof(e->result_own));
     return LKCUDA_OK;
 }

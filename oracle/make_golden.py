@@ -105,6 +105,20 @@ def synth_morph(tmp, ntaxa, nsite, nstates, seed, tag, variable_only=False):
     return aln, tre
 
 
+def site_freq_file(tmp, nsite, nstates, seed, tag, nclass=9):
+    """-fs input (ModelFactory::readSiteFreq, model/modelfactory.cpp:597-690): one line per site, `site f_1 .. f_S`; sites draw
+    their frequency vector from `nclass` random profiles"""
+    rng = np.random.default_rng(seed)
+    prof = rng.dirichlet(np.full(nstates, 0.8), size=nclass)
+    prof = np.clip(prof, 2e-3, None)
+    prof /= prof.sum(axis=1, keepdims=True)
+    path = os.path.join(tmp, tag + ".sitefreq")
+    with open(path, "w") as f:
+        for s in range(nsite):
+            f.write("%d %s\n" % (s + 1, " ".join("%.6f" % x for x in prof[rng.integers(nclass)])))
+    return path
+
+
 def random_tree_file(tmp, names, seed, tag, mean_len=0.1):
     tre = os.path.join(tmp, tag + ".nwk")
     open(tre, "w").write(mi.random_tree_newick(len(names), seed, names, mean_len=mean_len) + "\n")
@@ -169,6 +183,8 @@ def pack(case, d):
     for k in ("eval", "evec", "inv_evec", "rates", "props", "mixprops", "state_freq", "tip_partial_lh", "ptn_freq",
               "ptn_invar", "pattern_lh", "pattern_lh_scaled", "pattern_lh_cat", "branch_derv"):
         z[k] = rd(d, k + ".f64", np.float64)
+    if meta["family"] == "sitemodel":
+        z["ptn_model"] = rd(d, "ptn_model.i32", np.int32)
     z["traversal"] = rd(d, "traversal.i32", np.int32).reshape(-1, 2)
     for k in ("tree_adj", "tree_adj_oab1", "tree_adj_oabfull"):
         z[k] = open(os.path.join(d, k + ".txt")).read()
@@ -249,7 +265,14 @@ def main():
     mf_names = read_phylip_names(ex)
     mf_tree = multifurcating_tree_file(tmp, mf_names, 4, "multif")
 
+    ex_fs = site_freq_file(tmp, 384, 4, 31, "exfs")
+    prot_fs = site_freq_file(tmp, 269, 20, 32, "protfs")
+    deep_fs = site_freq_file(tmp, 90, 4, 33, "deepfs")
     cases = {
+        "dna_sitefreq_gtr_g4": ["-s", ex, "-m", "GTR+G4", "-fs", ex_fs, "-te", ex_tree],
+        "dna_sitefreq_deep_scaling": ["-s", deep_aln, "-m", "HKY+G4", "-fs", deep_fs, "-te", deep_tree],
+        "aa_sitefreq_lg_g4": ["-s", prot, "-m", "LG+G4", "-fs", prot_fs, "-te", prot_tree],
+        "aa_sitefreq_lg_generic": ["-s", prot, "-m", "LG", "-fs", prot_fs, "-te", prot_tree, "-fastlk"],
         "dna_example_gtr_g4": ["-s", ex, "-m", "GTR+G4", "-te", ex_tree],
         "dna_example_gtr_i_g4": ["-s", ex, "-m", "GTR+I+G4", "-te", ex_tree],
         "dna_example_hky_r3": ["-s", ex, "-m", "HKY+R3", "-te", ex_tree],

@@ -47,6 +47,7 @@
 #include "timeutil.h"
 #include "model/modelfactory.h"
 #include "model/modelmixture.h"
+#include "model/modelset.h"
 #include "model/rateheterogeneity.h"
 #include "vectorclass/instrset.h"
 #undef private
@@ -136,6 +137,7 @@ static IQTree *setup(int argc, char **argv, Params &params) {
 }
 
 static const char *familyName(IQTree *tree) {
+    if (tree->getModel()->isSiteSpecificModel()) return "sitemodel";
     if (tree->getModel()->isMixture())
         return tree->getModelFactory()->fused_mix_rate ? "mixrate" : "mixture";
     return "plain";
@@ -158,6 +160,8 @@ static int do_dump(int argc, char **argv) {
     size_t P = aln->size(), U = mf->unobserved_ptns.size(), nptn = P + U, ntaxa = aln->getNSeq();
     size_t block = tree->getModel()->isMixture() && !fused ? S * C * M : S * C;
     size_t E = M;   // number of eigensystems
+    const bool sitemodel = model->isSiteSpecificModel();     // -fs: one model per pattern (ModelSet, phylokernelsitemodel.cpp)
+    if (sitemodel) { E = P; M = P; }
 
     /* ---- kernel inputs ---- */
     std::vector<unsigned char> states(ntaxa * nptn);
@@ -176,12 +180,26 @@ static int do_dump(int argc, char **argv) {
         std::ofstream f((g_out + "/taxa.txt").c_str());
         for (size_t t = 0; t < ntaxa; t++) f << aln->getSeqName(t) << "\n";
     }
+    if (sitemodel) {
+        ModelSet *models = (ModelSet*)model;
+        std::vector<double> ev(E * S), evc(E * S * S), inv(E * S * S);
+        std::vector<int> pm(P);
+        for (size_t p = 0; p < P; p++) {
+            memcpy(&ev[p * S], models->at(p)->getEigenvalues(), S * 8);
+            memcpy(&evc[p * S * S], models->at(p)->getEigenvectors(), S * S * 8);
+            memcpy(&inv[p * S * S], models->at(p)->getInverseEigenvectors(), S * S * 8);
+            pm[p] = (int)p;
+        }
+        wbin("eval.f64", &ev[0], ev.size() * 8); wbin("evec.f64", &evc[0], evc.size() * 8); wbin("inv_evec.f64", &inv[0], inv.size() * 8);
+        wbin("ptn_model.i32", &pm[0], P * sizeof(int));
+    } else {
     wbin("eval.f64", model->getEigenvalues(), E * S * sizeof(double));
     wbin("evec.f64", model->getEigenvectors(), E * S * S * sizeof(double));
     wbin("inv_evec.f64", model->getInverseEigenvectors(), E * S * S * sizeof(double));
+    }
     std::vector<double> rates(C), props(C), mixprops(M, 1.0), sfreq(S);
     for (size_t c = 0; c < C; c++) { rates[c] = rate->getRate(c); props[c] = rate->getProp(c); }
-    if (model->isMixture()) for (size_t m = 0; m < M; m++) mixprops[m] = ((ModelMixture*)model)->prop[m];
+    if (model->isMixture() && !sitemodel) for (size_t m = 0; m < M; m++) mixprops[m] = ((ModelMixture*)model)->prop[m];
     model->getStateFrequency(&sfreq[0]);
     wbin("rates.f64", &rates[0], C * 8); wbin("props.f64", &props[0], C * 8);
     wbin("mixprops.f64", &mixprops[0], M * 8); wbin("state_freq.f64", &sfreq[0], S * 8);
@@ -197,7 +215,8 @@ static int do_dump(int argc, char **argv) {
     tree->clearAllPartialLH();
     double lnl = tree->computeLikelihood();
     // computeTipPartialLikelihood has run now
-    wbin("tip_partial_lh.f64", tree->tip_partial_lh, (aln->STATE_UNKNOWN + 1) * S * E * sizeof(double));
+    if (sitemodel) wbin("tip_partial_lh.f64", tree->tip_partial_lh, 0);     // [taxon][ptn][S] there: formed on the fly by the engine
+    else wbin("tip_partial_lh.f64", tree->tip_partial_lh, (aln->STATE_UNKNOWN + 1) * S * E * sizeof(double));
     wbin("ptn_freq.f64", tree->ptn_freq, P * 8);
     wbin("ptn_invar.f64", tree->ptn_invar, nptn * 8);
     wbin("pattern_lh.f64", tree->_pattern_lh, P * 8);
@@ -213,7 +232,12 @@ static int do_dump(int argc, char **argv) {
         dumpPartials(tree, tree->root, NULL, idx, nptn, block);
     }
     /* per-category pattern likelihoods via the generic kernel (phylotree.cpp:1108) */
-    {
+    if (sitemodel) {     // the site-model branch kernel always fills _pattern_lh_cat[ptn][c] (phylokernelsitemodel.cpp:579-603)
+        tree->computeSitemodelLikelihoodBranchEigen(tree->current_it, (PhyloNode*)tree->current_it_back->node);   // the SIMD twins never fill it
+        wbin("pattern_lh_cat.f64", tree->_pattern_lh_cat, P * C * 8);
+        tree->clearAllPartialLH();
+        tree->computeLikelihood();
+    } else {
         tree->computePatternLhCat(WSL_RATECAT);
         size_t ncat_tot = (model->isMixture() && !fused) ? C * M : C;
         wbin("pattern_lh_cat.f64", tree->_pattern_lh_cat, P * ncat_tot * 8);

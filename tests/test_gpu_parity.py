@@ -90,7 +90,8 @@ def test_cuda_matches_oracle_synthetic(shape, cuda_lib, oracle_lib):
 
 
 @pytest.mark.parametrize("host_sum", [False, True])
-@pytest.mark.parametrize("case,nshard", [("dna_example_gtr_i_g4", 2), ("dna_example_gtr_g4", 4), ("morph_mk_asc", 3), ("aa_lg_g4", 2)])
+@pytest.mark.parametrize("case,nshard", [("dna_example_gtr_i_g4", 2), ("dna_example_gtr_g4", 4), ("morph_mk_asc", 3), ("aa_lg_g4", 2),
+                                         ("aa_sitefreq_lg_g4", 3), ("dna_sitefreq_deep_scaling", 2)])
 def test_shards_one_device(case, nshard, host_sum, cuda_lib, monkeypatch):
     """pattern sharding: N engines on the same device (each on its own stream) give the sums of one.  Default: the reduction kernels
     exchange and add their result blocks among themselves through the peer mailboxes (fused all-reduce, lkcuda_attach_peers);
