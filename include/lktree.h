@@ -70,6 +70,9 @@ int lktree_set_stream(lktree *h, void *cuda_stream);
 int lktree_set_params(lktree *h, double min_branch_length, double max_branch_length, int32_t device_newton, int32_t generic_kernel);
 
 /* PhyloTree API */
+/* PhyloTree::getBestNNIForBran (phylotree.cpp:2873-3066): both NNIs around the internal branch (node1, node2); out[16] = per NNI
+   {newloglh, newLen[5], id of the subtree root taken from node1, id of the one taken from node2}.  The tree is left unchanged. */
+int lktree_get_best_nni_for_bran(lktree *h, int32_t node1, int32_t node2, int32_t nni5, double *out);
 int lktree_initialize_all_partial_lh(lktree *h);
 int lktree_delete_all_partial_lh(lktree *h);
 int lktree_clear_all_partial_lh(lktree *h);

@@ -146,6 +146,19 @@ int lktree_optimize_one_branch(lktree *h, int32_t node1, int32_t node2, int32_t 
     LK_CATCH(h)
 }
 
+int lktree_get_best_nni_for_bran(lktree *h, int32_t node1, int32_t node2, int32_t nni5, double *out) {
+    LK_TRY(h)
+    Node *n1 = nodeById(h, node1), *n2 = nodeById(h, node2);
+    PhyloTree::NNIMove mv[2];
+    h->tree.getBestNNIForBran(n1, n2, mv, nni5 != 0);
+    for (int c = 0; c < 2; c++) {
+        out[8 * c] = mv[c].newloglh;
+        for (int i = 0; i < 5; i++) out[8 * c + 1 + i] = mv[c].newLen[i];
+        out[8 * c + 6] = mv[c].node1_nei; out[8 * c + 7] = mv[c].node2_nei;
+    }
+    LK_CATCH(h)
+}
+
 int lktree_optimize_all_branches(lktree *h, int32_t iterations, double tolerance, int32_t max_nr_step, double *lnl) {
     LK_TRY(h) *lnl = h->tree.optimizeAllBranches(iterations, tolerance, max_nr_step); LK_CATCH(h)
 }

@@ -19,6 +19,8 @@
 
 namespace lk {
 
+enum { NNI_VECS = 6 };     // IT_NUM of getBestNNIForBran with params->nni5 (phylotree.cpp:857, 2878)
+
 #define FOR_NEI(nd_, dad_, it) \
     for (std::vector<Neighbor*>::iterator it = (nd_)->neighbors.begin(); it != (nd_)->neighbors.end(); ++it) \
         if ((*it)->node != (dad_))
@@ -397,7 +399,7 @@ void PhyloTree::initializeAllPartialLh() {
         memset(&cfg, 0, sizeof(cfg));
         cfg.device = devs[d];
         cfg.nstates = nstates; cfg.nblocks = K; cfg.neigen = nmix; cfg.ntaxa = ntaxa;
-        cfg.state_unknown = state_unknown; cfg.nvec = nvec_;
+        cfg.state_unknown = state_unknown; cfg.nvec = nvec_ + NNI_VECS;
         cfg.flags = (family == FAMILY_SITEMODEL ? LKCUDA_FLAG_SITEMODEL : 0) |
                     (family != FAMILY_PLAIN ? LKCUDA_FLAG_SCALE_IGNORES_INVAR : 0) |
                     (generic_kernel ? (LKCUDA_FLAG_ZERO_GUARD | LKCUDA_FLAG_PATTERN_LH_CAT) : 0);
@@ -455,7 +457,7 @@ void PhyloTree::initializeAllPartialLh() {
     weights_uploaded_ = model_uploaded_ = false;
     freq_dirty_ = invar_dirty_ = model_dirty_ = true;
     tip_partial_lh_computed_ = false;
-    vec_level_.assign(nvec_, 0);
+    vec_level_.assign(nvec_ + NNI_VECS, 0);
     clearAllPartialLH();
 }
 
@@ -966,6 +968,93 @@ void PhyloTree::optimizeOneBranch(Node *node1, Node *node2, bool clearLH, int ma
         clearReversePartialLh(node1, node2);
         clearReversePartialLh(node2, node1);
     }
+}
+
+/* phylotree.cpp:2873-3066, statement for statement (without the upper-bound shortcut, params->upper_bound_NNI, and the bootstrap hooks):
+   six (nni5) or two neighbour slots around the branch get fresh Neighbor objects whose partials live in the nni_partial_lh vectors, so the
+   tree's own partials survive; per NNI: swap, clear, optimise the branches in the reference's order with at most 10 Newton steps,
+   computeLikelihoodFromBuffer, swap back. */
+PhyloTree::NNIMove PhyloTree::getBestNNIForBran(Node *node1, Node *node2, NNIMove moves[2], bool nni5) {
+    if (node1->isLeaf() || node2->isLeaf() || node1->degree() != 3 || node2->degree() != 3)
+        throw std::runtime_error("getBestNNIForBran: both ends must be internal nodes of degree 3");
+    if (engines_.empty()) initializeAllPartialLh();
+    const int NNI_MAX_NR_STEP = 10;                 // pllnni.cpp:21
+    const int IT_NUM = nni5 ? 6 : 2;
+    Neighbor **saved_it[6];
+    int id = 0;
+    auto slot = [](Node *at, Node *to) -> Neighbor** {
+        for (size_t i = 0; i < at->neighbors.size(); i++) if (at->neighbors[i]->node == to) return &at->neighbors[i];
+        throw std::runtime_error("getBestNNIForBran: nodes are not adjacent");
+    };
+    saved_it[id++] = slot(node1, node2);
+    saved_it[id++] = slot(node2, node1);
+    if (nni5) {
+        FOR_NEI(node1, node2, it) saved_it[id++] = slot((*it)->node, node1);
+        FOR_NEI(node2, node1, it) saved_it[id++] = slot((*it)->node, node2);
+    }
+    Neighbor *saved_nei[6];
+    for (id = 0; id < IT_NUM; id++) {
+        saved_nei[id] = *saved_it[id];
+        *saved_it[id] = new Neighbor(saved_nei[id]->node, saved_nei[id]->length);
+        (*saved_it[id])->id = saved_nei[id]->id;
+        (*saved_it[id])->vec = nvec_ + id;          // nni_partial_lh + id*partial_lh_size
+    }
+    Neighbor *node12_it = node1->findNeighbor(node2), *node21_it = node2->findNeighbor(node1);
+    // the two NNIs: the first neighbour of node1 (other than node2) swaps with each of node2's two (phylotree.cpp:2951-2962)
+    Neighbor **node1_it = NULL, **node2_its[2] = {NULL, NULL};
+    for (size_t i = 0; i < node1->neighbors.size() && !node1_it; i++) if (node1->neighbors[i]->node != node2) node1_it = &node1->neighbors[i];
+    { int cnt = 0; for (size_t i = 0; i < node2->neighbors.size(); i++) if (node2->neighbors[i]->node != node1) node2_its[cnt++] = &node2->neighbors[i]; }
+    for (int cnt = 0; cnt < 2; cnt++) {
+        Neighbor **node2_it = node2_its[cnt];
+        Neighbor *node1_nei = *node1_it, *node2_nei = *node2_it;
+        moves[cnt].node1_nei = node1_nei->node->id; moves[cnt].node2_nei = node2_nei->node->id;
+        // do the NNI swap
+        *node1_it = node2_nei;
+        node2_nei->node->findNeighbor(node2)->node = node1;
+        *node2_it = node1_nei;
+        node1_nei->node->findNeighbor(node1)->node = node2;
+        node12_it->partial_lh_computed = 0;
+        node21_it->partial_lh_computed = 0;
+        int i = 1;
+        if (nni5) {
+            FOR_NEI(node1, node2, it) {
+                (*it)->node->findNeighbor(node1)->partial_lh_computed = 0;
+                optimizeOneBranch(node1, (*it)->node, false, NNI_MAX_NR_STEP);
+                moves[cnt].newLen[i] = node1->findNeighbor((*it)->node)->length;
+                i++;
+            }
+            node21_it->partial_lh_computed = 0;
+        }
+        optimizeOneBranch(node1, node2, false, NNI_MAX_NR_STEP);
+        moves[cnt].newLen[0] = node1->findNeighbor(node2)->length;
+        if (nni5) {
+            FOR_NEI(node2, node1, it) {
+                (*it)->node->findNeighbor(node2)->partial_lh_computed = 0;
+                optimizeOneBranch(node2, (*it)->node, false, NNI_MAX_NR_STEP);
+                moves[cnt].newLen[i] = node2->findNeighbor((*it)->node)->length;
+                i++;
+            }
+            node12_it->partial_lh_computed = 0;
+        }
+        for (; i < 5; i++) moves[cnt].newLen[i] = 0.0;
+        moves[cnt].newloglh = computeLikelihoodFromBuffer();
+        // swap back
+        *node1_it = node1_nei;
+        node1_nei->node->findNeighbor(node2)->node = node1;
+        *node2_it = node2_nei;
+        node2_nei->node->findNeighbor(node1)->node = node2;
+    }
+    // restore the Neighbor*
+    for (id = IT_NUM - 1; id >= 0; id--) {
+        if (*saved_it[id] == current_it) current_it = saved_nei[id];
+        if (*saved_it[id] == current_it_back) current_it_back = saved_nei[id];
+        delete *saved_it[id];
+        *saved_it[id] = saved_nei[id];
+    }
+    // restore the length of 4 branches around node1, node2
+    FOR_NEI(node1, node2, it) (*it)->length = (*it)->node->findNeighbor(node1)->length;
+    FOR_NEI(node2, node1, it) (*it)->length = (*it)->node->findNeighbor(node2)->length;
+    return moves[0].newloglh > moves[1].newloglh ? moves[0] : moves[1];
 }
 
 void PhyloTree::saveBranchLengths(std::vector<double> &lenvec, int startid, Node *node, Node *dad) {

@@ -22,6 +22,7 @@
  *   computeFuncDerv                      phylotree.cpp:2135-2146
  *   minimizeNewton                       optimization.cpp:388-465
  *   optimizeOneBranch / optimizeAllBranches  phylotree.cpp:2148-2192, 2252-2332
+ *   getBestNNIForBran                    phylotree.cpp:2873-3066 (NNI evaluation of the tree search)
  *   readTree / parseFile (Newick)        mtree.cpp:503-680
  */
 #ifndef LK_PHYLOTREE_H
@@ -126,6 +127,10 @@ public:
     double computeLikelihoodFromBuffer();
     double computeLikelihood(double *pattern_lh = NULL);
     int computePatternLhCat(double *pattern_lh_cat, int wsl = 4);    // phylotree.cpp:1108-1160; returns entries per pattern
+    /* NNI evaluation (phylotree.cpp:2873-3066): both NNIs around the internal branch (node1, node2), each with its 1 (nni5 = false) or 5
+       surrounding branches re-optimised by Newton-Raphson (NNI_MAX_NR_STEP = 10, pllnni.cpp:21); the tree is left as it was */
+    struct NNIMove { double newloglh; double newLen[5]; int node1_nei, node2_nei; /* ids of the swapped subtrees' roots */ };
+    NNIMove getBestNNIForBran(Node *node1, Node *node2, NNIMove moves[2], bool nni5 = true);
     /* the consumers of _pattern_lh_cat and _pattern_lh on the device */
     double optimizeMixtureWeights();                                 // ModelMixture::optimizeWeights, model/modelmixture.cpp:1356-1416
     const std::vector<double> &mixtureWeights() const { return mixprops_; }
@@ -190,7 +195,7 @@ private:
     int64_t ptn_begin_, ptn_end_;
     bool tip_partial_lh_computed_, weights_uploaded_, model_uploaded_;
     bool freq_dirty_, invar_dirty_, model_dirty_;   // which host inputs changed since they were last derived / uploaded
-    int nvec_;
+    int nvec_;                             // vectors of the tree; NNI_VECS more follow them (nni_partial_lh, phylotree.cpp:852-860)
     std::vector<lkcuda_partial_op> pending_ops_;
     std::vector<int> pending_level_;
     std::vector<int> vec_level_;           // level of the pending op writing each vector (0 = none)

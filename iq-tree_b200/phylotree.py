@@ -121,6 +121,7 @@ LKTREE_SYMBOLS = {
     "lktree_compute_likelihood_derv": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p]),
     "lktree_compute_likelihood_from_buffer": (C.c_int, [C.c_void_p, c_double_p]),
     "lktree_optimize_one_branch": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p]),
+    "lktree_get_best_nni_for_bran": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p]),
     "lktree_optimize_all_branches": (C.c_int, [C.c_void_p, C.c_int32, C.c_double, C.c_int32, c_double_p]),
     "lktree_set_branch_length": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_double]),
     "lktree_get_branch_length": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_double_p]),
@@ -373,6 +374,12 @@ class PhyloTree:
         ln = C.c_double()
         self._ck(self.lib.lktree_optimize_one_branch(self.h, node1, node2, max_nr_step, C.byref(ln)))
         return ln.value
+
+    def getBestNNIForBran(self, node1, node2, nni5=True):
+        """-> [(newloglh, newLen[5], node1_nei, node2_nei)] * 2 (PhyloTree::getBestNNIForBran, phylotree.cpp:2873-3066)"""
+        out = np.zeros(16, dtype=np.float64)
+        self._ck(self.lib.lktree_get_best_nni_for_bran(self.h, node1, node2, int(nni5), out.ctypes.data_as(c_double_p)))
+        return [(out[8 * c], out[8 * c + 1: 8 * c + 6].copy(), int(out[8 * c + 6]), int(out[8 * c + 7])) for c in range(2)]
 
     def optimizeAllBranches(self, iterations=100, tolerance=0.001, max_nr_step=100):
         lnl = C.c_double()

@@ -8,6 +8,7 @@ runs only in the build container; the resulting fixtures are committed and trave
 
     python oracle/make_golden.py            # all cases
     python oracle/make_golden.py dna_example_gtr_g4 ...
+    python oracle/make_golden.py --nni      # tests/golden/nni/*.npz: PhyloTree::getBestNNIForBran on every internal branch (NNI_CASES)
     python oracle/make_golden.py --aux      # tests/golden/aux/*.npz: RELL, pattern rates, mixture-weight EM of AUX_CASES
 
 Synthetic alignments (codon, deep DNA tree, morphological, multifurcating) are generated here with fixed seeds.
@@ -225,6 +226,19 @@ AUX_CASES = ["dna_example_gtr_g4", "dna_example_gtr_i_g4", "dna_deep_scaling", "
 AUX_SAMPLES = 24
 
 
+NNI_CASES = [("dna_example_gtr_g4", 1), ("dna_example_gtr_i_g4", 0), ("aa_lg_g4", 1), ("dna_deep_scaling", 1)]
+
+
+def pack_nni(case, nni5, d):
+    m = json.load(open(os.path.join(d, "metannni.json")))
+    z = {"meta": json.dumps(m), "ids": rd(d, "nni_ids.i32", np.int32).reshape(-1, 6), "vals": rd(d, "nni_vals.f64", np.float64).reshape(-1, 2, 6)}
+    os.makedirs(os.path.join(OUT, "nni"), exist_ok=True)
+    path = os.path.join(OUT, "nni", "%s.nni%d.npz" % (case, nni5))
+    np.savez_compressed(path, **z)
+    print("%-28s nni5=%d: %d branches, lnl %.10f (after: %.10f), best delta %.4f  %.0f KB" % (
+        case, nni5, m["nbranch"], m["lnl"], m["lnl_after"], z["vals"][:, :, 0].max() - m["lnl"], os.path.getsize(path) / 1024))
+
+
 def pack_aux(case, d):
     m = json.load(open(os.path.join(d, "metax.json")))
     P, ns = m["nptn"], m["nsamples"]
@@ -290,6 +304,17 @@ def main():
         "morph_mk_asc": ["-s", asc_aln, "-st", "MORPH", "-m", "MK+ASC", "-te", asc_tree],
         "bin_jc2_g4": ["-s", bin_aln, "-st", "BIN", "-m", "JC2+G4", "-te", bin_tree],
     }
+    if sys.argv[1:2] == ["--nni"]:
+        for case, nni5 in NNI_CASES:
+            d = os.path.join(tmp, "outn_" + case)
+            cmd = [HARNESS, "dumpnni", d, str(nni5)] + cases[case] + ["-nt", "1", "-seed", "1", "-pre", os.path.join(tmp, "runn_" + case)]
+            r = subprocess.run(cmd, cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            if r.returncode != 0:
+                print("%-28s nni FAILED:\n%s" % (case, r.stdout[-1500:]))
+                continue
+            pack_nni(case, nni5, d)
+        shutil.rmtree(tmp, ignore_errors=True)
+        return
     if sys.argv[1:2] == ["--aux"]:
         for case in (sys.argv[2:] or AUX_CASES):
             d = os.path.join(tmp, "outx_" + case)

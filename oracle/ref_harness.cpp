@@ -16,6 +16,7 @@
  *
  * usage: ref_harness dump <outdir> <iqtree args: -s aln -m MODEL -te tree -nt N ...>
  *        ref_harness dumpx <outdir> <nsamples> <iqtree args ...>
+ *        ref_harness dumpnni <outdir> <nni5: 0|1> <iqtree args ...>     PhyloTree::getBestNNIForBran on every internal branch
  *        ref_harness time <lnl_reps> <derv_reps> <oab_reps> <iqtree args ...>
  */
 #include <cstdio>
@@ -380,6 +381,55 @@ static int do_dumpx(int argc, char **argv) {
     return 0;
 }
 
+/* golden values of the NNI evaluation (PhyloTree::getBestNNIForBran, phylotree.cpp:2873-3066) on every internal branch, in the order of
+   computeBestTraversal; per branch: node1, node2 and, for both NNIs, newloglh, newLen[5] and the ids of the two swapped subtree roots */
+static int do_dumpnni(int argc, char **argv) {
+    g_out = argv[2];
+    mkdir(g_out.c_str(), 0755);
+    int nni5 = atoi(argv[3]);
+    std::vector<char*> args; args.push_back(argv[0]);
+    for (int i = 4; i < argc; i++) args.push_back(argv[i]);
+    Params &params = Params::getInstance();
+    IQTree *tree = setup((int)args.size(), &args[0], params);
+    if ((int)params.nni5 != nni5) {         // the nni_partial_lh buffers are sized by params->nni5 at allocation (phylotree.cpp:857)
+        params.nni5 = nni5 != 0;
+        tree->deleteAllPartialLh();
+        tree->initializeAllPartialLh();
+    }
+    tree->clearAllPartialLH();
+    double lnl = tree->computeLikelihood();
+    tree->curScore = lnl;
+    NodeVector nodes, nodes2;
+    tree->computeBestTraversal(nodes, nodes2);
+    std::vector<int> ids;
+    std::vector<double> vals;
+    for (size_t j = 0; j < nodes.size(); j++) {
+        if (nodes[j]->isLeaf() || nodes2[j]->isLeaf()) continue;
+        PhyloNode *node1 = (PhyloNode*)nodes[j], *node2 = (PhyloNode*)nodes2[j];
+        NNIMove mv[2];
+        mv[0].ptnlh = mv[1].ptnlh = NULL;
+        mv[0].node1 = NULL;
+        tree->getBestNNIForBran(node1, node2, mv);
+        ids.push_back(node1->id); ids.push_back(node2->id);
+        for (int c = 0; c < 2; c++) {
+            ids.push_back((*mv[c].node1Nei_it)->node->id); ids.push_back((*mv[c].node2Nei_it)->node->id);
+            vals.push_back(mv[c].newloglh);
+            for (int i = 0; i < 5; i++) vals.push_back(i < (nni5 ? 5 : 1) ? mv[c].newLen[i] : 0.0);
+        }
+    }
+    tree->clearAllPartialLH();
+    double lnl_after = tree->computeLikelihood();
+    wbin("nni_ids.i32", &ids[0], ids.size() * sizeof(int));
+    wbin("nni_vals.f64", &vals[0], vals.size() * 8);
+    {
+        std::ofstream f((g_out + "/metannni.json").c_str());
+        f << std::setprecision(17);
+        f << "{ \"nni5\": " << nni5 << ", \"nbranch\": " << ids.size() / 6 << ", \"lnl\": " << lnl << ", \"lnl_after\": " << lnl_after << " }\n";
+    }
+    printf("dumpnni nni5 %d branches %zu lnl %.10f after %.10f\n", nni5, ids.size() / 6, lnl, lnl_after);
+    return 0;
+}
+
 static int do_time(int argc, char **argv) {
     int lnl_reps = atoi(argv[2]), derv_reps = atoi(argv[3]), oab_reps = atoi(argv[4]);
     std::vector<char*> args; args.push_back(argv[0]);
@@ -424,6 +474,25 @@ static int do_time(int argc, char **argv) {
         t_oab += getRealTime() - a;
     }
     if (oab_reps) t_oab /= oab_reps;
+    /* LK_REF_NNI=n: time PhyloTree::getBestNNIForBran (both NNIs, 5 branches each) on the first n internal branches of the traversal */
+    int nni_n = getenv("LK_REF_NNI") ? atoi(getenv("LK_REF_NNI")) : 0, nni_done = 0;
+    double t_nni = 0.0;
+    if (nni_n > 0) {
+        tree->clearAllPartialLH();
+        tree->curScore = tree->computeLikelihood();
+        NodeVector nodes, nodes2;
+        tree->computeBestTraversal(nodes, nodes2);
+        for (size_t j = 0; j < nodes.size() && nni_done < nni_n; j++) {
+            if (nodes[j]->isLeaf() || nodes2[j]->isLeaf()) continue;
+            NNIMove mv[2];
+            mv[0].ptnlh = mv[1].ptnlh = NULL; mv[0].node1 = NULL;
+            a = getRealTime();
+            tree->getBestNNIForBran((PhyloNode*)nodes[j], (PhyloNode*)nodes2[j], mv);
+            t_nni += getRealTime() - a;
+            nni_done++;
+        }
+        if (nni_done) t_nni /= nni_done;
+    }
     double sum = 0, best = 1e300;
     for (size_t i = 0; i < lnl_t.size(); i++) { sum += lnl_t[i]; best = std::min(best, lnl_t[i]); }
     double mean = lnl_t.empty() ? 0 : sum / lnl_t.size();
@@ -433,10 +502,10 @@ static int do_time(int argc, char **argv) {
     printf("{\"ref_time\": true, \"kernel\": \"%s\", \"threads\": %d, \"nptn\": %zu, \"ntaxa\": %zu, \"blocks\": %zu, "
            "\"lnl\": %.12f, \"lnl_reps\": %d, \"lnl_s_mean\": %.6g, \"lnl_s_best\": %.6g, \"step_s_mean\": %.6g, \"step_s_total\": %.6g, "
            "\"df\": %.12g, \"ddf\": %.12g, \"derv_reps\": %d, \"derv_s_mean\": %.6g, "
-           "\"oab_lnl\": %.12f, \"oab_reps\": %d, \"oab_s_mean\": %.6g, \"setup_s\": %.4g}\n",
+           "\"oab_lnl\": %.12f, \"oab_reps\": %d, \"oab_s_mean\": %.6g, \"nni_branches\": %d, \"nni_s_mean\": %.6g, \"setup_s\": %.4g}\n",
            tree->sse == LK_EIGEN_SSE ? (instruction_set >= 7 ? "AVX" : "SSE") : "generic",
            params.num_threads, P, ntaxa, blocks, lnl, lnl_reps, mean, lnl_t.empty() ? 0.0 : best, step_mean, step_sum,
-           df, ddf, derv_reps, t_derv, oab, oab_reps, t_oab, t_setup);
+           df, ddf, derv_reps, t_derv, oab, oab_reps, t_oab, nni_done, t_nni, t_setup);
     return 0;
 }
 
@@ -444,6 +513,7 @@ int main(int argc, char **argv) {
     if (argc >= 4 && !strcmp(argv[1], "dump")) return do_dump(argc, argv);
     if (argc >= 6 && !strcmp(argv[1], "time")) return do_time(argc, argv);
     if (argc >= 5 && !strcmp(argv[1], "dumpx")) return do_dumpx(argc, argv);
+    if (argc >= 5 && !strcmp(argv[1], "dumpnni")) return do_dumpnni(argc, argv);
     fprintf(stderr, "usage: %s dump <outdir> <iqtree args>\n       %s time <lnl_reps> <derv_reps> <oab_reps> <iqtree args>\n", argv[0], argv[0]);
     return 2;
 }

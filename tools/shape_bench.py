@@ -67,6 +67,21 @@ def main():
         t.resetCounters()
         t0 = time.time(); l2 = t.optimizeAllBranches(1); out["oab1_second_s"] = time.time() - t0; out["oab1_second_lnl"] = l2
         out["oab_kernels"] = {k: {"n": v[0], "ms": v[2]} for k, v in t.kernelStats().items() if v[0]}
+    for a_ in sys.argv:
+        if a_.startswith("--nni="):     # PhyloTree::getBestNNIForBran (both NNIs, 5 branches each) on the first n internal branches
+            n = int(a_[6:])
+            t.clearAllPartialLH(); t.computeLikelihood()
+            deg = {}
+            for x, y in t.getTraversal():
+                deg[int(x)] = deg.get(int(x), 0) + 1; deg[int(y)] = deg.get(int(y), 0) + 1
+            br = [(int(x), int(y)) for x, y in t.getTraversal() if deg[int(x)] > 1 and deg[int(y)] > 1][:n]
+            t.getBestNNIForBran(*br[0])
+            t.resetCounters()
+            t0 = time.time()
+            best = [max(m[0] for m in t.getBestNNIForBran(x, y)) for x, y in br]
+            out["nni_branches"] = len(br); out["nni_ms_per_branch"] = (time.time() - t0) / len(br) * 1e3
+            out["nni_best_delta"] = max(best) - lnl
+            out["nni_kernels"] = {k: {"n": v[0], "ms": v[2]} for k, v in t.kernelStats().items() if v[0]}
     print(json.dumps(out))
     t.close()
 
