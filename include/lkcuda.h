@@ -188,6 +188,11 @@ int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result);
 int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, double xacc,
                          int32_t max_nr_step, double *out);
 
+/* lkcuda_theta_build + lkcuda_newton_branch on the branch (dad, node) in one call - for DNA with 4 categories ONE persistent launch that
+   builds theta_all in its first Newton step (optimizeOneBranch's device part, phylotree.cpp:2148-2170); same out[4] */
+int lkcuda_theta_newton(lkcuda_engine *e, int32_t dad, int32_t node, double x1, double xguess, double x2, double xacc,
+                        int32_t max_nr_step, double *out);
+
 /* results of the last enqueued reduction (synchronises) / their device address (for NCCL) */
 int lkcuda_read_result(lkcuda_engine *e, double *result);
 int lkcuda_result_device_ptr(lkcuda_engine *e, void **dev_ptr);

@@ -944,10 +944,9 @@ void PhyloTree::optimizeOneBranch(Node *node1, Node *node2, bool clearLH, int ma
         flushPartialOps();
         theta_computed = true;
         int32_t dad_end = dad->isLeaf() ? LKCUDA_TIP(dad->id) : node_branch->vec;
-        check(lkcuda_theta_build(engines_[0], dad_end, dad_branch->vec), engines_[0], "lkcuda_theta_build");
         double out[4];
-        check(lkcuda_newton_branch(engines_[0], min_branch_length, current_len, max_branch_length, min_branch_length, maxNRStep, out),
-              engines_[0], "lkcuda_newton_branch");
+        check(lkcuda_theta_newton(engines_[0], dad_end, dad_branch->vec, min_branch_length, current_len, max_branch_length, min_branch_length, maxNRStep, out),
+              engines_[0], "lkcuda_theta_newton");
         optx = out[0]; d2l = out[1];
         // minimizeNewton leaves the branch at the last length it evaluated (computeFuncDerv, phylotree.cpp:2136-2137)
         current_it->length = out[3]; current_it_back->length = out[3];

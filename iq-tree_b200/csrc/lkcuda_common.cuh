@@ -118,6 +118,7 @@ struct lkcuda_engine {
     unsigned int result_seq;                /* sequence number of the last publishing launch */
     lkc::PeerMbox *d_mbox; lkc::PeerMbox **d_peer_tab; void *peer_opened[LKCUDA_MAX_PEERS]; unsigned int peer_seq;
     double *d_newton_out; double *h_newton_out;
+    void *d_newton_ctl; int newton_max_grid;   /* state of the persistent Newton kernel; the largest grid that is co-resident */
     /* transition tables */
     double *d_tables; long long table_slots_cap;
     /* op upload ring (pinned host + device) */
@@ -279,43 +280,47 @@ __device__ __forceinline__ unsigned long long lk_globaltimer() {
     return t;
 }
 
-static __device__ __noinline__ void publish_result(const DevView &v, double (&r)[LKCUDA_NRESULT]) {
+/* the exchange alone (step 1 above) under sequence number `seq`; returns 1 when a peer did not show up in time */
+static __device__ __noinline__ unsigned int peer_exchange(const DevView &v, double (&r)[LKCUDA_NRESULT], unsigned int seq) {
     unsigned int err = 0;
-    if (v.peer_world > 1) {
-        const int par = (int)(v.peer_seq & 1u);
-        for (int q = 0; q < v.peer_world; q++) {
-            volatile double *dst = v.peer_mbox[q]->data[par][v.peer_rank];
+    const int par = (int)(seq & 1u);
+    for (int q = 0; q < v.peer_world; q++) {
+        volatile double *dst = v.peer_mbox[q]->data[par][v.peer_rank];
 #pragma unroll
-            for (int i = 0; i < LKCUDA_NRESULT; i++) dst[i] = r[i];
-        }
-        __threadfence_system();
-        for (int q = 0; q < v.peer_world; q++) {
-            unsigned int *f = &v.peer_mbox[q]->flag[par][v.peer_rank];
-            asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(f), "r"(v.peer_seq) : "memory");
-        }
-        PeerMbox *me = v.peer_mbox[v.peer_rank];
-        const unsigned long long t0 = lk_globaltimer();
-        for (int q = 0; q < v.peer_world && !err; q++) {
-            const unsigned int *f = &me->flag[par][q];
-            unsigned int seen;
-            for (;;) {
-                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
-                if (seen == v.peer_seq) break;
-                if (lk_globaltimer() - t0 > 10000000000ull) { err = 1; break; }      /* 10 s: a peer never launched its reduction */
-            }
-        }
-        if (!err) {
-            const double own6 = r[6];
-#pragma unroll
-            for (int i = 0; i < LKCUDA_NRESULT; i++) r[i] = 0.0;
-            for (int q = 0; q < v.peer_world; q++) {
-                const volatile double *src = me->data[par][q];
-#pragma unroll
-                for (int i = 0; i < LKCUDA_NRESULT; i++) r[i] += src[i];
-            }
-            r[6] = own6;
+        for (int i = 0; i < LKCUDA_NRESULT; i++) dst[i] = r[i];
+    }
+    __threadfence_system();
+    for (int q = 0; q < v.peer_world; q++) {
+        unsigned int *f = &v.peer_mbox[q]->flag[par][v.peer_rank];
+        asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(f), "r"(seq) : "memory");
+    }
+    PeerMbox *me = v.peer_mbox[v.peer_rank];
+    const unsigned long long t0 = lk_globaltimer();
+    for (int q = 0; q < v.peer_world && !err; q++) {
+        const unsigned int *f = &me->flag[par][q];
+        unsigned int seen;
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
+            if (seen == seq) break;
+            if (lk_globaltimer() - t0 > 10000000000ull) { err = 1; break; }      /* 10 s: a peer never launched its reduction */
         }
     }
+    if (!err) {
+        const double own6 = r[6];
+#pragma unroll
+        for (int i = 0; i < LKCUDA_NRESULT; i++) r[i] = 0.0;
+        for (int q = 0; q < v.peer_world; q++) {
+            const volatile double *src = me->data[par][q];
+#pragma unroll
+            for (int i = 0; i < LKCUDA_NRESULT; i++) r[i] += src[i];
+        }
+        r[6] = own6;
+    }
+    return err;
+}
+
+/* steps 2 and 3: device result block, host-mapped block + sequence number (| error << 32) */
+static __device__ __forceinline__ void post_result(const DevView &v, const double (&r)[LKCUDA_NRESULT], unsigned int err) {
 #pragma unroll
     for (int i = 0; i < LKCUDA_NRESULT; i++) v.result[i] = r[i];
     if (v.host_result) {
@@ -325,6 +330,12 @@ static __device__ __noinline__ void publish_result(const DevView &v, double (&r)
         __threadfence_system();
         *reinterpret_cast<volatile unsigned long long *>(v.host_result + LKCUDA_NRESULT) = (unsigned long long)v.seq | ((unsigned long long)err << 32);
     }
+}
+
+static __device__ __forceinline__ void publish_result(const DevView &v, double (&r)[LKCUDA_NRESULT]) {
+    unsigned int err = 0;
+    if (v.peer_world > 1) err = peer_exchange(v, r, v.peer_seq);
+    post_result(v, r, err);
 }
 
 }  // namespace lkc

@@ -161,7 +161,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     e->d_eval = e->d_evec = e->d_inv = e->d_rate = e->d_weight = e->d_tip = NULL; e->d_eigen = NULL;
     e->d_arena = NULL; e->d_scale = NULL; e->d_theta = NULL; e->d_theta_sc = NULL; e->d_theta_meta = NULL;
     e->d_plh = e->d_plhcat = e->d_plh_out = NULL; e->d_red = NULL; e->d_counter = NULL; e->d_result = NULL; e->h_result = NULL;
-    e->d_newton_out = NULL; e->h_newton_out = NULL;
+    e->d_newton_out = NULL; e->h_newton_out = NULL; e->d_newton_ctl = NULL; e->newton_max_grid = 0;
     e->d_ptn_model = NULL; e->d_state_mask = NULL;
     e->h_mapped = NULL; e->result_seq = 0; e->d_mbox = NULL; e->d_peer_tab = NULL; e->peer_seq = 0;
     memset(e->peer_opened, 0, sizeof(e->peer_opened));
@@ -275,7 +275,7 @@ int lkcuda_destroy(lkcuda_engine *e) {
     cudaFree(e->d_eval); cudaFree(e->d_evec); cudaFree(e->d_inv); cudaFree(e->d_rate); cudaFree(e->d_weight); cudaFree(e->d_eigen);
     cudaFree(e->d_tip); cudaFree(e->d_arena); cudaFree(e->d_scale); cudaFree(e->d_theta); cudaFree(e->d_theta_sc); cudaFree(e->d_theta_meta);
     cudaFree(e->d_plh); cudaFree(e->d_plhcat); cudaFree(e->d_plh_out); cudaFree(e->d_red); cudaFree(e->d_counter); cudaFree(e->d_result);
-    cudaFree(e->d_newton_out); cudaFree(e->d_tables); cudaFree(e->d_inv_frags);
+    cudaFree(e->d_newton_out); cudaFree(e->d_newton_ctl); cudaFree(e->d_tables); cudaFree(e->d_inv_frags);
     if (e->h_result) cudaFreeHost(e->h_result);
     if (e->h_newton_out) cudaFreeHost(e->h_newton_out);
     if (e->h_mapped) cudaFreeHost(e->h_mapped);

@@ -410,59 +410,194 @@ __device__ __forceinline__ void derv_finish(const DevView &v, const double (&acc
     publish_result(v, r);
 }
 
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
+
+/* the streaming pass of derv_b16_kernel / newton_b16_kernel: acc = {df, ddf, prob_const, df_const, ddf_const} partial sums of this thread.
+   DNA + 4 categories (128 bytes per pattern): one lane per pattern, the NEXT pattern's four sectors are requested before the current one
+   is reduced and the one after that is pulled into L2, so a lane always has 256 bytes on their way.  The first requests go out before
+   the exp() table is built. */
+__device__ __forceinline__ d4 ld_theta256(const double *p, bool coherent) {      /* coherent: theta_all was written earlier by this very launch */
+    if (!coherent) return ld_stream256(p);
+    d4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p) : "memory");
+    return r;
+}
+
+template <bool COHERENT>
+__device__ __forceinline__ void derv_b16_stream(const DevView &v, double len, double *val0, double *val1, double *val2, double (&acc)[5]) {
+    const long long nthr = (long long)gridDim.x * blockDim.x;
+    long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    d4 n[4]; double ninv = 0.0, nf = 0.0;
+    if (p < v.NP) {
+#pragma unroll
+        for (int u = 0; u < 4; u++) n[u] = ld_theta256(v.theta + p * 16 + 4 * u, COHERENT);
+        ninv = v.invar[p]; nf = p < v.P ? v.freq[p] : 0.0;
+        if (p + nthr < v.NP) prefetch_l2(v.theta + (p + nthr) * 16);
+    }
+    build_val(v, len, val0, val1, val2);
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 5; i++) acc[i] = 0.0;
+    while (p < v.NP) {
+        const d4 x[4] = {n[0], n[1], n[2], n[3]};
+        const double inv = ninv, f = nf;
+        const bool observed = p < v.P;
+        p += nthr;
+        if (p < v.NP) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) n[u] = ld_theta256(v.theta + p * 16 + 4 * u, COHERENT);
+            ninv = v.invar[p]; nf = p < v.P ? v.freq[p] : 0.0;
+            if (p + nthr < v.NP) prefetch_l2(v.theta + (p + nthr) * 16);
+        }
+        double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const double *w0 = val0 + 4 * u, *w1 = val1 + 4 * u, *w2 = val2 + 4 * u;
+            m0 = fma(x[u].x, w0[0], m0); m0 = fma(x[u].y, w0[1], m0); m0 = fma(x[u].z, w0[2], m0); m0 = fma(x[u].w, w0[3], m0);
+            m1 = fma(x[u].x, w1[0], m1); m1 = fma(x[u].y, w1[1], m1); m1 = fma(x[u].z, w1[2], m1); m1 = fma(x[u].w, w1[3], m1);
+            m2 = fma(x[u].x, w2[0], m2); m2 = fma(x[u].y, w2[1], m2); m2 = fma(x[u].z, w2[2], m2); m2 = fma(x[u].w, w2[3], m2);
+        }
+        const double lh = fabs(m0 + inv);
+        if (observed) {
+            const double df_frac = m1 / lh, ddf_frac = m2 / lh, t1 = df_frac * f, t2 = ddf_frac * f;
+            acc[0] += t1;
+            acc[1] += t2 - t1 * df_frac;
+        } else { acc[2] += lh; acc[3] += m1; acc[4] += m2; }
+    }
+}
+
 __global__ void __launch_bounds__(RED_THREADS, 2) derv_b16_kernel(DevView v, double len) {
     __shared__ __align__(32) double val0[16], val1[16], val2[16];
     __shared__ double sred[5 * 32];
-    build_val(v, len, val0, val1, val2);
-    __syncthreads();
-    double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
-    {
-        /* DNA + 4 categories (128 bytes per pattern): one lane per pattern, the NEXT pattern's four sectors are requested before the
-           current one is reduced, so every lane always has 128 bytes in flight */
-        const long long nthr = (long long)gridDim.x * blockDim.x;
-        long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-        d4 n[4]; double ninv = 0.0, nf = 0.0;
-        if (p < v.NP) {
-#pragma unroll
-            for (int u = 0; u < 4; u++) n[u] = ld_stream256(v.theta + p * 16 + 4 * u);
-            ninv = v.invar[p]; nf = p < v.P ? v.freq[p] : 0.0;
-        }
-        while (p < v.NP) {
-            const d4 x[4] = {n[0], n[1], n[2], n[3]};
-            const double inv = ninv, f = nf;
-            const bool observed = p < v.P;
-            p += nthr;
-            if (p < v.NP) {
-#pragma unroll
-                for (int u = 0; u < 4; u++) n[u] = ld_stream256(v.theta + p * 16 + 4 * u);
-                ninv = v.invar[p]; nf = p < v.P ? v.freq[p] : 0.0;
-            }
-            double m0 = 0.0, m1 = 0.0, m2 = 0.0;
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const double *w0 = val0 + 4 * u, *w1 = val1 + 4 * u, *w2 = val2 + 4 * u;
-                m0 = fma(x[u].x, w0[0], m0); m0 = fma(x[u].y, w0[1], m0); m0 = fma(x[u].z, w0[2], m0); m0 = fma(x[u].w, w0[3], m0);
-                m1 = fma(x[u].x, w1[0], m1); m1 = fma(x[u].y, w1[1], m1); m1 = fma(x[u].z, w1[2], m1); m1 = fma(x[u].w, w1[3], m1);
-                m2 = fma(x[u].x, w2[0], m2); m2 = fma(x[u].y, w2[1], m2); m2 = fma(x[u].z, w2[2], m2); m2 = fma(x[u].w, w2[3], m2);
-            }
-            const double lh = fabs(m0 + inv);
-            if (observed) {
-                const double df_frac = m1 / lh, ddf_frac = m2 / lh, t1 = df_frac * f, t2 = ddf_frac * f;
-                acc[0] += t1;
-                acc[1] += t2 - t1 * df_frac;
-            } else { acc[2] += lh; acc[3] += m1; acc[4] += m2; }
-        }
-    }
+    double acc[5];
+    derv_b16_stream<false>(v, len, val0, val1, val2, acc);
     if (grid_reduce<5>(acc, sred, v.red, v.counter)) derv_finish(v, acc);
+}
+
+/* ---- Optimization::minimizeNewton (optimization.cpp:388-465) as ONE persistent launch (DNA + 4 categories) ----
+   All blocks are co-resident (cooperative launch).  Per Newton step every block streams theta_all at the current length (the same
+   pass, grid and summation order as derv_b16_kernel: bit-identical df/ddf), the block that arrives last at the reduction forms df/ddf
+   (+ASC tail, NaN guard, cross-GPU exchange when peers are attached - every rank then takes the same decisions), advances the
+   reference's bracketing / Newton state machine by one evaluation and publishes the next length under a generation counter the other
+   blocks poll.  No launch, no host hand-over and no stream round trip between steps.  The state machine uses explicit _rn intrinsics:
+   no FMA contraction, the same IEEE operations as the host code it mirrors. */
+struct NewtonCtl {
+    double x;                       /* next length to evaluate */
+    double xl, xh, rts, dx, d2l, f, df;
+    int j, nev, phase, done;        /* done: 1 = finished, 2 = non-finite derivative, 3 = too many iterations */
+    double optx, last_x;
+    unsigned int gen;
+};
+
+__device__ __forceinline__ void newton_advance(NewtonCtl &c, double x1, double x2, double xacc, int maxNRStep) {
+    /* (f, df) = -(df, ddf) at c.rts have just been evaluated; mirrors optimization.cpp:396-463 */
+    const double f = c.f, df = c.df;
+    c.nev++; c.last_x = c.rts;
+    if (!isfinite(f) || !isfinite(df)) { c.done = 2; return; }
+    if (c.phase == 0) {
+        c.d2l = df;
+        if (df >= 0.0 && fabs(f) < xacc) { c.optx = c.rts; c.done = 1; return; }
+        if (f < 0.0) { c.xl = c.rts; c.xh = x2; } else { c.xh = c.rts; c.xl = x1; }
+        c.dx = fabs(__dsub_rn(c.xh, c.xl));
+        c.phase = 1; c.j = 1;
+    } else {
+        if (df > 0.0 && fabs(f) < xacc) { c.d2l = df; c.optx = c.rts; c.done = 1; return; }
+        if (f < 0.0) c.xl = c.rts; else c.xh = c.rts;
+        c.j++;
+        if (c.j > maxNRStep) { c.done = 3; return; }
+    }
+    const double rts_old = c.rts;
+    const double ta = __dsub_rn(__dmul_rn(__dsub_rn(c.rts, c.xh), df), f), tb = __dsub_rn(__dmul_rn(__dsub_rn(c.rts, c.xl), df), f);
+    if ((df <= 0.0) || (__dmul_rn(ta, tb) >= 0.0)) {
+        c.dx = __dmul_rn(0.5, __dsub_rn(c.xh, c.xl)); c.rts = __dadd_rn(c.xl, c.dx); c.d2l = df;
+        if (c.xl == c.rts) { c.optx = c.rts; c.done = 1; return; }
+    } else {
+        c.dx = __ddiv_rn(f, df); const double temp = c.rts; c.rts = __dsub_rn(c.rts, c.dx); c.d2l = df;
+        if (temp == c.rts) { c.optx = c.rts; c.done = 1; return; }
+    }
+    if (fabs(c.dx) < xacc || c.j == maxNRStep) { c.optx = rts_old; c.done = 1; return; }
+    c.x = c.rts;
+}
+
+template <bool TIP>
+__device__ __forceinline__ void theta_derv_b16_stream(const DevView &v, int dad, int node, double len, double *val0, double *val1, double *val2,
+                                                      double *tipT, double (&acc)[6]);
+
+/* BUILD 0: theta_all is there; 1 / 2: the first step builds it from the branch's two ends (dad a tip / an internal vector) while it
+   forms the first df/ddf (the pass of theta_derv_b16_kernel) - every lane later re-reads exactly the theta rows it wrote itself */
+template <int BUILD>
+__global__ void __launch_bounds__(RED_THREADS, 2) newton_b16_kernel(DevView v, NewtonCtl *ctl, int dad, int node, double x1, double xguess, double x2, double xacc, int maxNRStep) {
+    __shared__ __align__(32) double val0[16], val1[16], val2[16];
+    __shared__ __align__(32) double tipT[BUILD == 1 ? 32 * B16_TIPROW : 4];
+    __shared__ double sred[6 * 32];
+    __shared__ double sh_x; __shared__ int sh_done;
+    double x = xguess;
+    if (x < x1) x = x1;
+    if (x > x2) x = x2;
+    for (unsigned int it = 0;; it++) {
+        double acc[5];
+        bool elected;
+        if (BUILD != 0 && it == 0) {
+            double a6[6];
+            theta_derv_b16_stream<BUILD == 1>(v, dad, node, x, val0, val1, val2, tipT, a6);
+            elected = grid_reduce<6>(a6, sred, v.red, v.counter);
+            if (elected) v.theta_meta[0] = a6[5];
+#pragma unroll
+            for (int i = 0; i < 5; i++) acc[i] = a6[i];
+        } else {
+            derv_b16_stream<BUILD != 0>(v, x, val0, val1, val2, acc);
+            elected = grid_reduce<5>(acc, sred, v.red, v.counter);
+        }
+        if (elected) {          /* thread 0 of the block that arrived last */
+            double df = acc[0], ddf = acc[1];
+            if (isnan(df) || isinf(df)) { df = 0.0; ddf = 0.0; }    /* derv_finish */
+            if (v.U > 0) {
+                const double pc = 1.0 - acc[2], df_frac = acc[3] / pc, ddf_frac = acc[4] / pc;
+                df += v.nsite * df_frac;
+                ddf += v.nsite * (ddf_frac + df_frac * df_frac);
+            }
+            unsigned int err = 0;
+            if (v.peer_world > 1) {
+                double r[LKCUDA_NRESULT] = {0.0, df, ddf, 0.0, 0.0, 0.0, 0.0, 0.0};
+                err = peer_exchange(v, r, v.peer_seq + it);
+                df = r[LKCUDA_R_DF]; ddf = r[LKCUDA_R_DDF];
+            }
+            NewtonCtl c;            /* written by another SM in the previous step: read around L1 */
+            c.x = __ldcg(&ctl->x); c.xl = __ldcg(&ctl->xl); c.xh = __ldcg(&ctl->xh); c.rts = __ldcg(&ctl->rts); c.dx = __ldcg(&ctl->dx);
+            c.d2l = __ldcg(&ctl->d2l); c.j = __ldcg(&ctl->j); c.nev = __ldcg(&ctl->nev); c.phase = __ldcg(&ctl->phase); c.done = __ldcg(&ctl->done);
+            c.optx = __ldcg(&ctl->optx); c.last_x = __ldcg(&ctl->last_x);
+            if (it == 0) { c.rts = x; c.phase = 0; c.nev = 0; c.done = 0; c.j = 0; c.d2l = 0.0; c.optx = x; }
+            if (isnan(df) || isinf(df)) { df = 0.0; ddf = 0.0; }    /* computeLikelihoodDerv's own guard (phylokernel.h:647-651) */
+            c.f = -df; c.df = -ddf;                                 /* computeFuncDerv, phylotree.cpp:2143-2145 */
+            newton_advance(c, x1, x2, xacc, maxNRStep);
+            if (err) c.done = 4;
+            if (c.done) {
+                double r[LKCUDA_NRESULT] = {c.optx, c.d2l, (double)c.nev, c.last_x, (double)c.done, 0.0, 0.0, 0.0};
+                post_result(v, r, err);
+            }
+            ctl->x = c.x; ctl->xl = c.xl; ctl->xh = c.xh; ctl->rts = c.rts; ctl->dx = c.dx; ctl->d2l = c.d2l;
+            ctl->j = c.j; ctl->nev = c.nev; ctl->phase = c.phase; ctl->done = c.done; ctl->optx = c.optx; ctl->last_x = c.last_x;
+            __threadfence();
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(&ctl->gen), "r"(it + 1) : "memory");
+        }
+        if (threadIdx.x == 0) {
+            unsigned int g;
+            do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(g) : "l"(&ctl->gen) : "memory"); } while (g < it + 1);
+            sh_x = *reinterpret_cast<volatile double *>(&ctl->x);
+            sh_done = *reinterpret_cast<volatile int *>(&ctl->done);
+        }
+        __syncthreads();
+        if (sh_done) break;
+        x = sh_x;
+        __syncthreads();
+    }
 }
 
 /* theta_all build + first df/ddf in one pass (B = 16): lane = pattern; reads the node vector and the dad vector (or the dad
    tip's state), writes theta_all, keeps the three dot products.  acc[5] carries the scale sum that theta_kernel leaves in theta_meta. */
 template <bool TIP>
-__global__ void __launch_bounds__(RED_THREADS, 2) theta_derv_b16_kernel(DevView v, int dad, int node, double len) {
-    __shared__ __align__(32) double val0[16], val1[16], val2[16];
-    __shared__ __align__(32) double tipT[32 * B16_TIPROW];
-    __shared__ double sred[6 * 32];
+__device__ __forceinline__ void theta_derv_b16_stream(const DevView &v, int dad, int node, double len, double *val0, double *val1, double *val2,
+                                                      double *tipT, double (&acc)[6]) {
     build_val(v, len, val0, val1, val2);
     if (TIP) {
         for (int idx = threadIdx.x; idx < (v.SU + 1) * 16; idx += blockDim.x) {
@@ -475,7 +610,8 @@ __global__ void __launch_bounds__(RED_THREADS, 2) theta_derv_b16_kernel(DevView 
     const int16_t *sc_node = vec_sc(v, node), *sc_dad = TIP ? NULL : vec_sc(v, dad);
     const uint8_t *st = TIP ? tip_states(v, dad) : NULL;
     const long long nthr = (long long)gridDim.x * blockDim.x;
-    double acc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int i = 0; i < 6; i++) acc[i] = 0.0;
     for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < v.NP; p += nthr) {
         d4 x[4], y[4];
 #pragma unroll
@@ -509,6 +645,15 @@ __global__ void __launch_bounds__(RED_THREADS, 2) theta_derv_b16_kernel(DevView 
             if (sc) acc[5] += LK_LOG_THR * f * (double)sc;
         } else { acc[2] += lh; acc[3] += m1; acc[4] += m2; v.theta_sc[p - v.P] = (int16_t)sc; }
     }
+}
+
+template <bool TIP>
+__global__ void __launch_bounds__(RED_THREADS, 2) theta_derv_b16_kernel(DevView v, int dad, int node, double len) {
+    __shared__ __align__(32) double val0[16], val1[16], val2[16];
+    __shared__ __align__(32) double tipT[32 * B16_TIPROW];
+    __shared__ double sred[6 * 32];
+    double acc[6];
+    theta_derv_b16_stream<TIP>(v, dad, node, len, val0, val1, val2, tipT, acc);
     if (grid_reduce<6>(acc, sred, v.red, v.counter)) {
         v.theta_meta[0] = acc[5];
         const double a5[5] = {acc[0], acc[1], acc[2], acc[3], acc[4]};
@@ -646,7 +791,7 @@ void lkc::preload_reduce_kernels() {
     PRELOAD((branch_kernel<true, true>)); PRELOAD((branch_kernel<true, false>)); PRELOAD((branch_kernel<false, true>)); PRELOAD((branch_kernel<false, false>));
     PRELOAD(branch_tip_b16_kernel); PRELOAD(asc_adjust_kernel); PRELOAD(pattern_lh_cat_kernel);
     PRELOAD((theta_kernel<true, true>)); PRELOAD((theta_kernel<true, false>)); PRELOAD((theta_kernel<false, true>)); PRELOAD((theta_kernel<false, false>));
-    PRELOAD(derv_b16_kernel); PRELOAD(theta_derv_b16_kernel<true>); PRELOAD(theta_derv_b16_kernel<false>);
+    PRELOAD(newton_b16_kernel<0>); PRELOAD(newton_b16_kernel<1>); PRELOAD(newton_b16_kernel<2>); PRELOAD(derv_b16_kernel); PRELOAD(theta_derv_b16_kernel<true>); PRELOAD(theta_derv_b16_kernel<false>);
     PRELOAD(derv_kernel<true>); PRELOAD(derv_kernel<false>); PRELOAD(frombuf_kernel<true>); PRELOAD(frombuf_kernel<false>);
     PRELOAD(pattern_lh_corrected_kernel); PRELOAD(scale_factor_kernel);
     PRELOAD(sitemodel_reduce_kernel<0>); PRELOAD(sitemodel_reduce_kernel<1>); PRELOAD(sitemodel_reduce_kernel<2>); PRELOAD(sitemodel_reduce_kernel<3>);
@@ -881,10 +1026,80 @@ int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result) {
 
 /* Optimization::minimizeNewton (optimization.cpp:388-465) with computeFuncDerv = -(df, ddf) (phylotree.cpp:2135-2146).
    v1: the step sequence is driven from the host, one df/ddf launch + one 64-byte read-back per step. */
+/* the persistent launch; build: 0 = theta_all is ready, 1 / 2 = build it from (dad, node) in the first step.  Returns 1 when the shape has
+   no persistent kernel (the caller falls back to host-driven steps), 0 on success, < 0 = -(error code) */
+static int newton_persistent(lkcuda_engine *e, int build, int32_t dad, int32_t node, double x1, double xguess, double x2, double xacc, int32_t maxNRStep, double *out) {
+    const DevView &v = e->v;
+    GroupShape gs = group_shape(v);
+    static const bool host_loop = getenv("LKCUDA_HOST_NEWTON") && atoi(getenv("LKCUDA_HOST_NEWTON")) != 0;      /* test knob */
+    if (!(gs.vec && v.B == 16 && v.S == 4 && v.SU < 32) || IS_SITEMODEL(e) || host_loop) return 1;
+    int grid = red_grid(e, v.NP, gs.G);
+    if (grid > e->num_sms * 2) grid = e->num_sms * 2;
+    if (!e->d_newton_ctl) {
+        if (cudaMalloc((void **)&e->d_newton_ctl, 256) != cudaSuccess) return -cuda_fail(e, cudaGetLastError(), "cudaMalloc");
+        int occ = 0, o2 = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, newton_b16_kernel<0>, RED_THREADS, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, newton_b16_kernel<1>, RED_THREADS, 0); if (o2 < occ) occ = o2;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, newton_b16_kernel<2>, RED_THREADS, 0); if (o2 < occ) occ = o2;
+        e->newton_max_grid = occ * e->num_sms;
+    }
+    if (grid > e->newton_max_grid) grid = e->newton_max_grid;
+    if (grid < 1) return 1;
+    if (cudaMemsetAsync(e->d_newton_ctl, 0, 256, e->stream) != cudaSuccess) return -cuda_fail(e, cudaGetLastError(), "cudaMemsetAsync");
+    next_result(e);
+    launch_begin(e, KIND_NEWTON);
+    lkc::DevView vv = e->v;
+    NewtonCtl *ctl = (NewtonCtl *)e->d_newton_ctl;
+    int idad = dad, inode = node, imax = maxNRStep;
+    void *args[] = {&vv, &ctl, &idad, &inode, &x1, &xguess, &x2, &xacc, &imax};
+    const void *fn = build == 0 ? (const void *)newton_b16_kernel<0> : (build == 1 ? (const void *)newton_b16_kernel<1> : (const void *)newton_b16_kernel<2>);
+    cudaError_t ce = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(RED_THREADS), args, 0, e->stream);
+    if (ce != cudaSuccess) return -cuda_fail(e, ce, "newton_b16_kernel");
+    double r[LKCUDA_NRESULT];
+    int rcn = launch_end(e, KIND_NEWTON, 0, "newton_b16_kernel");
+    if (rcn) return -rcn;
+    rcn = lkcuda_wait_result(e, r);
+    if (rcn) return -rcn;
+    const int nev = (int)r[2], status = (int)r[4];
+    const uint64_t b = (uint64_t)v.B * 8;
+    uint64_t bytes = (uint64_t)nev * (uint64_t)v.NP * (b + 16);
+    if (build) bytes += (uint64_t)v.NP * (build == 1 ? 2 * b + 1 : 3 * b) - (uint64_t)v.NP * b;     /* the first step reads the two ends instead of theta_all */
+    e->kind_bytes[KIND_NEWTON] += bytes; e->bytes += bytes;
+    if (v.peer_world > 1 && nev > 1) e->peer_seq += (unsigned int)(nev - 1);     /* one exchange per evaluation */
+    out[0] = r[0]; out[1] = r[1]; out[2] = r[2]; out[3] = r[3];
+    if (status == 2) return -fail(e, LKCUDA_ERR_STATE, "Wrong computeFuncDerv");
+    if (status == 3) return -fail(e, LKCUDA_ERR_STATE, "Maximum number of iterations exceeded in minimizeNewton");
+    if (status != 1) return -fail(e, LKCUDA_ERR_STATE, "device Newton loop failed (status %d)", status);
+    return 0;
+}
+
+/* theta_all build + minimizeNewton on the branch (dad, node) in one call: optimizeOneBranch's device part (phylotree.cpp:2148-2170).
+   DNA + 4 categories: ONE persistent launch; other shapes: lkcuda_theta_build + lkcuda_newton_branch. */
+int lkcuda_theta_newton(lkcuda_engine *e, int32_t dad, int32_t node, double x1, double xguess, double x2, double xacc, int32_t maxNRStep, double *out) {
+    LK_ENTER(e);
+    if (!out) return fail(e, LKCUDA_ERR_ARG, "null output");
+    if (node < 0 || node >= e->cfg.nvec || !valid_end(e, dad) || dad == node) return fail(e, LKCUDA_ERR_ARG, "lkcuda_theta_newton: bad vector / taxon id");
+    int rc = check_ready(e, "lkcuda_theta_newton");
+    if (rc) return rc;
+    rc = states_barrier(e);
+    if (rc) return rc;
+    int pr = newton_persistent(e, LKCUDA_IS_TIP(dad) ? 1 : 2, dad, node, x1, xguess, x2, xacc, maxNRStep, out);
+    if (pr <= 0) {
+        if (pr == 0) { e->theta_ready = true; e->theta_dad = dad; e->theta_node = node; }
+        return -pr;
+    }
+    rc = lkcuda_theta_build(e, dad, node);
+    return rc ? rc : lkcuda_newton_branch(e, x1, xguess, x2, xacc, maxNRStep, out);
+}
+
 int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, double xacc, int32_t maxNRStep, double *out) {
     LK_ENTER(e);
     if (!out) return fail(e, LKCUDA_ERR_ARG, "null output");
     if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_newton_branch: theta_all not built");
+    {
+        int pr = newton_persistent(e, 0, 0, 0, x1, xguess, x2, xacc, maxNRStep, out);
+        if (pr <= 0) return -pr;
+    }
     int j, nev = 0, rc;
     double df, dx, f, temp, xh, xl, rts, rts_old, d2l, r[LKCUDA_NRESULT];
 #define FUNC_DERV(x) do { rc = enqueue_derv(e, (x)); if (rc) return rc; rc = lkcuda_wait_result(e, r); if (rc) return rc; \

@@ -56,6 +56,7 @@ LKCUDA_SYMBOLS = {
     "lkcuda_derv": (C.c_int, [C.c_void_p, C.c_double, c_double_p]),
     "lkcuda_lnl_from_buffer": (C.c_int, [C.c_void_p, C.c_double, c_double_p]),
     "lkcuda_newton_branch": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32, c_double_p]),
+    "lkcuda_theta_newton": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32, c_double_p]),
     "lkcuda_read_result": (C.c_int, [C.c_void_p, c_double_p]),
     "lkcuda_wait_result": (C.c_int, [C.c_void_p, c_double_p]),
     "lkcuda_peer_handle": (C.c_int, [C.c_void_p, c_uint8_p, C.POINTER(C.c_void_p)]),

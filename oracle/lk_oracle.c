@@ -627,6 +627,11 @@ int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, 
 #undef RETURN
 }
 
+int lkcuda_theta_newton(lkcuda_engine *e, int32_t dad, int32_t node, double x1, double xguess, double x2, double xacc, int32_t maxNRStep, double *out) {
+    int rc = lkcuda_theta_build(e, dad, node);
+    return rc ? rc : lkcuda_newton_branch(e, x1, xguess, x2, xacc, maxNRStep, out);
+}
+
 int lkcuda_read_result(lkcuda_engine *e, double *result) {
     if (!e || !result) return LKCUDA_ERR_ARG;
     memcpy(result, e->result, sizeof(e->result_own));
