@@ -98,6 +98,22 @@ lkcuda_engine *lktree_engine(lktree *h, int32_t i);
 int lktree_local_patterns(lktree *h, int64_t *begin, int64_t *end);
 /* global pattern range of in-process shard i (engine i) */
 int lktree_shard_patterns(lktree *h, int32_t i, int64_t *begin, int64_t *end);
+/* Fitch parsimony on the device (include/lkpars.h).  site_states[ntaxa][nsites] = the informative sites in
+   Alignment::ordered_pattern order with every pattern repeated `frequency` times (alignment.cpp:731-775); aln_nsite = getNSite().
+   lktree_compute_parsimony        PhyloTree::computeParsimony         phylotree.cpp:658-660
+   lktree_compute_parsimony_branch PhyloTree::computeParsimonyBranch   phylotree.cpp:653-655 (score of the tree, substitutions on the branch)
+   lktree_fix_negative_branch      PhyloTree::fixNegativeBranch        phylotree.cpp:2654-2694 (branch lengths from parsimony, JC-corrected)
+   lktree_compute_parsimony_tree   PhyloTree::computeParsimonyTree     phylotreepars.cpp:309-426: REPLACES the tree by the stepwise-addition
+                                   tree for the given addition order (the reference shuffles it with its own RNG), returns best_pars_score
+   lktree_get_branches             MTree::getBranches                  mtree.cpp:905-919: (node1, node2) id pairs in visiting order */
+int lktree_set_parsimony_sites(lktree *h, int64_t nsites, const uint8_t *site_states, int64_t aln_nsite, int32_t device /* -1: default */);
+int lktree_compute_parsimony(lktree *h, int32_t *score);
+int lktree_compute_parsimony_branch(lktree *h, int32_t node1, int32_t node2, int32_t *score, int32_t *branch_subst);
+int lktree_fix_negative_branch(lktree *h, int32_t force, int32_t *fixed);
+int lktree_compute_parsimony_tree(lktree *h, const int32_t *taxon_order /*[ntaxa]*/, int32_t *score);
+int lktree_get_branches(lktree *h, int32_t *pairs, int32_t capacity, int32_t *count);
+int lktree_get_adjacency(lktree *h, char *buf, size_t buflen);               /* the text format lktree_read_adjacency reads */
+struct lkpars_engine *lktree_pars_engine(lktree *h);
 uint64_t lktree_num_partial_lh_computations(lktree *h);
 
 #ifdef __cplusplus

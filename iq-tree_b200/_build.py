@@ -23,10 +23,11 @@ ORACLE_LIB = os.path.join(ORACLE_DIR, "_build", "liblktree_oracle.so")
 REF_HARNESS = os.path.join(ORACLE_DIR, "_ref", "ref_harness")
 REFERENCE = "/root/reference"
 
-CUDA_SOURCES = ["lkcuda_engine.cu", "lkcuda_partial.cu", "lkcuda_partial_mma.cu", "lkcuda_partial_mmak.cu", "lkcuda_reduce.cu", "lkcuda_aux.cu", "lkcuda_sitemodel.cu", "lk_phylotree.cpp", "lk_capi.cpp"]
-HOST_SOURCES = ["lk_phylotree.cpp", "lk_capi.cpp"]
+CUDA_SOURCES = ["lkcuda_engine.cu", "lkcuda_partial.cu", "lkcuda_partial_mma.cu", "lkcuda_partial_mmak.cu", "lkcuda_reduce.cu", "lkcuda_aux.cu", "lkcuda_sitemodel.cu", "lkcuda_pars.cu", "lk_phylotree.cpp", "lk_parsimony.cpp", "lk_capi.cpp"]
+HOST_SOURCES = ["lk_phylotree.cpp", "lk_parsimony.cpp", "lk_capi.cpp"]
+ORACLE_SOURCES = ["lk_oracle.c", "lkpars_oracle.c"]
 HEADERS = [os.path.join(CSRC, "lkcuda_common.cuh"), os.path.join(CSRC, "lkcuda_traverse.cuh"), os.path.join(CSRC, "lk_phylotree.h"),
-           os.path.join(ROOT, "include", "lkcuda.h"), os.path.join(ROOT, "include", "lktree.h")]
+           os.path.join(ROOT, "include", "lkcuda.h"), os.path.join(ROOT, "include", "lktree.h"), os.path.join(ROOT, "include", "lkpars.h")]
 
 
 def _newer(target, sources):
@@ -73,7 +74,7 @@ def build_cuda(force=False, verbose=False):
 
 def build_oracle(force=False):
     """TEST INFRASTRUCTURE: host mirror + scalar C oracle (no CUDA)."""
-    srcs = [os.path.join(CSRC, s) for s in HOST_SOURCES] + [os.path.join(ORACLE_DIR, "lk_oracle.c")]
+    srcs = [os.path.join(CSRC, s) for s in HOST_SOURCES] + [os.path.join(ORACLE_DIR, s) for s in ORACLE_SOURCES]
     if not force and not _newer(ORACLE_LIB, srcs + HEADERS):
         return ORACLE_LIB
     if shutil.which("gcc") is None or shutil.which("g++") is None:
@@ -83,9 +84,10 @@ def build_oracle(force=False):
     bdir = os.path.dirname(ORACLE_LIB)
     os.makedirs(bdir, exist_ok=True)
     objs = []
-    o = os.path.join(bdir, "lk_oracle.o")
-    _run(["gcc", "-O2", "-fPIC", "-ffp-contract=off", "-c", os.path.join(ORACLE_DIR, "lk_oracle.c"), "-o", o])
-    objs.append(o)
+    for s in ORACLE_SOURCES:
+        o = os.path.join(bdir, s.replace(".c", ".o"))
+        _run(["gcc", "-O2", "-fPIC", "-ffp-contract=off", "-c", os.path.join(ORACLE_DIR, s), "-o", o])
+        objs.append(o)
     for s in HOST_SOURCES:
         o = os.path.join(bdir, s.replace(".cpp", ".o"))
         _run(["g++", "-O2", "-fPIC", "-std=c++17", "-c", os.path.join(CSRC, s), "-o", o])

@@ -229,6 +229,63 @@ int lktree_shard_patterns(lktree *h, int32_t i, int64_t *begin, int64_t *end) {
     LK_CATCH(h)
 }
 
+/* ---- Fitch parsimony ---- */
+int lktree_set_parsimony_sites(lktree *h, int64_t nsites, const uint8_t *site_states, int64_t aln_nsite, int32_t device) {
+    LK_TRY(h) h->tree.setParsimonySites(nsites, site_states, aln_nsite); h->tree.pars_device = device; LK_CATCH(h)
+}
+int lktree_compute_parsimony(lktree *h, int32_t *score) { LK_TRY(h) *score = h->tree.computeParsimony(); LK_CATCH(h) }
+int lktree_compute_parsimony_branch(lktree *h, int32_t node1, int32_t node2, int32_t *score, int32_t *branch_subst) {
+    LK_TRY(h)
+    Node *n1 = nodeById(h, node1), *n2 = nodeById(h, node2);
+    Neighbor *nei = n1->findNeighbor(n2);
+    if (!nei) throw std::runtime_error("not a branch");
+    int subst = 0;
+    *score = h->tree.computeParsimonyBranch(nei, n1, &subst);
+    if (branch_subst) *branch_subst = subst;
+    LK_CATCH(h)
+}
+int lktree_fix_negative_branch(lktree *h, int32_t force, int32_t *fixed) {
+    LK_TRY(h) int n = h->tree.fixNegativeBranch(force != 0); if (fixed) *fixed = n; LK_CATCH(h)
+}
+int lktree_compute_parsimony_tree(lktree *h, const int32_t *taxon_order, int32_t *score) {
+    LK_TRY(h) *score = h->tree.computeParsimonyTree(taxon_order); LK_CATCH(h)
+}
+int lktree_get_branches(lktree *h, int32_t *pairs, int32_t capacity, int32_t *count) {
+    LK_TRY(h)
+    std::vector<Node*> a, b;
+    h->tree.getBranches(a, b);
+    *count = (int32_t)a.size();
+    for (size_t i = 0; i < a.size() && (int32_t)i < capacity; i++) { pairs[2 * i] = a[i]->id; pairs[2 * i + 1] = b[i]->id; }
+    LK_CATCH(h)
+}
+static void collectNodes(Node *node, Node *dad, std::vector<Node*> &out) {
+    out.push_back(node);
+    for (size_t i = 0; i < node->neighbors.size(); i++) if (node->neighbors[i]->node != dad) collectNodes(node->neighbors[i]->node, node, out);
+}
+/* the text lktree_read_adjacency reads: nodes in pre-order from the root, neighbours in their stored order */
+int lktree_get_adjacency(lktree *h, char *buf, size_t buflen) {
+    LK_TRY(h)
+    if (!h->tree.root) throw std::runtime_error("no tree");
+    std::vector<Node*> nodes;
+    collectNodes(h->tree.root, NULL, nodes);
+    std::string out = "root " + std::to_string(h->tree.root->id) + " nodes " + std::to_string(nodes.size()) + " leaves " + std::to_string(h->tree.leafNum) + "\n";
+    char num[64];
+    for (size_t i = 0; i < nodes.size(); i++) {
+        Node *n = nodes[i];
+        out += "node " + std::to_string(n->id) + " " + (n->isLeaf() ? "1" : "0") + " " + (n->name.empty() ? std::string("-") : n->name) + " " + std::to_string(n->neighbors.size());
+        for (size_t k = 0; k < n->neighbors.size(); k++) {
+            snprintf(num, sizeof num, " %d %.17g", n->neighbors[k]->node->id, n->neighbors[k]->length);
+            out += num;
+        }
+        out += "\n";
+    }
+    if (out.size() + 1 > buflen) throw std::runtime_error("buffer too small");
+    memcpy(buf, out.c_str(), out.size() + 1);
+    LK_CATCH(h)
+}
+
+lkpars_engine *lktree_pars_engine(lktree *h) { return h ? h->tree.parsEngine() : NULL; }
+
 uint64_t lktree_num_partial_lh_computations(lktree *h) { return h ? h->tree.num_partial_lh_computations : 0; }
 
 }  // extern "C"

@@ -32,10 +32,12 @@ PhyloTree::PhyloTree()
       state_unknown(0), seq_type(SEQ_DNA), ntaxa(0), nptn(0), nunobs(0), nsite(0), p_invar_(0.0),
       proc_rank_(0), proc_world_(1), allreduce_(NULL), allreduce_user_(NULL), stream_(NULL), peers_attached_(false), boot_nsamples_(0),
       ptn_begin_(0), ptn_end_(0), tip_partial_lh_computed_(false), weights_uploaded_(false), model_uploaded_(false),
-      freq_dirty_(true), invar_dirty_(true), model_dirty_(true), nvec_(0) {}
+      freq_dirty_(true), invar_dirty_(true), model_dirty_(true), nvec_(0),
+      pars_device(-1), pars_(NULL), pars_nsites_(0), pars_aln_nsite_(0), pars_nvec_(0) {}
 
 PhyloTree::~PhyloTree() {
     deleteAllPartialLh();
+    deleteAllPartialPars();
     for (size_t i = 0; i < allNodes.size(); i++) {
         for (size_t k = 0; k < allNodes[i]->neighbors.size(); k++) delete allNodes[i]->neighbors[k];
         delete allNodes[i];

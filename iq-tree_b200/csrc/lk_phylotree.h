@@ -24,6 +24,11 @@
  *   optimizeOneBranch / optimizeAllBranches  phylotree.cpp:2148-2192, 2252-2332
  *   getBestNNIForBran                    phylotree.cpp:2873-3066 (NNI evaluation of the tree search)
  *   readTree / parseFile (Newick)        mtree.cpp:503-680
+ *   initializeAllPartialPars             phylotree.cpp:596-624            (lk_parsimony.cpp)
+ *   computePartialParsimony / computeParsimonyBranch / computeParsimony   phylotreepars.cpp:18-282, phylotree.cpp:638-660
+ *   computeParsimonyTree / addTaxonMPFast    phylotreepars.cpp:309-465    (stepwise-addition start tree)
+ *   fixNegativeBranch                    phylotree.cpp:2654-2694
+ *   getBranches                          mtree.cpp:905-919
  */
 #ifndef LK_PHYLOTREE_H
 #define LK_PHYLOTREE_H
@@ -33,6 +38,7 @@
 #include <vector>
 #include <stdexcept>
 #include "../../include/lkcuda.h"
+#include "../../include/lkpars.h"
 
 namespace lk {
 
@@ -44,8 +50,9 @@ struct Neighbor {
     double length;
     int id;
     int vec;                    // arena vector holding the partial of the subtree rooted at `node`; -1 = none (leaf)
-    int partial_lh_computed;    // bit 0 = likelihood partial up to date
-    Neighbor(Node *n, double len) : node(n), length(len), id(-1), vec(-1), partial_lh_computed(0) {}
+    int partial_lh_computed;    // bit 0 = likelihood partial up to date, bit 1 = parsimony partial up to date
+    int pars_vec;               // partial_pars: block index in central_partial_pars (a neighbour that points to a leaf uses the tip's vector instead)
+    Neighbor(Node *n, double len) : node(n), length(len), id(-1), vec(-1), partial_lh_computed(0), pars_vec(-1) {}
 };
 
 struct Node {
@@ -148,6 +155,23 @@ public:
     void restoreBranchLengths(const std::vector<double> &lenvec, int startid = 0, Node *node = NULL, Node *dad = NULL);
     void clearReversePartialLh(Node *node, Node *dad);
 
+    /* ---- Fitch parsimony on the device (include/lkpars.h) ---- */
+    // the informative sites in Alignment::ordered_pattern order, pattern p repeated frequency[p] times (alignment.cpp:731-775):
+    // site_states[ntaxa][nsites]; aln_nsite = Alignment::getNSite() (all sites, for fixNegativeBranch)
+    void setParsimonySites(int64_t nsites, const uint8_t *site_states, int64_t aln_nsite);
+    void initializeAllPartialPars();                                 // phylotree.cpp:596-624
+    void deleteAllPartialPars();
+    void computePartialParsimony(Neighbor *dad_branch, Node *dad);   // phylotreepars.cpp:18-215: queues the dirty partials, post-order
+    int computeParsimonyBranch(Neighbor *dad_branch, Node *dad, int *branch_subst = NULL);   // phylotreepars.cpp:218-282
+    int computeParsimony();                                          // phylotree.cpp:658-660
+    int fixNegativeBranch(bool force, Node *node = NULL, Node *dad = NULL);   // phylotree.cpp:2654-2694, all branches in one launch
+    // phylotreepars.cpp:309-426; taxon_order = the shuffled addition order (my_random_shuffle stays with the caller's RNG).
+    // Replaces the tree; returns best_pars_score.  All 2k-3 insertions of a round are scored by ONE launch pair.
+    int computeParsimonyTree(const int32_t *taxon_order);
+    void getBranches(std::vector<Node*> &nodes, std::vector<Node*> &nodes2, Node *node = NULL, Node *dad = NULL);   // mtree.cpp:905-919
+    lkpars_engine *parsEngine() { return pars_; }
+    int pars_device;             // CUDA ordinal of the parsimony engine (default: the first of setDevices, else 0)
+
     /* parameters (tools.cpp:785-786, phyloanalysis.cpp:2488-2497) */
     double min_branch_length, max_branch_length;
     bool device_newton;          // run minimizeNewton's loop on the device (single shard only)
@@ -164,6 +188,20 @@ public:
     std::vector<std::string> seq_names;
 
 private:
+    /* parsimony bookkeeping (lk_parsimony.cpp) */
+    int parsVec(const Neighbor *nei) const;                          // the engine vector a neighbour's partial_pars lives in
+    int parsQueue(int kind, int dst, int a, int b, int c);
+    void parsFlush();                                                // one lkpars_run of everything queued; resolves the subtree scores
+    void parsCheck(int rc, const char *what);
+    void freeNodes();
+    lkpars_engine *pars_;
+    std::vector<uint8_t> pars_states_;
+    int64_t pars_nsites_, pars_aln_nsite_;
+    int pars_nvec_;
+    std::vector<uint32_t> pars_score_;                               // per engine vector: partial_pars[scoreid]
+    std::vector<lkpars_op> pars_ops_;
+    std::vector<uint32_t> pars_counts_;                              // [op][2] of the last flush
+
     void flushPartialOps();
     void enqueuePatternLhCat();
     int collapsePatternLhCat(int wsl);

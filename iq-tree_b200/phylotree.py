@@ -136,6 +136,26 @@ LKTREE_SYMBOLS = {
     "lktree_local_patterns": (C.c_int, [C.c_void_p, c_int64_p, c_int64_p]),
     "lktree_shard_patterns": (C.c_int, [C.c_void_p, C.c_int32, c_int64_p, c_int64_p]),
     "lktree_num_partial_lh_computations": (C.c_uint64, [C.c_void_p]),
+    "lktree_set_parsimony_sites": (C.c_int, [C.c_void_p, C.c_int64, c_uint8_p, C.c_int64, C.c_int32]),
+    "lktree_compute_parsimony": (C.c_int, [C.c_void_p, c_int32_p]),
+    "lktree_compute_parsimony_branch": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_int32_p, c_int32_p]),
+    "lktree_fix_negative_branch": (C.c_int, [C.c_void_p, C.c_int32, c_int32_p]),
+    "lktree_compute_parsimony_tree": (C.c_int, [C.c_void_p, c_int32_p, c_int32_p]),
+    "lktree_get_branches": (C.c_int, [C.c_void_p, c_int32_p, C.c_int32, c_int32_p]),
+    "lktree_get_adjacency": (C.c_int, [C.c_void_p, C.c_char_p, C.c_size_t]),
+    "lktree_pars_engine": (C.c_void_p, [C.c_void_p]),
+}
+
+# include/lkpars.h
+LKPARS_SYMBOLS = {
+    "lkpars_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, c_uint8_p, c_uint64_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    "lkpars_destroy": (C.c_int, [C.c_void_p]),
+    "lkpars_last_error": (C.c_char_p, [C.c_void_p]),
+    "lkpars_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(C.c_uint32)]),
+    "lkpars_words": (C.c_int, [C.c_void_p, c_int64_p]),
+    "lkpars_fetch_vector": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_uint32)]),
+    "lkpars_launch_count": (C.c_int, [C.c_void_p, c_uint64_p, c_double_p]),
+    "lkpars_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
 }
 
 
@@ -144,7 +164,7 @@ class LkError(RuntimeError):
 
 
 def _bind(lib):
-    for table in (LKCUDA_SYMBOLS, LKTREE_SYMBOLS):
+    for table in (LKCUDA_SYMBOLS, LKTREE_SYMBOLS, LKPARS_SYMBOLS):
         for name, (res, args) in table.items():
             fn = getattr(lib, name)      # AttributeError if the library does not export it
             fn.restype = res
@@ -409,6 +429,61 @@ class PhyloTree:
         cnt = C.c_int32()
         self._ck(self.lib.lktree_get_traversal(self.h, pairs.ctypes.data_as(c_int32_p), cap, C.byref(cnt)))
         return pairs[: 2 * cnt.value].reshape(-1, 2).copy()
+
+    # ---- Fitch parsimony ----
+    def setParsimonySites(self, site_states, aln_nsite, device=-1):
+        """site_states[ntaxa][nsites]: the informative sites in Alignment::ordered_pattern order, patterns repeated `frequency` times"""
+        st = np.ascontiguousarray(site_states, dtype=np.uint8)
+        assert st.ndim == 2 and st.shape[0] == self.ntaxa
+        self._pars_sites = st
+        self._ck(self.lib.lktree_set_parsimony_sites(self.h, st.shape[1], st.ctypes.data_as(c_uint8_p), int(aln_nsite), device))
+
+    def computeParsimony(self):
+        v = C.c_int32()
+        self._ck(self.lib.lktree_compute_parsimony(self.h, C.byref(v)))
+        return v.value
+
+    def computeParsimonyBranch(self, node1, node2):
+        """(parsimony score of the tree, substitutions on the branch) - PhyloTree::computeParsimonyBranch with branch_subst"""
+        v, b = C.c_int32(), C.c_int32()
+        self._ck(self.lib.lktree_compute_parsimony_branch(self.h, node1, node2, C.byref(v), C.byref(b)))
+        return v.value, b.value
+
+    def fixNegativeBranch(self, force=True):
+        v = C.c_int32()
+        self._ck(self.lib.lktree_fix_negative_branch(self.h, int(force), C.byref(v)))
+        return v.value
+
+    def computeParsimonyTree(self, taxon_order):
+        """PhyloTree::computeParsimonyTree for the given addition order: replaces the tree, returns best_pars_score"""
+        o = np.ascontiguousarray(taxon_order, dtype=np.int32)
+        assert o.size == self.ntaxa
+        v = C.c_int32()
+        self._ck(self.lib.lktree_compute_parsimony_tree(self.h, o.ctypes.data_as(c_int32_p), C.byref(v)))
+        return v.value
+
+    def getBranches(self):
+        cap = 4 * max(self.ntaxa, 2)
+        pairs = np.zeros(2 * cap, dtype=np.int32)
+        cnt = C.c_int32()
+        self._ck(self.lib.lktree_get_branches(self.h, pairs.ctypes.data_as(c_int32_p), cap, C.byref(cnt)))
+        return pairs[: 2 * cnt.value].reshape(-1, 2).copy()
+
+    def getAdjacency(self):
+        buf = C.create_string_buffer(256 * max(self.ntaxa, 4) + 4096)
+        self._ck(self.lib.lktree_get_adjacency(self.h, buf, len(buf)))
+        return buf.value.decode()
+
+    def parsEngine(self):
+        return self.lib.lktree_pars_engine(self.h)
+
+    def parsLaunches(self):
+        n, ms = C.c_uint64(), C.c_double()
+        e = self.parsEngine()
+        if not e:
+            return 0, 0.0
+        self.lib.lkpars_launch_count(e, C.byref(n), C.byref(ms))
+        return n.value, ms.value
 
     def branchVector(self, frm, to):
         vec, comp = C.c_int32(), C.c_int32()

@@ -10,6 +10,7 @@ runs only in the build container; the resulting fixtures are committed and trave
     python oracle/make_golden.py dna_example_gtr_g4 ...
     python oracle/make_golden.py --nni      # tests/golden/nni/*.npz: PhyloTree::getBestNNIForBran on every internal branch (NNI_CASES)
     python oracle/make_golden.py --aux      # tests/golden/aux/*.npz: RELL, pattern rates, mixture-weight EM of AUX_CASES
+    python oracle/make_golden.py --pars     # tests/golden/pars/*.npz: Fitch parsimony scores per branch + stepwise-addition trees (PARS_CASES)
 
 Synthetic alignments (codon, deep DNA tree, morphological, multifurcating) are generated here with fixed seeds.
 """
@@ -239,6 +240,23 @@ def pack_nni(case, nni5, d):
         case, nni5, m["nbranch"], m["lnl"], m["lnl_after"], z["vals"][:, :, 0].max() - m["lnl"], os.path.getsize(path) / 1024))
 
 
+PARS_CASES = [("dna_example_gtr_g4", 1), ("dna_example_gtr_g4", 7), ("dna_deep_scaling", 1), ("aa_lg_g4", 1), ("aa_lg_g4", 5), ("codon_gy", 1),
+              ("morph_mk_g4", 1), ("bin_jc2_g4", 3)]
+
+
+def pack_pars(case, seed, d):
+    m = json.load(open(os.path.join(d, "metapars.json")))
+    nt, ns = m["ntaxa"], m["nsites_informative"]
+    z = {"meta": json.dumps(m), "sites": rd(d, "pars_sites.u8", np.uint8).reshape(nt, ns),
+         "branches": rd(d, "pars_branches.i32", np.int32).reshape(-1, 4), "order": rd(d, "pars_order.i32", np.int32),
+         "tree": open(os.path.join(d, "pars_tree.txt")).read(), "stepwise_tree": open(os.path.join(d, "pars_stepwise_tree.txt")).read()}
+    os.makedirs(os.path.join(OUT, "pars"), exist_ok=True)
+    path = os.path.join(OUT, "pars", "%s.seed%d.npz" % (case, seed))
+    np.savez_compressed(path, **z)
+    print("%-28s seed %d: %d taxa x %d informative sites, score %d, stepwise %d (check %d)  %.0f KB" % (
+        case, seed, nt, ns, m["score"], m["stepwise_score"], m["stepwise_check"], os.path.getsize(path) / 1024))
+
+
 def pack_aux(case, d):
     m = json.load(open(os.path.join(d, "metax.json")))
     P, ns = m["nptn"], m["nsamples"]
@@ -313,6 +331,17 @@ def main():
                 print("%-28s nni FAILED:\n%s" % (case, r.stdout[-1500:]))
                 continue
             pack_nni(case, nni5, d)
+        shutil.rmtree(tmp, ignore_errors=True)
+        return
+    if sys.argv[1:2] == ["--pars"]:
+        for case, seed in PARS_CASES:
+            d = os.path.join(tmp, "outp_%s_%d" % (case, seed))
+            cmd = [HARNESS, "dumppars", d, str(seed)] + cases[case] + ["-nt", "1", "-seed", "1", "-pre", os.path.join(tmp, "runp_" + case)]
+            r = subprocess.run(cmd, cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            if r.returncode != 0:
+                print("%-28s pars FAILED:\n%s" % (case, r.stdout[-1500:]))
+                continue
+            pack_pars(case, seed, d)
         shutil.rmtree(tmp, ignore_errors=True)
         return
     if sys.argv[1:2] == ["--aux"]:

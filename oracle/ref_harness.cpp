@@ -17,6 +17,7 @@
  * usage: ref_harness dump <outdir> <iqtree args: -s aln -m MODEL -te tree -nt N ...>
  *        ref_harness dumpx <outdir> <nsamples> <iqtree args ...>
  *        ref_harness dumpnni <outdir> <nni5: 0|1> <iqtree args ...>     PhyloTree::getBestNNIForBran on every internal branch
+ *        ref_harness dumppars <outdir> <seed> <iqtree args ...>         Fitch parsimony: scores per branch, stepwise-addition tree
  *        ref_harness time <lnl_reps> <derv_reps> <oab_reps> <iqtree args ...>
  */
 #include <cstdio>
@@ -430,6 +431,71 @@ static int do_dumpnni(int argc, char **argv) {
     return 0;
 }
 
+/* Fitch parsimony: the inputs and outputs of the reference's own computeParsimony / computeParsimonyBranch on the
+   fixture tree, and of computeParsimonyTree (stepwise addition) with the addition order its RNG produces for <seed> */
+static int do_dumppars(int argc, char **argv) {
+    g_out = argv[2];
+    mkdir(g_out.c_str(), 0755);
+    int seed = atoi(argv[3]);
+    std::vector<char*> args; args.push_back(argv[0]);
+    for (int i = 4; i < argc; i++) args.push_back(argv[i]);
+    Params &params = Params::getInstance();
+    IQTree *tree = setup((int)args.size(), &args[0], params);
+    Alignment *aln = tree->aln;
+    if (aln->ordered_pattern.empty()) aln->orderPatternByNumChars();
+    const int ntaxa = aln->getNSeq();
+    const size_t nsites = aln->num_informative_sites;
+    std::vector<unsigned char> sites((size_t)ntaxa * nsites);
+    {
+        size_t site = 0;
+        for (Alignment::iterator pat = aln->ordered_pattern.begin(); pat != aln->ordered_pattern.end(); pat++)
+            for (int j = 0; j < pat->frequency; j++, site++)
+                for (int t = 0; t < ntaxa; t++) sites[(size_t)t * nsites + site] = (unsigned char)pat->at(t);
+        if (site != nsites) { fprintf(stderr, "informative site count mismatch\n"); return 4; }
+    }
+    wbin("pars_sites.u8", sites.empty() ? NULL : &sites[0], sites.size());
+    dumpAdjacency(tree, "pars_tree.txt");
+    int score = tree->computeParsimony();
+    NodeVector nodes1, nodes2;
+    tree->getBranches(nodes1, nodes2);
+    std::vector<int> br;
+    for (size_t i = 0; i < nodes1.size(); i++) {
+        int subst = -1;
+        int sc = tree->computeParsimonyBranch((PhyloNeighbor*)nodes1[i]->findNeighbor(nodes2[i]), (PhyloNode*)nodes1[i], &subst);
+        br.push_back(nodes1[i]->id); br.push_back(nodes2[i]->id); br.push_back(sc); br.push_back(subst);
+    }
+    wbin("pars_branches.i32", &br[0], br.size() * sizeof(int));
+    /* the addition order computeParsimonyTree will draw: same generator state, same shuffle (phylotreepars.cpp:318-323) */
+    init_random(seed, false);
+    IntVector order(ntaxa);
+    for (int i = 0; i < ntaxa; i++) order[i] = i;
+    my_random_shuffle(order.begin(), order.end());
+    wbin("pars_order.i32", &order[0], order.size() * sizeof(int));
+    init_random(seed, false);
+    IQTree *t2 = new IQTree(aln);
+    t2->setParams(&params);
+    double t0 = omp_get_wtime();
+    int best = t2->computeParsimonyTree(NULL, aln);
+    double secs = omp_get_wtime() - t0;
+    {   /* the reference fills its private taxon order from the same generator: check that ours is the one it used */
+        Node *r = t2->root;
+        if (r->id != order[0]) { fprintf(stderr, "taxon order mismatch: root %d vs order[0] %d\n", r->id, order[0]); return 5; }
+    }
+    dumpAdjacency(t2, "pars_stepwise_tree.txt");
+    int check = t2->computeParsimony();
+    {
+        std::ofstream f((g_out + "/metapars.json").c_str());
+        f << std::setprecision(17);
+        f << "{ \"ntaxa\": " << ntaxa << ", \"nsites_informative\": " << nsites << ", \"aln_nsite\": " << aln->getNSite()
+          << ", \"nstates\": " << aln->num_states << ", \"state_unknown\": " << (int)aln->STATE_UNKNOWN << ", \"seq_type\": " << (int)aln->seq_type
+          << ", \"min_branch_length\": " << params.min_branch_length
+          << ", \"score\": " << score << ", \"seed\": " << seed << ", \"stepwise_score\": " << best << ", \"stepwise_check\": " << check
+          << ", \"stepwise_seconds\": " << secs << ", \"threads\": " << omp_get_max_threads() << " }\n";
+    }
+    printf("dumppars score %d stepwise %d (check %d) %.3f s, %zu informative sites\n", score, best, check, secs, nsites);
+    return 0;
+}
+
 static int do_time(int argc, char **argv) {
     int lnl_reps = atoi(argv[2]), derv_reps = atoi(argv[3]), oab_reps = atoi(argv[4]);
     std::vector<char*> args; args.push_back(argv[0]);
@@ -514,6 +580,7 @@ int main(int argc, char **argv) {
     if (argc >= 6 && !strcmp(argv[1], "time")) return do_time(argc, argv);
     if (argc >= 5 && !strcmp(argv[1], "dumpx")) return do_dumpx(argc, argv);
     if (argc >= 5 && !strcmp(argv[1], "dumpnni")) return do_dumpnni(argc, argv);
+    if (argc >= 5 && !strcmp(argv[1], "dumppars")) return do_dumppars(argc, argv);
     fprintf(stderr, "usage: %s dump <outdir> <iqtree args>\n       %s time <lnl_reps> <derv_reps> <oab_reps> <iqtree args>\n", argv[0], argv[0]);
     return 2;
 }
