@@ -108,10 +108,27 @@ void PhyloTree::parsFlush() {
     const size_t n = pars_ops_.size();
     pars_counts_.assign(2 * n, 0);
     if (n == 0) return;
-    std::vector<int> order;
-    order.reserve(n);
-    for (size_t i = 0; i < n; i++) if (pars_ops_[i].kind == LKPARS_OP_PARTIAL || (pars_ops_[i].kind == LKPARS_OP_INSERT && pars_ops_[i].dst >= 0)) order.push_back((int)i);
-    for (size_t i = 0; i < n; i++) if (!(pars_ops_[i].kind == LKPARS_OP_PARTIAL || (pars_ops_[i].kind == LKPARS_OP_INSERT && pars_ops_[i].dst >= 0))) order.push_back((int)i);
+    /* level of a writing op = 1 + the highest level among the queued ops that produce its operands; ops of one level are
+       independent, so ordering the writers by level lets the engine overlap their memory round trips */
+    std::vector<int> level(n, 0), order;
+    {
+        std::vector<int> producer(pars_score_.size(), -1);
+        int maxlevel = 0;
+        for (size_t i = 0; i < n; i++) {
+            const lkpars_op &op = pars_ops_[i];
+            if (!(op.kind == LKPARS_OP_PARTIAL || (op.kind == LKPARS_OP_INSERT && op.dst >= 0))) continue;
+            int l = 0;
+            if (producer[op.a] >= 0) l = std::max(l, level[producer[op.a]]);
+            if (producer[op.b] >= 0) l = std::max(l, level[producer[op.b]]);
+            if (op.kind == LKPARS_OP_INSERT && producer[op.c] >= 0) l = std::max(l, level[producer[op.c]]);
+            level[i] = l + 1;
+            producer[op.dst] = (int)i;
+            maxlevel = std::max(maxlevel, l + 1);
+        }
+        order.reserve(n);
+        for (int l = 1; l <= maxlevel; l++) for (size_t i = 0; i < n; i++) if (level[i] == l) order.push_back((int)i);
+        for (size_t i = 0; i < n; i++) if (level[i] == 0) order.push_back((int)i);
+    }
     std::vector<lkpars_op> sorted(n);
     for (size_t i = 0; i < n; i++) sorted[i] = pars_ops_[order[i]];
     std::vector<uint32_t> counts(2 * n);

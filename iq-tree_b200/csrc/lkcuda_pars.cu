@@ -16,6 +16,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <algorithm>
 #include <string>
 #include <vector>
 #include "../../include/lkcuda.h"
@@ -121,27 +122,69 @@ __device__ __forceinline__ void pars_column(uint32_t *bits, long long vstride, l
     }
 }
 
-/* the dependent part of an op list: a thread owns word columns and walks all ops */
+/* the dependent part of an op list: a thread owns word columns and walks all ops.  A warp has only 2 * S loads of one op in flight
+   and 1M sites are just 977 warps, so a naive walk is bound by the memory round trip per op (about 1 us).  Consecutive PARTIAL ops
+   that do not read each other's results (the host orders a queue by tree level, so most do not) are therefore taken up to 8 at a
+   time: all their operands are loaded before the first result is stored (which also makes write-after-read inside a group safe). */
+#define PARS_GROUP_MAX 8
+
+__device__ __forceinline__ void pars_count(unsigned int *sh, int o, unsigned int c0, unsigned int c1, bool two) {
+    c0 = __reduce_add_sync(0xffffffffu, c0);
+    if (two) c1 = __reduce_add_sync(0xffffffffu, c1);
+    if ((threadIdx.x & 31) == 0) {
+        if (c0) atomicAdd(&sh[2 * o], c0);
+        if (two && c1) atomicAdd(&sh[2 * o + 1], c1);
+    }
+}
+
 template <int S>
 __global__ void __launch_bounds__(PARS_THREADS) pars_chain_kernel(uint32_t *bits, long long vstride, long long nw, int ns,
                                                                    const lkpars_op *ops, int nops, unsigned int *counts) {
     extern __shared__ unsigned int sh[];                /* [nops][2] */
     for (int i = threadIdx.x; i < 2 * nops; i += blockDim.x) sh[i] = 0;
     __syncthreads();
+    constexpr int G = S == 4 ? 8 : (S > 0 ? 4 : 1);     /* 2 * S * G registers of operands */
     const long long nthreads = (long long)gridDim.x * blockDim.x;
     const long long nw_round = (nw + 31) / 32 * 32;
     for (long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x; w < nw_round; w += nthreads) {
         const bool live = w < nw;
-        for (int o = 0; o < nops; o++) {
+        int o = 0;
+        while (o < nops) {
             const lkpars_op op = ops[o];
-            unsigned int c0 = 0, c1 = 0;
-            if (live) pars_column<S>(bits, vstride, nw, w, ns, op, c0, c1);
-            c0 = __reduce_add_sync(0xffffffffu, c0);
-            if (op.kind == LKPARS_OP_INSERT) c1 = __reduce_add_sync(0xffffffffu, c1);
-            if ((threadIdx.x & 31) == 0) {
-                if (c0) atomicAdd(&sh[2 * o], c0);
-                if (c1) atomicAdd(&sh[2 * o + 1], c1);
+            /* lkpars_run stored, in the unused third operand of a PARTIAL op, how many of the following ops form a hazard-free group */
+            const int g = (S > 0 && op.kind == LKPARS_OP_PARTIAL && op.c > 1) ? (op.c < G ? op.c : G) : 1;
+            if (S > 0 && g > 1) {
+                uint32_t xv[G][S > 0 ? S : 1], yv[G][S > 0 ? S : 1];
+                if (live) {
+#pragma unroll
+                    for (int j = 0; j < G; j++) if (j < g) {
+                        const lkpars_op n = ops[o + j];
+                        const uint32_t *x = bits + n.a * vstride + w, *y = bits + n.b * vstride + w;
+#pragma unroll
+                        for (int i = 0; i < S; i++) { xv[j][i] = x[i * nw]; yv[j][i] = y[i * nw]; }
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < G; j++) if (j < g) {
+                    unsigned int c0 = 0;
+                    if (live) {
+                        uint32_t any = 0;
+#pragma unroll
+                        for (int i = 0; i < S; i++) any |= xv[j][i] & yv[j][i];
+                        const uint32_t u = ~any;
+                        c0 = __popc(u);
+                        uint32_t *z = bits + ops[o + j].dst * vstride + w;
+#pragma unroll
+                        for (int i = 0; i < S; i++) z[i * nw] = (xv[j][i] & yv[j][i]) | (u & (xv[j][i] | yv[j][i]));
+                    }
+                    pars_count(sh, o + j, c0, 0, false);
+                }
+            } else {
+                unsigned int c0 = 0, c1 = 0;
+                if (live) pars_column<S>(bits, vstride, nw, w, ns, op, c0, c1);
+                pars_count(sh, o, c0, c1, op.kind == LKPARS_OP_INSERT);
             }
+            o += g;
         }
     }
     __syncthreads();
@@ -287,8 +330,25 @@ extern "C" int lkpars_run(lkpars_engine *e, const lkpars_op *ops, int32_t nops, 
     int nchain = nops;
     while (nchain > 0 && (ops[nchain - 1].kind == LKPARS_OP_BRANCH || (ops[nchain - 1].kind == LKPARS_OP_INSERT && ops[nchain - 1].dst < 0))) nchain--;
     const int nwide = nops - nchain;
-    /* shared memory of the chain kernel: 8 bytes per op; split very long chains */
-    const int CHAIN_MAX = 4096;
+    /* hazard-free groups of consecutive PARTIAL ops (no op reads or rewrites what an earlier op of the group writes): the size goes
+       into the unused third operand of the group's first op in the device copy */
+    const int CHAIN_MAX = 4096;      /* ops per chain launch: 8 bytes of shared memory each */
+    const int gmax = e->S == 4 ? 8 : (e->S == 20 ? 4 : 1);     /* = G of the kernel instantiation */
+    for (int o = 0; o < nchain;) {
+        int g = 1;
+        if (ops[o].kind == LKPARS_OP_PARTIAL) {
+            const int end = std::min(nchain, (o / CHAIN_MAX + 1) * CHAIN_MAX);
+            while (g < gmax && o + g < end && ops[o + g].kind == LKPARS_OP_PARTIAL) {
+                const lkpars_op &n = ops[o + g];
+                bool hazard = false;
+                for (int j = 0; j < g; j++) { const int d = ops[o + j].dst; hazard |= n.a == d || n.b == d || n.dst == d; }
+                if (hazard) break;
+                g++;
+            }
+            e->h_ops[o].c = g;
+        }
+        o += g;
+    }
     PARS_CUDA(e, cudaMemcpyAsync(e->d_ops, e->h_ops, sizeof(lkpars_op) * nops, cudaMemcpyHostToDevice, e->stream));
     PARS_CUDA(e, cudaMemsetAsync(e->d_counts, 0, sizeof(unsigned int) * 2 * nops, e->stream));
     if (e->profiling) PARS_CUDA(e, cudaEventRecord(e->ev0, e->stream));

@@ -166,6 +166,27 @@ def test_cuda_engine_matches_oracle_engine(S, nsites, cuda_lib, oracle_lib):
     assert np.array_equal(res[0][1], res[1][1])
 
 
+@pytest.mark.gpu
+def test_cuda_engine_long_chain(cuda_lib, oracle_lib):
+    """more dependent ops than one chain launch holds (4096): split launches, groups never straddle the split"""
+    rng = np.random.default_rng(11)
+    ntaxa, nvec = 6, 4500
+    ops, avail = [], list(range(ntaxa))
+    for d in range(ntaxa, ntaxa + nvec):
+        a, b = rng.choice(avail[-40:], 2, replace=False)
+        ops.append((0, d, int(a), int(b), -1))
+        avail.append(d)
+    ops += [(1, -1, ntaxa + nvec - 1, 0, -1), (2, -1, ntaxa + nvec - 2, 1, 2)]
+    res = []
+    for lib in (cuda_lib, oracle_lib):
+        e, _, _ = _random_engine(lib, np.random.default_rng(3), 4, ntaxa, 777, nvec)
+        rc, counts = _run_ops(lib, e, ops)
+        assert rc == 0, lib.lkpars_last_error(e)
+        res.append(counts)
+        lib.lkpars_destroy(e)
+    assert np.array_equal(res[0], res[1])
+
+
 def test_engine_argument_checks(oracle_lib):
     lib = oracle_lib
     e = C.c_void_p()
