@@ -42,9 +42,13 @@ for r in rows[hi + 1:]:
     s_ = r[ix["Source"]]
     m = re.match(r"\s*(@!?U?P\d+\s+)?([A-Z0-9_.]+)", s_)
     op = m.group(2).split(".")[0] if m else "?"
-    n = int(r[ix["Instructions Executed"]] or 0)
-    sm = int(r[ix["# Samples"]] or 0)
-    ops[op] += n; samp[op] += sm; tot += n; wf += int(r[ix["L1 Wavefronts Shared"]] or 0)
+    try:            # a report with several kernels repeats the header row; some columns are empty on non-executed lines
+        n = int(float(r[ix["Instructions Executed"]] or 0))
+        sm = int(float(r[ix["# Samples"]] or 0))
+        wf += int(float(r[ix["L1 Wavefronts Shared"]] or 0)) if "L1 Wavefronts Shared" in ix else 0
+    except ValueError:
+        continue
+    ops[op] += n; samp[op] += sm; tot += n
     data.append((sm, n, s_.strip()))
 print("total warp instructions %d, shared-memory wavefronts %d" % (tot, wf))
 for op, n in ops.most_common(ntop):
