@@ -98,6 +98,10 @@ lkcuda_engine *lktree_engine(lktree *h, int32_t i);
 int lktree_local_patterns(lktree *h, int64_t *begin, int64_t *end);
 /* global pattern range of in-process shard i (engine i) */
 int lktree_shard_patterns(lktree *h, int32_t i, int64_t *begin, int64_t *end);
+/* RateFree::optimizeWithEM (model/ratefree.cpp:450-578): EM on the +R proportions and rates; rates / props [ncat] out; copy_precision =
+   the reference's MTree::num_precision (6 unless min_branch_length was set before the tree was constructed, mtree.cpp:36-39) */
+int lktree_optimize_rate_free_em(lktree *h, int32_t copy_precision, double *lnl, double *rates, double *props);
+
 /* Fitch parsimony on the device (include/lkpars.h).  site_states[ntaxa][nsites] = the informative sites in
    Alignment::ordered_pattern order with every pattern repeated `frequency` times (alignment.cpp:731-775); aln_nsite = getNSite().
    lktree_compute_parsimony        PhyloTree::computeParsimony         phylotree.cpp:658-660

@@ -23,8 +23,8 @@ ORACLE_LIB = os.path.join(ORACLE_DIR, "_build", "liblktree_oracle.so")
 REF_HARNESS = os.path.join(ORACLE_DIR, "_ref", "ref_harness")
 REFERENCE = "/root/reference"
 
-CUDA_SOURCES = ["lkcuda_engine.cu", "lkcuda_partial.cu", "lkcuda_partial_mma.cu", "lkcuda_partial_mmak.cu", "lkcuda_reduce.cu", "lkcuda_aux.cu", "lkcuda_sitemodel.cu", "lkcuda_pars.cu", "lk_phylotree.cpp", "lk_parsimony.cpp", "lk_capi.cpp"]
-HOST_SOURCES = ["lk_phylotree.cpp", "lk_parsimony.cpp", "lk_capi.cpp"]
+CUDA_SOURCES = ["lkcuda_engine.cu", "lkcuda_partial.cu", "lkcuda_partial_mma.cu", "lkcuda_partial_mmak.cu", "lkcuda_reduce.cu", "lkcuda_aux.cu", "lkcuda_sitemodel.cu", "lkcuda_pars.cu", "lk_phylotree.cpp", "lk_parsimony.cpp", "lk_rate_em.cpp", "lk_capi.cpp"]
+HOST_SOURCES = ["lk_phylotree.cpp", "lk_parsimony.cpp", "lk_rate_em.cpp", "lk_capi.cpp"]
 ORACLE_SOURCES = ["lk_oracle.c", "lkpars_oracle.c"]
 HEADERS = [os.path.join(CSRC, "lkcuda_common.cuh"), os.path.join(CSRC, "lkcuda_traverse.cuh"), os.path.join(CSRC, "lk_phylotree.h"),
            os.path.join(ROOT, "include", "lkcuda.h"), os.path.join(ROOT, "include", "lktree.h"), os.path.join(ROOT, "include", "lkpars.h")]

@@ -229,6 +229,13 @@ int lktree_shard_patterns(lktree *h, int32_t i, int64_t *begin, int64_t *end) {
     LK_CATCH(h)
 }
 
+int lktree_optimize_rate_free_em(lktree *h, int32_t copy_precision, double *lnl, double *rates, double *props) {
+    LK_TRY(h)
+    *lnl = h->tree.optimizeRateFreeEM(copy_precision);
+    for (int c = 0; c < h->tree.ncat; c++) { if (rates) rates[c] = h->tree.categoryRates()[c]; if (props) props[c] = h->tree.categoryProps()[c]; }
+    LK_CATCH(h)
+}
+
 /* ---- Fitch parsimony ---- */
 int lktree_set_parsimony_sites(lktree *h, int64_t nsites, const uint8_t *site_states, int64_t aln_nsite, int32_t device) {
     LK_TRY(h) h->tree.setParsimonySites(nsites, site_states, aln_nsite); h->tree.pars_device = device; LK_CATCH(h)

@@ -33,7 +33,7 @@ PhyloTree::PhyloTree()
       proc_rank_(0), proc_world_(1), allreduce_(NULL), allreduce_user_(NULL), stream_(NULL), peers_attached_(false), boot_nsamples_(0),
       ptn_begin_(0), ptn_end_(0), tip_partial_lh_computed_(false), weights_uploaded_(false), model_uploaded_(false),
       freq_dirty_(true), invar_dirty_(true), model_dirty_(true), nvec_(0),
-      pars_device(-1), pars_(NULL), pars_nsites_(0), pars_aln_nsite_(0), pars_nvec_(0) {}
+      pars_device(-1), current_scaling_(1.0), keep_engines_(false), pars_(NULL), pars_nsites_(0), pars_aln_nsite_(0), pars_nvec_(0) {}
 
 PhyloTree::~PhyloTree() {
     deleteAllPartialLh();
@@ -128,7 +128,7 @@ void PhyloTree::initializeTreeIds(Node *node, Node *dad) {   // mtree.cpp:561-58
 }
 
 void PhyloTree::readTreeString(const std::string &newick) {
-    deleteAllPartialLh();
+    if (!keep_engines_) deleteAllPartialLh();
     for (size_t i = 0; i < allNodes.size(); i++) {
         for (size_t k = 0; k < allNodes[i]->neighbors.size(); k++) delete allNodes[i]->neighbors[k];
         delete allNodes[i];
@@ -160,6 +160,12 @@ void PhyloTree::readTreeString(const std::string &newick) {
         setRootNode(seq_names[0]);
     }
     current_it = current_it_back = NULL;
+    if (keep_engines_ && !engines_.empty()) {       // same taxa: the new nodes take over the arena vectors, nothing is computed yet
+        if (assignVectors(root, NULL, 0) != nvec_) throw std::runtime_error("readTreeString: the tree no longer fits the engines");
+        pending_ops_.clear(); pending_level_.clear();
+        std::fill(vec_level_.begin(), vec_level_.end(), 0);
+        theta_computed = false;
+    }
 }
 
 void PhyloTree::readAdjacency(const std::string &text) {

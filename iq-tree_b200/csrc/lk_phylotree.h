@@ -155,6 +155,17 @@ public:
     void restoreBranchLengths(const std::vector<double> &lenvec, int startid = 0, Node *node = NULL, Node *dad = NULL);
     void clearReversePartialLh(Node *node, Node *dad);
 
+    /* ---- RateFree::optimizeWithEM (model/ratefree.cpp:450-578; lk_rate_em.cpp) ---- */
+    // EM over the +R proportions and rates; copy_precision = MTree::num_precision of the reference's tree copy (mtree.cpp:36-39:
+    // 6, or ceil(-log10(min_branch_length)) + 1 if that is larger and min_branch_length was set before the tree was made)
+    double optimizeRateFreeEM(int copy_precision = 6);
+    const std::vector<double> &categoryRates() const { return rates_; }
+    const std::vector<double> &categoryProps() const { return props_; }
+    std::string printTreeFixed(int precision) const;                 // MTree::printTree(out, WT_BR_LEN), mtree.cpp:245-379
+    void scaleLength(double norm);                                   // mtree.cpp:1175-1186
+    double optimizeTreeLengthScaling(double min_scaling, double &scaling, double max_scaling, double gradient_epsilon);   // phylotree.cpp:2106-2118
+    double minimizeOneDimen(double xmin, double xguess, double xmax, double tolerance, double *fx, double *f2x);            // optimization.cpp:288-339
+
     /* ---- Fitch parsimony on the device (include/lkpars.h) ---- */
     // the informative sites in Alignment::ordered_pattern order, pattern p repeated frequency[p] times (alignment.cpp:731-775):
     // site_states[ntaxa][nsites]; aln_nsite = Alignment::getNSite() (all sites, for fixNegativeBranch)
@@ -188,6 +199,11 @@ public:
     std::vector<std::string> seq_names;
 
 private:
+    double computeFunctionScaling(double value);                     // PhyloTree::computeFunction with is_opt_scaling, phylotree.cpp:2125-2132
+    double brentOpt(double ax, double bx, double cx, double tol, double *foptx, double *f2optx, double fax, double fbx, double fcx);
+    double current_scaling_;
+    bool keep_engines_;                                              // readTreeString keeps the engines (same taxa, same model shape)
+
     /* parsimony bookkeeping (lk_parsimony.cpp) */
     int parsVec(const Neighbor *nei) const;                          // the engine vector a neighbour's partial_pars lives in
     int parsQueue(int kind, int dst, int a, int b, int c);

@@ -422,6 +422,41 @@ int lkcuda_lh_cat_collapse(lkcuda_engine *e, int32_t mode, int32_t ncat, int32_t
     return launch_end(e, KIND_MISC, (uint64_t)v.P * (v.K + a->ncol) * 8, "lhcat_collapse_kernel");
 }
 
+/* E-step posteriors of one class as the pattern weights of ANOTHER engine (ratefree.cpp:487-503, 547-549; modelmixture.cpp:1453-1511):
+   dst_freq[p] = w[p][col] * (ptn_freq[p] / sum_c w[p][c]) - the reference's own order of operations, no ptn_invar in the sum */
+__global__ void __launch_bounds__(AUX_THREADS) lhcat_posterior_kernel(DevView v, int ncol, const double *__restrict__ w, int col, double *dst_freq) {
+    for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < v.P; p += (long long)gridDim.x * blockDim.x) {
+        const double *row = w + p * ncol;
+        double lk = 0.0;
+        for (int c = 0; c < ncol; c++) lk += row[c];
+        lk = v.freq[p] / lk;
+        dst_freq[p] = row[col] * lk;
+    }
+}
+
+int lkcuda_lh_cat_posterior_weights(lkcuda_engine *e, int32_t col, lkcuda_engine *dst) {
+    LK_ENTER(e);
+    lkcuda_aux *a = e->aux;
+    if (!a || !a->d_w || a->ncol < 1) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lh_cat_posterior_weights: call lkcuda_lh_cat_collapse first");
+    if (!dst || dst == e) return fail(e, LKCUDA_ERR_ARG, "lkcuda_lh_cat_posterior_weights: destination engine");
+    if (col < 0 || col >= a->ncol) return fail(e, LKCUDA_ERR_ARG, "lkcuda_lh_cat_posterior_weights: column %d of %d", col, a->ncol);
+    if (dst->device != e->device || dst->v.P != e->v.P) return fail(e, LKCUDA_ERR_ARG, "lkcuda_lh_cat_posterior_weights: the engines must hold the same patterns on the same device");
+    if (!e->weights_set || !dst->weights_set) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lh_cat_posterior_weights: pattern weights not set (the destination keeps its ptn_invar)");
+    const DevView &v = e->v;
+    if (v.P == 0) return LKCUDA_OK;
+    /* whatever the destination still runs with its old weights finishes first; its later work waits for the new ones */
+    LK_CUDA(e, cudaStreamSynchronize(dst->stream));
+    long long grid = (v.P + AUX_THREADS - 1) / AUX_THREADS;
+    if (grid > (long long)e->num_sms * 8) grid = (long long)e->num_sms * 8;
+    launch_begin(e, KIND_EM);
+    lhcat_posterior_kernel<<<(int)grid, AUX_THREADS, 0, e->stream>>>(e->v, a->ncol, a->d_w, col, dst->d_freq);
+    int rc = launch_end(e, KIND_EM, (uint64_t)v.P * ((uint64_t)a->ncol * 8 + 16), "lhcat_posterior_kernel");
+    if (rc) return rc;
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    dst->theta_ready = false;
+    return LKCUDA_OK;
+}
+
 int lkcuda_lh_cat_em(lkcuda_engine *e, const double *ratio, double *sums) {
     LK_ENTER(e);
     lkcuda_aux *a = e->aux;

@@ -70,6 +70,7 @@ LKCUDA_SYMBOLS = {
     "lkcuda_rell_fetch": (C.c_int, [C.c_void_p, c_double_p]),
     "lkcuda_rell_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "lkcuda_lh_cat_collapse": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_int32_p]),
+    "lkcuda_lh_cat_posterior_weights": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p]),
     "lkcuda_lh_cat_em": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
     "lkcuda_lh_cat_pattern_rates": (C.c_int, [C.c_void_p, c_double_p, C.c_int32, c_double_p, c_int32_p]),
     "lkcuda_fetch_lh_cat_collapsed": (C.c_int, [C.c_void_p, c_double_p]),
@@ -136,6 +137,7 @@ LKTREE_SYMBOLS = {
     "lktree_local_patterns": (C.c_int, [C.c_void_p, c_int64_p, c_int64_p]),
     "lktree_shard_patterns": (C.c_int, [C.c_void_p, C.c_int32, c_int64_p, c_int64_p]),
     "lktree_num_partial_lh_computations": (C.c_uint64, [C.c_void_p]),
+    "lktree_optimize_rate_free_em": (C.c_int, [C.c_void_p, C.c_int32, c_double_p, c_double_p, c_double_p]),
     "lktree_set_parsimony_sites": (C.c_int, [C.c_void_p, C.c_int64, c_uint8_p, C.c_int64, C.c_int32]),
     "lktree_compute_parsimony": (C.c_int, [C.c_void_p, c_int32_p]),
     "lktree_compute_parsimony_branch": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_int32_p, c_int32_p]),
@@ -429,6 +431,13 @@ class PhyloTree:
         cnt = C.c_int32()
         self._ck(self.lib.lktree_get_traversal(self.h, pairs.ctypes.data_as(c_int32_p), cap, C.byref(cnt)))
         return pairs[: 2 * cnt.value].reshape(-1, 2).copy()
+
+    def optimizeRateFreeEM(self, ncat, copy_precision=6):
+        """RateFree::optimizeWithEM: (lnL, rates[ncat], props[ncat])"""
+        lnl = C.c_double()
+        r, p = np.zeros(ncat), np.zeros(ncat)
+        self._ck(self.lib.lktree_optimize_rate_free_em(self.h, copy_precision, C.byref(lnl), r.ctypes.data_as(c_double_p), p.ctypes.data_as(c_double_p)))
+        return lnl.value, r, p
 
     # ---- Fitch parsimony (SURVEY 8(f).4) ----
     def setParsimonySites(self, site_states, aln_nsite, device=-1):

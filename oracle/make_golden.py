@@ -10,6 +10,7 @@ runs only in the build container; the resulting fixtures are committed and trave
     python oracle/make_golden.py dna_example_gtr_g4 ...
     python oracle/make_golden.py --nni      # tests/golden/nni/*.npz: PhyloTree::getBestNNIForBran on every internal branch (NNI_CASES)
     python oracle/make_golden.py --aux      # tests/golden/aux/*.npz: RELL, pattern rates, mixture-weight EM of AUX_CASES
+    python oracle/make_golden.py --em       # tests/golden/em/*.npz: RateFree::optimizeWithEM (EM_CASES; the inputs are the main fixtures)
     python oracle/make_golden.py --pars     # tests/golden/pars/*.npz: Fitch parsimony scores per branch + stepwise-addition trees (PARS_CASES)
 
 Synthetic alignments (codon, deep DNA tree, morphological, multifurcating) are generated here with fixed seeds.
@@ -240,6 +241,19 @@ def pack_nni(case, nni5, d):
         case, nni5, m["nbranch"], m["lnl"], m["lnl_after"], z["vals"][:, :, 0].max() - m["lnl"], os.path.getsize(path) / 1024))
 
 
+EM_CASES = ["dna_example_hky_r3", "aa_lg_r4", "dna_deep_gtr_r4"]
+
+
+def pack_em(case, d):
+    m = json.load(open(os.path.join(d, "metaem.json")))
+    v = rd(d, "em_rates_props.f64", np.float64).reshape(4, m["ncat"])
+    z = {"meta": json.dumps(m), "rates_before": v[0], "props_before": v[1], "rates": v[2], "props": v[3]}
+    os.makedirs(os.path.join(OUT, "em"), exist_ok=True)
+    path = os.path.join(OUT, "em", case + ".npz")
+    np.savez_compressed(path, **z)
+    print("%-28s em: lnl %.6f -> %.6f rates %s props %s" % (case, m["lnl_before"], m["lnl_after"], np.round(v[2], 5), np.round(v[3], 5)))
+
+
 PARS_CASES = [("dna_example_gtr_g4", 1), ("dna_example_gtr_g4", 7), ("dna_deep_scaling", 1), ("aa_lg_g4", 1), ("aa_lg_g4", 5), ("codon_gy", 1),
               ("morph_mk_g4", 1), ("bin_jc2_g4", 3)]
 
@@ -309,6 +323,8 @@ def main():
         "dna_example_gtr_i_g4": ["-s", ex, "-m", "GTR+I+G4", "-te", ex_tree],
         "dna_example_hky_r3": ["-s", ex, "-m", "HKY+R3", "-te", ex_tree],
         "dna_example_jc": ["-s", ex, "-m", "JC", "-te", ex_tree],
+        "aa_lg_r4": ["-s", prot, "-m", "LG+R4", "-te", prot_tree],
+        "dna_deep_gtr_r4": ["-s", deep_aln, "-m", "GTR+R4", "-te", deep_tree],
         "dna_example_generic": ["-s", ex, "-m", "GTR+G4", "-te", ex_tree, "-fastlk"],
         "dna_example_multifurc": ["-s", ex, "-m", "GTR+G4", "-te", mf_tree],
         "dna_deep_scaling": ["-s", deep_aln, "-m", "GTR+G4", "-te", deep_tree],
@@ -331,6 +347,17 @@ def main():
                 print("%-28s nni FAILED:\n%s" % (case, r.stdout[-1500:]))
                 continue
             pack_nni(case, nni5, d)
+        shutil.rmtree(tmp, ignore_errors=True)
+        return
+    if sys.argv[1:2] == ["--em"]:
+        for case in EM_CASES:
+            d = os.path.join(tmp, "oute_" + case)
+            cmd = [HARNESS, "dumpem", d] + cases[case] + ["-nt", "1", "-seed", "1", "-pre", os.path.join(tmp, "rune_" + case)]
+            r = subprocess.run(cmd, cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            if r.returncode != 0:
+                print("%-28s em FAILED:\n%s" % (case, r.stdout[-1500:]))
+                continue
+            pack_em(case, d)
         shutil.rmtree(tmp, ignore_errors=True)
         return
     if sys.argv[1:2] == ["--pars"]:

@@ -18,6 +18,7 @@
  *        ref_harness dumpx <outdir> <nsamples> <iqtree args ...>
  *        ref_harness dumpnni <outdir> <nni5: 0|1> <iqtree args ...>     PhyloTree::getBestNNIForBran on every internal branch
  *        ref_harness dumppars <outdir> <seed> <iqtree args ...>         Fitch parsimony: scores per branch, stepwise-addition tree
+ *        ref_harness dumpem <outdir> <iqtree args ...>                  RateFree::optimizeWithEM: rates, proportions, lnL before / after
  *        ref_harness time <lnl_reps> <derv_reps> <oab_reps> <iqtree args ...>
  */
 #include <cstdio>
@@ -51,6 +52,7 @@
 #include "model/modelmixture.h"
 #include "model/modelset.h"
 #include "model/rateheterogeneity.h"
+#include "model/ratefree.h"
 #include "vectorclass/instrset.h"
 #undef private
 #undef protected
@@ -496,6 +498,35 @@ static int do_dumppars(int argc, char **argv) {
     return 0;
 }
 
+/* RateFree::optimizeWithEM: rates / proportions / lnL before and after the reference's own EM */
+static int do_dumpem(int argc, char **argv) {
+    g_out = argv[2];
+    mkdir(g_out.c_str(), 0755);
+    std::vector<char*> args; args.push_back(argv[0]);
+    for (int i = 3; i < argc; i++) args.push_back(argv[i]);
+    Params &params = Params::getInstance();
+    IQTree *tree = setup((int)args.size(), &args[0], params);
+    RateFree *rf = dynamic_cast<RateFree*>(tree->getRate());
+    if (!rf) { fprintf(stderr, "dumpem: not a +R model\n"); return 4; }
+    tree->clearAllPartialLH();
+    double lnl0 = tree->computeLikelihood();
+    int nc = rf->getNRate();
+    std::vector<double> v;
+    for (int c = 0; c < nc; c++) v.push_back(rf->getRate(c));
+    for (int c = 0; c < nc; c++) v.push_back(rf->getProp(c));
+    double lnl1 = rf->optimizeWithEM();
+    for (int c = 0; c < nc; c++) v.push_back(rf->getRate(c));
+    for (int c = 0; c < nc; c++) v.push_back(rf->getProp(c));
+    wbin("em_rates_props.f64", &v[0], v.size() * 8);
+    {
+        std::ofstream f((g_out + "/metaem.json").c_str());
+        f << std::setprecision(17);
+        f << "{ \"ncat\": " << nc << ", \"lnl_before\": " << lnl0 << ", \"lnl_after\": " << lnl1 << ", \"num_precision\": " << tree->num_precision << " }\n";
+    }
+    printf("dumpem ncat %d lnl %.10f -> %.10f\n", nc, lnl0, lnl1);
+    return 0;
+}
+
 static int do_time(int argc, char **argv) {
     int lnl_reps = atoi(argv[2]), derv_reps = atoi(argv[3]), oab_reps = atoi(argv[4]);
     std::vector<char*> args; args.push_back(argv[0]);
@@ -581,6 +612,7 @@ int main(int argc, char **argv) {
     if (argc >= 5 && !strcmp(argv[1], "dumpx")) return do_dumpx(argc, argv);
     if (argc >= 5 && !strcmp(argv[1], "dumpnni")) return do_dumpnni(argc, argv);
     if (argc >= 5 && !strcmp(argv[1], "dumppars")) return do_dumppars(argc, argv);
+    if (argc >= 4 && !strcmp(argv[1], "dumpem")) return do_dumpem(argc, argv);
     fprintf(stderr, "usage: %s dump <outdir> <iqtree args>\n       %s time <lnl_reps> <derv_reps> <oab_reps> <iqtree args>\n", argv[0], argv[0]);
     return 2;
 }

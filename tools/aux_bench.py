@@ -3,7 +3,9 @@
    rell : UFBoot RELL - NSAMPLES bootstrap replicates x NPTN patterns (DNA 100 taxa GTR+G4): ms per candidate tree, GB/s of the matrix
           actually streamed (uint8 counts) and of the reference's float matrix (algorithmic), vs a numpy fp32 GEMV on the host cores
    em   : ModelMixture::optimizeWeights on LG+C20+G4-like mixtures: ms per EM step vs the host pass it replaces
+   rem  : RateFree::optimizeWithEM (+R4 on DNA 100 taxa): wall time of the whole EM, likelihood evaluations, device share
 usage: python tools/aux_bench.py rell [NPTN=1000000] [NSAMPLES=1000] [reps=10]
+       python tools/aux_bench.py rem [NPTN=1000000]
        python tools/aux_bench.py em [NTAXA=100] [NPTN=10000] [reps=5]"""
 import json
 import os
@@ -110,9 +112,38 @@ def em(ntaxa, nptn, reps):
     t.close()
 
 
+def rem(nptn):
+    ntaxa = 100
+    names = ["t%d" % i for i in range(ntaxa)]
+    nwk = mi.random_tree_newick(ntaxa, 1, names)
+    st = mi.simulate_patterns(nwk, names, nptn, 4, 1)
+    mdl = mi.gtr_g4_inputs(1, ncat=4)
+    lib = iqtree_b200.load_library()
+    t = iqtree_b200.PhyloTree(lib=lib)
+    t.setAlignment(st, np.ones(nptn), names=names, seq_type=0, nstates=4, state_unknown=18)
+    t.readTreeString(nwk)
+    t.setModel(0, 4, 1, mdl["eval"], mdl["evec"], mdl["inv_evec"], mdl["rates"], mdl["props"], None, mdl["state_freq"], 0.0)
+    t.setParams(0.1 / nptn if nptn >= 100000 else 1e-6, 100.0)
+    t.initializeAllPartialLh()
+    lnl0 = t.computeLikelihood()
+    n0 = t.numPartialLhComputations()
+    t0 = time.time()
+    lnl1, rates, props = t.optimizeRateFreeEM(4)
+    wall = time.time() - t0
+    out = {"what": "ratefree_em", "ntaxa": ntaxa, "nptn": nptn, "ncat": 4, "lnl_before": lnl0, "lnl_after": lnl1,
+           "rates": [float(x) for x in rates], "props": [float(x) for x in props], "wall_s": wall,
+           "main_tree_partial_computations": t.numPartialLhComputations() - n0,
+           "note": "every EM step: 1 per-category likelihood pass (4 categories) + E-step on the device + 4 Brent searches of ~10-20 "
+                   "one-category full-tree likelihoods each; the P x 4 posterior matrix never leaves the device"}
+    print(json.dumps(out))
+    t.close()
+
+
 if __name__ == "__main__":
     a = sys.argv[1:]
-    if a and a[0] == "em":
+    if a and a[0] == "rem":
+        rem(int(a[1]) if len(a) > 1 else 1000000)
+    elif a and a[0] == "em":
         em(int(a[1]) if len(a) > 1 else 100, int(a[2]) if len(a) > 2 else 10000, int(a[3]) if len(a) > 3 else 5)
     else:
         rell(int(a[1]) if len(a) > 1 else 1000000, int(a[2]) if len(a) > 2 else 1000, int(a[3]) if len(a) > 3 else 10)
