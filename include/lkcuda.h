@@ -268,10 +268,11 @@ int lkcuda_rell_device_ptr(lkcuda_engine *e, void **dev_ptr);
      (model/rategammainvar.cpp:193-221) - ptn_invar joins the denominator and competes as category 0, the others become c + 1. */
 int lkcuda_lh_cat_collapse(lkcuda_engine *e, int32_t mode, int32_t ncat, int32_t nmix, int32_t *ncol);
 int lkcuda_lh_cat_em(lkcuda_engine *e, const double *ratio /*[ncol] or NULL*/, double *sums /*[ncol]*/);
-/* the E-step posterior of class `col` (w[p][col] * ptn_freq[p] / sum_c w[p][c], no ptn_invar: ratefree.cpp:487-503) becomes the
+/* the E-step posterior of class `col` (w[p][col] * ptn_freq[p] / ([ptn_invar[p] +] sum_c w[p][c]): ratefree.cpp:487-503 without,
+   modelmixture.cpp:1458-1471 with ptn_invar) becomes the
    ptn_freq of `dst`, an engine over the same patterns on the same device (the sub-tree of RateFree::optimizeWithEM, ratefree.cpp:533-549,
    and of ModelMixture::optimizeWithEM, modelmixture.cpp:1488-1511); nothing crosses PCIe */
-int lkcuda_lh_cat_posterior_weights(lkcuda_engine *e, int32_t col, lkcuda_engine *dst);
+int lkcuda_lh_cat_posterior_weights(lkcuda_engine *e, int32_t col, int32_t include_invar /* ModelMixture: 1, RateFree: 0 */, lkcuda_engine *dst);
 int lkcuda_lh_cat_pattern_rates(lkcuda_engine *e, const double *rates /*[ncol]*/, int32_t invar_class, double *ptn_rates /*[P]*/, int32_t *ptn_cat /*[P]*/);
 int lkcuda_fetch_lh_cat_collapsed(lkcuda_engine *e, double *w /*[P][ncol]*/);
 

@@ -236,7 +236,7 @@ double PhyloTree::optimizeRateFreeEM(int copy_precision) {
             tree->initializeAllPartialLh();
             tree->ensureInputs();                            // computePtnFreq + uploads; then the posteriors replace ptn_freq on the device
             for (size_t d = 0; d < engines_.size(); d++)
-                check(lkcuda_lh_cat_posterior_weights(engines_[d], c, tree->engines_[d]), engines_[d], "lkcuda_lh_cat_posterior_weights");
+                check(lkcuda_lh_cat_posterior_weights(engines_[d], c, 0, tree->engines_[d]), engines_[d], "lkcuda_lh_cat_posterior_weights");
             double scaling = rates[c];
             tree->scaleLength(scaling);
             tree->optimizeTreeLengthScaling(MIN_PROP, scaling, 1.0 / prop[c], 0.001);

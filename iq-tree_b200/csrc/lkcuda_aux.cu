@@ -423,18 +423,19 @@ int lkcuda_lh_cat_collapse(lkcuda_engine *e, int32_t mode, int32_t ncat, int32_t
 }
 
 /* E-step posteriors of one class as the pattern weights of ANOTHER engine (ratefree.cpp:487-503, 547-549; modelmixture.cpp:1453-1511):
-   dst_freq[p] = w[p][col] * (ptn_freq[p] / sum_c w[p][c]) - the reference's own order of operations, no ptn_invar in the sum */
-__global__ void __launch_bounds__(AUX_THREADS) lhcat_posterior_kernel(DevView v, int ncol, const double *__restrict__ w, int col, double *dst_freq) {
+   dst_freq[p] = w[p][col] * (ptn_freq[p] / ([ptn_invar[p] +] sum_c w[p][c])) - the reference's own order of operations; RateFree's
+   E-step leaves ptn_invar out, ModelMixture's starts the sum with it */
+__global__ void __launch_bounds__(AUX_THREADS) lhcat_posterior_kernel(DevView v, int ncol, const double *__restrict__ w, int col, int include_invar, double *dst_freq) {
     for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < v.P; p += (long long)gridDim.x * blockDim.x) {
         const double *row = w + p * ncol;
-        double lk = 0.0;
+        double lk = include_invar ? v.invar[p] : 0.0;
         for (int c = 0; c < ncol; c++) lk += row[c];
         lk = v.freq[p] / lk;
         dst_freq[p] = row[col] * lk;
     }
 }
 
-int lkcuda_lh_cat_posterior_weights(lkcuda_engine *e, int32_t col, lkcuda_engine *dst) {
+int lkcuda_lh_cat_posterior_weights(lkcuda_engine *e, int32_t col, int32_t include_invar, lkcuda_engine *dst) {
     LK_ENTER(e);
     lkcuda_aux *a = e->aux;
     if (!a || !a->d_w || a->ncol < 1) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lh_cat_posterior_weights: call lkcuda_lh_cat_collapse first");
@@ -449,7 +450,7 @@ int lkcuda_lh_cat_posterior_weights(lkcuda_engine *e, int32_t col, lkcuda_engine
     long long grid = (v.P + AUX_THREADS - 1) / AUX_THREADS;
     if (grid > (long long)e->num_sms * 8) grid = (long long)e->num_sms * 8;
     launch_begin(e, KIND_EM);
-    lhcat_posterior_kernel<<<(int)grid, AUX_THREADS, 0, e->stream>>>(e->v, a->ncol, a->d_w, col, dst->d_freq);
+    lhcat_posterior_kernel<<<(int)grid, AUX_THREADS, 0, e->stream>>>(e->v, a->ncol, a->d_w, col, include_invar ? 1 : 0, dst->d_freq);
     int rc = launch_end(e, KIND_EM, (uint64_t)v.P * ((uint64_t)a->ncol * 8 + 16), "lhcat_posterior_kernel");
     if (rc) return rc;
     LK_CUDA(e, cudaStreamSynchronize(e->stream));

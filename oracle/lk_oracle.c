@@ -771,14 +771,14 @@ int lkcuda_lh_cat_em(lkcuda_engine *e, const double *ratio, double *sums) {
     return LKCUDA_OK;
 }
 /* ratefree.cpp:487-503 (E-step) + :547-549 (the posterior of one category becomes the sub-tree's ptn_freq) */
-int lkcuda_lh_cat_posterior_weights(lkcuda_engine *e, int32_t col, lkcuda_engine *dst) {
+int lkcuda_lh_cat_posterior_weights(lkcuda_engine *e, int32_t col, int32_t include_invar, lkcuda_engine *dst) {
     if (!e || !dst || dst == e) return LKCUDA_ERR_ARG;
     if (!e->w || e->ncol < 1) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lh_cat_posterior_weights: call lkcuda_lh_cat_collapse first");
     if (col < 0 || col >= e->ncol || dst->cfg.nptn != e->cfg.nptn) return fail(e, LKCUDA_ERR_ARG, "lkcuda_lh_cat_posterior_weights: bad argument");
     size_t P = (size_t)e->cfg.nptn, n = (size_t)e->ncol;
     for (size_t ptn = 0; ptn < P; ptn++) {
         const double *this_lk_cat = e->w + ptn * n;
-        double lk_ptn = 0.0;
+        double lk_ptn = include_invar ? e->ptn_invar[ptn] : 0.0;       /* modelmixture.cpp:1460 starts with ptn_invar, ratefree.cpp:489 with 0 */
         for (size_t c = 0; c < n; c++) lk_ptn += this_lk_cat[c];
         lk_ptn = e->ptn_freq[ptn] / lk_ptn;
         dst->ptn_freq[ptn] = this_lk_cat[col] * lk_ptn;

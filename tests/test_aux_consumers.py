@@ -9,6 +9,7 @@ Tolerances:
   * pattern rates: 1e-10 relative (per-pattern likelihood tolerance), categories exact.
   * EM weights / lnL: 1e-9 relative.
 """
+import ctypes as C
 import glob
 import json
 import os
@@ -137,3 +138,31 @@ def test_cuda_em_matches_oracle_synthetic(shape, cuda_lib, oracle_lib):
     for k in range(2):
         assert abs(out[0][k][0] - out[1][k][0]) <= gu.LNL_RTOL * abs(out[1][k][0])
         gu.rel_close(out[0][k][1], out[1][k][1], 1e-9, "weights round %d" % k)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case,wsl,include_invar", [("dna_example_gtr_i_g4", 2, 1), ("dna_example_gtr_i_g4", 2, 0), ("aa_lg_c20_g4", 3, 1)])
+def test_cuda_posterior_weights_match_oracle(case, wsl, include_invar, cuda_lib, oracle_lib):
+    """lkcuda_lh_cat_posterior_weights (the sub-tree weights of RateFree / ModelMixture::optimizeWithEM): the posterior column of one class
+    becomes the ptn_freq of a second engine; its likelihood must agree between the CUDA engine and the CPU restatement"""
+    g = gu.Golden(case)
+    out = []
+    for lib in (cuda_lib, oracle_lib):
+        a, b = gu.build_tree(g, lib), gu.build_tree(g, lib)
+        for t in (a, b):
+            t.initializeAllPartialLh()
+            t.computeLikelihood()
+        a.computePatternLhCat(wsl)                  # fills _pattern_lh_cat on the device (the generic branch pass)
+        n = C.c_int32()
+        assert lib.lkcuda_lh_cat_collapse(a.engine(0), wsl, g.meta["ncat"], g.meta["nmix"], C.byref(n)) == 0, lib.lkcuda_last_error(a.engine(0))
+        vals = []
+        for col in (0, n.value - 1):
+            assert lib.lkcuda_lh_cat_posterior_weights(a.engine(0), col, include_invar, b.engine(0)) == 0, lib.lkcuda_last_error(a.engine(0))
+            b.clearAllPartialLH()
+            vals.append(b.computeLikelihood())
+        assert lib.lkcuda_lh_cat_posterior_weights(a.engine(0), n.value, include_invar, b.engine(0)) != 0      # column out of range
+        assert lib.lkcuda_lh_cat_posterior_weights(a.engine(0), 0, include_invar, a.engine(0)) != 0            # onto itself
+        out.append(vals)
+        a.close(); b.close()
+    gu.rel_close(np.array(out[0]), np.array(out[1]), 1e-9, "lnL under posterior weights")
+    assert out[0][0] != out[0][1]

@@ -13,21 +13,22 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def declared(header):
     text = open(os.path.join(ROOT, "include", header)).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(lk(?:cuda|tree)_[a-z0-9_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(lk(?:cuda|tree|pars)_[a-z0-9_]+)\s*\(", text)))
 
 
 def test_cuda_library_exports_every_declared_symbol():
     lib = ctypes.CDLL(_build.build_cuda())
-    names = declared("lkcuda.h") + declared("lktree.h")
-    assert len(names) > 60
+    names = declared("lkcuda.h") + declared("lktree.h") + declared("lkpars.h")
+    assert len(names) > 70
     missing = [n for n in names if not hasattr(lib, n)]
     assert not missing, missing
-    bound = set(iqtree_b200.LKCUDA_SYMBOLS) | set(iqtree_b200.LKTREE_SYMBOLS)
+    from iqtree_b200 import phylotree as pt
+    bound = set(iqtree_b200.LKCUDA_SYMBOLS) | set(iqtree_b200.LKTREE_SYMBOLS) | set(pt.LKPARS_SYMBOLS)
     assert set(names) - {"lktree_allreduce_fn"} <= bound, sorted(set(names) - bound)
 
 
 def test_oracle_library_exports_the_same_abi(oracle_lib):
-    for n in declared("lkcuda.h") + declared("lktree.h"):
+    for n in declared("lkcuda.h") + declared("lktree.h") + declared("lkpars.h"):
         assert hasattr(oracle_lib, n), n
 
 
@@ -39,6 +40,12 @@ def test_no_cpu_fallback_without_device():
         return      # running on a GPU box: nothing to check here
     import numpy as np
     from iqtree_b200 import modelinputs as mi
+    from iqtree_b200 import phylotree as pt
+    e = ctypes.c_void_p()
+    mask = np.array([1, 2, 4, 8, 15], dtype=np.uint64)
+    sites = np.zeros((3, 5), dtype=np.uint8)
+    assert lib.lkpars_create(0, 4, 3, 5, sites.ctypes.data_as(pt.c_uint8_p), mask.ctypes.data_as(pt.c_uint64_p), 5, 2, ctypes.byref(e)) != 0
+    assert b"no CUDA device" in lib.lkpars_last_error(None)
     t = iqtree_b200.PhyloTree(lib=lib)
     names = ["t%d" % i for i in range(4)]
     t.setAlignment(np.zeros((4, 8), dtype=np.uint8), np.ones(8), names=names)
