@@ -154,7 +154,9 @@ def test_cuda_posterior_weights_match_oracle(case, wsl, include_invar, cuda_lib,
             t.computeLikelihood()
         a.computePatternLhCat(wsl)                  # fills _pattern_lh_cat on the device (the generic branch pass)
         n = C.c_int32()
-        assert lib.lkcuda_lh_cat_collapse(a.engine(0), wsl, g.meta["ncat"], g.meta["nmix"], C.byref(n)) == 0, lib.lkcuda_last_error(a.engine(0))
+        mixture = g.meta["family"] == "mixture"          # the arguments lk::PhyloTree::collapsePatternLhCat passes
+        mode, outer = (1, g.meta["nmix"]) if mixture else (0, 1)
+        assert lib.lkcuda_lh_cat_collapse(a.engine(0), mode, g.meta["ncat"], outer, C.byref(n)) == 0, lib.lkcuda_last_error(a.engine(0))
         vals = []
         for col in (0, n.value - 1):
             assert lib.lkcuda_lh_cat_posterior_weights(a.engine(0), col, include_invar, b.engine(0)) == 0, lib.lkcuda_last_error(a.engine(0))
