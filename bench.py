@@ -377,6 +377,20 @@ def main():
     barrier()
     ms_e2e = ev2.elapsed_time(ev3)
     clocks = sampler.finish() if sampler else None
+    if os.environ.get("LK_BENCH_E2E_TRACE") and rank == 0:       # host-side wall time of the three calls of an e2e step (diagnostic)
+        acc = [0.0, 0.0, 0.0]
+        for _ in range(args.steps):
+            t0 = time.perf_counter()
+            lib.lkcuda_set_tip_states_async(eng, ctypes.cast(pinned_states.data_ptr(), c_u8p), nchunks)
+            t.clearAllPartialLH()
+            t1 = time.perf_counter()
+            lib.lktree_compute_likelihood(t.h, ctypes.byref(lnl_c), ctypes.cast(pinned_plh.data_ptr(), c_dp))
+            t2 = time.perf_counter()
+            t.computeLikelihoodDerv(root_leaf, root_nei, reset_theta=True)
+            t3 = time.perf_counter()
+            acc[0] += t1 - t0; acc[1] += t2 - t1; acc[2] += t3 - t2
+        sys.stderr.write("e2e trace (ms per step): upload call %.4f, computeLikelihood+fetch %.4f, computeLikelihoodDerv %.4f, chunks %d\n" % (
+            acc[0] / args.steps * 1e3, acc[1] / args.steps * 1e3, acc[2] / args.steps * 1e3, nchunks))
 
     tt = torch.tensor([ms, ms_e2e, ms_lnl], dtype=torch.float64, device=dev)
     if world > 1:
