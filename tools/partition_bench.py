@@ -3,6 +3,8 @@
 the partition trees' lnL, each partition an independent engine on its own stream (PhyloSuperTree::computeLikelihood,
 phylosupertree.cpp:955-980).  Times one full evaluation (clearAllPartialLH + computeLikelihood of every partition) driven
 sequentially and from a thread pool (the reference's `#pragma omp parallel for` over partitions).
+LK_PART_GPUS=n spreads WHOLE PARTITIONS over n GPUs of the box (the second sharding axis: independent PhyloTree handles, the
+host sums the partition likelihoods, phylosupertree.cpp:972-976) - DNA / protein pairs go to the same device so that the load is even.
 usage: python tools/partition_bench.py [NTAXA] [NPTN] [NPART] [reps]"""
 import json
 import os
@@ -18,7 +20,7 @@ import iqtree_b200
 from iqtree_b200 import modelinputs as mi
 
 
-def make_part(lib, ntaxa, nptn, S, seed):
+def make_part(lib, ntaxa, nptn, S, seed, device=0):
     names = ["t%d" % i for i in range(ntaxa)]
     nwk = mi.random_tree_newick(ntaxa, 1, names)        # edge-linked partitions share the topology
     st = mi.simulate_patterns(nwk, names, nptn, S, seed)
@@ -28,6 +30,7 @@ def make_part(lib, ntaxa, nptn, S, seed):
     t.readTreeString(nwk)
     t.setModel(0, 4, 1, mdl["eval"], mdl["evec"], mdl["inv_evec"], mdl["rates"], mdl["props"], None, mdl["state_freq"], 0.0)
     t.setParams(1e-6, 100.0)
+    t.setDevices([device])
     t.initializeAllPartialLh()
     return t
 
@@ -36,7 +39,8 @@ def main():
     a = [int(x) for x in sys.argv[1:5]]
     ntaxa, nptn, npart, reps = (a + [100, 20000, 50, 5][len(a):])[:4]
     lib = iqtree_b200.load_library()
-    parts = [make_part(lib, ntaxa, nptn, 4 if i % 2 == 0 else 20, 10 + i) for i in range(npart)]
+    ngpu = int(os.environ.get("LK_PART_GPUS", 1))
+    parts = [make_part(lib, ntaxa, nptn, 4 if i % 2 == 0 else 20, 10 + i, (i // 2) % ngpu) for i in range(npart)]
 
     def one(t):
         t.clearAllPartialLH()
@@ -48,8 +52,8 @@ def main():
         s = sum(one(t) for t in parts)
     seq = (time.time() - t0) / reps
     assert s == ref
-    out = {"partitions": npart, "ntaxa": ntaxa, "patterns_per_partition": nptn, "lnl": ref, "sequential_ms": seq * 1e3}
-    for nthr in (4, 16):
+    out = {"gpus": ngpu, "partitions": npart, "ntaxa": ntaxa, "patterns_per_partition": nptn, "lnl": ref, "sequential_ms": seq * 1e3}
+    for nthr in (4, 16, 32):
         with ThreadPoolExecutor(nthr) as ex:
             list(ex.map(one, parts))
             t0 = time.time()
