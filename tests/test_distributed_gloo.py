@@ -82,3 +82,53 @@ def test_two_ranks_gloo(case, tmp_path):
     trav = g["traversal"]
     for (a, b), ln in zip(trav, r[0]["lens"]):
         assert abs(ln - ref[(int(a), int(b))]) <= gu.BRLEN_ATOL
+
+
+def _em_worker(rank, world, port, case, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import json
+    import torch
+    import torch.distributed as dist
+    import golden_util as gu
+    from oracle.oracle_lib import load_oracle_library
+
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    g = gu.Golden(case)
+    m = json.loads(str(np.load(os.path.join(gu.GOLDEN_DIR, "em", case + ".npz"))["meta"]))
+    t = gu.build_tree(g, load_oracle_library(), shard=(rank, world))
+
+    def allreduce(host, dev_ptr, n):
+        if host is None:
+            host = np.ctypeslib.as_array((ctypes.c_double * n).from_address(dev_ptr))
+        x = torch.from_numpy(host.copy())
+        dist.all_reduce(x)
+        host[:] = x.numpy()
+
+    t.setAllReduce(allreduce)
+    t.initializeAllPartialLh()
+    t.computeLikelihood()
+    lnl, rates, props = t.optimizeRateFreeEM(m["ncat"], copy_precision=m["num_precision"])
+    np.savez(os.path.join(out_dir, "em_rank%d.npz" % rank), lnl=lnl, rates=rates, props=props)
+    t.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_rate_free_em_two_ranks_gloo(tmp_path):
+    """RateFree::optimizeWithEM with the patterns split over two ranks: the E-step sums and every likelihood of the one-category
+    copies go through the all-reduce; both ranks take the same Brent decisions and reach the reference's rates"""
+    import torch.multiprocessing as mp
+    import golden_util as gu
+    case, world = "dna_example_hky_r3", 2
+    mp.spawn(_em_worker, args=(world, _free_port(), case, str(tmp_path)), nprocs=world, join=True)
+    z = np.load(os.path.join(gu.GOLDEN_DIR, "em", case + ".npz"))
+    m = __import__("json").loads(str(z["meta"]))
+    r = [np.load(os.path.join(str(tmp_path), "em_rank%d.npz" % i)) for i in range(world)]
+    assert np.array_equal(r[0]["rates"], r[1]["rates"]) and np.array_equal(r[0]["props"], r[1]["props"])
+    for x in r:
+        assert abs(float(x["lnl"]) - m["lnl_after"]) <= 1e-9 * abs(m["lnl_after"])
+        gu.rel_close(x["rates"], z["rates"], 1e-7, "+R rates, two ranks")
+        gu.rel_close(x["props"], z["props"], 1e-7, "+R proportions, two ranks")
