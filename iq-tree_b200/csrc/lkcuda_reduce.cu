@@ -673,6 +673,64 @@ __global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) derv_kernel(De
     }
 }
 
+/* one evaluation of the persistent Newton loop, run by the thread that finished the grid reduction: the cross-GPU exchange, the
+   reference's state machine (newton_advance), the result when the loop ends, and the hand-over of the next length to the other blocks
+   (the same statements as in newton_b16_kernel) */
+__device__ __noinline__ void newton_elected(const DevView &v, NewtonCtl *ctl, unsigned int it, double x, double df, double ddf,
+                                            double x1, double x2, double xacc, int maxNRStep) {
+    unsigned int err = 0;
+    if (v.peer_world > 1) {
+        double r[LKCUDA_NRESULT] = {0.0, df, ddf, 0.0, 0.0, 0.0, 0.0, 0.0};
+        err = peer_exchange(v, r, v.peer_seq + it);
+        df = r[LKCUDA_R_DF]; ddf = r[LKCUDA_R_DDF];
+    }
+    NewtonCtl c;
+    c.x = __ldcg(&ctl->x); c.xl = __ldcg(&ctl->xl); c.xh = __ldcg(&ctl->xh); c.rts = __ldcg(&ctl->rts); c.dx = __ldcg(&ctl->dx);
+    c.d2l = __ldcg(&ctl->d2l); c.j = __ldcg(&ctl->j); c.nev = __ldcg(&ctl->nev); c.phase = __ldcg(&ctl->phase); c.done = __ldcg(&ctl->done);
+    c.optx = __ldcg(&ctl->optx); c.last_x = __ldcg(&ctl->last_x);
+    if (it == 0) { c.rts = x; c.phase = 0; c.nev = 0; c.done = 0; c.j = 0; c.d2l = 0.0; c.optx = x; }
+    if (isnan(df) || isinf(df)) { df = 0.0; ddf = 0.0; }
+    c.f = -df; c.df = -ddf;
+    newton_advance(c, x1, x2, xacc, maxNRStep);
+    if (err) c.done = 4;
+    if (c.done) {
+        double r[LKCUDA_NRESULT] = {c.optx, c.d2l, (double)c.nev, c.last_x, (double)c.done, 0.0, 0.0, 0.0};
+        post_result(v, r, err);
+    }
+    ctl->x = c.x; ctl->xl = c.xl; ctl->xh = c.xh; ctl->rts = c.rts; ctl->dx = c.dx; ctl->d2l = c.d2l;
+    ctl->j = c.j; ctl->nev = c.nev; ctl->phase = c.phase; ctl->done = c.done; ctl->optx = c.optx; ctl->last_x = c.last_x;
+    __threadfence();
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(&ctl->gen), "r"(it + 1) : "memory");
+}
+
+/* Optimization::minimizeNewton as ONE persistent cooperative launch for ANY block shape (protein, codon, mixtures): the pass, grid and
+   summation order of derv_kernel per evaluation (bit-identical df / ddf), theta_all built beforehand by theta_kernel */
+template <bool VEC>
+__global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) newton_generic_kernel(DevView v, NewtonCtl *ctl, double x1, double xguess, double x2,
+                                                                                       double xacc, int maxNRStep, int gshift) {
+    extern __shared__ __align__(32) double sh[];
+    __shared__ double sred[5 * 32];
+    __shared__ double sh_x; __shared__ int sh_done;
+    const int Bp = (v.B + 3) & ~3;
+    double x = xguess;
+    if (x < x1) x = x1;
+    if (x > x2) x = x2;
+    for (unsigned int it = 0;; it++) {
+        DervOut o;
+        if (derv_pass<VEC>(v, x, gshift, sh, sh + Bp, sh + 2 * Bp, sred, &o)) newton_elected(v, ctl, it, x, o.df, o.ddf, x1, x2, xacc, maxNRStep);
+        if (threadIdx.x == 0) {
+            unsigned int g;
+            do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(g) : "l"(&ctl->gen) : "memory"); } while (g < it + 1);
+            sh_x = *reinterpret_cast<volatile double *>(&ctl->x);
+            sh_done = *reinterpret_cast<volatile int *>(&ctl->done);
+        }
+        __syncthreads();
+        if (sh_done) break;
+        x = sh_x;
+        __syncthreads();
+    }
+}
+
 template <bool VEC>
 __global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) frombuf_kernel(DevView v, double len, int gshift) {
     extern __shared__ __align__(32) double sh[];
@@ -791,7 +849,7 @@ void lkc::preload_reduce_kernels() {
     PRELOAD((branch_kernel<true, true>)); PRELOAD((branch_kernel<true, false>)); PRELOAD((branch_kernel<false, true>)); PRELOAD((branch_kernel<false, false>));
     PRELOAD(branch_tip_b16_kernel); PRELOAD(asc_adjust_kernel); PRELOAD(pattern_lh_cat_kernel);
     PRELOAD((theta_kernel<true, true>)); PRELOAD((theta_kernel<true, false>)); PRELOAD((theta_kernel<false, true>)); PRELOAD((theta_kernel<false, false>));
-    PRELOAD(newton_b16_kernel<0>); PRELOAD(newton_b16_kernel<1>); PRELOAD(newton_b16_kernel<2>); PRELOAD(derv_b16_kernel); PRELOAD(theta_derv_b16_kernel<true>); PRELOAD(theta_derv_b16_kernel<false>);
+    PRELOAD(newton_generic_kernel<true>); PRELOAD(newton_generic_kernel<false>); PRELOAD(newton_b16_kernel<0>); PRELOAD(newton_b16_kernel<1>); PRELOAD(newton_b16_kernel<2>); PRELOAD(derv_b16_kernel); PRELOAD(theta_derv_b16_kernel<true>); PRELOAD(theta_derv_b16_kernel<false>);
     PRELOAD(derv_kernel<true>); PRELOAD(derv_kernel<false>); PRELOAD(frombuf_kernel<true>); PRELOAD(frombuf_kernel<false>);
     PRELOAD(pattern_lh_corrected_kernel); PRELOAD(scale_factor_kernel);
     PRELOAD(sitemodel_reduce_kernel<0>); PRELOAD(sitemodel_reduce_kernel<1>); PRELOAD(sitemodel_reduce_kernel<2>); PRELOAD(sitemodel_reduce_kernel<3>);
@@ -1032,11 +1090,49 @@ static int newton_persistent(lkcuda_engine *e, int build, int32_t dad, int32_t n
     const DevView &v = e->v;
     GroupShape gs = group_shape(v);
     static const bool host_loop = getenv("LKCUDA_HOST_NEWTON") && atoi(getenv("LKCUDA_HOST_NEWTON")) != 0;      /* test knob */
-    if (!(gs.vec && v.B == 16 && v.S == 4 && v.SU < 32) || IS_SITEMODEL(e) || host_loop) return 1;
+    if (IS_SITEMODEL(e) || host_loop) return 1;
+    const bool b16 = gs.vec && v.B == 16 && v.S == 4 && v.SU < 32;
+    if (!b16) {
+        /* any other block shape: theta_all must exist (the caller builds it with theta_kernel), then derv_kernel's pass in a loop */
+        if (build != 0) return 1;
+        static const bool generic_off = getenv("LKCUDA_NEWTON_B16_ONLY") && atoi(getenv("LKCUDA_NEWTON_B16_ONLY")) != 0;   /* test knob */
+        if (generic_off) return 1;
+        const size_t sm = (size_t)3 * ((v.B + 3) & ~3) * 8;
+        const void *fn = gs.vec ? (const void *)newton_generic_kernel<true> : (const void *)newton_generic_kernel<false>;
+        if (sm > 48 * 1024) return 1;
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, RED_THREADS, sm) != cudaSuccess || occ < 1) { cudaGetLastError(); return 1; }
+        int grid = red_grid(e, v.NP, gs.G);
+        if (grid > occ * e->num_sms) grid = occ * e->num_sms;
+        if (!e->d_newton_ctl && cudaMalloc((void **)&e->d_newton_ctl, 256) != cudaSuccess) return -cuda_fail(e, cudaGetLastError(), "cudaMalloc");
+        if (cudaMemsetAsync(e->d_newton_ctl, 0, 256, e->stream) != cudaSuccess) return -cuda_fail(e, cudaGetLastError(), "cudaMemsetAsync");
+        next_result(e);
+        launch_begin(e, KIND_NEWTON);
+        lkc::DevView vv = e->v;
+        NewtonCtl *ctl = (NewtonCtl *)e->d_newton_ctl;
+        int imax = maxNRStep, igs = gs.gshift;
+        void *args[] = {&vv, &ctl, &x1, &xguess, &x2, &xacc, &imax, &igs};
+        cudaError_t ce = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(RED_THREADS), args, sm, e->stream);
+        if (ce != cudaSuccess) return -cuda_fail(e, ce, "newton_generic_kernel");
+        double r[LKCUDA_NRESULT];
+        int rcn = launch_end(e, KIND_NEWTON, 0, "newton_generic_kernel");
+        if (rcn) return -rcn;
+        rcn = lkcuda_wait_result(e, r);
+        if (rcn) return -rcn;
+        const int nev = (int)r[2], status = (int)r[4];
+        const uint64_t bytes = (uint64_t)nev * (uint64_t)v.NP * ((uint64_t)v.B * 8 + 16);
+        e->kind_bytes[KIND_NEWTON] += bytes; e->bytes += bytes;
+        if (v.peer_world > 1 && nev > 1) e->peer_seq += (unsigned int)(nev - 1);
+        out[0] = r[0]; out[1] = r[1]; out[2] = r[2]; out[3] = r[3];
+        if (status == 2) return -fail(e, LKCUDA_ERR_STATE, "Wrong computeFuncDerv");
+        if (status == 3) return -fail(e, LKCUDA_ERR_STATE, "Maximum number of iterations exceeded in minimizeNewton");
+        if (status != 1) return -fail(e, LKCUDA_ERR_STATE, "device Newton loop failed (status %d)", status);
+        return 0;
+    }
     int grid = red_grid(e, v.NP, gs.G);
     if (grid > e->num_sms * 2) grid = e->num_sms * 2;
-    if (!e->d_newton_ctl) {
-        if (cudaMalloc((void **)&e->d_newton_ctl, 256) != cudaSuccess) return -cuda_fail(e, cudaGetLastError(), "cudaMalloc");
+    if (!e->newton_max_grid) {
+        if (!e->d_newton_ctl && cudaMalloc((void **)&e->d_newton_ctl, 256) != cudaSuccess) return -cuda_fail(e, cudaGetLastError(), "cudaMalloc");
         int occ = 0, o2 = 0;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, newton_b16_kernel<0>, RED_THREADS, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o2, newton_b16_kernel<1>, RED_THREADS, 0); if (o2 < occ) occ = o2;

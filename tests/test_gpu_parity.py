@@ -19,7 +19,7 @@ def test_cuda_matches_reference(case, cuda_lib):
     t.close()
 
 
-@pytest.mark.parametrize("case", ["dna_example_gtr_g4", "dna_deep_scaling", "aa_lg_g4", "morph_mk_asc"])
+@pytest.mark.parametrize("case", ["dna_example_gtr_g4", "dna_deep_scaling", "aa_lg_g4", "morph_mk_asc", "codon_gy", "aa_lg4x", "aa_lg_c20_g4", "bin_jc2_g4", "dna_example_hky_r3"])
 def test_cuda_device_newton(case, cuda_lib):
     """optimizeAllBranches with the Newton loop driven inside the engine gives the same lengths"""
     g = gu.Golden(case)

@@ -59,7 +59,7 @@ def test_oracle_nni_matches_reference(name, oracle_lib):
 @pytest.mark.parametrize("nshard,device_newton", [(1, False), (1, True), (2, False)])
 @pytest.mark.parametrize("name", NNI_FILES)
 def test_cuda_nni_matches_reference(name, nshard, device_newton, cuda_lib):
-    """device_newton: every branch optimisation is ONE persistent launch (newton_b16_kernel for DNA+G4; host-driven steps elsewhere)"""
+    """device_newton: every branch optimisation is ONE persistent launch (newton_b16_kernel for DNA+G4, newton_generic_kernel elsewhere)"""
     z, m, case = _load(name)
     g = gu.Golden(case)
     t = gu.build_tree(g, cuda_lib, devices=[0] * nshard, device_newton=device_newton)
