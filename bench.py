@@ -361,10 +361,14 @@ def main():
         if rc:
             raise RuntimeError(lib.lkcuda_last_error(eng).decode())
         t.clearAllPartialLH()
-        rc = lib.lktree_compute_likelihood(t.h, ctypes.byref(lnl_c), ctypes.cast(pinned_plh.data_ptr(), c_dp))
+        # the per-pattern log-likelihoods travel to the pinned host buffer while the df/ddf part of the step runs
+        rc = lib.lktree_compute_likelihood_async_fetch(t.h, ctypes.byref(lnl_c), ctypes.cast(pinned_plh.data_ptr(), c_dp))
         if rc:
             raise RuntimeError(lib.lktree_last_error(t.h).decode())
         d = t.computeLikelihoodDerv(root_leaf, root_nei, reset_theta=True)
+        rc = lib.lktree_wait_pattern_lh(t.h)
+        if rc:
+            raise RuntimeError(lib.lktree_last_error(t.h).decode())
         return lnl_c.value, d[0], d[1]
 
     e2e_step()

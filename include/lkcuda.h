@@ -225,6 +225,10 @@ int lkcuda_fetch_pattern_lh_cat(lkcuda_engine *e, double *pattern_lh_cat /*[P][K
 /* the tail of PhyloTree::computeLikelihood(double *pattern_lh) (phylotree.cpp:1055-1069) done on the device:
    dst[p] = _pattern_lh[p] + max(scale_num(vec)[p], 0) * LOG_SCALING_THRESHOLD; vec < 0 (a tip end): plain copy.
    _pattern_lh itself is left untouched. */
+/* the same without waiting: the correction runs on the engine's stream, the copy to `pattern_lh` (pinned host memory) on a copy stream,
+   so that the next kernels overlap it; lkcuda_fetch_wait returns when the data has arrived (one fetch in flight per engine) */
+int lkcuda_fetch_pattern_lh_corrected_async(lkcuda_engine *e, int32_t vec, double *pattern_lh /*[P], pinned*/);
+int lkcuda_fetch_wait(lkcuda_engine *e);
 int lkcuda_fetch_pattern_lh_corrected(lkcuda_engine *e, int32_t vec, double *pattern_lh /*[P]*/);
 int lkcuda_fetch_vector(lkcuda_engine *e, int32_t vec, double *partial_lh /*[(P+U)*K*S] or NULL*/,
                         int16_t *scale_num /*[P+U] or NULL*/);

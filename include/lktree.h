@@ -77,6 +77,10 @@ int lktree_initialize_all_partial_lh(lktree *h);
 int lktree_delete_all_partial_lh(lktree *h);
 int lktree_clear_all_partial_lh(lktree *h);
 int lktree_compute_likelihood(lktree *h, double *lnl, double *pattern_lh /* [local P] or NULL */);
+/* computeLikelihood whose per-pattern values (pinned host memory, [local P]) are still being copied when it returns: the caller
+   goes on (e.g. with computeLikelihoodDerv) and calls lktree_wait_pattern_lh before reading them */
+int lktree_compute_likelihood_async_fetch(lktree *h, double *lnl, double *pattern_lh);
+int lktree_wait_pattern_lh(lktree *h);
 int lktree_compute_likelihood_branch(lktree *h, int32_t node1, int32_t node2, double *lnl);
 int lktree_compute_likelihood_derv(lktree *h, int32_t node1, int32_t node2, int32_t reset_theta, double *df, double *ddf);
 int lktree_compute_likelihood_from_buffer(lktree *h, double *lnl);

@@ -229,6 +229,11 @@ int lktree_shard_patterns(lktree *h, int32_t i, int64_t *begin, int64_t *end) {
     LK_CATCH(h)
 }
 
+int lktree_compute_likelihood_async_fetch(lktree *h, double *lnl, double *pattern_lh) {
+    LK_TRY(h) *lnl = h->tree.computeLikelihoodAsyncFetch(pattern_lh); LK_CATCH(h)
+}
+int lktree_wait_pattern_lh(lktree *h) { LK_TRY(h) h->tree.waitPatternLh(); LK_CATCH(h) }
+
 int lktree_optimize_rate_free_em(lktree *h, int32_t copy_precision, double *lnl, double *rates, double *props) {
     LK_TRY(h)
     *lnl = h->tree.optimizeRateFreeEM(copy_precision);

@@ -745,6 +745,21 @@ double PhyloTree::computeLikelihood(double *pattern_lh) {   // phylotree.cpp:103
     return score;
 }
 
+double PhyloTree::computeLikelihoodAsyncFetch(double *pattern_lh) {
+    double score = computeLikelihood(NULL);
+    for (size_t d = 0; d < engines_.size(); d++) {
+        int64_t b = shard_begin_[d] - ptn_begin_, np = shard_begin_[d + 1] - shard_begin_[d];
+        if (!np) continue;
+        if (current_it->vec < 0) throw std::runtime_error("computeLikelihoodAsyncFetch: the root branch has no vector");
+        check(lkcuda_fetch_pattern_lh_corrected_async(engines_[d], current_it->vec, pattern_lh + b), engines_[d], "lkcuda_fetch_pattern_lh_corrected_async");
+    }
+    return score;
+}
+
+void PhyloTree::waitPatternLh() {
+    for (size_t d = 0; d < engines_.size(); d++) check(lkcuda_fetch_wait(engines_[d]), engines_[d], "lkcuda_fetch_wait");
+}
+
 /* phylotree.cpp:1108-1160: per-category pattern likelihoods on current_it (picked like the reference when unset);
    wsl: 2 = WSL_RATECAT, 3 = WSL_MIXTURE, 4 = WSL_MIXTURE_RATECAT (tools.h:406). Returns the entries per pattern. */
 void PhyloTree::enqueuePatternLhCat() {

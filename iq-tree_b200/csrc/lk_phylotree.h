@@ -133,6 +133,9 @@ public:
     void computeLikelihoodDerv(Neighbor *dad_branch, Node *dad, double &df, double &ddf);
     double computeLikelihoodFromBuffer();
     double computeLikelihood(double *pattern_lh = NULL);
+    // the same with the per-pattern values still on their way to (pinned) host memory when it returns; waitPatternLh() ends the transfer
+    double computeLikelihoodAsyncFetch(double *pattern_lh);
+    void waitPatternLh();
     int computePatternLhCat(double *pattern_lh_cat, int wsl = 4);    // phylotree.cpp:1108-1160; returns entries per pattern
     /* NNI evaluation (phylotree.cpp:2873-3066): both NNIs around the internal branch (node1, node2), each with its 1 (nni5 = false) or 5
        surrounding branches re-optimised by Newton-Raphson (NNI_MAX_NR_STEP = 10, pllnni.cpp:21); the tree is left as it was */

@@ -112,6 +112,7 @@ struct lkcuda_engine {
     double *d_theta; int16_t *d_theta_sc; double *d_theta_meta;
     int32_t *d_ptn_model; unsigned long long *d_state_mask;     /* LKCUDA_FLAG_SITEMODEL */
     double *d_plh, *d_plhcat, *d_plh_out;   /* d_plh_out: scale-corrected copy of _pattern_lh on its way to the host (lazy) */
+    cudaStream_t dstream; cudaEvent_t ev_plh_ready, ev_plh_done; bool plh_pending;   /* asynchronous device-to-host fetch of d_plh_out (lazy) */
     double *d_red; unsigned int *d_counter; double *d_result;
     double *h_result;                       /* pinned */
     double *h_mapped;                       /* pinned + mapped: [0..7] result block, [8] (as uint64) sequence number | error << 32, written by publish_result */

@@ -160,6 +160,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     e->d_states = NULL; e->d_freq = e->d_invar = NULL;
     e->d_eval = e->d_evec = e->d_inv = e->d_rate = e->d_weight = e->d_tip = NULL; e->d_eigen = NULL;
     e->d_arena = NULL; e->d_scale = NULL; e->d_theta = NULL; e->d_theta_sc = NULL; e->d_theta_meta = NULL;
+    e->dstream = NULL; e->ev_plh_ready = NULL; e->ev_plh_done = NULL; e->plh_pending = false;
     e->d_plh = e->d_plhcat = e->d_plh_out = NULL; e->d_red = NULL; e->d_counter = NULL; e->d_result = NULL; e->h_result = NULL;
     e->d_newton_out = NULL; e->h_newton_out = NULL; e->d_newton_ctl = NULL; e->newton_max_grid = 0;
     e->d_ptn_model = NULL; e->d_state_mask = NULL;
@@ -274,6 +275,7 @@ int lkcuda_destroy(lkcuda_engine *e) {
     cudaFree(e->d_states); cudaFree(e->d_freq); cudaFree(e->d_invar);
     cudaFree(e->d_eval); cudaFree(e->d_evec); cudaFree(e->d_inv); cudaFree(e->d_rate); cudaFree(e->d_weight); cudaFree(e->d_eigen);
     cudaFree(e->d_tip); cudaFree(e->d_arena); cudaFree(e->d_scale); cudaFree(e->d_theta); cudaFree(e->d_theta_sc); cudaFree(e->d_theta_meta);
+    if (e->dstream) { cudaStreamSynchronize(e->dstream); cudaStreamDestroy(e->dstream); cudaEventDestroy(e->ev_plh_ready); cudaEventDestroy(e->ev_plh_done); }
     cudaFree(e->d_plh); cudaFree(e->d_plhcat); cudaFree(e->d_plh_out); cudaFree(e->d_red); cudaFree(e->d_counter); cudaFree(e->d_result);
     cudaFree(e->d_newton_out); cudaFree(e->d_newton_ctl); cudaFree(e->d_tables); cudaFree(e->d_inv_frags);
     if (e->h_result) cudaFreeHost(e->h_result);

@@ -1230,6 +1230,45 @@ int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, 
 #undef NR_RETURN
 }
 
+/* the correction kernel on the engine's stream, the copy on a stream of its own: later kernels (the next branch's theta_all, df/ddf)
+   overlap the transfer; lkcuda_fetch_wait (or the synchronous variant) ends it.  dst should be pinned host memory. */
+int lkcuda_fetch_pattern_lh_corrected_async(lkcuda_engine *e, int32_t vec, double *dst) {
+    LK_ENTER(e);
+    if (!dst || vec < 0 || vec >= e->cfg.nvec) return fail(e, LKCUDA_ERR_ARG, "lkcuda_fetch_pattern_lh_corrected_async: bad argument");
+    const DevView &v = e->v;
+    if (!v.P) return LKCUDA_OK;
+    if (!e->d_plh_out) {
+        LK_CUDA(e, cudaMalloc((void **)&e->d_plh_out, (size_t)v.P * 8));
+        e->total_dev_bytes += (uint64_t)v.P * 8;
+    }
+    if (!e->dstream) {
+        LK_CUDA(e, cudaStreamCreateWithFlags(&e->dstream, cudaStreamNonBlocking));
+        LK_CUDA(e, cudaEventCreateWithFlags(&e->ev_plh_ready, cudaEventDisableTiming));
+        LK_CUDA(e, cudaEventCreateWithFlags(&e->ev_plh_done, cudaEventDisableTiming));
+    }
+    if (e->plh_pending) LK_CUDA(e, cudaStreamWaitEvent(e->stream, e->ev_plh_done, 0));     /* the staging buffer is still on its way out */
+    int grid = red_grid(e, v.P, 1);
+    launch_begin(e, KIND_MISC);
+    pattern_lh_corrected_kernel<<<grid, RED_THREADS, 0, e->stream>>>(e->v, vec, e->d_plh_out);
+    int rc = launch_end(e, KIND_MISC, 0, "pattern_lh_corrected_kernel");
+    if (rc) return rc;
+    LK_CUDA(e, cudaEventRecord(e->ev_plh_ready, e->stream));
+    LK_CUDA(e, cudaStreamWaitEvent(e->dstream, e->ev_plh_ready, 0));
+    LK_CUDA(e, cudaMemcpyAsync(dst, e->d_plh_out, (size_t)v.P * 8, cudaMemcpyDeviceToHost, e->dstream));
+    LK_CUDA(e, cudaEventRecord(e->ev_plh_done, e->dstream));
+    e->plh_pending = true;
+    return LKCUDA_OK;
+}
+
+int lkcuda_fetch_wait(lkcuda_engine *e) {
+    LK_ENTER(e);
+    if (e->plh_pending) {
+        LK_CUDA(e, cudaEventSynchronize(e->ev_plh_done));
+        e->plh_pending = false;
+    }
+    return upload_verdict(e);
+}
+
 int lkcuda_fetch_pattern_lh_corrected(lkcuda_engine *e, int32_t vec, double *dst) {
     LK_ENTER(e);
     if (!dst || vec >= e->cfg.nvec) return fail(e, LKCUDA_ERR_ARG, "lkcuda_fetch_pattern_lh_corrected: bad argument");
@@ -1240,6 +1279,7 @@ int lkcuda_fetch_pattern_lh_corrected(lkcuda_engine *e, int32_t vec, double *dst
             LK_CUDA(e, cudaMalloc((void **)&e->d_plh_out, (size_t)v.P * 8));
             e->total_dev_bytes += (uint64_t)v.P * 8;
         }
+        if (e->plh_pending) { LK_CUDA(e, cudaEventSynchronize(e->ev_plh_done)); e->plh_pending = false; }
         int grid = red_grid(e, v.P, 1);
         launch_begin(e, KIND_MISC);
         pattern_lh_corrected_kernel<<<grid, RED_THREADS, 0, e->stream>>>(e->v, vec, e->d_plh_out);

@@ -77,6 +77,8 @@ LKCUDA_SYMBOLS = {
     "lkcuda_set_result_buffer": (C.c_int, [C.c_void_p, C.c_void_p]),
     "lkcuda_fetch_pattern_lh": (C.c_int, [C.c_void_p, c_double_p]),
     "lkcuda_fetch_pattern_lh_cat": (C.c_int, [C.c_void_p, c_double_p]),
+    "lkcuda_fetch_pattern_lh_corrected_async": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),
+    "lkcuda_fetch_wait": (C.c_int, [C.c_void_p]),
     "lkcuda_fetch_pattern_lh_corrected": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),
     "lkcuda_fetch_vector": (C.c_int, [C.c_void_p, C.c_int32, c_double_p, c_int16_p]),
     "lkcuda_store_vector": (C.c_int, [C.c_void_p, C.c_int32, c_double_p, c_int16_p]),
@@ -119,6 +121,8 @@ LKTREE_SYMBOLS = {
     "lktree_delete_all_partial_lh": (C.c_int, [C.c_void_p]),
     "lktree_clear_all_partial_lh": (C.c_int, [C.c_void_p]),
     "lktree_compute_likelihood": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
+    "lktree_compute_likelihood_async_fetch": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
+    "lktree_wait_pattern_lh": (C.c_int, [C.c_void_p]),
     "lktree_compute_likelihood_branch": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_double_p]),
     "lktree_compute_likelihood_derv": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p]),
     "lktree_compute_likelihood_from_buffer": (C.c_int, [C.c_void_p, c_double_p]),

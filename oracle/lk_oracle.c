@@ -653,6 +653,9 @@ int lkcuda_fetch_pattern_lh(lkcuda_engine *e, double *dst) {
     memcpy(dst, e->pattern_lh, (size_t)e->cfg.nptn * 8);
     return LKCUDA_OK;
 }
+int lkcuda_fetch_pattern_lh_corrected(lkcuda_engine *e, int32_t vec, double *dst);
+int lkcuda_fetch_pattern_lh_corrected_async(lkcuda_engine *e, int32_t vec, double *dst) { return vec < 0 ? LKCUDA_ERR_ARG : lkcuda_fetch_pattern_lh_corrected(e, vec, dst); }
+int lkcuda_fetch_wait(lkcuda_engine *e) { return e ? LKCUDA_OK : LKCUDA_ERR_ARG; }
 int lkcuda_fetch_pattern_lh_corrected(lkcuda_engine *e, int32_t vec, double *dst) {   /* phylotree.cpp:1055-1069 */
     int rc = lkcuda_fetch_pattern_lh(e, dst);
     if (rc || vec < 0) return rc;

@@ -340,3 +340,26 @@ def test_ragged_and_empty_shards(npat, nshard, cuda_lib, oracle_lib):
     oa, ob = a.optimizeAllBranches(1), b.optimizeAllBranches(1)
     assert abs(oa - ob) <= gu.LNL_RTOL * abs(ob)
     a.close(); b.close()
+
+
+@pytest.mark.parametrize("nshard", [1, 3])
+def test_async_pattern_lh_fetch(nshard, cuda_lib):
+    """lktree_compute_likelihood_async_fetch + lktree_wait_pattern_lh deliver what the synchronous computeLikelihood(pattern_lh) does,
+    also when df/ddf work is queued behind the fetch and when fetches follow each other"""
+    import ctypes as C
+    g = gu.Golden("dna_deep_scaling")
+    t = gu.build_tree(g, cuda_lib, devices=[0] * nshard)
+    t.initializeAllPartialLh()
+    lnl, plh = t.computeLikelihood(pattern_lh=True)
+    a, b = g.meta["derv_branch"]
+    for _ in range(3):
+        out = np.zeros_like(plh)
+        v = C.c_double()
+        t.clearAllPartialLH()
+        assert cuda_lib.lktree_compute_likelihood_async_fetch(t.h, C.byref(v), out.ctypes.data_as(C.POINTER(C.c_double))) == 0
+        df, ddf = t.computeLikelihoodDerv(a, b, reset_theta=True)
+        assert cuda_lib.lktree_wait_pattern_lh(t.h) == 0
+        assert v.value == lnl and np.array_equal(out, plh)
+        assert abs(df - g.meta["df_root"]) <= 1e-7 * max(1.0, abs(g.meta["df_root"]))
+    gu.rel_close(plh, g["pattern_lh_scaled"], gu.PTN_RTOL, "pattern_lh")
+    t.close()
