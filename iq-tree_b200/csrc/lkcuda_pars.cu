@@ -254,7 +254,8 @@ extern "C" int lkpars_create(int32_t device, int32_t nstates, int32_t ntaxa, int
     e->d_bits = NULL; e->d_ops = NULL; e->d_counts = NULL; e->h_ops = NULL; e->h_counts = NULL; e->ops_cap = 0;
     e->profiling = false; e->launches = 0; e->device_ms = 0.0;
     cudaError_t c;
-#define CREATE_CUDA(call) if ((c = (call)) != cudaSuccess) { int rc = pfail(NULL, LKCUDA_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(c)); lkpars_destroy(e); return rc; }
+    uint8_t *d_states = NULL; unsigned long long *d_mask = NULL;
+#define CREATE_CUDA(call) if ((c = (call)) != cudaSuccess) { int rc = pfail(NULL, LKCUDA_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(c)); cudaFree(d_states); cudaFree(d_mask); lkpars_destroy(e); return rc; }
     CREATE_CUDA(cudaSetDevice(device));
     cudaDeviceProp prop;
     CREATE_CUDA(cudaGetDeviceProperties(&prop, device));
@@ -264,7 +265,6 @@ extern "C" int lkpars_create(int32_t device, int32_t nstates, int32_t ntaxa, int
     CREATE_CUDA(cudaEventCreate(&e->ev1));
     const size_t words = (size_t)(ntaxa + nvec) * nstates * e->nw;
     CREATE_CUDA(cudaMalloc((void **)&e->d_bits, words * 4));
-    uint8_t *d_states = NULL; unsigned long long *d_mask = NULL;
     CREATE_CUDA(cudaMalloc((void **)&d_states, (size_t)ntaxa * (nsites > 0 ? nsites : 1)));
     CREATE_CUDA(cudaMalloc((void **)&d_mask, 256 * 8));
     if (nsites > 0) CREATE_CUDA(cudaMemcpyAsync(d_states, site_states, (size_t)ntaxa * nsites, cudaMemcpyHostToDevice, e->stream));
