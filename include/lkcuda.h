@@ -184,12 +184,13 @@ int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result);
 /* Optimization::minimizeNewton (optimization.cpp:388-465) driven on the device over theta_all:
    same step sequence, one launch instead of one launch + one read-back per Newton step.
    out[4]: [0] = optx, [1] = d2l, [2] = number of computeFuncDerv evaluations, [3] = the last length
-   evaluated (where the reference leaves current_it->length).  Single shard only. */
+   evaluated (where the reference leaves current_it->length).  One persistent cooperative launch for every block shape
+   (site-specific models: host-driven steps); with peers attached every evaluation is exchanged inside the loop. */
 int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, double xacc,
                          int32_t max_nr_step, double *out);
 
 /* lkcuda_theta_build + lkcuda_newton_branch on the branch (dad, node) in one call - for DNA with 4 categories ONE persistent launch that
-   builds theta_all in its first Newton step (optimizeOneBranch's device part, phylotree.cpp:2148-2170); same out[4] */
+   builds theta_all in its first Newton step, for other shapes theta_kernel + one persistent launch (optimizeOneBranch's device part, phylotree.cpp:2148-2170); same out[4] */
 int lkcuda_theta_newton(lkcuda_engine *e, int32_t dad, int32_t node, double x1, double xguess, double x2, double xacc,
                         int32_t max_nr_step, double *out);
 
