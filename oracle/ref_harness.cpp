@@ -514,14 +514,17 @@ static int do_dumpem(int argc, char **argv) {
     std::vector<double> v;
     for (int c = 0; c < nc; c++) v.push_back(rf->getRate(c));
     for (int c = 0; c < nc; c++) v.push_back(rf->getProp(c));
+    double t_em = omp_get_wtime();
     double lnl1 = rf->optimizeWithEM();
+    t_em = omp_get_wtime() - t_em;
     for (int c = 0; c < nc; c++) v.push_back(rf->getRate(c));
     for (int c = 0; c < nc; c++) v.push_back(rf->getProp(c));
     wbin("em_rates_props.f64", &v[0], v.size() * 8);
     {
         std::ofstream f((g_out + "/metaem.json").c_str());
         f << std::setprecision(17);
-        f << "{ \"ncat\": " << nc << ", \"lnl_before\": " << lnl0 << ", \"lnl_after\": " << lnl1 << ", \"num_precision\": " << tree->num_precision << " }\n";
+        f << "{ \"ncat\": " << nc << ", \"lnl_before\": " << lnl0 << ", \"lnl_after\": " << lnl1 << ", \"num_precision\": " << tree->num_precision
+          << ", \"em_seconds\": " << t_em << ", \"threads\": " << omp_get_max_threads() << ", \"nptn\": " << tree->aln->getNPattern() << " }\n";
     }
     printf("dumpem ncat %d lnl %.10f -> %.10f\n", nc, lnl0, lnl1);
     return 0;

@@ -135,6 +135,33 @@ def rem(nptn):
            "main_tree_partial_computations": t.numPartialLhComputations() - n0,
            "note": "every EM step: 1 per-category likelihood pass (4 categories) + E-step on the device + 4 Brent searches of ~10-20 "
                    "one-category full-tree likelihoods each; the P x 4 posterior matrix never leaves the device"}
+    # the unmodified reference's own EM on a bounded sample of the same alignment, all host threads (oracle/_ref/ref_harness dumpem)
+    harness = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
+    ref_sites = int(os.environ.get("LK_REF_SITES", 100000))
+    if os.path.exists(harness) and ref_sites > 0:
+        import subprocess
+        import tempfile
+        tmp = tempfile.mkdtemp(prefix="lk_rem_")
+        ns = min(ref_sites, nptn)
+        lut = np.array(list("ACGT"))
+        aln = os.path.join(tmp, "sample.phy")
+        with open(aln, "w") as f:
+            f.write("%d %d\n" % (ntaxa, ns))
+            for i, n in enumerate(names):
+                f.write("%s  %s\n" % (n, "".join(lut[st[i, :ns]])))
+        tre = os.path.join(tmp, "sample.nwk")
+        open(tre, "w").write(nwk + "\n")
+        cmd = [harness, "dumpem", os.path.join(tmp, "out"), "-s", aln, "-m", "GTR+R4", "-te", tre, "-nt", str(os.cpu_count() or 1), "-seed", "1",
+               "-pre", os.path.join(tmp, "ref")]
+        r = subprocess.run(cmd, cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        try:
+            m = json.load(open(os.path.join(tmp, "out", "metaem.json")))
+            out["reference"] = {"sample_sites": ns, "patterns": m["nptn"], "threads": m["threads"], "em_seconds": m["em_seconds"],
+                                "lnl_before": m["lnl_before"], "lnl_after": m["lnl_after"],
+                                "note": "its own initial +R4 parameters (not the ones above): a timing, not a parity check"}
+            out["seconds_per_million_patterns"] = {"b200": wall * 1e6 / nptn, "reference": m["em_seconds"] * 1e6 / m["nptn"]}
+        except Exception as ex:
+            out["reference"] = {"error": str(ex), "tail": r.stdout[-400:]}
     print(json.dumps(out))
     t.close()
 
