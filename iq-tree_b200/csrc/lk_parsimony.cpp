@@ -349,6 +349,7 @@ int PhyloTree::computeParsimonyTree(const int32_t *taxon_order) {
     nodeNum = leafNum;                           /* initializeTree, mtree.cpp:561-583 */
     initializeTreeIds(root, NULL);
     fixNegativeBranch(true);
+    if (size == 3) return computeParsimony();    /* no insertion round ran (the reference returns its stale best_pars_score here) */
     return best_pars_score;
 }
 
