@@ -273,6 +273,8 @@ int lkcuda_rell_device_ptr(lkcuda_engine *e, void **dev_ptr);
      (model/rategammainvar.cpp:193-221) - ptn_invar joins the denominator and competes as category 0, the others become c + 1. */
 int lkcuda_lh_cat_collapse(lkcuda_engine *e, int32_t mode, int32_t ncat, int32_t nmix, int32_t *ncol);
 int lkcuda_lh_cat_em(lkcuda_engine *e, const double *ratio /*[ncol] or NULL*/, double *sums /*[ncol]*/);
+/* include_invar = 0: the pattern likelihood of RateFree::optimizeWithEM's E-step, which leaves ptn_invar out (ratefree.cpp:487-503, also under +I+R) */
+int lkcuda_lh_cat_em_ex(lkcuda_engine *e, const double *ratio /*[ncol] or NULL*/, int32_t include_invar, double *sums /*[ncol]*/);
 /* the E-step posterior of class `col` (w[p][col] * ptn_freq[p] / ([ptn_invar[p] +] sum_c w[p][c]): ratefree.cpp:487-503 without,
    modelmixture.cpp:1458-1471 with ptn_invar) becomes the
    ptn_freq of `dst`, an engine over the same patterns on the same device (the sub-tree of RateFree::optimizeWithEM, ratefree.cpp:533-549,

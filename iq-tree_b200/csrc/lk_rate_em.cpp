@@ -177,7 +177,7 @@ double PhyloTree::optimizeTreeLengthScaling(double min_scaling, double &scaling,
 /* RateFree::optimizeWithEM, model/ratefree.cpp:450-578 */
 double PhyloTree::optimizeRateFreeEM(int copy_precision) {
     if (family != FAMILY_PLAIN && family != FAMILY_MIXRATE) throw std::runtime_error("optimizeRateFreeEM: a +R model (plain or fused mixture) is needed");
-    if (p_invar_ != 0.0) throw std::runtime_error("optimizeRateFreeEM: +I+R is not mirrored (the reference's E-step leaves ptn_invar out of the pattern likelihood)");
+    if (p_invar_ != 0.0) throw std::runtime_error("optimizeRateFreeEM: +I+R is not mirrored (no reference values: the reference's own EM asserts at the default +I+R start)");
     if (nunobs) throw std::runtime_error("optimizeRateFreeEM: the reference turns the EM off for +ASC (ratefree.cpp:211)");
     const int nmixc = ncat;
     const double MIN_PROP = 1e-4;
@@ -202,8 +202,8 @@ double PhyloTree::optimizeRateFreeEM(int copy_precision) {
         int ncol = collapsePatternLhCat(2);
         if (ncol != nmixc) throw std::runtime_error("optimizeRateFreeEM: unexpected column count");
         std::fill(new_prop.begin(), new_prop.end(), 0.0);
-        for (size_t d = 0; d < engines_.size(); d++) {       // E-step; ptn_invar is 0 here, so the mixture kernel's sum is the reference's
-            check(lkcuda_lh_cat_em(engines_[d], NULL, &part[0]), engines_[d], "lkcuda_lh_cat_em");
+        for (size_t d = 0; d < engines_.size(); d++) {       // E-step; the reference leaves ptn_invar out of lk_ptn, also for +I+R (RateFreeInvar)
+            check(lkcuda_lh_cat_em_ex(engines_[d], NULL, 0, &part[0]), engines_[d], "lkcuda_lh_cat_em_ex");
             for (int c = 0; c < nmixc; c++) new_prop[c] += part[c];
         }
         if (allreduce_) allreduce_(allreduce_user_, &new_prop[0], NULL, nmixc);

@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(AUX_THREADS) lhcat_collapse_kernel(DevView v, 
    Tiles of AUX_THREADS patterns are staged in shared memory; thread (seg, c) adds its segment of the tile in pattern order, thread c
    adds the segments in order: the result does not depend on scheduling. */
 #define EM_MAXCOL 96      /* a tile of 256 patterns x (ncol + 1) doubles must fit in shared memory; C60 and C20+G4 (80) do */
-__global__ void __launch_bounds__(AUX_THREADS) lhcat_em_kernel(DevView v, int ncol, double *w, const double *__restrict__ ratio, int use_ratio,
+__global__ void __launch_bounds__(AUX_THREADS) lhcat_em_kernel(DevView v, int ncol, double *w, const double *__restrict__ ratio, int use_ratio, int include_invar,
                                                                double *part, unsigned int *ticket, double *out) {
     extern __shared__ __align__(16) double shm[];
     double *tile = shm;                                   /* [AUX_THREADS][ncol + 1] */
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(AUX_THREADS) lhcat_em_kernel(DevView v, int nc
         }
         __syncthreads();
         if (threadIdx.x < np) {
-            double lk = v.invar[base + threadIdx.x];
+            double lk = include_invar ? v.invar[base + threadIdx.x] : 0.0;
             const double *row = tile + threadIdx.x * (ncol + 1);
             for (int c = 0; c < ncol; c++) lk += row[c];
             scale[threadIdx.x] = v.freq[base + threadIdx.x] / lk;
@@ -458,7 +458,9 @@ int lkcuda_lh_cat_posterior_weights(lkcuda_engine *e, int32_t col, int32_t inclu
     return LKCUDA_OK;
 }
 
-int lkcuda_lh_cat_em(lkcuda_engine *e, const double *ratio, double *sums) {
+int lkcuda_lh_cat_em(lkcuda_engine *e, const double *ratio, double *sums) { return lkcuda_lh_cat_em_ex(e, ratio, 1, sums); }
+
+int lkcuda_lh_cat_em_ex(lkcuda_engine *e, const double *ratio, int32_t include_invar, double *sums) {
     LK_ENTER(e);
     lkcuda_aux *a = e->aux;
     if (!a || !a->d_w || a->ncol < 1) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lh_cat_em: call lkcuda_lh_cat_collapse first");
@@ -484,7 +486,7 @@ int lkcuda_lh_cat_em(lkcuda_engine *e, const double *ratio, double *sums) {
     size_t sm = ((size_t)AUX_THREADS * (ncol + 1) + AUX_THREADS + AUX_THREADS + ncol) * 8;
     if (sm > 48 * 1024) LK_CUDA(e, cudaFuncSetAttribute(lhcat_em_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
     launch_begin(e, KIND_EM);
-    lhcat_em_kernel<<<grid, AUX_THREADS, sm, e->stream>>>(e->v, ncol, a->d_w, a->d_em_io + EM_MAXCOL, ratio ? 1 : 0, a->d_em_part, a->d_em_ticket, a->d_em_io);
+    lhcat_em_kernel<<<grid, AUX_THREADS, sm, e->stream>>>(e->v, ncol, a->d_w, a->d_em_io + EM_MAXCOL, ratio ? 1 : 0, include_invar ? 1 : 0, a->d_em_part, a->d_em_ticket, a->d_em_io);
     int rc = launch_end(e, KIND_EM, (uint64_t)v.P * ((uint64_t)ncol * (ratio ? 16 : 8) + 16), "lhcat_em_kernel");
     if (rc) return rc;
     LK_CUDA(e, cudaMemcpyAsync(a->h_em_io, a->d_em_io, (size_t)ncol * 8, cudaMemcpyDeviceToHost, e->stream));

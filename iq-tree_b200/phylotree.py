@@ -72,6 +72,7 @@ LKCUDA_SYMBOLS = {
     "lkcuda_lh_cat_collapse": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_int32_p]),
     "lkcuda_lh_cat_posterior_weights": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "lkcuda_lh_cat_em": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
+    "lkcuda_lh_cat_em_ex": (C.c_int, [C.c_void_p, c_double_p, C.c_int32, c_double_p]),
     "lkcuda_lh_cat_pattern_rates": (C.c_int, [C.c_void_p, c_double_p, C.c_int32, c_double_p, c_int32_p]),
     "lkcuda_fetch_lh_cat_collapsed": (C.c_int, [C.c_void_p, c_double_p]),
     "lkcuda_set_result_buffer": (C.c_int, [C.c_void_p, C.c_void_p]),

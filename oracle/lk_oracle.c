@@ -756,7 +756,9 @@ int lkcuda_lh_cat_collapse(lkcuda_engine *e, int32_t mode, int32_t ncat, int32_t
     }
     return LKCUDA_OK;
 }
-int lkcuda_lh_cat_em(lkcuda_engine *e, const double *ratio, double *sums) {
+int lkcuda_lh_cat_em_ex(lkcuda_engine *e, const double *ratio, int32_t include_invar, double *sums);
+int lkcuda_lh_cat_em(lkcuda_engine *e, const double *ratio, double *sums) { return lkcuda_lh_cat_em_ex(e, ratio, 1, sums); }
+int lkcuda_lh_cat_em_ex(lkcuda_engine *e, const double *ratio, int32_t include_invar, double *sums) {
     if (!e || !sums) return LKCUDA_ERR_ARG;
     if (!e->w || e->ncol < 1) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lh_cat_em: call lkcuda_lh_cat_collapse first");
     size_t P = (size_t)e->cfg.nptn, n = (size_t)e->ncol;
@@ -766,7 +768,7 @@ int lkcuda_lh_cat_em(lkcuda_engine *e, const double *ratio, double *sums) {
     memset(sums, 0, n * 8);
     for (size_t ptn = 0; ptn < P; ptn++) {       /* modelmixture.cpp:1379-1388 */
         const double *this_lk_cat = e->w + ptn * n;
-        double lk_ptn = e->ptn_invar[ptn];
+        double lk_ptn = include_invar ? e->ptn_invar[ptn] : 0.0;     /* ratefree.cpp:489 starts from 0 */
         for (size_t c = 0; c < n; c++) lk_ptn += this_lk_cat[c];
         lk_ptn = e->ptn_freq[ptn] / lk_ptn;
         for (size_t c = 0; c < n; c++) sums[c] += this_lk_cat[c] * lk_ptn;
