@@ -787,14 +787,21 @@ __global__ void __launch_bounds__(RED_THREADS) scale_factor_kernel(DevView v, in
 template <int MODE>
 __global__ void __launch_bounds__(RED_THREADS) sitemodel_reduce_kernel(DevView v, int dad, int node, double len) {
     __shared__ double sred[5 * 32];
-    const int lane = threadIdx.x & 31, ns = v.S;
-    const bool on = lane < ns;
+    const int wlane = threadIdx.x & 31, ns = v.S;
+    /* a warp holds 32 / SP patterns, SP = the state count rounded up to a power of two (DNA: 8 patterns of 4 lanes), as in the traversal kernel;
+       the butterfly sums stay inside a pattern's lanes and add the same values in the same order as a 32-lane one padded with zeros */
+    int SP = 1;
+    while (SP < ns) SP <<= 1;
+    const int gpw = 32 / SP, grp = wlane / SP, lane = wlane - grp * SP;
     const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
     const bool tip = (MODE <= 1) && LKCUDA_IS_TIP(dad);
     const double *lh_node = MODE <= 1 ? vec_lh(v, node) : NULL, *lh_dad = (MODE <= 1 && !tip) ? vec_lh(v, dad) : NULL;
     double acc4[4] = {0.0, 0.0, 0.0, 0.0}, acc5[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
     double theta_sc = 0.0;
-    for (long long p = warp0; p < v.NP; p += nwarps) {
+    for (long long base = warp0 * gpw; base < v.NP; base += nwarps * gpw) {
+        const bool live = base + grp < v.NP;
+        const long long p = live ? base + grp : v.NP - 1;       /* idle groups shadow the last pattern, write and add nothing */
+        const bool on = live && lane < ns;
         const long long m = v.ptn_model[p];
         const double ev = on ? v.eval[m * ns + lane] : 0.0;
         double t = 0.0;
@@ -812,16 +819,15 @@ __global__ void __launch_bounds__(RED_THREADS) sitemodel_reduce_kernel(DevView v
             if (MODE == 1) { if (on) v.theta[j] = th; continue; }
             const double cof = ev * v.blk_rate[c];
             double val = on ? exp(cof * len) * th : 0.0, val1 = cof * val, val2 = cof * val1;
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) {
+            for (int off = SP >> 1; off > 0; off >>= 1) {
                 val += __shfl_xor_sync(0xffffffffu, val, off);
                 if (MODE == 2) { val1 += __shfl_xor_sync(0xffffffffu, val1, off); val2 += __shfl_xor_sync(0xffffffffu, val2, off); }
             }
             const double prop = v.blk_weight[c];
-            if (MODE == 0 && lane == 0 && p < v.P) v.pattern_lh_cat[p * v.K + c] = val * prop;
+            if (MODE == 0 && lane == 0 && live && p < v.P) v.pattern_lh_cat[p * v.K + c] = val * prop;
             lh_ptn += val * prop; df_ptn += val1 * prop; ddf_ptn += val2 * prop;
         }
-        if (lane != 0) continue;
+        if (lane != 0 || !live) continue;
         if (MODE == 1) {
             const int sc = vec_sc(v, node)[p] + (tip ? 0 : vec_sc(v, dad)[p]);
             if (sc && p < v.P) theta_sc += LK_LOG_THR * v.freq[p] * (double)sc;
@@ -860,7 +866,9 @@ void lkc::preload_reduce_kernels() {
 static int sitemodel_reduce(lkcuda_engine *e, int mode, int dad, int node, double len) {
     const DevView &v = e->v;
     if (!v.ptn_model) return fail(e, LKCUDA_ERR_STATE, "site-specific model: lkcuda_set_site_models first");
-    long long need = (v.NP * 32 + RED_THREADS - 1) / RED_THREADS;
+    int sp = 1;
+    while (sp < v.S) sp <<= 1;
+    long long need = (v.NP * sp + RED_THREADS - 1) / RED_THREADS;       /* 32 / sp patterns per warp and step */
     long long cap = (long long)e->num_sms * 4 < e->red_blocks ? (long long)e->num_sms * 4 : e->red_blocks;
     int grid = (int)(need < 1 ? 1 : (need < cap ? need : cap));
     const uint64_t b = (uint64_t)v.B * 8, tipd = LKCUDA_IS_TIP(dad) ? 1 : 0;
