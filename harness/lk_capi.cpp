@@ -5,7 +5,7 @@
  * lktree_last_error().
  */
 #include "lk_phylotree.h"
-#include "../../include/lktree.h"
+#include "lktree.h"
 #include <cstring>
 #include <map>
 

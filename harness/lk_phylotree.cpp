@@ -253,6 +253,10 @@ std::string PhyloTree::getTreeString(int precision) const {
 
 void PhyloTree::setAlignment(int ntaxa_, int64_t nptn_, const uint8_t *states, const double *freq,
                              const std::vector<std::string> &names, int seq_type_, int nstates_, int state_unknown_) {
+    // computeTipPartialLikelihood fills the DNA ambiguity rows 4..17 and the protein rows 20..22 of a (state_unknown + 1)-row table
+    if (state_unknown_ < nstates_ || (seq_type_ == SEQ_DNA && nstates_ == 4 && state_unknown_ < 18) ||
+        (seq_type_ == SEQ_PROTEIN && nstates_ == 20 && state_unknown_ < 23))
+        throw std::runtime_error("setAlignment: state_unknown too small for this sequence type (DNA: 18, protein: 23; alignment.cpp:470-472)");
     deleteAllPartialLh();
     ntaxa = ntaxa_; nptn = nptn_; seq_type = seq_type_; nstates = nstates_; state_unknown = state_unknown_;
     states_.assign(states, states + (size_t)ntaxa * (size_t)nptn);
@@ -1106,7 +1110,10 @@ double PhyloTree::optimizeAllBranches(int my_iterations, double tolerance, int m
     for (int i = 0; i < my_iterations; i++) {
         std::vector<double> lenvec;
         saveBranchLengths(lenvec);
-        for (size_t j = 0; j < nodes.size(); j++) optimizeOneBranch(nodes[j], nodes2[j], true, maxNRStep);
+        // the reference calls optimizeOneBranch with its defaults here (clearLH = true, maxNRStep = 100) whatever maxNRStep the caller
+        // passed (phylotree.cpp:2252-2332; IQTree::optimizeNNI passes PLL_NEWZPERCYCLE = 10, iqtree.cpp:2215, without effect)
+        (void)maxNRStep;
+        for (size_t j = 0; j < nodes.size(); j++) optimizeOneBranch(nodes[j], nodes2[j], true, 100);
         double new_tree_lh = computeLikelihoodFromBuffer();
         if (new_tree_lh < tree_lh) {
             // IN RARE CASE: tree log-likelihood decreases, revert the branch length and stop

@@ -37,8 +37,8 @@
 #include <string>
 #include <vector>
 #include <stdexcept>
-#include "../../include/lkcuda.h"
-#include "../../include/lkpars.h"
+#include "../include/lkcuda.h"
+#include "../include/lkpars.h"
 
 namespace lk {
 

@@ -14,7 +14,7 @@
 
 #include <stddef.h>
 #include <stdint.h>
-#include "lkcuda.h"
+#include "../include/lkcuda.h"
 
 #ifdef __cplusplus
 extern "C" {

@@ -1,12 +1,16 @@
 """In-tree builds of the native libraries.
 
-* ``build_cuda()``   -> iq-tree_b200/lib/liblktree_cuda.so : the product (sm_100a kernels + C ABI of
-  include/lkcuda.h + the host PhyloTree mirror of include/lktree.h).  nvcc cross-compiles it without a GPU.
-* ``build_oracle()`` -> oracle/_build/liblktree_oracle.so  : TEST INFRASTRUCTURE.  The same host mirror linked
+* ``build_cuda()``   -> iq-tree_b200/lib/liblktree_cuda.so : THE PRODUCT: the sm_100a kernels behind the C ABI of
+  include/lkcuda.h and include/lkpars.h, nothing else.  nvcc cross-compiles it without a GPU.
+* ``build_harness()`` -> harness/_build/liblktree_harness.so : TEST / BENCH DRIVER.  harness/*.cpp is a stand-alone C++ mirror of the
+  reference's PhyloTree call sequences (flat C view: harness/lktree.h) so that tests and bench.py can drive the engine from
+  Python exactly as the reference would; linked against the product library.  The real binding is integration/.
+* ``build_oracle()`` -> oracle/_build/liblktree_oracle.so  : TEST INFRASTRUCTURE.  The same driver linked
   against the scalar C restatement oracle/lk_oracle.c instead of the CUDA engine; only tests/,
   __graft_entry__.smoke() and bench.py's cpu_baseline leg load it.
-* ``build_reference()`` -> oracle/_ref/ref_harness : the UNMODIFIED reference compiled from /root/reference by
-  oracle/Makefile.ref (only where /root/reference exists; the GPU box uses the prebuilt binary).
+* ``build_reference()`` -> oracle/_ref/ref_harness (+ ref_harness_cuda, ref_harness_oracle) : the UNMODIFIED reference compiled from
+  /root/reference by oracle/Makefile.ref, and the same sources with integration/ applied, linked against the product library
+  (only where /root/reference exists; the GPU box uses the prebuilt binaries).
 """
 import os
 import shutil
@@ -18,16 +22,20 @@ ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIBDIR = os.path.join(PKG, "lib")
 CUDA_LIB = os.path.join(LIBDIR, "liblktree_cuda.so")
+HARNESS_DIR = os.path.join(ROOT, "harness")
+HARNESS_LIB = os.path.join(HARNESS_DIR, "_build", "liblktree_harness.so")
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 ORACLE_LIB = os.path.join(ORACLE_DIR, "_build", "liblktree_oracle.so")
 REF_HARNESS = os.path.join(ORACLE_DIR, "_ref", "ref_harness")
+REF_HARNESS_CUDA = os.path.join(ORACLE_DIR, "_ref", "ref_harness_cuda")
 REFERENCE = "/root/reference"
 
-CUDA_SOURCES = ["lkcuda_engine.cu", "lkcuda_partial.cu", "lkcuda_partial_mma.cu", "lkcuda_partial_mmak.cu", "lkcuda_reduce.cu", "lkcuda_aux.cu", "lkcuda_sitemodel.cu", "lkcuda_pars.cu", "lk_phylotree.cpp", "lk_parsimony.cpp", "lk_rate_em.cpp", "lk_capi.cpp"]
+CUDA_SOURCES = ["lkcuda_engine.cu", "lkcuda_partial.cu", "lkcuda_partial_mma.cu", "lkcuda_partial_mmak.cu", "lkcuda_reduce.cu", "lkcuda_aux.cu", "lkcuda_sitemodel.cu", "lkcuda_pars.cu"]
 HOST_SOURCES = ["lk_phylotree.cpp", "lk_parsimony.cpp", "lk_rate_em.cpp", "lk_capi.cpp"]
 ORACLE_SOURCES = ["lk_oracle.c", "lkpars_oracle.c"]
-HEADERS = [os.path.join(CSRC, "lkcuda_common.cuh"), os.path.join(CSRC, "lkcuda_traverse.cuh"), os.path.join(CSRC, "lk_phylotree.h"),
-           os.path.join(ROOT, "include", "lkcuda.h"), os.path.join(ROOT, "include", "lktree.h"), os.path.join(ROOT, "include", "lkpars.h")]
+HEADERS = [os.path.join(CSRC, "lkcuda_common.cuh"), os.path.join(CSRC, "lkcuda_traverse.cuh"),
+           os.path.join(ROOT, "include", "lkcuda.h"), os.path.join(ROOT, "include", "lkpars.h")]
+HARNESS_HEADERS = HEADERS + [os.path.join(HARNESS_DIR, "lk_phylotree.h"), os.path.join(HARNESS_DIR, "lktree.h")]
 
 
 def _newer(target, sources):
@@ -72,10 +80,31 @@ def build_cuda(force=False, verbose=False):
     return CUDA_LIB
 
 
+def build_harness(force=False):
+    """TEST / BENCH DRIVER: the C++ mirror of the reference's PhyloTree call sequences, linked against the product library."""
+    cuda = build_cuda()
+    srcs = [os.path.join(HARNESS_DIR, s) for s in HOST_SOURCES]
+    if not force and not _newer(HARNESS_LIB, srcs + HARNESS_HEADERS + [cuda]):
+        return HARNESS_LIB
+    if shutil.which("g++") is None:
+        if os.path.exists(HARNESS_LIB):
+            return HARNESS_LIB
+        raise RuntimeError("g++ not found and %s is not built" % HARNESS_LIB)
+    bdir = os.path.dirname(HARNESS_LIB)
+    os.makedirs(bdir, exist_ok=True)
+    objs = []
+    for s in HOST_SOURCES:
+        o = os.path.join(bdir, s.replace(".cpp", ".o"))
+        _run(["g++", "-O2", "-fPIC", "-std=c++17", "-c", os.path.join(HARNESS_DIR, s), "-o", o])
+        objs.append(o)
+    _run(["g++", "-shared", "-o", HARNESS_LIB] + objs + ["-L" + LIBDIR, "-llktree_cuda", "-Wl,-rpath,$ORIGIN/../../iq-tree_b200/lib", "-lm"])
+    return HARNESS_LIB
+
+
 def build_oracle(force=False):
-    """TEST INFRASTRUCTURE: host mirror + scalar C oracle (no CUDA)."""
-    srcs = [os.path.join(CSRC, s) for s in HOST_SOURCES] + [os.path.join(ORACLE_DIR, s) for s in ORACLE_SOURCES]
-    if not force and not _newer(ORACLE_LIB, srcs + HEADERS):
+    """TEST INFRASTRUCTURE: harness mirror + scalar C oracle (no CUDA)."""
+    srcs = [os.path.join(HARNESS_DIR, s) for s in HOST_SOURCES] + [os.path.join(ORACLE_DIR, s) for s in ORACLE_SOURCES]
+    if not force and not _newer(ORACLE_LIB, srcs + HARNESS_HEADERS):
         return ORACLE_LIB
     if shutil.which("gcc") is None or shutil.which("g++") is None:
         if os.path.exists(ORACLE_LIB):
@@ -90,7 +119,7 @@ def build_oracle(force=False):
         objs.append(o)
     for s in HOST_SOURCES:
         o = os.path.join(bdir, s.replace(".cpp", ".o"))
-        _run(["g++", "-O2", "-fPIC", "-std=c++17", "-c", os.path.join(CSRC, s), "-o", o])
+        _run(["g++", "-O2", "-fPIC", "-std=c++17", "-c", os.path.join(HARNESS_DIR, s), "-o", o])
         objs.append(o)
     _run(["g++", "-shared", "-o", ORACLE_LIB] + objs + ["-lm"])
     return ORACLE_LIB
@@ -101,4 +130,7 @@ def build_reference(jobs=8):
     if not os.path.isdir(REFERENCE):
         return REF_HARNESS if os.path.exists(REF_HARNESS) else None
     _run(["make", "-f", os.path.join("oracle", "Makefile.ref"), "-j%d" % jobs], cwd=ROOT)
+    # the same sources with the reference-side binding (integration/) applied, linked against the product and the oracle libraries
+    build_cuda(); build_oracle()
+    _run(["make", "-f", os.path.join("oracle", "Makefile.ref"), "-j%d" % jobs, "cuda"], cwd=ROOT)
     return REF_HARNESS

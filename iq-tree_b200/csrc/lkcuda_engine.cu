@@ -14,7 +14,7 @@
 #include <chrono>
 #include <new>
 
-static char g_create_err[512] = "";
+static thread_local char g_create_err[512] = "";     /* engines are created concurrently from several host threads (phylosupertree.cpp:969-976) */
 
 namespace lkc {
 
@@ -342,10 +342,13 @@ int lkcuda_attach_arena(lkcuda_engine *e, void *partial_lh, int64_t vec_stride, 
     /* the kernels move whole 32-byte sectors: vectors must start on 32-byte boundaries */
     if (((uintptr_t)partial_lh & 31) || (v.B % 4 == 0 && vec_stride % 4 != 0) || ((uintptr_t)scale_num & 1))
         return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_arena: base must be 32-byte aligned and the stride a multiple of 4 doubles");
-    cudaPointerAttributes at;
-    if (cudaPointerGetAttributes(&at, partial_lh) != cudaSuccess || at.type != cudaMemoryTypeDevice || at.device != e->device) {
-        cudaGetLastError();
-        return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_arena: not device memory of device %d", e->device);
+    const void *both[2] = {partial_lh, scale_num};
+    for (int k = 0; k < 2; k++) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, both[k]) != cudaSuccess || at.type != cudaMemoryTypeDevice || at.device != e->device) {
+            cudaGetLastError();
+            return fail(e, LKCUDA_ERR_ARG, "lkcuda_attach_arena: %s is not device memory of device %d", k ? "scale_num" : "partial_lh", e->device);
+        }
     }
     LK_CUDA(e, cudaStreamSynchronize(e->stream));
     v.arena = (double *)partial_lh; v.scale = (int16_t *)scale_num;

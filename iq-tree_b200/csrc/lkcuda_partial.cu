@@ -769,31 +769,9 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
     return launch_end(e, KIND_PARTIAL, bytes, "traverse_s4_kernel");
 }
 
-extern "C" {
-
-int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t nops,
-                         const int32_t *level_start, int32_t nlevels) {
-    LK_ENTER(e);
-    if (nops < 0 || (nops && !ops)) return fail(e, LKCUDA_ERR_ARG, "bad op list");
-    if (!e->model_set || !e->states_set || !e->weights_set) return fail(e, LKCUDA_ERR_STATE, "lkcuda_partial_batch: tip states, pattern weights and model must be set first");
-    if (nops == 0) return LKCUDA_OK;
-    std::vector<int32_t> seq;
-    if (level_start) {
-        if (nlevels < 0 || level_start[0] != 0 || level_start[nlevels] != nops) return fail(e, LKCUDA_ERR_ARG, "bad level_start");
-        for (int l = 0; l < nlevels; l++) if (level_start[l] > level_start[l + 1]) return fail(e, LKCUDA_ERR_ARG, "bad level_start");
-    } else {
-        seq.resize(nops + 1);
-        for (int i = 0; i <= nops; i++) seq[i] = i;
-        level_start = &seq[0]; nlevels = nops;
-    }
-    for (int i = 0; i < nops; i++) {
-        const lkcuda_partial_op &op = ops[i];
-        if (op.dst < 0 || op.dst >= e->cfg.nvec || !valid_end(e, op.left) || !valid_end(e, op.right))
-            return fail(e, LKCUDA_ERR_ARG, "partial op %d: bad vector / taxon id", i);
-        if (!LKCUDA_IS_TIP(op.left) && LKCUDA_IS_TIP(op.right))
-            return fail(e, LKCUDA_ERR_ARG, "partial op %d: a leaf child must be 'left' (phylokernel.h:116-121)", i);
-        if (op.dst == op.left || op.dst == op.right) return fail(e, LKCUDA_ERR_ARG, "partial op %d: destination aliases a child", i);
-    }
+/* one hazard-free group of nodes: every vector is written at most once and never written after it was read */
+static int partial_batch_segment(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t nops,
+                                 const int32_t *level_start, int32_t nlevels) {
     const bool sitemodel = (e->v.flags & LKCUDA_FLAG_SITEMODEL) != 0;
     if (!sitemodel && use_traverse(e->v)) {
         e->theta_ready = false;
@@ -806,6 +784,34 @@ int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t
     if (!sitemodel && use_traverse_mmak(e)) {
         e->theta_ready = false;
         return launch_traverse_mmak(e, ops, nops);
+    }
+    /* level-batched kernels: without caller-supplied levels, level(op) = 1 + max level of the children produced in this group */
+    std::vector<lkcuda_partial_op> sorted;
+    std::vector<int32_t> starts;
+    if (!level_start && !sitemodel) {
+        std::vector<int> producer(e->cfg.nvec, -1), lvl(nops, 1);
+        int maxlevel = 1;
+        for (int i = 0; i < nops; i++) {
+            const int a = ops[i].left >= 0 ? producer[ops[i].left] : -1, b = ops[i].right >= 0 ? producer[ops[i].right] : -1;
+            if (a >= 0 && lvl[a] + 1 > lvl[i]) lvl[i] = lvl[a] + 1;
+            if (b >= 0 && lvl[b] + 1 > lvl[i]) lvl[i] = lvl[b] + 1;
+            if (lvl[i] > maxlevel) maxlevel = lvl[i];
+            producer[ops[i].dst] = i;
+        }
+        starts.assign(maxlevel + 1, 0);
+        for (int i = 0; i < nops; i++) starts[lvl[i]]++;
+        int32_t acc = 0;
+        for (int l = 1; l <= maxlevel; l++) { const int32_t c = starts[l]; starts[l] = acc; acc += c; }
+        std::vector<int32_t> cursor(starts);
+        sorted.resize(nops);
+        for (int i = 0; i < nops; i++) sorted[cursor[lvl[i]]++] = ops[i];       /* stable inside a level */
+        for (int l = 1; l <= maxlevel; l++) starts[l - 1] = starts[l];
+        starts[maxlevel] = nops;
+        ops = &sorted[0]; level_start = &starts[0]; nlevels = maxlevel;
+    } else if (!level_start) {
+        starts.resize(nops + 1);
+        for (int i = 0; i <= nops; i++) starts[i] = i;
+        level_start = &starts[0]; nlevels = nops;
     }
     int slot;
     int rc = ring_acquire(e, nops, 2 * nops, &slot);
@@ -825,6 +831,56 @@ int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t
     e->theta_ready = false;
     if (sitemodel) return launch_traverse_sitemodel(e, slot, nops);
     return launch_ops(e, slot, nops, 2 * nops, level_start, nlevels, &lbytes[0]);
+}
+
+extern "C" {
+
+int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t nops,
+                         const int32_t *level_start, int32_t nlevels) {
+    LK_ENTER(e);
+    if (nops < 0 || (nops && !ops)) return fail(e, LKCUDA_ERR_ARG, "bad op list");
+    if (!e->model_set || !e->states_set || !e->weights_set) return fail(e, LKCUDA_ERR_STATE, "lkcuda_partial_batch: tip states, pattern weights and model must be set first");
+    if (nops == 0) return LKCUDA_OK;
+    if (level_start) {
+        if (nlevels < 0 || level_start[0] != 0 || level_start[nlevels] != nops) return fail(e, LKCUDA_ERR_ARG, "bad level_start");
+        for (int l = 0; l < nlevels; l++) if (level_start[l] > level_start[l + 1]) return fail(e, LKCUDA_ERR_ARG, "bad level_start");
+    }
+    for (int i = 0; i < nops; i++) {
+        const lkcuda_partial_op &op = ops[i];
+        if (op.dst < 0 || op.dst >= e->cfg.nvec || !valid_end(e, op.left) || !valid_end(e, op.right))
+            return fail(e, LKCUDA_ERR_ARG, "partial op %d: bad vector / taxon id", i);
+        if (!LKCUDA_IS_TIP(op.left) && LKCUDA_IS_TIP(op.right))
+            return fail(e, LKCUDA_ERR_ARG, "partial op %d: a leaf child must be 'left' (phylokernel.h:116-121)", i);
+        if (op.dst == op.left || op.dst == op.right) return fail(e, LKCUDA_ERR_ARG, "partial op %d: destination aliases a child", i);
+    }
+    /* A vector may be the destination of several ops of one list: under the reference's default LM_PER_NODE buffer mode a node's single
+       vector is re-oriented on demand (phylonode.cpp:22-39, phylokernel.h:127-143), so a later op may overwrite what an earlier op of
+       the same list wrote or read.  With the ops in EXECUTION order (level_start == NULL) the list is cut at every write-after-write /
+       write-after-read hazard and the pieces run back to back; a caller-supplied level grouping has no defined order across such a
+       hazard and is refused. */
+    std::vector<unsigned char> mark(e->cfg.nvec, 0);        /* 1 = written, 2 = read in the current piece */
+    int begin = 0;
+    for (int i = 0; i <= nops; i++) {
+        const bool cut = i == nops || mark[ops[i].dst] != 0;
+        if (cut) {
+            if (i < nops && level_start) return fail(e, LKCUDA_ERR_ARG, "partial op %d overwrites a vector an earlier op of the list wrote or read: pass the ops in execution order with level_start = NULL", i);
+            if (i > begin) {
+                int rc = level_start ? partial_batch_segment(e, ops, nops, level_start, nlevels) : partial_batch_segment(e, ops + begin, i - begin, NULL, 0);
+                if (rc) return rc;
+            }
+            if (i == nops) break;
+            for (int j = begin; j < i; j++) {
+                mark[ops[j].dst] = 0;
+                if (ops[j].left >= 0) mark[ops[j].left] = 0;
+                if (ops[j].right >= 0) mark[ops[j].right] = 0;
+            }
+            begin = i;
+        }
+        mark[ops[i].dst] |= 1;
+        if (ops[i].left >= 0) mark[ops[i].left] |= 2;
+        if (ops[i].right >= 0) mark[ops[i].right] |= 2;
+    }
+    return LKCUDA_OK;
 }
 
 int lkcuda_partial_multi(lkcuda_engine *e, int32_t dst, int32_t nchild, const int32_t *child, const double *child_len) {

@@ -183,9 +183,11 @@ _libs = {}
 
 
 def load_library(path=None):
-    """Load (building first if sources are newer) the CUDA product library.  Never falls back to a CPU library."""
+    """Load (building first if sources are newer) the CUDA product library through the harness library that drives it
+    (harness/: the PhyloTree mirror used by tests and bench.py; it links iq-tree_b200/lib/liblktree_cuda.so).  Never falls back to a
+    CPU library."""
     if path is None:
-        path = _build.build_cuda()
+        path = _build.build_harness()
     path = os.path.abspath(path)
     if path not in _libs:
         if not os.path.exists(path):

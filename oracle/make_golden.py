@@ -292,16 +292,11 @@ def pack_aux(case, d):
         case, m["lnl"], z["rell"][0], m["nrate_cat"], m["has_em"], m["em_lnl"], os.path.getsize(path) / 1024))
 
 
-def main():
-    if not os.path.exists(HARNESS):
-        raise SystemExit("build the reference first: make -f oracle/Makefile.ref -j8")
-    tmp = tempfile.mkdtemp(prefix="lk_golden_")
-    ex = os.path.join(tmp, "example.phy")
-    shutil.copy(os.path.join(REF, "example", "example.phy"), ex)
+def build_cases(tmp, ex, prot):
+    """harness arguments of every golden case; `ex` / `prot` are the two alignments that come from the reference's example
+    directories (the tests rebuild them from the fixtures), everything else is generated here with fixed seeds"""
     ex_tree = os.path.join(tmp, "example.nwk")
     open(ex_tree, "w").write(EXAMPLE_TREE + "\n")
-    prot = os.path.join(tmp, "prot.phy")
-    shutil.copy(os.path.join(REF, "test_scripts", "test_data", "prot_M126_27_269.phy"), prot)
     prot_tree = random_tree_file(tmp, read_phylip_names(prot), 3, "prot", mean_len=0.15)
     deep_aln, deep_tree = synth_dna(tmp, 320, 90, 11, "deep", mean_len=0.35)
     cod_aln, cod_tree = synth_codon(tmp, 8, 60, 5, "codon")
@@ -314,7 +309,7 @@ def main():
     ex_fs = site_freq_file(tmp, 384, 4, 31, "exfs")
     prot_fs = site_freq_file(tmp, 269, 20, 32, "protfs")
     deep_fs = site_freq_file(tmp, 90, 4, 33, "deepfs")
-    cases = {
+    return {
         "dna_sitefreq_gtr_g4": ["-s", ex, "-m", "GTR+G4", "-fs", ex_fs, "-te", ex_tree],
         "dna_sitefreq_deep_scaling": ["-s", deep_aln, "-m", "HKY+G4", "-fs", deep_fs, "-te", deep_tree],
         "aa_sitefreq_lg_g4": ["-s", prot, "-m", "LG+G4", "-fs", prot_fs, "-te", prot_tree],
@@ -338,6 +333,17 @@ def main():
         "morph_mk_asc": ["-s", asc_aln, "-st", "MORPH", "-m", "MK+ASC", "-te", asc_tree],
         "bin_jc2_g4": ["-s", bin_aln, "-st", "BIN", "-m", "JC2+G4", "-te", bin_tree],
     }
+
+
+def main():
+    if not os.path.exists(HARNESS):
+        raise SystemExit("build the reference first: make -f oracle/Makefile.ref -j8")
+    tmp = tempfile.mkdtemp(prefix="lk_golden_")
+    ex = os.path.join(tmp, "example.phy")
+    shutil.copy(os.path.join(REF, "example", "example.phy"), ex)
+    prot = os.path.join(tmp, "prot.phy")
+    shutil.copy(os.path.join(REF, "test_scripts", "test_data", "prot_M126_27_269.phy"), prot)
+    cases = build_cases(tmp, ex, prot)
     if sys.argv[1:2] == ["--nni"]:
         for case, nni5 in NNI_CASES:
             d = os.path.join(tmp, "outn_" + case)

@@ -69,6 +69,22 @@ static void wbin(const std::string &name, const void *p, size_t bytes) {
     fclose(f);
 }
 
+/* With -DLK_CUDA_SHIM this file is compiled against the patched reference (integration/): under `-cuda` the likelihood buffers live on
+   the device and are fetched through the shim's accessors; without it the helpers below read the reference's host buffers directly. */
+#ifdef LK_CUDA_SHIM
+#define ON_DEVICE(tree) ((tree)->lk_cuda != NULL)
+#else
+#define ON_DEVICE(tree) false
+#endif
+
+static void syncPatternLh(IQTree *tree) {
+#ifdef LK_CUDA_SHIM
+    tree->lkCudaSyncPatternLh();
+#else
+    (void)tree;
+#endif
+}
+
 static void collectNodes(Node *node, Node *dad, std::vector<Node*> &out) {
     out.push_back(node);
     FOR_NEIGHBOR_IT(node, dad, it) collectNodes((*it)->node, node, out);
@@ -103,9 +119,22 @@ static void dumpPartials(IQTree *tree, Node *node, Node *dad, std::ofstream &idx
             if ((b->partial_lh_computed & 1) && b->partial_lh && !b->node->isLeaf()) {
                 std::ostringstream nm;
                 nm << "partial_" << from[k]->id << "_" << b->node->id;
+                double factor = b->lh_scale_factor;
+#ifdef LK_CUDA_SHIM
+                if (ON_DEVICE(tree)) {
+                    std::vector<double> lh(nptn * block);
+                    std::vector<UBYTE> sc(nptn);
+                    tree->lkCudaFetchVector(b, &lh[0], &sc[0]);
+                    factor = tree->lkCudaScaleFactor(b);
+                    wbin(nm.str() + ".f64", &lh[0], nptn * block * sizeof(double));
+                    wbin(nm.str() + ".i16", &sc[0], nptn * sizeof(UBYTE));
+                } else
+#endif
+                {
                 wbin(nm.str() + ".f64", b->partial_lh, nptn * block * sizeof(double));
                 wbin(nm.str() + ".i16", b->scale_num, nptn * sizeof(UBYTE));
-                idx << from[k]->id << " " << b->node->id << " " << std::setprecision(17) << b->lh_scale_factor << "\n";
+                }
+                idx << from[k]->id << " " << b->node->id << " " << std::setprecision(17) << factor << "\n";
             }
         }
         dumpPartials(tree, (*it)->node, node, idx, nptn, block);
@@ -223,6 +252,7 @@ static int do_dump(int argc, char **argv) {
     else wbin("tip_partial_lh.f64", tree->tip_partial_lh, (aln->STATE_UNKNOWN + 1) * S * E * sizeof(double));
     wbin("ptn_freq.f64", tree->ptn_freq, P * 8);
     wbin("ptn_invar.f64", tree->ptn_invar, nptn * 8);
+    syncPatternLh(tree);
     wbin("pattern_lh.f64", tree->_pattern_lh, P * 8);
     int root_from = tree->current_it_back->node->id, root_to = tree->current_it->node->id;
     {
@@ -254,6 +284,13 @@ static int do_dump(int argc, char **argv) {
     double df, ddf;
     tree->theta_computed = false;
     tree->computeLikelihoodDerv((PhyloNeighbor*)n1->findNeighbor(n2), n1, df, ddf);
+#ifdef LK_CUDA_SHIM
+    if (ON_DEVICE(tree)) {
+        std::vector<double> th(nptn * block);
+        tree->lkCudaFetchTheta(&th[0]);
+        wbin("theta_root.f64", &th[0], nptn * block * 8);
+    } else
+#endif
     wbin("theta_root.f64", tree->theta_all, nptn * block * 8);
     NodeVector nodes, nodes2;
     tree->computeBestTraversal(nodes, nodes2);
@@ -296,7 +333,8 @@ static int do_dump(int argc, char **argv) {
           << " \"lnl\": " << lnl << ", \"df_root\": " << df << ", \"ddf_root\": " << ddf << ",\n"
           << " \"derv_branch\": [" << n1->id << ", " << n2->id << "],\n"
           << " \"oab1_lnl\": " << oab1 << ", \"oabfull_lnl\": " << oabfull << ",\n"
-          << " \"kernel\": \"" << (tree->sse == LK_EIGEN_SSE ? (instruction_set >= 7 ? "AVX" : "SSE") : "generic") << "\",\n"
+          << " \"kernel\": \"" << (ON_DEVICE(tree) ? "cuda" : (tree->sse == LK_EIGEN_SSE ? (instruction_set >= 7 ? "AVX" : "SSE") : "generic")) << "\",\n"
+          << " \"lh_mem_save\": " << (int)params.lh_mem_save << ",\n"
           << " \"threads\": " << params.num_threads << "\n}\n";
     }
     printf("lnl %.10f df %.10g ddf %.10g oab1 %.10f oabfull %.10f\n", lnl, df, ddf, oab1, oabfull);
@@ -603,13 +641,17 @@ static int do_time(int argc, char **argv) {
            "\"lnl\": %.12f, \"lnl_reps\": %d, \"lnl_s_mean\": %.6g, \"lnl_s_best\": %.6g, \"step_s_mean\": %.6g, \"step_s_total\": %.6g, "
            "\"df\": %.12g, \"ddf\": %.12g, \"derv_reps\": %d, \"derv_s_mean\": %.6g, "
            "\"oab_lnl\": %.12f, \"oab_reps\": %d, \"oab_s_mean\": %.6g, \"nni_branches\": %d, \"nni_s_mean\": %.6g, \"setup_s\": %.4g}\n",
-           tree->sse == LK_EIGEN_SSE ? (instruction_set >= 7 ? "AVX" : "SSE") : "generic",
+           ON_DEVICE(tree) ? "cuda" : (tree->sse == LK_EIGEN_SSE ? (instruction_set >= 7 ? "AVX" : "SSE") : "generic"),
            params.num_threads, P, ntaxa, blocks, lnl, lnl_reps, mean, lnl_t.empty() ? 0.0 : best, step_mean, step_sum,
            df, ddf, derv_reps, t_derv, oab, oab_reps, t_oab, nni_done, t_nni, t_setup);
     return 0;
 }
 
+int iqtree_main(int argc, char *argv[]);     /* the reference's own main() (pda.cpp compiled with -Dmain=iqtree_main) */
+
 int main(int argc, char **argv) {
+    /* ref_harness iqtree <iqtree args>: the complete IQ-TREE command line (tree search, ModelFinder, ...) of the unmodified reference */
+    if (argc >= 2 && !strcmp(argv[1], "iqtree")) { argv[1] = argv[0]; return iqtree_main(argc - 1, argv + 1); }
     if (argc >= 4 && !strcmp(argv[1], "dump")) return do_dump(argc, argv);
     if (argc >= 6 && !strcmp(argv[1], "time")) return do_time(argc, argv);
     if (argc >= 5 && !strcmp(argv[1], "dumpx")) return do_dumpx(argc, argv);
