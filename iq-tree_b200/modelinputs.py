@@ -124,6 +124,24 @@ def simulate_patterns(newick, names, nptn, nstates, seed, gamma_shape=0.5):
     return out
 
 
+def simulate_distinct_patterns(newick, names, nptn, nstates, seed, gamma_shape=0.5):
+    """nptn DISTINCT columns in first-occurrence order: what Alignment::addPattern (alignment.cpp:674-700) turns into exactly nptn
+    patterns of frequency 1, pattern p = column p.  The reference then compresses nothing away, and a GPU run that treats every column
+    as one pattern evaluates the very same alignment."""
+    T = len(names)
+    cols = np.zeros((0, T), dtype=np.uint8)
+    k = 0
+    while cols.shape[0] < nptn:
+        need = nptn - cols.shape[0]
+        more = simulate_patterns(newick, names, int(need * 1.6) + 64, nstates, seed + 1000 * k, gamma_shape).T
+        cols = np.ascontiguousarray(np.concatenate([cols, more], axis=0))
+        key = cols.view(np.dtype((np.void, T))).ravel()
+        _, first = np.unique(key, return_index=True)
+        cols = cols[np.sort(first)]
+        k += 1
+    return np.ascontiguousarray(cols[:nptn].T)
+
+
 def gtr_g4_inputs(seed=1, alpha=0.7, ncat=4):
     """A fixed, seeded GTR+G4 parameter set (not fitted to anything): dict ready for PhyloTree.setModel."""
     rng = np.random.default_rng(seed)
