@@ -3,9 +3,9 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
-Workload (config.workload): BASELINE.json configs[1] — synthetic DNA, 100 taxa x 1,000,000 patterns, GTR+G4,
-patterns sharded over the N ranks (strong scaling, one process per GPU under torchrun; only the scalar
-lnL/df/ddf sums cross NVLink in one NCCL all-reduce per evaluation).
+Workload (config.workload): BASELINE.json configs[1] — synthetic DNA, 100 taxa x 1,000,000 DISTINCT patterns, GTR+G4, patterns sharded
+over the N ranks (strong scaling, one process per GPU under torchrun; only the scalar lnL/df/ddf sums cross NVLink).  The patterns are
+distinct columns in first-occurrence order, so the reference (which compresses identical columns) sees exactly the same 1M patterns.
 
 One STEP = one pass of the hot path over the whole alignment:
     clearAllPartialLH + computeLikelihood()            every internal node's partial-likelihood vector + branch lnL
@@ -15,13 +15,23 @@ value   = inputs resident in HBM, device-timed (CUDA events, max over ranks)
 e2e     = the same step through the C ABI with HOST buffers: the tip-state matrix goes up from pinned host memory
           (lkcuda_set_tip_states_async: chunked on a copy stream, overlapped with the traversal kernel), per-pattern
           log-likelihoods and the sums come back, all inside the timed region
-roofline= the partial-likelihood level kernel (dominant): algorithmic bytes / CUDA-event time
-cpu_baseline = the UNMODIFIED reference (oracle/_ref/ref_harness, AVX + OpenMP, all host cores) on a bounded sample
+roofline= the dominant kernel (whole-traversal kernel): DRAM traffic the kernel is designed to move / CUDA-event time, against the
+          measured HBM peak; the SURVEY 8d algorithmic-byte ratio is kept beside it (frac_algorithmic)
+At N = 1 the line also carries
+cpu_baseline  the UNMODIFIED reference (oracle/_ref/ref_harness, AVX + OpenMP, all host cores) on the SAME alignment file, full size
+dropin        the reference's OWN computeLikelihood / computeLikelihoodDerv / optimizeAllBranches running on the engine
+              (oracle/_ref/ref_harness_cuda = the reference sources + integration/, option -cuda) on that file
+parity        lnL / df / ddf of `dropin` against `cpu_baseline`: same alignment, tree and model; the run FAILS when lnL differs by > 1e-9 rel
+configs       BASELINE configs 3-5 (protein 200 x 200k LG+G4, codon 64 x 50k GY and MG+G4, LG+C20+G4 100 x 10k, 50-partition DNA+protein
+              PartitionModel): reference on the host cores and reference-on-engine on the same files, device time per kernel kind, real
+              flops by node case against the FP64 peak measured in this run (tools/fp64_peak), lnL parity
+With --impl reference: the reference's CPU kernels on the full workload (rank 0 only).
 """
 import argparse
 import ctypes
 import json
 import os
+import shutil
 import subprocess
 import sys
 import tempfile
@@ -38,17 +48,24 @@ NPTN = int(os.environ.get("LK_BENCH_PATTERNS", 1000000))
 NCAT = 4
 SEED = 1
 UPLOAD_CHUNKS = int(os.environ.get("LK_BENCH_UPLOAD_CHUNKS", 0))     # 0 = about 2 MB per chunk, 2..16 chunks
-CPU_SAMPLE_SITES = int(os.environ.get("LK_BENCH_CPU_SITES", 200000))
+WITH_CONFIGS = int(os.environ.get("LK_BENCH_CONFIGS", 1))            # BASELINE configs 3-5 beside the headline (N = 1)
+WITH_DROPIN = int(os.environ.get("LK_BENCH_DROPIN", 1))
+CPU_STEPS = int(os.environ.get("LK_BENCH_CPU_STEPS", 4))
 WORKLOAD = "synthetic DNA %d taxa x %d patterns, GTR+G4 (BASELINE configs[1])" % (NTAXA, NPTN)
+METRIC = "partial-LH updates/s (patterns x cats x nodes)"
+HARNESS_REF = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
+HARNESS_CUDA = os.path.join(ROOT, "oracle", "_ref", "ref_harness_cuda")
+AA = "ARNDCQEGHILKMFPSTWYV"
+SENSE = [a + b + c for a in "ACGT" for b in "ACGT" for c in "ACGT" if a + b + c not in ("TAA", "TAG", "TGA")]
 
 
-def make_inputs(nptn):
+def make_inputs(nptn, ntaxa=None, nstates=4, seed=SEED):
     from iqtree_b200 import modelinputs as mi
-    names = ["t%d" % i for i in range(NTAXA)]
-    nwk = mi.random_tree_newick(NTAXA, SEED, names)
-    states = mi.simulate_patterns(nwk, names, nptn, 4, SEED)
-    model = mi.gtr_g4_inputs(SEED, ncat=NCAT)
-    return names, nwk, states, model
+    ntaxa = ntaxa or NTAXA
+    names = ["t%d" % i for i in range(ntaxa)]
+    nwk = mi.random_tree_newick(ntaxa, SEED, names)
+    states = mi.simulate_distinct_patterns(nwk, names, nptn, nstates, seed)
+    return names, nwk, states
 
 
 class ClockSampler(threading.Thread):
@@ -105,68 +122,61 @@ def measured_hbm_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def write_sample_files(tmp, names, nwk, states, nsites):
-    lut = np.array(list("ACGT"))
-    aln = os.path.join(tmp, "sample.phy")
-    with open(aln, "w") as f:
-        f.write("%d %d\n" % (len(names), nsites))
+def measured_fp64_peak():
+    """FP64 denominators measured on THIS box in THIS run: tools/fp64_peak (DFMA loop, mma.sync DMMA loop; built by __graft_entry__.build())"""
+    exe = os.path.join(ROOT, "tools", "fp64_peak")
+    if not os.path.exists(exe):
+        return None
+    try:
+        r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=120)
+        for line in r.stdout.split("\n"):
+            if line.startswith("{"):
+                return json.loads(line)
+    except Exception:
+        pass
+    return None
+
+
+# ------------------------------------------------------------------ files for the reference binaries ------------------------------------------------------------------
+
+def write_phylip(path, names, states, alphabet):
+    if isinstance(alphabet, str):
+        lut = np.frombuffer(alphabet.encode(), dtype=np.uint8)
+        width = 1
+    else:
+        lut = np.array([s.encode() for s in alphabet], dtype="S%d" % len(alphabet[0]))
+        width = len(alphabet[0])
+    with open(path, "wb") as f:
+        f.write(b"%d %d\n" % (len(names), states.shape[1] * width))
         for i, n in enumerate(names):
-            f.write("%s  %s\n" % (n, "".join(lut[states[i, :nsites]])))
-    tre = os.path.join(tmp, "sample.nwk")
-    open(tre, "w").write(nwk + "\n")
-    return aln, tre
+            f.write(n.encode() + b"  " + lut[states[i]].tobytes() + b"\n")
 
 
-def run_reference(names, nwk, states, steps, warmup, threads=None):
-    """time the unmodified reference's CPU kernels on a bounded sample (oracle/_ref/ref_harness time ...)"""
-    harness = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
-    if not os.path.exists(harness):
+def run_harness(exe, args, reps, oab_reps=0, warmup=0, threads=None, cuda=False, cwd=None):
+    """`ref_harness[_cuda] time`: the reference's own loop of clearAllPartialLH + computeLikelihood (+ theta / df / ddf, + optimizeAllBranches(1))"""
+    if not os.path.exists(exe):
         return None
     threads = threads or os.cpu_count() or 1
-    nsites = min(CPU_SAMPLE_SITES, states.shape[1])
-    tmp = tempfile.mkdtemp(prefix="lk_ref_")
-    aln, tre = write_sample_files(tmp, names, nwk, states, nsites)
-    cmd = [harness, "time", str(max(1, steps)), "0", "0", "-s", aln, "-m", "GTR+G4", "-te", tre, "-nt", str(threads), "-seed", "1",
-           "-pre", os.path.join(tmp, "ref")]
+    cmd = [exe, "time", str(max(1, reps + warmup)), "0", str(oab_reps)] + args + ["-nt", str(threads), "-seed", "1", "-pre", os.path.join(cwd, "run_%d" % int(cuda))]
+    if cuda:
+        cmd.append("-cuda")
+    env = dict(os.environ, LK_REF_WARMUP=str(warmup))
     t0 = time.time()
-    r = subprocess.run(cmd, cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    r = subprocess.run(cmd, cwd=cwd, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     wall = time.time() - t0
     out = None
     for line in r.stdout.split("\n"):
         if line.startswith('{"ref_time"'):
             out = json.loads(line)
     if out is None:
-        sys.stderr.write(r.stdout[-2000:])
+        sys.stderr.write("%s failed:\n%s\n" % (" ".join(cmd[:6]), r.stdout[-2000:]))
         return None
     out["wall_s"] = wall
-    out["sample"] = "%d taxa x %d sites -> %d patterns, GTR+G4, %d timed steps (lnL + theta + df/ddf)" % (
-        NTAXA, nsites, out["nptn"], out["lnl_reps"])
-    out["updates_per_s"] = (NTAXA - 2) * out["nptn"] * NCAT / out["step_s_mean"]
     return out
 
 
-def reference_arm(args):
-    rank = int(os.environ.get("RANK", 0))
-    if rank != 0:
-        return 0
-    names, nwk, states, _ = make_inputs(min(CPU_SAMPLE_SITES, NPTN))
-    ref = run_reference(names, nwk, states, args.steps + args.warmup, 0)
-    if ref is None:
-        emit({"impl": "reference", "unavailable": "oracle/_ref/ref_harness missing or failed"})
-        return 0
-    v = ref["updates_per_s"]
-    line = {
-        "impl": "reference", "metric": "partial-LH updates/s (patterns x cats x nodes)", "value": v, "unit": "updates/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ref["step_s_mean"] * 1e3,
-        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": ref["sample"], "kernel": "reference %s + OpenMP" % ref["kernel"]},
-        "lnl_evals_per_s": 1.0 / ref["lnl_s_mean"],
-        "cpu_baseline": {"value": v, "unit": "updates/s", "cores": ref["threads"], "kind": "reference", "sample": ref["sample"]},
-        "e2e": {"value": v, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
-    }
-    emit(line)
-    return 0
+def rel(a, b):
+    return abs(a - b) / max(abs(b), 1e-300)
 
 
 _REAL_STDOUT = None
@@ -189,6 +199,155 @@ def emit(line):
         os.write(_REAL_STDOUT, data)
 
 
+def headline_files(tmp, names, nwk, states):
+    aln, tre = os.path.join(tmp, "dna.phy"), os.path.join(tmp, "dna.nwk")
+    write_phylip(aln, names, states, "ACGT")
+    open(tre, "w").write(nwk + "\n")
+    return ["-s", aln, "-m", "GTR+G4", "-te", tre]
+
+
+def reference_arm(args):
+    """the reference's CPU kernels (AVX + OpenMP, all host cores) on the full workload; rank 0 only"""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return 0
+    names, nwk, states = make_inputs(NPTN)
+    tmp = tempfile.mkdtemp(prefix="lk_ref_")
+    try:
+        ref = run_harness(HARNESS_REF, headline_files(tmp, names, nwk, states), args.steps, warmup=args.warmup, cwd=tmp)
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    if ref is None:
+        emit({"impl": "reference", "unavailable": "oracle/_ref/ref_harness missing or failed"})
+        return 0
+    v = (NTAXA - 2) * ref["nptn"] * NCAT / ref["step_s_mean"]
+    sample = "the full workload: %d taxa x %d patterns, GTR+G4, %d timed steps after %d warm-up (lnL + theta + df/ddf per step)" % (
+        NTAXA, ref["nptn"], ref["lnl_reps"], args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "updates/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ref["step_s_mean"] * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "ntaxa": NTAXA, "patterns": ref["nptn"], "ncat": NCAT,
+                   "kernel": "reference %s + OpenMP, LM_PER_NODE buffers" % ref["kernel"]},
+        "lnl_evals_per_s": 1.0 / ref["lnl_s_mean"], "lnl": ref["lnl"], "df": ref["df"], "ddf": ref["ddf"],
+        "cpu_baseline": {"value": v, "unit": "updates/s", "cores": ref["threads"], "kind": "reference", "sample": sample},
+        "e2e": {"value": v, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    emit(line)
+    return 0
+
+
+# ------------------------------------------------------------------ BASELINE configs 3-5 ------------------------------------------------------------------
+
+def config_list():
+    return [
+        dict(name="protein 200 taxa x 200k patterns, LG+G4", key="protein_lg_g4", ntaxa=200, nptn=200000, S=20, blocks=4, alphabet=AA, margs=["-m", "LG+G4"], reps=2, bound="fp64"),
+        dict(name="codon 64 taxa x 50k patterns, GY (64-state layout)", key="codon_gy", ntaxa=64, nptn=50000, S=61, blocks=1, alphabet=SENSE, margs=["-st", "CODON", "-m", "GY"], reps=3, bound="fp64"),
+        dict(name="codon 64 taxa x 50k patterns, MG+G4", key="codon_mg_g4", ntaxa=64, nptn=50000, S=61, blocks=4, alphabet=SENSE, margs=["-st", "CODON", "-m", "MG+G4"], reps=2, bound="fp64"),
+        dict(name="protein mixture 100 taxa x 10k patterns, LG+C20+G4", key="lg_c20_g4", ntaxa=100, nptn=10000, S=20, blocks=80, alphabet=AA, margs=["-m", "LG+C20+G4"], reps=2, bound="fp64"),
+    ]
+
+
+def kernel_summary(res, fp64):
+    """device time per lnL evaluation from the per-kind CUDA-event statistics of a `ref_harness_cuda time` run"""
+    k = res.get("kernels") or {}
+    reps = max(res.get("lnl_reps", 1), 1)
+    out = {}
+    lnl_ms = 0.0
+    for kind in ("prep", "partial", "branch", "misc"):
+        if kind in k:
+            lnl_ms += k[kind]["device_ms"] / reps
+    out["device_ms_per_lnl_eval"] = lnl_ms
+    out["kernels"] = {kk: {"launches_per_step": v["launches"] / reps, "device_ms_per_step": v["device_ms"] / reps,
+                           "algorithmic_gb_per_step": v["bytes"] / reps / 1e9} for kk, v in k.items()}
+    if "partial" in k and k["partial"]["device_ms"] > 0:
+        p = k["partial"]
+        tf = p["flops"] / (p["device_ms"] * 1e-3) / 1e12
+        out["partial_tflops"] = tf
+        out["partial_flops_per_eval"] = p["flops"] / reps
+        if fp64:
+            peak = fp64.get("dmma_m8n8k4_tflops")
+            out["roofline"] = {"bound": "fp64 tensor (mma.sync DMMA)", "achieved": tf, "peak": peak, "unit": "TFLOP/s",
+                               "frac": tf / peak if peak else None, "peak_source": "tools/fp64_peak DMMA m8n8k4 loop, this run",
+                               "flops": "real flops by node case from the op list (2S^2 per internal child + 2S^2 back to state space + S per product)"}
+    return out
+
+
+def run_config(cfg, tmp, fp64):
+    names, nwk, states = make_inputs(cfg["nptn"], cfg["ntaxa"], cfg["S"], seed=SEED + 3)
+    d = os.path.join(tmp, cfg["key"])
+    os.makedirs(d, exist_ok=True)
+    aln, tre = os.path.join(d, "a.phy"), os.path.join(d, "a.nwk")
+    write_phylip(aln, names, states, cfg["alphabet"])
+    open(tre, "w").write(nwk + "\n")
+    fargs = ["-s", aln] + cfg["margs"] + ["-te", tre]
+    cpu = run_harness(HARNESS_REF, fargs, cfg["reps"], cwd=d)
+    gpu = run_harness(HARNESS_CUDA, fargs, 5, warmup=1, cuda=True, threads=1, cwd=d)
+    shutil.rmtree(d, ignore_errors=True)
+    out = {"config": cfg["name"], "ntaxa": cfg["ntaxa"], "patterns": cfg["nptn"], "blocks_per_pattern": cfg["blocks"]}
+    units = (cfg["ntaxa"] - 2) * cfg["nptn"] * cfg["blocks"]
+    out["updates_per_lnl_eval"] = units
+    if cpu:
+        out["reference"] = {"kernel": cpu["kernel"], "cores": cpu["threads"], "lnl_evals_per_s": 1.0 / cpu["lnl_s_mean"], "ms_per_lnl_eval": cpu["lnl_s_mean"] * 1e3,
+                            "updates_per_s": units / cpu["lnl_s_mean"], "steps": cpu["lnl_reps"], "input": "same files, full size"}
+    if gpu:
+        ks = kernel_summary(gpu, fp64)
+        out["engine"] = {"through": "the reference's own computeLikelihood on the engine (ref_harness_cuda -cuda)",
+                         "ms_per_lnl_eval_host_wall": gpu["lnl_s_mean"] * 1e3, "lnl_evals_per_s": 1.0 / gpu["lnl_s_mean"],
+                         "updates_per_s": units / gpu["lnl_s_mean"]}
+        out["engine"].update(ks)
+        if ks["device_ms_per_lnl_eval"] > 0:
+            out["engine"]["updates_per_s_device"] = units / (ks["device_ms_per_lnl_eval"] * 1e-3)
+    if cpu and gpu:
+        out["parity"] = {"lnl_reference": cpu["lnl"], "lnl_engine": gpu["lnl"], "lnl_rel": rel(gpu["lnl"], cpu["lnl"]),
+                         "df_rel": rel(gpu["df"], cpu["df"]), "ddf_rel": rel(gpu["ddf"], cpu["ddf"]), "ok": rel(gpu["lnl"], cpu["lnl"]) <= 1e-9}
+        out["speedup_lnl_eval"] = cpu["lnl_s_mean"] / gpu["lnl_s_mean"]
+    return out
+
+
+def run_partition_config(tmp, fp64):
+    """BASELINE configs[4]: 25 DNA GTR+G4 + 25 protein LG+G4 partitions of 20k patterns, 100 taxa, unlinked PartitionModel (-sp):
+    PhyloSuperTree::computeLikelihood (phylosupertree.cpp:955-980), one engine per partition under -cuda"""
+    from iqtree_b200 import modelinputs as mi
+    d = os.path.join(tmp, "part50")
+    os.makedirs(d, exist_ok=True)
+    ntaxa, nptn, npart = 100, 20000, 50
+    names = ["t%d" % i for i in range(ntaxa)]
+    nwk = mi.random_tree_newick(ntaxa, SEED, names)
+    tre = os.path.join(d, "p.nwk")
+    open(tre, "w").write(nwk + "\n")
+    lines, cp = ["#nexus", "begin sets;"], []
+    for i in range(npart):
+        S = 4 if i % 2 == 0 else 20
+        st = mi.simulate_distinct_patterns(nwk, names, nptn, S, 10 + i)
+        write_phylip(os.path.join(d, "p%d.phy" % i), names, st, "ACGT" if S == 4 else AA)
+        lines.append("  charset part%d = p%d.phy: 1-%d;" % (i, i, nptn))
+        cp.append("%s:part%d" % ("GTR+G4" if S == 4 else "LG+G4", i))
+    lines += ["  charpartition mine = " + ", ".join(cp) + ";", "end;"]
+    nex = os.path.join(d, "p.nex")
+    open(nex, "w").write("\n".join(lines) + "\n")
+    fargs = ["-sp", nex, "-te", tre]
+    cpu = run_harness(HARNESS_REF, fargs, 2, cwd=d)
+    gpu = run_harness(HARNESS_CUDA, fargs, 5, warmup=1, cuda=True, threads=8, cwd=d)
+    shutil.rmtree(d, ignore_errors=True)
+    out = {"config": "50-partition PartitionModel: 25 DNA GTR+G4 + 25 protein LG+G4, 100 taxa x 20k patterns each (-sp)"}
+    if cpu:
+        u = cpu["updates_per_eval"]
+        out["updates_per_lnl_eval"] = u
+        out["reference"] = {"cores": cpu["threads"], "ms_per_lnl_eval": cpu["lnl_s_mean"] * 1e3, "lnl_evals_per_s": 1.0 / cpu["lnl_s_mean"], "updates_per_s": u / cpu["lnl_s_mean"]}
+    if gpu:
+        u = gpu["updates_per_eval"]
+        out["engine"] = {"through": "the reference's own PhyloSuperTree::computeLikelihood, one engine per partition (ref_harness_cuda -cuda, 8 host threads)",
+                         "ms_per_lnl_eval_host_wall": gpu["lnl_s_mean"] * 1e3, "lnl_evals_per_s": 1.0 / gpu["lnl_s_mean"], "updates_per_s": u / gpu["lnl_s_mean"]}
+    if cpu and gpu:
+        out["parity"] = {"lnl_reference": cpu["lnl"], "lnl_engine": gpu["lnl"], "lnl_rel": rel(gpu["lnl"], cpu["lnl"]), "ok": rel(gpu["lnl"], cpu["lnl"]) <= 1e-9}
+        out["speedup_lnl_eval"] = cpu["lnl_s_mean"] / gpu["lnl_s_mean"]
+    return out
+
+
+# ------------------------------------------------------------------ the engine arm ------------------------------------------------------------------
+
 def main():
     claim_stdout()
     ap = argparse.ArgumentParser()
@@ -206,6 +365,7 @@ def main():
     import torch.distributed as dist
     import iqtree_b200
     from iqtree_b200 import PhyloTree
+    from iqtree_b200 import modelinputs as mi
 
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -218,7 +378,8 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     lib = iqtree_b200.load_library()
-    names, nwk, states, model = make_inputs(NPTN)
+    names, nwk, states = make_inputs(NPTN)
+    model = mi.gtr_g4_inputs(SEED, ncat=NCAT)
     freq = np.ones(NPTN)
 
     t = PhyloTree(lib=lib)
@@ -342,6 +503,18 @@ def main():
     stats_lnl = t.kernelStats()
     t.setProfiling(False)
 
+    # ---- optimizeAllBranches(1): one Newton-Raphson pass over all 2n-3 branches, host wall time ----
+    oab_ms = None
+    if world == 1:
+        t.clearAllPartialLH()
+        t.computeLikelihood()
+        t0 = time.perf_counter()
+        oab_lnl = t.optimizeAllBranches(1)
+        torch.cuda.synchronize()
+        oab_ms = (time.perf_counter() - t0) * 1e3
+        t.readTreeString(nwk)          # back to the generating lengths
+        t.clearAllPartialLH()
+
     # ---- e2e: host buffers through the C ABI, copies inside the timed region --------------------------------
     b0, b1 = t.localPatterns()
     nloc = b1 - b0
@@ -381,41 +554,41 @@ def main():
     barrier()
     ms_e2e = ev2.elapsed_time(ev3)
     clocks = sampler.finish() if sampler else None
-    if os.environ.get("LK_BENCH_E2E_TRACE") and rank == 0:       # host-side wall time of the three calls of an e2e step (diagnostic)
-        acc = [0.0, 0.0, 0.0]
-        for _ in range(args.steps):
-            t0 = time.perf_counter()
-            lib.lkcuda_set_tip_states_async(eng, ctypes.cast(pinned_states.data_ptr(), c_u8p), nchunks)
-            t.clearAllPartialLH()
-            t1 = time.perf_counter()
-            lib.lktree_compute_likelihood(t.h, ctypes.byref(lnl_c), ctypes.cast(pinned_plh.data_ptr(), c_dp))
-            t2 = time.perf_counter()
-            t.computeLikelihoodDerv(root_leaf, root_nei, reset_theta=True)
-            t3 = time.perf_counter()
-            acc[0] += t1 - t0; acc[1] += t2 - t1; acc[2] += t3 - t2
-        sys.stderr.write("e2e trace (ms per step): upload call %.4f, computeLikelihood+fetch %.4f, computeLikelihoodDerv %.4f, chunks %d\n" % (
-            acc[0] / args.steps * 1e3, acc[1] / args.steps * 1e3, acc[2] / args.steps * 1e3, nchunks))
 
     tt = torch.tensor([ms, ms_e2e, ms_lnl], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     ms, ms_e2e, ms_lnl = float(tt[0]), float(tt[1]), float(tt[2])
+    nloc_all = t.localPatterns()[1] - t.localPatterns()[0]
+    t.close()
+    if world > 1:
+        dist.barrier()
 
+    failed = None
     if rank == 0:
         updates = (NTAXA - 2) * NPTN * NCAT
         value = updates * args.steps / (ms * 1e-3)
         e2e_value = updates * args.steps / (ms_e2e * 1e-3)
         peak, peak_src = measured_hbm_peak()
         n_p, b_p, ms_p = stats_lnl["partial"]      # the full-tree traversal launches of the lnL-only loop
-        achieved = (b_p / 1e9) / (ms_p * 1e-3) if ms_p > 0 else 0.0
-        nloc_all = t.localPatterns()[1] - t.localPatterns()[0]
-        # what the traversal kernel is designed to move: every node's vector + scale_num written once, one byte per tip child read
+        avg_ms = ms_p / max(n_p, 1)
+        alg_gbps = (b_p / 1e9) / (ms_p * 1e-3) if ms_p > 0 else 0.0
+        # what the traversal kernel is designed to move per launch: every node's vector + scale_num written once, one byte per tip child read
         traffic_model = nloc_all * ((NTAXA - 2) * (4 * NCAT * 8 + 2) + NTAXA)
-        traffic_ncu = 12.79e9 if (world == 1 and NTAXA == 100 and NPTN == 1000000) else None   # profiles/r1_trv_ncu_summary.txt
+        model_gbps = (traffic_model / 1e9) / (avg_ms * 1e-3) if avg_ms > 0 else 0.0
+        traffic, traffic_src = None, "no ncu capture of this kernel committed for this shape"
+        tp = os.path.join(ROOT, "profiles", "r2_trv_ncu_traffic.json")
+        if os.path.exists(tp) and world == 1 and NTAXA == 100 and NPTN == 1000000:
+            try:
+                tj = json.load(open(tp))
+                traffic = tj["dram_bytes_per_launch"]
+                traffic_src = "profiles/r2_trv_ncu_traffic.json (ncu --set full of commit %s: dram__bytes_read.sum + dram__bytes_write.sum)" % tj.get("commit", "?")
+            except Exception:
+                pass
         kinds = {k: {"launches": v[0], "algorithmic_gb": v[1] / 1e9, "device_ms": v[2],
                      "gbps": (v[1] / 1e9) / (v[2] * 1e-3) if v[2] > 0 else None} for k, v in stats.items() if v[0]}
         line = {
-            "metric": "partial-LH updates/s (patterns x cats x nodes)", "value": value, "unit": "updates/s",
+            "metric": METRIC, "value": value, "unit": "updates/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "ntaxa": NTAXA, "patterns": NPTN, "ncat": NCAT, "sharding": "patterns x%d" % world, "exchange": exchange,
@@ -429,29 +602,80 @@ def main():
                     "h2d_bytes_per_step": int(NTAXA * nloc), "d2h_bytes_per_step": int(8 * nloc + 3 * 64)},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "traverse_s4_kernel (whole post-order schedule in one launch; full-tree lnL launches only)",
-                         "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": traffic_ncu, "peak_source": peak_src,
-                         "launches": int(n_p), "algorithmic_bytes_per_launch": b_p / max(n_p, 1), "avg_launch_ms": ms_p / max(n_p, 1),
-                         "traffic_model_bytes_per_launch": traffic_model,
-                         "hbm_gbps_on_model_traffic": (traffic_model / 1e9) / (ms_p / max(n_p, 1) * 1e-3) if ms_p > 0 else None,
-                         "note": "achieved counts ALGORITHMIC bytes (SURVEY 8d: children read + result written per node); the kernel keeps "
-                                 "children in shared memory/registers and only writes each node once, so DRAM traffic is ~0.38x algorithmic "
-                                 "and frac can exceed 1"},
+                         "achieved": model_gbps, "peak": peak, "unit": "GB/s", "frac": model_gbps / peak if peak else None,
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                         "launches": int(n_p), "avg_launch_ms": avg_ms,
+                         "bytes_per_launch": traffic_model,
+                         "bytes_model": "DRAM traffic by design: every node's vector + scale_num written once, one byte per tip child read (children stay in registers / shared memory)",
+                         "algorithmic_bytes_per_launch": b_p / max(n_p, 1), "achieved_algorithmic": alg_gbps,
+                         "frac_algorithmic": alg_gbps / peak if peak else None,
+                         "note": "frac is on the traffic the fused kernel moves; frac_algorithmic (SURVEY 8d: children read + result written per node) can exceed 1"},
             "kernels": kinds,
             "clocks": clocks,
         }
-        if not args.no_cpu_baseline and world == 1:      # the contract asks for it on rank 0 at N=1 only (at N>1 the other ranks' polling threads share the cores)
-            ref = run_reference(names, nwk, states, 6, 0)
-            if ref is not None:
-                line["cpu_baseline"] = {"value": ref["updates_per_s"], "unit": "updates/s", "cores": ref["threads"], "kind": "reference",
-                                        "sample": ref["sample"], "lnl_evals_per_s_on_sample": 1.0 / ref["lnl_s_mean"]}
-            else:
-                line["cpu_baseline"] = None
+        if oab_ms is not None:
+            line["optimize_all_branches_1"] = {"ms": oab_ms, "lnl": oab_lnl, "branches": 2 * NTAXA - 3, "through": "harness driver (host-driven Newton steps, one launch per evaluation)"}
+        if not args.no_cpu_baseline and world == 1:
+            tmp = tempfile.mkdtemp(prefix="lk_bench_")
+            try:
+                fargs = headline_files(tmp, names, nwk, states)
+                # the contract asks for the CPU baseline on rank 0 at N=1 only; the FULL workload, a few steps
+                ref = run_harness(HARNESS_REF, fargs, CPU_STEPS, oab_reps=1, warmup=1, cwd=tmp)
+                if ref is not None:
+                    ups = (NTAXA - 2) * ref["nptn"] * NCAT / ref["step_s_mean"]
+                    line["cpu_baseline"] = {"value": ups, "unit": "updates/s", "cores": ref["threads"], "kind": "reference",
+                                            "sample": "the full workload (same alignment file): %d taxa x %d patterns, %d timed steps after 1 warm-up" % (NTAXA, ref["nptn"], ref["lnl_reps"]),
+                                            "kernel": ref["kernel"], "ms_per_step": ref["step_s_mean"] * 1e3, "lnl_evals_per_s": 1.0 / ref["lnl_s_mean"],
+                                            "optimize_all_branches_1_ms": ref["oab_s_mean"] * 1e3, "setup_s": ref["setup_s"]}
+                else:
+                    line["cpu_baseline"] = None
+                if WITH_DROPIN:
+                    dro = run_harness(HARNESS_CUDA, fargs, args.steps, oab_reps=1, warmup=2, cuda=True, threads=1, cwd=tmp)
+                    if dro is not None:
+                        dups = (NTAXA - 2) * dro["nptn"] * NCAT / dro["step_s_mean"]
+                        line["dropin"] = {"what": "the reference's OWN PhyloTree::computeLikelihood + computeLikelihoodDerv (+ optimizeAllBranches(1)) on the engine: "
+                                                  "IQ-TREE 1.4.3 sources + integration/iqtree-1.4.3-lkcuda.patch + integration/phylotree_cuda.cpp, option -cuda, LM_PER_NODE buffers",
+                                          "value": dups, "unit": "updates/s", "ms_per_step_host_wall": dro["step_s_mean"] * 1e3,
+                                          "lnl_evals_per_s": 1.0 / dro["lnl_s_mean"], "optimize_all_branches_1_ms": dro["oab_s_mean"] * 1e3,
+                                          "kernels": kernel_summary(dro, None)["kernels"], "lnl": dro["lnl"], "df": dro["df"], "ddf": dro["ddf"], "setup_s": dro["setup_s"]}
+                        if ref is not None:
+                            par = {"lnl_reference": ref["lnl"], "lnl_engine": dro["lnl"], "lnl_rel": rel(dro["lnl"], ref["lnl"]),
+                                   "df_rel": rel(dro["df"], ref["df"]), "ddf_rel": rel(dro["ddf"], ref["ddf"]),
+                                   "oab1_lnl_rel": rel(dro["oab_lnl"], ref["oab_lnl"]),
+                                   "what": "reference-on-engine vs the reference's AVX kernels: same alignment file (%d patterns), tree and model" % ref["nptn"],
+                                   "tolerance": "lnL 1e-9 relative (north_star); df / ddf 1e-7"}
+                            par["ok"] = bool(par["lnl_rel"] <= 1e-9 and par["df_rel"] <= 1e-7 and par["ddf_rel"] <= 1e-7)
+                            line["parity"] = par
+                            line["dropin"]["speedup_vs_reference_step"] = ref["step_s_mean"] / dro["step_s_mean"]
+                            line["dropin"]["speedup_vs_reference_oab1"] = ref["oab_s_mean"] / dro["oab_s_mean"] if dro["oab_s_mean"] > 0 else None
+                            if not par["ok"]:
+                                failed = "parity: lnL rel %.3g, df rel %.3g, ddf rel %.3g" % (par["lnl_rel"], par["df_rel"], par["ddf_rel"])
+                if WITH_CONFIGS:
+                    fp64 = measured_fp64_peak()
+                    line["fp64_peaks"] = fp64
+                    cfgs = []
+                    for cfg in config_list():
+                        try:
+                            cfgs.append(run_config(cfg, tmp, fp64))
+                        except Exception as ex:
+                            cfgs.append({"config": cfg["name"], "error": str(ex)})
+                    try:
+                        cfgs.append(run_partition_config(tmp, fp64))
+                    except Exception as ex:
+                        cfgs.append({"config": "50-partition PartitionModel", "error": str(ex)})
+                    line["configs"] = cfgs
+                    bad = [c["config"] for c in cfgs if c.get("parity") and not c["parity"]["ok"]]
+                    if bad and not failed:
+                        failed = "parity of configs: " + "; ".join(bad)
+            finally:
+                shutil.rmtree(tmp, ignore_errors=True)
         emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-    t.close()
+    if failed:
+        sys.stderr.write("bench.py: FAILED %s\n" % failed)
+        return 3
     return 0
 
 

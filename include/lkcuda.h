@@ -299,6 +299,10 @@ enum {
 };
 int lkcuda_set_profiling(lkcuda_engine *e, int32_t on);
 int lkcuda_kernel_stats(lkcuda_engine *e, int32_t kind, uint64_t *launches, uint64_t *bytes, double *device_ms);
+/* algorithmic FP64 operations of those launches (per pattern and block 2*S^2 for every internal child and for the way back
+   to state space, S per product - 6S^2+S / 4S^2+S / 2S^2+S for the three node cases); counted for the partial-likelihood kernels:
+   the numerator of the FP64 roofline */
+int lkcuda_kernel_flops(lkcuda_engine *e, int32_t kind, uint64_t *flops);
 
 #ifdef __cplusplus
 }

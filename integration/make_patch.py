@@ -74,7 +74,9 @@ EDITS = {
          "    void lkCudaPatternLh(double *pattern_lh);\n"
          "    double computePatternLhCatCuda(SiteLoglType wsl);\n"
          "    void computePatternLikelihoodCuda(double *ptn_lh, double *cur_logl, double *ptn_lh_cat, SiteLoglType wsl);\n"
-         "    void lkCudaStats(uint64_t &flushes, uint64_t &ops, uint64_t &launches);\n"),
+         "    void lkCudaStats(uint64_t &flushes, uint64_t &ops, uint64_t &launches);\n"
+         "    void lkCudaProfile(bool on, bool reset);\n"
+         "    bool lkCudaKernelStats(int kind, uint64_t &launches, uint64_t &bytes, uint64_t &flops, double &device_ms);\n"),
     ],
     "phylotree.cpp": [
         ("    var_matrix = NULL;\n    setLikelihoodKernel(LK_EIGEN_SSE);",

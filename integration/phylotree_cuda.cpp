@@ -463,6 +463,21 @@ void PhyloTree::computePatternLikelihoodCuda(double *ptn_lh, double *cur_logl, d
     }
 }
 
+/* per-kernel-kind statistics of the engine (lkcuda_kernel_stats): launches, algorithmic bytes / flops, device time with profiling on */
+void PhyloTree::lkCudaProfile(bool on, bool reset) {
+    if (!lk_cuda) return;
+    if (reset) lkcuda_reset_counters(lk_cuda->engine);
+    lkcuda_set_profiling(lk_cuda->engine, on ? 1 : 0);
+}
+
+bool PhyloTree::lkCudaKernelStats(int kind, uint64_t &launches, uint64_t &bytes, uint64_t &flops, double &device_ms) {
+    launches = bytes = flops = 0; device_ms = 0.0;
+    if (!lk_cuda || kind < 0 || kind >= LKCUDA_NKIND) return false;
+    lkcuda_kernel_stats(lk_cuda->engine, kind, &launches, &bytes, &device_ms);
+    lkcuda_kernel_flops(lk_cuda->engine, kind, &flops);
+    return true;
+}
+
 /* counters for the harness / log output */
 void PhyloTree::lkCudaStats(uint64_t &flushes, uint64_t &ops, uint64_t &launches) {
     flushes = ops = launches = 0;

@@ -80,6 +80,18 @@ def build_cuda(force=False, verbose=False):
     return CUDA_LIB
 
 
+def build_tools(force=False):
+    """tools/fp64_peak: the FP64 / HBM peak probe bench.py runs for the roofline denominators of the protein / codon configs"""
+    src, exe = os.path.join(ROOT, "tools", "fp64_peak.cu"), os.path.join(ROOT, "tools", "fp64_peak")
+    if not force and not _newer(exe, [src]):
+        return exe
+    nvcc = nvcc_path()
+    if nvcc is None:
+        return exe if os.path.exists(exe) else None
+    _run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-o", exe, src])
+    return exe
+
+
 def build_harness(force=False):
     """TEST / BENCH DRIVER: the C++ mirror of the reference's PhyloTree call sequences, linked against the product library."""
     cuda = build_cuda()

@@ -147,7 +147,7 @@ struct lkcuda_engine {
     bool profiling;
     std::vector<lkc::PendingEvent> pending;
     std::vector<cudaEvent_t> event_pool;
-    double kind_ms[lkc::KIND_COUNT]; uint64_t kind_launches[lkc::KIND_COUNT]; uint64_t kind_bytes[lkc::KIND_COUNT];
+    double kind_ms[lkc::KIND_COUNT]; uint64_t kind_launches[lkc::KIND_COUNT]; uint64_t kind_bytes[lkc::KIND_COUNT]; uint64_t kind_flops[lkc::KIND_COUNT];
     uint64_t total_dev_bytes;
     char err[512];
 };

@@ -180,7 +180,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     e->upload_base = 0; e->upload_chunks = 0; e->upload_chunk_pat = 0; e->upload_pending = e->upload_check = false;
     e->model_set = e->states_set = e->weights_set = false;
     e->launches = e->bytes = 0; e->profiling = false; e->total_dev_bytes = 0;
-    memset(e->kind_ms, 0, sizeof(e->kind_ms)); memset(e->kind_launches, 0, sizeof(e->kind_launches)); memset(e->kind_bytes, 0, sizeof(e->kind_bytes));
+    memset(e->kind_ms, 0, sizeof(e->kind_ms)); memset(e->kind_launches, 0, sizeof(e->kind_launches)); memset(e->kind_bytes, 0, sizeof(e->kind_bytes)); memset(e->kind_flops, 0, sizeof(e->kind_flops));
     e->err[0] = 0;
 
     DevView &v = e->v;
@@ -661,7 +661,7 @@ int lkcuda_reset_counters(lkcuda_engine *e) {
     LK_ENTER(e);
     drain_events(e);
     e->launches = 0; e->bytes = 0;
-    memset(e->kind_ms, 0, sizeof(e->kind_ms)); memset(e->kind_launches, 0, sizeof(e->kind_launches)); memset(e->kind_bytes, 0, sizeof(e->kind_bytes));
+    memset(e->kind_ms, 0, sizeof(e->kind_ms)); memset(e->kind_launches, 0, sizeof(e->kind_launches)); memset(e->kind_bytes, 0, sizeof(e->kind_bytes)); memset(e->kind_flops, 0, sizeof(e->kind_flops));
     return LKCUDA_OK;
 }
 
@@ -669,6 +669,12 @@ int lkcuda_set_profiling(lkcuda_engine *e, int32_t on) {
     LK_ENTER(e);
     drain_events(e);
     e->profiling = on != 0;
+    return LKCUDA_OK;
+}
+
+int lkcuda_kernel_flops(lkcuda_engine *e, int32_t kind, uint64_t *flops) {
+    if (!e || !flops || kind < 0 || kind >= KIND_COUNT) return LKCUDA_ERR_ARG;
+    *flops = e->kind_flops[kind];
     return LKCUDA_OK;
 }
 

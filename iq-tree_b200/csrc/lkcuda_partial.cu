@@ -658,6 +658,12 @@ uint64_t lkc::op_bytes(const DevView &v, int ntip, int nint) {
     return (uint64_t)v.NP * ((uint64_t)(nint + 1) * b + (uint64_t)ntip * 1 + (uint64_t)(nint + 1) * 2);
 }
 
+/* algorithmic flops of one node: 2*S^2 per internal child and for the way back to state space, S per product; per pattern and block */
+uint64_t lkc::op_flops(const DevView &v, int ntip, int nint) {
+    const uint64_t S = (uint64_t)v.S;
+    return (uint64_t)v.NP * (uint64_t)v.K * (2 * S * S * (uint64_t)(nint + 1) + S * (uint64_t)(ntip + nint - 1));
+}
+
 static int launch_ops(lkcuda_engine *e, int slot, int nops, int nchild_total, const int32_t *level_start, int nlevels, uint64_t *bytes_per_level) {
     const DevView &v = e->v;
     int rc = ensure_tables(e, nchild_total);
@@ -732,6 +738,7 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
         b.id = n.src1; b.pad = 0; b.len = n.len1;
         int ntip = (LKCUDA_IS_TIP(a.id) ? 1 : 0) + (LKCUDA_IS_TIP(b.id) ? 1 : 0);
         bytes += op_bytes(v, ntip, 2 - ntip);
+        e->kind_flops[KIND_PARTIAL] += op_flops(v, ntip, 2 - ntip);
     }
     rc = ensure_tables(e, 2 * nops);
     if (rc) return rc;
@@ -827,6 +834,7 @@ static int partial_batch_segment(lkcuda_engine *e, const lkcuda_partial_op *ops,
         b.id = ops[i].right; b.pad = 0; b.len = ops[i].len_right;
         int ntip = (LKCUDA_IS_TIP(a.id) ? 1 : 0) + (LKCUDA_IS_TIP(b.id) ? 1 : 0);
         lbytes[l] += op_bytes(e->v, ntip, 2 - ntip);
+        e->kind_flops[KIND_PARTIAL] += op_flops(e->v, ntip, 2 - ntip);
     }
     e->theta_ready = false;
     if (sitemodel) return launch_traverse_sitemodel(e, slot, nops);
@@ -901,6 +909,7 @@ int lkcuda_partial_multi(lkcuda_engine *e, int32_t dst, int32_t nchild, const in
         ntip += LKCUDA_IS_TIP(child[c]) ? 1 : 0;
     }
     uint64_t bytes = op_bytes(e->v, ntip, nchild - ntip);
+    e->kind_flops[KIND_PARTIAL] += op_flops(e->v, ntip, nchild - ntip);
     e->theta_ready = false;
     /* multifurcations always take the generic kernel: force it by launching here */
     const DevView &v = e->v;

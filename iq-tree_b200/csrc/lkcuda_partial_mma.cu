@@ -366,6 +366,7 @@ int launch_traverse_mma(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops
         b.id = n.src1; b.pad = 0; b.len = n.len1;
         int ntip = (LKCUDA_IS_TIP(a.id) ? 1 : 0) + (LKCUDA_IS_TIP(b.id) ? 1 : 0);
         bytes += op_bytes(v, ntip, 2 - ntip);
+        e->kind_flops[KIND_PARTIAL] += op_flops(v, ntip, 2 - ntip);
     }
     rc = ensure_tables(e, 2 * nops);
     if (rc) return rc;

@@ -135,6 +135,7 @@ int lkc::launch_traverse_sitemodel(lkcuda_engine *e, int slot, int nops) {
     for (int i = 0; i < nops; i++) {
         const int ntip = (LKCUDA_IS_TIP(e->h_child[slot][2 * i].id) ? 1 : 0) + (LKCUDA_IS_TIP(e->h_child[slot][2 * i + 1].id) ? 1 : 0);
         bytes += op_bytes(v, ntip, 2 - ntip);
+        e->kind_flops[KIND_PARTIAL] += op_flops(v, ntip, 2 - ntip);
     }
     bytes += (uint64_t)v.NP * (uint64_t)(2 * v.S * v.S + v.S) * 8;      /* the pattern's eigensystem, once per launch */
     launch_begin(e, KIND_PARTIAL);

@@ -66,6 +66,7 @@ struct TravSchedule { std::vector<TravNode> nodes; int nslots; };
 int schedule_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops, int maxslots, bool use_prev, TravSchedule &sch);
 int ring_acquire(lkcuda_engine *e, int nops, int nchild, int *slot_out);
 uint64_t op_bytes(const DevView &v, int ntip, int nint);
+uint64_t op_flops(const DevView &v, int ntip, int nint);
 
 /* implemented in lkcuda_partial_mma.cu */
 bool use_traverse_mma(const lkcuda_engine *e);

@@ -91,6 +91,7 @@ LKCUDA_SYMBOLS = {
     "lkcuda_reset_counters": (C.c_int, [C.c_void_p]),
     "lkcuda_set_profiling": (C.c_int, [C.c_void_p, C.c_int32]),
     "lkcuda_kernel_stats": (C.c_int, [C.c_void_p, C.c_int32, c_uint64_p, c_uint64_p, c_double_p]),
+    "lkcuda_kernel_flops": (C.c_int, [C.c_void_p, C.c_int32, c_uint64_p]),
 }
 
 LKTREE_SYMBOLS = {
@@ -620,6 +621,16 @@ class PhyloTree:
             n, b, ms = C.c_uint64(), C.c_uint64(), C.c_double()
             self._eck(e, self.lib.lkcuda_kernel_stats(e, k, C.byref(n), C.byref(b), C.byref(ms)))
             out[name] = (n.value, b.value, ms.value)
+        return out
+
+    def kernelFlops(self, shard=0):
+        """{kind: algorithmic FP64 operations}"""
+        e = self.engine(shard)
+        out = {}
+        for k, name in enumerate(KIND_NAMES):
+            f = C.c_uint64()
+            self._eck(e, self.lib.lkcuda_kernel_flops(e, k, C.byref(f)))
+            out[name] = f.value
         return out
 
     def resultDevicePtr(self, shard=0):

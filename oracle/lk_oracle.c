@@ -844,6 +844,12 @@ int lkcuda_launch_count(const lkcuda_engine *e, uint64_t *c) { if (!e || !c) ret
 int lkcuda_algorithmic_bytes(const lkcuda_engine *e, uint64_t *b) { if (!e || !b) return LKCUDA_ERR_ARG; *b = e->bytes; return LKCUDA_OK; }
 int lkcuda_reset_counters(lkcuda_engine *e) { if (!e) return LKCUDA_ERR_ARG; e->launches = 0; e->bytes = 0; return LKCUDA_OK; }
 int lkcuda_set_profiling(lkcuda_engine *e, int32_t on) { (void)on; return e ? LKCUDA_OK : LKCUDA_ERR_ARG; }
+int lkcuda_kernel_flops(lkcuda_engine *e, int32_t kind, uint64_t *flops) {
+    if (!e || !flops) return LKCUDA_ERR_ARG;
+    (void)kind; *flops = 0;      /* the CPU restatement keeps no flop statistics */
+    return LKCUDA_OK;
+}
+
 int lkcuda_kernel_stats(lkcuda_engine *e, int32_t kind, uint64_t *launches, uint64_t *bytes, double *device_ms) {
     if (!e || kind < 0 || kind >= LKCUDA_NKIND) return LKCUDA_ERR_ARG;
     if (launches) *launches = 0; if (bytes) *bytes = 0; if (device_ms) *device_ms = 0.0;

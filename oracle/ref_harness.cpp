@@ -44,6 +44,8 @@
 #include "phylotree.h"
 #include "iqtree.h"
 #include "phyloanalysis.h"
+#include "phylosupertree.h"
+#include "phylosupertreeplen.h"
 #include "tools.h"
 #include "alignment.h"
 #include "checkpoint.h"
@@ -149,8 +151,12 @@ static IQTree *setup(int argc, char **argv, Params &params) {
     omp_set_nested(false);
 #endif
     init_random(params.ran_seed, false);
-    Alignment *aln = new Alignment(params.aln_file, params.sequence_type, params.intype);
-    IQTree *tree = new IQTree(aln);
+    IQTree *tree;
+    if (params.partition_file) {        // partition models, as runPhyloAnalysis creates them (phyloanalysis.cpp:2461-2476)
+        if (params.partition_type) tree = new PhyloSuperTreePlen(params);
+        else tree = new PhyloSuperTree(params);
+    } else
+        tree = new IQTree(new Alignment(params.aln_file, params.sequence_type, params.intype));
     tree->setCheckpoint(new Checkpoint);
     if (params.min_branch_length <= 0.0) {       // phyloanalysis.cpp:2488-2497
         params.min_branch_length = 1e-6;
@@ -586,6 +592,34 @@ static int do_time(int argc, char **argv) {
     double lnl = tree->computeLikelihood();           // warm-up
     PhyloNode *n1 = (PhyloNode*)tree->root, *n2 = (PhyloNode*)tree->root->neighbors[0]->node;
     double df = 0, ddf = 0;
+    if (tree->isSuperTree()) {
+        /* PartitionModel: full-tree lnL of all partitions (PhyloSuperTree::computeLikelihood, phylosupertree.cpp:955-980) */
+        std::vector<double> t;
+        for (int r = 0; r < lnl_reps; r++) {
+            double a = getRealTime();
+            tree->clearAllPartialLH();
+            lnl = tree->computeLikelihood();
+            t.push_back(getRealTime() - a);
+        }
+        size_t warm = getenv("LK_REF_WARMUP") ? (size_t)atoi(getenv("LK_REF_WARMUP")) : 0;
+        if (warm >= t.size()) warm = 0;
+        double sum = 0;
+        for (size_t i = warm; i < t.size(); i++) sum += t[i];
+        PhyloSuperTree *st = (PhyloSuperTree*)tree;
+        size_t units = 0, ptns = 0;
+        bool dev = false;
+        for (PhyloSuperTree::iterator it = st->begin(); it != st->end(); it++) {
+            size_t k = (*it)->getRate()->getNRate() * ((*it)->getModel()->isMixture() && !(*it)->getModelFactory()->fused_mix_rate ? (*it)->getModel()->getNMixtures() : 1);
+            units += (size_t)((*it)->leafNum - 2) * (*it)->aln->size() * k;
+            ptns += (*it)->aln->size();
+            dev = dev || ON_DEVICE(*it);
+        }
+        printf("{\"ref_time\": true, \"kernel\": \"%s\", \"threads\": %d, \"partitions\": %zu, \"nptn\": %zu, \"ntaxa\": %d, \"updates_per_eval\": %zu, "
+               "\"lnl\": %.17g, \"lnl_reps\": %d, \"lnl_s_mean\": %.6g, \"setup_s\": %.4g}\n",
+               dev ? "cuda" : "cpu", params.num_threads, st->size(), ptns, tree->leafNum, units, lnl, (int)(t.size() - warm),
+               t.size() > warm ? sum / (t.size() - warm) : 0.0, t_setup);
+        return 0;
+    }
     /* one "step" = full-tree lnL (all partials recomputed) + theta_all rebuild + df/ddf on the root-leaf branch */
     std::vector<double> lnl_t, step_t;
     for (int r = 0; r < lnl_reps; r++) {
@@ -631,19 +665,49 @@ static int do_time(int argc, char **argv) {
         }
         if (nni_done) t_nni /= nni_done;
     }
+    /* under -cuda: the same steps once more with every launch bracketed by CUDA events -> device time per kernel kind */
+    std::ostringstream kstats;
+    kstats << "{";
+#ifdef LK_CUDA_SHIM
+    if (ON_DEVICE(tree) && lnl_reps > 0) {
+        static const char *kind_name[] = {"prep", "partial", "branch", "theta", "derv", "frombuf", "newton", "misc", "rell", "em"};
+        tree->lkCudaProfile(true, true);
+        for (int r = 0; r < lnl_reps; r++) {
+            tree->clearAllPartialLH();
+            tree->computeLikelihood();
+            tree->theta_computed = false;
+            double df2, ddf2;
+            tree->computeLikelihoodDerv((PhyloNeighbor*)n1->findNeighbor(n2), n1, df2, ddf2);
+        }
+        bool first = true;
+        for (int k = 0; k < 10; k++) {
+            uint64_t nl, nb, nf; double ms;
+            if (!tree->lkCudaKernelStats(k, nl, nb, nf, ms) || !nl) continue;
+            kstats << (first ? "" : ", ") << "\"" << kind_name[k] << "\": {\"launches\": " << nl << ", \"bytes\": " << nb << ", \"flops\": " << nf
+                   << ", \"device_ms\": " << std::setprecision(8) << ms << "}";
+            first = false;
+        }
+        tree->lkCudaProfile(false, false);
+    }
+#endif
+    kstats << "}";
+    /* LK_REF_WARMUP=w: the first w steps are untimed warm-up (bench.py --warmup) */
+    size_t warm = getenv("LK_REF_WARMUP") ? (size_t)atoi(getenv("LK_REF_WARMUP")) : 0;
+    if (warm >= lnl_t.size()) warm = 0;
     double sum = 0, best = 1e300;
-    for (size_t i = 0; i < lnl_t.size(); i++) { sum += lnl_t[i]; best = std::min(best, lnl_t[i]); }
-    double mean = lnl_t.empty() ? 0 : sum / lnl_t.size();
+    for (size_t i = warm; i < lnl_t.size(); i++) { sum += lnl_t[i]; best = std::min(best, lnl_t[i]); }
+    double mean = lnl_t.empty() ? 0 : sum / (lnl_t.size() - warm);
     double step_sum = 0;
-    for (size_t i = 0; i < step_t.size(); i++) step_sum += step_t[i];
-    double step_mean = step_t.empty() ? 0 : step_sum / step_t.size();
+    for (size_t i = warm; i < step_t.size(); i++) step_sum += step_t[i];
+    double step_mean = step_t.empty() ? 0 : step_sum / (step_t.size() - warm);
+    lnl_reps -= (int)warm;
     printf("{\"ref_time\": true, \"kernel\": \"%s\", \"threads\": %d, \"nptn\": %zu, \"ntaxa\": %zu, \"blocks\": %zu, "
-           "\"lnl\": %.12f, \"lnl_reps\": %d, \"lnl_s_mean\": %.6g, \"lnl_s_best\": %.6g, \"step_s_mean\": %.6g, \"step_s_total\": %.6g, "
-           "\"df\": %.12g, \"ddf\": %.12g, \"derv_reps\": %d, \"derv_s_mean\": %.6g, "
-           "\"oab_lnl\": %.12f, \"oab_reps\": %d, \"oab_s_mean\": %.6g, \"nni_branches\": %d, \"nni_s_mean\": %.6g, \"setup_s\": %.4g}\n",
+           "\"lnl\": %.17g, \"lnl_reps\": %d, \"lnl_s_mean\": %.6g, \"lnl_s_best\": %.6g, \"step_s_mean\": %.6g, \"step_s_total\": %.6g, "
+           "\"df\": %.17g, \"ddf\": %.17g, \"derv_reps\": %d, \"derv_s_mean\": %.6g, "
+           "\"oab_lnl\": %.12f, \"oab_reps\": %d, \"oab_s_mean\": %.6g, \"nni_branches\": %d, \"nni_s_mean\": %.6g, \"setup_s\": %.4g, \"kernels\": %s}\n",
            ON_DEVICE(tree) ? "cuda" : (tree->sse == LK_EIGEN_SSE ? (instruction_set >= 7 ? "AVX" : "SSE") : "generic"),
            params.num_threads, P, ntaxa, blocks, lnl, lnl_reps, mean, lnl_t.empty() ? 0.0 : best, step_mean, step_sum,
-           df, ddf, derv_reps, t_derv, oab, oab_reps, t_oab, nni_done, t_nni, t_setup);
+           df, ddf, derv_reps, t_derv, oab, oab_reps, t_oab, nni_done, t_nni, t_setup, kstats.str().c_str());
     return 0;
 }
 
