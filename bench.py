@@ -503,18 +503,6 @@ def main():
     stats_lnl = t.kernelStats()
     t.setProfiling(False)
 
-    # ---- optimizeAllBranches(1) (SURVEY 8d): one Newton-Raphson pass over all 2n-3 branches, host wall time ----
-    oab_ms = None
-    if world == 1:
-        t.clearAllPartialLH()
-        t.computeLikelihood()
-        t0 = time.perf_counter()
-        oab_lnl = t.optimizeAllBranches(1)
-        torch.cuda.synchronize()
-        oab_ms = (time.perf_counter() - t0) * 1e3
-        t.readTreeString(nwk)          # back to the generating lengths
-        t.clearAllPartialLH()
-
     # ---- e2e: host buffers through the C ABI, copies inside the timed region --------------------------------
     b0, b1 = t.localPatterns()
     nloc = b1 - b0
@@ -554,6 +542,17 @@ def main():
     barrier()
     ms_e2e = ev2.elapsed_time(ev3)
     clocks = sampler.finish() if sampler else None
+
+    # ---- optimizeAllBranches(1) (SURVEY 8d): one Newton-Raphson pass over all 2n-3 branches, host wall time ----
+    oab_ms = None
+    if world == 1:
+        t.clearAllPartialLH()
+        t.computeLikelihood()
+        t0 = time.perf_counter()
+        oab_lnl = t.optimizeAllBranches(1)
+        torch.cuda.synchronize()
+        oab_ms = (time.perf_counter() - t0) * 1e3
+
 
     tt = torch.tensor([ms, ms_e2e, ms_lnl], dtype=torch.float64, device=dev)
     if world > 1:

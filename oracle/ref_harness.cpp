@@ -20,6 +20,10 @@
  *        ref_harness dumppars <outdir> <seed> <iqtree args ...>         Fitch parsimony: scores per branch, stepwise-addition tree
  *        ref_harness dumpem <outdir> <iqtree args ...>                  RateFree::optimizeWithEM: rates, proportions, lnL before / after
  *        ref_harness time <lnl_reps> <derv_reps> <oab_reps> <iqtree args ...>
+ *        ref_harness dumplite <outdir> <stride> <iqtree args ...>      BASELINE-size parity: model inputs, lnL, every stride-th pattern log-likelihood,
+ *                                                                       scale_num of three vectors, df / ddf / lnL-from-buffer on three branches
+ *        ref_harness dumprepair <outdir> <iqtree args ...>             the NaN / Inf repair of the branch kernel (phylokernel.h:848-866) on a zeroed vector
+ *        ref_harness iqtree <iqtree args ...>                          the complete command line
  */
 #include <cstdio>
 #include <cstdlib>
@@ -574,6 +578,145 @@ static int do_dumpem(int argc, char **argv) {
     return 0;
 }
 
+
+/* the fixtures of the BASELINE-size parity tests: what do_dump writes, without the bulk (no tip states, no partial_lh values) */
+static int do_dumplite(int argc, char **argv) {
+    g_out = argv[2];
+    mkdir(g_out.c_str(), 0755);
+    size_t stride = (size_t)atol(argv[3]);
+    if (stride < 1) stride = 1;
+    std::vector<char*> args; args.push_back(argv[0]);
+    for (int i = 4; i < argc; i++) args.push_back(argv[i]);
+    Params &params = Params::getInstance();
+    IQTree *tree = setup((int)args.size(), &args[0], params);
+    Alignment *aln = tree->aln;
+    ModelSubst *model = tree->getModel();
+    RateHeterogeneity *rate = tree->getRate();
+    ModelFactory *mf = tree->getModelFactory();
+    size_t S = aln->num_states, C = rate->getNRate(), M = model->getNMixtures();
+    bool fused = mf->fused_mix_rate;
+    size_t P = aln->size(), U = mf->unobserved_ptns.size(), nptn = P + U, ntaxa = aln->getNSeq();
+    size_t block = model->isMixture() && !fused ? S * C * M : S * C;
+    size_t E = M;
+    wbin("eval.f64", model->getEigenvalues(), E * S * sizeof(double));
+    wbin("evec.f64", model->getEigenvectors(), E * S * S * sizeof(double));
+    wbin("inv_evec.f64", model->getInverseEigenvectors(), E * S * S * sizeof(double));
+    std::vector<double> rates(C), props(C), mixprops(M, 1.0), sfreq(S);
+    for (size_t c = 0; c < C; c++) { rates[c] = rate->getRate(c); props[c] = rate->getProp(c); }
+    if (model->isMixture()) for (size_t m = 0; m < M; m++) mixprops[m] = ((ModelMixture*)model)->prop[m];
+    model->getStateFrequency(&sfreq[0]);
+    wbin("rates.f64", &rates[0], C * 8); wbin("props.f64", &props[0], C * 8);
+    wbin("mixprops.f64", &mixprops[0], M * 8); wbin("state_freq.f64", &sfreq[0], S * 8);
+    dumpAdjacency(tree, "tree_adj.txt");
+
+    tree->clearAllPartialLH();
+    double lnl = tree->computeLikelihood();
+    int root_from = tree->current_it_back->node->id, root_to = tree->current_it->node->id;
+    std::vector<double> plh(P), samp;
+    tree->computeLikelihood(&plh[0]);       // with the scale_num correction of current_it
+    for (size_t p = 0; p < P; p += stride) samp.push_back(plh[p]);
+    wbin("pattern_lh_scaled_sample.f64", &samp[0], samp.size() * 8);
+    double freq_sum = 0.0;
+    for (size_t p = 0; p < P; p++) freq_sum += tree->ptn_freq[p];
+
+    /* scale_num of three vectors valid after the call above + strided row sums of their partial_lh */
+    std::vector<PhyloNeighbor*> vecs; std::vector<std::pair<int,int> > vid;
+    {
+        std::vector<Node*> nodes;
+        collectNodes(tree->root, NULL, nodes);
+        for (size_t i = 0; i < nodes.size(); i++)
+            for (size_t k = 0; k < nodes[i]->neighbors.size(); k++) {
+                PhyloNeighbor *b = (PhyloNeighbor*)nodes[i]->neighbors[k];
+                if ((b->partial_lh_computed & 1) && b->partial_lh && !b->node->isLeaf()) { vecs.push_back(b); vid.push_back(std::make_pair(nodes[i]->id, b->node->id)); }
+            }
+    }
+    std::ofstream vf((g_out + "/vectors.txt").c_str());
+    size_t pick[3] = {0, vecs.size() / 2, vecs.size() - 1};
+    for (int q = 0; q < 3 && !vecs.empty(); q++) {
+        PhyloNeighbor *b = vecs[pick[q]];
+        std::vector<UBYTE> sc(nptn); std::vector<double> rs;
+        std::vector<double> lh;
+        const double *src = b->partial_lh;
+        if (ON_DEVICE(tree)) {
+#ifdef LK_CUDA_SHIM
+            lh.resize(nptn * block);
+            tree->lkCudaFetchVector(b, &lh[0], &sc[0]);
+            src = &lh[0];
+#endif
+        } else memcpy(&sc[0], b->scale_num, nptn * sizeof(UBYTE));
+        for (size_t p = 0; p < nptn; p += stride) { double a = 0.0; for (size_t i = 0; i < block; i++) a += src[p * block + i]; rs.push_back(a); }
+        std::ostringstream nm; nm << "vec" << q;
+        wbin(nm.str() + "_scale.i16", &sc[0], nptn * sizeof(UBYTE));
+        wbin(nm.str() + "_rowsum_sample.f64", &rs[0], rs.size() * 8);
+        vf << vid[pick[q]].first << " " << vid[pick[q]].second << "\n";
+    }
+    vf.close();
+
+    /* df / ddf / lnL-from-buffer on three branches of the reference's traversal */
+    NodeVector nodes, nodes2;
+    tree->computeBestTraversal(nodes, nodes2);
+    size_t bpick[3] = {0, nodes.size() / 2, nodes.size() - 1};
+    std::vector<int> bid; std::vector<double> dv;
+    for (int q = 0; q < 3; q++) {
+        size_t j = bpick[q];
+        double a, b;
+        tree->theta_computed = false;
+        PhyloNeighbor *nb = (PhyloNeighbor*)nodes[j]->findNeighbor(nodes2[j]);
+        tree->computeLikelihoodDerv(nb, (PhyloNode*)nodes[j], a, b);
+        tree->current_it = nb;
+        tree->current_it_back = (PhyloNeighbor*)nodes2[j]->findNeighbor(nodes[j]);
+        double fb = tree->computeLikelihoodFromBuffer();
+        bid.push_back(nodes[j]->id); bid.push_back(nodes2[j]->id);
+        dv.push_back(a); dv.push_back(b); dv.push_back(fb);
+    }
+    wbin("branch_ids.i32", &bid[0], bid.size() * sizeof(int));
+    wbin("branch_derv.f64", &dv[0], dv.size() * 8);
+    {
+        std::ofstream f((g_out + "/meta.json").c_str());
+        f << std::setprecision(17);
+        f << "{ \"nstates\": " << S << ", \"ncat\": " << C << ", \"nmix\": " << M << ", \"family\": \"" << familyName(tree) << "\", \"block\": " << block
+          << ", \"nptn\": " << P << ", \"nunobs\": " << U << ", \"ntaxa\": " << ntaxa << ", \"nsite\": " << aln->getNSite() << ", \"freq_sum\": " << freq_sum
+          << ", \"state_unknown\": " << (int)aln->STATE_UNKNOWN << ", \"seq_type\": " << (int)aln->seq_type << ", \"p_invar\": " << rate->getPInvar()
+          << ", \"min_branch_length\": " << params.min_branch_length << ", \"max_branch_length\": " << params.max_branch_length
+          << ", \"root_branch\": [" << root_from << ", " << root_to << "], \"lnl\": " << lnl << ", \"stride\": " << stride
+          << ", \"kernel\": \"" << (ON_DEVICE(tree) ? "cuda" : (tree->sse == LK_EIGEN_SSE ? (instruction_set >= 7 ? "AVX" : "SSE") : "generic"))
+          << "\", \"threads\": " << params.num_threads << " }\n";
+    }
+    printf("dumplite lnl %.10f, %zu vectors valid, %zu pattern samples\n", lnl, vecs.size(), samp.size());
+    return 0;
+}
+
+/* the NaN / Inf repair of the branch kernels (phylokernel.h:848-866): zero three patterns' rows of the root branch's vector, so that
+   their likelihood is 0 and log() gives -inf, and let the reference's own kernel repair them (CPU buffers only) */
+static int do_dumprepair(int argc, char **argv) {
+    g_out = argv[2];
+    mkdir(g_out.c_str(), 0755);
+    std::vector<char*> args; args.push_back(argv[0]);
+    for (int i = 3; i < argc; i++) args.push_back(argv[i]);
+    Params &params = Params::getInstance();
+    IQTree *tree = setup((int)args.size(), &args[0], params);
+    if (ON_DEVICE(tree)) { fprintf(stderr, "dumprepair: host buffers only\n"); return 4; }
+    size_t P = tree->aln->size();
+    size_t block = tree->getPartialLhBytes() / sizeof(double) / ((P + tree->aln->num_states + 3) / 4 * 4);
+    tree->clearAllPartialLH();
+    double lnl0 = tree->computeLikelihood();
+    PhyloNeighbor *it = tree->current_it;
+    PhyloNode *dad = (PhyloNode*)tree->current_it_back->node;
+    if (!it->partial_lh) { fprintf(stderr, "dumprepair: root branch vector missing\n"); return 5; }
+    int zp[3] = {0, (int)(P / 2), (int)P - 1};
+    for (int q = 0; q < 3; q++) memset(it->partial_lh + (size_t)zp[q] * block, 0, block * sizeof(double));
+    double lnl1 = tree->computeLikelihoodBranch(it, dad);
+    wbin("pattern_lh_repaired.f64", tree->_pattern_lh, P * 8);
+    {
+        std::ofstream f((g_out + "/metarepair.json").c_str());
+        f << std::setprecision(17);
+        f << "{ \"lnl\": " << lnl0 << ", \"lnl_repaired\": " << lnl1 << ", \"zeroed\": [" << zp[0] << ", " << zp[1] << ", " << zp[2] << "]"
+          << ", \"vector\": [" << dad->id << ", " << it->node->id << "], \"block\": " << block << " }\n";
+    }
+    printf("dumprepair lnl %.10f -> %.10f\n", lnl0, lnl1);
+    return 0;
+}
+
 static int do_time(int argc, char **argv) {
     int lnl_reps = atoi(argv[2]), derv_reps = atoi(argv[3]), oab_reps = atoi(argv[4]);
     std::vector<char*> args; args.push_back(argv[0]);
@@ -722,6 +865,8 @@ int main(int argc, char **argv) {
     if (argc >= 5 && !strcmp(argv[1], "dumpnni")) return do_dumpnni(argc, argv);
     if (argc >= 5 && !strcmp(argv[1], "dumppars")) return do_dumppars(argc, argv);
     if (argc >= 4 && !strcmp(argv[1], "dumpem")) return do_dumpem(argc, argv);
+    if (argc >= 5 && !strcmp(argv[1], "dumplite")) return do_dumplite(argc, argv);
+    if (argc >= 4 && !strcmp(argv[1], "dumprepair")) return do_dumprepair(argc, argv);
     fprintf(stderr, "usage: %s dump <outdir> <iqtree args>\n       %s time <lnl_reps> <derv_reps> <oab_reps> <iqtree args>\n", argv[0], argv[0]);
     return 2;
 }
