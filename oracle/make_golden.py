@@ -12,6 +12,7 @@ runs only in the build container; the resulting fixtures are committed and trave
     python oracle/make_golden.py --aux      # tests/golden/aux/*.npz: RELL, pattern rates, mixture-weight EM of AUX_CASES
     python oracle/make_golden.py --em       # tests/golden/em/*.npz: RateFree::optimizeWithEM (EM_CASES; the inputs are the main fixtures)
     python oracle/make_golden.py --pars     # tests/golden/pars/*.npz: Fitch parsimony scores per branch + stepwise-addition trees (PARS_CASES)
+    python oracle/make_golden.py --repair   # tests/golden/repair/*.npz: the branch kernel's NaN / Inf repair on a zeroed vector (REPAIR_CASES)
 
 Synthetic alignments (codon, deep DNA tree, morphological, multifurcating) are generated here with fixed seeds.
 """
@@ -271,6 +272,18 @@ def pack_pars(case, seed, d):
         case, seed, nt, ns, m["score"], m["stepwise_score"], m["stepwise_check"], os.path.getsize(path) / 1024))
 
 
+REPAIR_CASES = ["dna_example_gtr_g4", "aa_lg_g4", "dna_deep_scaling", "codon_gy"]
+
+
+def pack_repair(case, d):
+    m = json.load(open(os.path.join(d, "metarepair.json")))
+    z = {"meta": json.dumps(m), "pattern_lh_repaired": rd(d, "pattern_lh_repaired.f64", np.float64)}
+    os.makedirs(os.path.join(OUT, "repair"), exist_ok=True)
+    path = os.path.join(OUT, "repair", case + ".npz")
+    np.savez_compressed(path, **z)
+    print("%-28s repair: lnl %.10f -> %.10f, zeroed %s of vector %s" % (case, m["lnl"], m["lnl_repaired"], m["zeroed"], m["vector"]))
+
+
 def pack_aux(case, d):
     m = json.load(open(os.path.join(d, "metax.json")))
     P, ns = m["nptn"], m["nsamples"]
@@ -364,6 +377,17 @@ def main():
                 print("%-28s em FAILED:\n%s" % (case, r.stdout[-1500:]))
                 continue
             pack_em(case, d)
+        shutil.rmtree(tmp, ignore_errors=True)
+        return
+    if sys.argv[1:2] == ["--repair"]:
+        for case in REPAIR_CASES:
+            d = os.path.join(tmp, "outr_" + case)
+            cmd = [HARNESS, "dumprepair", d] + cases[case] + ["-nt", "1", "-seed", "1", "-pre", os.path.join(tmp, "runr_" + case)]
+            r = subprocess.run(cmd, cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+            if r.returncode != 0:
+                print("%-28s repair FAILED:\n%s" % (case, r.stdout[-1500:]))
+                continue
+            pack_repair(case, d)
         shutil.rmtree(tmp, ignore_errors=True)
         return
     if sys.argv[1:2] == ["--pars"]:

@@ -810,11 +810,13 @@ static int do_time(int argc, char **argv) {
     }
     /* under -cuda: the same steps once more with every launch bracketed by CUDA events -> device time per kernel kind */
     std::ostringstream kstats;
+    int profiled_steps = 0;
     kstats << "{";
 #ifdef LK_CUDA_SHIM
     if (ON_DEVICE(tree) && lnl_reps > 0) {
         static const char *kind_name[] = {"prep", "partial", "branch", "theta", "derv", "frombuf", "newton", "misc", "rell", "em"};
         tree->lkCudaProfile(true, true);
+        profiled_steps = lnl_reps;
         for (int r = 0; r < lnl_reps; r++) {
             tree->clearAllPartialLH();
             tree->computeLikelihood();
@@ -847,10 +849,10 @@ static int do_time(int argc, char **argv) {
     printf("{\"ref_time\": true, \"kernel\": \"%s\", \"threads\": %d, \"nptn\": %zu, \"ntaxa\": %zu, \"blocks\": %zu, "
            "\"lnl\": %.17g, \"lnl_reps\": %d, \"lnl_s_mean\": %.6g, \"lnl_s_best\": %.6g, \"step_s_mean\": %.6g, \"step_s_total\": %.6g, "
            "\"df\": %.17g, \"ddf\": %.17g, \"derv_reps\": %d, \"derv_s_mean\": %.6g, "
-           "\"oab_lnl\": %.12f, \"oab_reps\": %d, \"oab_s_mean\": %.6g, \"nni_branches\": %d, \"nni_s_mean\": %.6g, \"setup_s\": %.4g, \"kernels\": %s}\n",
+           "\"oab_lnl\": %.12f, \"oab_reps\": %d, \"oab_s_mean\": %.6g, \"nni_branches\": %d, \"nni_s_mean\": %.6g, \"setup_s\": %.4g, \"profiled_steps\": %d, \"kernels\": %s}\n",
            ON_DEVICE(tree) ? "cuda" : (tree->sse == LK_EIGEN_SSE ? (instruction_set >= 7 ? "AVX" : "SSE") : "generic"),
            params.num_threads, P, ntaxa, blocks, lnl, lnl_reps, mean, lnl_t.empty() ? 0.0 : best, step_mean, step_sum,
-           df, ddf, derv_reps, t_derv, oab, oab_reps, t_oab, nni_done, t_nni, t_setup, kstats.str().c_str());
+           df, ddf, derv_reps, t_derv, oab, oab_reps, t_oab, nni_done, t_nni, t_setup, profiled_steps, kstats.str().c_str());
     return 0;
 }
 

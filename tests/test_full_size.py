@@ -1,0 +1,146 @@
+"""Parity at the BASELINE sizes (VERDICT r1 "untested configs"): 100 taxa x 1M patterns DNA GTR+G4, 200 x 200k protein LG+G4,
+64 x 50k codon GY, 100 x 10k LG+C20+G4 - tile rounds, 64-bit offsets, multi-wave reductions and tile_stride evening only differ there.
+
+The checker at these sizes is the UNMODIFIED reference itself (oracle/_ref/ref_harness, AVX + OpenMP on the box's host cores,
+`dumplite`): lnL, every stride-th scale-corrected pattern log-likelihood (>= 10k samples), scale_num of three vectors (exact) with
+strided partial_lh row sums, df / ddf / lnL-from-buffer on three branches.  Compared with it:
+  (1) the reference's OWN code on the engine (ref_harness_cuda -cuda: integration/ applied to the same sources), same files;
+  (2) the engine driven through the C ABI by the harness library, from the model inputs the reference dumped: one shard, and for
+      the DNA shape also 2 and 8 pattern shards (in-process engines that exchange their sums through the peer mailboxes).
+Tolerances as everywhere: lnL 1e-9 relative, per-pattern 1e-10, scale_num exact.
+"""
+import json
+import os
+import shutil
+import sys
+
+import numpy as np
+import pytest
+
+import dropin_util as du
+import golden_util as gu
+
+ROOT = du.ROOT
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402  (alphabets, PHYLIP writer and the distinct-pattern generator of the headline bench)
+
+SHAPES = {
+    "dna_100x1M_gtr_g4": dict(ntaxa=100, nptn=1000000, S=4, alphabet="ACGT", margs=["-m", "GTR+G4"], stride=97, shards=[1, 2, 8]),
+    "protein_200x200k_lg_g4": dict(ntaxa=200, nptn=200000, S=20, alphabet=bench.AA, margs=["-m", "LG+G4"], stride=19, shards=[1]),
+    "codon_64x50k_gy": dict(ntaxa=64, nptn=50000, S=61, alphabet=bench.SENSE, margs=["-st", "CODON", "-m", "GY"], stride=5, shards=[1]),
+    "protein_100x10k_lg_c20_g4": dict(ntaxa=100, nptn=10000, S=20, alphabet=bench.AA, margs=["-m", "LG+C20+G4"], stride=1, shards=[1, 2]),
+}
+if os.environ.get("LK_FULL_SIZE_SCALE"):        # debugging aid: shrink every shape
+    for _v in SHAPES.values():
+        _v["nptn"] = max(2000, int(_v["nptn"] * float(os.environ["LK_FULL_SIZE_SCALE"])))
+
+
+class Lite:
+    """a `dumplite` directory"""
+
+    def __init__(self, d):
+        self.d = d
+        self.meta = json.load(open(os.path.join(d, "meta.json")))
+        self.vectors = [tuple(int(x) for x in l.split()) for l in open(os.path.join(d, "vectors.txt")) if l.strip()]
+
+    def f64(self, name):
+        return np.fromfile(os.path.join(self.d, name), dtype=np.float64)
+
+    def i16(self, name):
+        return np.fromfile(os.path.join(self.d, name), dtype=np.int16)
+
+
+@pytest.fixture(scope="module", params=sorted(SHAPES))
+def shape(request, tmp_path_factory):
+    name = request.param
+    cfg = SHAPES[name]
+    assert os.path.exists(du.HARNESS_REF) and os.path.exists(du.HARNESS_CUDA), "reference harnesses not built (__graft_entry__.build())"
+    tmp = str(tmp_path_factory.mktemp(name))
+    names, nwk, states = bench.make_inputs(cfg["nptn"], cfg["ntaxa"], cfg["S"], seed=5)
+    aln, tre = os.path.join(tmp, "a.phy"), os.path.join(tmp, "a.nwk")
+    bench.write_phylip(aln, names, states, cfg["alphabet"])
+    open(tre, "w").write(nwk + "\n")
+    fargs = ["-s", aln] + cfg["margs"] + ["-te", tre, "-seed", "1"]
+    nthr = str(os.cpu_count() or 1)
+    du.run(du.HARNESS_REF, ["dumplite", os.path.join(tmp, "cpu"), str(cfg["stride"])] + fargs + ["-nt", nthr, "-pre", os.path.join(tmp, "rc")], tmp, timeout=3000)
+    yield dict(name=name, cfg=cfg, tmp=tmp, names=names, states=states, fargs=fargs, ref=Lite(os.path.join(tmp, "cpu")))
+    shutil.rmtree(tmp, ignore_errors=True)
+
+
+def _compare_lite(a, ref, S):
+    m, rm = a.meta, ref.meta
+    for k in ("nstates", "ncat", "nmix", "block", "nptn", "ntaxa", "root_branch"):
+        assert m[k] == rm[k], (k, m[k], rm[k])
+    assert abs(m["lnl"] - rm["lnl"]) <= gu.LNL_RTOL * abs(rm["lnl"]), (m["lnl"], rm["lnl"])
+    x, y = a.f64("pattern_lh_scaled_sample.f64"), ref.f64("pattern_lh_scaled_sample.f64")
+    assert x.size == y.size and x.size >= min(10000, rm["nptn"])
+    gu.rel_close(x, y, gu.PTN_RTOL, "pattern_lh samples")
+    assert a.vectors == ref.vectors and len(ref.vectors) == 3
+    rtol = 1e-7 if S >= 61 else gu.PARTIAL_RTOL
+    B = rm["block"]
+    for q in range(3):
+        assert np.array_equal(a.i16("vec%d_scale.i16" % q), ref.i16("vec%d_scale.i16" % q)), "scale_num of vector %r" % (ref.vectors[q],)
+        rs, rrs = a.f64("vec%d_rowsum_sample.f64" % q), ref.f64("vec%d_rowsum_sample.f64" % q)
+        assert np.all(np.abs(rs - rrs) <= rtol * B * np.maximum(np.abs(rrs), 1e-300)), "partial_lh row sums of vector %r" % (ref.vectors[q],)
+    assert np.array_equal(np.fromfile(os.path.join(a.d, "branch_ids.i32"), dtype=np.int32), np.fromfile(os.path.join(ref.d, "branch_ids.i32"), dtype=np.int32))
+    dv, rdv = a.f64("branch_derv.f64").reshape(3, 3), ref.f64("branch_derv.f64").reshape(3, 3)
+    for j in range(3):
+        tol = rtol * max(abs(rdv[j, 0]), abs(rdv[j, 1]), 1.0)
+        assert abs(dv[j, 0] - rdv[j, 0]) <= tol and abs(dv[j, 1] - rdv[j, 1]) <= tol, (j, dv[j], rdv[j])
+        assert abs(dv[j, 2] - rdv[j, 2]) <= gu.LNL_RTOL * abs(rdv[j, 2])
+
+
+@pytest.mark.gpu
+def test_reference_on_engine_full_size(shape, cuda_lib):
+    tmp, cfg = shape["tmp"], shape["cfg"]
+    d = os.path.join(tmp, "gpu")
+    du.run(du.HARNESS_CUDA, ["dumplite", d, str(cfg["stride"])] + shape["fargs"] + ["-nt", "1", "-pre", os.path.join(tmp, "rg"), "-cuda"], tmp, timeout=3000)
+    a = Lite(d)
+    assert a.meta["kernel"] == "cuda"
+    _compare_lite(a, shape["ref"], cfg["S"])
+
+
+@pytest.mark.gpu
+def test_engine_abi_full_size_and_shards(shape, cuda_lib):
+    import iqtree_b200
+    ref, cfg = shape["ref"], shape["cfg"]
+    rm = ref.meta
+    P = rm["nptn"]
+    st = shape["states"]
+    if cfg["S"] == 61:      # sense codon index -> the reference's 64-state code 16a + 4b + c (alignment.cpp:1337)
+        code = np.array(["ACGT".index(c[0]) * 16 + "ACGT".index(c[1]) * 4 + "ACGT".index(c[2]) for c in bench.SENSE], dtype=np.uint8)
+        st = code[st]
+    rtol = 1e-7 if cfg["S"] >= 61 else gu.PARTIAL_RTOL
+    for nshard in cfg["shards"]:
+        t = iqtree_b200.PhyloTree(lib=cuda_lib)
+        t.setAlignment(st, np.ones(P), names=shape["names"], seq_type=rm["seq_type"], nstates=rm["nstates"], state_unknown=rm["state_unknown"])
+        t.readAdjacency(open(os.path.join(ref.d, "tree_adj.txt")).read())
+        t.setModel(gu.FAMILY[rm["family"]], rm["ncat"], rm["nmix"], ref.f64("eval.f64"), ref.f64("evec.f64"), ref.f64("inv_evec.f64"),
+                   ref.f64("rates.f64"), ref.f64("props.f64"), ref.f64("mixprops.f64"), ref.f64("state_freq.f64"), rm["p_invar"])
+        t.setParams(rm["min_branch_length"], rm["max_branch_length"])
+        t.setDevices([0] * nshard)
+        t.initializeAllPartialLh()
+        t.clearAllPartialLH()
+        lnl = t.computeLikelihood()
+        assert abs(lnl - rm["lnl"]) <= gu.LNL_RTOL * abs(rm["lnl"]), "%d shards: lnL %.12f vs reference %.12f" % (nshard, lnl, rm["lnl"])
+        assert list(t.rootBranch()) == list(rm["root_branch"])
+        _, plh = t.computeLikelihood(pattern_lh=True)
+        gu.rel_close(plh[:: rm["stride"]], ref.f64("pattern_lh_scaled_sample.f64"), gu.PTN_RTOL, "%d shards: pattern_lh samples" % nshard)
+        B = rm["block"]
+        for q, (a, b) in enumerate(ref.vectors):
+            vec, comp = t.branchVector(a, b)
+            assert vec >= 0 and comp, "vector %d->%d not computed" % (a, b)
+            lh, sc = t.fetchVector(vec)
+            assert np.array_equal(sc, ref.i16("vec%d_scale.i16" % q)[: sc.size]), "%d shards: scale_num of vector %d->%d" % (nshard, a, b)
+            rs, rrs = lh[:: rm["stride"]].sum(axis=1), ref.f64("vec%d_rowsum_sample.f64" % q)
+            assert np.all(np.abs(rs - rrs) <= rtol * B * np.maximum(np.abs(rrs), 1e-300))
+            del lh
+        bid = np.fromfile(os.path.join(ref.d, "branch_ids.i32"), dtype=np.int32).reshape(3, 2)
+        rdv = ref.f64("branch_derv.f64").reshape(3, 3)
+        for j in range(3):
+            df, ddf = t.computeLikelihoodDerv(int(bid[j, 0]), int(bid[j, 1]), reset_theta=True)
+            fb = t.computeLikelihoodFromBuffer()
+            tol = rtol * max(abs(rdv[j, 0]), abs(rdv[j, 1]), 1.0)
+            assert abs(df - rdv[j, 0]) <= tol and abs(ddf - rdv[j, 1]) <= tol, (nshard, j, df, ddf, rdv[j])
+            assert abs(fb - rdv[j, 2]) <= gu.LNL_RTOL * abs(rdv[j, 2])
+        t.close()
