@@ -7,7 +7,10 @@ strided partial_lh row sums, df / ddf / lnL-from-buffer on three branches.  Comp
   (1) the reference's OWN code on the engine (ref_harness_cuda -cuda: integration/ applied to the same sources), same files;
   (2) the engine driven through the C ABI by the harness library, from the model inputs the reference dumped: one shard, and for
       the DNA shape also 2 and 8 pattern shards (in-process engines that exchange their sums through the peer mailboxes).
-Tolerances as everywhere: lnL 1e-9 relative, per-pattern 1e-10, scale_num exact.
+Tolerances as everywhere: lnL 1e-9 relative, per-pattern 1e-10, scale_num exact.  One exception, measured rather than chosen: for
+the 64-state codon eigen-system the reference's own two kernels (AVX vs the generic -fastlk one) disagree per pattern by 1.2e-9
+relative at 64 x 50k (ill-conditioned eigenvectors), so there the fixture also runs the generic kernel and the per-pattern
+bound is 3x the reference's own self-disagreement (never below 1e-10); lnL keeps 1e-9.
 """
 import json
 import os
@@ -63,7 +66,14 @@ def shape(request, tmp_path_factory):
     fargs = ["-s", aln] + cfg["margs"] + ["-te", tre, "-seed", "1"]
     nthr = str(os.cpu_count() or 1)
     du.run(du.HARNESS_REF, ["dumplite", os.path.join(tmp, "cpu"), str(cfg["stride"])] + fargs + ["-nt", nthr, "-pre", os.path.join(tmp, "rc")], tmp, timeout=3000)
-    yield dict(name=name, cfg=cfg, tmp=tmp, names=names, states=states, fargs=fargs, ref=Lite(os.path.join(tmp, "cpu")))
+    ref = Lite(os.path.join(tmp, "cpu"))
+    ref.ptn_rtol = gu.PTN_RTOL
+    if cfg["S"] >= 61:
+        du.run(du.HARNESS_REF, ["dumplite", os.path.join(tmp, "cpu_generic"), str(cfg["stride"])] + fargs + ["-fastlk", "-nt", nthr, "-pre", os.path.join(tmp, "rcg")], tmp, timeout=3000)
+        y, yg = ref.f64("pattern_lh_scaled_sample.f64"), Lite(os.path.join(tmp, "cpu_generic")).f64("pattern_lh_scaled_sample.f64")
+        ref.ptn_rtol = max(gu.PTN_RTOL, 3.0 * float(np.max(np.abs(y - yg) / np.abs(y))))
+        assert ref.ptn_rtol < 1e-7
+    yield dict(name=name, cfg=cfg, tmp=tmp, names=names, states=states, fargs=fargs, ref=ref)
     shutil.rmtree(tmp, ignore_errors=True)
 
 
@@ -74,7 +84,7 @@ def _compare_lite(a, ref, S):
     assert abs(m["lnl"] - rm["lnl"]) <= gu.LNL_RTOL * abs(rm["lnl"]), (m["lnl"], rm["lnl"])
     x, y = a.f64("pattern_lh_scaled_sample.f64"), ref.f64("pattern_lh_scaled_sample.f64")
     assert x.size == y.size and x.size >= min(10000, rm["nptn"])
-    gu.rel_close(x, y, gu.PTN_RTOL, "pattern_lh samples")
+    gu.rel_close(x, y, ref.ptn_rtol, "pattern_lh samples")
     assert a.vectors == ref.vectors and len(ref.vectors) == 3
     rtol = 1e-7 if S >= 61 else gu.PARTIAL_RTOL
     B = rm["block"]
@@ -125,7 +135,7 @@ def test_engine_abi_full_size_and_shards(shape, cuda_lib):
         assert abs(lnl - rm["lnl"]) <= gu.LNL_RTOL * abs(rm["lnl"]), "%d shards: lnL %.12f vs reference %.12f" % (nshard, lnl, rm["lnl"])
         assert list(t.rootBranch()) == list(rm["root_branch"])
         _, plh = t.computeLikelihood(pattern_lh=True)
-        gu.rel_close(plh[:: rm["stride"]], ref.f64("pattern_lh_scaled_sample.f64"), gu.PTN_RTOL, "%d shards: pattern_lh samples" % nshard)
+        gu.rel_close(plh[:: rm["stride"]], ref.f64("pattern_lh_scaled_sample.f64"), ref.ptn_rtol, "%d shards: pattern_lh samples" % nshard)
         B = rm["block"]
         for q, (a, b) in enumerate(ref.vectors):
             vec, comp = t.branchVector(a, b)
