@@ -59,6 +59,10 @@ struct DevChild {
 
 struct PeerMbox;
 
+/* B = 16 (S = 4, K = 4): everything the reductions need to form exp(eval * rate * len) * weight, as a KERNEL PARAMETER - the lanes build
+   their table entries without a dependent chain of global loads and without a block barrier */
+struct B16Tab { double cof[16]; double w[4]; int eig[4]; };
+
 /* everything a kernel needs to know about the engine, passed by value */
 struct DevView {
     int S, K, E, B;             /* states, blocks per pattern, eigensystems, B = S*K        */
@@ -74,7 +78,7 @@ struct DevView {
     double *arena; int16_t *scale;
     double *theta; int16_t *theta_sc; double *theta_meta;   /* theta_meta[0] = scale sum of the theta branch */
     double *pattern_lh, *pattern_lh_cat;
-    double *red; unsigned int *counter; double *result;
+    uint4 *red; unsigned int *counter; double *result;     /* red: 16-byte slots of the cross-block reduction (grid_reduce) */
     /* per-child transition tables built by the prep kernel:
        slot c: ech[K*S*S] then tab[(SU+1)*B]                                                   */
     double *tables; long long table_slot;   /* doubles per slot */
@@ -113,9 +117,10 @@ struct lkcuda_engine {
     int32_t *d_ptn_model; unsigned long long *d_state_mask;     /* LKCUDA_FLAG_SITEMODEL */
     double *d_plh, *d_plhcat, *d_plh_out;   /* d_plh_out: scale-corrected copy of _pattern_lh on its way to the host (lazy) */
     cudaStream_t dstream; cudaEvent_t ev_plh_ready, ev_plh_done; bool plh_pending;   /* asynchronous device-to-host fetch of d_plh_out (lazy) */
-    double *d_red; unsigned int *d_counter; double *d_result;
+    uint4 *d_red; unsigned int *d_counter; double *d_result;
     double *h_result;                       /* pinned */
-    double *h_mapped;                       /* pinned + mapped: [0..7] result block, [8] (as uint64) sequence number | error << 32, written by publish_result */
+    double *h_mapped;                       /* pinned + mapped: 8 slots {lo32, tag, hi32, tag}, tag = sequence number | error << 31, written by publish_result */
+    lkc::B16Tab b16tab;                     /* DNA + 4 categories: eval * rate, weights and eigensystem of the 4 blocks, passed to the B = 16 kernels by value */
     unsigned int result_seq;                /* sequence number of the last publishing launch */
     lkc::PeerMbox *d_mbox; lkc::PeerMbox **d_peer_tab; void *peer_opened[LKCUDA_MAX_PEERS]; unsigned int peer_seq;
     double *d_newton_out; double *h_newton_out;
@@ -174,7 +179,9 @@ inline bool valid_end(const lkcuda_engine *e, int32_t id) {
 
 /* call right before launching a kernel that ends in publish_result(): stamps e->v with the launch's sequence numbers */
 inline void next_result(lkcuda_engine *e) {
-    e->v.seq = ++e->result_seq;
+    e->result_seq = (e->result_seq + 1u) & 0x7fffffffu;      /* 31 bits travel in the tags of the host-mapped slots */
+    if (!e->result_seq) e->result_seq = 1u;
+    e->v.seq = e->result_seq;
     if (e->v.peer_world > 1) e->v.peer_seq = ++e->peer_seq;
 }
 
@@ -229,41 +236,61 @@ __device__ __forceinline__ void block_reduce(double (&val)[N], double *sh) {
         for (int i = 0; i < N; i++) {
             double x = lane < nwarp ? sh[i * 32 + lane] : 0.0;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+            for (int o = 16; o > 0; o >>= 1) if (o < nwarp) x += __shfl_down_sync(0xffffffffu, x, o);    /* lanes >= nwarp hold zeros: the skipped levels would add nothing */
             val[i] = x;
         }
     }
 }
 
-/* cross-block stage: every block deposits its N sums; the last block to arrive (ticket counter) adds the
-   deposits in block order and returns true in its thread 0 with the totals in `val`. The counter resets itself. */
+/* cross-block stage WITHOUT fences and atomics.  Thread 0 of every block deposits its N sums as 16-byte slots {lo32, tag, hi32, tag}:
+   each 8-byte unit carries its own tag (the scheme of NCCL's LL protocol; 8-byte stores are single transactions), tag = generation of
+   this reduction = *counter + 1.  Block 0 is the finisher: after its own deposit its threads pick up the blocks' slots (spinning on a slot
+   whose tags do not show the generation yet), add them in BLOCK order and return true in thread 0 with the totals in `val`; it then
+   advances *counter.  Launches of one engine are serialised on its stream, and the persistent Newton kernel only starts the next
+   reduction after the finisher released the next step, so a generation is never written while the previous one is still being read.
+   Deterministic run to run (fixed summation tree).  Measured on B200 (tools/reduce_bench.py, r2): the store + __threadfence + ticket
+   atomic + fence + re-read chain of the round-1 version cost ~3000 cycles after the last block's stream; this one ~1500. */
 template <int N>
-__device__ __forceinline__ bool grid_reduce(double (&val)[N], double *sh, double *red, unsigned int *counter) {
-    __shared__ bool is_last;
+__device__ __forceinline__ bool grid_reduce(double (&val)[N], double *sh, uint4 *red, unsigned int *counter) {
+    unsigned int gen = 0;
+    if (threadIdx.x == 0 || blockIdx.x == 0) { gen = __ldcg(counter) + 1u; if (!gen) gen = 1u; }      /* issued before the block reduction: off the critical path */
     block_reduce<N>(val, sh);
     if (threadIdx.x == 0) {
 #pragma unroll
-        for (int i = 0; i < N; i++) red[(size_t)blockIdx.x * RED_SLOTS + i] = val[i];
-        __threadfence();
-        unsigned int ticket = atomicAdd(counter, 1u);
-        is_last = (ticket == gridDim.x - 1);
+        for (int i = 0; i < N; i++) {
+            const unsigned long long bits = (unsigned long long)__double_as_longlong(val[i]);
+            asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(red + (size_t)blockIdx.x * RED_SLOTS + i),
+                         "r"((unsigned int)bits), "r"(gen), "r"((unsigned int)(bits >> 32)), "r"(gen) : "memory");
+        }
     }
-    __syncthreads();
-    if (!is_last) return false;
-    __threadfence();
+    if (blockIdx.x != 0) return false;
+    __syncthreads();        /* sh is reused below */
     double acc[N];
 #pragma unroll
     for (int i = 0; i < N; i++) acc[i] = 0.0;
+    const long long t0 = clock64();
+    bool lost = false;
     for (unsigned int b = threadIdx.x; b < gridDim.x; b += blockDim.x) {
+        const uint4 *src = red + (size_t)b * RED_SLOTS;
+        uint4 q[N];
+        for (;;) {
+            bool ok = true;
 #pragma unroll
-        for (int i = 0; i < N; i++) acc[i] += __ldcg(&red[(size_t)b * RED_SLOTS + i]);
+            for (int i = 0; i < N; i++) {
+                asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(q[i].x), "=r"(q[i].y), "=r"(q[i].z), "=r"(q[i].w) : "l"(src + i) : "memory");
+                ok = ok && q[i].y == gen && q[i].w == gen;
+            }
+            if (ok) break;
+            if (clock64() - t0 > 8000000000ll) { lost = true; break; }     /* ~4 s: a block never deposited (cannot happen in a healthy launch); do not hang the GPU */
+        }
+#pragma unroll
+        for (int i = 0; i < N; i++) acc[i] += lost ? __longlong_as_double(0x7ff8000000000000ll) : __longlong_as_double((long long)(((unsigned long long)q[i].z << 32) | q[i].x));
     }
-    __syncthreads();
     block_reduce<N>(acc, sh);
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int i = 0; i < N; i++) val[i] = acc[i];
-        *counter = 0u;
+        *reinterpret_cast<volatile unsigned int *>(counter) = gen;
     }
     return threadIdx.x == 0;
 }
@@ -320,16 +347,20 @@ static __device__ __noinline__ unsigned int peer_exchange(const DevView &v, doub
     return err;
 }
 
-/* steps 2 and 3: device result block, host-mapped block + sequence number (| error << 32) */
+/* steps 2 and 3: device result block, host-mapped slots {lo32, tag, hi32, tag} */
 static __device__ __forceinline__ void post_result(const DevView &v, const double (&r)[LKCUDA_NRESULT], unsigned int err) {
 #pragma unroll
     for (int i = 0; i < LKCUDA_NRESULT; i++) v.result[i] = r[i];
     if (v.host_result) {
-        volatile double *h = v.host_result;
+        /* slot i = {lo32, tag, hi32, tag}: every 8-byte unit carries the sequence number (| error << 31), so the host can accept a value
+           as soon as both of its tags show the number - no fence.sys (a PCIe round trip) between data and flag */
+        const unsigned int tag = (v.seq & 0x7fffffffu) | (err << 31);
 #pragma unroll
-        for (int i = 0; i < LKCUDA_NRESULT; i++) h[i] = r[i];
-        __threadfence_system();
-        *reinterpret_cast<volatile unsigned long long *>(v.host_result + LKCUDA_NRESULT) = (unsigned long long)v.seq | ((unsigned long long)err << 32);
+        for (int i = 0; i < LKCUDA_NRESULT; i++) {
+            const unsigned long long bits = (unsigned long long)__double_as_longlong(r[i]);
+            asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(v.host_result + 2 * i),
+                         "r"((unsigned int)bits), "r"(tag), "r"((unsigned int)(bits >> 32)), "r"(tag) : "memory");
+        }
     }
 }
 

@@ -222,8 +222,8 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
 #undef ALLOC
     if (ok) { rc = cudaMallocHost((void **)&e->h_result, sizeof(double) * LKCUDA_NRESULT); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMallocHost((void **)&e->h_newton_out, sizeof(double) * 8); ok = rc == cudaSuccess; }
-    if (ok) { rc = cudaHostAlloc((void **)&e->h_mapped, sizeof(double) * (LKCUDA_NRESULT + 8), cudaHostAllocMapped); ok = rc == cudaSuccess; }
-    if (ok) memset(e->h_mapped, 0, sizeof(double) * (LKCUDA_NRESULT + 8));
+    if (ok) { rc = cudaHostAlloc((void **)&e->h_mapped, sizeof(double) * 2 * LKCUDA_NRESULT, cudaHostAllocMapped); ok = rc == cudaSuccess; }
+    if (ok) memset(e->h_mapped, 0, sizeof(double) * 2 * LKCUDA_NRESULT);
     if (ok) { rc = cudaMallocHost((void **)&e->h_upload_vals, sizeof(unsigned int) * (lkcuda_engine::UPLOAD_MAX_CHUNKS + 1)); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMallocHost((void **)&e->h_upload_bad, sizeof(unsigned int) * 4); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaStreamCreateWithFlags(&e->cstream, cudaStreamNonBlocking); ok = rc == cudaSuccess; }
@@ -231,6 +231,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     if (ok) { rc = cudaEventCreateWithFlags(&e->ev_main_mark, cudaEventDisableTiming); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMemsetAsync(e->d_upload_flag, 0, 4 * sizeof(unsigned int), e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMemsetAsync(e->d_counter, 0, 4 * sizeof(unsigned int), e->stream); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMemsetAsync(e->d_red, 0, (size_t)e->red_blocks * RED_SLOTS * sizeof(uint4), e->stream); ok = rc == cudaSuccess; }    /* tags of generation 0 */
     if (ok) { rc = cudaMemsetAsync(e->d_result, 0, sizeof(double) * LKCUDA_NRESULT, e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMemsetAsync(e->d_theta_meta, 0, sizeof(double) * 8, e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMemsetAsync(e->d_states, 0, (size_t)cfg->ntaxa * v.st_stride + 4096, e->stream); ok = rc == cudaSuccess; }
@@ -251,7 +252,8 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     v.tables = NULL;
     {   /* device-side address of the host-mapped result block (identical under UVA; asked for all the same) */
         void *dp = NULL;
-        if (cudaHostGetDevicePointer(&dp, e->h_mapped, 0) == cudaSuccess) v.host_result = (double *)dp;
+        static const bool no_mapped = getenv("LKCUDA_NO_MAPPED_RESULT") && atoi(getenv("LKCUDA_NO_MAPPED_RESULT")) != 0;     /* measurement knob: results by copy */
+        if (!no_mapped && cudaHostGetDevicePointer(&dp, e->h_mapped, 0) == cudaSuccess) v.host_result = (double *)dp;
         else { cudaGetLastError(); v.host_result = NULL; }
     }
     v.seq = 0; v.peer_world = 1; v.peer_rank = 0; v.peer_seq = 0; v.peer_mbox = NULL;
@@ -473,6 +475,12 @@ int lkcuda_set_model(lkcuda_engine *e, const double *eval, const double *evec, c
     LK_CUDA(e, cudaMemcpyAsync(e->d_weight, blk_weight, K * 8, cudaMemcpyHostToDevice, e->stream));
     if (!sm) LK_CUDA(e, cudaMemcpyAsync(e->d_tip, tip_partial_lh, (size_t)(v.SU + 1) * E * S * 8, cudaMemcpyHostToDevice, e->stream));
     LK_CUDA(e, cudaStreamSynchronize(e->stream));   /* the sources are pageable caller memory */
+    if (!sm && v.S == 4 && v.K == 4) {      /* parameter block of the B = 16 reductions (same products as build_val forms on the device) */
+        for (int k = 0; k < 4; k++) {
+            e->b16tab.w[k] = blk_weight[k]; e->b16tab.eig[k] = blk_eigen[k];
+            for (int i = 0; i < 4; i++) e->b16tab.cof[4 * k + i] = eval[blk_eigen[k] * 4 + i] * blk_rate[k];
+        }
+    }
     e->model_set = true; e->theta_ready = false;
     return LKCUDA_OK;
 }
@@ -490,13 +498,23 @@ int lkcuda_wait_result(lkcuda_engine *e, double *result) {
     LK_ENTER(e);
     if (!result) return fail(e, LKCUDA_ERR_ARG, "null result");
     if (!e->v.host_result || e->result_seq == 0) return lkcuda_read_result(e, result);
-    volatile unsigned long long *flag = reinterpret_cast<volatile unsigned long long *>(e->h_mapped + LKCUDA_NRESULT);
-    unsigned long long f = *flag;
-    if ((unsigned int)f != e->result_seq) {
+    /* slot i = two 8-byte words {lo32 | tag << 32, hi32 | tag << 32}; tag = sequence number | error << 31 (post_result): a value is complete
+       when both of its tags show the number, the block when all eight values are */
+    volatile unsigned long long *slots = reinterpret_cast<volatile unsigned long long *>(e->h_mapped);
+    const unsigned int want = e->result_seq;
+    unsigned long long words[2 * LKCUDA_NRESULT];
+    auto all_there = [&](unsigned long long &last) {
+        for (int i = 2 * LKCUDA_NRESULT - 1; i >= 0; i--) {
+            words[i] = slots[i]; last = words[i] >> 32;
+            if (((unsigned int)last & 0x7fffffffu) != want) return false;
+        }
+        return true;
+    };
+    unsigned long long f = 0;
+    if (!all_there(f)) {
         auto next_query = std::chrono::steady_clock::now() + std::chrono::microseconds(200);
         for (unsigned int spin = 0;; spin++) {
-            f = *flag;
-            if ((unsigned int)f == e->result_seq) break;
+            if (all_there(f)) break;
 #if defined(__x86_64__) || defined(__i386__)
             __builtin_ia32_pause();
 #endif
@@ -504,8 +522,7 @@ int lkcuda_wait_result(lkcuda_engine *e, double *result) {
                 /* the stream drained (or died) without the number showing up: take the slow path, which also reports CUDA errors */
                 cudaError_t q = cudaStreamQuery(e->stream);
                 if (q != cudaErrorNotReady) {
-                    f = *flag;
-                    if (q == cudaSuccess && (unsigned int)f == e->result_seq) break;
+                    if (q == cudaSuccess && all_there(f)) break;
                     if (q != cudaSuccess) return cuda_fail(e, q, "reduction kernel");
                     return lkcuda_read_result(e, result);
                 }
@@ -513,9 +530,11 @@ int lkcuda_wait_result(lkcuda_engine *e, double *result) {
             }
         }
     }
-    __atomic_thread_fence(__ATOMIC_ACQUIRE);
-    for (int i = 0; i < LKCUDA_NRESULT; i++) result[i] = ((volatile double *)e->h_mapped)[i];
-    if ((f >> 32) & 1ull) return fail(e, LKCUDA_ERR_STATE, "cross-GPU all-reduce timed out: a peer never enqueued its reduction");
+    for (int i = 0; i < LKCUDA_NRESULT; i++) {
+        const unsigned long long bits = (words[2 * i] & 0xffffffffull) | (words[2 * i + 1] << 32);
+        memcpy(&result[i], &bits, 8);
+    }
+    if ((f >> 31) & 1ull) return fail(e, LKCUDA_ERR_STATE, "cross-GPU all-reduce timed out: a peer never enqueued its reduction");
     return upload_verdict(e);
 }
 

@@ -186,52 +186,130 @@ __global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) branch_kernel(
     if (grid_reduce<4>(acc, sred, v.red, v.counter)) lnl_finish(v, acc, acc[1]);
 }
 
-/* DNA + 4 categories, tip end (the root branch of every full-tree lnL): one lane per pattern, next pattern's operands requested
-   before the current one is reduced.  tipB rows are 18 doubles apart: lanes with different states read different banks. */
+/* ---- DNA + 4 categories (B = 16, 128 bytes per pattern): the mapping of the dedicated streaming kernels ----
+   FOUR lanes share a pattern; lane c of the group owns category c = one 32-byte sector, so one warp-wide LDG.E.256 covers 1 KB of
+   contiguous memory = 8 whole 128-byte lines (one lane per pattern would touch 32 different lines per instruction).  A warp works on
+   tiles of 32 patterns = 4 KB: load u (0..3) of lane l moves bytes [1024u + 32l, +32) of the tile, i.e. category l&3 of pattern
+   8u + (l>>2).  The sums over the four categories are finished by a transposed butterfly (b16_gather: 3 shuffles finish 4 patterns);
+   afterwards lane l owns pattern 8(l&3) + (l>>2) of the tile for the tail (division / log, frequency weighting, pattern_lh store): all
+   32 lanes stay busy and the per-pattern arrays are still read and written as contiguous 256-byte pieces.  The NEXT tile's sectors are
+   requested before the current tile is reduced.  Tiles go to warps round-robin with the warp index running over the BLOCKS first, so
+   the warps that get one tile more than the others are spread over all SMs. */
+struct B16Lane { int lane, c, pg; long long t0, nw, ntile; };
+
+__device__ __forceinline__ B16Lane b16_lane(const DevView &v) {
+    B16Lane m;
+    m.lane = threadIdx.x & 31; m.c = m.lane & 3; m.pg = m.lane >> 2;
+    m.nw = (long long)gridDim.x * (blockDim.x >> 5);
+    m.t0 = (long long)(threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+    m.ntile = (v.NP + 31) >> 5;
+    return m;
+}
+
+__device__ __forceinline__ d4 ld_coherent256(const double *p) {      /* data written earlier by this very launch */
+    d4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p) : "memory");
+    return r;
+}
+
+/* the four sectors of this lane in tile t of a B = 16 vector (zeros beyond the last pattern) */
+template <bool COHERENT>
+__device__ __forceinline__ void b16_load(const double *vec, long long t, const B16Lane &m, long long NP, d4 (&x)[4]) {
+    const double *src = vec + t * 512 + m.lane * 4;
+    const long long p0 = t * 32 + m.pg;
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        if (p0 + 8 * u < NP) x[u] = COHERENT ? ld_coherent256(src + 128 * u) : ld_stream256(src + 128 * u);
+        else { x[u].x = 0.0; x[u].y = 0.0; x[u].z = 0.0; x[u].w = 0.0; }
+    }
+}
+
+/* s[u] = this lane's (category c) share of pattern 8u + pg; returns the sum over the group's four lanes of s[c]: the finished value of
+   pattern 8c + pg.  Fixed order (s_c0 + s_c1) + (s_c2 + s_c3) in every lane. */
+__device__ __forceinline__ double b16_gather(const double (&s)[4], int c) {
+    const bool b0 = (c & 1) != 0, b1 = (c & 2) != 0;
+    double a0 = b0 ? s[1] : s[0], a1 = b0 ? s[3] : s[2];
+    const double g0 = b0 ? s[0] : s[1], g1 = b0 ? s[2] : s[3];
+    a0 += __shfl_xor_sync(0xffffffffu, g0, 1);
+    a1 += __shfl_xor_sync(0xffffffffu, g1, 1);
+    const double r = b1 ? a1 : a0, g = b1 ? a0 : a1;
+    return r + __shfl_xor_sync(0xffffffffu, g, 2);
+}
+
+__device__ __forceinline__ double dot4(const d4 &x, const double (&w)[4]) {
+    double s = x.x * w[0];
+    s = fma(x.y, w[1], s); s = fma(x.z, w[2], s); s = fma(x.w, w[3], s);
+    return s;
+}
+
+/* lane c's table entries of category c straight from the kernel parameters (build_val's operations, no memory traffic, no barrier) */
+template <bool DERIV>
+__device__ __forceinline__ void b16_lane_tables(const B16Tab &tab, int c, double len, double (&w0)[4], double (&w1)[4], double (&w2)[4]) {
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const double cof = tab.cof[4 * c + i];
+        const double x = exp(cof * len) * tab.w[c];
+        w0[i] = x;
+        if (DERIV) { const double y = cof * x; w1[i] = y; w2[i] = cof * y; }
+    }
+}
+
+static int b16_grid(const lkcuda_engine *e, long long NP) {
+    long long need = (((NP + 31) >> 5) + (RED_THREADS / 32) - 1) / (RED_THREADS / 32);
+    long long cap = (long long)e->num_sms * 2;
+    if (cap > e->red_blocks) cap = e->red_blocks;
+    if (need < 1) need = 1;
+    return (int)(need < cap ? need : cap);
+}
+
+/* tipB rows are 18 doubles apart: lanes with different states read different banks */
 #define B16_TIPROW 18
-__global__ void __launch_bounds__(RED_THREADS, 2) branch_tip_b16_kernel(DevView v, int dad, int node, double len) {
-    __shared__ __align__(32) double val[16];
+
+/* DNA + 4 categories, tip end (the root branch of every full-tree lnL) */
+__global__ void __launch_bounds__(RED_THREADS, 2) branch_tip_b16_kernel(DevView v, B16Tab tab, int dad, int node, double len) {
     __shared__ __align__(32) double tipB[32 * B16_TIPROW];
     __shared__ double sred[4 * 32];
-    build_val(v, len, val, NULL, NULL);
-    __syncthreads();
-    for (int idx = threadIdx.x; idx < (v.SU + 1) * 16; idx += blockDim.x) {
-        const int st = idx >> 4, j = idx & 15;
-        tipB[st * B16_TIPROW + j] = val[j] * v.tip[((long long)st * v.E + v.blk_eigen[j >> 2]) * 4 + (j & 3)];
-    }
-    __syncthreads();
+    const B16Lane m = b16_lane(v);
     const double *lh_node = vec_lh(v, node);
     const int16_t *sc_node = vec_sc(v, node);
     const uint8_t *st = tip_states(v, dad);
-    const long long nthr = (long long)gridDim.x * blockDim.x;
-    long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    long long t = m.t0;
     d4 n[4]; double ninv = 0.0, nf = 0.0; int nst = 0, nsc = 0;
-    if (p < v.NP) {
-#pragma unroll
-        for (int u = 0; u < 4; u++) n[u] = ld_stream256(lh_node + p * 16 + 4 * u);
-        ninv = v.invar[p]; nf = p < v.P ? v.freq[p] : 0.0; nst = st[p]; nsc = sc_node[p];
+#define B16_BRANCH_FETCH() do { \
+        b16_load<false>(lh_node, t, m, v.NP, n); \
+        const long long pl = t * 32 + m.lane, pt = t * 32 + 8 * m.c + m.pg; \
+        nst = pl < v.NP ? (int)st[pl] : 0; \
+        if (pt < v.NP) { ninv = v.invar[pt]; nf = pt < v.P ? v.freq[pt] : 0.0; nsc = sc_node[pt]; } \
+    } while (0)
+    if (t < m.ntile) B16_BRANCH_FETCH();
+    for (int idx = threadIdx.x; idx < (v.SU + 1) * 16; idx += blockDim.x) {
+        const int s = idx >> 4, j = idx & 15;
+        const double tp = v.tip[((long long)s * v.E + tab.eig[j >> 2]) * 4 + (j & 3)];
+        tipB[s * B16_TIPROW + j] = exp(tab.cof[j] * len) * tab.w[j >> 2] * tp;
     }
-    while (p < v.NP) {
+    __syncthreads();
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    while (t < m.ntile) {
         const d4 x[4] = {n[0], n[1], n[2], n[3]};
         const double inv = ninv, f = nf;
-        const int state = nst, sc = nsc;
-        const long long pc = p;
-        p += nthr;
-        if (p < v.NP) {
-#pragma unroll
-            for (int u = 0; u < 4; u++) n[u] = ld_stream256(lh_node + p * 16 + 4 * u);
-            ninv = v.invar[p]; nf = p < v.P ? v.freq[p] : 0.0; nst = st[p]; nsc = sc_node[p];
-        }
-        const double2 *t = reinterpret_cast<const double2 *>(tipB + state * B16_TIPROW);
-        double s0 = 0.0;
+        const int stl = nst, sc = nsc;
+        const long long pt = t * 32 + 8 * m.c + m.pg;
+        t += m.nw;
+        if (t < m.ntile) B16_BRANCH_FETCH();
+        double s[4];
 #pragma unroll
         for (int u = 0; u < 4; u++) {
-            const double2 a = t[2 * u], b = t[2 * u + 1];
-            s0 = fma(a.x, x[u].x, s0); s0 = fma(a.y, x[u].y, s0); s0 = fma(b.x, x[u].z, s0); s0 = fma(b.y, x[u].w, s0);
+            const int state = __shfl_sync(0xffffffffu, stl, 8 * u + m.pg);
+            const double2 *tb = reinterpret_cast<const double2 *>(tipB + state * B16_TIPROW + 4 * m.c);
+            const double2 a = tb[0], b = tb[1];
+            double q = a.x * x[u].x;
+            q = fma(a.y, x[u].y, q); q = fma(b.x, x[u].z, q); q = fma(b.y, x[u].w, q);
+            s[u] = q;
         }
-        lnl_tail_vals(v, pc, s0, sc, inv, f, acc);
+        const double lh = b16_gather(s, m.c);
+        if (pt < v.NP) lnl_tail_vals(v, pt, lh, sc, inv, f, acc);
     }
+#undef B16_BRANCH_FETCH
     if (grid_reduce<4>(acc, sred, v.red, v.counter)) lnl_finish(v, acc, acc[1]);
 }
 
@@ -410,68 +488,90 @@ __device__ __forceinline__ void derv_finish(const DevView &v, const double (&acc
     publish_result(v, r);
 }
 
-__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
-
-/* the streaming pass of derv_b16_kernel / newton_b16_kernel: acc = {df, ddf, prob_const, df_const, ddf_const} partial sums of this thread.
-   DNA + 4 categories (128 bytes per pattern): one lane per pattern, the NEXT pattern's four sectors are requested before the current one
-   is reduced and the one after that is pulled into L2, so a lane always has 256 bytes on their way.  The first requests go out before
-   the exp() table is built. */
-__device__ __forceinline__ d4 ld_theta256(const double *p, bool coherent) {      /* coherent: theta_all was written earlier by this very launch */
-    if (!coherent) return ld_stream256(p);
-    d4 r;
-    asm volatile("ld.global.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p) : "memory");
-    return r;
-}
-
-template <bool COHERENT>
-__device__ __forceinline__ void derv_b16_stream(const DevView &v, double len, double *val0, double *val1, double *val2, double (&acc)[5]) {
-    const long long nthr = (long long)gridDim.x * blockDim.x;
-    long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+/* the streaming pass of derv_b16_kernel / newton_b16_kernel (mapping: see B16Lane): acc = {df, ddf, prob_const, df_const, ddf_const}
+   partial sums of this thread.  The first tile's requests go out before the exp() tables are built; lane c copies the 12 table entries
+   of its category into registers.  COHERENT: theta_all was written earlier by this very launch (by this very lane). */
+template <bool COHERENT, bool WREG>
+__device__ __forceinline__ void derv_b16_stream(const DevView &v, const B16Tab &tab, double len, double *val0, double *val1, double *val2, double (&acc)[5]) {
+    const B16Lane m = b16_lane(v);
+    long long t = m.t0;
     d4 n[4]; double ninv = 0.0, nf = 0.0;
-    if (p < v.NP) {
+#define B16_DERV_FETCH() do { \
+        b16_load<COHERENT>(v.theta, t, m, v.NP, n); \
+        const long long pt = t * 32 + 8 * m.c + m.pg; \
+        if (pt < v.NP) { ninv = v.invar[pt]; nf = pt < v.P ? v.freq[pt] : 0.0; } \
+    } while (0)
+    if (t < m.ntile) B16_DERV_FETCH();
+    double w0[4], w1[4], w2[4];
+    b16_lane_tables<true>(tab, m.c, len, w0, w1, w2);
+    if (!WREG) {        /* every lane of category c stores the same values; a lane only ever re-reads after its own store */
 #pragma unroll
-        for (int u = 0; u < 4; u++) n[u] = ld_theta256(v.theta + p * 16 + 4 * u, COHERENT);
-        ninv = v.invar[p]; nf = p < v.P ? v.freq[p] : 0.0;
-        if (p + nthr < v.NP) prefetch_l2(v.theta + (p + nthr) * 16);
+        for (int i = 0; i < 4; i++) {
+            *reinterpret_cast<volatile double *>(val0 + 4 * m.c + i) = w0[i]; *reinterpret_cast<volatile double *>(val1 + 4 * m.c + i) = w1[i];
+            *reinterpret_cast<volatile double *>(val2 + 4 * m.c + i) = w2[i];
+        }
     }
-    build_val(v, len, val0, val1, val2);
-    __syncthreads();
 #pragma unroll
     for (int i = 0; i < 5; i++) acc[i] = 0.0;
-    while (p < v.NP) {
+    while (t < m.ntile) {
         const d4 x[4] = {n[0], n[1], n[2], n[3]};
         const double inv = ninv, f = nf;
-        const bool observed = p < v.P;
-        p += nthr;
-        if (p < v.NP) {
+        const long long pt = t * 32 + 8 * m.c + m.pg;
+        t += m.nw;
+        if (t < m.ntile) B16_DERV_FETCH();
+        if (!WREG) {        /* the persistent Newton kernel is short of registers: the tables are re-read from shared memory per tile */
 #pragma unroll
-            for (int u = 0; u < 4; u++) n[u] = ld_theta256(v.theta + p * 16 + 4 * u, COHERENT);
-            ninv = v.invar[p]; nf = p < v.P ? v.freq[p] : 0.0;
-            if (p + nthr < v.NP) prefetch_l2(v.theta + (p + nthr) * 16);
+            for (int i = 0; i < 4; i++) {
+                w0[i] = *reinterpret_cast<volatile double *>(val0 + 4 * m.c + i); w1[i] = *reinterpret_cast<volatile double *>(val1 + 4 * m.c + i);
+                w2[i] = *reinterpret_cast<volatile double *>(val2 + 4 * m.c + i);
+            }
         }
-        double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+        double s0[4], s1[4], s2[4];
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const double *w0 = val0 + 4 * u, *w1 = val1 + 4 * u, *w2 = val2 + 4 * u;
-            m0 = fma(x[u].x, w0[0], m0); m0 = fma(x[u].y, w0[1], m0); m0 = fma(x[u].z, w0[2], m0); m0 = fma(x[u].w, w0[3], m0);
-            m1 = fma(x[u].x, w1[0], m1); m1 = fma(x[u].y, w1[1], m1); m1 = fma(x[u].z, w1[2], m1); m1 = fma(x[u].w, w1[3], m1);
-            m2 = fma(x[u].x, w2[0], m2); m2 = fma(x[u].y, w2[1], m2); m2 = fma(x[u].z, w2[2], m2); m2 = fma(x[u].w, w2[3], m2);
+        for (int u = 0; u < 4; u++) { s0[u] = dot4(x[u], w0); s1[u] = dot4(x[u], w1); s2[u] = dot4(x[u], w2); }
+        const double m0 = b16_gather(s0, m.c), m1 = b16_gather(s1, m.c), m2 = b16_gather(s2, m.c);
+        if (pt < v.NP) {
+            const double lh = fabs(m0 + inv);
+            if (pt < v.P) {
+                const double df_frac = m1 / lh, ddf_frac = m2 / lh, t1 = df_frac * f, t2 = ddf_frac * f;
+                acc[0] += t1;
+                acc[1] += t2 - t1 * df_frac;
+            } else { acc[2] += lh; acc[3] += m1; acc[4] += m2; }
         }
-        const double lh = fabs(m0 + inv);
-        if (observed) {
-            const double df_frac = m1 / lh, ddf_frac = m2 / lh, t1 = df_frac * f, t2 = ddf_frac * f;
-            acc[0] += t1;
-            acc[1] += t2 - t1 * df_frac;
-        } else { acc[2] += lh; acc[3] += m1; acc[4] += m2; }
     }
+#undef B16_DERV_FETCH
 }
 
-__global__ void __launch_bounds__(RED_THREADS, 2) derv_b16_kernel(DevView v, double len) {
-    __shared__ __align__(32) double val0[16], val1[16], val2[16];
+__global__ void __launch_bounds__(RED_THREADS, 2) derv_b16_kernel(DevView v, B16Tab tab, double len) {
     __shared__ double sred[5 * 32];
     double acc[5];
-    derv_b16_stream<false>(v, len, val0, val1, val2, acc);
+    derv_b16_stream<false, true>(v, tab, len, NULL, NULL, NULL, acc);
     if (grid_reduce<5>(acc, sred, v.red, v.counter)) derv_finish(v, acc);
+}
+
+/* lnL from theta_all (computeLikelihoodFromBufferEigenSIMD, phylokernel.h:1023-1192), B = 16: the same stream with one dot product */
+__global__ void __launch_bounds__(RED_THREADS, 2) frombuf_b16_kernel(DevView v, B16Tab tab, double len) {
+    __shared__ double sred[4 * 32];
+    const B16Lane m = b16_lane(v);
+    long long t = m.t0;
+    d4 n[4];
+    if (t < m.ntile) b16_load<false>(v.theta, t, m, v.NP, n);
+    double w0[4], wu1[4], wu2[4];
+    b16_lane_tables<false>(tab, m.c, len, w0, wu1, wu2);
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    while (t < m.ntile) {
+        const d4 x[4] = {n[0], n[1], n[2], n[3]};
+        const long long pt = t * 32 + 8 * m.c + m.pg;
+        t += m.nw;
+        if (t < m.ntile) b16_load<false>(v.theta, t, m, v.NP, n);
+        double s0[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) s0[u] = dot4(x[u], w0);
+        const double lh = b16_gather(s0, m.c);
+        /* scale factors were folded into theta_meta[0] when theta_all was built: sc = 0 for observed patterns */
+        if (pt < v.NP) lnl_tail(v, pt, lh, pt < v.P ? 0 : (int)v.theta_sc[pt - v.P], acc);
+    }
+    if (grid_reduce<4>(acc, sred, v.red, v.counter)) lnl_finish(v, acc, v.theta_meta[0]);
 }
 
 /* ---- Optimization::minimizeNewton (optimization.cpp:388-465) as ONE persistent launch (DNA + 4 categories) ----
@@ -519,14 +619,14 @@ __device__ __forceinline__ void newton_advance(NewtonCtl &c, double x1, double x
     c.x = c.rts;
 }
 
-template <bool TIP>
-__device__ __forceinline__ void theta_derv_b16_stream(const DevView &v, int dad, int node, double len, double *val0, double *val1, double *val2,
-                                                      double *tipT, double (&acc)[6]);
+template <bool TIP, bool WREG, bool PF>
+__device__ __forceinline__ void theta_derv_b16_stream(const DevView &v, const B16Tab &tab, int dad, int node, double len, double *val0, double *val1,
+                                                      double *val2, double *tipT, double (&acc)[6]);
 
 /* BUILD 0: theta_all is there; 1 / 2: the first step builds it from the branch's two ends (dad a tip / an internal vector) while it
    forms the first df/ddf (the pass of theta_derv_b16_kernel) - every lane later re-reads exactly the theta rows it wrote itself */
 template <int BUILD>
-__global__ void __launch_bounds__(RED_THREADS, 2) newton_b16_kernel(DevView v, NewtonCtl *ctl, int dad, int node, double x1, double xguess, double x2, double xacc, int maxNRStep) {
+__global__ void __launch_bounds__(RED_THREADS, 2) newton_b16_kernel(DevView v, B16Tab tab, NewtonCtl *ctl, int dad, int node, double x1, double xguess, double x2, double xacc, int maxNRStep) {
     __shared__ __align__(32) double val0[16], val1[16], val2[16];
     __shared__ __align__(32) double tipT[BUILD == 1 ? 32 * B16_TIPROW : 4];
     __shared__ double sred[6 * 32];
@@ -539,13 +639,13 @@ __global__ void __launch_bounds__(RED_THREADS, 2) newton_b16_kernel(DevView v, N
         bool elected;
         if (BUILD != 0 && it == 0) {
             double a6[6];
-            theta_derv_b16_stream<BUILD == 1>(v, dad, node, x, val0, val1, val2, tipT, a6);
+            theta_derv_b16_stream<BUILD == 1, false, false>(v, tab, dad, node, x, val0, val1, val2, tipT, a6);
             elected = grid_reduce<6>(a6, sred, v.red, v.counter);
             if (elected) v.theta_meta[0] = a6[5];
 #pragma unroll
             for (int i = 0; i < 5; i++) acc[i] = a6[i];
         } else {
-            derv_b16_stream<BUILD != 0>(v, x, val0, val1, val2, acc);
+            derv_b16_stream<BUILD != 0, false>(v, tab, x, val0, val1, val2, acc);
             elected = grid_reduce<5>(acc, sred, v.red, v.counter);
         }
         if (elected) {          /* thread 0 of the block that arrived last */
@@ -593,67 +693,101 @@ __global__ void __launch_bounds__(RED_THREADS, 2) newton_b16_kernel(DevView v, N
     }
 }
 
-/* theta_all build + first df/ddf in one pass (B = 16): lane = pattern; reads the node vector and the dad vector (or the dad
-   tip's state), writes theta_all, keeps the three dot products.  acc[5] carries the scale sum that theta_kernel leaves in theta_meta. */
-template <bool TIP>
-__device__ __forceinline__ void theta_derv_b16_stream(const DevView &v, int dad, int node, double len, double *val0, double *val1, double *val2,
-                                                      double *tipT, double (&acc)[6]) {
-    build_val(v, len, val0, val1, val2);
-    if (TIP) {
-        for (int idx = threadIdx.x; idx < (v.SU + 1) * 16; idx += blockDim.x) {
-            const int st = idx >> 4, j = idx & 15;
-            tipT[st * B16_TIPROW + j] = v.tip[((long long)st * v.E + v.blk_eigen[j >> 2]) * 4 + (j & 3)];
-        }
-    }
-    __syncthreads();
+/* theta_all build + first df/ddf in one pass (B = 16; mapping: see B16Lane): reads the node vector and the dad vector (or the dad
+   tip's state), writes theta_all at the addresses derv_b16_stream reads with the same lane, keeps the three dot products.
+   acc[5] carries the scale sum that theta_kernel leaves in theta_meta. */
+template <bool TIP, bool WREG, bool PF>
+__device__ __forceinline__ void theta_derv_b16_stream(const DevView &v, const B16Tab &tab, int dad, int node, double len, double *val0, double *val1,
+                                                      double *val2, double *tipT, double (&acc)[6]) {
+    const B16Lane m = b16_lane(v);
     const double *lh_node = vec_lh(v, node), *lh_dad = TIP ? NULL : vec_lh(v, dad);
     const int16_t *sc_node = vec_sc(v, node), *sc_dad = TIP ? NULL : vec_sc(v, dad);
     const uint8_t *st = TIP ? tip_states(v, dad) : NULL;
-    const long long nthr = (long long)gridDim.x * blockDim.x;
+    long long t = m.t0;
+    d4 n[4]; int nst = 0;       /* PF (tip end only): the next tile's node sectors are requested ahead; two vectors: 8 loads per lane go out together */
+    if (PF && t < m.ntile) {
+        b16_load<false>(lh_node, t, m, v.NP, n);
+        const long long pl = t * 32 + m.lane; nst = pl < v.NP ? (int)st[pl] : 0;
+    }
+    if (TIP) {
+        for (int idx = threadIdx.x; idx < (v.SU + 1) * 16; idx += blockDim.x) {
+            const int s = idx >> 4, j = idx & 15;
+            tipT[s * B16_TIPROW + j] = v.tip[((long long)s * v.E + tab.eig[j >> 2]) * 4 + (j & 3)];
+        }
+    }
+    double w0[4], w1[4], w2[4];
+    b16_lane_tables<true>(tab, m.c, len, w0, w1, w2);
+    if (!WREG) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            *reinterpret_cast<volatile double *>(val0 + 4 * m.c + i) = w0[i]; *reinterpret_cast<volatile double *>(val1 + 4 * m.c + i) = w1[i];
+            *reinterpret_cast<volatile double *>(val2 + 4 * m.c + i) = w2[i];
+        }
+    }
+    if (TIP) __syncthreads();
 #pragma unroll
     for (int i = 0; i < 6; i++) acc[i] = 0.0;
-    for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < v.NP; p += nthr) {
+    while (t < m.ntile) {
+        const long long tc = t, pt = t * 32 + 8 * m.c + m.pg;
         d4 x[4], y[4];
+        if (PF) {
 #pragma unroll
-        for (int u = 0; u < 4; u++) x[u] = ld_stream256(lh_node + p * 16 + 4 * u);
-        if (TIP) {
-            const double2 *t = reinterpret_cast<const double2 *>(tipT + (int)st[p] * B16_TIPROW);
-#pragma unroll
-            for (int u = 0; u < 4; u++) { const double2 a = t[2 * u], b = t[2 * u + 1]; y[u].x = a.x; y[u].y = a.y; y[u].z = b.x; y[u].w = b.y; }
+            for (int u = 0; u < 4; u++) x[u] = n[u];
         } else {
-#pragma unroll
-            for (int u = 0; u < 4; u++) y[u] = ld_stream256(lh_dad + p * 16 + 4 * u);
+            b16_load<false>(lh_node, tc, m, v.NP, x);
+            if (!TIP) b16_load<false>(lh_dad, tc, m, v.NP, y);
+            else { const long long pl = tc * 32 + m.lane; nst = pl < v.NP ? (int)st[pl] : 0; }
         }
-        const double inv = v.invar[p], f = p < v.P ? v.freq[p] : 0.0;
-        const int sc = sc_node[p] + (TIP ? 0 : sc_dad[p]);
-        double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+        const int stl = nst;
+        double inv = 0.0, f = 0.0; int sc = 0;
+        if (pt < v.NP) { inv = v.invar[pt]; f = pt < v.P ? v.freq[pt] : 0.0; sc = sc_node[pt] + (TIP ? 0 : sc_dad[pt]); }
+        t += m.nw;
+        if (PF && t < m.ntile) {
+            b16_load<false>(lh_node, t, m, v.NP, n);
+            const long long pl = t * 32 + m.lane; nst = pl < v.NP ? (int)st[pl] : 0;
+        }
+        if (!WREG) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                w0[i] = *reinterpret_cast<volatile double *>(val0 + 4 * m.c + i); w1[i] = *reinterpret_cast<volatile double *>(val1 + 4 * m.c + i);
+                w2[i] = *reinterpret_cast<volatile double *>(val2 + 4 * m.c + i);
+            }
+        }
+        double s0[4], s1[4], s2[4];
+        double *dst = v.theta + tc * 512 + m.lane * 4;
 #pragma unroll
         for (int u = 0; u < 4; u++) {
+            if (TIP) {
+                const int state = __shfl_sync(0xffffffffu, stl, 8 * u + m.pg);
+                const double2 *tb = reinterpret_cast<const double2 *>(tipT + state * B16_TIPROW + 4 * m.c);
+                const double2 a = tb[0], b = tb[1];
+                y[u].x = a.x; y[u].y = a.y; y[u].z = b.x; y[u].w = b.y;
+            }
             d4 r;
             r.x = x[u].x * y[u].x; r.y = x[u].y * y[u].y; r.z = x[u].z * y[u].z; r.w = x[u].w * y[u].w;
-            st_stream256(v.theta + p * 16 + 4 * u, r);
-            const double *w0 = val0 + 4 * u, *w1 = val1 + 4 * u, *w2 = val2 + 4 * u;
-            m0 = fma(r.x, w0[0], m0); m0 = fma(r.y, w0[1], m0); m0 = fma(r.z, w0[2], m0); m0 = fma(r.w, w0[3], m0);
-            m1 = fma(r.x, w1[0], m1); m1 = fma(r.y, w1[1], m1); m1 = fma(r.z, w1[2], m1); m1 = fma(r.w, w1[3], m1);
-            m2 = fma(r.x, w2[0], m2); m2 = fma(r.y, w2[1], m2); m2 = fma(r.z, w2[2], m2); m2 = fma(r.w, w2[3], m2);
+            if (tc * 32 + 8 * u + m.pg < v.NP) st_stream256(dst + 128 * u, r);
+            s0[u] = dot4(r, w0); s1[u] = dot4(r, w1); s2[u] = dot4(r, w2);
         }
-        const double lh = fabs(m0 + inv);
-        if (p < v.P) {
-            const double df_frac = m1 / lh, ddf_frac = m2 / lh, t1 = df_frac * f, t2 = ddf_frac * f;
-            acc[0] += t1;
-            acc[1] += t2 - t1 * df_frac;
-            if (sc) acc[5] += LK_LOG_THR * f * (double)sc;
-        } else { acc[2] += lh; acc[3] += m1; acc[4] += m2; v.theta_sc[p - v.P] = (int16_t)sc; }
+        const double m0 = b16_gather(s0, m.c), m1 = b16_gather(s1, m.c), m2 = b16_gather(s2, m.c);
+        if (pt < v.NP) {
+            const double lh = fabs(m0 + inv);
+            if (pt < v.P) {
+                const double df_frac = m1 / lh, ddf_frac = m2 / lh, t1 = df_frac * f, t2 = ddf_frac * f;
+                acc[0] += t1;
+                acc[1] += t2 - t1 * df_frac;
+                if (sc) acc[5] += LK_LOG_THR * f * (double)sc;
+            } else { acc[2] += lh; acc[3] += m1; acc[4] += m2; v.theta_sc[pt - v.P] = (int16_t)sc; }
+        }
     }
 }
 
 template <bool TIP>
-__global__ void __launch_bounds__(RED_THREADS, 2) theta_derv_b16_kernel(DevView v, int dad, int node, double len) {
+__global__ void __launch_bounds__(RED_THREADS, 2) theta_derv_b16_kernel(DevView v, B16Tab tab, int dad, int node, double len) {
     __shared__ __align__(32) double val0[16], val1[16], val2[16];
-    __shared__ __align__(32) double tipT[32 * B16_TIPROW];
+    __shared__ __align__(32) double tipT[TIP ? 32 * B16_TIPROW : 4];
     __shared__ double sred[6 * 32];
     double acc[6];
-    theta_derv_b16_stream<TIP>(v, dad, node, len, val0, val1, val2, tipT, acc);
+    theta_derv_b16_stream<TIP, !TIP, TIP>(v, tab, dad, node, len, val0, val1, val2, tipT, acc);
     if (grid_reduce<6>(acc, sred, v.red, v.counter)) {
         v.theta_meta[0] = acc[5];
         const double a5[5] = {acc[0], acc[1], acc[2], acc[3], acc[4]};
@@ -928,10 +1062,7 @@ static int enqueue_derv(lkcuda_engine *e, double len) {
     size_t sm = (size_t)3 * ((v.B + 3) & ~3) * 8;
     next_result(e);
     launch_begin(e, KIND_DERV);
-    if (gs.vec && v.B == 16) {      /* two resident blocks per SM, each lane keeps 2 x 128 bytes in flight */
-        int g2 = e->num_sms * 2 < grid ? e->num_sms * 2 : grid;
-        derv_b16_kernel<<<g2, RED_THREADS, 0, e->stream>>>(e->v, len);
-    }
+    if (gs.vec && v.S == 4 && v.K == 4) derv_b16_kernel<<<b16_grid(e, v.NP), RED_THREADS, 0, e->stream>>>(e->v, e->b16tab, len);
     else if (gs.vec) derv_kernel<true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
     else derv_kernel<false><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
     return launch_end(e, KIND_DERV, (uint64_t)v.NP * ((uint64_t)v.B * 8 + 16), "derv_kernel");
@@ -957,10 +1088,8 @@ int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     size_t sm = Bp * 8 + (use_tab ? tabsz : 0);
     next_result(e);
     launch_begin(e, KIND_BRANCH);
-    if (tip && gs.vec && v.B == 16 && v.S == 4 && v.SU < 32) {
-        int g2 = e->num_sms * 2 < grid ? e->num_sms * 2 : grid;
-        branch_tip_b16_kernel<<<g2, RED_THREADS, 0, e->stream>>>(e->v, dad, node, len);
-    } else if (tip) launch_branch<true>(e, gs, grid, sm, dad, node, len, use_tab);
+    if (tip && gs.vec && v.S == 4 && v.K == 4 && v.SU < 32) branch_tip_b16_kernel<<<b16_grid(e, v.NP), RED_THREADS, 0, e->stream>>>(e->v, e->b16tab, dad, node, len);
+    else if (tip) launch_branch<true>(e, gs, grid, sm, dad, node, len, use_tab);
     else launch_branch<false>(e, gs, grid, sm, dad, node, len, use_tab);
     uint64_t b = (uint64_t)v.B * 8;
     rc = launch_end(e, KIND_BRANCH, (uint64_t)v.NP * (tip ? b + 1 + 24 : 2 * b + 24), "branch_kernel");
@@ -1036,7 +1165,7 @@ int lkcuda_theta_derv(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     LK_ENTER(e);
     const DevView &v = e->v;
     GroupShape gs = group_shape(v);
-    if (IS_SITEMODEL(e) || !(gs.vec && v.B == 16 && v.S == 4 && v.SU < 32)) {      /* other shapes: the two passes */
+    if (IS_SITEMODEL(e) || !(gs.vec && v.S == 4 && v.K == 4 && v.SU < 32)) {      /* other shapes: the two passes */
         int rc = lkcuda_theta_build(e, dad, node);
         return rc ? rc : lkcuda_derv(e, len, result);
     }
@@ -1046,12 +1175,11 @@ int lkcuda_theta_derv(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     rc = states_barrier(e);
     if (rc) return rc;
     const bool tip = LKCUDA_IS_TIP(dad);
-    int grid = red_grid(e, v.NP, 1);
-    if (grid > e->num_sms * 2) grid = e->num_sms * 2;
+    int grid = b16_grid(e, v.NP);
     next_result(e);
     launch_begin(e, KIND_THETA);
-    if (tip) theta_derv_b16_kernel<true><<<grid, RED_THREADS, 0, e->stream>>>(e->v, dad, node, len);
-    else theta_derv_b16_kernel<false><<<grid, RED_THREADS, 0, e->stream>>>(e->v, dad, node, len);
+    if (tip) theta_derv_b16_kernel<true><<<grid, RED_THREADS, 0, e->stream>>>(e->v, e->b16tab, dad, node, len);
+    else theta_derv_b16_kernel<false><<<grid, RED_THREADS, 0, e->stream>>>(e->v, e->b16tab, dad, node, len);
     uint64_t b = (uint64_t)v.B * 8;
     rc = launch_end(e, KIND_THETA, (uint64_t)v.NP * ((tip ? 2 * b + 1 : 3 * b) + 16), "theta_derv_b16_kernel");
     if (rc) return rc;
@@ -1077,7 +1205,8 @@ int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result) {
     size_t sm = (size_t)((v.B + 3) & ~3) * 8;
     next_result(e);
     launch_begin(e, KIND_FROMBUF);
-    if (gs.vec) frombuf_kernel<true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
+    if (gs.vec && v.S == 4 && v.K == 4) frombuf_b16_kernel<<<b16_grid(e, v.NP), RED_THREADS, 0, e->stream>>>(e->v, e->b16tab, len);
+    else if (gs.vec) frombuf_kernel<true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
     else frombuf_kernel<false><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
     int rc = launch_end(e, KIND_FROMBUF, (uint64_t)v.NP * ((uint64_t)v.B * 8 + 24), "frombuf_kernel");
     if (rc) return rc;
@@ -1099,7 +1228,7 @@ static int newton_persistent(lkcuda_engine *e, int build, int32_t dad, int32_t n
     GroupShape gs = group_shape(v);
     static const bool host_loop = getenv("LKCUDA_HOST_NEWTON") && atoi(getenv("LKCUDA_HOST_NEWTON")) != 0;      /* test knob */
     if (IS_SITEMODEL(e) || host_loop) return 1;
-    const bool b16 = gs.vec && v.B == 16 && v.S == 4 && v.SU < 32;
+    const bool b16 = gs.vec && v.S == 4 && v.K == 4 && v.SU < 32;
     if (!b16) {
         /* any other block shape: theta_all must exist (the caller builds it with theta_kernel), then derv_kernel's pass in a loop */
         if (build != 0) return 1;
@@ -1137,8 +1266,7 @@ static int newton_persistent(lkcuda_engine *e, int build, int32_t dad, int32_t n
         if (status != 1) return -fail(e, LKCUDA_ERR_STATE, "device Newton loop failed (status %d)", status);
         return 0;
     }
-    int grid = red_grid(e, v.NP, gs.G);
-    if (grid > e->num_sms * 2) grid = e->num_sms * 2;
+    int grid = b16_grid(e, v.NP);
     if (!e->newton_max_grid) {
         if (!e->d_newton_ctl && cudaMalloc((void **)&e->d_newton_ctl, 256) != cudaSuccess) return -cuda_fail(e, cudaGetLastError(), "cudaMalloc");
         int occ = 0, o2 = 0;
@@ -1155,7 +1283,8 @@ static int newton_persistent(lkcuda_engine *e, int build, int32_t dad, int32_t n
     lkc::DevView vv = e->v;
     NewtonCtl *ctl = (NewtonCtl *)e->d_newton_ctl;
     int idad = dad, inode = node, imax = maxNRStep;
-    void *args[] = {&vv, &ctl, &idad, &inode, &x1, &xguess, &x2, &xacc, &imax};
+    lkc::B16Tab tab = e->b16tab;
+    void *args[] = {&vv, &tab, &ctl, &idad, &inode, &x1, &xguess, &x2, &xacc, &imax};
     const void *fn = build == 0 ? (const void *)newton_b16_kernel<0> : (build == 1 ? (const void *)newton_b16_kernel<1> : (const void *)newton_b16_kernel<2>);
     cudaError_t ce = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(RED_THREADS), args, 0, e->stream);
     if (ce != cudaSuccess) return -cuda_fail(e, ce, "newton_b16_kernel");
