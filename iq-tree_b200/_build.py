@@ -71,12 +71,28 @@ def build_cuda(force=False, verbose=False):
             return CUDA_LIB       # a GPU box without nvcc uses the prebuilt library
         raise RuntimeError("nvcc not found and %s is not built" % CUDA_LIB)
     os.makedirs(LIBDIR, exist_ok=True)
-    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-           "-shared", "-Xcompiler", "-fPIC", "-Xptxas", "-v" if verbose else "-O3",
-           "-o", CUDA_LIB] + srcs
-    out = _run(cmd)
-    if verbose:
-        print(out)
+    # one object per source (only the changed ones are recompiled, all of them in parallel), then one link
+    objdir = os.path.join(LIBDIR, "obj")
+    os.makedirs(objdir, exist_ok=True)
+    flags = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
+             "-Xptxas", "-v" if verbose else "-O3"]
+    procs, objs = [], []
+    for s in srcs:
+        o = os.path.join(objdir, os.path.basename(s).replace(".cu", ".o"))
+        objs.append(o)
+        if force or _newer(o, [s] + HEADERS):
+            procs.append((s, subprocess.Popen([nvcc] + flags + ["-c", s, "-o", o], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    failed = []
+    for s, pr in procs:
+        out = pr.communicate()[0]
+        if pr.returncode != 0:
+            sys.stderr.write(out)
+            failed.append(s)
+        elif verbose:
+            print(out)
+    if failed:
+        raise RuntimeError("build failed: " + " ".join(failed))
+    _run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", CUDA_LIB] + objs)
     return CUDA_LIB
 
 

@@ -19,6 +19,7 @@
  *                          correctness fallback for shapes without a tuned kernel.
  */
 #include "lkcuda_traverse.cuh"
+#include <type_traits>
 
 using namespace lkc;
 
@@ -113,11 +114,18 @@ __global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevCh
  * asynchronous copies (cp.async.bulk -> UBLKCP) that complete on mbarriers; consumers hand a stage
  * back through a second mbarrier.  Nothing in the consumers' inner loop reads a table from global memory.
  */
+#ifndef TRV_CWARPS
 #define TRV_CWARPS 11
+#endif
 #define TRV_CTHREADS (TRV_CWARPS * 32)
 #define TRV_THREADS (TRV_CTHREADS + 32)
 #define TRV_MAX_STAGES 8
+#ifndef TRV_R
 #define TRV_R 4
+#endif
+#ifndef TRV_INV_REGS
+#define TRV_INV_REGS 0      /* 1: the inverse eigenvectors of the lane's category stay in registers for the whole launch */
+#endif
 #define S4_MPAD 18  /* doubles per k of a staged 4x4 matrix: 16 + 2 keeps LDS.128 conflict-free across k */
 #define THR_HI 0x2FF00000   /* high word of 2^-256: |x| < 2^-256  <=>  (hi(x) & 0x7fffffff) < THR_HI */
 /* doubles from the start of a staged tip table to the row of state st (K*4 doubles per row + the skew written by prep_tables_kernel) */
@@ -135,6 +143,14 @@ __host__ __device__ __forceinline__ int trv_stage_bytes(int cbs, int spad) { ret
     dst[2] = m[4].x * L.x + m[4].y * L.y + m[5].x * L.z + m[5].y * L.w;         \
     dst[3] = m[6].x * L.x + m[6].y * L.y + m[7].x * L.z + m[7].y * L.w;
 
+/* first pattern of this CTA's tile in `round`: full rounds give every CTA R slices (tile_pats patterns), interleaved over the CTAs so
+   that the pattern ranges are visited in ascending order (the pipelined upload delivers them in that order); the last round gives
+   every CTA only ract_last slices */
+__device__ __forceinline__ long long trv_tile_start(int round, int nfull, int ract_last, int tile_pats, int slice_pats) {
+    if (round < nfull) return ((long long)round * gridDim.x + blockIdx.x) * tile_pats;
+    return (long long)nfull * gridDim.x * tile_pats + (long long)blockIdx.x * ract_last * slice_pats;
+}
+
 __device__ __forceinline__ void st_stream256_if(bool pred, double *p, const d4 &v) {
     asm volatile("{\n.reg .pred q;\nsetp.ne.u32 q, %5, 0;\n@q st.global.L1::no_allocate.v4.f64 [%0], {%1,%2,%3,%4};\n}"
                  :: "l"(p), "d"(v.x), "d"(v.y), "d"(v.z), "d"(v.w), "r"((unsigned)pred) : "memory");
@@ -144,7 +160,7 @@ __device__ __forceinline__ void st_s16_if(bool pred, int16_t *p, int val) {
 }
 
 __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, const TravOp *__restrict__ ops, int nops, int upw, int nslots,
-                                                                     int cbs, int spad, int stage_shift, int tile_stride, long long ntiles,
+                                                                     int cbs, int spad, int stage_shift, int nfull, int ract_last,
                                                                      const unsigned int *upload_flag, unsigned int upload_base, long long upload_chunk_pat) {
     constexpr int R = TRV_R, CT = TRV_CTHREADS;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -166,7 +182,9 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
     }
     __syncthreads();
     const int cta_units = TRV_CWARPS * upw;
-    const int tile_pats = cta_units * R / K;     /* upw is a multiple of K */
+    const int slice_pats = cta_units / K;        /* upw is a multiple of K: one slice = the patterns of ONE unit per consumer thread */
+    const int tile_pats = slice_pats * R;
+    const int nrounds = nfull + (ract_last > 0 ? 1 : 0);
 
     if (warp == TRV_CWARPS) {
         /* ------------------------------ producer: one lane feeds the ring ------------------------------ */
@@ -174,11 +192,14 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
             uint32_t c = 0;
             unsigned int seen = upload_base;
             const uint32_t mat_bytes = (uint32_t)K * S4_MPAD * 8, tab_bytes = (uint32_t)TRV_TAB_DOUBLES(v.SU, K) * 8;
-            for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-                const long long p0 = tile * tile_stride, a0 = p0 & ~15ll;         /* bulk copies start 16-byte aligned */
+            for (int round = 0; round < nrounds; round++) {
+                const int ract = round < nfull ? R : ract_last;
+                const long long p0 = trv_tile_start(round, nfull, ract_last, tile_pats, slice_pats);
+                if (p0 >= v.NP) break;
+                const long long a0 = p0 & ~15ll;         /* bulk copies start 16-byte aligned */
                 if (upload_flag) {
                     /* pipelined upload (lkcuda_set_tip_states_async): wait until the copy engine has delivered this tile's pattern range */
-                    long long last = p0 + tile_stride - 1;
+                    long long last = p0 + (long long)ract * slice_pats - 1;
                     if (last > v.NP - 1) last = v.NP - 1;
                     const unsigned int need = upload_base + (unsigned int)(last / upload_chunk_pat) + 1u;
                     while ((int)(seen - need) < 0) {
@@ -186,7 +207,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                         if ((int)(seen - need) < 0) __nanosleep(500);
                     }
                 }
-                const uint32_t st_bytes = (uint32_t)((p0 - a0 + tile_pats + 15) & ~15ll);
+                const uint32_t st_bytes = (uint32_t)((p0 - a0 + ract * slice_pats + 15) & ~15ll);
                 for (int i = 0; i < nops; i++, c++) {
                     const uint32_t s = c & stage_mask, ph = (c >> stage_shift) & 1;
                     const int src0 = ops[i].src0, src1 = ops[i].src1;
@@ -222,23 +243,28 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
 #pragma unroll
     for (int r = 0; r < R; r++) q[r] = (r * cta_units + warp * upw + (lane_on ? lane : 0)) / K;
     uint32_t c = 0;     /* ring position of the node being computed, continues across tiles */
+#if TRV_INV_REGS
+    const double2 iv[8] = {inv[0], inv[1], inv[2], inv[3], inv[4], inv[5], inv[6], inv[7]};
+#endif
 
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        long long p[R], off[R];     /* pattern, element offset of the unit inside a vector */
-        bool valid[R];
-        const long long p0 = tile * tile_stride;
+    /* one tile = RA <= R slices, RA a compile-time constant: the R units of a thread are independent instruction streams the compiler
+       interleaves, so the last round (fewer slices) runs its own instantiation instead of predicating slices off */
+    auto do_tile = [&](auto ra_tag, const long long p0) {
+        constexpr int RA = decltype(ra_tag)::value;
+        long long p[RA], off[RA];     /* pattern, element offset of the unit inside a vector */
+        bool valid[RA];
         const int sdelta = (int)(p0 & 15);
 #pragma unroll
-        for (int r = 0; r < R; r++) {
+        for (int r = 0; r < RA; r++) {
             p[r] = p0 + q[r];
-            valid[r] = lane_on && q[r] < tile_stride && p[r] < v.NP;
+            valid[r] = lane_on && p[r] < v.NP;
             if (!valid[r]) p[r] = v.NP - 1;          /* out-of-range units shadow the last pattern; only their stores are masked */
             off[r] = p[r] * B + k * 4;
         }
-        d4 pv[R];       /* result of the previous node (TRV_SLOT_PREV) */
-        int pvsc[R];
+        d4 pv[RA];       /* result of the previous node (TRV_SLOT_PREV) */
+        int pvsc[RA];
 #pragma unroll
-        for (int r = 0; r < R; r++) { pv[r].x = pv[r].y = pv[r].z = pv[r].w = 0.0; pvsc[r] = 0; }
+        for (int r = 0; r < RA; r++) { pv[r].x = pv[r].y = pv[r].z = pv[r].w = 0.0; pvsc[r] = 0; }
 
         for (int i = 0; i < nops; i++, c++) {
             const uint32_t s = c & stage_mask;
@@ -249,13 +275,13 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
             const bool tip0 = LKCUDA_IS_TIP(src0), tip1 = LKCUDA_IS_TIP(src1);
             const double *blk0 = reinterpret_cast<const double *>(stage + 64), *blk1 = blk0 + cbs;
             const unsigned char *sst0 = stage + 64 + 2 * cbs * 8 + sdelta, *sst1 = sst0 + spad;
-            double t[R][4];
-            int sc[R];
+            double t[RA][4];
+            int sc[RA];
             /* ---- child 0: tip | slot | arena ---- */
             if (tip0) {
                 const double *tab = blk0 + k * 4;
 #pragma unroll
-                for (int r = 0; r < R; r++) {
+                for (int r = 0; r < RA; r++) {
                     const int st = min((int)sst0[q[r]], v.SU);      /* clamped: an out-of-range code is reported by the upload's range check */
                     const double2 *row = reinterpret_cast<const double2 *>(tab + TRV_TAB_ROW(st, K));
                     const double2 a = row[0], b = row[1];
@@ -268,7 +294,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                     const double2 *ps = sl_t + slot0 * (R * 2 * CT);
                     const int *pc = ssc_t + slot0 * (R * CT);
 #pragma unroll
-                    for (int r = 0; r < R; r++) {
+                    for (int r = 0; r < RA; r++) {
                         const double2 a = ps[(r * 2) * CT], b = ps[(r * 2 + 1) * CT];
                         d4 L; L.x = a.x; L.y = a.y; L.z = b.x; L.w = b.y;
                         sc[r] = pc[r * CT];
@@ -278,7 +304,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                     const double *g = op->src0_lh;
                     const int16_t *gs = vec_sc(v, src0);
 #pragma unroll
-                    for (int r = 0; r < R; r++) {
+                    for (int r = 0; r < RA; r++) {
                         const d4 L = ld_coherent256(g + off[r]);
                         sc[r] = gs[p[r]];
                         TRV_MATVEC(t[r], m, L)
@@ -289,7 +315,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
             if (tip1) {
                 const double *tab = blk1 + k * 4;
 #pragma unroll
-                for (int r = 0; r < R; r++) {
+                for (int r = 0; r < RA; r++) {
                     const int st = min((int)sst1[q[r]], v.SU);
                     const double2 *row = reinterpret_cast<const double2 *>(tab + TRV_TAB_ROW(st, K));
                     const double2 a = row[0], b = row[1];
@@ -301,7 +327,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                 double u[4];
                 if (slot1 == TRV_SLOT_PREV) {
 #pragma unroll
-                    for (int r = 0; r < R; r++) {
+                    for (int r = 0; r < RA; r++) {
                         sc[r] += pvsc[r];
                         TRV_MATVEC(u, m, pv[r])
                         t[r][0] *= u[0]; t[r][1] *= u[1]; t[r][2] *= u[2]; t[r][3] *= u[3];
@@ -310,7 +336,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                     const double2 *ps = sl_t + slot1 * (R * 2 * CT);
                     const int *pc = ssc_t + slot1 * (R * CT);
 #pragma unroll
-                    for (int r = 0; r < R; r++) {
+                    for (int r = 0; r < RA; r++) {
                         const double2 a = ps[(r * 2) * CT], b = ps[(r * 2 + 1) * CT];
                         d4 L; L.x = a.x; L.y = a.y; L.z = b.x; L.w = b.y;
                         sc[r] += pc[r * CT];
@@ -321,7 +347,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                     const double *g = op->src1_lh;
                     const int16_t *gs = vec_sc(v, src1);
 #pragma unroll
-                    for (int r = 0; r < R; r++) {
+                    for (int r = 0; r < RA; r++) {
                         const d4 L = ld_coherent256(g + off[r]);
                         sc[r] += gs[p[r]];
                         TRV_MATVEC(u, m, L)
@@ -335,11 +361,13 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[s]);
             /* ---- back to state space, scaling test, stores ---- */
+#if !TRV_INV_REGS
             const double2 iv[8] = {inv[0], inv[1], inv[2], inv[3], inv[4], inv[5], inv[6], inv[7]};
+#endif
             const bool may_scale = !(tip0 && tip1);   /* tip-tip never scales (phylokernel.h:246-281) */
             bool tiny = false;
 #pragma unroll
-            for (int r = 0; r < R; r++) {
+            for (int r = 0; r < RA; r++) {
                 const d4 T = {t[r][0], t[r][1], t[r][2], t[r][3]};
                 double w[4];
                 TRV_MATVEC(w, iv, T)
@@ -352,7 +380,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
             if (may_scale && __any_sync(0xffffffffu, tiny)) {
                 /* rare path: some unit of this warp is below the threshold; agree per pattern (lane group) with ballots */
 #pragma unroll
-                for (int r = 0; r < R; r++) {
+                for (int r = 0; r < RA; r++) {
                     const int h0 = __double2hiint(pv[r].x) & 0x7fffffff, h1 = __double2hiint(pv[r].y) & 0x7fffffff,
                               h2 = __double2hiint(pv[r].z) & 0x7fffffff, h3 = __double2hiint(pv[r].w) & 0x7fffffff;
                     const unsigned small = __ballot_sync(0xffffffffu, max(max(h0, h1), max(h2, h3)) < THR_HI);
@@ -371,7 +399,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                 }
             }
 #pragma unroll
-            for (int r = 0; r < R; r++) {
+            for (int r = 0; r < RA; r++) {
                 pvsc[r] = sc[r];
                 st_stream256_if(valid[r], dst_lh + off[r], pv[r]);
                 st_s16_if(valid[r] && k == 0, dst_sc + p[r], sc[r]);
@@ -380,7 +408,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                 double2 *pd = sl_t + dst_slot * (R * 2 * CT);
                 int *pdc = ssc_t + dst_slot * (R * CT);
 #pragma unroll
-                for (int r = 0; r < R; r++) {
+                for (int r = 0; r < RA; r++) {
                     pd[(r * 2) * CT] = make_double2(pv[r].x, pv[r].y);
                     pd[(r * 2 + 1) * CT] = make_double2(pv[r].z, pv[r].w);
                     pdc[r * CT] = sc[r];
@@ -388,6 +416,17 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
             }
             /* spilled result: its consumer re-reads scale_num, which lane k == 0 wrote for the whole lane group */
             if (dst_slot == -2) { __threadfence_block(); __syncwarp(); }
+        }
+    };
+    for (int round = 0; round < nrounds; round++) {
+        const long long p0 = trv_tile_start(round, nfull, ract_last, tile_pats, slice_pats);
+        if (p0 >= v.NP) break;
+        if (round < nfull) { do_tile(std::integral_constant<int, R>{}, p0); continue; }
+        switch (ract_last) {
+            case 1: do_tile(std::integral_constant<int, 1>{}, p0); break;
+            case 2: do_tile(std::integral_constant<int, (R >= 2 ? 2 : R)>{}, p0); break;
+            case 3: do_tile(std::integral_constant<int, (R >= 3 ? 3 : R)>{}, p0); break;
+            default: do_tile(std::integral_constant<int, R>{}, p0); break;
         }
     }
 }
@@ -754,24 +793,24 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
     rc = launch_end(e, KIND_PREP, 0, "prep_tables_kernel");
     if (rc) return rc;
 
-    /* a CTA takes tile_pats patterns per round at most; the rounds are evened out (tile_stride <= tile_pats patterns per tile, the
-       same for every tile) so that no CTA runs a whole round more than the others - it matters for small shards (8-GPU runs) */
-    long long ntiles = (v.NP + tile_pats - 1) / tile_pats;
-    const long long nrounds = (ntiles + e->num_sms - 1) / e->num_sms;
-    long long tile_stride = ((v.NP + nrounds * e->num_sms - 1) / (nrounds * e->num_sms) + 31) / 32 * 32;
-    if (tile_stride > tile_pats) tile_stride = tile_pats;
-    ntiles = (v.NP + tile_stride - 1) / tile_stride;
+    /* work is dealt in SLICES (one unit per consumer thread = slice_pats patterns): every CTA runs nfull rounds of TRV_R slices and
+       one last round of ract_last <= TRV_R slices, so the cost of the launch is ceil-ed to one slice per CTA, not to one whole tile */
+    const int slice_pats = tile_pats / TRV_R;
+    const long long nslices = (v.NP + slice_pats - 1) / slice_pats;
+    long long grid = e->num_sms;      /* one persistent CTA per SM (384 threads, shared memory bound) */
+    if (grid > nslices) grid = nslices;
+    const int nfull = (int)(nslices / (TRV_R * grid));
+    const long long rem = nslices - (long long)nfull * TRV_R * grid;
+    const int ract_last = (int)((rem + grid - 1) / grid);
     const size_t sm = (size_t)sch.nslots * slot_bytes + fixed;
     if (e->trav_smem_set != LK_MAX_DYN_SMEM) {
         LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
         e->trav_smem_set = LK_MAX_DYN_SMEM;
     }
-    long long grid = e->num_sms;      /* one persistent CTA per SM (384 threads, shared memory bound) */
-    if (grid > ntiles) grid = ntiles;
     launch_begin(e, KIND_PARTIAL);
     /* with a pipelined upload in flight the kernel is NOT ordered after it: its producer polls the per-chunk counter instead */
     const unsigned int *flag = e->upload_pending ? e->d_upload_flag : NULL;
-    traverse_s4_kernel<<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, (int)tile_stride, ntiles,
+    traverse_s4_kernel<<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, nfull, ract_last,
                                                                       flag, e->upload_base, e->upload_chunk_pat > 0 ? e->upload_chunk_pat : 1);
     return launch_end(e, KIND_PARTIAL, bytes, "traverse_s4_kernel");
 }
