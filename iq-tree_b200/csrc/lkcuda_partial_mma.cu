@@ -33,7 +33,9 @@ using namespace lkc;
 #define MM_NT 3                 /* 8-wide tiles covering the padded 24 */
 #define MM_FRAGS (MM_NT * MM_NT * 2)    /* B fragments of one 20x20 matrix: (rt, ct, c) */
 #define MM_FRAG_DOUBLES (MM_FRAGS * 32) /* 576 doubles = 4608 bytes per matrix */
-#define MM_CWARPS 8
+#ifndef MM_CWARPS
+#define MM_CWARPS 16     /* 8 -> 16 consumer warps: 14.1 -> 12.9 ms per 200 x 200k LG+G4 traversal although only one slot is left (profiles/r2_s13_mma_variants.txt) */
+#endif
 #define MM_CTHREADS (MM_CWARPS * 32)
 #define MM_THREADS (MM_CTHREADS + 32)
 #define MM_TP (MM_CWARPS * 8)   /* patterns per tile: one 8-pattern group per consumer warp */

@@ -189,6 +189,64 @@ def test_full_command_line_on_engine(work, cuda_lib):
     assert gpu[2] == cpu[2], "topology differs"
 
 
+def _mixture_em(harness, work, tag, extra):
+    """`-m MIX{HKY,GTR}+G4 -te BIONJ`: components with free parameters make ModelMixture::optimizeParameters take optimizeWithEM
+    (model/modelmixture.cpp:1418-1532): computePatternLhCat(WSL_MIXTURE), posterior weights -> ptn_freq of a temporary one-component tree that
+    aliases the arena pointers, BFGS on that tree, new weights.  Returns lnL, the component table of the report and the tree."""
+    pre = os.path.join(work, "mixem_" + tag)
+    out = du.run(harness, ["iqtree", "-s", os.path.join(work, "example.phy"), "-m", "MIX{HKY,GTR}+G4", "-te", "BIONJ", "-nt", "1", "-seed", "1", "-pre", pre] + extra,
+                 work, timeout=3000)
+    rep = open(pre + ".iqtree").read()
+    assert "Mixture model of substitution: MIX{HKY+F,GTR+F}+G4" in rep
+    lnl = float(re.search(r"BEST SCORE FOUND : (-?[0-9.]+)", out).group(1))
+    comps = re.findall(r"^\s+[12]\s+(?:HKY|GTR)\s+([0-9.]+)\s+([0-9.]+)\s+(\S+)", rep, flags=re.M)
+    assert len(comps) == 2
+    return lnl, comps, open(pre + ".treefile").read().strip()
+
+
+def _check_mixture_em(cpu, eng):
+    assert abs(eng[0] - cpu[0]) <= 2e-3, (eng[0], cpu[0])               # the report prints 4 decimals
+    for (r0, w0, par0), (r1, w1, par1) in zip(cpu[1], eng[1]):
+        assert abs(float(w0) - float(w1)) <= 2e-4, (w0, w1)             # EM weights, printed with 4 decimals
+        a = [float(x) for x in re.findall(r"[0-9]+\.[0-9]+(?:e[+-]?[0-9]+)?", par0)]
+        b = [float(x) for x in re.findall(r"[0-9]+\.[0-9]+(?:e[+-]?[0-9]+)?", par1)]
+        assert len(a) == len(b) and all(abs(x - y) <= 2e-3 * max(1.0, abs(x)) for x, y in zip(a, b)), (par0, par1)
+    la = gu.parse_newick_lengths(cpu[2]) if hasattr(gu, "parse_newick_lengths") else None
+    if la is None:      # branch lengths of the two reports, in file order
+        la = [float(x) for x in re.findall(r":([0-9.eE+-]+)", cpu[2])]
+        lb = [float(x) for x in re.findall(r":([0-9.eE+-]+)", eng[2])]
+        assert len(la) == len(lb) and max(abs(x - y) for x, y in zip(la, lb)) <= 1e-4
+    assert re.sub(r":[0-9.eE+-]+", "", cpu[2]) == re.sub(r":[0-9.eE+-]+", "", eng[2])
+
+
+def test_reference_mixture_em_on_scalar_engine(work):
+    """ModelMixture::optimizeWithEM (SURVEY 8(f).1) is the reference's own code: with the binding it runs unchanged on the engine ABI,
+    including the temporary tree that borrows central_partial_lh (modelmixture.cpp:1427-1429)"""
+    _need(du.HARNESS_ORACLE)
+    if not os.path.exists(du.HARNESS_REF):
+        pytest.skip("unmodified reference harness not built")
+    du.case_args(work)
+    _check_mixture_em(_mixture_em(du.HARNESS_REF, work, "cpu", []), _mixture_em(du.HARNESS_ORACLE, work, "eng", ["-cuda"]))
+
+
+@pytest.mark.gpu
+def test_reference_mixture_em_on_engine(work, cuda_lib):
+    du.case_args(work)
+    assert os.path.exists(du.HARNESS_REF) and os.path.exists(du.HARNESS_CUDA)
+    _check_mixture_em(_mixture_em(du.HARNESS_REF, work, "cpug", []), _mixture_em(du.HARNESS_CUDA, work, "gpu", ["-cuda"]))
+
+
+def test_reference_invar_free_rate_em_is_broken_upstream(work):
+    """+I+R (model/ratefreeinvar.cpp) cannot be mirrored: the UNMODIFIED reference aborts at its own default start
+    (ratefree.cpp:535: Assertion `fabs(sum_prop-1.0) < MIN_PROP')"""
+    if not os.path.exists(du.HARNESS_REF):
+        pytest.skip("unmodified reference harness not built")
+    du.case_args(work)
+    r = subprocess.run([du.HARNESS_REF, "iqtree", "-s", os.path.join(work, "example.phy"), "-m", "GTR+I+R3", "-te", "BIONJ", "-nt", "1", "-seed", "1",
+                        "-pre", os.path.join(work, "ir_cpu")], cwd=work, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode != 0 and "sum_prop" in r.stdout
+
+
 def test_binding_short_search_on_scalar_engine(work):
     """a short fixed-model search through the complete command line (CPU, scalar engine): topology and likelihood of the reference's CPU run"""
     _need(du.HARNESS_ORACLE)
