@@ -599,10 +599,16 @@ void PhyloTree::computePartialLikelihood(Neighbor *dad_branch, Node *dad) {
     pending_level_.push_back(level);
 }
 
-/* hand the recorded post-order schedule to the device, grouped by tree level */
-void PhyloTree::flushPartialOps() {
+/* hand the recorded post-order schedule to the device, grouped by tree level; with `branch` the branch lnL of (dad_end, node_vec) is
+   asked for in the same call (lkcuda_partial_batch_lnl: PhyloTree::computeLikelihood's traversal + root branch) */
+void PhyloTree::flushPartialOps(const BranchRequest *branch) {
     ensureInputs();
-    if (pending_ops_.empty()) return;
+    if (pending_ops_.empty()) {
+        if (branch)
+            for (size_t d = 0; d < engines_.size(); d++)
+                check(lkcuda_branch_lnl(engines_[d], branch->dad_end, branch->node_vec, branch->len, NULL), engines_[d], "lkcuda_branch_lnl");
+        return;
+    }
     size_t n = pending_ops_.size();
     int maxlevel = 0;
     for (size_t i = 0; i < n; i++) maxlevel = std::max(maxlevel, pending_level_[i]);
@@ -617,8 +623,18 @@ void PhyloTree::flushPartialOps() {
     std::vector<int32_t> starts(maxlevel + 1);
     for (int l = 1; l <= maxlevel; l++) starts[l - 1] = level_start[l];
     starts[maxlevel] = (int32_t)n;
-    for (size_t d = 0; d < engines_.size(); d++)
-        check(lkcuda_partial_batch(engines_[d], &sorted[0], (int32_t)n, &starts[0], maxlevel), engines_[d], "lkcuda_partial_batch");
+    if (branch && engines_.size() == 1) {
+        check(lkcuda_partial_batch_lnl(engines_[0], &sorted[0], (int32_t)n, &starts[0], maxlevel, branch->dad_end, branch->node_vec, branch->len, NULL),
+              engines_[0], "lkcuda_partial_batch_lnl");
+    } else {
+        // in-process shards exchange their sums inside the reduction kernels: every shard's traversal is queued before the first
+        // reduction starts to wait for its peers
+        for (size_t d = 0; d < engines_.size(); d++)
+            check(lkcuda_partial_batch(engines_[d], &sorted[0], (int32_t)n, &starts[0], maxlevel), engines_[d], "lkcuda_partial_batch");
+        if (branch)
+            for (size_t d = 0; d < engines_.size(); d++)
+                check(lkcuda_branch_lnl(engines_[d], branch->dad_end, branch->node_vec, branch->len, NULL), engines_[d], "lkcuda_branch_lnl");
+    }
     for (size_t i = 0; i < n; i++) vec_level_[pending_ops_[i].dst] = 0;
     pending_ops_.clear(); pending_level_.clear();
 }
@@ -654,11 +670,11 @@ double PhyloTree::computeLikelihoodBranch(Neighbor *dad_branch, Node *dad) {   /
     if (node->isLeaf()) { std::swap(dad, node); std::swap(dad_branch, node_branch); }
     if ((dad_branch->partial_lh_computed & 1) == 0) computePartialLikelihood(dad_branch, dad);
     if ((node_branch->partial_lh_computed & 1) == 0) computePartialLikelihood(node_branch, node);
-    flushPartialOps();
     // dad_branch points from dad to node: its vector is the subtree at `node`; node_branch's is the subtree at `dad`
-    int32_t dad_end = dad->isLeaf() ? LKCUDA_TIP(dad->id) : node_branch->vec;
-    for (size_t d = 0; d < engines_.size(); d++)
-        check(lkcuda_branch_lnl(engines_[d], dad_end, dad_branch->vec, dad_branch->length, NULL), engines_[d], "lkcuda_branch_lnl");
+    BranchRequest br;
+    br.dad_end = dad->isLeaf() ? LKCUDA_TIP(dad->id) : node_branch->vec;
+    br.node_vec = dad_branch->vec; br.len = dad_branch->length;
+    flushPartialOps(&br);
     double r[LKCUDA_NRESULT];
     reduceResult(r);
     if (r[LKCUDA_R_NREPAIRED] > 0)

@@ -221,7 +221,8 @@ private:
     std::vector<lkpars_op> pars_ops_;
     std::vector<uint32_t> pars_counts_;                              // [op][2] of the last flush
 
-    void flushPartialOps();
+    struct BranchRequest { int32_t dad_end, node_vec; double len; };
+    void flushPartialOps(const BranchRequest *branch = NULL);
     void enqueuePatternLhCat();
     int collapsePatternLhCat(int wsl);
     void check(int rc, lkcuda_engine *e, const char *what);

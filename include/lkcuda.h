@@ -157,6 +157,13 @@ int lkcuda_set_model(lkcuda_engine *e, const double *eval, const double *evec, c
    nodes (one launch per level).  Asynchronous: enqueues on the engine stream and returns. */
 int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t nops,
                          const int32_t *level_start, int32_t nlevels);
+/* PhyloTree::computeLikelihood (phylotree.cpp:1031-1071) in one call: the traversal towards the root branch (lkcuda_partial_batch) and
+   computeLikelihoodBranch on that branch (lkcuda_branch_lnl; dad = LKCUDA_TIP(taxon) or a vector, node = the vector of the branch's
+   other end).  Same results and side effects (_pattern_lh, result block) as the two calls; when the list ends in `node`, `dad` is a
+   leaf and the data are DNA with 4 categories the branch is evaluated in the tail of the traversal launch, from registers. */
+int lkcuda_partial_batch_lnl(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t nops,
+                             const int32_t *level_start, int32_t nlevels,
+                             int32_t dad, int32_t node, double len, double *result);
 /* multifurcating node (degree > 3) — the generic kernel's path (phylotreesse.cpp:702-806) */
 int lkcuda_partial_multi(lkcuda_engine *e, int32_t dst, int32_t nchild, const int32_t *child,
                          const double *child_len);

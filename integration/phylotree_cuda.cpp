@@ -32,6 +32,10 @@
 
 extern int instruction_set;     // pda.cpp
 
+/* set around lkCudaBranchEnds by the branch-lnL wrapper: the recorded nodes are not flushed there but handed over together with the branch
+   (thread_local: partition models evaluate different PhyloTree objects from several OpenMP threads, phylosupertree.cpp:969-976) */
+static thread_local bool lk_defer_flush = false;
+
 struct PhyloTree::LkCuda {
     lkcuda_engine *engine;
     int device;
@@ -312,7 +316,8 @@ void PhyloTree::lkCudaBranchEnds(PhyloNeighbor *&dad_branch, PhyloNode *&dad, in
         computePartialLikelihoodCuda(dad_branch, dad);
     if ((node_branch->partial_lh_computed & 1) == 0)
         computePartialLikelihoodCuda(node_branch, node);
-    lkCudaFlush();
+    if (!lk_defer_flush)
+        lkCudaFlush();
     // dad_branch (stored at dad, pointing to node) holds the subtree at `node`; node_branch the one at `dad`
     dad_end = dad->isLeaf() ? LKCUDA_TIP(dad->id) : lkCudaVector(node_branch);
     node_vec = lkCudaVector(dad_branch);
@@ -320,9 +325,18 @@ void PhyloTree::lkCudaBranchEnds(PhyloNeighbor *&dad_branch, PhyloNode *&dad, in
 
 double PhyloTree::computeLikelihoodBranchCuda(PhyloNeighbor *dad_branch, PhyloNode *dad) {
     int dad_end, node_vec;
+    lk_defer_flush = true;      // the recorded traversal and this branch go to the device in ONE call (lkcuda_partial_batch_lnl)
     lkCudaBranchEnds(dad_branch, dad, dad_end, node_vec);
+    lk_defer_flush = false;
     double r[LKCUDA_NRESULT];
-    lkCheck(lkcuda_branch_lnl(lk_cuda->engine, dad_end, node_vec, dad_branch->length, r), lk_cuda->engine, "lkcuda_branch_lnl");
+    lkCudaSyncInputs();
+    if (!lk_cuda->pending.empty()) {
+        lkCheck(lkcuda_partial_batch_lnl(lk_cuda->engine, &lk_cuda->pending[0], (int32_t)lk_cuda->pending.size(), NULL, 0,
+                                         dad_end, node_vec, dad_branch->length, r), lk_cuda->engine, "lkcuda_partial_batch_lnl");
+        lk_cuda->nflush++; lk_cuda->nops += lk_cuda->pending.size();
+        lk_cuda->pending.clear();
+    } else
+        lkCheck(lkcuda_branch_lnl(lk_cuda->engine, dad_end, node_vec, dad_branch->length, r), lk_cuda->engine, "lkcuda_branch_lnl");
     if (r[LKCUDA_R_NREPAIRED] > 0)      // phylokernel.h:848-866
         outWarning("Numerical underflow for " + convertIntToString((int)r[LKCUDA_R_NREPAIRED]) + " alignment patterns");
     assert(!isnan(r[LKCUDA_R_LNL]) && !isinf(r[LKCUDA_R_LNL]));

@@ -16,6 +16,7 @@
 
 #include "../../include/lkcuda.h"
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
@@ -145,6 +146,9 @@ struct lkcuda_engine {
     bool upload_pending;        /* the main stream has not yet been ordered after the upload */
     bool upload_check;          /* the range check of the uploaded states has not been examined yet */
     bool theta_ready; int theta_dad; int theta_node;
+    /* lkcuda_partial_batch_lnl: root branch the LAST piece of the current op list may evaluate in the tail of its traversal launch
+       (fuse_state: 0 = no request, 1 = requested, 2 = the last piece is being issued, 3 = done by the traversal kernel) */
+    int fuse_state, fuse_dad, fuse_node; double fuse_len;
     bool model_set, states_set, weights_set;
     int num_sms;
     uint64_t launches, bytes;
@@ -187,6 +191,7 @@ inline void next_result(lkcuda_engine *e) {
 
 /* implemented in lkcuda_partial.cu / lkcuda_reduce.cu */
 int ensure_tables(lkcuda_engine *e, long long slots);
+int branch_lnl_followups(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result);   /* lkcuda_reduce.cu */
 /* order the engine stream after a pipelined tip-state upload (every kernel that reads tip states without polling calls this) */
 int states_barrier(lkcuda_engine *e);
 /* after a synchronisation point: report a failed range check of an asynchronous upload */
@@ -368,6 +373,102 @@ static __device__ __forceinline__ void publish_result(const DevView &v, double (
     unsigned int err = 0;
     if (v.peer_world > 1) err = peer_exchange(v, r, v.peer_seq);
     post_result(v, r, err);
+}
+
+/* ---- the same two stages for PART of a block: threads 0 .. nthr-1 (whole warps) of a kernel whose other warps have other roles
+   (the traversal kernel's consumer warps).  Synchronises on named barrier 1 instead of __syncthreads(). ---- */
+__device__ __forceinline__ void bar_part(int nthr) { asm volatile("bar.sync 1, %0;" :: "r"(nthr) : "memory"); }
+
+template <int N>
+__device__ __forceinline__ void block_reduce_part(double (&val)[N], double *sh, int nthr) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = nthr >> 5;
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+        double x = val[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+        if (lane == 0) sh[i * 32 + warp] = x;
+    }
+    bar_part(nthr);
+    if (warp == 0) {
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+            double x = lane < nwarp ? sh[i * 32 + lane] : 0.0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+            val[i] = x;
+        }
+    }
+}
+
+template <int N>
+__device__ __forceinline__ bool grid_reduce_part(double (&val)[N], double *sh, uint4 *red, unsigned int *counter, int nthr) {
+    unsigned int gen = 0;
+    if (threadIdx.x == 0 || blockIdx.x == 0) { gen = __ldcg(counter) + 1u; if (!gen) gen = 1u; }
+    block_reduce_part<N>(val, sh, nthr);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+            const unsigned long long bits = (unsigned long long)__double_as_longlong(val[i]);
+            asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(red + (size_t)blockIdx.x * RED_SLOTS + i),
+                         "r"((unsigned int)bits), "r"(gen), "r"((unsigned int)(bits >> 32)), "r"(gen) : "memory");
+        }
+    }
+    if (blockIdx.x != 0) return false;
+    bar_part(nthr);
+    double acc[N];
+#pragma unroll
+    for (int i = 0; i < N; i++) acc[i] = 0.0;
+    const long long t0 = clock64();
+    bool lost = false;
+    for (unsigned int b = threadIdx.x; b < gridDim.x; b += (unsigned int)nthr) {
+        const uint4 *src = red + (size_t)b * RED_SLOTS;
+        uint4 q[N];
+        for (;;) {
+            bool ok = true;
+#pragma unroll
+            for (int i = 0; i < N; i++) {
+                asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(q[i].x), "=r"(q[i].y), "=r"(q[i].z), "=r"(q[i].w) : "l"(src + i) : "memory");
+                ok = ok && q[i].y == gen && q[i].w == gen;
+            }
+            if (ok) break;
+            if (clock64() - t0 > 8000000000ll) { lost = true; break; }
+        }
+#pragma unroll
+        for (int i = 0; i < N; i++) acc[i] += lost ? __longlong_as_double(0x7ff8000000000000ll) : __longlong_as_double((long long)(((unsigned long long)q[i].z << 32) | q[i].x));
+    }
+    block_reduce_part<N>(acc, sh, nthr);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < N; i++) val[i] = acc[i];
+        *reinterpret_cast<volatile unsigned int *>(counter) = gen;
+    }
+    return threadIdx.x == 0;
+}
+
+/* log, NaN repair, pattern_lh, frequency weighting, +ASC accumulation: the common tail of branch lnL and
+   lnL-from-buffer (phylokernel.h:828-866, 895-900, 1009-1016). acc[0..3] = {sum freq*log, scale sum, prob_const, repaired} */
+__device__ __forceinline__ void lnl_tail_vals(const DevView &v, long long p, double lh, int sc, double inv, double f, double (&acc)[4]) {
+    if (p < v.P) {
+        double l = log(fabs(lh + inv));
+        if (isnan(l) || isinf(l)) { l = LK_LOG_THR * 4.0; acc[3] += 1.0; }
+        v.pattern_lh[p] = l;
+        acc[0] += l * f;
+        if (sc) acc[1] += LK_LOG_THR * f * (double)sc;
+    } else {
+        if (sc >= 1) lh *= LK_THR;
+        acc[2] += lh + inv;
+    }
+}
+__device__ __forceinline__ void lnl_tail(const DevView &v, long long p, double lh, int sc, double (&acc)[4]) {
+    lnl_tail_vals(v, p, lh, sc, v.invar[p], p < v.P ? v.freq[p] : 0.0, acc);
+}
+
+__device__ __forceinline__ void lnl_finish(const DevView &v, const double (&acc)[4], double scale_sum) {
+    double lnl = acc[0] + scale_sum, lc = 0.0;
+    if (v.U > 0) { lc = log(1.0 - acc[2]); lnl -= v.nsite * lc; }
+    double r[LKCUDA_NRESULT] = {lnl, 0.0, 0.0, acc[2], acc[3], scale_sum, lc, 0.0};
+    publish_result(v, r);
 }
 
 }  // namespace lkc

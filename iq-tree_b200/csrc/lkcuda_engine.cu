@@ -171,7 +171,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
         e->h_ops[i] = e->d_ops[i] = NULL; e->h_child[i] = e->d_child[i] = NULL;
         e->ring_cap_ops[i] = e->ring_cap_child[i] = 0; e->ring_ev[i] = NULL; e->ring_used[i] = false;
     }
-    e->ring_next = 0; e->red_blocks = 0; e->trav_smem_set = 48 * 1024;
+    e->ring_next = 0; e->red_blocks = 0; e->trav_smem_set = 48 * 1024; e->fuse_state = 0;
     e->d_inv_frags = NULL; e->mma_smem_set = 48 * 1024;
     { const char *r = getenv("LKCUDA_NO_MMA"); e->trav_disable_mma = r && atoi(r) != 0; }
     { const char *r = getenv("LKCUDA_TRV_MAXSLOTS"); e->trav_maxslots = r ? atoi(r) : -1; }

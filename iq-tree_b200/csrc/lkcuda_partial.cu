@@ -143,6 +143,11 @@ __host__ __device__ __forceinline__ int trv_stage_bytes(int cbs, int spad) { ret
     dst[2] = m[4].x * L.x + m[4].y * L.y + m[5].x * L.z + m[5].y * L.w;         \
     dst[3] = m[6].x * L.x + m[6].y * L.y + m[7].x * L.z + m[7].y * L.w;
 
+/* root branch fused into the tail of the traversal (lkcuda_partial_batch_lnl): the leaf end, its length and the table parameters */
+#define TRV_ROOT_ROW 18
+struct TravRoot { int on, tip; double len; B16Tab tab; };     /* tip: LKCUDA_TIP(taxon) */
+#define TRV_ROOT_SMEM ((32 * TRV_ROOT_ROW + 4 * TRV_CTHREADS + 4 * 32) * 8)
+
 /* first pattern of this CTA's tile in `round`: full rounds give every CTA R slices (tile_pats patterns), interleaved over the CTAs so
    that the pattern ranges are visited in ascending order (the pipelined upload delivers them in that order); the last round gives
    every CTA only ract_last slices */
@@ -159,9 +164,11 @@ __device__ __forceinline__ void st_s16_if(bool pred, int16_t *p, int val) {
     asm volatile("{\n.reg .pred q;\nsetp.ne.u32 q, %2, 0;\n@q st.global.u16 [%0], %1;\n}" :: "l"(p), "h"((short)val), "r"((unsigned)pred) : "memory");
 }
 
+template <bool FUSE>
 __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, const TravOp *__restrict__ ops, int nops, int upw, int nslots,
                                                                      int cbs, int spad, int stage_shift, int nfull, int ract_last,
-                                                                     const unsigned int *upload_flag, unsigned int upload_base, long long upload_chunk_pat) {
+                                                                     const unsigned int *upload_flag, unsigned int upload_base, long long upload_chunk_pat,
+                                                                     TravRoot root) {
     constexpr int R = TRV_R, CT = TRV_CTHREADS;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int K = v.K, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -172,9 +179,19 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
     int *ssc = reinterpret_cast<int *>(sl + nslots * R * 2 * CT);                            /* [nslots][R][CT] */
     double *sINV = reinterpret_cast<double *>(ssc + nslots * R * CT);                        /* [K][S4_MPAD] */
     uint64_t *full = reinterpret_cast<uint64_t *>(sINV + K * S4_MPAD), *empty = full + TRV_MAX_STAGES;
+    /* fused root-branch lnL (root.on; K = 4): weighted tip table of the root leaf [state][TRV_ROOT_ROW] | per-thread sums [4][CT] | [4][32] */
+    double *rootB = reinterpret_cast<double *>(empty + TRV_MAX_STAGES), *racc = rootB + 32 * TRV_ROOT_ROW, *rred = racc + 4 * CT;
+    constexpr bool fuse_root = FUSE;
     for (int idx = tid; idx < K * 16; idx += TRV_THREADS) {
         int kk = idx >> 4, r = idx & 15;
         sINV[kk * S4_MPAD + r] = v.inv_evec[v.blk_eigen[kk] * 16 + r];
+    }
+    if (fuse_root) {        /* val[k][i] * tip_partial_lh[state][i] of computeLikelihoodBranchEigenSIMD's tip case (phylokernel.h:767-775, 779-830) */
+        for (int idx = tid; idx < (v.SU + 1) * 16; idx += TRV_THREADS) {
+            const int st = idx >> 4, j = idx & 15;
+            rootB[st * TRV_ROOT_ROW + j] = exp(root.tab.cof[j] * root.len) * root.tab.w[j >> 2] * v.tip[((long long)st * v.E + root.tab.eig[j >> 2]) * 4 + (j & 3)];
+        }
+        for (int idx = tid; idx < 4 * CT; idx += TRV_THREADS) racc[idx] = 0.0;
     }
     if (tid == 0) {
         for (uint32_t s = 0; s < nstages; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], TRV_CWARPS); }
@@ -261,6 +278,9 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
             if (!valid[r]) p[r] = v.NP - 1;          /* out-of-range units shadow the last pattern; only their stores are masked */
             off[r] = p[r] * B + k * 4;
         }
+        /* fused root branch: lane k of a pattern's lane group finishes the pattern of slice r = k (one log per lane); everything it needs
+           from global memory is requested now and used after the last node */
+        int root_st = 0; double root_inv = 0.0, root_f = 0.0; long long root_p = 0; bool root_mine = false;
         d4 pv[RA];       /* result of the previous node (TRV_SLOT_PREV) */
         int pvsc[RA];
 #pragma unroll
@@ -269,6 +289,17 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
         for (int i = 0; i < nops; i++, c++) {
             const uint32_t s = c & stage_mask;
             mbar_wait(&full[s], (c >> stage_shift) & 1);
+            if (fuse_root && i == 0) {
+                /* requested behind the tile's first stage: with a pipelined upload the producer has seen this pattern range arrive by then
+                   (read around L1: the copy engine may have written the bytes while this kernel was already running) */
+                const uint8_t *rst = tip_states(v, root.tip);
+#pragma unroll
+                for (int r = 0; r < RA; r++) {
+                    root_st |= min((int)__ldcg(rst + p[r]), v.SU) << (8 * r);
+                    if (r == k) { root_p = p[r]; root_mine = valid[r]; }
+                }
+                if (root_mine) { root_inv = v.invar[root_p]; root_f = root_p < v.P ? v.freq[root_p] : 0.0; }
+            }
             const unsigned char *stage = ring + s * stage_bytes;
             const TravOp *op = reinterpret_cast<const TravOp *>(stage);
             const int src0 = op->src0, src1 = op->src1, slot0 = op->slot0, slot1 = op->slot1, dst_slot = op->dst_slot;
@@ -416,6 +447,28 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
             }
             /* spilled result: its consumer re-reads scale_num, which lane k == 0 wrote for the whole lane group */
             if (dst_slot == -2) { __threadfence_block(); __syncwarp(); }
+            if (fuse_root && i == nops - 1) {
+                /* the last node is the inner end of the root branch and still in registers: lh = sum_k sum_i val[k][i] * tip[state][i] * L[k][i]
+                   over the 4 lanes of the pattern (every lane ends up with the total), then lane k runs branch_tip_b16_kernel's tail for slice k */
+                double lh_mine = 0.0; int sc_mine = 0;
+#pragma unroll
+                for (int r = 0; r < RA; r++) {
+                    const int st = (root_st >> (8 * r)) & 255;
+                    const double2 *row = reinterpret_cast<const double2 *>(rootB + st * TRV_ROOT_ROW + 4 * k);
+                    const double2 a = row[0], b = row[1];
+                    double lh = a.x * pv[r].x;
+                    lh = fma(a.y, pv[r].y, lh); lh = fma(b.x, pv[r].z, lh); lh = fma(b.y, pv[r].w, lh);
+                    lh += __shfl_xor_sync(0xffffffffu, lh, 1);
+                    lh += __shfl_xor_sync(0xffffffffu, lh, 2);
+                    if (r == k) { lh_mine = lh; sc_mine = sc[r]; }       /* scale_num is per pattern: the group's lanes all carry it */
+                }
+                if (root_mine) {
+                    double a4[4] = {0.0, 0.0, 0.0, 0.0};
+                    lnl_tail_vals(v, root_p, lh_mine, sc_mine, root_inv, root_f, a4);
+#pragma unroll
+                    for (int j = 0; j < 4; j++) racc[j * CT + tid] += a4[j];
+                }
+            }
         }
     };
     for (int round = 0; round < nrounds; round++) {
@@ -428,6 +481,10 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
             case 3: do_tile(std::integral_constant<int, (R >= 3 ? 3 : R)>{}, p0); break;
             default: do_tile(std::integral_constant<int, R>{}, p0); break;
         }
+    }
+    if (fuse_root) {
+        double acc[4] = {racc[tid], racc[CT + tid], racc[2 * CT + tid], racc[3 * CT + tid]};
+        if (grid_reduce_part<4>(acc, rred, v.red, v.counter, CT)) lnl_finish(v, acc, acc[1]);
     }
 }
 
@@ -746,7 +803,10 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
     const size_t slot_bytes = (size_t)TRV_R * TRV_CTHREADS * (32 + 4);
     const int upw = (32 / v.K) * v.K, tile_pats = TRV_CWARPS * upw * TRV_R / v.K, spad = (tile_pats + 15 + 15) & ~15;
     /* ring depth: 8 stages when they fit beside the slots the schedule is likely to need, else 4, else 2 */
-    const size_t other = (size_t)v.K * S4_MPAD * 8 + 2 * TRV_MAX_STAGES * 8 + 128;
+    /* the root branch rides along when the caller asked for it (lkcuda_partial_batch_lnl), this is the list's last piece, the leaf end
+       is a tip and the shape is DNA + 4 categories; whether the LAST scheduled node is the branch's inner end is checked below */
+    bool fuse = e->fuse_state == 2 && v.K == 4 && v.SU < 32 && LKCUDA_IS_TIP(e->fuse_dad) && v.NP > 0;
+    const size_t other = (size_t)v.K * S4_MPAD * 8 + 2 * TRV_MAX_STAGES * 8 + 128 + (fuse ? TRV_ROOT_SMEM : 0);
     const size_t stage_b = (size_t)trv_stage_bytes(cbs, spad);
     int stage_shift = 3;
     while (stage_shift > 1 && (size_t)(1 << stage_shift) * stage_b + other + 3 * slot_bytes > 227 * 1024) stage_shift--;
@@ -804,14 +864,27 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
     const int ract_last = (int)((rem + grid - 1) / grid);
     const size_t sm = (size_t)sch.nslots * slot_bytes + fixed;
     if (e->trav_smem_set != LK_MAX_DYN_SMEM) {
-        LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
+        LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
+        LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
         e->trav_smem_set = LK_MAX_DYN_SMEM;
+    }
+    TravRoot root;
+    root.on = 0; root.tip = 0; root.len = 0.0; root.tab = e->b16tab;
+    if (fuse && ops[sch.nodes[nops - 1].op].dst == e->fuse_node) {
+        root.on = 1; root.tip = e->fuse_dad; root.len = e->fuse_len;
+        next_result(e);
+        e->fuse_state = 3;
+        bytes += (uint64_t)v.NP * 25;       /* states, ptn_freq, ptn_invar read, _pattern_lh written: the vector itself is not re-read */
     }
     launch_begin(e, KIND_PARTIAL);
     /* with a pipelined upload in flight the kernel is NOT ordered after it: its producer polls the per-chunk counter instead */
     const unsigned int *flag = e->upload_pending ? e->d_upload_flag : NULL;
-    traverse_s4_kernel<<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, nfull, ract_last,
-                                                                      flag, e->upload_base, e->upload_chunk_pat > 0 ? e->upload_chunk_pat : 1);
+    if (root.on)
+        traverse_s4_kernel<true><<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, nfull, ract_last,
+                                                                                flag, e->upload_base, e->upload_chunk_pat > 0 ? e->upload_chunk_pat : 1, root);
+    else
+        traverse_s4_kernel<false><<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, nfull, ract_last,
+                                                                                 flag, e->upload_base, e->upload_chunk_pat > 0 ? e->upload_chunk_pat : 1, root);
     return launch_end(e, KIND_PARTIAL, bytes, "traverse_s4_kernel");
 }
 
@@ -912,6 +985,7 @@ int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t
         if (cut) {
             if (i < nops && level_start) return fail(e, LKCUDA_ERR_ARG, "partial op %d overwrites a vector an earlier op of the list wrote or read: pass the ops in execution order with level_start = NULL", i);
             if (i > begin) {
+                if (e->fuse_state == 1 && i == nops) e->fuse_state = 2;     /* the last piece may carry the root branch */
                 int rc = level_start ? partial_batch_segment(e, ops, nops, level_start, nlevels) : partial_batch_segment(e, ops + begin, i - begin, NULL, 0);
                 if (rc) return rc;
             }
@@ -928,6 +1002,28 @@ int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t
         if (ops[i].right >= 0) mark[ops[i].right] |= 2;
     }
     return LKCUDA_OK;
+}
+
+/* lkcuda_partial_batch followed by lkcuda_branch_lnl(dad, node, len): what PhyloTree::computeLikelihood asks for (phylotree.cpp:1031-1071:
+   the traversal towards the root branch, then computeLikelihoodBranch on it).  When the list's last node is the branch's inner end, the
+   other end is a leaf and the shape is DNA + 4 categories, the branch is evaluated in the TAIL of the traversal launch from the registers
+   that still hold the node (no re-read of the vector, no second launch); every other case runs the two calls back to back. */
+int lkcuda_partial_batch_lnl(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t nops, const int32_t *level_start, int32_t nlevels,
+                             int32_t dad, int32_t node, double len, double *result) {
+    LK_ENTER(e);
+    if (node < 0 || node >= e->cfg.nvec || !valid_end(e, dad) || dad == node) return fail(e, LKCUDA_ERR_ARG, "lkcuda_partial_batch_lnl: bad vector / taxon id");
+    /* OFF unless LKCUDA_FUSED_LNL=1: measured on B200 (profiles/r2_s16_fused_root_lnl.txt) the traversal instantiation that carries the
+       branch is slower than the plain one by more than branch_tip_b16_kernel costs (1M patterns: 2.52 vs 2.44 ms per evaluation) */
+    static const bool on = getenv("LKCUDA_FUSED_LNL") && atoi(getenv("LKCUDA_FUSED_LNL")) != 0;
+    const bool off = !on;
+    e->fuse_state = (!off && nops > 0 && LKCUDA_IS_TIP(dad) && !(e->v.flags & LKCUDA_FLAG_SITEMODEL)) ? 1 : 0;
+    e->fuse_dad = dad; e->fuse_node = node; e->fuse_len = len;
+    int rc = lkcuda_partial_batch(e, ops, nops, level_start, nlevels);
+    const bool done = e->fuse_state == 3;
+    e->fuse_state = 0;
+    if (rc) return rc;
+    if (!done) return lkcuda_branch_lnl(e, dad, node, len, result);
+    return lkc::branch_lnl_followups(e, dad, node, len, result);
 }
 
 int lkcuda_partial_multi(lkcuda_engine *e, int32_t dst, int32_t nchild, const int32_t *child, const double *child_len) {

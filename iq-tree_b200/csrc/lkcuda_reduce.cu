@@ -80,31 +80,6 @@ __device__ __forceinline__ void group_sum(double (&a)[N], int G) {
     }
 }
 
-/* log, NaN repair, pattern_lh, frequency weighting, +ASC accumulation: the common tail of branch lnL and
-   lnL-from-buffer (phylokernel.h:828-866, 895-900, 1009-1016). acc[0..3] = {sum freq*log, scale sum, prob_const, repaired} */
-__device__ __forceinline__ void lnl_tail_vals(const DevView &v, long long p, double lh, int sc, double inv, double f, double (&acc)[4]) {
-    if (p < v.P) {
-        double l = log(fabs(lh + inv));
-        if (isnan(l) || isinf(l)) { l = LK_LOG_THR * 4.0; acc[3] += 1.0; }
-        v.pattern_lh[p] = l;
-        acc[0] += l * f;
-        if (sc) acc[1] += LK_LOG_THR * f * (double)sc;
-    } else {
-        if (sc >= 1) lh *= LK_THR;
-        acc[2] += lh + inv;
-    }
-}
-__device__ __forceinline__ void lnl_tail(const DevView &v, long long p, double lh, int sc, double (&acc)[4]) {
-    lnl_tail_vals(v, p, lh, sc, v.invar[p], p < v.P ? v.freq[p] : 0.0, acc);
-}
-
-__device__ __forceinline__ void lnl_finish(const DevView &v, const double (&acc)[4], double scale_sum) {
-    double lnl = acc[0] + scale_sum, lc = 0.0;
-    if (v.U > 0) { lc = log(1.0 - acc[2]); lnl -= v.nsite * lc; }
-    double r[LKCUDA_NRESULT] = {lnl, 0.0, 0.0, acc[2], acc[3], scale_sum, lc, 0.0};
-    publish_result(v, r);
-}
-
 /* ------------------------------------------------------------------ branch lnL ------------------------------------------------------------------ */
 
 template <bool TIP, bool VEC>
@@ -1068,6 +1043,28 @@ static int enqueue_derv(lkcuda_engine *e, double len) {
     return launch_end(e, KIND_DERV, (uint64_t)v.NP * ((uint64_t)v.B * 8 + 16), "derv_kernel");
 }
 
+/* what follows the lnL reduction of a branch (also when the traversal kernel did the reduction, lkcuda_partial_batch_lnl): the +ASC
+   correction of _pattern_lh, _pattern_lh_cat when the engine keeps it, the hand-over of the result block */
+int lkc::branch_lnl_followups(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result) {
+    const DevView &v = e->v;
+    int rc;
+    if (v.U > 0 && v.P > 0) {
+        launch_begin(e, KIND_MISC);
+        asc_adjust_kernel<<<(int)((v.P + 255) / 256 < 1184 ? (v.P + 255) / 256 : 1184), 256, 0, e->stream>>>(e->v);
+        rc = launch_end(e, KIND_MISC, 0, "asc_adjust_kernel");
+        if (rc) return rc;
+    }
+    if ((v.flags & LKCUDA_FLAG_PATTERN_LH_CAT) && v.P > 0) {
+        long long total = v.P * v.K;
+        int g2 = (int)((total + RED_THREADS - 1) / RED_THREADS < (long long)e->num_sms * 8 ? (total + RED_THREADS - 1) / RED_THREADS : (long long)e->num_sms * 8);
+        launch_begin(e, KIND_MISC);
+        pattern_lh_cat_kernel<<<g2, RED_THREADS, (size_t)((v.B + 3) & ~3) * 8, e->stream>>>(e->v, dad, node, len);
+        rc = launch_end(e, KIND_MISC, 0, "pattern_lh_cat_kernel");
+        if (rc) return rc;
+    }
+    return finish_result(e, result);
+}
+
 extern "C" {
 
 int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result) {
@@ -1094,21 +1091,7 @@ int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     uint64_t b = (uint64_t)v.B * 8;
     rc = launch_end(e, KIND_BRANCH, (uint64_t)v.NP * (tip ? b + 1 + 24 : 2 * b + 24), "branch_kernel");
     if (rc) return rc;
-    if (v.U > 0 && v.P > 0) {
-        launch_begin(e, KIND_MISC);
-        asc_adjust_kernel<<<(int)((v.P + 255) / 256 < 1184 ? (v.P + 255) / 256 : 1184), 256, 0, e->stream>>>(e->v);
-        rc = launch_end(e, KIND_MISC, 0, "asc_adjust_kernel");
-        if (rc) return rc;
-    }
-    if ((v.flags & LKCUDA_FLAG_PATTERN_LH_CAT) && v.P > 0) {
-        long long total = v.P * v.K;
-        int g2 = (int)((total + RED_THREADS - 1) / RED_THREADS < (long long)e->num_sms * 8 ? (total + RED_THREADS - 1) / RED_THREADS : (long long)e->num_sms * 8);
-        launch_begin(e, KIND_MISC);
-        pattern_lh_cat_kernel<<<g2, RED_THREADS, Bp * 8, e->stream>>>(e->v, dad, node, len);
-        rc = launch_end(e, KIND_MISC, 0, "pattern_lh_cat_kernel");
-        if (rc) return rc;
-    }
-    return finish_result(e, result);
+    return branch_lnl_followups(e, dad, node, len, result);
 }
 
 int lkcuda_pattern_lh_cat(lkcuda_engine *e, int32_t dad, int32_t node, double len) {

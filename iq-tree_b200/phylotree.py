@@ -48,6 +48,7 @@ LKCUDA_SYMBOLS = {
     "lkcuda_set_pattern_weights": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
     "lkcuda_set_model": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p, c_int32_p, c_double_p, c_double_p, c_double_p]),
     "lkcuda_partial_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, c_int32_p, C.c_int32]),
+    "lkcuda_partial_batch_lnl": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, c_int32_p, C.c_int32, C.c_int32, C.c_int32, C.c_double, c_double_p]),
     "lkcuda_partial_multi": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_int32_p, c_double_p]),
     "lkcuda_branch_lnl": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_double, c_double_p]),
     "lkcuda_pattern_lh_cat": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_double]),

@@ -463,6 +463,13 @@ int lkcuda_branch_lnl(lkcuda_engine *e, int32_t dad, int32_t node, double len, d
     return LKCUDA_OK;
 }
 
+/* the fused call of the CUDA engine, restated as its definition: the two calls back to back (phylotree.cpp:1031-1071) */
+int lkcuda_partial_batch_lnl(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t nops, const int32_t *level_start, int32_t nlevels,
+                             int32_t dad, int32_t node, double len, double *result) {
+    int rc = lkcuda_partial_batch(e, ops, nops, level_start, nlevels);
+    return rc ? rc : lkcuda_branch_lnl(e, dad, node, len, result);
+}
+
 /* _pattern_lh_cat only (phylotreesse.cpp:1194-1237) */
 int lkcuda_pattern_lh_cat(lkcuda_engine *e, int32_t dad, int32_t node, double len) {
     if (!e || node < 0 || node >= e->cfg.nvec || bad_end(e, dad)) return LKCUDA_ERR_ARG;

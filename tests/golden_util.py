@@ -118,7 +118,9 @@ def check_likelihood(t, g):
     assert abs(lnl - m["lnl"]) <= LNL_RTOL * abs(m["lnl"]), "lnL %.12f vs reference %.12f" % (lnl, m["lnl"])
     assert list(t.rootBranch()) == list(m["root_branch"]), "root branch differs"
     lnl2, plh = t.computeLikelihood(pattern_lh=True)
-    assert lnl2 == lnl
+    # the second evaluation finds every partial computed and runs the plain branch kernel, the first one may have evaluated the branch in
+    # the tail of the traversal launch (lkcuda_partial_batch_lnl): same sums, other summation order
+    assert abs(lnl2 - lnl) <= 1e-13 * abs(lnl)
     rel_close(plh, g["pattern_lh_scaled"], PTN_RTOL, "pattern_lh (scale corrected)")
     return lnl
 

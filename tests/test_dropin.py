@@ -256,3 +256,26 @@ def test_binding_short_search_on_scalar_engine(work):
     cpu = _search(du.HARNESS_REF, work, "cpu_s", [], ["-m", "HKY+G4", "-n", "1"])
     eng = _search(du.HARNESS_ORACLE, work, "eng_s", ["-cuda"], ["-m", "HKY+G4", "-n", "1"])
     assert abs(eng[1] - cpu[1]) <= 2e-3 and eng[2] == cpu[2]
+
+
+def test_reference_codon_site_frequencies_are_broken_upstream(tmp_path):
+    """Site-specific frequency models with more than 32 states (the reference's generic site-model kernels take any state
+    count, and 64-state codon data is the only alphabet beyond 32) have no parity target: the UNMODIFIED reference corrupts its heap on
+    `-st CODON -m GY -fs <file>` before the first likelihood is computed"""
+    if not os.path.exists(du.HARNESS_REF):
+        pytest.skip("unmodified reference harness not built")
+    import sys
+    sys.path.insert(0, os.path.join(du.ROOT, "oracle"))
+    import make_golden as mg
+    tmp = str(tmp_path)
+    aln, tre = mg.synth_codon(tmp, 8, 60, 5, "codon")
+    rng = np.random.default_rng(34)
+    prof = np.clip(rng.dirichlet(np.full(64, 0.8), size=7), 2e-3, None)
+    prof /= prof.sum(axis=1, keepdims=True)
+    fs = os.path.join(tmp, "codfs.sitefreq")
+    with open(fs, "w") as f:
+        for s in range(60):     # codon sites are addressed as nucleotide ranges
+            f.write("%d-%d %s\n" % (3 * s + 1, 3 * s + 3, " ".join("%.6f" % x for x in prof[rng.integers(7)])))
+    r = subprocess.run([du.HARNESS_REF, "dump", os.path.join(tmp, "out"), "-s", aln, "-st", "CODON", "-m", "GY", "-fs", fs, "-te", tre, "-nt", "1", "-seed", "1",
+                        "-pre", os.path.join(tmp, "run")], cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode != 0 and not os.path.exists(os.path.join(tmp, "out", "meta.json"))

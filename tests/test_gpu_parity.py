@@ -1,5 +1,8 @@
 """GPU suite (-m gpu): the CUDA engine, driven through the C ABI, against the golden fixtures of the unmodified
 reference AND against the CPU oracle on the same inputs."""
+import os
+import sys
+
 import numpy as np
 import pytest
 
@@ -363,3 +366,19 @@ def test_async_pattern_lh_fetch(nshard, cuda_lib):
         assert abs(df - g.meta["df_root"]) <= 1e-7 * max(1.0, abs(g.meta["df_root"]))
     gu.rel_close(plh, g["pattern_lh_scaled"], gu.PTN_RTOL, "pattern_lh")
     t.close()
+
+
+@pytest.mark.gpu
+def test_fused_root_branch_variant(cuda_lib):
+    """lkcuda_partial_batch_lnl can evaluate the root branch in the tail of the traversal launch (traverse_s4_kernel<true>, opt-in with
+    LKCUDA_FUSED_LNL=1 because it measured slower, profiles/r2_s16_fused_root_lnl.txt): the DNA fixtures, the pipelined upload and the
+    sharded runs once more with the variant switched on, in a child process (the switch is read once per process)"""
+    import subprocess
+    if os.environ.get("LKCUDA_FUSED_LNL"):
+        pytest.skip("already inside the variant run")
+    env = dict(os.environ, LKCUDA_FUSED_LNL="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-m", "gpu", "-x", "-q", "-k",
+                        "test_cuda_matches_reference or test_pipelined_tip_state_upload or test_shards_one_device or test_ragged_and_empty_shards"],
+                       env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert " passed" in r.stdout
