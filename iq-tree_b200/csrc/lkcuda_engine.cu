@@ -235,6 +235,16 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     if (ok) { rc = cudaMemsetAsync(e->d_result, 0, sizeof(double) * LKCUDA_NRESULT, e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMemsetAsync(e->d_theta_meta, 0, sizeof(double) * 8, e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMemsetAsync(e->d_states, 0, (size_t)cfg->ntaxa * v.st_stride + 4096, e->stream); ok = rc == cudaSuccess; }
+    {   /* test knob: fill everything a kernel must write before anything reads it with NaN bit patterns, so that a pattern no kernel
+           covered cannot pass for computed because the allocation happened to hold an earlier run's values */
+        static const bool poison = getenv("LKCUDA_POISON") && atoi(getenv("LKCUDA_POISON")) != 0;
+        if (poison && ok) {
+            cudaMemsetAsync(e->d_arena, 0xff, nvec * (size_t)v.vec_stride * 8, e->stream);
+            cudaMemsetAsync(e->d_scale, 0x7f, nvec * (size_t)v.sc_stride * 2, e->stream);
+            cudaMemsetAsync(e->d_theta, 0xff, (size_t)v.vec_stride * 8, e->stream);
+            cudaMemsetAsync(e->d_plh, 0xff, ((size_t)v.NP + 4) * 8, e->stream);
+        }
+    }
     if (ok) { rc = cudaMemsetAsync(e->d_scale, 0, nvec * (size_t)v.sc_stride * sizeof(int16_t), e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaStreamSynchronize(e->stream); ok = rc == cudaSuccess; }
     if (!ok) {

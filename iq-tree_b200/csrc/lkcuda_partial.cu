@@ -119,6 +119,11 @@ __global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevCh
 #endif
 #define TRV_CTHREADS (TRV_CWARPS * 32)
 #define TRV_THREADS (TRV_CTHREADS + 32)
+/* Tried on the B200 and not kept (round 2): (a) forming pattern / offset / validity of a unit where they are used instead of
+   keeping p[], off[], valid[] per unit - no unit more fits and the kernel gets 2 % slower; (b) 12 consumer warps x 152 registers with the
+   producer as a fourth warpgroup that hands its registers over (setmaxnreg): 2.33 vs 2.40 ms per 1M-pattern traversal
+   (profiles/r2_s21_traverse_setmaxnreg_variants.txt), but in 3 of 9 runs that build left the 32 patterns of ONE warp of ONE tile of a
+   partial traversal unwritten (found with LKCUDA_POISON=1, never seen with the single producer warp). */
 #define TRV_MAX_STAGES 8
 #ifndef TRV_R
 #define TRV_R 4

@@ -8,6 +8,11 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+# every engine the tests create starts with NaN-filled partial_lh / theta_all / _pattern_lh and 0x7f7f scale_num (lkcuda_create): a pattern
+# no kernel covered shows up as NaN instead of passing on whatever the allocation held before
+os.environ.setdefault("LKCUDA_POISON", "1")
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 

@@ -6,7 +6,7 @@ for d in tools/_variants/*/; do
   cp $d/liblktree_cuda.so iq-tree_b200/lib/liblktree_cuda.so
   for np in ${SIZES:-1000000 125000}; do
     echo -n "$n NP=$np: "
-    python tools/shape_bench.py 100 $np 4 4 8 2>&1 | python -c "
+    timeout 90 python tools/shape_bench.py 100 $np 4 4 8 2>&1 | python -c "
 import sys, json
 for l in sys.stdin:
     if l.startswith('{'):

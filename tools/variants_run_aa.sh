@@ -5,7 +5,7 @@ for d in tools/_variants/*/; do
   n=$(basename $d)
   cp $d/liblktree_cuda.so iq-tree_b200/lib/liblktree_cuda.so
   echo -n "$n: "
-  python tools/shape_bench.py ${SHAPE:-200 200000 20 4} 4 2>&1 | python -c "
+  timeout 120 python tools/shape_bench.py ${SHAPE:-200 200000 20 4} 4 2>&1 | python -c "
 import sys, json
 for l in sys.stdin:
     if l.startswith('{'):
