@@ -106,17 +106,37 @@ __device__ __forceinline__ void dmma(double &d0, double &d1, double a, double b)
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
-/* acc[rt][c] += sum over k-steps (ct, cc) of X[ct][cc] * frag[rt][ct][cc]   (frag: this lane's column of a fragment-ordered matrix) */
+/* acc[rt][c] += sum over k-steps (ct, cc) of X[ct][cc] * frag[rt][ct][cc]   (frag: this lane's column of a fragment-ordered matrix).
+   The k-steps run in the OUTER loop: the three accumulator tiles are independent chains, and the asm statements keep their program
+   order, so consecutive DMMAs never wait for each other (with the tiles outside, five dependent DMMAs followed one another) */
 __device__ __forceinline__ void contract(double (&acc)[MM_NT][2], const double (&X)[MM_NT][2], const double *frag) {
 #pragma unroll
-    for (int rt = 0; rt < MM_NT; rt++) {
-        acc[rt][0] = 0.0; acc[rt][1] = 0.0;
+    for (int rt = 0; rt < MM_NT; rt++) { acc[rt][0] = 0.0; acc[rt][1] = 0.0; }
 #pragma unroll
-        for (int ct = 0; ct < MM_NT; ct++) {
+    for (int ct = 0; ct < MM_NT; ct++) {
 #pragma unroll
-            for (int cc = 0; cc < 2; cc++) {
-                if (ct == MM_NT - 1 && cc == 1) continue;       /* all-padding k-step */
-                dmma(acc[rt][0], acc[rt][1], X[ct][cc], frag[((rt * MM_NT + ct) * 2 + cc) * 32]);
+        for (int cc = 0; cc < 2; cc++) {
+            if (ct == MM_NT - 1 && cc == 1) continue;       /* all-padding k-step */
+#pragma unroll
+            for (int rt = 0; rt < MM_NT; rt++) dmma(acc[rt][0], acc[rt][1], X[ct][cc], frag[((rt * MM_NT + ct) * 2 + cc) * 32]);
+        }
+    }
+}
+
+/* the two children's contractions of an internal-internal node, interleaved: six independent chains */
+__device__ __forceinline__ void contract2(double (&a0)[MM_NT][2], const double (&X0)[MM_NT][2], const double *f0,
+                                          double (&a1)[MM_NT][2], const double (&X1)[MM_NT][2], const double *f1) {
+#pragma unroll
+    for (int rt = 0; rt < MM_NT; rt++) { a0[rt][0] = 0.0; a0[rt][1] = 0.0; a1[rt][0] = 0.0; a1[rt][1] = 0.0; }
+#pragma unroll
+    for (int ct = 0; ct < MM_NT; ct++) {
+#pragma unroll
+        for (int cc = 0; cc < 2; cc++) {
+            if (ct == MM_NT - 1 && cc == 1) continue;
+#pragma unroll
+            for (int rt = 0; rt < MM_NT; rt++) {
+                dmma(a0[rt][0], a0[rt][1], X0[ct][cc], f0[((rt * MM_NT + ct) * 2 + cc) * 32]);
+                dmma(a1[rt][0], a1[rt][1], X1[ct][cc], f1[((rt * MM_NT + ct) * 2 + cc) * 32]);
             }
         }
     }
@@ -233,6 +253,31 @@ __global__ void __launch_bounds__(MM_THREADS, 1) traverse_mma20_kernel(DevView v
 
             for (int k = 0; k < K; k++) {
                 double t[MM_NT][2];
+                if (!tip0 && !tip1) {
+                    /* ---- both children are vectors: load both, contract them together ---- */
+                    double X0[MM_NT][2], X1[MM_NT][2], u[MM_NT][2];
+                    if (slot0 >= 0) {
+                        const double *ps = sl + (size_t)slot0 * K * MM_TP * MM_S;
+#pragma unroll
+                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_s_ld(ps, k, nt, pat, q); X0[nt][0] = a.x; X0[nt][1] = a.y; }
+                    } else {
+                        const double *gp = g0 + p * B + k * MM_S;
+#pragma unroll
+                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_g_ld(gp, nt, q); X0[nt][0] = a.x; X0[nt][1] = a.y; }
+                    }
+                    if (slot1 >= 0) {
+                        const double *ps = sl + (size_t)slot1 * K * MM_TP * MM_S;
+#pragma unroll
+                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_s_ld(ps, k, nt, pat, q); X1[nt][0] = a.x; X1[nt][1] = a.y; }
+                    } else {
+                        const double *gp = g1 + p * B + k * MM_S;
+#pragma unroll
+                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_g_ld(gp, nt, q); X1[nt][0] = a.x; X1[nt][1] = a.y; }
+                    }
+                    contract2(t, X0, blk0 + (size_t)k * MM_FRAG_DOUBLES + lane, u, X1, blk1 + (size_t)k * MM_FRAG_DOUBLES + lane);
+#pragma unroll
+                    for (int nt = 0; nt < MM_NT; nt++) { t[nt][0] *= u[nt][0]; t[nt][1] *= u[nt][1]; }
+                } else {
                 /* ---- child 0 ---- */
                 if (tip0) {
                     const double *row = blk0 + ((size_t)st0 * K + k) * MM_ROW + 2 * q;
@@ -270,6 +315,7 @@ __global__ void __launch_bounds__(MM_THREADS, 1) traverse_mma20_kernel(DevView v
                     contract(u, X, blk1 + (size_t)k * MM_FRAG_DOUBLES + lane);
 #pragma unroll
                     for (int nt = 0; nt < MM_NT; nt++) { t[nt][0] *= u[nt][0]; t[nt][1] *= u[nt][1]; }
+                }
                 }
                 /* ---- back to state space ---- */
                 double o[MM_NT][2];
