@@ -106,6 +106,24 @@ int lktree_compute_likelihood(lktree *h, double *lnl, double *pattern_lh) {
     LK_TRY(h) *lnl = h->tree.computeLikelihood(pattern_lh); LK_CATCH(h)
 }
 
+/* the benchmark step as a host C++ caller issues it - clearAllPartialLH(); computeLikelihood(); computeLikelihoodDerv(node1 - node2, theta
+   rebuilt) - repeated `steps` times without returning to the interpreter in between; out = {lnl, df, ddf} of the last step */
+int lktree_bench_steps(lktree *h, int32_t node1, int32_t node2, int32_t steps, double *out) {
+    LK_TRY(h)
+    Node *n1 = nodeById(h, node1), *n2 = nodeById(h, node2);
+    Neighbor *nb = n1->findNeighbor(n2);
+    if (!nb) throw std::runtime_error("nodes are not adjacent");
+    for (int s = 0; s < steps; s++) {
+        h->tree.clearAllPartialLH();
+        out[0] = h->tree.computeLikelihood(NULL);
+        h->tree.theta_computed = false;
+        h->tree.current_it = nb;
+        h->tree.current_it_back = n2->findNeighbor(n1);
+        h->tree.computeLikelihoodDerv(nb, n1, out[1], out[2]);
+    }
+    LK_CATCH(h)
+}
+
 int lktree_compute_likelihood_branch(lktree *h, int32_t node1, int32_t node2, double *lnl) {
     LK_TRY(h)
     Node *n1 = nodeById(h, node1), *n2 = nodeById(h, node2);

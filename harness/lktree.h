@@ -81,6 +81,8 @@ int lktree_compute_likelihood(lktree *h, double *lnl, double *pattern_lh /* [loc
    goes on (e.g. with computeLikelihoodDerv) and calls lktree_wait_pattern_lh before reading them */
 int lktree_compute_likelihood_async_fetch(lktree *h, double *lnl, double *pattern_lh);
 int lktree_wait_pattern_lh(lktree *h);
+/* bench.py's timed loop: `steps` x { clearAllPartialLH; computeLikelihood; computeLikelihoodDerv(node1 - node2, theta rebuilt) }; out[3] = lnl, df, ddf */
+int lktree_bench_steps(lktree *h, int32_t node1, int32_t node2, int32_t steps, double *out);
 int lktree_compute_likelihood_branch(lktree *h, int32_t node1, int32_t node2, double *lnl);
 int lktree_compute_likelihood_derv(lktree *h, int32_t node1, int32_t node2, int32_t reset_theta, double *df, double *ddf);
 int lktree_compute_likelihood_from_buffer(lktree *h, double *lnl);

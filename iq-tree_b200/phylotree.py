@@ -128,6 +128,7 @@ LKTREE_SYMBOLS = {
     "lktree_wait_pattern_lh": (C.c_int, [C.c_void_p]),
     "lktree_compute_likelihood_branch": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_double_p]),
     "lktree_compute_likelihood_derv": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p]),
+    "lktree_bench_steps": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p]),
     "lktree_compute_likelihood_from_buffer": (C.c_int, [C.c_void_p, c_double_p]),
     "lktree_optimize_one_branch": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p]),
     "lktree_get_best_nni_for_bran": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p]),
@@ -396,6 +397,12 @@ class PhyloTree:
         df, ddf = C.c_double(), C.c_double()
         self._ck(self.lib.lktree_compute_likelihood_derv(self.h, node1, node2, int(reset_theta), C.byref(df), C.byref(ddf)))
         return df.value, ddf.value
+
+    def benchSteps(self, node1, node2, steps):
+        """`steps` x { clearAllPartialLH; computeLikelihood; computeLikelihoodDerv(node1 - node2, theta rebuilt) } driven from C++"""
+        out = (C.c_double * 3)()
+        self._ck(self.lib.lktree_bench_steps(self.h, node1, node2, steps, out))
+        return out[0], out[1], out[2]
 
     def computeLikelihoodFromBuffer(self):
         lnl = C.c_double()
