@@ -222,7 +222,12 @@ int lkcuda_wait_result(lkcuda_engine *e, double *result);
    that lkcuda_wait_result returns the GLOBAL sums on every rank (bit-identical across ranks).  All ranks must enqueue the same
    sequence of reductions (they do: tree, model and host control flow are replicated).  `handles`: [world][LKCUDA_PEER_HANDLE_BYTES]
    or NULL; `raw_ptrs`: [world] device addresses or NULL; entry `rank` of either is ignored.  A peer that never shows up makes the
-   kernel give up after 10 s and the next lkcuda_wait_result fail with LKCUDA_ERR_STATE. */
+   kernel give up after 10 s and the next lkcuda_wait_result fail with LKCUDA_ERR_STATE.
+   CONSTRAINT: a reduction kernel WAITS, on the device, for its peers' kernels - the peers' kernels must be able to run while it
+   waits.  One process per GPU satisfies that by construction.  Engines of ONE process on one device (several shards driven by one
+   host thread) need the device to run their streams concurrently and the host to queue every shard's preceding work before the
+   first reduction is launched (harness/lk_phylotree.cpp does): under CUDA_LAUNCH_BLOCKING=1, compute-sanitizer or ncu (which
+   serialise kernels) such a set-up runs into the 10 s time-out; use lkcuda_detach_peers and add the shards' blocks on the host there. */
 int lkcuda_peer_handle(lkcuda_engine *e, uint8_t *handle /*[LKCUDA_PEER_HANDLE_BYTES] or NULL*/, void **local_ptr /*or NULL*/);
 int lkcuda_attach_peers(lkcuda_engine *e, int32_t rank, int32_t world, const uint8_t *handles, void *const *raw_ptrs);
 int lkcuda_detach_peers(lkcuda_engine *e);
