@@ -55,6 +55,7 @@ WORKLOAD = "synthetic DNA %d taxa x %d patterns, GTR+G4 (BASELINE configs[1])" %
 METRIC = "partial-LH updates/s (patterns x cats x nodes)"
 HARNESS_REF = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
 HARNESS_CUDA = os.path.join(ROOT, "oracle", "_ref", "ref_harness_cuda")
+HARNESS_FMA = os.path.join(ROOT, "oracle", "_ref", "ref_harness_fma")
 AA = "ARNDCQEGHILKMFPSTWYV"
 SENSE = [a + b + c for a in "ACGT" for b in "ACGT" for c in "ACGT" if a + b + c not in ("TAA", "TAG", "TGA")]
 

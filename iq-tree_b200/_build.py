@@ -161,4 +161,6 @@ def build_reference(jobs=8):
     # the same sources with the reference-side binding (integration/) applied, linked against the product and the oracle libraries
     build_cuda(); build_oracle()
     _run(["make", "-f", os.path.join("oracle", "Makefile.ref"), "-j%d" % jobs, "cuda"], cwd=ROOT)
+    # the second CPU baseline of SURVEY 8(d): the reference built as IQTREE_FLAGS="omp fma"
+    _run(["make", "-f", os.path.join("oracle", "Makefile.ref"), "-j%d" % jobs, "fma"], cwd=ROOT)
     return REF_HARNESS
