@@ -649,6 +649,20 @@ def main():
                                             "optimize_all_branches_1_ms": ref["oab_s_mean"] * 1e3, "setup_s": ref["setup_s"]}
                 else:
                     line["cpu_baseline"] = None
+                # SURVEY 8(d) also asks for the "omp fma" build of the reference and for -nt 1 (bounded: one or two timed steps on the full workload)
+                extra = {}
+                if CPU_STEPS > 0:
+                    fma = run_harness(HARNESS_FMA, fargs, max(1, CPU_STEPS // 2), warmup=1, cwd=tmp)
+                    if fma is not None:
+                        extra["omp_fma"] = {"value": (NTAXA - 2) * fma["nptn"] * NCAT / fma["step_s_mean"], "unit": "updates/s", "cores": fma["threads"],
+                                            "kernel": fma["kernel"], "ms_per_step": fma["step_s_mean"] * 1e3, "steps": fma["lnl_reps"],
+                                            "build": "oracle/Makefile.ref fma (-mavx -mfma for every unit, CMakeLists.txt:249-267)"}
+                    one = run_harness(HARNESS_REF, fargs, 1, warmup=0, threads=1, cwd=tmp)
+                    if one is not None:
+                        extra["nt1"] = {"value": (NTAXA - 2) * one["nptn"] * NCAT / one["step_s_mean"], "unit": "updates/s", "cores": 1,
+                                        "kernel": one["kernel"], "ms_per_step": one["step_s_mean"] * 1e3, "steps": one["lnl_reps"]}
+                if extra and line.get("cpu_baseline"):
+                    line["cpu_baseline"]["other_builds"] = extra
                 if WITH_DROPIN:
                     dro = run_harness(HARNESS_CUDA, fargs, args.steps, oab_reps=1, warmup=2, cuda=True, threads=1, cwd=tmp)
                     if dro is not None:
