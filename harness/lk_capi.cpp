@@ -106,6 +106,14 @@ int lktree_compute_likelihood(lktree *h, double *lnl, double *pattern_lh) {
     LK_TRY(h) *lnl = h->tree.computeLikelihood(pattern_lh); LK_CATCH(h)
 }
 
+/* how often getBestNNIForBran ran in its queued form (device length slots) and how often that had to be redone call by call */
+int lktree_nni_queued_stats(lktree *h, uint64_t *calls, uint64_t *fallbacks) {
+    LK_TRY(h)
+    if (calls) *calls = h->tree.nni_queued_calls;
+    if (fallbacks) *fallbacks = h->tree.nni_queued_fallbacks;
+    LK_CATCH(h)
+}
+
 /* the benchmark step as a host C++ caller issues it - clearAllPartialLH(); computeLikelihood(); computeLikelihoodDerv(node1 - node2, theta
    rebuilt) - repeated `steps` times without returning to the interpreter in between; out = {lnl, df, ddf} of the last step */
 int lktree_bench_steps(lktree *h, int32_t node1, int32_t node2, int32_t steps, double *out) {

@@ -27,7 +27,8 @@ enum { NNI_VECS = 6 };     // IT_NUM of getBestNNIForBran with params->nni5 (phy
 
 PhyloTree::PhyloTree()
     : leafNum(0), nodeNum(0), root(NULL), min_branch_length(1e-6), max_branch_length(100.0),
-      device_newton(false), generic_kernel(false), current_it(NULL), current_it_back(NULL),
+      device_newton(false), nni_queued(true), nni_queued_calls(0), nni_queued_fallbacks(0), nni_async_(false), nni_next_slot_(0),
+      generic_kernel(false), current_it(NULL), current_it_back(NULL),
       theta_computed(false), num_partial_lh_computations(0), nstates(0), ncat(1), nmix(1), family(FAMILY_PLAIN),
       state_unknown(0), seq_type(SEQ_DNA), ntaxa(0), nptn(0), nunobs(0), nsite(0), p_invar_(0.0),
       proc_rank_(0), proc_world_(1), allreduce_(NULL), allreduce_user_(NULL), stream_(NULL), peers_attached_(false), boot_nsamples_(0),
@@ -590,7 +591,7 @@ void PhyloTree::computePartialLikelihood(Neighbor *dad_branch, Node *dad) {
     op.dst = dad_branch->vec;
     op.left = left->node->isLeaf() ? LKCUDA_TIP(left->node->id) : left->vec;
     op.right = right->node->isLeaf() ? LKCUDA_TIP(right->node->id) : right->vec;
-    op.reserved = 0;
+    op.reserved = LKCUDA_LEN_REFS(left->len_slot, right->len_slot);      // 0 unless a queued NNI left a length on the device
     op.len_left = left->length;
     op.len_right = right->length;
     int level = 1 + std::max(opLevel(left), opLevel(right));
@@ -987,6 +988,17 @@ void PhyloTree::optimizeOneBranch(Node *node1, Node *node2, bool clearLH, int ma
         flushPartialOps();
         theta_computed = true;
         int32_t dad_end = dad->isLeaf() ? LKCUDA_TIP(dad->id) : node_branch->vec;
+        if (nni_async_) {
+            // queued NNI: no wait.  The run starts from the branch's current length (a host value, or the slot an earlier run of this
+            // NNI pair left it in) and leaves optx in a fresh slot, which later node updates, Newton starts and the score refer to
+            if (nni_next_slot_ >= LKCUDA_NLENSLOT) throw std::runtime_error("queued NNI: out of length slots");
+            const int slot = nni_next_slot_++;
+            check(lkcuda_theta_newton_async(engines_[0], dad_end, dad_branch->vec, min_branch_length, current_len, current_it->len_slot, max_branch_length,
+                                            min_branch_length, maxNRStep, slot), engines_[0], "lkcuda_theta_newton_async");
+            current_it->len_slot = slot; current_it_back->len_slot = slot;
+            nni_touched_.push_back(current_it); nni_touched_.push_back(current_it_back);
+            return;     // the "diverged to the upper bound" rule below is applied by getBestNNIForBran once the slots are back
+        }
         double out[4];
         check(lkcuda_theta_newton(engines_[0], dad_end, dad_branch->vec, min_branch_length, current_len, max_branch_length, min_branch_length, maxNRStep, out),
               engines_[0], "lkcuda_theta_newton");
@@ -1022,6 +1034,14 @@ PhyloTree::NNIMove PhyloTree::getBestNNIForBran(Node *node1, Node *node2, NNIMov
     if (engines_.empty()) initializeAllPartialLh();
     const int NNI_MAX_NR_STEP = 10;                 // pllnni.cpp:21
     const int IT_NUM = nni5 ? 6 : 2;
+    /* queued form: the ten branch optimisations and the two scores of the call are queued with ONE host wait per NNI;
+       optimised lengths stay in device length slots until the end.  Same statements otherwise; if a run did not converge or a length
+       ran into the upper bound (the rule of optimizeOneBranch that needs a host decision), the call is redone one step at a time. */
+    static const bool env_off = getenv("LKTREE_NNI_QUEUED") && atoi(getenv("LKTREE_NNI_QUEUED")) == 0;      // measurement knob
+    const bool queued = nni_queued && !env_off && device_newton && engines_.size() == 1 && !allreduce_ && !peers_attached_;
+    int len_slots[2][5];
+    for (int a = 0; a < 2; a++) for (int b = 0; b < 5; b++) len_slots[a][b] = -1;
+    if (queued) { nni_async_ = true; nni_next_slot_ = 0; nni_touched_.clear(); nni_queued_calls++; }
     Neighbor **saved_it[6];
     int id = 0;
     auto slot = [](Node *at, Node *to) -> Neighbor** {
@@ -1063,23 +1083,33 @@ PhyloTree::NNIMove PhyloTree::getBestNNIForBran(Node *node1, Node *node2, NNIMov
                 (*it)->node->findNeighbor(node1)->partial_lh_computed = 0;
                 optimizeOneBranch(node1, (*it)->node, false, NNI_MAX_NR_STEP);
                 moves[cnt].newLen[i] = node1->findNeighbor((*it)->node)->length;
+                len_slots[cnt][i] = node1->findNeighbor((*it)->node)->len_slot;
                 i++;
             }
             node21_it->partial_lh_computed = 0;
         }
         optimizeOneBranch(node1, node2, false, NNI_MAX_NR_STEP);
         moves[cnt].newLen[0] = node1->findNeighbor(node2)->length;
+        len_slots[cnt][0] = node1->findNeighbor(node2)->len_slot;
         if (nni5) {
             FOR_NEI(node2, node1, it) {
                 (*it)->node->findNeighbor(node2)->partial_lh_computed = 0;
                 optimizeOneBranch(node2, (*it)->node, false, NNI_MAX_NR_STEP);
                 moves[cnt].newLen[i] = node2->findNeighbor((*it)->node)->length;
+                len_slots[cnt][i] = node2->findNeighbor((*it)->node)->len_slot;
                 i++;
             }
             node12_it->partial_lh_computed = 0;
         }
         for (; i < 5; i++) moves[cnt].newLen[i] = 0.0;
-        moves[cnt].newloglh = computeLikelihoodFromBuffer();
+        if (queued) {
+            // the score at the length the last run left on the device: the only host wait of this NNI
+            check(lkcuda_lnl_from_buffer_slot(engines_[0], current_it->len_slot, NULL), engines_[0], "lkcuda_lnl_from_buffer_slot");
+            double r[LKCUDA_NRESULT];
+            reduceResult(r);
+            moves[cnt].newloglh = r[LKCUDA_R_LNL];
+        } else
+            moves[cnt].newloglh = computeLikelihoodFromBuffer();
         // swap back
         *node1_it = node1_nei;
         node1_nei->node->findNeighbor(node2)->node = node1;
@@ -1096,6 +1126,30 @@ PhyloTree::NNIMove PhyloTree::getBestNNIForBran(Node *node1, Node *node2, NNIMov
     // restore the length of 4 branches around node1, node2
     FOR_NEI(node1, node2, it) (*it)->length = (*it)->node->findNeighbor(node1)->length;
     FOR_NEI(node2, node1, it) (*it)->length = (*it)->node->findNeighbor(node2)->length;
+    if (queued) {
+        nni_async_ = false;
+        // the tree's own neighbours that took part only ever carried a slot number (their lengths were never overwritten); the temporary
+        // ones are gone: every survivor goes back to "length is the value"
+        FOR_NEI(node1, node2, it) { (*it)->len_slot = -1; (*it)->node->findNeighbor(node1)->len_slot = -1; }
+        FOR_NEI(node2, node1, it) { (*it)->len_slot = -1; (*it)->node->findNeighbor(node2)->len_slot = -1; }
+        node1->findNeighbor(node2)->len_slot = -1; node2->findNeighbor(node1)->len_slot = -1;
+        nni_touched_.clear();
+        double lens[LKCUDA_NLENSLOT], info[4 * LKCUDA_NLENSLOT];
+        check(lkcuda_len_slots_fetch(engines_[0], lens, info), engines_[0], "lkcuda_len_slots_fetch");
+        bool redo = false;
+        for (int sl = 0; sl < nni_next_slot_; sl++)
+            if ((int)info[4 * sl + 3] != 1 || lens[sl] > max_branch_length * 0.95) redo = true;
+        if (redo) {
+            nni_queued_fallbacks++;
+            const bool keep = nni_queued;
+            nni_queued = false;
+            NNIMove best = getBestNNIForBran(node1, node2, moves, nni5);
+            nni_queued = keep;
+            return best;
+        }
+        for (int cnt = 0; cnt < 2; cnt++)
+            for (int b = 0; b < 5; b++) if (len_slots[cnt][b] >= 0) moves[cnt].newLen[b] = lens[len_slots[cnt][b]];
+    }
     return moves[0].newloglh > moves[1].newloglh ? moves[0] : moves[1];
 }
 

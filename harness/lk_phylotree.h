@@ -52,7 +52,8 @@ struct Neighbor {
     int vec;                    // arena vector holding the partial of the subtree rooted at `node`; -1 = none (leaf)
     int partial_lh_computed;    // bit 0 = likelihood partial up to date, bit 1 = parsimony partial up to date
     int pars_vec;               // partial_pars: block index in central_partial_pars (a neighbour that points to a leaf uses the tip's vector instead)
-    Neighbor(Node *n, double len) : node(n), length(len), id(-1), vec(-1), partial_lh_computed(0), pars_vec(-1) {}
+    int len_slot;               // >= 0 while an NNI is queued: the branch's current length is in this device length slot (lkcuda.h), not in `length`
+    Neighbor(Node *n, double len) : node(n), length(len), id(-1), vec(-1), partial_lh_computed(0), pars_vec(-1), len_slot(-1) {}
 };
 
 struct Node {
@@ -141,6 +142,7 @@ public:
        surrounding branches re-optimised by Newton-Raphson (NNI_MAX_NR_STEP = 10, pllnni.cpp:21); the tree is left as it was */
     struct NNIMove { double newloglh; double newLen[5]; int node1_nei, node2_nei; /* ids of the swapped subtrees' roots */ };
     NNIMove getBestNNIForBran(Node *node1, Node *node2, NNIMove moves[2], bool nni5 = true);
+    uint64_t nni_queued_calls, nni_queued_fallbacks;    // how often the queued form ran / had to be redone call by call
     /* the consumers of _pattern_lh_cat and _pattern_lh on the device */
     double optimizeMixtureWeights();                                 // ModelMixture::optimizeWeights, model/modelmixture.cpp:1356-1416
     const std::vector<double> &mixtureWeights() const { return mixprops_; }
@@ -189,6 +191,7 @@ public:
     /* parameters (tools.cpp:785-786, phyloanalysis.cpp:2488-2497) */
     double min_branch_length, max_branch_length;
     bool device_newton;          // run minimizeNewton's loop on the device (single shard only)
+    bool nni_queued;             // with device_newton: queue a whole NNI (5 branch optimisations + score) without waiting (device length slots)
     bool generic_kernel;         // -fastlk semantics: zero guard + _pattern_lh_cat in every branch call
 
     Neighbor *current_it, *current_it_back;
@@ -222,6 +225,9 @@ private:
     std::vector<uint32_t> pars_counts_;                              // [op][2] of the last flush
 
     struct BranchRequest { int32_t dad_end, node_vec; double len; };
+    bool nni_async_;             // inside a queued NNI: optimizeOneBranch queues, lengths live in slots
+    int nni_next_slot_;
+    std::vector<Neighbor*> nni_touched_;
     void flushPartialOps(const BranchRequest *branch = NULL);
     void enqueuePatternLhCat();
     int collapsePatternLhCat(int wsl);

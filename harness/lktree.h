@@ -81,6 +81,9 @@ int lktree_compute_likelihood(lktree *h, double *lnl, double *pattern_lh /* [loc
    goes on (e.g. with computeLikelihoodDerv) and calls lktree_wait_pattern_lh before reading them */
 int lktree_compute_likelihood_async_fetch(lktree *h, double *lnl, double *pattern_lh);
 int lktree_wait_pattern_lh(lktree *h);
+/* PhyloTree::getBestNNIForBran in its queued form (with device_newton: the ten branch optimisations of a call are queued through device
+   length slots, one host wait per NNI): calls that took it / calls that had to be redone step by step (a run hit the upper bound) */
+int lktree_nni_queued_stats(lktree *h, uint64_t *calls, uint64_t *fallbacks);
 /* bench.py's timed loop: `steps` x { clearAllPartialLH; computeLikelihood; computeLikelihoodDerv(node1 - node2, theta rebuilt) }; out[3] = lnl, df, ddf */
 int lktree_bench_steps(lktree *h, int32_t node1, int32_t node2, int32_t steps, double *out);
 int lktree_compute_likelihood_branch(lktree *h, int32_t node1, int32_t node2, double *lnl);

@@ -92,10 +92,19 @@ typedef struct lkcuda_partial_op {
     int32_t dst;            /* vector receiving L_dad                          */
     int32_t left;           /* vector (>=0) or LKCUDA_TIP(taxon)               */
     int32_t right;          /* vector (>=0) or LKCUDA_TIP(taxon)               */
-    int32_t reserved;
+    int32_t reserved;       /* 0, or LKCUDA_LEN_REFS(left_slot, right_slot): take a child's branch length from a device length slot */
     double  len_left;       /* left->length                                    */
     double  len_right;      /* right->length                                   */
 } lkcuda_partial_op;
+
+/* ---- device length slots ----
+   PhyloTree::getBestNNIForBran (phylotree.cpp:2873-3066) optimises five branches per NNI, and every optimised length feeds the next node
+   update: driven call by call, the host waits for each Newton run before it can state the next op's lengths.  A length slot breaks that
+   dependency: lkcuda_theta_newton_async leaves the optimised length in slot s ON THE DEVICE, a later op names the slot instead of a value
+   (LKCUDA_LEN_REFS), a later Newton run may start from it, lkcuda_lnl_from_buffer_slot evaluates at it - the whole NNI is queued
+   without a host wait and lkcuda_len_slots_fetch returns all lengths at the end.  Slot -1 = none. */
+#define LKCUDA_NLENSLOT 64
+#define LKCUDA_LEN_REFS(left_slot, right_slot) ((int32_t)((((left_slot) + 1) & 0xffff) | ((((right_slot) + 1) & 0xffff) << 16)))
 
 /* results of the reductions, all additive over shards except [LKCUDA_R_PROB_CONST] */
 enum {
@@ -195,6 +204,18 @@ int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result);
    (site-specific models: host-driven steps); with peers attached every evaluation is exchanged inside the loop. */
 int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, double xacc,
                          int32_t max_nr_step, double *out);
+/* lkcuda_theta_newton without the wait: theta_all of (dad, node) and minimizeNewton are queued; the start is `xguess`, or the content of
+   slot `xguess_slot` when that is >= 0; the run leaves optx in slot `len_slot` and {optx, d2l, evaluations, status} beside it
+   (status 1 = converged, 2 / 3 / 4 = the errors lkcuda_theta_newton reports).  One engine without peers, shapes that have a
+   persistent Newton kernel; returns LKCUDA_ERR_STATE otherwise (the caller then uses the synchronous calls). */
+int lkcuda_theta_newton_async(lkcuda_engine *e, int32_t dad, int32_t node, double x1, double xguess, int32_t xguess_slot, double x2,
+                              double xacc, int32_t maxNRStep, int32_t len_slot);
+/* lkcuda_lnl_from_buffer at the length held by a slot */
+int lkcuda_lnl_from_buffer_slot(lkcuda_engine *e, int32_t len_slot, double *result);
+/* set slots from the host (n values starting at slot `first`), and read all of them back after the queued work has finished:
+   lens[LKCUDA_NLENSLOT], info[LKCUDA_NLENSLOT][4] = {optx, d2l, evaluations, status} (either may be NULL) */
+int lkcuda_len_slots_set(lkcuda_engine *e, int32_t first, int32_t n, const double *values);
+int lkcuda_len_slots_fetch(lkcuda_engine *e, double *lens, double *info);
 
 /* lkcuda_theta_build + lkcuda_newton_branch on the branch (dad, node) in one call - for DNA with 4 categories ONE persistent launch that
    builds theta_all in its first Newton step, for other shapes theta_kernel + one persistent launch (optimizeOneBranch's device part, phylotree.cpp:2148-2170); same out[4] */

@@ -54,7 +54,7 @@ struct DevOp {
 
 struct DevChild {
     int32_t id;         /* vector (>=0) or LKCUDA_TIP(taxon)                    */
-    int32_t pad;
+    int32_t pad;        /* 0, or 1 + the device length slot that holds this branch's length (lkcuda.h: length slots) */
     double  len;
 };
 
@@ -88,6 +88,9 @@ struct DevView {
     double *host_result; unsigned int seq;
     int peer_world, peer_rank; unsigned int peer_seq;
     PeerMbox *const *peer_mbox;
+    /* device length slots (lkcuda.h): lens[LKCUDA_NLENSLOT] branch lengths written by the persistent Newton kernels and read by the table
+       kernels / lnL-from-buffer of later launches, then [LKCUDA_NLENSLOT][4] = {optx, d2l, evaluations, status} of the run that wrote a slot */
+    double *lens;
     /* site-specific frequency models (LKCUDA_FLAG_SITEMODEL): pattern -> eigensystem, tip code -> set of plain states */
     const int32_t *ptn_model; const unsigned long long *state_mask;
 };
@@ -125,6 +128,7 @@ struct lkcuda_engine {
     unsigned int result_seq;                /* sequence number of the last publishing launch */
     lkc::PeerMbox *d_mbox; lkc::PeerMbox **d_peer_tab; void *peer_opened[LKCUDA_MAX_PEERS]; unsigned int peer_seq;
     double *d_newton_out; double *h_newton_out;
+    double *d_lens; double *h_lens;         /* device length slots and the pinned buffer lkcuda_len_slots_fetch copies them to */
     void *d_newton_ctl; int newton_max_grid;   /* state of the persistent Newton kernel; the largest grid that is co-resident */
     /* transition tables */
     double *d_tables; long long table_slots_cap;
@@ -204,6 +208,11 @@ int upload_verdict(lkcuda_engine *e);
 namespace lkc {
 
 struct __align__(32) d4 { double x, y, z, w; };
+
+/* length of the branch to a child: the value the caller gave, or the device slot a Newton run of an earlier launch left it in */
+__device__ __forceinline__ double child_len(const DevView &v, const DevChild &ch) {
+    return ch.pad ? __ldcg(v.lens + (ch.pad - 1)) : ch.len;
+}
 
 /* whole-sector streaming accesses: LDG.E.256 / STG.E.256 on sm_100a */
 __device__ __forceinline__ d4 ld_stream256(const double *p) {

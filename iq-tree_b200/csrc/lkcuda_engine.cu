@@ -161,7 +161,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     e->d_eval = e->d_evec = e->d_inv = e->d_rate = e->d_weight = e->d_tip = NULL; e->d_eigen = NULL;
     e->d_arena = NULL; e->d_scale = NULL; e->d_theta = NULL; e->d_theta_sc = NULL; e->d_theta_meta = NULL;
     e->dstream = NULL; e->ev_plh_ready = NULL; e->ev_plh_done = NULL; e->plh_pending = false;
-    e->d_plh = e->d_plhcat = e->d_plh_out = NULL; e->d_red = NULL; e->d_counter = NULL; e->d_result = NULL; e->h_result = NULL;
+    e->d_plh = e->d_plhcat = e->d_plh_out = NULL; e->d_red = NULL; e->d_counter = NULL; e->d_result = NULL; e->h_result = NULL; e->d_lens = NULL; e->h_lens = NULL;
     e->d_newton_out = NULL; e->h_newton_out = NULL; e->d_newton_ctl = NULL; e->newton_max_grid = 0;
     e->d_ptn_model = NULL; e->d_state_mask = NULL;
     e->h_mapped = NULL; e->result_seq = 0; e->d_mbox = NULL; e->d_peer_tab = NULL; e->peer_seq = 0;
@@ -218,10 +218,13 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     ALLOC(e->d_plh, v.NP + 4); ALLOC(e->d_plhcat, (size_t)v.P * v.K + 4);
     ALLOC(e->d_red, (size_t)e->red_blocks * RED_SLOTS); ALLOC(e->d_counter, 4); ALLOC(e->d_result, LKCUDA_NRESULT);
     ALLOC(e->d_newton_out, 8);
+    ALLOC(e->d_lens, 5 * LKCUDA_NLENSLOT);
     ALLOC(e->d_upload_flag, 4);
 #undef ALLOC
     if (ok) { rc = cudaMallocHost((void **)&e->h_result, sizeof(double) * LKCUDA_NRESULT); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaMallocHost((void **)&e->h_newton_out, sizeof(double) * 8); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMallocHost((void **)&e->h_lens, sizeof(double) * 5 * LKCUDA_NLENSLOT); ok = rc == cudaSuccess; }
+    if (ok) { rc = cudaMemsetAsync(e->d_lens, 0, sizeof(double) * 5 * LKCUDA_NLENSLOT, e->stream); ok = rc == cudaSuccess; }
     if (ok) { rc = cudaHostAlloc((void **)&e->h_mapped, sizeof(double) * 2 * LKCUDA_NRESULT, cudaHostAllocMapped); ok = rc == cudaSuccess; }
     if (ok) memset(e->h_mapped, 0, sizeof(double) * 2 * LKCUDA_NRESULT);
     if (ok) { rc = cudaMallocHost((void **)&e->h_upload_vals, sizeof(unsigned int) * (lkcuda_engine::UPLOAD_MAX_CHUNKS + 1)); ok = rc == cudaSuccess; }
@@ -258,7 +261,7 @@ int lkcuda_create(const lkcuda_config *cfg, lkcuda_engine **out) {
     e->own_vec_stride = v.vec_stride; e->own_sc_stride = v.sc_stride; e->own_nvec = cfg->nvec;
     v.arena = e->d_arena; v.scale = e->d_scale; v.theta = e->d_theta; v.theta_sc = e->d_theta_sc; v.theta_meta = e->d_theta_meta;
     v.pattern_lh = e->d_plh; v.pattern_lh_cat = e->d_plhcat;
-    v.red = e->d_red; v.counter = e->d_counter; v.result = e->d_result;
+    v.red = e->d_red; v.counter = e->d_counter; v.result = e->d_result; v.lens = e->d_lens;
     v.tables = NULL;
     {   /* device-side address of the host-mapped result block (identical under UVA; asked for all the same) */
         void *dp = NULL;
@@ -288,7 +291,7 @@ int lkcuda_destroy(lkcuda_engine *e) {
     cudaFree(e->d_eval); cudaFree(e->d_evec); cudaFree(e->d_inv); cudaFree(e->d_rate); cudaFree(e->d_weight); cudaFree(e->d_eigen);
     cudaFree(e->d_tip); cudaFree(e->d_arena); cudaFree(e->d_scale); cudaFree(e->d_theta); cudaFree(e->d_theta_sc); cudaFree(e->d_theta_meta);
     if (e->dstream) { cudaStreamSynchronize(e->dstream); cudaStreamDestroy(e->dstream); cudaEventDestroy(e->ev_plh_ready); cudaEventDestroy(e->ev_plh_done); }
-    cudaFree(e->d_plh); cudaFree(e->d_plhcat); cudaFree(e->d_plh_out); cudaFree(e->d_red); cudaFree(e->d_counter); cudaFree(e->d_result);
+    cudaFree(e->d_plh); cudaFree(e->d_plhcat); cudaFree(e->d_plh_out); cudaFree(e->d_red); cudaFree(e->d_counter); cudaFree(e->d_result); cudaFree(e->d_lens); if (e->h_lens) cudaFreeHost(e->h_lens);
     cudaFree(e->d_newton_out); cudaFree(e->d_newton_ctl); cudaFree(e->d_tables); cudaFree(e->d_inv_frags);
     if (e->h_result) cudaFreeHost(e->h_result);
     if (e->h_newton_out) cudaFreeHost(e->h_newton_out);

@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevCh
     double *tab = ech + (long long)K * MS;
     for (int idx = threadIdx.x; idx < B; idx += blockDim.x) {
         int k = idx / S, j = idx - k * S;
-        sh_ex[idx] = exp(v.eval[v.blk_eigen[k] * S + j] * (v.blk_rate[k] * ch.len));
+        sh_ex[idx] = exp(v.eval[v.blk_eigen[k] * S + j] * (v.blk_rate[k] * child_len(v, ch)));
     }
     __syncthreads();
     const int SS = S * S;
@@ -693,9 +693,10 @@ int lkc::schedule_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
                 n.op = i; n.dst_slot = -1;
                 int k0 = kid0[i], k1 = kid1[i];
                 n.src0 = ops[i].left; n.len0 = ops[i].len_left; n.src1 = ops[i].right; n.len1 = ops[i].len_right;
+                n.ref0 = ops[i].reserved & 0xffff; n.ref1 = (ops[i].reserved >> 16) & 0xffff;
                 /* the child executed right before this node goes to position 1 and is taken from registers */
                 if (k0 >= 0 && k0 != k1 && pos[k0] == j - 1 && last_kid[k0] && !(k1 >= 0 && pos[k1] == j - 1)) {
-                    std::swap(n.src0, n.src1); std::swap(n.len0, n.len1); std::swap(k0, k1);
+                    std::swap(n.src0, n.src1); std::swap(n.len0, n.len1); std::swap(n.ref0, n.ref1); std::swap(k0, k1);
                 }
                 n.slot0 = n.slot1 = -1;
                 if (k0 >= 0) { n.slot0 = slot_of[k0]; }
@@ -838,8 +839,8 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
         t.src1_lh = n.src1 >= 0 ? e->v.arena + (size_t)n.src1 * v.vec_stride : NULL;
         t.pad[0] = t.pad[1] = 0;
         DevChild &a = e->h_child[slot][2 * j], &b = e->h_child[slot][2 * j + 1];
-        a.id = n.src0; a.pad = 0; a.len = n.len0;
-        b.id = n.src1; b.pad = 0; b.len = n.len1;
+        a.id = n.src0; a.pad = n.ref0; a.len = n.len0;
+        b.id = n.src1; b.pad = n.ref1; b.len = n.len1;
         int ntip = (LKCUDA_IS_TIP(a.id) ? 1 : 0) + (LKCUDA_IS_TIP(b.id) ? 1 : 0);
         bytes += op_bytes(v, ntip, 2 - ntip);
         e->kind_flops[KIND_PARTIAL] += op_flops(v, ntip, 2 - ntip);
@@ -947,8 +948,8 @@ static int partial_batch_segment(lkcuda_engine *e, const lkcuda_partial_op *ops,
         DevOp &d = e->h_ops[slot][i];
         d.dst = ops[i].dst; d.nchild = 2; d.child0 = 2 * i; d.pad = 0;
         DevChild &a = e->h_child[slot][2 * i], &b = e->h_child[slot][2 * i + 1];
-        a.id = ops[i].left; a.pad = 0; a.len = ops[i].len_left;
-        b.id = ops[i].right; b.pad = 0; b.len = ops[i].len_right;
+        a.id = ops[i].left; a.pad = ops[i].reserved & 0xffff; a.len = ops[i].len_left;
+        b.id = ops[i].right; b.pad = (ops[i].reserved >> 16) & 0xffff; b.len = ops[i].len_right;
         int ntip = (LKCUDA_IS_TIP(a.id) ? 1 : 0) + (LKCUDA_IS_TIP(b.id) ? 1 : 0);
         lbytes[l] += op_bytes(e->v, ntip, 2 - ntip);
         e->kind_flops[KIND_PARTIAL] += op_flops(e->v, ntip, 2 - ntip);
@@ -977,6 +978,7 @@ int lkcuda_partial_batch(lkcuda_engine *e, const lkcuda_partial_op *ops, int32_t
         if (!LKCUDA_IS_TIP(op.left) && LKCUDA_IS_TIP(op.right))
             return fail(e, LKCUDA_ERR_ARG, "partial op %d: a leaf child must be 'left' (phylokernel.h:116-121)", i);
         if (op.dst == op.left || op.dst == op.right) return fail(e, LKCUDA_ERR_ARG, "partial op %d: destination aliases a child", i);
+        if ((op.reserved & 0xffff) > LKCUDA_NLENSLOT || ((op.reserved >> 16) & 0xffff) > LKCUDA_NLENSLOT) return fail(e, LKCUDA_ERR_ARG, "partial op %d: bad length slot", i);
     }
     /* A vector may be the destination of several ops of one list: under the reference's default LM_PER_NODE buffer mode a node's single
        vector is re-oriented on demand (phylonode.cpp:22-39, phylokernel.h:127-143), so a later op may overwrite what an earlier op of

@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(256) prep_frag_kernel(DevView v, const DevChil
         __syncthreads();
         for (int idx = threadIdx.x; idx < MM_S * MM_S; idx += blockDim.x) {
             int j = idx % MM_S;
-            sh_m[idx] = evec[idx] * exp(eval[j] * (v.blk_rate[k] * ch.len));
+            sh_m[idx] = evec[idx] * exp(eval[j] * (v.blk_rate[k] * child_len(v, ch)));
         }
         __syncthreads();
         for (int idx = threadIdx.x; idx < MM_FRAG_DOUBLES; idx += blockDim.x) {
@@ -410,8 +410,8 @@ int launch_traverse_mma(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops
         t.src1_lh = n.src1 >= 0 ? e->v.arena + (size_t)n.src1 * v.vec_stride : NULL;
         t.pad[0] = t.pad[1] = 0;
         DevChild &a = e->h_child[slot][2 * j], &b = e->h_child[slot][2 * j + 1];
-        a.id = n.src0; a.pad = 0; a.len = n.len0;
-        b.id = n.src1; b.pad = 0; b.len = n.len1;
+        a.id = n.src0; a.pad = n.ref0; a.len = n.len0;
+        b.id = n.src1; b.pad = n.ref1; b.len = n.len1;
         int ntip = (LKCUDA_IS_TIP(a.id) ? 1 : 0) + (LKCUDA_IS_TIP(b.id) ? 1 : 0);
         bytes += op_bytes(v, ntip, 2 - ntip);
         e->kind_flops[KIND_PARTIAL] += op_flops(v, ntip, 2 - ntip);

@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(256) prep_fragk_kernel(DevView v, const DevChi
     double *out = v.tables + (long long)c * v.table_slot + (long long)k * Sh::FRAG_DOUBLES;
     double *tab = v.tables + (long long)c * v.table_slot + (long long)K * Sh::FRAG_DOUBLES + (long long)k * (v.SU + 1) * Sh::ROW;
     const double *evec = v.evec + (long long)v.blk_eigen[k] * S * S, *eval = v.eval + v.blk_eigen[k] * S;
-    const double rl = v.blk_rate[k] * ch.len;
+    const double rl = v.blk_rate[k] * child_len(v, ch);
     for (int idx = threadIdx.x; idx < S * S; idx += blockDim.x) sh_m[idx] = evec[idx] * exp(eval[idx % S] * rl);
     __syncthreads();
     for (int idx = threadIdx.x; idx < Sh::FRAG_DOUBLES; idx += blockDim.x) {
@@ -440,8 +440,8 @@ static int launch_mmak(lkcuda_engine *e, const lkcuda_partial_op *ops, int nops)
         t.src1_lh = n.src1 >= 0 ? e->v.arena + (size_t)n.src1 * v.vec_stride : NULL;
         t.pad[0] = t.pad[1] = 0;
         DevChild &a = e->h_child[slot][2 * j], &b = e->h_child[slot][2 * j + 1];
-        a.id = n.src0; a.pad = 0; a.len = n.len0;
-        b.id = n.src1; b.pad = 0; b.len = n.len1;
+        a.id = n.src0; a.pad = n.ref0; a.len = n.len0;
+        b.id = n.src1; b.pad = n.ref1; b.len = n.len1;
         int ntip = (LKCUDA_IS_TIP(a.id) ? 1 : 0) + (LKCUDA_IS_TIP(b.id) ? 1 : 0);
         bytes += op_bytes(v, ntip, 2 - ntip);
         e->kind_flops[KIND_PARTIAL] += op_flops(v, ntip, 2 - ntip);

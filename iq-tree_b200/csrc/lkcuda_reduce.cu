@@ -525,8 +525,9 @@ __global__ void __launch_bounds__(RED_THREADS, 2) derv_b16_kernel(DevView v, B16
 }
 
 /* lnL from theta_all (computeLikelihoodFromBufferEigenSIMD, phylokernel.h:1023-1192), B = 16: the same stream with one dot product */
-__global__ void __launch_bounds__(RED_THREADS, 2) frombuf_b16_kernel(DevView v, B16Tab tab, double len) {
+__global__ void __launch_bounds__(RED_THREADS, 2) frombuf_b16_kernel(DevView v, B16Tab tab, double len, const double *len_slot) {
     __shared__ double sred[4 * 32];
+    if (len_slot) len = __ldcg(len_slot);
     const B16Lane m = b16_lane(v);
     long long t = m.t0;
     d4 n[4];
@@ -563,6 +564,15 @@ struct NewtonCtl {
     double optx, last_x;
     unsigned int gen;
 };
+
+/* a finished run leaves the length optimizeOneBranch would put into the branch (optx; the caller applies the rare "diverged to the upper
+   bound" rule, phylotree.cpp:2172-2180, after it fetched the slots) in its device length slot, with {optx, d2l, evaluations, status} beside it */
+__device__ __forceinline__ void newton_leave_length(const DevView &v, int len_slot, const NewtonCtl &c) {
+    if (len_slot < 0) return;
+    v.lens[len_slot] = c.optx;
+    double *info = v.lens + LKCUDA_NLENSLOT + 4 * len_slot;
+    info[0] = c.optx; info[1] = c.d2l; info[2] = (double)c.nev; info[3] = (double)c.done;
+}
 
 __device__ __forceinline__ void newton_advance(NewtonCtl &c, double x1, double x2, double xacc, int maxNRStep) {
     /* (f, df) = -(df, ddf) at c.rts have just been evaluated; mirrors optimization.cpp:396-463 */
@@ -601,12 +611,13 @@ __device__ __forceinline__ void theta_derv_b16_stream(const DevView &v, const B1
 /* BUILD 0: theta_all is there; 1 / 2: the first step builds it from the branch's two ends (dad a tip / an internal vector) while it
    forms the first df/ddf (the pass of theta_derv_b16_kernel) - every lane later re-reads exactly the theta rows it wrote itself */
 template <int BUILD>
-__global__ void __launch_bounds__(RED_THREADS, 2) newton_b16_kernel(DevView v, B16Tab tab, NewtonCtl *ctl, int dad, int node, double x1, double xguess, double x2, double xacc, int maxNRStep) {
+__global__ void __launch_bounds__(RED_THREADS, 2) newton_b16_kernel(DevView v, B16Tab tab, NewtonCtl *ctl, int dad, int node, double x1, double xguess, double x2, double xacc, int maxNRStep,
+                  int xguess_slot, int len_slot) {
     __shared__ __align__(32) double val0[16], val1[16], val2[16];
     __shared__ __align__(32) double tipT[BUILD == 1 ? 32 * B16_TIPROW : 4];
     __shared__ double sred[6 * 32];
     __shared__ double sh_x; __shared__ int sh_done;
-    double x = xguess;
+    double x = xguess_slot >= 0 ? __ldcg(v.lens + xguess_slot) : xguess;       /* a length an earlier launch left on the device */
     if (x < x1) x = x1;
     if (x > x2) x = x2;
     for (unsigned int it = 0;; it++) {
@@ -649,6 +660,7 @@ __global__ void __launch_bounds__(RED_THREADS, 2) newton_b16_kernel(DevView v, B
             if (c.done) {
                 double r[LKCUDA_NRESULT] = {c.optx, c.d2l, (double)c.nev, c.last_x, (double)c.done, 0.0, 0.0, 0.0};
                 post_result(v, r, err);
+                newton_leave_length(v, len_slot, c);
             }
             ctl->x = c.x; ctl->xl = c.xl; ctl->xh = c.xh; ctl->rts = c.rts; ctl->dx = c.dx; ctl->d2l = c.d2l;
             ctl->j = c.j; ctl->nev = c.nev; ctl->phase = c.phase; ctl->done = c.done; ctl->optx = c.optx; ctl->last_x = c.last_x;
@@ -786,7 +798,7 @@ __global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) derv_kernel(De
    reference's state machine (newton_advance), the result when the loop ends, and the hand-over of the next length to the other blocks
    (the same statements as in newton_b16_kernel) */
 __device__ __noinline__ void newton_elected(const DevView &v, NewtonCtl *ctl, unsigned int it, double x, double df, double ddf,
-                                            double x1, double x2, double xacc, int maxNRStep) {
+                                            double x1, double x2, double xacc, int maxNRStep, int len_slot) {
     unsigned int err = 0;
     if (v.peer_world > 1) {
         double r[LKCUDA_NRESULT] = {0.0, df, ddf, 0.0, 0.0, 0.0, 0.0, 0.0};
@@ -805,6 +817,7 @@ __device__ __noinline__ void newton_elected(const DevView &v, NewtonCtl *ctl, un
     if (c.done) {
         double r[LKCUDA_NRESULT] = {c.optx, c.d2l, (double)c.nev, c.last_x, (double)c.done, 0.0, 0.0, 0.0};
         post_result(v, r, err);
+        newton_leave_length(v, len_slot, c);
     }
     ctl->x = c.x; ctl->xl = c.xl; ctl->xh = c.xh; ctl->rts = c.rts; ctl->dx = c.dx; ctl->d2l = c.d2l;
     ctl->j = c.j; ctl->nev = c.nev; ctl->phase = c.phase; ctl->done = c.done; ctl->optx = c.optx; ctl->last_x = c.last_x;
@@ -816,17 +829,17 @@ __device__ __noinline__ void newton_elected(const DevView &v, NewtonCtl *ctl, un
    summation order of derv_kernel per evaluation (bit-identical df / ddf), theta_all built beforehand by theta_kernel */
 template <bool VEC>
 __global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) newton_generic_kernel(DevView v, NewtonCtl *ctl, double x1, double xguess, double x2,
-                                                                                       double xacc, int maxNRStep, int gshift) {
+                                                                                       double xacc, int maxNRStep, int gshift, int xguess_slot, int len_slot) {
     extern __shared__ __align__(32) double sh[];
     __shared__ double sred[5 * 32];
     __shared__ double sh_x; __shared__ int sh_done;
     const int Bp = (v.B + 3) & ~3;
-    double x = xguess;
+    double x = xguess_slot >= 0 ? __ldcg(v.lens + xguess_slot) : xguess;
     if (x < x1) x = x1;
     if (x > x2) x = x2;
     for (unsigned int it = 0;; it++) {
         DervOut o;
-        if (derv_pass<VEC>(v, x, gshift, sh, sh + Bp, sh + 2 * Bp, sred, &o)) newton_elected(v, ctl, it, x, o.df, o.ddf, x1, x2, xacc, maxNRStep);
+        if (derv_pass<VEC>(v, x, gshift, sh, sh + Bp, sh + 2 * Bp, sred, &o)) newton_elected(v, ctl, it, x, o.df, o.ddf, x1, x2, xacc, maxNRStep, len_slot);
         if (threadIdx.x == 0) {
             unsigned int g;
             do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(g) : "l"(&ctl->gen) : "memory"); } while (g < it + 1);
@@ -841,9 +854,10 @@ __global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) newton_generic
 }
 
 template <bool VEC>
-__global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) frombuf_kernel(DevView v, double len, int gshift) {
+__global__ void __launch_bounds__(RED_THREADS, RED_BLOCKS_PER_SM) frombuf_kernel(DevView v, double len, int gshift, const double *len_slot) {
     extern __shared__ __align__(32) double sh[];
     __shared__ double sred[4 * 32];
+    if (len_slot) len = __ldcg(len_slot);
     build_val(v, len, sh, NULL, NULL);
     __syncthreads();
     const int G = 1 << gshift, g = threadIdx.x & (G - 1);
@@ -1188,9 +1202,9 @@ int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result) {
     size_t sm = (size_t)((v.B + 3) & ~3) * 8;
     next_result(e);
     launch_begin(e, KIND_FROMBUF);
-    if (gs.vec && v.S == 4 && v.K == 4) frombuf_b16_kernel<<<b16_grid(e, v.NP), RED_THREADS, 0, e->stream>>>(e->v, e->b16tab, len);
-    else if (gs.vec) frombuf_kernel<true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
-    else frombuf_kernel<false><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift);
+    if (gs.vec && v.S == 4 && v.K == 4) frombuf_b16_kernel<<<b16_grid(e, v.NP), RED_THREADS, 0, e->stream>>>(e->v, e->b16tab, len, NULL);
+    else if (gs.vec) frombuf_kernel<true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift, NULL);
+    else frombuf_kernel<false><<<grid, RED_THREADS, sm, e->stream>>>(e->v, len, gs.gshift, NULL);
     int rc = launch_end(e, KIND_FROMBUF, (uint64_t)v.NP * ((uint64_t)v.B * 8 + 24), "frombuf_kernel");
     if (rc) return rc;
     if (v.U > 0 && v.P > 0) {
@@ -1206,7 +1220,8 @@ int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result) {
    v1: the step sequence is driven from the host, one df/ddf launch + one 64-byte read-back per step. */
 /* the persistent launch; build: 0 = theta_all is ready, 1 / 2 = build it from (dad, node) in the first step.  Returns 1 when the shape has
    no persistent kernel (the caller falls back to host-driven steps), 0 on success, < 0 = -(error code) */
-static int newton_persistent(lkcuda_engine *e, int build, int32_t dad, int32_t node, double x1, double xguess, double x2, double xacc, int32_t maxNRStep, double *out) {
+static int newton_persistent(lkcuda_engine *e, int build, int32_t dad, int32_t node, double x1, double xguess, double x2, double xacc, int32_t maxNRStep, double *out,
+                             int32_t xguess_slot = -1, int32_t len_slot = -1, bool async = false) {
     const DevView &v = e->v;
     GroupShape gs = group_shape(v);
     static const bool host_loop = getenv("LKCUDA_HOST_NEWTON") && atoi(getenv("LKCUDA_HOST_NEWTON")) != 0;      /* test knob */
@@ -1230,13 +1245,14 @@ static int newton_persistent(lkcuda_engine *e, int build, int32_t dad, int32_t n
         launch_begin(e, KIND_NEWTON);
         lkc::DevView vv = e->v;
         NewtonCtl *ctl = (NewtonCtl *)e->d_newton_ctl;
-        int imax = maxNRStep, igs = gs.gshift;
-        void *args[] = {&vv, &ctl, &x1, &xguess, &x2, &xacc, &imax, &igs};
+        int imax = maxNRStep, igs = gs.gshift, ixs = xguess_slot, ils = len_slot;
+        void *args[] = {&vv, &ctl, &x1, &xguess, &x2, &xacc, &imax, &igs, &ixs, &ils};
         cudaError_t ce = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(RED_THREADS), args, sm, e->stream);
         if (ce != cudaSuccess) return -cuda_fail(e, ce, "newton_generic_kernel");
         double r[LKCUDA_NRESULT];
         int rcn = launch_end(e, KIND_NEWTON, 0, "newton_generic_kernel");
         if (rcn) return -rcn;
+        if (async) return 0;
         rcn = lkcuda_wait_result(e, r);
         if (rcn) return -rcn;
         const int nev = (int)r[2], status = (int)r[4];
@@ -1265,15 +1281,16 @@ static int newton_persistent(lkcuda_engine *e, int build, int32_t dad, int32_t n
     launch_begin(e, KIND_NEWTON);
     lkc::DevView vv = e->v;
     NewtonCtl *ctl = (NewtonCtl *)e->d_newton_ctl;
-    int idad = dad, inode = node, imax = maxNRStep;
+    int idad = dad, inode = node, imax = maxNRStep, ixs = xguess_slot, ils = len_slot;
     lkc::B16Tab tab = e->b16tab;
-    void *args[] = {&vv, &tab, &ctl, &idad, &inode, &x1, &xguess, &x2, &xacc, &imax};
+    void *args[] = {&vv, &tab, &ctl, &idad, &inode, &x1, &xguess, &x2, &xacc, &imax, &ixs, &ils};
     const void *fn = build == 0 ? (const void *)newton_b16_kernel<0> : (build == 1 ? (const void *)newton_b16_kernel<1> : (const void *)newton_b16_kernel<2>);
     cudaError_t ce = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(RED_THREADS), args, 0, e->stream);
     if (ce != cudaSuccess) return -cuda_fail(e, ce, "newton_b16_kernel");
     double r[LKCUDA_NRESULT];
     int rcn = launch_end(e, KIND_NEWTON, 0, "newton_b16_kernel");
     if (rcn) return -rcn;
+    if (async) return 0;
     rcn = lkcuda_wait_result(e, r);
     if (rcn) return -rcn;
     const int nev = (int)r[2], status = (int)r[4];
@@ -1348,6 +1365,80 @@ int lkcuda_newton_branch(lkcuda_engine *e, double x1, double xguess, double x2, 
     return fail(e, LKCUDA_ERR_STATE, "Maximum number of iterations exceeded in minimizeNewton");
 #undef FUNC_DERV
 #undef NR_RETURN
+}
+
+/* ---- device length slots (lkcuda.h): a whole NNI evaluation queued without a host wait ---- */
+int lkcuda_theta_newton_async(lkcuda_engine *e, int32_t dad, int32_t node, double x1, double xguess, int32_t xguess_slot, double x2,
+                              double xacc, int32_t maxNRStep, int32_t len_slot) {
+    LK_ENTER(e);
+    if (node < 0 || node >= e->cfg.nvec || !valid_end(e, dad) || dad == node) return fail(e, LKCUDA_ERR_ARG, "lkcuda_theta_newton_async: bad vector / taxon id");
+    if (len_slot < 0 || len_slot >= LKCUDA_NLENSLOT || xguess_slot >= LKCUDA_NLENSLOT) return fail(e, LKCUDA_ERR_ARG, "lkcuda_theta_newton_async: bad length slot");
+    if (e->v.peer_world > 1) return fail(e, LKCUDA_ERR_STATE, "lkcuda_theta_newton_async: not with peers attached (the exchange counts evaluations on the host)");
+    int rc = check_ready(e, "lkcuda_theta_newton_async");
+    if (rc) return rc;
+    rc = states_barrier(e);
+    if (rc) return rc;
+    const DevView &v = e->v;
+    GroupShape gs = group_shape(v);
+    const bool b16 = gs.vec && v.S == 4 && v.K == 4 && v.SU < 32;
+    int pr;
+    if (b16) pr = newton_persistent(e, LKCUDA_IS_TIP(dad) ? 1 : 2, dad, node, x1, xguess, x2, xacc, maxNRStep, NULL, xguess_slot, len_slot, true);
+    else {
+        rc = lkcuda_theta_build(e, dad, node);
+        if (rc) return rc;
+        pr = newton_persistent(e, 0, 0, 0, x1, xguess, x2, xacc, maxNRStep, NULL, xguess_slot, len_slot, true);
+    }
+    if (pr > 0) return fail(e, LKCUDA_ERR_STATE, "lkcuda_theta_newton_async: this shape has no persistent Newton kernel");
+    if (pr < 0) return -pr;
+    e->theta_ready = true; e->theta_dad = dad; e->theta_node = node;
+    return LKCUDA_OK;
+}
+
+/* frombuf kernels take the length by value; a one-thread kernel cannot hand it over, so the B = 16 kernel and the generic one read the
+   slot themselves when given one */
+int lkcuda_lnl_from_buffer_slot(lkcuda_engine *e, int32_t len_slot, double *result) {
+    LK_ENTER(e);
+    if (len_slot < 0 || len_slot >= LKCUDA_NLENSLOT) return fail(e, LKCUDA_ERR_ARG, "lkcuda_lnl_from_buffer_slot: bad length slot");
+    if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lnl_from_buffer_slot: theta_all not built");
+    if (IS_SITEMODEL(e)) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lnl_from_buffer_slot: not for site-specific models");
+    const DevView &v = e->v;
+    GroupShape gs = group_shape(v);
+    int grid = red_grid(e, v.NP, gs.G);
+    size_t sm = (size_t)((v.B + 3) & ~3) * 8;
+    next_result(e);
+    launch_begin(e, KIND_FROMBUF);
+    const double *lp = v.lens + len_slot;
+    if (gs.vec && v.S == 4 && v.K == 4) frombuf_b16_kernel<<<b16_grid(e, v.NP), RED_THREADS, 0, e->stream>>>(e->v, e->b16tab, 0.0, lp);
+    else if (gs.vec) frombuf_kernel<true><<<grid, RED_THREADS, sm, e->stream>>>(e->v, 0.0, gs.gshift, lp);
+    else frombuf_kernel<false><<<grid, RED_THREADS, sm, e->stream>>>(e->v, 0.0, gs.gshift, lp);
+    int rc = launch_end(e, KIND_FROMBUF, (uint64_t)v.NP * ((uint64_t)v.B * 8 + 24), "frombuf_kernel");
+    if (rc) return rc;
+    if (v.U > 0 && v.P > 0) {
+        launch_begin(e, KIND_MISC);
+        asc_adjust_kernel<<<(int)((v.P + 255) / 256 < 1184 ? (v.P + 255) / 256 : 1184), 256, 0, e->stream>>>(e->v);
+        rc = launch_end(e, KIND_MISC, 0, "asc_adjust_kernel");
+        if (rc) return rc;
+    }
+    return finish_result(e, result);
+}
+
+int lkcuda_len_slots_set(lkcuda_engine *e, int32_t first, int32_t n, const double *values) {
+    LK_ENTER(e);
+    if (first < 0 || n < 0 || first + n > LKCUDA_NLENSLOT || (n && !values)) return fail(e, LKCUDA_ERR_ARG, "lkcuda_len_slots_set: bad range");
+    if (n == 0) return LKCUDA_OK;
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));           /* h_lens may still be the source of an earlier copy */
+    memcpy(e->h_lens, values, sizeof(double) * n);
+    LK_CUDA(e, cudaMemcpyAsync(e->d_lens + first, e->h_lens, sizeof(double) * n, cudaMemcpyHostToDevice, e->stream));
+    return LKCUDA_OK;
+}
+
+int lkcuda_len_slots_fetch(lkcuda_engine *e, double *lens, double *info) {
+    LK_ENTER(e);
+    LK_CUDA(e, cudaMemcpyAsync(e->h_lens, e->d_lens, sizeof(double) * 5 * LKCUDA_NLENSLOT, cudaMemcpyDeviceToHost, e->stream));
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (lens) memcpy(lens, e->h_lens, sizeof(double) * LKCUDA_NLENSLOT);
+    if (info) memcpy(info, e->h_lens + LKCUDA_NLENSLOT, sizeof(double) * 4 * LKCUDA_NLENSLOT);
+    return upload_verdict(e);
 }
 
 /* the correction kernel on the engine's stream, the copy on a stream of its own: later kernels (the next branch's theta_all, df/ddf)

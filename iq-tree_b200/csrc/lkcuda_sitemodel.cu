@@ -76,8 +76,8 @@ __global__ void __launch_bounds__(SM_THREADS) sitemodel_traverse_kernel(DevView 
                 const double rate = v.blk_rate[c];
                 if (on) {
                     const double a = tip0 ? t0 : l0[c * ns + lane], b = tip1 ? t1 : l1[c * ns + lane];
-                    bl[lane] = exp(ev * (rate * c0.len)) * a;
-                    br[lane] = exp(ev * (rate * c1.len)) * b;
+                    bl[lane] = exp(ev * (rate * child_len(v, c0))) * a;
+                    br[lane] = exp(ev * (rate * child_len(v, c1))) * b;
                 }
                 __syncwarp();
                 double vl = 0.0, vr = 0.0;

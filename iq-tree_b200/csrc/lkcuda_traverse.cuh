@@ -59,7 +59,7 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
 
 #endif  /* __CUDACC__ */
 
-struct TravNode { int op; int32_t src0, slot0, src1, slot1, dst_slot; double len0, len1; };
+struct TravNode { int op; int32_t src0, slot0, src1, slot1, dst_slot; double len0, len1; int32_t ref0, ref1; /* 1 + length slot, or 0 */ };
 struct TravSchedule { std::vector<TravNode> nodes; int nslots; };
 
 /* implemented in lkcuda_partial.cu */

@@ -48,6 +48,10 @@ LKCUDA_SYMBOLS = {
     "lkcuda_set_pattern_weights": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
     "lkcuda_set_model": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_double_p, c_int32_p, c_double_p, c_double_p, c_double_p]),
     "lkcuda_partial_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, c_int32_p, C.c_int32]),
+    "lkcuda_theta_newton_async": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_int32, C.c_double, C.c_double, C.c_int32, C.c_int32]),
+    "lkcuda_lnl_from_buffer_slot": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),
+    "lkcuda_len_slots_set": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_double_p]),
+    "lkcuda_len_slots_fetch": (C.c_int, [C.c_void_p, c_double_p, c_double_p]),
     "lkcuda_partial_batch_lnl": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, c_int32_p, C.c_int32, C.c_int32, C.c_int32, C.c_double, c_double_p]),
     "lkcuda_partial_multi": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_int32_p, c_double_p]),
     "lkcuda_branch_lnl": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_double, c_double_p]),
@@ -128,6 +132,7 @@ LKTREE_SYMBOLS = {
     "lktree_wait_pattern_lh": (C.c_int, [C.c_void_p]),
     "lktree_compute_likelihood_branch": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, c_double_p]),
     "lktree_compute_likelihood_derv": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p, c_double_p]),
+    "lktree_nni_queued_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "lktree_bench_steps": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p]),
     "lktree_compute_likelihood_from_buffer": (C.c_int, [C.c_void_p, c_double_p]),
     "lktree_optimize_one_branch": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, c_double_p]),
@@ -397,6 +402,12 @@ class PhyloTree:
         df, ddf = C.c_double(), C.c_double()
         self._ck(self.lib.lktree_compute_likelihood_derv(self.h, node1, node2, int(reset_theta), C.byref(df), C.byref(ddf)))
         return df.value, ddf.value
+
+    def nniQueuedStats(self):
+        """(calls of getBestNNIForBran that ran queued through device length slots, calls redone step by step)"""
+        a, b = C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.lktree_nni_queued_stats(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def benchSteps(self, node1, node2, steps):
         """`steps` x { clearAllPartialLH; computeLikelihood; computeLikelihoodDerv(node1 - node2, theta rebuilt) } driven from C++"""

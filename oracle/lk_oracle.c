@@ -52,8 +52,15 @@ struct lkcuda_engine {
     float *boot; int32_t nboot; double *rell; double *w; int32_t ncol;
     /* site-specific models */
     int32_t *ptn_model; uint64_t *state_mask;
+    double lens[5 * LKCUDA_NLENSLOT];   /* length slots (lkcuda.h): the oracle executes "queued" work at once, so a slot is just a variable */
     char err[256];
 };
+
+/* a child's branch length: the value, or the slot named in op->reserved (LKCUDA_LEN_REFS) */
+static double op_len(const lkcuda_engine *e, const lkcuda_partial_op *op, int right) {
+    int ref = right ? (op->reserved >> 16) & 0xffff : op->reserved & 0xffff;
+    return ref ? e->lens[ref - 1] : (right ? op->len_right : op->len_left);
+}
 
 static char g_create_err[256];
 
@@ -256,8 +263,8 @@ static int partial_one(lkcuda_engine *e, const lkcuda_partial_op *op) {
     double *eleft = (double *)malloc(block * S * 8), *eright = (double *)malloc(block * S * 8);
     double *tab_l = NULL, *tab_r = NULL;
     double *tmp = (double *)malloc(S * 8);
-    build_echild(e, op->len_left, eleft);
-    build_echild(e, op->len_right, eright);
+    build_echild(e, op_len(e, op, 0), eleft);
+    build_echild(e, op_len(e, op, 1), eright);
     if (LKCUDA_IS_TIP(op->left)) { tab_l = (double *)malloc((SU + 1) * block * 8); build_leaf_table(e, eleft, tab_l); }
     if (LKCUDA_IS_TIP(op->right)) { tab_r = (double *)malloc((SU + 1) * block * 8); build_leaf_table(e, eright, tab_r); }
     double *dst = vec_lh(e, op->dst);
@@ -639,6 +646,35 @@ int lkcuda_theta_newton(lkcuda_engine *e, int32_t dad, int32_t node, double x1, 
     return rc ? rc : lkcuda_newton_branch(e, x1, xguess, x2, xacc, maxNRStep, out);
 }
 
+/* ---- device length slots, executed at once ---- */
+int lkcuda_theta_newton_async(lkcuda_engine *e, int32_t dad, int32_t node, double x1, double xguess, int32_t xguess_slot, double x2,
+                              double xacc, int32_t maxNRStep, int32_t len_slot) {
+    if (!e) return LKCUDA_ERR_ARG;
+    if (len_slot < 0 || len_slot >= LKCUDA_NLENSLOT || xguess_slot >= LKCUDA_NLENSLOT) return fail(e, LKCUDA_ERR_ARG, "lkcuda_theta_newton_async: bad length slot");
+    double out[4] = {0.0, 0.0, 0.0, 0.0};
+    int rc = lkcuda_theta_newton(e, dad, node, x1, xguess_slot >= 0 ? e->lens[xguess_slot] : xguess, x2, xacc, maxNRStep, out);
+    double *info = e->lens + LKCUDA_NLENSLOT + 4 * len_slot;
+    info[0] = out[0]; info[1] = out[1]; info[2] = out[2]; info[3] = rc ? 2.0 : 1.0;
+    e->lens[len_slot] = out[0];
+    return LKCUDA_OK;           /* a failed run is reported through the slot's status, as on the device */
+}
+int lkcuda_lnl_from_buffer_slot(lkcuda_engine *e, int32_t len_slot, double *result) {
+    if (!e) return LKCUDA_ERR_ARG;
+    if (len_slot < 0 || len_slot >= LKCUDA_NLENSLOT) return fail(e, LKCUDA_ERR_ARG, "lkcuda_lnl_from_buffer_slot: bad length slot");
+    return lkcuda_lnl_from_buffer(e, e->lens[len_slot], result);
+}
+int lkcuda_len_slots_set(lkcuda_engine *e, int32_t first, int32_t n, const double *values) {
+    if (!e || first < 0 || n < 0 || first + n > LKCUDA_NLENSLOT || (n && !values)) return LKCUDA_ERR_ARG;
+    memcpy(e->lens + first, values, sizeof(double) * (size_t)n);
+    return LKCUDA_OK;
+}
+int lkcuda_len_slots_fetch(lkcuda_engine *e, double *lens, double *info) {
+    if (!e) return LKCUDA_ERR_ARG;
+    if (lens) memcpy(lens, e->lens, sizeof(double) * LKCUDA_NLENSLOT);
+    if (info) memcpy(info, e->lens + LKCUDA_NLENSLOT, sizeof(double) * 4 * LKCUDA_NLENSLOT);
+    return LKCUDA_OK;
+}
+
 int lkcuda_read_result(lkcuda_engine *e, double *result) {
     if (!e || !result) return LKCUDA_ERR_ARG;
     memcpy(result, e->result, sizeof(e->result_own));
@@ -920,7 +956,7 @@ static int sm_partial_one(lkcuda_engine *e, const lkcuda_partial_op *op) {
         if (st_l) sm_tip(e, ptn, st_l[ptn], tipl);
         if (st_r) sm_tip(e, ptn, st_r[ptn], tipr);
         for (size_t c = 0; c < K; c++) {
-            const double len_left = e->blk_rate[c] * op->len_left, len_right = e->blk_rate[c] * op->len_right;
+            const double len_left = e->blk_rate[c] * op_len(e, op, 0), len_right = e->blk_rate[c] * op_len(e, op, 1);
             const double *pl = st_l ? tipl : lh_l + ptn * block + c * S, *pr = st_r ? tipr : lh_r + ptn * block + c * S;
             for (size_t i = 0; i < S; i++) {
                 expleft[i] = exp(eval[i] * len_left) * pl[i];

@@ -52,6 +52,20 @@ def test_oracle_nni_matches_reference(name, oracle_lib):
     g = gu.Golden(case)
     t = gu.build_tree(g, oracle_lib)
     run_nni_checks(t, g, z, m, max_branches=24)
+    assert t.nniQueuedStats() == (0, 0)
+    t.close()
+
+
+@pytest.mark.parametrize("name", [n for n in NNI_FILES if n.startswith("dna_example_gtr_i_g4") or n.startswith("aa_lg_g4")])
+def test_oracle_nni_queued_form(name, oracle_lib):
+    """the host logic of the queued form (device length slots: lengths referenced by later ops, Newton starts and the score) on the scalar
+    engine, which executes queued work at once"""
+    z, m, case = _load(name)
+    g = gu.Golden(case)
+    t = gu.build_tree(g, oracle_lib, device_newton=True)
+    run_nni_checks(t, g, z, m, max_branches=16)
+    calls, fallbacks = t.nniQueuedStats()
+    assert calls > 0 and fallbacks <= calls // 4
     t.close()
 
 
@@ -64,4 +78,9 @@ def test_cuda_nni_matches_reference(name, nshard, device_newton, cuda_lib):
     g = gu.Golden(case)
     t = gu.build_tree(g, cuda_lib, devices=[0] * nshard, device_newton=device_newton)
     run_nni_checks(t, g, z, m, max_branches=None if nshard == 1 else 12)
+    calls, fallbacks = t.nniQueuedStats()
+    if nshard == 1 and device_newton:
+        assert calls > 0 and fallbacks <= calls // 4, (calls, fallbacks)      # the queued form is what ran
+    else:
+        assert calls == 0
     t.close()
