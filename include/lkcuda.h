@@ -195,6 +195,23 @@ int lkcuda_theta_build(lkcuda_engine *e, int32_t dad, int32_t node);
 int lkcuda_theta_derv(lkcuda_engine *e, int32_t dad, int32_t node, double len, double *result);
 /* df, ddf at branch length len from theta_all (phylokernel.h:521-532, 599-725) */
 int lkcuda_derv(lkcuda_engine *e, double len, double *result);
+/* lkcuda_derv for callers that must not allocate (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+   cudaMalloc).  NO COUNTERPART IN THE REFERENCE; the arithmetic is lkcuda_derv's
+   (phylokernel.h:606-651) without +ASC and for one eigen system.  It needs no engine and calls no cudaMalloc / cudaFree / allocating
+   library routine: the caller passes every input and the output as DEVICE pointers - theta_all[nptn][ncat][nstates], ptn_freq[nptn],
+   ptn_invar[nptn], df_ddf[2] = {df, ddf} - and the model as small HOST arrays - eval[nstates], cat_rate[ncat], cat_prop[ncat] (copied
+   into the kernel's parameters).  The cross-block scratch is a static device array of LKCUDA_NOALLOC_SCRATCH_BYTES that every GPU
+   loading the library holds until the process exits; hence the limits: nptn <= LKCUDA_NOALLOC_MAX_PATTERNS, nstates <= 64,
+   ncat <= 64, nstates * ncat <= LKCUDA_NOALLOC_MAX_BLOCK - anything larger is refused with LKCUDA_ERR_ARG (text:
+   lkcuda_last_error(NULL)).  Asynchronous on `cuda_stream` (NULL = the default stream): df_ddf is valid once the stream has reached the
+   call.  All calls on a device share the one scratch array, so calls that OVERLAP on the GPU (different streams or host threads without
+   an ordering between them) race; calls ordered on one stream do not.  Same inputs give the same bits on every call. */
+#define LKCUDA_NOALLOC_MAX_PATTERNS (1 << 21)
+#define LKCUDA_NOALLOC_MAX_BLOCK 256
+#define LKCUDA_NOALLOC_SCRATCH_BYTES (65536 + 256)
+int lkcuda_derv_noalloc(int32_t device, void *cuda_stream, const double *theta_all, const double *ptn_freq, const double *ptn_invar,
+                        int64_t nptn, int32_t nstates, int32_t ncat, const double *eval, const double *cat_rate, const double *cat_prop,
+                        double len, double *df_ddf);
 /* PhyloTree::computeLikelihoodFromBuffer (phylotreesse.cpp:349; phylokernel.h:1023-1192) */
 int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result);
 /* Optimization::minimizeNewton (optimization.cpp:388-465) driven on the device over theta_all:

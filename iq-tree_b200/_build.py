@@ -30,7 +30,7 @@ REF_HARNESS = os.path.join(ORACLE_DIR, "_ref", "ref_harness")
 REF_HARNESS_CUDA = os.path.join(ORACLE_DIR, "_ref", "ref_harness_cuda")
 REFERENCE = "/root/reference"
 
-CUDA_SOURCES = ["lkcuda_engine.cu", "lkcuda_partial.cu", "lkcuda_partial_mma.cu", "lkcuda_partial_mmak.cu", "lkcuda_reduce.cu", "lkcuda_aux.cu", "lkcuda_sitemodel.cu", "lkcuda_pars.cu"]
+CUDA_SOURCES = ["lkcuda_engine.cu", "lkcuda_partial.cu", "lkcuda_partial_mma.cu", "lkcuda_partial_mmak.cu", "lkcuda_reduce.cu", "lkcuda_aux.cu", "lkcuda_sitemodel.cu", "lkcuda_pars.cu", "lkcuda_noalloc.cu"]
 HOST_SOURCES = ["lk_phylotree.cpp", "lk_parsimony.cpp", "lk_rate_em.cpp", "lk_capi.cpp"]
 ORACLE_SOURCES = ["lk_oracle.c", "lkpars_oracle.c"]
 HEADERS = [os.path.join(CSRC, "lkcuda_common.cuh"), os.path.join(CSRC, "lkcuda_traverse.cuh"),

@@ -59,6 +59,8 @@ LKCUDA_SYMBOLS = {
     "lkcuda_theta_build": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
     "lkcuda_theta_derv": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_double, c_double_p]),
     "lkcuda_derv": (C.c_int, [C.c_void_p, C.c_double, c_double_p]),
+    "lkcuda_derv_noalloc": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, c_double_p, c_double_p, c_double_p,
+                            C.c_double, C.c_void_p]),
     "lkcuda_lnl_from_buffer": (C.c_int, [C.c_void_p, C.c_double, c_double_p]),
     "lkcuda_newton_branch": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32, c_double_p]),
     "lkcuda_theta_newton": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32, c_double_p]),

@@ -582,6 +582,38 @@ int lkcuda_derv(lkcuda_engine *e, double len, double *result) {
     return LKCUDA_OK;
 }
 
+/* scalar statement of lkcuda_derv_noalloc (no counterpart in the reference; the loop of phylotreesse.cpp:1106-1132 on the caller's
+   arrays, which are HOST arrays here); same limits and refusals as the CUDA entry point */
+int lkcuda_derv_noalloc(int32_t device, void *cuda_stream, const double *theta_all, const double *ptn_freq, const double *ptn_invar,
+                        int64_t nptn, int32_t nstates, int32_t ncat, const double *eval, const double *cat_rate, const double *cat_prop,
+                        double len, double *df_ddf) {
+    (void)device; (void)cuda_stream;
+    if (!theta_all || !ptn_freq || !ptn_invar || !eval || !cat_rate || !cat_prop || !df_ddf) return fail(NULL, LKCUDA_ERR_ARG, "lkcuda_derv_noalloc: null argument");
+    if (nptn < 0 || nstates <= 0 || ncat <= 0) return fail(NULL, LKCUDA_ERR_ARG, "lkcuda_derv_noalloc: invalid shape");
+    if (nptn > LKCUDA_NOALLOC_MAX_PATTERNS) return fail(NULL, LKCUDA_ERR_ARG, "lkcuda_derv_noalloc: patterns exceed LKCUDA_NOALLOC_MAX_PATTERNS");
+    if (nstates > 64 || ncat > 64 || nstates * ncat > LKCUDA_NOALLOC_MAX_BLOCK) return fail(NULL, LKCUDA_ERR_ARG, "lkcuda_derv_noalloc: states x categories exceed the limits");
+    double val0[LKCUDA_NOALLOC_MAX_BLOCK], val1[LKCUDA_NOALLOC_MAX_BLOCK], val2[LKCUDA_NOALLOC_MAX_BLOCK];
+    size_t block = (size_t)nstates * ncat;
+    for (int c = 0; c < ncat; c++)
+        for (int i = 0; i < nstates; i++) {
+            double cof = eval[i] * cat_rate[c], x = exp(cof * len) * cat_prop[c];
+            val0[c * nstates + i] = x; val1[c * nstates + i] = cof * x; val2[c * nstates + i] = cof * cof * x;
+        }
+    double my_df = 0.0, my_ddf = 0.0;
+    for (int64_t ptn = 0; ptn < nptn; ptn++) {
+        double lh_ptn = ptn_invar[ptn], df_ptn = 0.0, ddf_ptn = 0.0;
+        const double *theta = theta_all + (size_t)ptn * block;
+        for (size_t i = 0; i < block; i++) { lh_ptn += val0[i] * theta[i]; df_ptn += val1[i] * theta[i]; ddf_ptn += val2[i] * theta[i]; }
+        lh_ptn = fabs(lh_ptn);
+        double df_frac = df_ptn / lh_ptn, ddf_frac = ddf_ptn / lh_ptn, tmp1 = df_frac * ptn_freq[ptn], tmp2 = ddf_frac * ptn_freq[ptn];
+        my_df += tmp1;
+        my_ddf += tmp2 - tmp1 * df_frac;
+    }
+    if (isnan(my_df) || isinf(my_df)) { my_df = 0.0; my_ddf = 0.0; }
+    df_ddf[0] = my_df; df_ddf[1] = my_ddf;
+    return LKCUDA_OK;
+}
+
 int lkcuda_lnl_from_buffer(lkcuda_engine *e, double len, double *result) {
     if (!e) return LKCUDA_ERR_ARG;
     if (!e->theta_ready) return fail(e, LKCUDA_ERR_STATE, "lkcuda_lnl_from_buffer: theta_all not built");
