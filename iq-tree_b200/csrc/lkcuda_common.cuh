@@ -141,6 +141,7 @@ struct lkcuda_engine {
     double *d_inv_frags;                    /* fragment-ordered inverse eigenvectors of the protein MMA kernel */
     size_t mma_smem_set; bool trav_disable_mma;   /* LKCUDA_NO_MMA=1: protein falls back to the generic kernel (test knob) */
     int trav_maxslots;                      /* LKCUDA_TRV_MAXSLOTS: cap on shared-memory slots (-1 = what fits) */
+    std::vector<char> trav_mark;            /* launch_traverse: vectors written by the list being scheduled (all zero between calls) */
     /* pipelined tip-state upload (lkcuda_set_tip_states_async): chunks of patterns go up on `cstream`; after each chunk the copy
        engine bumps *d_upload_flag, which the DNA traversal kernel's producer warp polls before it stages a tile's tip states */
     enum { UPLOAD_MAX_CHUNKS = 64 };

@@ -123,10 +123,18 @@ __global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevCh
    keeping p[], off[], valid[] per unit - no unit more fits and the kernel gets 2 % slower; (b) 12 consumer warps x 152 registers with the
    producer as a fourth warpgroup that hands its registers over (setmaxnreg): 2.33 vs 2.40 ms per 1M-pattern traversal
    (profiles/r2_s21_traverse_setmaxnreg_variants.txt), but in 3 of 9 runs that build left the 32 patterns of ONE warp of ONE tile of a
-   partial traversal unwritten (found with LKCUDA_POISON=1, never seen with the single producer warp). */
+   partial traversal unwritten (found with LKCUDA_POISON=1) - the stage-release hole described at TRV_ARRIVE_DEP, which that build's timing
+   exposed; not re-measured since the fix. */
 #define TRV_MAX_STAGES 8
+/* units (pattern, category) per consumer thread.  Measured on one box, A/B (profiles/r2_s50_step_variants.txt): 5 units make the full-tree
+   traversal 3 % faster than 4 (2.56 vs 2.63 ms per lnL evaluation at 1M patterns) but a list whose internal children mostly come from
+   the arena - the path to the derivative's branch: one streamed child per node - 10 % slower (1.00 vs 0.90 ms); launch_traverse picks
+   per launch */
 #ifndef TRV_R
-#define TRV_R 4
+#define TRV_R 5             /* lists that read (almost) no child from the arena */
+#endif
+#ifndef TRV_R_ARENA
+#define TRV_R_ARENA 4       /* lists with arena-read children; also the instantiation that can carry the fused root branch */
 #endif
 #ifndef TRV_INV_REGS
 #define TRV_INV_REGS 0      /* 1: the inverse eigenvectors of the lane's category stay in registers for the whole launch */
@@ -141,12 +149,42 @@ __global__ void __launch_bounds__(256) prep_tables_kernel(DevView v, const DevCh
    child 0 tip states | child 1 tip states (spad bytes each: the tile's patterns of that taxon) */
 __host__ __device__ __forceinline__ int trv_stage_bytes(int cbs, int spad) { return 64 + 2 * cbs * 8 + 2 * spad; }
 
+/* one row of a 4x4 row-major matrix (a = (Mi0, Mi1), b = (Mi2, Mi3)) times L.  The order of the operations is spelled out - it is the one
+   nvcc's contraction gives `a.x*L.x + a.y*L.y + b.x*L.z + b.y*L.w` (first product fused, second rounded) - so that every form of the
+   products below (whole matrix per unit, column halves over all units, row by row over all units) gives the same bits */
+#define TRV_DOT(a, b, L) fma((b).y, (L).w, fma((b).x, (L).z, fma((a).x, (L).x, (a).y * (L).y)))
 /* dst = M * L for a 4x4 row-major matrix held as 8 double2 */
-#define TRV_MATVEC(dst, m, L)                                                   \
-    dst[0] = m[0].x * L.x + m[0].y * L.y + m[1].x * L.z + m[1].y * L.w;         \
-    dst[1] = m[2].x * L.x + m[2].y * L.y + m[3].x * L.z + m[3].y * L.w;         \
-    dst[2] = m[4].x * L.x + m[4].y * L.y + m[5].x * L.z + m[5].y * L.w;         \
-    dst[3] = m[6].x * L.x + m[6].y * L.y + m[7].x * L.z + m[7].y * L.w;
+#define TRV_MATVEC(dst, m, L)                   \
+    dst[0] = TRV_DOT(m[0], m[1], L);            \
+    dst[1] = TRV_DOT(m[2], m[3], L);            \
+    dst[2] = TRV_DOT(m[4], m[5], L);            \
+    dst[3] = TRV_DOT(m[6], m[7], L);
+/* TRV_FORM 1: the matrix of child 0 is applied in two column halves over all units of the thread (8 of its 16 entries live at a time),
+   the matrix of child 1 and the inverse eigenvectors row by row (4 entries live at a time); 0: one whole matrix per unit */
+#ifndef TRV_FORM
+#define TRV_FORM 0
+#endif
+/* How a consumer warp hands a ring stage back.  On sm_100a mbarrier.arrive does not wait for an earlier LDS of the same warp that is still
+   in flight, and ptxas adds no scoreboard wait: the producer's next bulk copy can replace the stage under the load.  Measured (round 2,
+   profiles/r2_s44..s46): with the descriptor words dst_lh / dst_sc loaded two instructions before the arrive, whole warps stored a node's
+   result through the descriptor of the node that got the stage next (8 patterns x R slices of NaN in the poisoned arena, a few per 1M x 98
+   nodes) as soon as the code in front of the arrive was LDS-heavy (TRV_FORM 1); the shipped form had the same instruction pair and was only
+   luckier.  1 (shipped): the barrier address depends on the words loaded last, so the arrive cannot issue before the stage reads are in
+   (shared loads of a warp complete in order); 2 / 3: membar.cta / fence.proxy.async in front of the arrive (also clean, 2-3 % slower);
+   0: nothing.  tools/sass_release_check.py (tests/test_sass_release.py) checks the built SASS for an LDS in flight at a consumer arrive. */
+#ifndef TRV_ARRIVE_DEP
+#define TRV_ARRIVE_DEP 1
+#endif
+#ifndef TRV_INV_FORM
+#define TRV_INV_FORM 0      /* 1: the inverse eigenvectors are applied row by row over all units */
+#endif
+/* columns (0,1) of M times (x,y) of L: starts the four sums of a unit; columns (2,3) times (z,w): finishes them */
+#define TRV_COLS_LO(t, c0, c1, c2, c3, a)                                       \
+    t[0] = fma((c0).x, (a).x, (c0).y * (a).y); t[1] = fma((c1).x, (a).x, (c1).y * (a).y); \
+    t[2] = fma((c2).x, (a).x, (c2).y * (a).y); t[3] = fma((c3).x, (a).x, (c3).y * (a).y);
+#define TRV_COLS_HI(t, c0, c1, c2, c3, b)                                       \
+    t[0] = fma((c0).y, (b).y, fma((c0).x, (b).x, t[0])); t[1] = fma((c1).y, (b).y, fma((c1).x, (b).x, t[1])); \
+    t[2] = fma((c2).y, (b).y, fma((c2).x, (b).x, t[2])); t[3] = fma((c3).y, (b).y, fma((c3).x, (b).x, t[3]));
 
 /* root branch fused into the tail of the traversal (lkcuda_partial_batch_lnl): the leaf end, its length and the table parameters */
 #define TRV_ROOT_ROW 18
@@ -169,12 +207,13 @@ __device__ __forceinline__ void st_s16_if(bool pred, int16_t *p, int val) {
     asm volatile("{\n.reg .pred q;\nsetp.ne.u32 q, %2, 0;\n@q st.global.u16 [%0], %1;\n}" :: "l"(p), "h"((short)val), "r"((unsigned)pred) : "memory");
 }
 
-template <bool FUSE>
+template <int R, bool FUSE>
 __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, const TravOp *__restrict__ ops, int nops, int upw, int nslots,
                                                                      int cbs, int spad, int stage_shift, int nfull, int ract_last,
                                                                      const unsigned int *upload_flag, unsigned int upload_base, long long upload_chunk_pat,
                                                                      TravRoot root) {
-    constexpr int R = TRV_R, CT = TRV_CTHREADS;
+    constexpr int CT = TRV_CTHREADS;
+    static_assert(R <= 6, "the last round is instantiated for 1..5 slices and R");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int K = v.K, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int stage_bytes = trv_stage_bytes(cbs, spad);
@@ -186,7 +225,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
     uint64_t *full = reinterpret_cast<uint64_t *>(sINV + K * S4_MPAD), *empty = full + TRV_MAX_STAGES;
     /* fused root-branch lnL (root.on; K = 4): weighted tip table of the root leaf [state][TRV_ROOT_ROW] | per-thread sums [4][CT] | [4][32] */
     double *rootB = reinterpret_cast<double *>(empty + TRV_MAX_STAGES), *racc = rootB + 32 * TRV_ROOT_ROW, *rred = racc + 4 * CT;
-    constexpr bool fuse_root = FUSE;
+    constexpr bool fuse_root = FUSE && R <= 4;       /* lane k of a pattern finishes slice k: at most K = 4 slices (launch_traverse) */
     for (int idx = tid; idx < K * 16; idx += TRV_THREADS) {
         int kk = idx >> 4, r = idx & 15;
         sINV[kk * S4_MPAD + r] = v.inv_evec[v.blk_eigen[kk] * 16 + r];
@@ -300,7 +339,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                 const uint8_t *rst = tip_states(v, root.tip);
 #pragma unroll
                 for (int r = 0; r < RA; r++) {
-                    root_st |= min((int)__ldcg(rst + p[r]), v.SU) << (8 * r);
+                    root_st |= min((int)__ldcg(rst + p[r]), v.SU) << (8 * (r & 3));
                     if (r == k) { root_p = p[r]; root_mine = valid[r]; }
                 }
                 if (root_mine) { root_inv = v.invar[root_p]; root_f = root_p < v.P ? v.freq[root_p] : 0.0; }
@@ -325,6 +364,49 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                 }
             } else {
                 const double2 *mp = reinterpret_cast<const double2 *>(blk0 + k * S4_MPAD);
+#if TRV_FORM == 1
+                if (slot0 >= 0) {
+                    const double2 *ps = sl_t + slot0 * (R * 2 * CT);
+                    const int *pc = ssc_t + slot0 * (R * CT);
+                    {
+                        const double2 c0 = mp[0], c1 = mp[2], c2 = mp[4], c3 = mp[6];
+#pragma unroll
+                        for (int r = 0; r < RA; r++) {
+                            const double2 a = ps[(r * 2) * CT];
+                            sc[r] = pc[r * CT];
+                            TRV_COLS_LO(t[r], c0, c1, c2, c3, a)
+                        }
+                    }
+                    {
+                        const double2 c0 = mp[1], c1 = mp[3], c2 = mp[5], c3 = mp[7];
+#pragma unroll
+                        for (int r = 0; r < RA; r++) {
+                            const double2 b = ps[(r * 2 + 1) * CT];
+                            TRV_COLS_HI(t[r], c0, c1, c2, c3, b)
+                        }
+                    }
+                } else {
+                    const double *g = op->src0_lh;
+                    const int16_t *gs = vec_sc(v, src0);
+                    {
+                        const double2 c0 = mp[0], c1 = mp[2], c2 = mp[4], c3 = mp[6];
+#pragma unroll
+                        for (int r = 0; r < RA; r++) {
+                            const double2 a = ld_coherent128(g + off[r]);
+                            sc[r] = gs[p[r]];
+                            TRV_COLS_LO(t[r], c0, c1, c2, c3, a)
+                        }
+                    }
+                    {
+                        const double2 c0 = mp[1], c1 = mp[3], c2 = mp[5], c3 = mp[7];
+#pragma unroll
+                        for (int r = 0; r < RA; r++) {
+                            const double2 b = ld_coherent128(g + off[r] + 2);
+                            TRV_COLS_HI(t[r], c0, c1, c2, c3, b)
+                        }
+                    }
+                }
+#else
                 const double2 m[8] = {mp[0], mp[1], mp[2], mp[3], mp[4], mp[5], mp[6], mp[7]};
                 if (slot0 >= 0) {
                     const double2 *ps = sl_t + slot0 * (R * 2 * CT);
@@ -346,6 +428,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                         TRV_MATVEC(t[r], m, L)
                     }
                 }
+#endif
             }
             /* ---- child 1: tip | previous node (registers) | slot | arena ---- */
             if (tip1) {
@@ -359,6 +442,47 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                 }
             } else {
                 const double2 *mp = reinterpret_cast<const double2 *>(blk1 + k * S4_MPAD);
+#if TRV_FORM == 1
+                if (slot1 == TRV_SLOT_PREV) {
+#pragma unroll
+                    for (int r = 0; r < RA; r++) sc[r] += pvsc[r];
+#pragma unroll
+                    for (int i4 = 0; i4 < 4; i4++) {
+                        const double2 ra = mp[2 * i4], rb = mp[2 * i4 + 1];
+#pragma unroll
+                        for (int r = 0; r < RA; r++) t[r][i4] *= TRV_DOT(ra, rb, pv[r]);
+                    }
+                } else if (slot1 >= 0) {    /* rare (a vector with two consumers in the list): the slot is re-read for every row */
+                    const double2 *ps = sl_t + slot1 * (R * 2 * CT);
+                    const int *pc = ssc_t + slot1 * (R * CT);
+#pragma unroll
+                    for (int r = 0; r < RA; r++) sc[r] += pc[r * CT];
+#pragma unroll
+                    for (int i4 = 0; i4 < 4; i4++) {
+                        const double2 ra = mp[2 * i4], rb = mp[2 * i4 + 1];
+#pragma unroll
+                        for (int r = 0; r < RA; r++) {
+                            const double2 a = ps[(r * 2) * CT], b = ps[(r * 2 + 1) * CT];
+                            d4 L; L.x = a.x; L.y = a.y; L.z = b.x; L.w = b.y;
+                            t[r][i4] *= TRV_DOT(ra, rb, L);
+                        }
+                    }
+                } else {
+                    const double *g = op->src1_lh;
+                    const int16_t *gs = vec_sc(v, src1);
+#pragma unroll
+                    for (int r = 0; r < RA; r++) sc[r] += gs[p[r]];
+#pragma unroll
+                    for (int i4 = 0; i4 < 4; i4++) {
+                        const double2 ra = mp[2 * i4], rb = mp[2 * i4 + 1];
+#pragma unroll
+                        for (int r = 0; r < RA; r++) {
+                            const d4 L = ld_coherent256(g + off[r]);
+                            t[r][i4] *= TRV_DOT(ra, rb, L);
+                        }
+                    }
+                }
+#else
                 const double2 m[8] = {mp[0], mp[1], mp[2], mp[3], mp[4], mp[5], mp[6], mp[7]};
                 double u[4];
                 if (slot1 == TRV_SLOT_PREV) {
@@ -390,18 +514,47 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                         t[r][0] *= u[0]; t[r][1] *= u[1]; t[r][2] *= u[2]; t[r][3] *= u[3];
                     }
                 }
+#endif
             }
             double *const dst_lh = op->dst_lh;
             int16_t *const dst_sc = op->dst_sc;
             /* everything this node needs from the stage is in registers now: hand the stage back to the producer */
+#if TRV_ARRIVE_DEP == 2
+            __threadfence_block();
+#elif TRV_ARRIVE_DEP == 3
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
             __syncwarp();
+#if TRV_ARRIVE_DEP == 1
+            /* the barrier's address depends on the two descriptor words loaded last (always + 0): the arrive cannot issue before they are in */
+            if (lane == 0) mbar_arrive(&empty[s] + (((unsigned long long)dst_lh | (unsigned long long)dst_sc) >> 63));
+#else
             if (lane == 0) mbar_arrive(&empty[s]);
+#endif
             /* ---- back to state space, scaling test, stores ---- */
+            const bool may_scale = !(tip0 && tip1);   /* tip-tip never scales (phylokernel.h:246-281) */
+            bool tiny = false;
+#if TRV_INV_FORM == 1
+#define TRV_INV_ROW(i4, comp) do {                                               \
+                const double2 ra = inv[2 * (i4)], rb = inv[2 * (i4) + 1];         \
+                _Pragma("unroll")                                                 \
+                for (int r = 0; r < RA; r++) {                                    \
+                    const d4 T = {t[r][0], t[r][1], t[r][2], t[r][3]};            \
+                    pv[r].comp = TRV_DOT(ra, rb, T);                              \
+                }                                                                 \
+            } while (0)
+            TRV_INV_ROW(0, x); TRV_INV_ROW(1, y); TRV_INV_ROW(2, z); TRV_INV_ROW(3, w);
+#undef TRV_INV_ROW
+#pragma unroll
+            for (int r = 0; r < RA; r++) {
+                const int mx = max(max(__double2hiint(pv[r].x) & 0x7fffffff, __double2hiint(pv[r].y) & 0x7fffffff),
+                                   max(__double2hiint(pv[r].z) & 0x7fffffff, __double2hiint(pv[r].w) & 0x7fffffff));
+                tiny |= mx < THR_HI;
+            }
+#else
 #if !TRV_INV_REGS
             const double2 iv[8] = {inv[0], inv[1], inv[2], inv[3], inv[4], inv[5], inv[6], inv[7]};
 #endif
-            const bool may_scale = !(tip0 && tip1);   /* tip-tip never scales (phylokernel.h:246-281) */
-            bool tiny = false;
 #pragma unroll
             for (int r = 0; r < RA; r++) {
                 const d4 T = {t[r][0], t[r][1], t[r][2], t[r][3]};
@@ -413,6 +566,7 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
                                    max(__double2hiint(w[2]) & 0x7fffffff, __double2hiint(w[3]) & 0x7fffffff));
                 tiny |= mx < THR_HI;
             }
+#endif
             if (may_scale && __any_sync(0xffffffffu, tiny)) {
                 /* rare path: some unit of this warp is below the threshold; agree per pattern (lane group) with ballots */
 #pragma unroll
@@ -484,6 +638,8 @@ __global__ void __launch_bounds__(TRV_THREADS, 1) traverse_s4_kernel(DevView v, 
             case 1: do_tile(std::integral_constant<int, 1>{}, p0); break;
             case 2: do_tile(std::integral_constant<int, (R >= 2 ? 2 : R)>{}, p0); break;
             case 3: do_tile(std::integral_constant<int, (R >= 3 ? 3 : R)>{}, p0); break;
+            case 4: do_tile(std::integral_constant<int, (R >= 4 ? 4 : R)>{}, p0); break;
+            case 5: do_tile(std::integral_constant<int, (R >= 5 ? 5 : R)>{}, p0); break;
             default: do_tile(std::integral_constant<int, R>{}, p0); break;
         }
     }
@@ -806,12 +962,26 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
     const DevView &v = e->v;
     /* child block of a ring stage: a padded matrix set or a tip lookup table, whichever is larger */
     const int cbs_mat = v.K * S4_MPAD, cbs_tab = TRV_TAB_DOUBLES(v.SU, v.K), cbs = cbs_mat > cbs_tab ? cbs_mat : cbs_tab;
-    const size_t slot_bytes = (size_t)TRV_R * TRV_CTHREADS * (32 + 4);
-    const int upw = (32 / v.K) * v.K, tile_pats = TRV_CWARPS * upw * TRV_R / v.K, spad = (tile_pats + 15 + 15) & ~15;
     /* ring depth: 8 stages when they fit beside the slots the schedule is likely to need, else 4, else 2 */
     /* the root branch rides along when the caller asked for it (lkcuda_partial_batch_lnl), this is the list's last piece, the leaf end
        is a tip and the shape is DNA + 4 categories; whether the LAST scheduled node is the branch's inner end is checked below */
-    bool fuse = e->fuse_state == 2 && v.K == 4 && v.SU < 32 && LKCUDA_IS_TIP(e->fuse_dad) && v.NP > 0;
+    bool fuse = TRV_R_ARENA <= 4 && e->fuse_state == 2 && v.K == 4 && v.SU < 32 && LKCUDA_IS_TIP(e->fuse_dad) && v.NP > 0;
+    /* units per thread: children that are vectors of EARLIER launches are streamed from the arena, and a list made of those runs better
+       with fewer units per thread (see TRV_R) */
+    int narena = 0;
+    {
+        std::vector<char> &made = e->trav_mark;
+        if ((int)made.size() < e->cfg.nvec) made.assign(e->cfg.nvec, 0);
+        for (int j = 0; j < nops; j++) made[ops[j].dst] = 1;
+        for (int j = 0; j < nops; j++) {
+            if (ops[j].left >= 0 && !made[ops[j].left]) narena++;
+            if (ops[j].right >= 0 && !made[ops[j].right]) narena++;
+        }
+        for (int j = 0; j < nops; j++) made[ops[j].dst] = 0;
+    }
+    const int R = (fuse || TRV_R == TRV_R_ARENA || 8 * narena > nops) ? TRV_R_ARENA : TRV_R;
+    const size_t slot_bytes = (size_t)R * TRV_CTHREADS * (32 + 4);
+    const int upw = (32 / v.K) * v.K, tile_pats = TRV_CWARPS * upw * R / v.K, spad = (tile_pats + 15 + 15) & ~15;
     const size_t other = (size_t)v.K * S4_MPAD * 8 + 2 * TRV_MAX_STAGES * 8 + 128 + (fuse ? TRV_ROOT_SMEM : 0);
     const size_t stage_b = (size_t)trv_stage_bytes(cbs, spad);
     int stage_shift = 3;
@@ -861,17 +1031,18 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
 
     /* work is dealt in SLICES (one unit per consumer thread = slice_pats patterns): every CTA runs nfull rounds of TRV_R slices and
        one last round of ract_last <= TRV_R slices, so the cost of the launch is ceil-ed to one slice per CTA, not to one whole tile */
-    const int slice_pats = tile_pats / TRV_R;
+    const int slice_pats = tile_pats / R;
     const long long nslices = (v.NP + slice_pats - 1) / slice_pats;
     long long grid = e->num_sms;      /* one persistent CTA per SM (384 threads, shared memory bound) */
     if (grid > nslices) grid = nslices;
-    const int nfull = (int)(nslices / (TRV_R * grid));
-    const long long rem = nslices - (long long)nfull * TRV_R * grid;
+    const int nfull = (int)(nslices / (R * grid));
+    const long long rem = nslices - (long long)nfull * R * grid;
     const int ract_last = (int)((rem + grid - 1) / grid);
     const size_t sm = (size_t)sch.nslots * slot_bytes + fixed;
     if (e->trav_smem_set != LK_MAX_DYN_SMEM) {
-        LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
-        LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
+        LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel<TRV_R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
+        LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel<TRV_R_ARENA, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
+        LK_CUDA(e, cudaFuncSetAttribute(traverse_s4_kernel<TRV_R_ARENA, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LK_MAX_DYN_SMEM));
         e->trav_smem_set = LK_MAX_DYN_SMEM;
     }
     TravRoot root;
@@ -886,10 +1057,13 @@ static int launch_traverse(lkcuda_engine *e, const lkcuda_partial_op *ops, int n
     /* with a pipelined upload in flight the kernel is NOT ordered after it: its producer polls the per-chunk counter instead */
     const unsigned int *flag = e->upload_pending ? e->d_upload_flag : NULL;
     if (root.on)
-        traverse_s4_kernel<true><<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, nfull, ract_last,
+        traverse_s4_kernel<TRV_R_ARENA, true><<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, nfull, ract_last,
                                                                                 flag, e->upload_base, e->upload_chunk_pat > 0 ? e->upload_chunk_pat : 1, root);
+    else if (R == TRV_R_ARENA)
+        traverse_s4_kernel<TRV_R_ARENA, false><<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, nfull, ract_last,
+                                                                                                flag, e->upload_base, e->upload_chunk_pat > 0 ? e->upload_chunk_pat : 1, root);
     else
-        traverse_s4_kernel<false><<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, nfull, ract_last,
+        traverse_s4_kernel<TRV_R, false><<<(unsigned)grid, TRV_THREADS, sm, e->stream>>>(e->v, d, nops, upw, sch.nslots, cbs, spad, stage_shift, nfull, ract_last,
                                                                                  flag, e->upload_base, e->upload_chunk_pat > 0 ? e->upload_chunk_pat : 1, root);
     return launch_end(e, KIND_PARTIAL, bytes, "traverse_s4_kernel");
 }

@@ -142,11 +142,6 @@ __device__ __forceinline__ void contract2(double (&a0)[MM_NT][2], const double (
     }
 }
 
-__device__ __forceinline__ double2 ld_coherent128(const double *p) {
-    double2 r;
-    asm volatile("ld.global.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p) : "memory");
-    return r;
-}
 __device__ __forceinline__ void st_stream128(double *p, double x, double y) {
     asm volatile("st.global.L1::no_allocate.v2.f64 [%0], {%1,%2};" :: "l"(p), "d"(x), "d"(y) : "memory");
 }

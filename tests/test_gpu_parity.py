@@ -3,6 +3,8 @@ reference AND against the CPU oracle on the same inputs."""
 import os
 import sys
 
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
 import numpy as np
 import pytest
 
@@ -382,3 +384,26 @@ def test_fused_root_branch_variant(cuda_lib):
                        env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1500, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     assert r.returncode == 0, r.stdout[-3000:]
     assert " passed" in r.stdout
+
+
+@pytest.mark.gpu
+def test_traversal_writes_every_pattern_of_every_vector(cuda_lib, monkeypatch):
+    """Coverage of the whole-traversal kernel on NaN-poisoned engines (tests/conftest.py sets LKCUDA_POISON): after ONE full traversal of a
+    fresh engine no arena vector may hold a NaN row - a pattern no warp wrote, or one written through a ring stage that had already been
+    refilled (the hole DESIGN 3.1 describes) - and the bits of all vectors must not depend on the run or on how many shared-memory slots
+    the schedule got (slot, register and arena-read paths compute the same bits)."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import trv_probe
+    big = trv_probe.shape(100, 250_000)
+    runs = [trv_probe.probe(cuda_lib, *big, 4) for _ in range(3)]
+    for r in runs:
+        assert r["nan_rows"] == 0 and r["vectors"] == 98, r
+        assert r["digest"] == runs[0]["digest"] and r["lnl"] == runs[0]["lnl"], (r, runs[0])
+    small = trv_probe.shape(100, 60_011)
+    ref = trv_probe.probe(cuda_lib, *small, 4)
+    assert ref["nan_rows"] == 0
+    for maxslots in (0, 1, 2):
+        monkeypatch.setenv("LKCUDA_TRV_MAXSLOTS", str(maxslots))
+        r = trv_probe.probe(cuda_lib, *small, 4)
+        assert r["nan_rows"] == 0 and r["digest"] == ref["digest"] and r["lnl"] == ref["lnl"], (maxslots, r, ref)
