@@ -52,6 +52,7 @@ struct PhyloTree::LkCuda {
     bool weights_uploaded;
     std::vector<double> model_cache;    // what the engine currently holds (eval | evec | inv_evec | rate | weight | tip table)
     uint64_t nflush, nops;
+    void *pinned[3];                    // ptn_freq, ptn_invar, _pattern_lh while they are page-locked (lkcuda_host_register)
 };
 
 static void lkCheck(int rc, lkcuda_engine *e, const char *what) {
@@ -81,6 +82,9 @@ void PhyloTree::setLikelihoodKernel(LikelihoodKernel lk) {
 
 void PhyloTree::lkCudaRelease() {
     if (!lk_cuda) return;
+    // the reference frees ptn_freq / ptn_invar / _pattern_lh right after this call (phylotree.cpp:736-746)
+    for (int i = 0; i < 3; i++)
+        if (lk_cuda->engine && lk_cuda->pinned[i]) lkcuda_host_unregister(lk_cuda->engine, lk_cuda->pinned[i]);
     if (lk_cuda->engine) lkcuda_destroy(lk_cuda->engine);
     if (lk_cuda->d_lh) lkcuda_device_free(lk_cuda->device, lk_cuda->d_lh);
     if (lk_cuda->d_sc) lkcuda_device_free(lk_cuda->device, lk_cuda->d_sc);
@@ -127,6 +131,7 @@ void PhyloTree::lkCudaPrepareArena() {
         lk_cuda->nstates = S; lk_cuda->nblocks = K; lk_cuda->neigen = nmix; lk_cuda->ntaxa = ntaxa; lk_cuda->flags = flags;
         lk_cuda->nptn = P; lk_cuda->nunobs = U; lk_cuda->nodeNum = nodeNum; lk_cuda->leafNum = leafNum; lk_cuda->mem_save = params->lh_mem_save;
         lk_cuda->weights_uploaded = false; lk_cuda->nflush = lk_cuda->nops = 0;
+        lk_cuda->pinned[0] = lk_cuda->pinned[1] = lk_cuda->pinned[2] = NULL;
         lk_cuda->tip_partial_lh_size = (size_t)S * (aln->STATE_UNKNOWN + 1) * nmix;
         lk_cuda->tip_partial_lh = aligned_alloc<double>(lk_cuda->tip_partial_lh_size);
 
@@ -165,7 +170,17 @@ void PhyloTree::lkCudaPrepareArena() {
 
 /* after the recursion: it pointed tip_partial_lh behind the last vector of the (device) arena, phylotree.cpp:886-894 */
 void PhyloTree::lkCudaAfterInit() {
-    if (lk_cuda) tip_partial_lh = lk_cuda->tip_partial_lh;
+    if (!lk_cuda) return;
+    tip_partial_lh = lk_cuda->tip_partial_lh;
+    // the per-pattern host arrays live until deleteAllPartialLh (phylotree.cpp:683-693): page-locked, the re-upload of ptn_freq / ptn_invar
+    // after every clearAllPartialLH (phylotree.cpp:499) and the fetch of _pattern_lh run at PCIe speed.  Best effort: a refusal is ignored.
+    void *arr[3] = {ptn_freq, ptn_invar, _pattern_lh};
+    const size_t bytes[3] = {lk_cuda->nptn * sizeof(double), (lk_cuda->nptn + lk_cuda->nunobs) * sizeof(double), lk_cuda->nptn * sizeof(double)};
+    for (int i = 0; i < 3; i++) {
+        if (lk_cuda->pinned[i] == arr[i]) continue;
+        if (lk_cuda->pinned[i]) { lkcuda_host_unregister(lk_cuda->engine, lk_cuda->pinned[i]); lk_cuda->pinned[i] = NULL; }
+        if (arr[i] && bytes[i] >= (1u << 20) && lkcuda_host_register(lk_cuda->engine, arr[i], bytes[i]) == LKCUDA_OK) lk_cuda->pinned[i] = arr[i];
+    }
 }
 
 int PhyloTree::lkCudaScaleNumBytes() {

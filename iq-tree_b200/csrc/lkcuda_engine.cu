@@ -335,6 +335,25 @@ int lkcuda_device_free(int32_t device, void *ptr) {
     return LKCUDA_OK;
 }
 
+int lkcuda_host_register(lkcuda_engine *e, void *ptr, uint64_t bytes) {
+    LK_ENTER(e);
+    if (!ptr || !bytes) return fail(e, LKCUDA_ERR_ARG, "lkcuda_host_register: null array");
+    cudaError_t rc = cudaHostRegister(ptr, (size_t)bytes, cudaHostRegisterDefault);
+    if (rc == cudaErrorHostMemoryAlreadyRegistered) { cudaGetLastError(); return LKCUDA_OK; }
+    if (rc != cudaSuccess) { cudaGetLastError(); return cuda_fail(e, rc, "cudaHostRegister"); }
+    return LKCUDA_OK;
+}
+
+int lkcuda_host_unregister(lkcuda_engine *e, void *ptr) {
+    LK_ENTER(e);
+    if (!ptr) return LKCUDA_OK;
+    LK_CUDA(e, cudaStreamSynchronize(e->stream));
+    cudaError_t rc = cudaHostUnregister(ptr);
+    if (rc == cudaErrorHostMemoryNotRegistered) { cudaGetLastError(); return LKCUDA_OK; }
+    if (rc != cudaSuccess) { cudaGetLastError(); return cuda_fail(e, rc, "cudaHostUnregister"); }
+    return LKCUDA_OK;
+}
+
 int lkcuda_arena_layout(const lkcuda_engine *e, int64_t *vec_stride, int64_t *scale_stride) {
     if (!e) return LKCUDA_ERR_ARG;
     if (vec_stride) *vec_stride = e->v.vec_stride;

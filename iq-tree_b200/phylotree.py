@@ -39,6 +39,8 @@ LKCUDA_SYMBOLS = {
     "lkcuda_memory_bytes": (C.c_int, [C.c_void_p, c_uint64_p]),
     "lkcuda_device_malloc": (C.c_int, [C.c_int32, C.c_uint64, C.POINTER(C.c_void_p)]),
     "lkcuda_device_free": (C.c_int, [C.c_int32, C.c_void_p]),
+    "lkcuda_host_register": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "lkcuda_host_unregister": (C.c_int, [C.c_void_p, C.c_void_p]),
     "lkcuda_arena_layout": (C.c_int, [C.c_void_p, c_int64_p, c_int64_p]),
     "lkcuda_attach_arena": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int32]),
     "lkcuda_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -130,6 +130,8 @@ int lkcuda_device_malloc(int32_t device, uint64_t bytes, void **ptr) {
     return LKCUDA_OK;
 }
 int lkcuda_device_free(int32_t device, void *ptr) { (void)device; free(ptr); return LKCUDA_OK; }
+int lkcuda_host_register(lkcuda_engine *e, void *ptr, uint64_t bytes) { (void)bytes; return e && ptr ? LKCUDA_OK : LKCUDA_ERR_ARG; }
+int lkcuda_host_unregister(lkcuda_engine *e, void *ptr) { (void)ptr; return e ? LKCUDA_OK : LKCUDA_ERR_ARG; }
 int lkcuda_arena_layout(const lkcuda_engine *e, int64_t *vec_stride, int64_t *scale_stride) {
     if (!e) return LKCUDA_ERR_ARG;
     if (vec_stride) *vec_stride = (int64_t)e->vec_stride;

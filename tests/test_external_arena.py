@@ -66,3 +66,37 @@ def test_shared_arena_oracle(oracle_lib):
 @pytest.mark.gpu
 def test_shared_arena_cuda(cuda_lib):
     _shared_arena_roundtrip(cuda_lib)
+
+
+@pytest.mark.gpu
+def test_page_locked_host_arrays(cuda_lib):
+    """lkcuda_host_register / lkcuda_host_unregister (the binding page-locks ptn_freq / ptn_invar / _pattern_lh): same results from a
+    registered array, idempotent, and unregistering an unknown pointer is not an error"""
+    import ctypes as C
+    g = gu.Golden("dna_example_gtr_i_g4")
+    t = gu.build_tree(g, cuda_lib)
+    t.initializeAllPartialLh()
+    lnl = t.computeLikelihood()
+    e = t.engine(0)
+    P = g.meta["nptn"]
+    freq = np.ascontiguousarray(g["ptn_freq"], dtype=np.float64).copy()
+    invar = np.ascontiguousarray(t.ptnInvar()[:P]).copy()
+    plh = np.zeros(P)
+    dp = C.POINTER(C.c_double)
+    for a in (freq, invar, plh):
+        assert cuda_lib.lkcuda_host_register(e, a.ctypes.data, a.nbytes) == 0, cuda_lib.lkcuda_last_error(e)
+    assert cuda_lib.lkcuda_host_register(e, freq.ctypes.data, freq.nbytes) == 0          # already registered: fine
+    assert cuda_lib.lkcuda_set_pattern_weights(e, freq.ctypes.data_as(dp), invar.ctypes.data_as(dp)) == 0
+    t.clearAllPartialLH()
+    assert t.computeLikelihood() == lnl
+    assert cuda_lib.lkcuda_fetch_pattern_lh(e, plh.ctypes.data_as(dp)) == 0
+    assert np.all(np.isfinite(plh)) and np.all(plh < 0)
+    # half the weight on every pattern: half the log-likelihood (no +ASC in this fixture)
+    half = freq * 0.5
+    assert cuda_lib.lkcuda_set_pattern_weights(e, half.ctypes.data_as(dp), invar.ctypes.data_as(dp)) == 0
+    t.clearAllPartialLH()
+    assert abs(t.computeLikelihood() - 0.5 * lnl) <= 1e-12 * abs(lnl)
+    for a in (freq, invar, plh):
+        assert cuda_lib.lkcuda_host_unregister(e, a.ctypes.data) == 0
+    assert cuda_lib.lkcuda_host_unregister(e, half.ctypes.data) == 0                     # never registered: fine
+    t.close()
