@@ -38,7 +38,10 @@ using namespace lkc;
 #endif
 #define MM_CTHREADS (MM_CWARPS * 32)
 #define MM_THREADS (MM_CTHREADS + 32)
-#define MM_TP (MM_CWARPS * 8)   /* patterns per tile: one 8-pattern group per consumer warp */
+#ifndef MM_G
+#define MM_G 1                  /* 8-pattern groups per consumer warp: they share the B fragments of every contraction */
+#endif
+#define MM_TP (MM_CWARPS * 8 * MM_G)   /* patterns per tile */
 #define MM_STAGES 2
 #define MM_MAXK 4
 #define MM_ROW 24               /* doubles per (state, k) row of a staged tip table */
@@ -106,28 +109,39 @@ __device__ __forceinline__ void dmma(double &d0, double &d1, double a, double b)
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
-/* acc[rt][c] += sum over k-steps (ct, cc) of X[ct][cc] * frag[rt][ct][cc]   (frag: this lane's column of a fragment-ordered matrix).
-   The k-steps run in the OUTER loop: the three accumulator tiles are independent chains, and the asm statements keep their program
+/* acc[gi][rt][c] += sum over k-steps (ct, cc) of X[gi][ct][cc] * frag[rt][ct][cc]   (frag: this lane's column of a fragment-ordered matrix;
+   gi: the warp's G groups of 8 patterns, which share every B fragment - one LDS.64 feeds G DMMAs).
+   The k-steps run in the OUTER loop: the accumulator tiles are independent chains, and the asm statements keep their program
    order, so consecutive DMMAs never wait for each other (with the tiles outside, five dependent DMMAs followed one another) */
-__device__ __forceinline__ void contract(double (&acc)[MM_NT][2], const double (&X)[MM_NT][2], const double *frag) {
+template <int G>
+__device__ __forceinline__ void contract(double (&acc)[G][MM_NT][2], const double (&X)[G][MM_NT][2], const double *frag) {
 #pragma unroll
-    for (int rt = 0; rt < MM_NT; rt++) { acc[rt][0] = 0.0; acc[rt][1] = 0.0; }
+    for (int gi = 0; gi < G; gi++)
+#pragma unroll
+        for (int rt = 0; rt < MM_NT; rt++) { acc[gi][rt][0] = 0.0; acc[gi][rt][1] = 0.0; }
 #pragma unroll
     for (int ct = 0; ct < MM_NT; ct++) {
 #pragma unroll
         for (int cc = 0; cc < 2; cc++) {
             if (ct == MM_NT - 1 && cc == 1) continue;       /* all-padding k-step */
 #pragma unroll
-            for (int rt = 0; rt < MM_NT; rt++) dmma(acc[rt][0], acc[rt][1], X[ct][cc], frag[((rt * MM_NT + ct) * 2 + cc) * 32]);
+            for (int rt = 0; rt < MM_NT; rt++) {
+                const double f = frag[((rt * MM_NT + ct) * 2 + cc) * 32];
+#pragma unroll
+                for (int gi = 0; gi < G; gi++) dmma(acc[gi][rt][0], acc[gi][rt][1], X[gi][ct][cc], f);
+            }
         }
     }
 }
 
-/* the two children's contractions of an internal-internal node, interleaved: six independent chains */
-__device__ __forceinline__ void contract2(double (&a0)[MM_NT][2], const double (&X0)[MM_NT][2], const double *f0,
-                                          double (&a1)[MM_NT][2], const double (&X1)[MM_NT][2], const double *f1) {
+/* the two children's contractions of an internal-internal node, interleaved: 6 G independent chains */
+template <int G>
+__device__ __forceinline__ void contract2(double (&a0)[G][MM_NT][2], const double (&X0)[G][MM_NT][2], const double *f0,
+                                          double (&a1)[G][MM_NT][2], const double (&X1)[G][MM_NT][2], const double *f1) {
 #pragma unroll
-    for (int rt = 0; rt < MM_NT; rt++) { a0[rt][0] = 0.0; a0[rt][1] = 0.0; a1[rt][0] = 0.0; a1[rt][1] = 0.0; }
+    for (int gi = 0; gi < G; gi++)
+#pragma unroll
+        for (int rt = 0; rt < MM_NT; rt++) { a0[gi][rt][0] = 0.0; a0[gi][rt][1] = 0.0; a1[gi][rt][0] = 0.0; a1[gi][rt][1] = 0.0; }
 #pragma unroll
     for (int ct = 0; ct < MM_NT; ct++) {
 #pragma unroll
@@ -135,8 +149,12 @@ __device__ __forceinline__ void contract2(double (&a0)[MM_NT][2], const double (
             if (ct == MM_NT - 1 && cc == 1) continue;
 #pragma unroll
             for (int rt = 0; rt < MM_NT; rt++) {
-                dmma(a0[rt][0], a0[rt][1], X0[ct][cc], f0[((rt * MM_NT + ct) * 2 + cc) * 32]);
-                dmma(a1[rt][0], a1[rt][1], X1[ct][cc], f1[((rt * MM_NT + ct) * 2 + cc) * 32]);
+                const double b0 = f0[((rt * MM_NT + ct) * 2 + cc) * 32], b1 = f1[((rt * MM_NT + ct) * 2 + cc) * 32];
+#pragma unroll
+                for (int gi = 0; gi < G; gi++) {
+                    dmma(a0[gi][rt][0], a0[gi][rt][1], X0[gi][ct][cc], b0);
+                    dmma(a1[gi][rt][0], a1[gi][rt][1], X1[gi][ct][cc], b1);
+                }
             }
         }
     }
@@ -168,6 +186,23 @@ __device__ __forceinline__ void mm_s_st(double *slot, int k, int nt, int pat, in
     double *b = slot + k * (MM_TP * MM_S) + nt * (MM_TP * 8);
     if (nt < 2) *reinterpret_cast<double2 *>(b + pat * 8 + 2 * q) = make_double2(x, y);
     else b[pat * 4 + q] = x;
+}
+
+/* the warp's G pattern groups of block k of a child vector: from its slot, else from the arena */
+template <int G>
+__device__ __forceinline__ void mm_load(double (&X)[G][MM_NT][2], const double *ps, const double *gv, const long long (&p)[G], const int (&pat)[G],
+                                        int B, int k, int q) {
+    if (ps) {
+#pragma unroll
+        for (int gi = 0; gi < G; gi++)
+#pragma unroll
+            for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_s_ld(ps, k, nt, pat[gi], q); X[gi][nt][0] = a.x; X[gi][nt][1] = a.y; }
+    } else {
+#pragma unroll
+        for (int gi = 0; gi < G; gi++)
+#pragma unroll
+            for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_g_ld(gv + p[gi] * B + k * MM_S, nt, q); X[gi][nt][0] = a.x; X[gi][nt][1] = a.y; }
+    }
 }
 
 /* ring stage: descriptor (64) | child 0 block | child 1 block (cbs doubles each: K fragment matrices or tip table) | states 0 | states 1 */
@@ -218,16 +253,24 @@ __global__ void __launch_bounds__(MM_THREADS, 1) traverse_mma20_kernel(DevView v
         return;
     }
 
-    /* ------------------------------ consumers: warp w owns patterns 8w..8w+7 of the tile ------------------------------ */
-    const int g = lane >> 2, q = lane & 3, pat = warp * 8 + g;
+    /* ------------------------------ consumers: warp w owns MM_G groups of 8 patterns of the tile ------------------------------ */
+    const int g = lane >> 2, q = lane & 3;
+    int pat[MM_G];
+#pragma unroll
+    for (int gi = 0; gi < MM_G; gi++) pat[gi] = (warp * MM_G + gi) * 8 + g;
     const bool zero_guard = (v.flags & LKCUDA_FLAG_ZERO_GUARD) != 0, ignore_invar = (v.flags & LKCUDA_FLAG_SCALE_IGNORES_INVAR) != 0;
     const int B = v.B;
     uint32_t c = 0;
 
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        long long p = tile * MM_TP + pat;
-        const bool valid = p < v.NP;
-        if (!valid) p = v.NP - 1;
+        long long p[MM_G];
+        bool valid[MM_G];
+#pragma unroll
+        for (int gi = 0; gi < MM_G; gi++) {
+            p[gi] = tile * MM_TP + pat[gi];
+            valid[gi] = p[gi] < v.NP;
+            if (!valid[gi]) p[gi] = v.NP - 1;
+        }
         for (int i = 0; i < nops; i++, c++) {
             const uint32_t s = c % MM_STAGES;
             mbar_wait(&full[s], (c / MM_STAGES) & 1);
@@ -239,91 +282,76 @@ __global__ void __launch_bounds__(MM_THREADS, 1) traverse_mma20_kernel(DevView v
             const double *g0 = op->src0_lh, *g1 = op->src1_lh;
             double *const dst_lh = op->dst_lh;
             int16_t *const dst_sc = op->dst_sc;
-            const int st0 = tip0 ? stage[64 + 2 * cbs * 8 + pat] : 0, st1 = tip1 ? stage[64 + 2 * cbs * 8 + MM_TP + 16 + pat] : 0;
-            int sc = 0;
-            if (!tip0) sc += slot0 >= 0 ? ssc[slot0 * MM_TP + pat] : (int)vec_sc(v, src0)[p];
-            if (!tip1) sc += slot1 >= 0 ? ssc[slot1 * MM_TP + pat] : (int)vec_sc(v, src1)[p];
-            int mx = 0, nz = 0;
+            int st0[MM_G], st1[MM_G], sc[MM_G], mx[MM_G], nz[MM_G];
+#pragma unroll
+            for (int gi = 0; gi < MM_G; gi++) {
+                st0[gi] = tip0 ? stage[64 + 2 * cbs * 8 + pat[gi]] : 0;
+                st1[gi] = tip1 ? stage[64 + 2 * cbs * 8 + MM_TP + 16 + pat[gi]] : 0;
+                sc[gi] = 0; mx[gi] = 0; nz[gi] = 0;
+                if (!tip0) sc[gi] += slot0 >= 0 ? ssc[slot0 * MM_TP + pat[gi]] : (int)vec_sc(v, src0)[p[gi]];
+                if (!tip1) sc[gi] += slot1 >= 0 ? ssc[slot1 * MM_TP + pat[gi]] : (int)vec_sc(v, src1)[p[gi]];
+            }
             double *dslot = dst_slot >= 0 ? sl + (size_t)dst_slot * K * MM_TP * MM_S : NULL;
+            const double *ps0 = slot0 >= 0 ? sl + (size_t)slot0 * K * MM_TP * MM_S : NULL;
+            const double *ps1 = slot1 >= 0 ? sl + (size_t)slot1 * K * MM_TP * MM_S : NULL;
 
             for (int k = 0; k < K; k++) {
-                double t[MM_NT][2];
+                double t[MM_G][MM_NT][2];
                 if (!tip0 && !tip1) {
                     /* ---- both children are vectors: load both, contract them together ---- */
-                    double X0[MM_NT][2], X1[MM_NT][2], u[MM_NT][2];
-                    if (slot0 >= 0) {
-                        const double *ps = sl + (size_t)slot0 * K * MM_TP * MM_S;
+                    double X0[MM_G][MM_NT][2], X1[MM_G][MM_NT][2], u[MM_G][MM_NT][2];
+                    mm_load<MM_G>(X0, ps0, g0, p, pat, B, k, q);
+                    mm_load<MM_G>(X1, ps1, g1, p, pat, B, k, q);
+                    contract2<MM_G>(t, X0, blk0 + (size_t)k * MM_FRAG_DOUBLES + lane, u, X1, blk1 + (size_t)k * MM_FRAG_DOUBLES + lane);
 #pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_s_ld(ps, k, nt, pat, q); X0[nt][0] = a.x; X0[nt][1] = a.y; }
-                    } else {
-                        const double *gp = g0 + p * B + k * MM_S;
+                    for (int gi = 0; gi < MM_G; gi++)
 #pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_g_ld(gp, nt, q); X0[nt][0] = a.x; X0[nt][1] = a.y; }
-                    }
-                    if (slot1 >= 0) {
-                        const double *ps = sl + (size_t)slot1 * K * MM_TP * MM_S;
-#pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_s_ld(ps, k, nt, pat, q); X1[nt][0] = a.x; X1[nt][1] = a.y; }
-                    } else {
-                        const double *gp = g1 + p * B + k * MM_S;
-#pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_g_ld(gp, nt, q); X1[nt][0] = a.x; X1[nt][1] = a.y; }
-                    }
-                    contract2(t, X0, blk0 + (size_t)k * MM_FRAG_DOUBLES + lane, u, X1, blk1 + (size_t)k * MM_FRAG_DOUBLES + lane);
-#pragma unroll
-                    for (int nt = 0; nt < MM_NT; nt++) { t[nt][0] *= u[nt][0]; t[nt][1] *= u[nt][1]; }
+                        for (int nt = 0; nt < MM_NT; nt++) { t[gi][nt][0] *= u[gi][nt][0]; t[gi][nt][1] *= u[gi][nt][1]; }
                 } else {
-                /* ---- child 0 ---- */
-                if (tip0) {
-                    const double *row = blk0 + ((size_t)st0 * K + k) * MM_ROW + 2 * q;
+                    /* ---- child 0 ---- */
+                    if (tip0) {
 #pragma unroll
-                    for (int nt = 0; nt < MM_NT; nt++) { const double2 a = *reinterpret_cast<const double2 *>(row + 8 * nt); t[nt][0] = a.x; t[nt][1] = a.y; }
-                } else {
-                    double X[MM_NT][2];
-                    if (slot0 >= 0) {
-                        const double *ps = sl + (size_t)slot0 * K * MM_TP * MM_S;
+                        for (int gi = 0; gi < MM_G; gi++) {
+                            const double *row = blk0 + ((size_t)st0[gi] * K + k) * MM_ROW + 2 * q;
 #pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_s_ld(ps, k, nt, pat, q); X[nt][0] = a.x; X[nt][1] = a.y; }
+                            for (int nt = 0; nt < MM_NT; nt++) { const double2 a = *reinterpret_cast<const double2 *>(row + 8 * nt); t[gi][nt][0] = a.x; t[gi][nt][1] = a.y; }
+                        }
                     } else {
-                        const double *gp = g0 + p * B + k * MM_S;
-#pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_g_ld(gp, nt, q); X[nt][0] = a.x; X[nt][1] = a.y; }
+                        double X[MM_G][MM_NT][2];
+                        mm_load<MM_G>(X, ps0, g0, p, pat, B, k, q);
+                        contract<MM_G>(t, X, blk0 + (size_t)k * MM_FRAG_DOUBLES + lane);
                     }
-                    contract(t, X, blk0 + (size_t)k * MM_FRAG_DOUBLES + lane);
-                }
-                /* ---- child 1 ---- */
-                if (tip1) {
-                    const double *row = blk1 + ((size_t)st1 * K + k) * MM_ROW + 2 * q;
+                    /* ---- child 1 ---- */
+                    if (tip1) {
 #pragma unroll
-                    for (int nt = 0; nt < MM_NT; nt++) { const double2 a = *reinterpret_cast<const double2 *>(row + 8 * nt); t[nt][0] *= a.x; t[nt][1] *= a.y; }
-                } else {
-                    double X[MM_NT][2], u[MM_NT][2];
-                    if (slot1 >= 0) {
-                        const double *ps = sl + (size_t)slot1 * K * MM_TP * MM_S;
+                        for (int gi = 0; gi < MM_G; gi++) {
+                            const double *row = blk1 + ((size_t)st1[gi] * K + k) * MM_ROW + 2 * q;
 #pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_s_ld(ps, k, nt, pat, q); X[nt][0] = a.x; X[nt][1] = a.y; }
+                            for (int nt = 0; nt < MM_NT; nt++) { const double2 a = *reinterpret_cast<const double2 *>(row + 8 * nt); t[gi][nt][0] *= a.x; t[gi][nt][1] *= a.y; }
+                        }
                     } else {
-                        const double *gp = g1 + p * B + k * MM_S;
+                        double X[MM_G][MM_NT][2], u[MM_G][MM_NT][2];
+                        mm_load<MM_G>(X, ps1, g1, p, pat, B, k, q);
+                        contract<MM_G>(u, X, blk1 + (size_t)k * MM_FRAG_DOUBLES + lane);
 #pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) { const double2 a = mm_g_ld(gp, nt, q); X[nt][0] = a.x; X[nt][1] = a.y; }
+                        for (int gi = 0; gi < MM_G; gi++)
+#pragma unroll
+                            for (int nt = 0; nt < MM_NT; nt++) { t[gi][nt][0] *= u[gi][nt][0]; t[gi][nt][1] *= u[gi][nt][1]; }
                     }
-                    contract(u, X, blk1 + (size_t)k * MM_FRAG_DOUBLES + lane);
-#pragma unroll
-                    for (int nt = 0; nt < MM_NT; nt++) { t[nt][0] *= u[nt][0]; t[nt][1] *= u[nt][1]; }
-                }
                 }
                 /* ---- back to state space ---- */
-                double o[MM_NT][2];
-                contract(o, t, sINV + (size_t)k * MM_FRAG_DOUBLES + lane);
-                double *gd = dst_lh + p * B + k * MM_S;
+                double o[MM_G][MM_NT][2];
+                contract<MM_G>(o, t, sINV + (size_t)k * MM_FRAG_DOUBLES + lane);
 #pragma unroll
-                for (int nt = 0; nt < MM_NT; nt++) {
-                    {
-                        const int h0 = __double2hiint(o[nt][0]) & 0x7fffffff, h1 = __double2hiint(o[nt][1]) & 0x7fffffff;
-                        mx = max(mx, max(h0, h1));
-                        nz |= h0 | h1 | __double2loint(o[nt][0]) | __double2loint(o[nt][1]);
-                        if (valid) mm_g_st(gd, nt, q, o[nt][0], o[nt][1]);
-                        if (dslot) mm_s_st(dslot, k, nt, pat, q, o[nt][0], o[nt][1]);
+                for (int gi = 0; gi < MM_G; gi++) {
+                    double *gd = dst_lh + p[gi] * B + k * MM_S;
+#pragma unroll
+                    for (int nt = 0; nt < MM_NT; nt++) {
+                        const int h0 = __double2hiint(o[gi][nt][0]) & 0x7fffffff, h1 = __double2hiint(o[gi][nt][1]) & 0x7fffffff;
+                        mx[gi] = max(mx[gi], max(h0, h1));
+                        nz[gi] |= h0 | h1 | __double2loint(o[gi][nt][0]) | __double2loint(o[gi][nt][1]);
+                        if (valid[gi]) mm_g_st(gd, nt, q, o[gi][nt][0], o[gi][nt][1]);
+                        if (dslot) mm_s_st(dslot, k, nt, pat[gi], q, o[gi][nt][0], o[gi][nt][1]);
                     }
                 }
             }
@@ -331,32 +359,36 @@ __global__ void __launch_bounds__(MM_THREADS, 1) traverse_mma20_kernel(DevView v
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[s]);
             /* ---- scaling (phylokernel.h:380-392, 462-474): lh_max over all k and states of the pattern = the quad's maximum ---- */
-            mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 1)); mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-            nz |= __shfl_xor_sync(0xffffffffu, nz, 1); nz |= __shfl_xor_sync(0xffffffffu, nz, 2);
-            const bool tiny = !(tip0 && tip1) && mx < MM_THR_HI;
-            if (__any_sync(0xffffffffu, tiny)) {
-                /* rare: re-read what this lane just wrote, rescale (or refill), write again */
-                const bool refill = tiny && zero_guard && nz == 0;
-                const bool rescale = tiny && !refill && (ignore_invar || v.invar[p] == 0.0);
-                if (refill || rescale) {
-                    for (int k = 0; k < K; k++) {
-                        double *gd = dst_lh + p * B + k * MM_S;
-                        const double *tu = v.tip + ((long long)v.SU * v.E + v.blk_eigen[k]) * MM_S;
 #pragma unroll
-                        for (int nt = 0; nt < MM_NT; nt++) {
-                            double2 a;
-                            if (refill) a = nt < 2 ? make_double2(tu[8 * nt + 2 * q], tu[8 * nt + 2 * q + 1]) : make_double2(tu[16 + q], 0.0);
-                            else { a = dslot ? mm_s_ld(dslot, k, nt, pat, q) : mm_g_ld(gd, nt, q); a.x *= LK_THR_INV; a.y *= LK_THR_INV; }
-                            if (valid) mm_g_st(gd, nt, q, a.x, a.y);
-                            if (dslot) mm_s_st(dslot, k, nt, pat, q, a.x, a.y);
+            for (int gi = 0; gi < MM_G; gi++) {
+                int m = mx[gi], z = nz[gi];
+                m = max(m, __shfl_xor_sync(0xffffffffu, m, 1)); m = max(m, __shfl_xor_sync(0xffffffffu, m, 2));
+                z |= __shfl_xor_sync(0xffffffffu, z, 1); z |= __shfl_xor_sync(0xffffffffu, z, 2);
+                const bool tiny = !(tip0 && tip1) && m < MM_THR_HI;
+                if (__any_sync(0xffffffffu, tiny)) {
+                    /* rare: re-read what this lane just wrote, rescale (or refill), write again */
+                    const bool refill = tiny && zero_guard && z == 0;
+                    const bool rescale = tiny && !refill && (ignore_invar || v.invar[p[gi]] == 0.0);
+                    if (refill || rescale) {
+                        for (int k = 0; k < K; k++) {
+                            double *gd = dst_lh + p[gi] * B + k * MM_S;
+                            const double *tu = v.tip + ((long long)v.SU * v.E + v.blk_eigen[k]) * MM_S;
+#pragma unroll
+                            for (int nt = 0; nt < MM_NT; nt++) {
+                                double2 a;
+                                if (refill) a = nt < 2 ? make_double2(tu[8 * nt + 2 * q], tu[8 * nt + 2 * q + 1]) : make_double2(tu[16 + q], 0.0);
+                                else { a = dslot ? mm_s_ld(dslot, k, nt, pat[gi], q) : mm_g_ld(gd, nt, q); a.x *= LK_THR_INV; a.y *= LK_THR_INV; }
+                                if (valid[gi]) mm_g_st(gd, nt, q, a.x, a.y);
+                                if (dslot) mm_s_st(dslot, k, nt, pat[gi], q, a.x, a.y);
+                            }
                         }
+                        sc[gi] += refill ? 4 : 1;
                     }
-                    sc += refill ? 4 : 1;
                 }
-            }
-            if (q == 0) {
-                if (valid) dst_sc[p] = (int16_t)sc;
-                if (dst_slot >= 0) ssc[dst_slot * MM_TP + pat] = sc;
+                if (q == 0) {
+                    if (valid[gi]) dst_sc[p[gi]] = (int16_t)sc[gi];
+                    if (dst_slot >= 0) ssc[dst_slot * MM_TP + pat[gi]] = sc[gi];
+                }
             }
             /* a parked result is read back by the other lanes of the quad (scale count) and, when spilled, from the arena */
             __syncwarp();
