@@ -137,3 +137,44 @@ def test_noalloc_many_blocks(cuda_lib):
         torch.cuda.synchronize()
         o = out.cpu().numpy()
         assert abs(o[0] - df) <= 1e-11 * abs(df) and abs(o[1] - ddf) <= 1e-11 * abs(ddf), (o, df, ddf)
+
+
+def test_noalloc_oracle_edge_cases(oracle_lib):
+    """CPU: empty input gives zeros; a pattern whose likelihood is 0 makes df NaN/Inf, which the entry point reports as df = ddf = 0 like
+    the reference's derivative kernels (phylokernel.h:647-651)"""
+    ev = np.array([0.0, -1.0, -2.0, -3.0]); rates = np.array([0.5, 1.5]); props = np.array([0.5, 0.5])
+    out = np.full(2, 7.0)
+    one = np.ones(8)
+    rc = oracle_lib.lkcuda_derv_noalloc(0, None, one.ctypes.data, one.ctypes.data, one.ctypes.data, 0, 4, 2, _dp(ev), _dp(rates), _dp(props), 0.1, out.ctypes.data)
+    assert rc == 0 and out[0] == 0.0 and out[1] == 0.0
+    theta = np.zeros((3, 8)); theta[0] = 1e-3; theta[2] = 2e-3          # pattern 1: all zero -> lh = 0 -> 0 / 0
+    freq = np.ones(3); invar = np.zeros(3)
+    rc = oracle_lib.lkcuda_derv_noalloc(0, None, theta.ctypes.data, freq.ctypes.data, invar.ctypes.data, 3, 4, 2, _dp(ev), _dp(rates), _dp(props), 0.1, out.ctypes.data)
+    assert rc == 0 and out[0] == 0.0 and out[1] == 0.0
+    theta[1] = 5e-4
+    rc = oracle_lib.lkcuda_derv_noalloc(0, None, theta.ctypes.data, freq.ctypes.data, invar.ctypes.data, 3, 4, 2, _dp(ev), _dp(rates), _dp(props), 0.1, out.ctypes.data)
+    assert rc == 0 and np.isfinite(out).all() and out[0] < 0.0
+
+
+@pytest.mark.gpu
+def test_noalloc_edge_cases_on_the_device(cuda_lib):
+    """the same edge cases through the CUDA entry point: no pattern -> zeros (no launch), a 0 / 0 pattern -> df = ddf = 0"""
+    import torch
+    dev = torch.device("cuda:0")
+    ev = np.array([0.0, -1.0, -2.0, -3.0]); rates = np.array([0.5, 1.5]); props = np.array([0.5, 0.5])
+    out = torch.full((2,), 7.0, dtype=torch.float64, device=dev)
+    theta = torch.zeros((3, 8), dtype=torch.float64, device=dev); theta[0] = 1e-3; theta[2] = 2e-3
+    freq = torch.ones(3, dtype=torch.float64, device=dev); invar = torch.zeros(3, dtype=torch.float64, device=dev)
+    call = lambda n: cuda_lib.lkcuda_derv_noalloc(0, None, theta.data_ptr(), freq.data_ptr(), invar.data_ptr(), n, 4, 2, _dp(ev), _dp(rates), _dp(props), 0.1, out.data_ptr())
+    assert call(0) == 0
+    torch.cuda.synchronize()
+    assert out.cpu().tolist() == [0.0, 0.0]
+    out.fill_(7.0)
+    assert call(3) == 0
+    torch.cuda.synchronize()
+    assert out.cpu().tolist() == [0.0, 0.0]
+    theta[1] = 5e-4
+    assert call(3) == 0
+    torch.cuda.synchronize()
+    o = out.cpu().numpy()
+    assert np.isfinite(o).all() and o[0] < 0.0
