@@ -166,7 +166,7 @@ __host__ __device__ __forceinline__ int trv_stage_bytes(int cbs, int spad) { ret
 #endif
 /* How a consumer warp hands a ring stage back.  On sm_100a mbarrier.arrive does not wait for an earlier LDS of the same warp that is still
    in flight, and ptxas adds no scoreboard wait: the producer's next bulk copy can replace the stage under the load.  Measured (round 2,
-   profiles/r2_s44..s46): with the descriptor words dst_lh / dst_sc loaded two instructions before the arrive, whole warps stored a node's
+   profiles/r2_s44_traverse_stage_release_race.txt): with the descriptor words dst_lh / dst_sc loaded two instructions before the arrive, whole warps stored a node's
    result through the descriptor of the node that got the stage next (8 patterns x R slices of NaN in the poisoned arena, a few per 1M x 98
    nodes) as soon as the code in front of the arrive was LDS-heavy (TRV_FORM 1); the shipped form had the same instruction pair and was only
    luckier.  1 (shipped): the barrier address depends on the words loaded last, so the arrive cannot issue before the stage reads are in
