@@ -138,6 +138,25 @@ def measured_fp64_peak():
     return None
 
 
+def measured_write_peak(gb=8.0):
+    """Ceiling of a WRITE-ONLY HBM stream on THIS box in THIS run (tools/write_peak.cu: the traversal kernel's 256-bit streaming store from
+    148 x 4 CTAs): the DNA traversal writes 99 % of its DRAM traffic, the copy figure of MEASURED_PEAKS.json is half reads"""
+    exe = os.path.join(ROOT, "tools", "write_peak")
+    if not os.path.exists(exe):
+        return None
+    try:
+        r = subprocess.run([exe, str(gb)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=120)
+        best = None
+        for line in r.stdout.split("\n"):
+            if line.startswith("{"):
+                d = json.loads(line)
+                if d["kernel"].startswith("st.v4.f64"):
+                    best = d["best_gbps"] if best is None else max(best, d["best_gbps"])
+        return best
+    except Exception:
+        return None
+
+
 # ------------------------------------------------------------------ files for the reference binaries ------------------------------------------------------------------
 
 def write_phylip(path, names, states, alphabet):
@@ -633,6 +652,12 @@ def main():
             "kernels": kinds,
             "clocks": clocks,
         }
+        if world == 1 and not args.no_cpu_baseline:
+            wp = measured_write_peak()
+            if wp:
+                line["roofline"]["write_only_peak"] = wp
+                line["roofline"]["frac_of_write_only_peak"] = model_gbps / wp
+                line["roofline"]["write_only_peak_source"] = "tools/write_peak.cu, this run: best of the st.global.v4.f64 streams over 8 GB (the kernel's own store instruction)"
         if oab_ms is not None:
             line["optimize_all_branches_1"] = {"ms": oab_ms, "lnl": oab_lnl, "branches": 2 * NTAXA - 3, "through": "harness driver (host-driven Newton steps, one launch per evaluation)"}
         if not args.no_cpu_baseline and world == 1:

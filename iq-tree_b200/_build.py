@@ -108,6 +108,18 @@ def build_tools(force=False):
     return exe
 
 
+def build_write_peak(force=False):
+    """tools/write_peak: ceiling of a write-only HBM stream issued with the DNA traversal kernel's store (bench.py: roofline.write_only_peak)"""
+    src, exe = os.path.join(ROOT, "tools", "write_peak.cu"), os.path.join(ROOT, "tools", "write_peak")
+    if not force and not _newer(exe, [src]):
+        return exe
+    nvcc = nvcc_path()
+    if nvcc is None:
+        return exe if os.path.exists(exe) else None
+    _run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-o", exe, src])
+    return exe
+
+
 def build_harness(force=False):
     """TEST / BENCH DRIVER: the C++ mirror of the reference's PhyloTree call sequences, linked against the product library."""
     cuda = build_cuda()
